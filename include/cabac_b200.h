@@ -1,0 +1,295 @@
+/*
+ * cabac_b200.h - C ABI of the B200-native VVC CABAC engine.
+ *
+ * This is the drop-in boundary for the entropy-coding hot path of
+ * p-sawicki/entropy_coding (reference paths below are relative to that repo):
+ *
+ *   (1) the arithmetic coder    src/entropy_codec/arith_codec.{hpp,cpp}
+ *   (2) the probability models  src/common/contexts.{hpp,cpp}
+ *   (3) residual binarisation   src/entropy_codec/cabac_{writer,reader}.cpp
+ *                               src/common/context_modelling.{hpp,cpp}
+ *
+ * Plain C: pointers and sizes only, no C++/torch types.  Every entry point
+ * exists in two flavours:
+ *   - `*_dev`  : all buffer arguments are DEVICE pointers, the launch is
+ *                asynchronous on the handle's CUDA stream (call cabac_sync);
+ *   - no suffix: all buffer arguments are HOST pointers; the call copies
+ *                inputs H2D, launches, copies results D2H and synchronises.
+ * There is no CPU fallback: without a CUDA device every call fails with
+ * CABAC_ERR_CUDA.
+ *
+ * One independent substream (slice, tile, WPP CTU row, all-intra frame) is
+ * coded by one warp.  Batches of 10^4..10^6 substreams per launch are the
+ * design point.
+ */
+#ifndef CABAC_B200_H
+#define CABAC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Ctx::NumberOfContexts, src/common/contexts.cpp:773-774 */
+#define CABAC_NUM_CTX 379
+
+/* ---- status codes (returned by every call) ------------------------------ */
+enum {
+  CABAC_OK = 0,
+  CABAC_ERR_CUDA = -1,     /* CUDA runtime failure; see cabac_last_error() */
+  CABAC_ERR_ARG = -2,      /* bad argument                                  */
+  CABAC_ERR_SUBSTREAM = -3 /* >=1 substream failed; see the status[] array  */
+};
+
+/* ---- per-substream status bits (status[] output arrays) ----------------- */
+/* Mirror the reference's CHECK/THROW sites (src/common/type_def.hpp:295-329). */
+enum {
+  CABAC_SS_OK = 0,
+  CABAC_SS_OUT_OVERFLOW = 1, /* output capacity exhausted (bytes truncated)  */
+  CABAC_SS_EMPTY_TU = 2,     /* "Coefficient coding called for empty TU",
+                                cabac_writer.cpp:2457                        */
+  CABAC_SS_BAD_CMD = 4,      /* malformed command word                       */
+  CABAC_SS_IN_OVERRUN = 8,   /* decoder read past the substream's bytes,
+                                bit_stream.cpp:269                           */
+  CABAC_SS_COEFF_RANGE = 16, /* "TransCoeffLevel outside allowable range",
+                                cabac_reader.cpp:2942-2946                   */
+  CABAC_SS_NO_TERMINATE = 32 /* terminating bin / stop pattern missing,
+                                arith_codec.cpp:68-73                        */
+};
+
+/* ---- probability model as exchanged over the boundary ------------------- */
+/* BinProbModel_Std::m_state[0..1], contexts.hpp:184-190.  The rate
+ * (m_rate) is a per-context-index constant (row [3] of the init tables,
+ * contexts.cpp:1012) and is exported once by cabac_ctx_rates().            */
+typedef struct cabac_ctx_model {
+  uint16_t state0; /* 10 significant bits, MASK_0 = 0x7FE0 */
+  uint16_t state1; /* 14 significant bits, MASK_1 = 0x7FFE */
+} cabac_ctx_model;
+
+/* ---- per-substream parameters ------------------------------------------- */
+enum {
+  CABAC_SUB_DEP_QUANT = 1,   /* Slice::getDepQuantEnabledFlag()              */
+  CABAC_SUB_SIGN_HIDING = 2, /* Slice::getSignDataHidingEnabledFlag()        */
+  CABAC_SUB_TSRC_DISABLED = 4, /* Slice::getTSResidualCodingDisabledFlag()   */
+  CABAC_SUB_TERMINATE = 8,   /* after the last unit: encodeBinTrm(1) +
+                                finish() (end_of_slice, cabac_writer.cpp:104)
+                                / decode: terminating_bit + finish check     */
+  CABAC_SUB_ALIGN = 16,      /* encode: append writeByteAlignment()
+                                (bit_stream.cpp:152-155, EncSlice.cpp:2114)  */
+  CABAC_SUB_CTX_IN = 32      /* start from ctx_in[] instead of Ctx::init     */
+};
+
+typedef struct cabac_substream_params {
+  int8_t qp;       /* slice QP, clipped to 0..63 as CtxStore::init does      */
+  uint8_t init_id; /* 0 = B, 1 = P, 2 = I table (type_def.hpp:22-25)         */
+  uint8_t flags;   /* CABAC_SUB_*                                            */
+  uint8_t reserved;
+} cabac_substream_params;
+
+/* ---- bin-level command words (BinEncIf / BinDecoderBase calls) ---------- */
+/* One 32-bit word per call recorded from arith_codec.hpp:53-59 / 238-246.
+ *   bits 31..29 kind
+ *   CTX   : bit 9 = bin, bits 8..0 = ctxId        encodeBin / decodeBin
+ *   EP    : bits 28..24 = n (0..24), 23..0 = bins encodeBinsEP / decodeBinsEP
+ *           (encodeBinEP(b) == EP with n = 1; longer runs are split by the
+ *            recorder, which is arithmetically identical)
+ *   REM   : bits 28..24 = rice, 23..0 = value     encodeRemAbsEP(v, rice, 5, 15)
+ *   TRM   : bit 0 = bin                           encodeBinTrm / decodeBinTrm
+ *   ALIGN :                                       align()  (m_Range = 256)
+ */
+enum {
+  CABAC_CMD_CTX = 0,
+  CABAC_CMD_EP = 1,
+  CABAC_CMD_REM = 2,
+  CABAC_CMD_TRM = 3,
+  CABAC_CMD_ALIGN = 4
+};
+#define CABAC_CMD_KIND(w) ((uint32_t)(w) >> 29)
+#define CABAC_MK_CTX(ctx, bin) \
+  (((uint32_t)CABAC_CMD_CTX << 29) | (((uint32_t)(bin) & 1u) << 9) | ((uint32_t)(ctx) & 511u))
+#define CABAC_MK_EP(bins, n) \
+  (((uint32_t)CABAC_CMD_EP << 29) | (((uint32_t)(n) & 31u) << 24) | ((uint32_t)(bins) & 0xFFFFFFu))
+#define CABAC_MK_REM(value, rice) \
+  (((uint32_t)CABAC_CMD_REM << 29) | (((uint32_t)(rice) & 31u) << 24) | ((uint32_t)(value) & 0xFFFFFFu))
+#define CABAC_MK_TRM(bin) (((uint32_t)CABAC_CMD_TRM << 29) | ((uint32_t)(bin) & 1u))
+#define CABAC_MK_ALIGN() ((uint32_t)CABAC_CMD_ALIGN << 29)
+
+/* ---- flat transform-unit descriptor (residual level) --------------------- */
+/* Replaces the (TransformUnit&, ComponentID) argument pair of
+ * CABACWriter::residual_coding (cabac_writer.hpp:128-129) and
+ * CABACReader::residual_coding (cabac_reader.hpp:111).                      */
+enum {
+  CABAC_TU_TS = 1,          /* tu.mtsIdx[comp] == MTS_SKIP  (encode input)   */
+  CABAC_TU_TS_ALLOWED = 2,  /* TU::isTSAllowed() -> transform_skip_flag is
+                               coded (unit_tools.cpp:651-664)                */
+  CABAC_TU_BDPCM = 4,       /* cu.bdpcmMode / bdpcmModeChroma for this comp  */
+  CABAC_TU_SBT_ZEROOUT = 8  /* sps.getUseMTS() && cu.sbtInfo != 0 (luma):
+                               32-sized dims are zeroed beyond 16
+                               (cabac_writer.cpp:2508-2517, 2661-2667)       */
+};
+
+typedef struct cabac_tu_desc {
+  uint64_t coeff_offset; /* first TCoeff (int32) of the block in the slab;
+                            row-major, stride == width (unit.hpp:551)        */
+  uint8_t log2_w;        /* width  = 1 << log2_w, 2..64                      */
+  uint8_t log2_h;        /* height = 1 << log2_h, 2..64                      */
+  uint8_t comp_id;       /* 0 = Y, 1 = Cb, 2 = Cr                            */
+  uint8_t flags;         /* CABAC_TU_*                                       */
+  uint32_t reserved;
+} cabac_tu_desc;
+
+/* Per-TU result flags (side effects of residual_coding on CUCtx / tu,
+ * cabac_writer.cpp:2460-2478, 2520-2523; cabac_reader.cpp:2672-2690, 2751). */
+enum {
+  CABAC_TUR_TS = 1,               /* decoded transform_skip_flag             */
+  CABAC_TUR_VIOLATES_LFNST = 2,   /* violatesLfnstConstrained[chType]        */
+  CABAC_TUR_LFNST_LAST_POS = 4,   /* lfnstLastScanPos                        */
+  CABAC_TUR_MTS_LAST_POS = 8,     /* mtsLastScanPos                          */
+  CABAC_TUR_VIOLATES_MTS = 16     /* violatesMtsCoeffConstraint              */
+};
+
+typedef struct cabac_handle cabac_handle;
+
+/* ---- lifetime ------------------------------------------------------------ */
+/* device < 0 selects the current CUDA device.  Returns NULL on failure.     */
+cabac_handle *cabac_create(int device);
+void cabac_destroy(cabac_handle *h);
+/* Use an externally owned CUDA stream (cudaStream_t as void*); NULL restores
+ * the handle's own stream.                                                  */
+int cabac_set_stream(cabac_handle *h, void *cuda_stream);
+int cabac_sync(cabac_handle *h);
+const char *cabac_last_error(cabac_handle *h);
+const char *cabac_version(void);
+/* Number of kernel launches issued through this handle so far.              */
+uint64_t cabac_launch_count(cabac_handle *h);
+
+/* ---- (2) context initialisation ----------------------------------------- */
+/* Ctx::init(qp, initId) for n (qp, init_id) pairs, contexts.cpp:996-1015,
+ * 893-901.  out: n * CABAC_NUM_CTX models.                                   */
+int cabac_ctx_init(cabac_handle *h, const cabac_substream_params *params,
+                   size_t n, cabac_ctx_model *out);
+int cabac_ctx_init_dev(cabac_handle *h, const cabac_substream_params *params,
+                       size_t n, cabac_ctx_model *out);
+/* m_rate of every context index (host memory, CABAC_NUM_CTX bytes);
+ * BinProbModel_Std::setLog2WindowSize, contexts.cpp:915-920.                 */
+int cabac_ctx_rates(uint8_t *rates_out);
+/* Raw init table row (0=B,1=P,2=I,3=window sizes), CABAC_NUM_CTX bytes.     */
+int cabac_ctx_init_table(int row, uint8_t *table_out);
+
+/* ---- (1) bin-level arithmetic coder -------------------------------------- */
+/* Encodes n_sub recorded command streams.  Substream i owns command words
+ * cmds[cmd_offsets[i] .. cmd_offsets[i+1]) and output bytes
+ * out[out_offsets[i] .. out_offsets[i+1]) (its capacity).
+ *   out_sizes[i]  bytes produced (incl. finish/alignment when flagged)
+ *   num_bins[i]   BinCounter::getAll(), arith_codec.cpp:302-308   (optional)
+ *   ctx_in        n_sub*CABAC_NUM_CTX models, used when CABAC_SUB_CTX_IN
+ *   ctx_out       n_sub*CABAC_NUM_CTX models after the run       (optional)
+ *   status[i]     CABAC_SS_* bits                                 (optional)
+ */
+int cabac_encode_bins(cabac_handle *h, const uint32_t *cmds,
+                      const uint64_t *cmd_offsets,
+                      const cabac_substream_params *params, size_t n_sub,
+                      const cabac_ctx_model *ctx_in, uint8_t *out,
+                      const uint64_t *out_offsets, uint32_t *out_sizes,
+                      uint32_t *num_bins, cabac_ctx_model *ctx_out,
+                      uint32_t *status);
+int cabac_encode_bins_dev(cabac_handle *h, const uint32_t *cmds,
+                          const uint64_t *cmd_offsets,
+                          const cabac_substream_params *params, size_t n_sub,
+                          const cabac_ctx_model *ctx_in, uint8_t *out,
+                          const uint64_t *out_offsets, uint32_t *out_sizes,
+                          uint32_t *num_bins, cabac_ctx_model *ctx_out,
+                          uint32_t *status);
+
+/* Decodes with a known call skeleton (the context of every bin is given by
+ * the command words; bin/bins/value payload fields are ignored on input).
+ * values[k] receives the decoded bin / bins / remainder of command k.
+ * Substream i reads bytes in[in_offsets[i] .. in_offsets[i+1]).
+ *   bits_read[i]  BinDecoderBase::getNumBitsRead(), arith_codec.cpp:201-203
+ */
+int cabac_decode_bins(cabac_handle *h, const uint8_t *in,
+                      const uint64_t *in_offsets, const uint32_t *cmds,
+                      const uint64_t *cmd_offsets,
+                      const cabac_substream_params *params, size_t n_sub,
+                      const cabac_ctx_model *ctx_in, uint32_t *values,
+                      uint32_t *bits_read, cabac_ctx_model *ctx_out,
+                      uint32_t *status);
+int cabac_decode_bins_dev(cabac_handle *h, const uint8_t *in,
+                          const uint64_t *in_offsets, const uint32_t *cmds,
+                          const uint64_t *cmd_offsets,
+                          const cabac_substream_params *params, size_t n_sub,
+                          const cabac_ctx_model *ctx_in, uint32_t *values,
+                          uint32_t *bits_read, cabac_ctx_model *ctx_out,
+                          uint32_t *status);
+
+/* ---- (3) residual-level coder ------------------------------------------- */
+/* For each substream i: reset(qp, init_id) [or ctx_in], then
+ * residual_coding() for TUs tus[tu_offsets[i] .. tu_offsets[i+1]) in order,
+ * then (CABAC_SUB_TERMINATE) encodeBinTrm(1) + finish() and
+ * (CABAC_SUB_ALIGN) writeByteAlignment().
+ *   coeffs       the TCoeff (int32) slab the descriptors point into
+ *   n_coeffs     slab length in TCoeff units (bounds the H2D copy)
+ *   tu_flags[t]  CABAC_TUR_* per TU                               (optional)
+ */
+int cabac_encode_residual(cabac_handle *h, const cabac_tu_desc *tus,
+                          const uint64_t *tu_offsets,
+                          const cabac_substream_params *params, size_t n_sub,
+                          const int32_t *coeffs, size_t n_coeffs,
+                          const cabac_ctx_model *ctx_in, uint8_t *out,
+                          const uint64_t *out_offsets, uint32_t *out_sizes,
+                          uint32_t *num_bins, uint8_t *tu_flags,
+                          cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets,
+                              const cabac_substream_params *params,
+                              size_t n_sub, const int32_t *coeffs,
+                              const cabac_ctx_model *ctx_in, uint8_t *out,
+                              const uint64_t *out_offsets, uint32_t *out_sizes,
+                              uint32_t *num_bins, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* Mirror of the above.  The kernel zeroes each TU's coefficient block before
+ * parsing (the reference requires the caller to pre-zero,
+ * cabac_reader.cpp:2952-2953).  descriptor flag CABAC_TU_TS is ignored when
+ * CABAC_TU_TS_ALLOWED is set (the flag is parsed) and otherwise supplies the
+ * inferred value (cabac_reader.cpp:2738-2741).
+ */
+int cabac_decode_residual(cabac_handle *h, const uint8_t *in,
+                          const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                          const uint64_t *tu_offsets,
+                          const cabac_substream_params *params, size_t n_sub,
+                          const cabac_ctx_model *ctx_in, int32_t *coeffs,
+                          size_t n_coeffs, uint32_t *num_bins,
+                          uint32_t *bits_read, uint8_t *tu_flags,
+                          cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in,
+                              const uint64_t *in_offsets,
+                              const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets,
+                              const cabac_substream_params *params,
+                              size_t n_sub, const cabac_ctx_model *ctx_in,
+                              int32_t *coeffs, uint32_t *num_bins,
+                              uint32_t *bits_read, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* ---- substream packing + entry points ------------------------------------ */
+/* Compacts the per-substream output slabs of an encode call into one
+ * contiguous payload in substream order (OutputBitstream::addSubstream for
+ * byte-aligned substreams, bit_stream.cpp:139-150; EncGOP.cpp:3811-3824) and
+ * returns the entry-point table: entry_points[i] = byte offset of substream i
+ * in `packed`, entry_points[n_sub] = total bytes.  packed must hold
+ * sum(out_sizes).  Device pointers; asynchronous.
+ */
+int cabac_pack_dev(cabac_handle *h, const uint8_t *out,
+                   const uint64_t *out_offsets, const uint32_t *out_sizes,
+                   size_t n_sub, uint8_t *packed, uint64_t *entry_points);
+int cabac_pack(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets,
+               const uint32_t *out_sizes, size_t n_sub, uint8_t *packed,
+               size_t packed_cap, uint64_t *entry_points);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CABAC_B200_H */

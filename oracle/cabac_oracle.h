@@ -1,0 +1,39 @@
+/* oracle/cabac_oracle.h - TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * Entry points of the plain-C restatement (cabac_oracle.c).  Signatures are
+ * identical to oracle/ref_driver.cpp's `ref_*` functions so oracle/checker.py
+ * drives both through the same code.
+ */
+#ifndef CABAC_ORACLE_H
+#define CABAC_ORACLE_H
+#include <stdint.h>
+
+#include "cabac_b200.h"
+
+int orc_num_contexts(void);
+void orc_init_table(int row, uint8_t *out);
+void orc_ctx_init(int qp, int initId, cabac_ctx_model *out, uint8_t *rates);
+int orc_scan_table(int log2w, int log2h, uint32_t *out);
+void orc_ctx_offsets(uint32_t *out);
+
+long orc_encode_bins(const uint32_t *cmds, long ncmd, const cabac_substream_params *p,
+                     const cabac_ctx_model *ctxIn, uint8_t *out, long cap, uint32_t *numBins,
+                     cabac_ctx_model *ctxOut);
+long orc_decode_bins(const uint8_t *in, long nbytes, const uint32_t *cmds, long ncmd,
+                     const cabac_substream_params *p, const cabac_ctx_model *ctxIn, uint32_t *values,
+                     cabac_ctx_model *ctxOut, uint32_t *status);
+long orc_encode_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                         const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint8_t *out, long cap,
+                         uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut, int useMTS);
+long orc_decode_residual(const uint8_t *in, long nbytes, const cabac_tu_desc *tus, long ntu,
+                         const cabac_substream_params *p, const cabac_ctx_model *ctxIn, int32_t *coeffs,
+                         uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status, int useMTS);
+double orc_time_encode_residual(const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                const cabac_substream_params *params, long nSub, const int32_t *coeffs,
+                                int nthreads, uint64_t *totalBins, uint64_t *totalBytes, uint8_t *out,
+                                const uint64_t *outOffsets, uint32_t *outSizes);
+double orc_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets, const uint32_t *inSizes,
+                                const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                const cabac_substream_params *params, long nSub, int32_t *coeffs,
+                                int nthreads);
+#endif

@@ -1,0 +1,203 @@
+"""oracle/checker.py - TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes front-ends for the two CPU checkers:
+
+* ``Checker("ref")``    -> oracle/_ref/libcabac_ref.so: the UNMODIFIED reference
+  sources (/root/reference/src) behind oracle/ref_driver.cpp.
+* ``Checker("oracle")`` -> oracle/libcabac_oracle.so: the plain-C restatement
+  (oracle/cabac_oracle.c).
+
+Both export the same entry points (prefix ``ref_`` / ``orc_``).  Only tests/,
+``__graft_entry__.smoke()`` and bench.py's CPU legs may import this module; the
+product package (entropy_coding_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NUM_CTX = 379
+
+# numpy mirrors of include/cabac_b200.h
+PARAMS_DT = np.dtype([("qp", "i1"), ("init_id", "u1"), ("flags", "u1"), ("reserved", "u1")])
+TU_DT = np.dtype(
+    [("coeff_offset", "<u8"), ("log2_w", "u1"), ("log2_h", "u1"), ("comp_id", "u1"),
+     ("flags", "u1"), ("reserved", "<u4")]
+)
+CTX_DT = np.dtype([("state0", "<u2"), ("state1", "<u2")])
+assert PARAMS_DT.itemsize == 4 and TU_DT.itemsize == 16 and CTX_DT.itemsize == 4
+
+SUB_DEP_QUANT, SUB_SIGN_HIDING, SUB_TSRC_DISABLED = 1, 2, 4
+SUB_TERMINATE, SUB_ALIGN, SUB_CTX_IN = 8, 16, 32
+TU_TS, TU_TS_ALLOWED, TU_BDPCM, TU_SBT_ZEROOUT = 1, 2, 4, 8
+CMD_CTX, CMD_EP, CMD_REM, CMD_TRM, CMD_ALIGN = 0, 1, 2, 3, 4
+
+
+def mk_ctx(ctx, b):
+    return (CMD_CTX << 29) | ((b & 1) << 9) | (ctx & 511)
+
+
+def mk_ep(bins, n):
+    return (CMD_EP << 29) | ((n & 31) << 24) | (bins & 0xFFFFFF)
+
+
+def mk_rem(value, rice):
+    return (CMD_REM << 29) | ((rice & 31) << 24) | (value & 0xFFFFFF)
+
+
+def mk_trm(b):
+    return (CMD_TRM << 29) | (b & 1)
+
+
+def mk_align():
+    return CMD_ALIGN << 29
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def lib_path(kind: str) -> str:
+    if kind == "ref":
+        return os.path.join(HERE, "_ref", "libcabac_ref.so")
+    return os.path.join(HERE, "libcabac_oracle.so")
+
+
+def available(kind: str) -> bool:
+    return os.path.exists(lib_path(kind))
+
+
+class Checker:
+    def __init__(self, kind: str = "oracle"):
+        assert kind in ("ref", "oracle")
+        self.kind = kind
+        self.pfx = "ref_" if kind == "ref" else "orc_"
+        path = lib_path(kind)
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} missing: run `make -C oracle` (or __graft_entry__.build())")
+        # The reference's loggers open bin_log.txt / bit_log.txt in the CWD at
+        # static-init time (src/log/log.cpp:3-4): load from a scratch directory.
+        cwd = os.getcwd()
+        with tempfile.TemporaryDirectory() as tmp:
+            os.chdir(tmp)
+            try:
+                self.lib = C.CDLL(path)
+            finally:
+                os.chdir(cwd)
+        for name in ("encode_bins", "decode_bins", "encode_residual", "decode_residual"):
+            getattr(self.lib, self.pfx + name).restype = C.c_long
+        for name in ("time_encode_residual", "time_decode_residual"):
+            getattr(self.lib, self.pfx + name).restype = C.c_double
+
+    def _f(self, name):
+        return getattr(self.lib, self.pfx + name)
+
+    # ---- tables ---------------------------------------------------------
+    def init_table(self, row: int) -> np.ndarray:
+        out = np.zeros(NUM_CTX, np.uint8)
+        self._f("init_table")(C.c_int(row), _ptr(out))
+        return out
+
+    def ctx_init(self, qp: int, init_id: int):
+        out = np.zeros(NUM_CTX, CTX_DT)
+        rates = np.zeros(NUM_CTX, np.uint8)
+        self._f("ctx_init")(C.c_int(qp), C.c_int(init_id), _ptr(out), _ptr(rates))
+        return out, rates
+
+    def scan_table(self, log2w: int, log2h: int):
+        out = np.zeros(1 << (log2w + log2h), np.uint32)
+        r = self._f("scan_table")(C.c_int(log2w), C.c_int(log2h), _ptr(out))
+        return out, r & 255, r >> 8
+
+    def ctx_offsets(self) -> np.ndarray:
+        out = np.zeros(25, np.uint32)
+        self._f("ctx_offsets")(_ptr(out))
+        return out
+
+    # ---- bin level --------------------------------------------------------
+    def encode_bins(self, cmds, qp, init_id, flags=SUB_TERMINATE | SUB_ALIGN, ctx_in=None,
+                    want_ctx=False, cap=None):
+        cmds = np.ascontiguousarray(cmds, np.uint32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        cap = cap or (len(cmds) * 5 + 64)
+        out = np.zeros(cap, np.uint8)
+        nb = np.zeros(1, np.uint32)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        n = self._f("encode_bins")(_ptr(cmds), C.c_long(len(cmds)), _ptr(p), _ptr(ctx_in), _ptr(out),
+                                   C.c_long(cap), _ptr(nb), _ptr(ctx_out))
+        assert 0 <= n <= cap, n
+        res = (out[:n].copy(), int(nb[0]))
+        return res + (ctx_out,) if want_ctx else res
+
+    def decode_bins(self, data, cmds, qp, init_id, flags=SUB_TERMINATE, ctx_in=None, want_ctx=False):
+        data = np.ascontiguousarray(data, np.uint8)
+        cmds = np.ascontiguousarray(cmds, np.uint32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        vals = np.zeros(len(cmds), np.uint32)
+        st = np.zeros(1, np.uint32)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        bits = self._f("decode_bins")(_ptr(data), C.c_long(len(data)), _ptr(cmds), C.c_long(len(cmds)), _ptr(p),
+                                      _ptr(ctx_in), _ptr(vals), _ptr(ctx_out), _ptr(st))
+        res = (vals, int(bits), int(st[0]))
+        return res + (ctx_out,) if want_ctx else res
+
+    # ---- residual level ---------------------------------------------------
+    def encode_residual(self, tus, coeffs, qp, init_id, flags, ctx_in=None, want_ctx=False, cap=None,
+                        use_mts=False):
+        tus = np.ascontiguousarray(tus, TU_DT)
+        coeffs = np.ascontiguousarray(coeffs, np.int32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        cap = cap or (coeffs.size * 5 + 64 * len(tus) + 64)
+        out = np.zeros(cap, np.uint8)
+        nb = np.zeros(1, np.uint32)
+        tuf = np.zeros(len(tus), np.uint8)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        n = self._f("encode_residual")(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in),
+                                       _ptr(out), C.c_long(cap), _ptr(nb), _ptr(tuf), _ptr(ctx_out),
+                                       C.c_int(int(use_mts)))
+        assert 0 <= n <= cap, n
+        res = (out[:n].copy(), int(nb[0]), tuf)
+        return res + (ctx_out,) if want_ctx else res
+
+    def decode_residual(self, data, tus, n_coeffs, qp, init_id, flags, ctx_in=None, want_ctx=False,
+                        use_mts=False):
+        data = np.ascontiguousarray(data, np.uint8)
+        tus = np.ascontiguousarray(tus, TU_DT)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        coeffs = np.zeros(n_coeffs, np.int32)
+        tuf = np.zeros(len(tus), np.uint8)
+        st = np.zeros(1, np.uint32)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        bits = self._f("decode_residual")(_ptr(data), C.c_long(len(data)), _ptr(tus), C.c_long(len(tus)), _ptr(p),
+                                          _ptr(ctx_in), _ptr(coeffs), _ptr(tuf), _ptr(ctx_out), _ptr(st),
+                                          C.c_int(int(use_mts)))
+        res = (coeffs, int(bits), tuf, int(st[0]))
+        return res + (ctx_out,) if want_ctx else res
+
+    # ---- timed batches (CPU baseline) ------------------------------------
+    def time_encode_residual(self, tus, tu_offsets, params, coeffs, nthreads, out=None, out_offsets=None,
+                             out_sizes=None):
+        tus = np.ascontiguousarray(tus, TU_DT)
+        tu_offsets = np.ascontiguousarray(tu_offsets, np.uint64)
+        params = np.ascontiguousarray(params, PARAMS_DT)
+        coeffs = np.ascontiguousarray(coeffs, np.int32)
+        bins = np.zeros(1, np.uint64)
+        nbytes = np.zeros(1, np.uint64)
+        t = self._f("time_encode_residual")(_ptr(tus), _ptr(tu_offsets), _ptr(params), C.c_long(len(params)),
+                                            _ptr(coeffs), C.c_int(nthreads), _ptr(bins), _ptr(nbytes), _ptr(out),
+                                            _ptr(out_offsets), _ptr(out_sizes))
+        return float(t), int(bins[0]), int(nbytes[0])
+
+    def time_decode_residual(self, data, in_offsets, in_sizes, tus, tu_offsets, params, coeffs_out, nthreads):
+        t = self._f("time_decode_residual")(_ptr(data), _ptr(in_offsets), _ptr(in_sizes), _ptr(tus),
+                                            _ptr(tu_offsets), _ptr(params), C.c_long(len(params)),
+                                            _ptr(coeffs_out), C.c_int(nthreads))
+        return float(t)
