@@ -1,0 +1,59 @@
+"""ctypes loader for libcabac_b200.so (built in-tree by __graft_entry__.build()).
+
+Fails loudly when the CUDA library is missing: there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcabac_b200.so")
+
+_lib = None
+
+_P = C.c_void_p
+_SZ = C.c_size_t
+
+_SIGS = {
+    "cabac_create": (_P, [C.c_int]),
+    "cabac_destroy": (None, [_P]),
+    "cabac_set_stream": (C.c_int, [_P, _P]),
+    "cabac_sync": (C.c_int, [_P]),
+    "cabac_last_error": (C.c_char_p, [_P]),
+    "cabac_version": (C.c_char_p, []),
+    "cabac_launch_count": (C.c_uint64, [_P]),
+    "cabac_ctx_init": (C.c_int, [_P, _P, _SZ, _P]),
+    "cabac_ctx_init_dev": (C.c_int, [_P, _P, _SZ, _P]),
+    "cabac_ctx_rates": (C.c_int, [_P]),
+    "cabac_ctx_init_table": (C.c_int, [C.c_int, _P]),
+    "cabac_encode_bins": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_bins_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_bins": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_decode_bins_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_encode_residual": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_residual_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
+    "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
+}
+
+EXPORTS = tuple(_SIGS)
+
+
+def load() -> C.CDLL:
+    """Returns the loaded library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                "entropy_coding_b200 has no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib

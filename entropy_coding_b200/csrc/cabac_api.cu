@@ -1,0 +1,495 @@
+// cabac_api.cu - the C ABI of include/cabac_b200.h.
+//
+// `*_dev` entry points launch asynchronously on the handle's stream with
+// device pointers.  The host-pointer entry points wrap them: pinned staging,
+// H2D copies, launch, D2H copies, one synchronise.  There is no CPU fallback:
+// every failure to reach the GPU is reported as CABAC_ERR_CUDA.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "cabac_b200.h"
+#include "cabac_kernels.h"
+
+struct cabac_handle {
+  int device = 0;
+  cudaStream_t ownStream = nullptr;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  // grow-only device scratch for the host-pointer entry points
+  void *scratch = nullptr;
+  size_t scratchBytes = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+int fail(cabac_handle *h, cudaError_t e, const char *what) {
+  if (h) h->err = std::string(what) + ": " + cudaGetErrorString(e);
+  return CABAC_ERR_CUDA;
+}
+int badArg(cabac_handle *h, const char *what) {
+  if (h) h->err = std::string("bad argument: ") + what;
+  return CABAC_ERR_ARG;
+}
+
+// Bump allocator over the handle's scratch buffer (256-byte aligned pieces).
+struct Arena {
+  cabac_handle *h;
+  size_t need = 0;
+  std::vector<std::pair<void **, size_t>> slots;
+  explicit Arena(cabac_handle *hh) : h(hh) {}
+  void want(void **p, size_t bytes) {
+    slots.emplace_back(p, need);
+    need += (bytes + 255) & ~size_t(255);
+  }
+  cudaError_t commit() {
+    if (need > h->scratchBytes) {
+      if (h->scratch) cudaFree(h->scratch);
+      h->scratch = nullptr;
+      h->scratchBytes = 0;
+      const size_t sz = need + (need >> 2) + (1 << 20);
+      cudaError_t e = cudaMalloc(&h->scratch, sz);
+      if (e != cudaSuccess) return e;
+      h->scratchBytes = sz;
+    }
+    for (auto &s : slots) *s.first = static_cast<char *>(h->scratch) + s.second;
+    return cudaSuccess;
+  }
+};
+
+#define CK(call, what)                                   \
+  do {                                                   \
+    cudaError_t e__ = (call);                            \
+    if (e__ != cudaSuccess) return fail(h, e__, what);   \
+  } while (0)
+
+int anySubstreamFailed(const uint32_t *status, size_t n) {
+  if (!status) return CABAC_OK;
+  for (size_t i = 0; i < n; i++)
+    if (status[i]) return CABAC_ERR_SUBSTREAM;
+  return CABAC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *cabac_version(void) { return "cabac_b200 0.1 (sm_100a)"; }
+
+cabac_handle *cabac_create(int device) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return nullptr;
+  if (device < 0) {
+    if (cudaGetDevice(&device) != cudaSuccess) return nullptr;
+  }
+  if (device >= count) return nullptr;
+  cabac_handle *h = new cabac_handle();
+  h->device = device;
+  DeviceGuard g(device);
+  if (cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking) != cudaSuccess ||
+      cabac::uploadRom() != cudaSuccess) {
+    delete h;
+    return nullptr;
+  }
+  h->stream = h->ownStream;
+  return h;
+}
+
+void cabac_destroy(cabac_handle *h) {
+  if (!h) return;
+  DeviceGuard g(h->device);
+  cudaStreamSynchronize(h->stream);
+  if (h->scratch) cudaFree(h->scratch);
+  if (h->ownStream) cudaStreamDestroy(h->ownStream);
+  delete h;
+}
+
+int cabac_set_stream(cabac_handle *h, void *cuda_stream) {
+  if (!h) return CABAC_ERR_ARG;
+  h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->ownStream;
+  return CABAC_OK;
+}
+
+int cabac_sync(cabac_handle *h) {
+  if (!h) return CABAC_ERR_ARG;
+  DeviceGuard g(h->device);
+  CK(cudaStreamSynchronize(h->stream), "cabac_sync");
+  return CABAC_OK;
+}
+
+const char *cabac_last_error(cabac_handle *h) { return h ? h->err.c_str() : "null handle"; }
+uint64_t cabac_launch_count(cabac_handle *h) { return h ? h->launches : 0; }
+
+int cabac_ctx_rates(uint8_t *rates_out) {
+  if (!rates_out) return CABAC_ERR_ARG;
+  const unsigned char *win = cabac::hostInitTable(3);
+  for (int k = 0; k < CABAC_NUM_CTX; k++) {
+    const int r0 = 2 + ((win[k] >> 2) & 3), r1 = 3 + r0 + (win[k] & 3);
+    rates_out[k] = uint8_t(16 * r0 + r1);
+  }
+  return CABAC_OK;
+}
+
+int cabac_ctx_init_table(int row, uint8_t *table_out) {
+  if (row < 0 || row > 3 || !table_out) return CABAC_ERR_ARG;
+  memcpy(table_out, cabac::hostInitTable(row), CABAC_NUM_CTX);
+  return CABAC_OK;
+}
+
+// ---- device-pointer entry points -----------------------------------------
+int cabac_ctx_init_dev(cabac_handle *h, const cabac_substream_params *params, size_t n, cabac_ctx_model *out) {
+  if (!h || (n && (!params || !out))) return badArg(h, "cabac_ctx_init_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchCtxInit(h->stream, h->device, params, n, out), "ctx_init_kernel");
+  h->launches += n ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_encode_bins_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                          const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
+                          uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                          cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)))
+    return badArg(h, "cabac_encode_bins_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchEncodeBins(h->stream, h->device, cmds, cmd_offsets, params, n_sub, ctx_in, out, out_offsets,
+                             out_sizes, num_bins, ctx_out, status),
+     "encode_bins_kernel");
+  h->launches += n_sub ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_decode_bins_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const uint32_t *cmds,
+                          const uint64_t *cmd_offsets, const cabac_substream_params *params, size_t n_sub,
+                          const cabac_ctx_model *ctx_in, uint32_t *values, uint32_t *bits_read,
+                          cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !cmd_offsets || !params))) return badArg(h, "cabac_decode_bins_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchDecodeBins(h->stream, h->device, in, in_offsets, cmds, cmd_offsets, params, n_sub, ctx_in,
+                             values, bits_read, ctx_out, status),
+     "decode_bins_kernel");
+  h->launches += n_sub ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                              const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                              const cabac_ctx_model *ctx_in, uint8_t *out, const uint64_t *out_offsets,
+                              uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !out || !out_offsets || !out_sizes)))
+    return badArg(h, "cabac_encode_residual_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchEncodeResidual(h->stream, h->device, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
+                                 out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
+     "encode_residual_kernel");
+  h->launches += n_sub ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                              const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                              const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
+                              int32_t *coeffs, uint32_t *num_bins, uint32_t *bits_read, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !tu_offsets || !params || !coeffs)))
+    return badArg(h, "cabac_decode_residual_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchDecodeResidual(h->stream, h->device, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
+                                 coeffs, num_bins, bits_read, tu_flags, ctx_out, status),
+     "decode_residual_kernel");
+  h->launches += n_sub ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_pack_dev(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets, const uint32_t *out_sizes,
+                   size_t n_sub, uint8_t *packed, uint64_t *entry_points) {
+  if (!h || !entry_points || (n_sub && (!out || !out_offsets || !out_sizes || !packed)))
+    return badArg(h, "cabac_pack_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchPack(h->stream, h->device, out, out_offsets, out_sizes, n_sub, packed, entry_points),
+     "pack kernels");
+  h->launches += n_sub ? 2 : 1;
+  return CABAC_OK;
+}
+
+// ---- host-pointer entry points -------------------------------------------
+#define H2D(dst, src, bytes)                                                                       \
+  do {                                                                                             \
+    if ((bytes) && (src))                                                                          \
+      CK(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyHostToDevice, h->stream), "H2D copy");   \
+  } while (0)
+#define D2H(dst, src, bytes)                                                                       \
+  do {                                                                                             \
+    if ((bytes) && (dst))                                                                          \
+      CK(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, h->stream), "D2H copy");   \
+  } while (0)
+
+int cabac_ctx_init(cabac_handle *h, const cabac_substream_params *params, size_t n, cabac_ctx_model *out) {
+  if (!h || (n && (!params || !out))) return badArg(h, "cabac_ctx_init");
+  if (!n) return CABAC_OK;
+  DeviceGuard g(h->device);
+  cabac_substream_params *dP;
+  cabac_ctx_model *dO;
+  Arena a(h);
+  a.want((void **)&dP, n * sizeof(*params));
+  a.want((void **)&dO, n * CABAC_NUM_CTX * sizeof(*out));
+  CK(a.commit(), "scratch alloc");
+  H2D(dP, params, n * sizeof(*params));
+  int rc = cabac_ctx_init_dev(h, dP, n, dO);
+  if (rc) return rc;
+  D2H(out, dO, n * CABAC_NUM_CTX * sizeof(*out));
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
+int cabac_encode_bins(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                      const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
+                      uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                      cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)))
+    return badArg(h, "cabac_encode_bins");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nCmd = cmd_offsets[n_sub], outCap = out_offsets[n_sub];
+  uint32_t *dCmds, *dSizes, *dBins, *dStatus;
+  uint64_t *dCmdOff, *dOutOff;
+  cabac_substream_params *dP;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dOut;
+  Arena a(h);
+  a.want((void **)&dCmds, nCmd * 4);
+  a.want((void **)&dCmdOff, (n_sub + 1) * 8);
+  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dOut, outCap);
+  a.want((void **)&dSizes, n_sub * 4);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dCmds, cmds, nCmd * 4);
+  H2D(dCmdOff, cmd_offsets, (n_sub + 1) * 8);
+  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  int rc = cabac_encode_bins_dev(h, dCmds, dCmdOff, dP, n_sub, ctx_in ? dCin : nullptr, dOut, dOutOff, dSizes,
+                                 dBins, ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  D2H(out, dOut, outCap);
+  D2H(out_sizes, dSizes, n_sub * 4);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_decode_bins(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const uint32_t *cmds,
+                      const uint64_t *cmd_offsets, const cabac_substream_params *params, size_t n_sub,
+                      const cabac_ctx_model *ctx_in, uint32_t *values, uint32_t *bits_read,
+                      cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !cmd_offsets || !params))) return badArg(h, "cabac_decode_bins");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nCmd = cmd_offsets[n_sub], nIn = in_offsets[n_sub];
+  uint32_t *dCmds, *dVals, *dBits, *dStatus;
+  uint64_t *dCmdOff, *dInOff;
+  cabac_substream_params *dP;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dIn;
+  Arena a(h);
+  a.want((void **)&dCmds, nCmd * 4);
+  a.want((void **)&dVals, nCmd * 4);
+  a.want((void **)&dCmdOff, (n_sub + 1) * 8);
+  a.want((void **)&dInOff, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dIn, nIn);
+  a.want((void **)&dBits, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dCmds, cmds, nCmd * 4);
+  H2D(dCmdOff, cmd_offsets, (n_sub + 1) * 8);
+  H2D(dInOff, in_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  H2D(dIn, in, nIn);
+  int rc = cabac_decode_bins_dev(h, dIn, dInOff, dCmds, dCmdOff, dP, n_sub, ctx_in ? dCin : nullptr, dVals, dBits,
+                                 ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  D2H(values, dVals, nCmd * 4);
+  D2H(bits_read, dBits, n_sub * 4);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_encode_residual(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                          const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                          size_t n_coeffs, const cabac_ctx_model *ctx_in, uint8_t *out,
+                          const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                          uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !out || !out_offsets || !out_sizes)))
+    return badArg(h, "cabac_encode_residual");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nTu = tu_offsets[n_sub], outCap = out_offsets[n_sub];
+  if (nTu && (!tus || !coeffs)) return badArg(h, "cabac_encode_residual: tus/coeffs");
+  cabac_tu_desc *dTus;
+  uint64_t *dTuOff, *dOutOff;
+  cabac_substream_params *dP;
+  int32_t *dCoeffs;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dOut, *dTuFlags;
+  uint32_t *dSizes, *dBins, *dStatus;
+  Arena a(h);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCoeffs, n_coeffs * 4);
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dOut, outCap);
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dSizes, n_sub * 4);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  int rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
+                                     dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  D2H(out_sizes, dSizes, n_sub * 4);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(tu_flags, dTuFlags, nTu);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  // copy back only the bytes every substream produced
+  for (size_t i = 0; i < n_sub; i++) {
+    const size_t cap = out_offsets[i + 1] - out_offsets[i];
+    const size_t nb = out_sizes[i] < cap ? out_sizes[i] : cap;
+    if (nb) CK(cudaMemcpyAsync(out + out_offsets[i], dOut + out_offsets[i], nb, cudaMemcpyDeviceToHost, h->stream),
+               "D2H copy");
+  }
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                          const uint64_t *tu_offsets, const cabac_substream_params *params, size_t n_sub,
+                          const cabac_ctx_model *ctx_in, int32_t *coeffs, size_t n_coeffs, uint32_t *num_bins,
+                          uint32_t *bits_read, uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !tu_offsets || !params || !coeffs)))
+    return badArg(h, "cabac_decode_residual");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nTu = tu_offsets[n_sub], nIn = in_offsets[n_sub];
+  cabac_tu_desc *dTus;
+  uint64_t *dTuOff, *dInOff;
+  cabac_substream_params *dP;
+  int32_t *dCoeffs;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dIn, *dTuFlags;
+  uint32_t *dBins, *dBits, *dStatus;
+  Arena a(h);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dInOff, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCoeffs, n_coeffs * 4);
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dIn, nIn);
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dBits, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dInOff, in_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  H2D(dIn, in, nIn);
+  // blocks no descriptor points at keep the caller's values
+  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
+                                     dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  D2H(coeffs, dCoeffs, n_coeffs * 4);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(bits_read, dBits, n_sub * 4);
+  D2H(tu_flags, dTuFlags, nTu);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_pack(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets, const uint32_t *out_sizes,
+               size_t n_sub, uint8_t *packed, size_t packed_cap, uint64_t *entry_points) {
+  if (!h || !entry_points || (n_sub && (!out || !out_offsets || !out_sizes || !packed)))
+    return badArg(h, "cabac_pack");
+  DeviceGuard g(h->device);
+  size_t total = 0;
+  for (size_t i = 0; i < n_sub; i++) total += out_sizes[i];
+  if (total > packed_cap) return badArg(h, "cabac_pack: packed_cap too small");
+  const size_t outCap = n_sub ? out_offsets[n_sub] : 0;
+  uint8_t *dOut, *dPacked;
+  uint64_t *dOutOff, *dEntry;
+  uint32_t *dSizes;
+  Arena a(h);
+  a.want((void **)&dOut, outCap);
+  a.want((void **)&dPacked, total);
+  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dEntry, (n_sub + 1) * 8);
+  a.want((void **)&dSizes, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dOut, out, outCap);
+  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dSizes, out_sizes, n_sub * 4);
+  int rc = cabac_pack_dev(h, dOut, dOutOff, dSizes, n_sub, dPacked, dEntry);
+  if (rc) return rc;
+  D2H(packed, dPacked, total);
+  D2H(entry_points, dEntry, (n_sub + 1) * 8);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
+}  // extern "C"

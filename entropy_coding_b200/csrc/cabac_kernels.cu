@@ -1,0 +1,742 @@
+// cabac_kernels.cu - sm_100a kernels of the B200-native VVC CABAC engine.
+//
+// One warp per substream; WARPS_PER_BLOCK substreams per CTA.  Each warp owns a
+// private slice of shared memory: its probability models, a coefficient tile,
+// a command queue and an output staging ring (see cabac_device.cuh).
+#include <cuda_runtime.h>
+
+#include <cstring>
+
+#include "cabac_residual.cuh"
+#include "cabac_kernels.h"
+
+namespace cabac {
+
+#define CABAC_CTX_TABLE_QUALIFIER __device__ __constant__
+#include "cabac_ctx_tables.inc"
+#undef CABAC_CTX_TABLE_QUALIFIER
+#define CABAC_CTX_TABLE_QUALIFIER static const
+namespace hosttab {
+#include "cabac_ctx_tables.inc"
+}
+
+constexpr int WARPS_PER_BLOCK = 4;
+
+__device__ __forceinline__ int clipQp(int qp) { return qp < 0 ? 0 : (qp > 63 ? 63 : qp); }
+
+// ---------------------------------------------------------------------------
+// K1: context initialisation (Ctx::init, contexts.cpp:996-1015)
+// ---------------------------------------------------------------------------
+__global__ void ctx_init_kernel(const cabac_substream_params *__restrict__ params, size_t n,
+                                cabac_ctx_model *__restrict__ out) {
+  const size_t total = n * CABAC_NUM_CTX;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const size_t s = i / CABAC_NUM_CTX;
+    const int k = int(i - s * CABAC_NUM_CTX);
+    const cabac_substream_params p = params[s];
+    const uint32_t w = model_init(clipQp(p.qp), CABAC_CTX_INIT_TABLE[p.init_id][k], CABAC_CTX_INIT_TABLE[3][k]);
+    cabac_ctx_model m;
+    m.state0 = uint16_t(model_state0(w));
+    m.state1 = uint16_t(model_state1(w));
+    out[i] = m;
+  }
+}
+
+// Loads the warp's models: full table (379) or the residual subset (230).
+template <bool kResidualOnly>
+__device__ inline void loadCtx(uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                               size_t sub, int lane) {
+  const int qp = clipQp(p.qp);
+  constexpr int N = kResidualOnly ? RCTX : CABAC_NUM_CTX;
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int k = lane; k < N; k += 32) {
+    const int id = kResidualOnly ? rctx_inv(k) : k;
+    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
+    uint32_t w;
+    if (imp) {
+      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+      w = model_pack(m.state0, m.state1, win);
+    } else {
+      w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
+    }
+    ctx[k] = w;
+  }
+  __syncwarp();
+}
+
+template <bool kResidualOnly>
+__device__ inline void storeCtx(const uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                cabac_ctx_model *ctxOut, size_t sub, int lane) {
+  if (!ctxOut) return;
+  __syncwarp();
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    cabac_ctx_model m;
+    if (!kResidualOnly || is_residual_ctx(id)) {
+      const uint32_t w = ctx[kResidualOnly ? rctx(id) : id];
+      m.state0 = uint16_t(model_state0(w));
+      m.state1 = uint16_t(model_state1(w));
+    } else if (imp) {
+      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else {
+      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
+      m.state0 = uint16_t(model_state0(w));
+      m.state1 = uint16_t(model_state1(w));
+    }
+    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K2: bin-level encoder (recorded BinEncIf calls -> bytes)
+// ---------------------------------------------------------------------------
+struct __align__(16) BinsWarpSmem {
+  uint8_t ring[STAGE_BYTES];
+  uint32_t ctx[CABAC_NUM_CTX + 5];  // 384 words
+  uint32_t queue[32];
+};
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+encode_bins_kernel(const uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
+                   const cabac_substream_params *__restrict__ params, size_t nSub,
+                   const cabac_ctx_model *__restrict__ ctxIn, uint8_t *__restrict__ out,
+                   const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
+                   uint32_t *__restrict__ numBins, cabac_ctx_model *__restrict__ ctxOut,
+                   uint32_t *__restrict__ status) {
+  __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  BinsWarpSmem &sm = smem[wib];
+  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
+       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+    const cabac_substream_params p = params[sub];
+    loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
+    Encoder enc;
+    enc.start();
+    enc.out.ring = sm.ring;
+    enc.out.dst = out + outOffsets[sub];
+    enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
+    enc.out.n = 0;
+    enc.out.flushed = 0;
+    uint32_t st = 0;
+    const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
+    for (uint64_t c = c0; c < c1; c += 32) {
+      const int n = (c1 - c) < 32 ? int(c1 - c) : 32;
+      if (lane < n) sm.queue[lane] = cmds[c + lane];
+      __syncwarp();
+      if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, n);
+      __syncwarp();
+      if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+        stage_flush(enc.out, lane, false);
+    }
+    if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+    stage_flush(enc.out, lane, true);
+    if (lane == 0) {
+      if (enc.out.n > enc.out.cap) st |= CABAC_SS_OUT_OVERFLOW;
+      outSizes[sub] = enc.out.n;
+      if (numBins) numBins[sub] = enc.nbins;
+      if (status) status[sub] = st;
+    }
+    storeCtx<false>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K3: bin-level decoder with a known call skeleton
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
+                   const uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
+                   const cabac_substream_params *__restrict__ params, size_t nSub,
+                   const cabac_ctx_model *__restrict__ ctxIn, uint32_t *__restrict__ values,
+                   uint32_t *__restrict__ bitsRead, cabac_ctx_model *__restrict__ ctxOut,
+                   uint32_t *__restrict__ status) {
+  __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  BinsWarpSmem &sm = smem[wib];
+  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
+       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+    const cabac_substream_params p = params[sub];
+    loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
+    Decoder dec;
+    dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+    const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
+    for (uint64_t c = c0; c < c1; c += 32) {
+      const int n = (c1 - c) < 32 ? int(c1 - c) : 32;
+      if (lane < n) sm.queue[lane] = cmds[c + lane];
+      __syncwarp();
+      if (lane == 0) {
+        for (int i = 0; i < n; i++) {
+          const uint32_t w = sm.queue[i];
+          uint32_t v = 0;
+          switch (CABAC_CMD_KIND(w)) {
+            case CABAC_CMD_CTX: v = dec.decodeBin(sm.ctx + (w & 511u)); break;
+            case CABAC_CMD_EP: v = dec.decodeBinsEP((w >> 24) & 31u); break;
+            case CABAC_CMD_REM: v = dec.decodeRemAbsEP((w >> 24) & 31u); break;
+            case CABAC_CMD_TRM: v = dec.decodeBinTrm(); break;
+            case CABAC_CMD_ALIGN: dec.range = 256; break;
+            default: dec.status |= CABAC_SS_BAD_CMD; break;
+          }
+          sm.queue[i] = v;
+        }
+      }
+      __syncwarp();
+      if (values && lane < n) values[c + lane] = sm.queue[lane];
+      __syncwarp();
+    }
+    if (lane == 0) {
+      if (p.flags & CABAC_SUB_TERMINATE)
+        if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
+      if (bitsRead) bitsRead[sub] = dec.bitsRead();
+      if (status) status[sub] = dec.status;
+    }
+    storeCtx<false>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K4: residual-level encoder
+// ---------------------------------------------------------------------------
+struct __align__(16) EncWarpSmem {
+  uint8_t ring[STAGE_BYTES];
+  int16_t tile[32 * 32];
+  uint32_t ctx[RCTX + 2];  // 232 words
+  uint32_t queue[QUEUE_WORDS];
+  uint16_t cgMask[64];     // nonzero mask of every coefficient group, by scan index
+};
+
+// Stages the coded region of a TU into the int16 tile (all lanes).  Returns
+// false (warp-uniform) when a level is outside the int16 TCoeff range.
+__device__ inline bool loadTile(int16_t *tile, const int32_t *__restrict__ src, const TuGeom &g, int lane) {
+  bool ok = true;
+  const int n = g.tw * g.th;
+  if ((g.tw & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+    for (int i = lane * 4; i < n; i += 128) {
+      const int y = i >> g.log2tw, x = i & (g.tw - 1);
+      const int4 v = __ldg(reinterpret_cast<const int4 *>(src + (size_t(y) << g.log2w) + x));
+      ok &= (v.x == int16_t(v.x)) & (v.y == int16_t(v.y)) & (v.z == int16_t(v.z)) & (v.w == int16_t(v.w));
+      *reinterpret_cast<short4 *>(tile + i) = make_short4(short(v.x), short(v.y), short(v.z), short(v.w));
+    }
+  } else {
+    for (int i = lane; i < n; i += 32) {
+      const int y = i >> g.log2tw, x = i & (g.tw - 1);
+      const int v = __ldg(src + (size_t(y) << g.log2w) + x);
+      ok &= v == int16_t(v);
+      tile[i] = int16_t(v);
+    }
+  }
+  __syncwarp();
+  return __all_sync(FULL, ok);
+}
+
+// One regular-residual coefficient group, binarised by lanes 0..cgSize-1
+// (residual_coding_subblock, cabac_writer.cpp:2724-2872).  Returns the number
+// of command words written to `queue`.  All lanes must call.
+__device__ inline int binariseCG(uint32_t *queue, const int16_t *tile, const TuGeom &g, int lane, int s,
+                                 int scanPosLast, bool codeSigGroup, int sigGroupCtx, bool depQuant,
+                                 bool signHiding, int &state, int &remRegBins) {
+  const int cgSize = 1 << g.log2cg;
+  const int minSubPos = s << g.log2cg;
+  const bool isLast = (scanPosLast >> g.log2cg) == s;
+  const int P0 = isLast ? scanPosLast - minSubPos : cgSize - 1;  // first coded position (in-CG index)
+  const bool active = lane <= P0;                                 // implies lane < cgSize
+  const uint32_t activeMask = (P0 >= 31) ? FULL : ((2u << P0) - 1u);
+  const uint32_t above = activeMask & ~((2u << lane) - 1u);       // positions coded before this lane's
+  int nq = 0;
+  if (codeSigGroup) {
+    if (lane == 0) queue[0] = CABAC_MK_CTX(sigGroupCtx, 1);
+    nq = 1;
+  }
+
+  int x = 0, y = 0, v = 0, sumAbs1 = 0, numPos = 0, sumAll = 0;
+  if (active) {
+    const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
+    const uint32_t q = __ldg(&g_rom.inScan[g.shape][lane]);
+    x = int((c & 15u) << g.log2cgw) + int(q & 15u);
+    y = int((c >> 4) << g.log2cgh) + int(q >> 4);
+    v = tile[(y << g.log2tw) + x];
+    templateSums(tile, g, x, y, sumAbs1, numPos, sumAll);
+  }
+  const int a = abs(v);
+  const bool nz = a != 0;
+  const uint32_t Z = __ballot_sync(FULL, active && nz);
+  const uint32_t G = __ballot_sync(FULL, active && a > 1);
+  const uint32_t Pm = __ballot_sync(FULL, active && (a & 1));
+  const uint32_t Neg = __ballot_sync(FULL, active && v < 0);
+
+  // sig_coeff_flag is inferred at one position when nothing non-zero preceded it
+  const int inferLane = isLast ? P0 : (s != 0 ? 0 : -1);
+  const bool sigCoded = active && ((Z & above) != 0 || lane != inferLane);
+  const uint32_t S = __ballot_sync(FULL, sigCoded);
+  // context-coded bins spent before this position if everything so far was context coded
+  const int cum = __popc(S & above) + __popc(Z & above) + 2 * __popc(G & above);
+  const bool inPass1 = active && (remRegBins - cum >= 4);
+  const uint32_t M1 = __ballot_sync(FULL, inPass1);
+  const int myBins = inPass1 ? (int(sigCoded) + (nz ? 1 + (a > 1 ? 2 : 0) : 0)) : 0;
+  const int pass1Total = __popc(S & M1) + __popc(Z & M1) + 2 * __popc(G & M1);
+
+  // dependent-quantisation state before this position (see stateStep)
+  int st = 0;
+  int stateEnd = 0;
+  if (depQuant) {
+    // step t = P0 - pos + 1 for the position `pos`; odd t <=> (P0 - pos) even
+    const uint32_t evenDist = (P0 & 1) ? 0xAAAAAAAAu : 0x55555555u;  // positions with (P0 - pos) even
+    const int h0 = state >> 1, l0 = state & 1;
+    {
+      const int k = P0 - lane;  // steps taken before this lane's position
+      const int O = __popc(Pm & above & evenDist) & 1, E = __popc(Pm & above & ~evenDist) & 1;
+      const int hi = (k & 1) ? (l0 ^ O) : (h0 ^ E);
+      const int lo = (k & 1) ? (h0 ^ E) : (l0 ^ O);
+      st = (hi << 1) | lo;
+    }
+    {
+      const int k = P0 + 1;
+      const int O = __popc(Pm & activeMask & evenDist) & 1, E = __popc(Pm & activeMask & ~evenDist) & 1;
+      const int hi = (k & 1) ? (l0 ^ O) : (h0 ^ E);
+      const int lo = (k & 1) ? (h0 ^ E) : (l0 ^ O);
+      stateEnd = (hi << 1) | lo;
+    }
+  }
+
+  const int diag = x + y;
+  const bool atLast = isLast && lane == P0;
+  if (inPass1) {
+    int qi = nq + cum;
+    if (sigCoded) {
+      const int ctxId = sigFlagBase(g.ch, max(0, st - 1)) + sigCtxOffset(g, sumAbs1, diag);
+      queue[qi++] = CABAC_MK_CTX(ctxId, nz);
+    }
+    if (nz) {
+      const int ofs = atLast ? 0 : gtxCtxOffset(g, sumAbs1, numPos, diag);
+      queue[qi++] = CABAC_MK_CTX(gtxFlagBase(g.ch + 2) + ofs, a > 1);
+      if (a > 1) {
+        const int rem = a - 2;
+        queue[qi++] = CABAC_MK_CTX(parFlagBase(g.ch) + ofs, rem & 1);
+        queue[qi++] = CABAC_MK_CTX(gtxFlagBase(g.ch) + ofs, (rem >> 1) != 0);
+      }
+    }
+  }
+  nq += pass1Total;
+  // 2nd pass: abs_remainder of context-coded positions with |level| >= 4
+  const bool hasRem = inPass1 && a >= 4;
+  const uint32_t R = __ballot_sync(FULL, hasRem);
+  if (hasRem) queue[nq + __popc(R & above)] = CABAC_MK_REM((a - 4) >> 1, goRicePar(sumAll - 20));
+  nq += __popc(R);
+  // bypass-only positions: dec_abs_level
+  const bool inPass3 = active && !inPass1;
+  const uint32_t M3 = activeMask & ~M1;
+  if (inPass3) {
+    const uint32_t rice = goRicePar(sumAll);
+    const uint32_t pos0 = (st < 2 ? 1u : 2u) << rice;
+    const uint32_t rem = a == 0 ? pos0 : (uint32_t(a) <= pos0 ? uint32_t(a) - 1u : uint32_t(a));
+    queue[nq + __popc(M3 & above)] = CABAC_MK_REM(rem, rice);
+  }
+  nq += __popc(M3);
+  // signs: first coded non-zero is the pattern's MSB
+  uint32_t numSigns = __popc(Z);
+  uint32_t mySign = (active && nz && v < 0) ? (1u << __popc(Z & ((1u << lane) - 1u))) : 0u;
+  uint32_t pattern = __reduce_or_sync(FULL, mySign);
+  (void)Neg;
+  if (signHiding && Z) {
+    const int lastNZ = 31 - __clz(Z), firstNZ = __ffs(Z) - 1;
+    if (lastNZ - firstNZ >= 4) {  // SBH_THRESHOLD, common_def.hpp:96
+      numSigns--;
+      pattern >>= 1;
+    }
+  }
+  if (lane == 0) queue[nq] = CABAC_MK_EP(pattern, numSigns);
+  nq += 1;
+  remRegBins -= pass1Total;
+  (void)myBins;
+  if (depQuant) state = stateEnd;
+  __syncwarp();
+  return nq;
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
+                       const cabac_substream_params *__restrict__ params, size_t nSub,
+                       const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
+                       uint8_t *__restrict__ out, const uint64_t *__restrict__ outOffsets,
+                       uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins,
+                       uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
+                       uint32_t *__restrict__ status) {
+  __shared__ EncWarpSmem smem[WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  EncWarpSmem &sm = smem[wib];
+  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
+       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+    const cabac_substream_params p = params[sub];
+    loadCtx<true>(sm.ctx, p, ctxIn, sub, lane);
+    Encoder enc;
+    enc.start();
+    enc.out.ring = sm.ring;
+    enc.out.dst = out + outOffsets[sub];
+    enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
+    enc.out.n = 0;
+    enc.out.flushed = 0;
+    uint32_t st = 0;
+    const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
+    const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
+    const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
+    for (uint64_t t = t0; t < t1; t++) {
+      const cabac_tu_desc d = tus[t];
+      const TuGeom g = makeGeom(d);
+      const bool ts = (d.flags & CABAC_TU_TS) != 0;
+      const bool tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
+      uint32_t res = ts ? CABAC_TUR_TS : 0;
+      if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+
+      // ---- pre-scan: non-zero mask per coefficient group, last position ----
+      int lastCG = -1;
+      const int cgSize = 1 << g.log2cg;
+      const int perIter = 32 >> g.log2cg;  // coefficient groups handled per iteration
+      for (int s0 = 0; s0 < g.numCG; s0 += perIter) {
+        const int s = s0 + (lane >> g.log2cg), pl = lane & (cgSize - 1);
+        bool nz = false;
+        if (s < g.numCG) {
+          int x, y;
+          scanXY(g, (s << g.log2cg) + pl, x, y);
+          nz = sm.tile[(y << g.log2tw) + x] != 0;
+        }
+        const uint32_t b = __ballot_sync(FULL, nz);
+        if (pl == 0 && s < g.numCG) sm.cgMask[s] = uint16_t((b >> (lane & 31 & ~(cgSize - 1))) & ((1u << cgSize) - 1u));
+        if (b) lastCG = s0 + ((31 - __clz(b)) >> g.log2cg);
+      }
+      __syncwarp();
+      if (lastCG < 0) {  // "Coefficient coding called for empty TU", cabac_writer.cpp:2457
+        st |= CABAC_SS_EMPTY_TU;
+        if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+        continue;
+      }
+      // ---- transform_skip_flag (ts_flag, cabac_writer.cpp:2527-2535) ----
+      if (lane == 0 && (d.flags & CABAC_TU_TS_ALLOWED)) enc.encodeBin(ts, sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0));
+      if (tsPath) {
+        if (lane == 0) encResidualTS(enc, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0, sm.cgMask);
+        __syncwarp();
+      } else {
+        const int scanPosLast = (lastCG << g.log2cg) + (31 - __clz(uint32_t(sm.cgMask[lastCG])));
+        if (!ts && g.w >= 4 && g.h >= 4) {  // CUCtx side effects, cabac_writer.cpp:2460-2478
+          const int maxLfnstPos = ((g.h == 4 && g.w == 4) || (g.h == 8 && g.w == 8)) ? 7 : 15;
+          if (scanPosLast > maxLfnstPos) res |= CABAC_TUR_VIOLATES_LFNST;
+          if (scanPosLast >= 1) res |= CABAC_TUR_LFNST_LAST_POS;
+        }
+        if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
+        if (lane == 0) {
+          int x, y;
+          scanXY(g, scanPosLast, x, y);
+          encLastSigCoeff(enc, sm.ctx, g, x, y);
+        }
+        int state = 0;
+        int remRegBins = regBinLimit(g);
+        uint64_t sigGroups = 0;
+        for (int s = lastCG; s >= 0; s--) {
+          const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
+          const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
+          const bool sig = sm.cgMask[s] != 0;
+          // initSubblock, context_modelling.cpp:81-106
+          if (sig) sigGroups |= 1ull << cgPos;
+          if (g.sbtZero) {
+            if ((g.h == 32 && cgy >= (16 >> g.log2cgh)) || (g.w == 32 && cgx >= (16 >> g.log2cgw))) continue;
+          }
+          const bool codeSigGroup = s != lastCG && s != 0;
+          const int right = (cgx + 1 < g.wig) ? int((sigGroups >> (cgPos + 1)) & 1) : 0;
+          const int lower = (cgy + 1 < g.hig) ? int((sigGroups >> (cgPos + g.wig)) & 1) : 0;
+          const int sigGroupCtx = R_SIG_GROUP + 2 * g.ch + (right | lower);
+          int nq;
+          if (codeSigGroup && !sig) {
+            if (lane == 0) sm.queue[0] = CABAC_MK_CTX(sigGroupCtx, 0);
+            nq = 1;
+            __syncwarp();
+          } else {
+            nq = binariseCG(sm.queue, sm.tile, g, lane, s, scanPosLast, codeSigGroup, sigGroupCtx, depQuant,
+                            signHiding, state, remRegBins);
+            if (sig && g.comp == 0 && (cgy > 3 || cgx > 3)) res |= CABAC_TUR_VIOLATES_MTS;
+          }
+          if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, nq);
+          __syncwarp();
+          if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+            stage_flush(enc.out, lane, false);
+        }
+      }
+      if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+      if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+        stage_flush(enc.out, lane, false);
+    }
+    if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+    stage_flush(enc.out, lane, true);
+    if (lane == 0) {
+      if (enc.out.n > enc.out.cap) st |= CABAC_SS_OUT_OVERFLOW;
+      outSizes[sub] = enc.out.n;
+      if (numBins) numBins[sub] = enc.nbins;
+      if (status) status[sub] = st;
+    }
+    storeCtx<true>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K5: residual-level decoder
+// ---------------------------------------------------------------------------
+struct __align__(16) DecWarpSmem {
+  int32_t tile[32 * 32];
+  uint32_t ctx[RCTX + 2];
+};
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
+                       const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
+                       const cabac_substream_params *__restrict__ params, size_t nSub,
+                       const cabac_ctx_model *__restrict__ ctxIn, int32_t *__restrict__ coeffs,
+                       uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
+                       uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
+                       uint32_t *__restrict__ status) {
+  __shared__ DecWarpSmem smem[WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  DecWarpSmem &sm = smem[wib];
+  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
+       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+    const cabac_substream_params p = params[sub];
+    loadCtx<true>(sm.ctx, p, ctxIn, sub, lane);
+    Decoder dec;
+    dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+    const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
+    for (uint64_t t = t0; t < t1; t++) {
+      const cabac_tu_desc d = tus[t];
+      const TuGeom g = makeGeom(d);
+      const int n = g.tw * g.th;
+      for (int i = lane; i < n; i += 32) sm.tile[i] = 0;
+      __syncwarp();
+      if (lane == 0) {
+        // ts_flag, cabac_reader.cpp:2737-2752
+        bool ts = (d.flags & CABAC_TU_BDPCM) ? true : (d.flags & CABAC_TU_TS) != 0;
+        if (d.flags & CABAC_TU_TS_ALLOWED) ts = dec.decodeBin(sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0)) != 0;
+        uint32_t res = ts ? CABAC_TUR_TS : 0;
+        if (ts && !(p.flags & CABAC_SUB_TSRC_DISABLED))
+          decResidualTS(dec, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0);
+        else
+          res |= decResidualRegular(dec, sm.ctx, sm.tile, g, p.flags, ts);
+        if (tuFlags) tuFlags[t] = uint8_t(res);
+      }
+      __syncwarp();
+      // write the block back (the zero-out region of 64-point blocks as zeros)
+      int32_t *dst = coeffs + d.coeff_offset;
+      const int total = g.w * g.h;
+      for (int i = lane; i < total; i += 32) {
+        const int y = i >> g.log2w, x = i & (g.w - 1);
+        dst[i] = (x < g.tw && y < g.th) ? sm.tile[(y << g.log2tw) + x] : 0;
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      if (p.flags & CABAC_SUB_TERMINATE)
+        if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
+      if (numBins) numBins[sub] = dec.nbins;
+      if (bitsRead) bitsRead[sub] = dec.bitsRead();
+      if (status) status[sub] = dec.status;
+    }
+    storeCtx<true>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K6/K7: substream packing (entry points + compaction)
+// ---------------------------------------------------------------------------
+// Single-CTA exclusive scan of the substream sizes (n_sub <= ~10^6: a few
+// dozen microseconds; the sizes are 4 bytes per substream).
+__global__ void __launch_bounds__(1024) entry_points_kernel(const uint32_t *__restrict__ sizes, size_t n,
+                                                            uint64_t *__restrict__ entry) {
+  __shared__ uint64_t warpSums[32];
+  __shared__ uint64_t carry;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (size_t base = 0; base < n; base += blockDim.x) {
+    const size_t i = base + threadIdx.x;
+    const uint64_t v = i < n ? sizes[i] : 0;
+    uint64_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint64_t t = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) warpSums[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+      uint64_t s = warpSums[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t t = __shfl_up_sync(FULL, s, o);
+        if (lane >= o) s += t;
+      }
+      warpSums[lane] = s;  // inclusive over warps
+    }
+    __syncthreads();
+    const uint64_t before = carry + (w ? warpSums[w - 1] : 0) + incl - v;
+    if (i < n) entry[i] = before;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) entry[n] = carry;
+}
+
+// One warp per substream: slab -> packed payload at its entry point.
+__global__ void __launch_bounds__(256) pack_kernel(const uint8_t *__restrict__ out,
+                                                   const uint64_t *__restrict__ outOffsets,
+                                                   const uint32_t *__restrict__ sizes, size_t n,
+                                                   uint8_t *__restrict__ packed,
+                                                   const uint64_t *__restrict__ entry) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
+  for (size_t s = warp; s < n; s += nWarps) {
+    const uint8_t *src = out + outOffsets[s];
+    uint8_t *dst = packed + entry[s];
+    const uint32_t len = sizes[s];
+    // head: bytes up to the destination's 16-byte boundary
+    uint32_t head = uint32_t((16 - (reinterpret_cast<uintptr_t>(dst) & 15u)) & 15u);
+    if (head > len) head = len;
+    for (uint32_t i = lane; i < head; i += 32) dst[i] = src[i];
+    const uint32_t body = (len - head) & ~15u;
+    if ((reinterpret_cast<uintptr_t>(src + head) & 3u) == 0) {
+      for (uint32_t i = 16u * lane; i < body; i += 512u) {
+        const uint32_t *s4 = reinterpret_cast<const uint32_t *>(src + head + i);
+        *reinterpret_cast<uint4 *>(dst + head + i) = make_uint4(s4[0], s4[1], s4[2], s4[3]);
+      }
+    } else {
+      for (uint32_t i = 16u * lane; i < body; i += 512u) {
+        uint32_t wv[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const uint8_t *b = src + head + i + 4 * k;
+          wv[k] = uint32_t(b[0]) | (uint32_t(b[1]) << 8) | (uint32_t(b[2]) << 16) | (uint32_t(b[3]) << 24);
+        }
+        *reinterpret_cast<uint4 *>(dst + head + i) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+      }
+    }
+    for (uint32_t i = head + body + lane; i < len; i += 32) dst[i] = src[i];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host-side launchers (called by cabac_api.cpp)
+// ---------------------------------------------------------------------------
+static void buildRom(ScanRom &r) {
+  auto diag = [](int bw, int bh, uint8_t *xs, uint8_t *ys) {  // ScanGenerator SCAN_DIAG, rom.cpp:75-93
+    int k = 0;
+    for (int d = 0; d <= bw + bh - 2; d++) {
+      int y = d < bh ? d : bh - 1;
+      int x = d - y;
+      for (; y >= 0 && x < bw; y--, x++) { xs[k] = uint8_t(x); ys[k] = uint8_t(y); k++; }
+    }
+  };
+  uint8_t xs[64], ys[64];
+  memset(&r, 0, sizeof(r));
+  for (int lw = 0; lw < 4; lw++)
+    for (int lh = 0; lh < 4; lh++) {
+      const int w = 1 << lw, h = 1 << lh;
+      diag(w, h, xs, ys);
+      for (int k = 0; k < w * h; k++) {
+        r.cgScan[lw][lh][k] = uint8_t(xs[k] | (ys[k] << 4));
+        r.cgScanInv[lw][lh][ys[k] * w + xs[k]] = uint8_t(k);
+      }
+    }
+  const int shapes[4][2] = {{4, 4}, {2, 2}, {2, 8}, {8, 2}};
+  for (int s = 0; s < 4; s++) {
+    const int w = shapes[s][0], h = shapes[s][1];
+    diag(w, h, xs, ys);
+    for (int k = 0; k < w * h; k++) {
+      r.inScan[s][k] = uint8_t(xs[k] | (ys[k] << 4));
+      r.inScanInv[s][ys[k] * w + xs[k]] = uint8_t(k);
+    }
+  }
+}
+
+cudaError_t uploadRom() {
+  ScanRom r;
+  buildRom(r);
+  return cudaMemcpyToSymbol(g_rom, &r, sizeof(r));
+}
+
+const unsigned char *hostInitTable(int row) { return hosttab::CABAC_CTX_INIT_TABLE[row]; }
+
+static int gridFor(size_t nSub, int device) {
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const size_t blocks = (nSub + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+  const size_t cap = size_t(sms) * 32;  // more CTAs than can be resident: grid-stride picks up the rest
+  return int(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
+                          cabac_ctx_model *out) {
+  (void)device;
+  if (n == 0) return cudaSuccess;
+  const size_t total = n * CABAC_NUM_CTX;
+  const size_t wantBlocks = (total + 255) / 256;
+  const int blocks = int(wantBlocks < size_t(148 * 16) ? wantBlocks : size_t(148 * 16));
+  ctx_init_kernel<<<blocks, 256, 0, s>>>(params, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launchEncodeBins(cudaStream_t s, int device, const uint32_t *cmds, const uint64_t *cmdOffsets,
+                             const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
+                             uint8_t *out, const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
+                             cabac_ctx_model *ctxOut, uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  encode_bins_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      cmds, cmdOffsets, params, nSub, ctxIn, out, outOffsets, outSizes, numBins, ctxOut, status);
+  return cudaGetLastError();
+}
+
+cudaError_t launchDecodeBins(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+                             const uint32_t *cmds, const uint64_t *cmdOffsets,
+                             const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
+                             uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  decode_bins_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      in, inOffsets, cmds, cmdOffsets, params, nSub, ctxIn, values, bitsRead, ctxOut, status);
+  return cudaGetLastError();
+}
+
+cudaError_t launchEncodeResidual(cudaStream_t s, int device, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                 const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
+                                 const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
+                                 uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
+                                 cabac_ctx_model *ctxOut, uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  encode_residual_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut, status);
+  return cudaGetLastError();
+}
+
+cudaError_t launchDecodeResidual(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+                                 const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                 const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
+                                 int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
+                                 cabac_ctx_model *ctxOut, uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  decode_residual_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status);
+  return cudaGetLastError();
+}
+
+cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
+                       const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints) {
+  entry_points_kernel<<<1, 1024, 0, s>>>(outSizes, nSub, entryPoints);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess || nSub == 0) return e;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const size_t wantBlocks = (nSub + 7) / 8;
+  const size_t blocks = wantBlocks < size_t(sms) * 8 ? wantBlocks : size_t(sms) * 8;
+  pack_kernel<<<int(blocks), 256, 0, s>>>(out, outOffsets, outSizes, nSub, packed, entryPoints);
+  return cudaGetLastError();
+}
+
+}  // namespace cabac

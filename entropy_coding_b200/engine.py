@@ -1,0 +1,207 @@
+"""Python face of the C ABI (include/cabac_b200.h).
+
+`CabacEngine` owns one handle (one CUDA stream on one device).  Methods named
+after the C entry points take numpy arrays (host pointers; copies happen inside
+the library) or, for the `*_dev` variants, torch CUDA tensors / raw device
+pointers.  Nothing here computes: every call lands in a CUDA kernel, and fails
+loudly when the library or a GPU is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .types import (CTX_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, TU_DT)
+
+
+class CabacError(RuntimeError):
+    """Mirrors the reference's Common::Exception (CHECK/THROW, type_def.hpp:295-329)."""
+
+    def __init__(self, code, msg, status=None):
+        super().__init__(f"cabac_b200 error {code}: {msg}")
+        self.code = code
+        self.status = status
+
+
+def _np(a, dt):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dt)
+    return a
+
+
+def _hp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _dp(t):
+    """Device pointer of a torch tensor (or a raw int / None)."""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    assert t.is_cuda and t.is_contiguous(), "device tensors must be contiguous CUDA tensors"
+    return C.c_void_p(t.data_ptr())
+
+
+class CabacEngine:
+    def __init__(self, device: int = -1):
+        self.lib = _lib.load()
+        self.h = self.lib.cabac_create(device)
+        if not self.h:
+            raise CabacError(-1, "cabac_create failed: no usable CUDA device (there is no CPU fallback)")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cabac_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing ---------------------------------------------------------
+    def _check(self, rc, status=None):
+        if rc == OK:
+            return
+        if rc == ERR_SUBSTREAM:
+            raise CabacError(rc, "one or more substreams failed", status)
+        raise CabacError(rc, self.lib.cabac_last_error(self.h).decode())
+
+    def set_stream(self, cuda_stream_ptr: int | None):
+        self._check(self.lib.cabac_set_stream(self.h, C.c_void_p(cuda_stream_ptr or 0)))
+
+    def sync(self):
+        self._check(self.lib.cabac_sync(self.h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.cabac_launch_count(self.h))
+
+    # ---- tables -------------------------------------------------------------
+    def ctx_rates(self) -> np.ndarray:
+        out = np.zeros(NUM_CTX, np.uint8)
+        self._check(self.lib.cabac_ctx_rates(_hp(out)))
+        return out
+
+    def ctx_init_table(self, row: int) -> np.ndarray:
+        out = np.zeros(NUM_CTX, np.uint8)
+        self._check(self.lib.cabac_ctx_init_table(row, _hp(out)))
+        return out
+
+    def ctx_init(self, params) -> np.ndarray:
+        params = _np(params, PARAMS_DT)
+        out = np.zeros((len(params), NUM_CTX), CTX_DT)
+        self._check(self.lib.cabac_ctx_init(self.h, _hp(params), len(params), _hp(out)))
+        return out
+
+    # ---- host-pointer calls ---------------------------------------------------
+    def encode_bins(self, cmds, cmd_offsets, params, out_offsets, ctx_in=None, want_ctx=False, raise_on_status=True):
+        cmds, cmd_offsets = _np(cmds, np.uint32), _np(cmd_offsets, np.uint64)
+        params, out_offsets = _np(params, PARAMS_DT), _np(out_offsets, np.uint64)
+        n = len(params)
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_bins(self.h, _hp(cmds), _hp(cmd_offsets), _hp(params), n, _hp(ctx_in), _hp(out),
+                                        _hp(out_offsets), _hp(sizes), _hp(bins), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, status=status, ctx_out=ctx_out)
+
+    def decode_bins(self, data, in_offsets, cmds, cmd_offsets, params, ctx_in=None, want_ctx=False,
+                    raise_on_status=True):
+        data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
+        cmds, cmd_offsets, params = _np(cmds, np.uint32), _np(cmd_offsets, np.uint64), _np(params, PARAMS_DT)
+        n = len(params)
+        values = np.zeros(len(cmds), np.uint32)
+        bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_decode_bins(self.h, _hp(data), _hp(in_offsets), _hp(cmds), _hp(cmd_offsets), _hp(params),
+                                        n, _hp(ctx_in), _hp(values), _hp(bits), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(values=values, bits_read=bits, status=status, ctx_out=ctx_out)
+
+    def encode_residual(self, tus, tu_offsets, params, coeffs, out_offsets, ctx_in=None, want_ctx=False,
+                        raise_on_status=True):
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        n = len(params)
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_residual(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
+                                            coeffs.size, _hp(ctx_in), _hp(out), _hp(out_offsets), _hp(sizes),
+                                            _hp(bins), _hp(tu_flags), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    def decode_residual(self, data, in_offsets, tus, tu_offsets, params, n_coeffs, ctx_in=None, want_ctx=False,
+                        raise_on_status=True):
+        data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
+        tus, tu_offsets, params = _np(tus, TU_DT), _np(tu_offsets, np.uint64), _np(params, PARAMS_DT)
+        n = len(params)
+        coeffs = np.zeros(n_coeffs, np.int32)
+        bins, bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_decode_residual(self.h, _hp(data), _hp(in_offsets), _hp(tus), _hp(tu_offsets),
+                                            _hp(params), n, _hp(ctx_in), _hp(coeffs), n_coeffs, _hp(bins), _hp(bits),
+                                            _hp(tu_flags), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(coeffs=coeffs, num_bins=bins, bits_read=bits, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    def pack(self, out, out_offsets, sizes):
+        out, out_offsets, sizes = _np(out, np.uint8), _np(out_offsets, np.uint64), _np(sizes, np.uint32)
+        n = len(sizes)
+        total = int(sizes.astype(np.uint64).sum())
+        packed = np.zeros(total, np.uint8)
+        entry = np.zeros(n + 1, np.uint64)
+        self._check(self.lib.cabac_pack(self.h, _hp(out), _hp(out_offsets), _hp(sizes), n, _hp(packed), total,
+                                        _hp(entry)))
+        return packed, entry
+
+    # ---- device-pointer calls (torch tensors), asynchronous ------------------
+    def encode_residual_dev(self, tus, tu_offsets, params, n_sub, coeffs, out, out_offsets, out_sizes, num_bins=None,
+                            tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_encode_residual_dev(self.h, _dp(tus), _dp(tu_offsets), _dp(params), n_sub,
+                                                       _dp(coeffs), _dp(ctx_in), _dp(out), _dp(out_offsets),
+                                                       _dp(out_sizes), _dp(num_bins), _dp(tu_flags), _dp(ctx_out),
+                                                       _dp(status)))
+
+    def decode_residual_dev(self, data, in_offsets, tus, tu_offsets, params, n_sub, coeffs, num_bins=None,
+                            bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_decode_residual_dev(self.h, _dp(data), _dp(in_offsets), _dp(tus), _dp(tu_offsets),
+                                                       _dp(params), n_sub, _dp(ctx_in), _dp(coeffs), _dp(num_bins),
+                                                       _dp(bits_read), _dp(tu_flags), _dp(ctx_out), _dp(status)))
+
+    def encode_bins_dev(self, cmds, cmd_offsets, params, n_sub, out, out_offsets, out_sizes, num_bins=None,
+                        ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_encode_bins_dev(self.h, _dp(cmds), _dp(cmd_offsets), _dp(params), n_sub,
+                                                   _dp(ctx_in), _dp(out), _dp(out_offsets), _dp(out_sizes),
+                                                   _dp(num_bins), _dp(ctx_out), _dp(status)))
+
+    def decode_bins_dev(self, data, in_offsets, cmds, cmd_offsets, params, n_sub, values, bits_read=None,
+                        ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_decode_bins_dev(self.h, _dp(data), _dp(in_offsets), _dp(cmds), _dp(cmd_offsets),
+                                                   _dp(params), n_sub, _dp(ctx_in), _dp(values), _dp(bits_read),
+                                                   _dp(ctx_out), _dp(status)))
+
+    def pack_dev(self, out, out_offsets, out_sizes, n_sub, packed, entry_points):
+        self._check(self.lib.cabac_pack_dev(self.h, _dp(out), _dp(out_offsets), _dp(out_sizes), n_sub, _dp(packed),
+                                            _dp(entry_points)))
+
+    def ctx_init_dev(self, params, n, out):
+        self._check(self.lib.cabac_ctx_init_dev(self.h, _dp(params), n, _dp(out)))

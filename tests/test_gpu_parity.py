@@ -1,0 +1,299 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI, against the CPU
+oracle and the reference-generated golden fixtures.  Bit-exact everywhere: this
+path is integer/byte work."""
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from entropy_coding_b200 import workload as W
+from entropy_coding_b200.types import (CTX_DT, PARAMS_DT, SS_EMPTY_TU, SS_OUT_OVERFLOW, SUB_ALIGN, SUB_CTX_IN,
+                                       SUB_DEP_QUANT, SUB_SIGN_HIDING, SUB_TERMINATE, SUB_TSRC_DISABLED, TU_DT,
+                                       mk_ctx, mk_ep, mk_trm)
+from helpers import T, ctx_pairs, expected_values, random_cmds, sub_range
+
+pytestmark = pytest.mark.gpu
+
+
+def offsets_of(lengths, align=1):
+    lengths = (np.asarray(lengths, np.int64) + align - 1) // align * align
+    return np.concatenate([[0], np.cumsum(lengths)]).astype(np.uint64)
+
+
+def split(out, offsets, sizes):
+    return [out[int(offsets[i]):int(offsets[i]) + int(sizes[i])] for i in range(len(sizes))]
+
+
+# ---------------------------------------------------------------- (2) contexts
+def test_ctx_init_matches_golden_and_oracle(engine, oracle):
+    g = load_golden("ctx_init")
+    qps = (-5, 0, 9, 17, 26, 32, 40, 51, 63, 70)
+    params = np.zeros(len(qps) * 3, PARAMS_DT)
+    k = 0
+    for qp in qps:
+        for iid in range(3):
+            params[k] = (qp, iid, 0, 0)
+            k += 1
+    out = engine.ctx_init(params)
+    k = 0
+    for qp in qps:
+        for iid in range(3):
+            assert (ctx_pairs(out[k]) == g[f"q{qp}_i{iid}"]).all()
+            assert (ctx_pairs(out[k]) == ctx_pairs(oracle.ctx_init(qp, iid)[0])).all()
+            k += 1
+    assert (engine.ctx_rates() == g["rates"]).all()
+
+
+# ---------------------------------------------------------------- (1) bin level
+def test_kats_on_gpu(engine):
+    g = load_golden("kat")
+    names = ["kat0", "kat1", "kat2", "kat3"]
+    cmds = [g[n + "_cmds"] for n in names]
+    params = np.zeros(4, PARAMS_DT)
+    for i, n in enumerate(names):
+        qp, iid, _ = (int(v) for v in g[n + "_meta"])
+        params[i] = (qp, iid, T, 0)
+    coff = offsets_of([len(c) for c in cmds])
+    ooff = offsets_of([128] * 4)
+    r = engine.encode_bins(np.concatenate(cmds), coff, params, ooff)
+    for i, n in enumerate(names):
+        got = split(r["out"], ooff, r["sizes"])[i]
+        assert got.tobytes() == g[n + "_bytes"].tobytes(), n
+        assert int(r["num_bins"][i]) == int(g[n + "_meta"][2])
+    assert not r["status"].any()
+
+
+def test_bins_golden_on_gpu(engine):
+    g = load_golden("bins")
+    n = int(g["n"][0])
+    cmds = [g[f"cmds{i}"] for i in range(n)]
+    params = np.zeros(n, PARAMS_DT)
+    for i in range(n):
+        params[i] = (int(g[f"meta{i}"][0]), int(g[f"meta{i}"][1]), T, 0)
+    coff = offsets_of([len(c) for c in cmds])
+    ooff = offsets_of([len(g[f"bytes{i}"]) + 32 for i in range(n)], 16)
+    r = engine.encode_bins(np.concatenate(cmds), coff, params, ooff, want_ctx=True)
+    outs = split(r["out"], ooff, r["sizes"])
+    for i in range(n):
+        assert outs[i].tobytes() == g[f"bytes{i}"].tobytes(), i
+        assert int(r["num_bins"][i]) == int(g[f"meta{i}"][2])
+        assert (ctx_pairs(r["ctx_out"][i]) == g[f"ctx{i}"]).all()
+    # decode the reference's bytes
+    blobs = [g[f"bytes{i}"] for i in range(n)]
+    ioff = offsets_of([len(b) for b in blobs])
+    params["flags"] = SUB_TERMINATE
+    d = engine.decode_bins(np.concatenate(blobs), ioff, np.concatenate(cmds), coff, params, want_ctx=True)
+    for i in range(n):
+        a, b = int(coff[i]), int(coff[i + 1])
+        assert (d["values"][a:b] == g[f"vals{i}"]).all(), i
+        assert int(d["bits_read"][i]) == int(g[f"meta{i}"][3]) and int(d["status"][i]) == int(g[f"meta{i}"][4])
+        assert (ctx_pairs(d["ctx_out"][i]) == g[f"ctx{i}"]).all()
+
+
+def test_bins_random_vs_oracle(engine, oracle):
+    rng = np.random.default_rng(2024)
+    n = 300
+    cmds = [random_cmds(rng, int(rng.integers(0, 900))) for _ in range(n)]
+    cmds[0] = np.zeros(0, np.uint32)  # empty substream
+    params = np.zeros(n, PARAMS_DT)
+    params["qp"] = rng.integers(0, 64, n)
+    params["init_id"] = rng.integers(0, 3, n)
+    params["flags"] = T
+    coff = offsets_of([len(c) for c in cmds])
+    ooff = offsets_of([len(c) * 5 + 64 for c in cmds], 16)
+    r = engine.encode_bins(np.concatenate(cmds), coff, params, ooff, want_ctx=True)
+    outs = split(r["out"], ooff, r["sizes"])
+    for i in range(n):
+        eb, nb, ectx = oracle.encode_bins(cmds[i], int(params["qp"][i]), int(params["init_id"][i]), T, want_ctx=True)
+        assert outs[i].tobytes() == eb.tobytes(), i
+        assert int(r["num_bins"][i]) == nb and (r["ctx_out"][i] == ectx).all()
+    ioff = offsets_of(r["sizes"])
+    params["flags"] = SUB_TERMINATE
+    d = engine.decode_bins(np.concatenate(outs), ioff, np.concatenate(cmds), coff, params)
+    assert (d["values"] == expected_values(np.concatenate(cmds))).all()
+    assert not d["status"].any()
+    assert (d["bits_read"] <= 8 * r["sizes"]).all()
+
+
+def test_bins_ctx_handoff(engine, oracle):
+    """Encoding in two launches with exported/imported contexts (WPP-style hand-off) keeps the models exact."""
+    rng = np.random.default_rng(5)
+    c1, c2 = random_cmds(rng, 400), random_cmds(rng, 400)
+    p = np.zeros(1, PARAMS_DT)
+    p[0] = (27, 1, 0, 0)
+    r1 = engine.encode_bins(c1, offsets_of([len(c1)]), p, offsets_of([4096]), want_ctx=True)
+    p2 = p.copy()
+    p2["flags"] = T | SUB_CTX_IN
+    r2 = engine.encode_bins(c2, offsets_of([len(c2)]), p2, offsets_of([4096]), ctx_in=r1["ctx_out"], want_ctx=True)
+    _, _, ectx1 = oracle.encode_bins(c1, 27, 1, 0, want_ctx=True)
+    assert (r1["ctx_out"][0] == ectx1).all()
+    eb, nb, ectx2 = oracle.encode_bins(c2, 27, 1, T, ctx_in=ectx1, want_ctx=True)
+    assert r2["out"][:r2["sizes"][0]].tobytes() == eb.tobytes() and (r2["ctx_out"][0] == ectx2).all()
+
+
+def test_long_ff_run_and_overflow(engine, oracle):
+    """Carry propagation through a long outstanding-byte run (numBufferedBytes), and the overflow status."""
+    cmds = np.asarray([mk_ctx(246, 1)] * 300 + [mk_ep(1, 1)] * 3000 + [mk_trm(0)], np.uint32)
+    p = np.zeros(1, PARAMS_DT)
+    p[0] = (51, 0, T, 0)
+    r = engine.encode_bins(cmds, offsets_of([len(cmds)]), p, offsets_of([1024]))
+    eb, nb = oracle.encode_bins(cmds, 51, 0, T)
+    assert r["out"][:r["sizes"][0]].tobytes() == eb.tobytes() and len(eb) > 300
+    r = engine.encode_bins(cmds, offsets_of([len(cmds)]), p, offsets_of([64]), raise_on_status=False)
+    assert int(r["status"][0]) & SS_OUT_OVERFLOW and int(r["sizes"][0]) == len(eb)
+    assert r["out"][:64].tobytes() == eb[:64].tobytes()
+
+
+# ---------------------------------------------------------------- (3) residual level
+def run_residual(engine, wl):
+    cap = wl.out_capacity(bytes_per_coeff=5.0)
+    r = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap, want_ctx=True)
+    return r, split(r["out"], cap, r["sizes"])
+
+
+def test_residual_golden_on_gpu(engine):
+    g = load_golden("residual")
+    for name in g["names"]:
+        wl = W.Workload(g[f"{name}_tus"], g[f"{name}_tu_offsets"], g[f"{name}_params"], g[f"{name}_coeffs"], name)
+        r, outs = run_residual(engine, wl)
+        meta, blob = g[f"{name}_meta"], g[f"{name}_bytes"]
+        pos = 0
+        for i in range(wl.n_sub):
+            nb, bits, nbytes = (int(v) for v in meta[i])
+            assert outs[i].tobytes() == blob[pos:pos + nbytes].tobytes(), (name, i)
+            pos += nbytes
+            assert int(r["num_bins"][i]) == nb
+            assert (ctx_pairs(r["ctx_out"][i]) == g[f"{name}_ctx"][i]).all()
+        assert (r["tu_flags"] == g[f"{name}_tu_flags"]).all()
+        # decode the reference's bytes
+        ioff = offsets_of(meta[:, 2])
+        d = engine.decode_residual(blob, ioff, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size, want_ctx=True)
+        assert (d["coeffs"] == g[f"{name}_decoded"]).all(), name
+        assert (d["bits_read"] == meta[:, 1]).all() and (d["num_bins"] == meta[:, 0]).all()
+        assert (d["tu_flags"] == g[f"{name}_tu_flags"]).all() and not d["status"].any()
+        assert (ctx_pairs(d["ctx_out"]) == g[f"{name}_ctx"]).all()
+
+
+@pytest.mark.parametrize("seed,flags,kw", [
+    (201, None, {}),
+    (202, T | SUB_SIGN_HIDING, {}),
+    (203, T | SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3}),
+    (204, T | SUB_DEP_QUANT | SUB_TSRC_DISABLED, {"ts_fraction": 0.4}),
+    (205, T | SUB_DEP_QUANT, {"sbt_fraction": 0.2, "bdpcm_fraction": 0.1}),
+    (206, T, {"preset": "qp0", "tus_per_sub": (1, 3)}),
+    (207, None, {"preset": "qp51", "tus_per_sub": (30, 60)}),
+])
+def test_residual_random_vs_oracle(engine, oracle, seed, flags, kw):
+    wl = W.random_substreams(40, seed, flags=flags, **kw)
+    r, outs = run_residual(engine, wl)
+    assert not r["status"].any()
+    for i in range(wl.n_sub):
+        a, b, lo, hi = sub_range(wl, i)
+        p = wl.params[i]
+        eb, nb, tuf, ectx = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]),
+                                                   int(p["flags"]), want_ctx=True)
+        assert outs[i].tobytes() == eb.tobytes(), (seed, i)
+        assert int(r["num_bins"][i]) == nb and (r["tu_flags"][a:b] == tuf).all()
+        assert (r["ctx_out"][i] == ectx).all()
+    ioff = offsets_of(r["sizes"])
+    d = engine.decode_residual(np.concatenate(outs), ioff, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size,
+                               want_ctx=True)
+    assert not d["status"].any()
+    assert (d["num_bins"] == r["num_bins"]).all() and (d["tu_flags"] == r["tu_flags"]).all()
+    assert (d["ctx_out"] == r["ctx_out"]).all()
+    assert (np.abs(d["coeffs"]) == np.abs(wl.coeffs)).all()
+    if not (wl.params["flags"] & SUB_SIGN_HIDING).any():
+        assert (d["coeffs"] == wl.coeffs).all()
+    else:  # hidden signs follow the parity rule: compare with the oracle's decode
+        for i in range(0, wl.n_sub, 7):
+            a, b, lo, hi = sub_range(wl, i)
+            p = wl.params[i]
+            od = oracle.decode_residual(outs[i], wl.tus[a:b], wl.coeffs.size, int(p["qp"]), int(p["init_id"]),
+                                        int(p["flags"]))
+            assert (od[0][lo:hi] == d["coeffs"][lo:hi]).all() and od[1] == int(d["bits_read"][i])
+
+
+def test_residual_all_shapes_single_coeff(engine, oracle):
+    """Every block shape 2..64 x 2..64, one level at DC / at the last coded column, extreme magnitudes."""
+    tus, coeffs, cur = [], [], 0
+    for lw in range(1, 7):
+        for lh in range(1, 7):
+            for pos, val in ((0, -3), ((1 << min(lw, 5)) - 1, 32767), (0, -32768)):
+                t = np.zeros(1, TU_DT)
+                t["coeff_offset"], t["log2_w"], t["log2_h"], t["comp_id"] = cur, lw, lh, (lw + lh) % 3
+                c = np.zeros(1 << (lw + lh), np.int32)
+                c[pos] = val
+                tus.append(t)
+                coeffs.append(c)
+                cur += c.size
+    tus, coeffs = np.concatenate(tus), np.concatenate(coeffs)
+    n = len(tus)
+    params = np.zeros(n, PARAMS_DT)
+    params["qp"], params["init_id"], params["flags"] = 30, 2, T | SUB_DEP_QUANT
+    wl = W.Workload(tus, np.arange(n + 1, dtype=np.uint64), params, coeffs)
+    r, outs = run_residual(engine, wl)
+    for i in range(n):
+        eb, nb, tuf = oracle.encode_residual(tus[i:i + 1], coeffs, 30, 2, T | SUB_DEP_QUANT)
+        assert outs[i].tobytes() == eb.tobytes(), (i, tus[i])
+    d = engine.decode_residual(np.concatenate(outs), offsets_of(r["sizes"]), tus, wl.tu_offsets, params, coeffs.size)
+    assert (d["coeffs"] == coeffs).all()
+
+
+def test_residual_errors(engine):
+    """Empty TU and output overflow are reported per substream, as the reference's CHECKs would throw."""
+    tus = np.zeros(2, TU_DT)
+    tus["log2_w"], tus["log2_h"] = 3, 3
+    tus["coeff_offset"] = [0, 64]
+    coeffs = np.zeros(128, np.int32)
+    coeffs[64 + 5] = 9
+    params = np.zeros(2, PARAMS_DT)
+    params["qp"], params["init_id"], params["flags"] = 32, 2, T
+    r = engine.encode_residual(tus, np.asarray([0, 1, 2], np.uint64), params, coeffs, offsets_of([64, 64]),
+                               raise_on_status=False)
+    assert int(r["status"][0]) & SS_EMPTY_TU and int(r["status"][1]) == 0
+    import entropy_coding_b200 as E
+    with pytest.raises(E.CabacError):
+        engine.encode_residual(tus, np.asarray([0, 1, 2], np.uint64), params, coeffs, offsets_of([64, 64]))
+    wl = W.random_substreams(2, 3, preset="qp0")
+    r = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, offsets_of([32, 32]),
+                               raise_on_status=False)
+    assert (r["status"] & SS_OUT_OVERFLOW).all() and (r["sizes"] > 32).all()
+
+
+def test_empty_batches(engine):
+    z64 = np.zeros(1, np.uint64)
+    r = engine.encode_residual(np.zeros(0, TU_DT), z64, np.zeros(0, PARAMS_DT), np.zeros(0, np.int32), z64)
+    assert len(r["sizes"]) == 0
+    # a substream with no TUs still terminates: trm(1) + finish + alignment == KAT0
+    p = np.zeros(1, PARAMS_DT)
+    p[0] = (32, 2, T, 0)
+    r = engine.encode_residual(np.zeros(0, TU_DT), np.zeros(2, np.uint64), p, np.zeros(0, np.int32),
+                               offsets_of([16]))
+    assert r["out"][:r["sizes"][0]].tobytes().hex() == "fe80"
+
+
+def test_pack_and_entry_points(engine):
+    wl = W.random_substreams(257, 77, tus_per_sub=(1, 6))
+    r, outs = run_residual(engine, wl)
+    packed, entry = engine.pack(r["out"], wl.out_capacity(bytes_per_coeff=5.0), r["sizes"])
+    assert packed.tobytes() == b"".join(o.tobytes() for o in outs)
+    assert (entry == offsets_of(r["sizes"])).all()
+
+
+# ---------------------------------------------------------------- full-size properties
+def test_full_size_round_trip_and_checksum(engine, oracle):
+    """At bench scale the oracle is too slow for every substream: check size-independent properties
+    (decode(encode(x)) == x, bins conserved) on everything and the oracle on a sample."""
+    wl = W.frames_as_ctu_substreams(4, 1920, 1080)  # 540 substreams, ~12.4 M coefficients
+    cap = wl.out_capacity()
+    r = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap)
+    outs = split(r["out"], cap, r["sizes"])
+    ioff = offsets_of(r["sizes"])
+    d = engine.decode_residual(np.concatenate(outs), ioff, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size)
+    assert (d["coeffs"] == wl.coeffs).all()
+    assert (d["num_bins"] == r["num_bins"]).all()
+    assert (d["bits_read"] <= 8 * r["sizes"]).all() and (d["bits_read"] > 8 * (r["sizes"].astype(np.int64) - 3)).all()
+    for i in range(0, wl.n_sub, 45):
+        a, b, lo, hi = sub_range(wl, i)
+        p = wl.params[i]
+        eb, nb, _ = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
+        assert outs[i].tobytes() == eb.tobytes() and nb == int(r["num_bins"][i])
