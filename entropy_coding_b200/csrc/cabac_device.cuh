@@ -87,11 +87,17 @@ struct OutStage {
   uint32_t flushed; // bytes already in global memory (multiple of 16)
 };
 
+// Lane 0 only.  When the ring is full (an outstanding-0xFF run longer than the
+// ring was released between two warp-wide flushes) lane 0 spills the whole ring
+// itself; rare, so the serial stores do not matter.
+__device__ __noinline__ void stage_spill(OutStage &o) {
+  for (uint32_t b = o.flushed; b < o.flushed + uint32_t(STAGE_BYTES); b++)
+    if (b < o.cap) o.dst[b] = o.ring[b & (STAGE_BYTES - 1)];
+  o.flushed += STAGE_BYTES;
+}
 __device__ __forceinline__ void stage_put(OutStage &o, uint32_t byte) {
+  if (o.n - o.flushed >= uint32_t(STAGE_BYTES)) stage_spill(o);
   o.ring[o.n & (STAGE_BYTES - 1)] = uint8_t(byte);
-  if (o.n - o.flushed >= uint32_t(STAGE_BYTES)) {  // ring overrun (long 0xFF-run release): direct store
-    if (o.n < o.cap) o.dst[o.n] = uint8_t(byte);
-  }
   o.n++;
 }
 
@@ -99,10 +105,8 @@ __device__ __forceinline__ void stage_put(OutStage &o, uint32_t byte) {
 // of [flushed, n) to global memory.
 __device__ inline void stage_flush(OutStage &o, int lane, bool final) {
   const uint32_t n = __shfl_sync(FULL, o.n, 0);
-  const uint32_t f = o.flushed;
-  const bool overrun = n - f > uint32_t(STAGE_BYTES);
-  const uint32_t lim = overrun ? f + STAGE_BYTES : n;
-  const uint32_t limChunks = lim & ~15u;
+  const uint32_t f = __shfl_sync(FULL, o.flushed, 0);  // lane 0 may have spilled
+  const uint32_t limChunks = n & ~15u;
   __syncwarp();
   if ((reinterpret_cast<uintptr_t>(o.dst) & 15u) == 0) {
     for (uint32_t b = f + 16u * lane; b < limChunks; b += 16u * 32u) {
@@ -117,7 +121,7 @@ __device__ inline void stage_flush(OutStage &o, int lane, bool final) {
     for (uint32_t b = f + lane; b < limChunks; b += 32u)
       if (b < o.cap) o.dst[b] = o.ring[b & (STAGE_BYTES - 1)];
   }
-  uint32_t nf = overrun ? (n & ~15u) : limChunks;
+  uint32_t nf = limChunks;
   if (final) {
     for (uint32_t b = nf + lane; b < n; b += 32u)
       if (b < o.cap) o.dst[b] = o.ring[b & (STAGE_BYTES - 1)];

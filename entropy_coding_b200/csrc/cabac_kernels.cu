@@ -126,7 +126,7 @@ encode_bins_kernel(const uint32_t *__restrict__ cmds, const uint64_t *__restrict
       __syncwarp();
       if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, n);
       __syncwarp();
-      if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+      if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
         stage_flush(enc.out, lane, false);
     }
     if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
@@ -457,12 +457,12 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
           }
           if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, nq);
           __syncwarp();
-          if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+          if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
             stage_flush(enc.out, lane, false);
         }
       }
       if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
-      if (__shfl_sync(FULL, enc.out.n, 0) - enc.out.flushed >= uint32_t(STAGE_BYTES / 2))
+      if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
         stage_flush(enc.out, lane, false);
     }
     if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
