@@ -1,0 +1,434 @@
+#!/usr/bin/env python
+"""bench.py - CABAC encode/decode throughput of the B200 engine (BASELINE.json metric).
+
+A "step" is one pass of the hot path over one batch: encode every substream of the
+batch (residual binarisation + arithmetic coder + substream packing) and decode the
+produced bitstreams back to coefficients.  Workload at every N: BASELINE.json
+configs[2], "synthetic 1080p all-intra batch, 64 frames", one substream per 128x128
+CTU (135 per frame, 8 640 per GPU); each rank codes its own 64 frames (weak scaling,
+no data-path collective - SURVEY.md section 8e).
+
+  value   Mbins/s with inputs resident in HBM (CUDA events on the launching stream,
+          max over ranks), bins = BinCounter::getAll() of encode + decode
+  e2e     same metric through the host-pointer C ABI (pinned host buffers, H2D of the
+          coefficient slab / bitstreams and D2H of the results inside the timed region)
+  roofline / issue_roofline   dominant kernel vs measured HBM copy bandwidth, and vs the
+          per-SM integer issue bound (north_star)
+  cpu_baseline  the compiled reference (oracle/_ref) - or the C port when it is absent -
+          on this box's host cores over a bounded sample of the same workload
+
+`--impl reference` times only the CPU reference with all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cabac_encode_decode_throughput"
+UNIT = "Mbins/s"
+WORKLOAD = "1080p-all-intra-64-frames, one substream per 128x128 CTU (8640 substreams/GPU), mixed qp0/qp32/qp51 presets"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=64, help="frames per GPU (64 = the BASELINE config)")
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-frames", type=int, default=16)
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # samples under load = the upper half (the sampler also sees the idle edges)
+        hi = sorted(sm)[len(sm) // 2:]
+        return {"sm_mhz": float(np.median(hi)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- CPU reference leg
+def cpu_checker():
+    """The compiled reference when it travelled with the repo (oracle/_ref), else the C port."""
+    from oracle import checker
+    if checker.available("ref"):
+        return checker.Checker("ref"), "reference"
+    if not checker.available("oracle"):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"])
+    return checker.Checker("oracle"), "port"
+
+
+def host_threads() -> int:
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_pass(chk, wl, threads):
+    """One encode + decode pass of the CPU reference over a workload.  Returns (seconds, bins)."""
+    cap = wl.out_capacity()
+    out = np.zeros(int(cap[-1]), np.uint8)
+    sizes = np.zeros(wl.n_sub, np.uint32)
+    t_enc, bins, _ = chk.time_encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, threads, out, cap, sizes)
+    dec = np.zeros(wl.coeffs.size, np.int32)
+    t_dec = chk.time_decode_residual(out, cap, sizes, wl.tus, wl.tu_offsets, wl.params, dec, threads)
+    assert (dec == wl.coeffs).all(), "CPU reference decode(encode(x)) != x"
+    return t_enc, t_dec, bins
+
+
+def run_reference_arm(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from entropy_coding_b200 import workload as W
+    chk, kind = cpu_checker()
+    threads = host_threads()
+    frames = max(1, min(args.cpu_sample_frames, args.frames))
+    wl = W.frames_as_ctu_substreams(frames, args.width, args.height, seed0=1000)
+    for _ in range(max(1, args.warmup)):
+        cpu_pass(chk, wl, threads)
+    t_enc = t_dec = 0.0
+    bins = 0
+    for _ in range(args.steps):
+        a, b, n = cpu_pass(chk, wl, threads)
+        t_enc += a; t_dec += b; bins += 2 * n
+    total = t_enc + t_dec
+    val = bins / total / 1e6
+    sample = (f"{frames} of {args.frames} frames ({wl.n_sub} substreams, {bins // (2 * args.steps)} bins) per step, "
+              f"encode+decode, {threads} threads, dynamic substream hand-out")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "encode_mbins_s": bins / 2 / t_enc / 1e6, "decode_mbins_s": bins / 2 / t_dec / 1e6,
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- B200 arm
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def load_profile_facts():
+    """ncu-derived per-launch facts committed under profiles/ (traffic, instructions per bin)."""
+    p = os.path.join(ROOT, "profiles", "kernel_facts.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p))
+        except Exception:
+            pass
+    return {}
+
+
+def dev_bytes(t, a: np.ndarray):
+    """numpy array (any dtype, incl. structured) -> device uint8 tensor."""
+    import torch
+    return torch.from_numpy(np.frombuffer(a.tobytes(), np.uint8).copy()).to(t)
+
+
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    import entropy_coding_b200 as E
+    from entropy_coding_b200 import workload as W
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - entropy_coding_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- workload: this rank's 64 frames (weak scaling: different frames per rank) ----
+    wl = W.frames_as_ctu_substreams(args.frames, args.width, args.height, seed0=1000 + rank * args.frames)
+    n_sub, n_tu, n_co = wl.n_sub, len(wl.tus), int(wl.coeffs.size)
+    cap = wl.out_capacity()
+    eng = E.CabacEngine(local_rank)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+
+    d_tus, d_tuoff = dev_bytes(dev, wl.tus), dev_bytes(dev, wl.tu_offsets)
+    d_par, d_cap = dev_bytes(dev, wl.params), dev_bytes(dev, cap)
+    d_co = torch.from_numpy(wl.coeffs).to(dev)
+    d_out = torch.empty(int(cap[-1]), dtype=torch.uint8, device=dev)
+    d_packed = torch.empty(int(cap[-1]), dtype=torch.uint8, device=dev)
+    d_entry = torch.zeros(n_sub + 1, dtype=torch.int64, device=dev)
+    d_sizes = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_ebins = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_est = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_eflags = torch.zeros(n_tu, dtype=torch.uint8, device=dev)
+    d_dec = torch.empty(n_co, dtype=torch.int32, device=dev)
+    d_dbins = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_dbits = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_dst = torch.zeros(n_sub, dtype=torch.int32, device=dev)
+    d_dflags = torch.zeros(n_tu, dtype=torch.uint8, device=dev)
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    t_kernel = {"encode_residual_kernel": 0.0, "pack": 0.0, "decode_residual_kernel": 0.0}
+
+    def step(timed):
+        e = [ev() for _ in range(4)] if timed else None
+        if timed: e[0].record(stream)
+        eng.encode_residual_dev(d_tus, d_tuoff, d_par, n_sub, d_co, d_out, d_cap, d_sizes, d_ebins, d_eflags,
+                                status=d_est)
+        if timed: e[1].record(stream)
+        eng.pack_dev(d_out, d_cap, d_sizes, n_sub, d_packed, d_entry)
+        if timed: e[2].record(stream)
+        eng.decode_residual_dev(d_packed, d_entry, d_tus, d_tuoff, d_par, n_sub, d_dec, d_dbins, d_dbits, d_dflags,
+                                status=d_dst)
+        if timed: e[3].record(stream)
+        return e
+
+    for _ in range(max(args.warmup, 3)):  # never fewer than 3 warm-up steps
+        step(False)
+    barrier()
+    launches0 = eng.launch_count
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    t0, t1 = ev(), ev()
+    t0.record(stream)
+    evs = [step(True) for _ in range(args.steps)]
+    t1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    launches = eng.launch_count - launches0
+    elapsed_ms = t0.elapsed_time(t1)
+    for e in evs:
+        t_kernel["encode_residual_kernel"] += e[0].elapsed_time(e[1])
+        t_kernel["pack"] += e[1].elapsed_time(e[2])
+        t_kernel["decode_residual_kernel"] += e[2].elapsed_time(e[3])
+    for k in t_kernel:
+        t_kernel[k] /= args.steps
+
+    # ---- correctness of what was timed ----
+    assert int(d_est.abs().max()) == 0 and int(d_dst.abs().max()) == 0, "substream status set"
+    assert torch.equal(d_dec, d_co), "decode(encode(x)) != x on the timed batch"
+    assert torch.equal(d_ebins, d_dbins), "encoder and decoder disagree on bin counts"
+    enc_bins = int(d_ebins.to(torch.int64).sum())
+    out_bytes = int(d_sizes.to(torch.int64).sum())
+    bins_step = 2 * enc_bins
+
+    tt = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    tb = torch.tensor([float(bins_step)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tb, op=dist.ReduceOp.SUM)
+    ms_per_step = float(tt) / args.steps
+    value = float(tb) / (ms_per_step * 1e-3) / 1e6
+    res = dict(wl=wl, cap=cap, eng=eng, value=value, ms_per_step=ms_per_step, t_kernel=t_kernel, clk=clk,
+               launches=launches, enc_bins=enc_bins, out_bytes=out_bytes, n_sub=n_sub, n_tu=n_tu, n_co=n_co,
+               world=world, rank=rank, dev=dev, barrier=barrier, all_bins=float(tb))
+    # free the device-resident buffers before the end-to-end leg allocates its own
+    del d_out, d_packed, d_dec, d_co
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_e2e(args, r):
+    """The same step through the host-pointer C ABI: pinned host buffers in, pinned host buffers out."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    eng, wl, cap = r["eng"], r["wl"], r["cap"]
+    n_sub, n_tu, n_co = r["n_sub"], r["n_tu"], r["n_co"]
+    lib, h = eng.lib, eng.h
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    h_tus, h_tuoff = eng.pinned_copy(wl.tus), eng.pinned_copy(wl.tu_offsets)
+    h_par, h_cap, h_co = eng.pinned_copy(wl.params), eng.pinned_copy(cap), eng.pinned_copy(wl.coeffs)
+    packed_cap = int(r["out_bytes"] * 1.25) + 4096
+    h_packed = eng.host_array(packed_cap, np.uint8)
+    h_entry = eng.host_array(n_sub + 1, np.uint64)
+    h_sizes, h_ebins, h_est = (eng.host_array(n_sub, np.uint32) for _ in range(3))
+    h_eflags, h_dflags = eng.host_array(n_tu, np.uint8), eng.host_array(n_tu, np.uint8)
+    h_dec = eng.host_array(n_co, np.int32)
+    h_dbins, h_dbits, h_dst = (eng.host_array(n_sub, np.uint32) for _ in range(3))
+
+    def step():
+        rc = lib.cabac_encode_residual_packed(h, P(h_tus), P(h_tuoff), P(h_par), n_sub, P(h_co), n_co, None,
+                                              P(h_cap), P(h_packed), packed_cap, P(h_entry), P(h_sizes),
+                                              P(h_ebins), P(h_eflags), None, P(h_est))
+        assert rc == 0, (rc, lib.cabac_last_error(h))
+        rc = lib.cabac_decode_residual(h, P(h_packed), P(h_entry), P(h_tus), P(h_tuoff), P(h_par), n_sub, None,
+                                       P(h_dec), n_co, P(h_dbins), P(h_dbits), P(h_dflags), None, P(h_dst))
+        assert rc == 0, (rc, lib.cabac_last_error(h))
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    r["barrier"]()
+    launches0 = eng.launch_count
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    r["barrier"]()
+    assert (h_dec == wl.coeffs).all() and (h_ebins == h_dbins).all(), "e2e round trip failed"
+    total = int(h_entry[n_sub])
+    tt = torch.tensor([dt], dtype=torch.float64, device=r["dev"])
+    if r["world"] > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    small = h_tus.nbytes + h_tuoff.nbytes + h_par.nbytes
+    h2d = (h_co.nbytes + small + h_cap.nbytes) + (total + h_entry.nbytes + small)
+    d2h = (total + h_entry.nbytes + 3 * h_sizes.nbytes + h_eflags.nbytes) + (h_dec.nbytes + 3 * h_dbins.nbytes + h_dflags.nbytes)
+    return {"value": r["all_bins"] * args.steps / float(tt) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(tt) / args.steps,
+            "gpu_launches": int(eng.launch_count - launches0),
+            "api": "cabac_encode_residual_packed + cabac_decode_residual (host pointers, pinned)"}
+
+
+def run_cpu_baseline(args, r):
+    chk, kind = cpu_checker()
+    threads = host_threads()
+    frames = max(1, min(args.cpu_sample_frames, args.frames))
+    per_frame = r["n_sub"] // args.frames
+    sample = r["wl"].subset(range(frames * per_frame))
+    cpu_pass(chk, sample, threads)  # warm-up (first-touch pages, thread start-up)
+    t_enc, t_dec, bins = cpu_pass(chk, sample, threads)
+    t1_enc, t1_dec, bins1 = cpu_pass(chk, r["wl"].subset(range(per_frame)), 1)
+    return {"value": 2 * bins / (t_enc + t_dec) / 1e6, "unit": UNIT, "cores": threads, "kind": kind,
+            "sample": f"frames 0-{frames - 1} of the timed batch ({sample.n_sub} substreams, {bins} bins), "
+                      f"encode+decode, {threads} threads, dynamic substream hand-out",
+            "encode_mbins_s": bins / t_enc / 1e6, "decode_mbins_s": bins / t_dec / 1e6,
+            "single_thread_mbins_s": 2 * bins1 / (t1_enc + t1_dec) / 1e6}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    r = run_b200_arm(args)
+    e2e = None if args.no_e2e else run_e2e(args, r)
+    if r["rank"] != 0:
+        return
+    peak, peak_src = load_peaks()
+    facts = load_profile_facts()
+    tk = r["t_kernel"]
+    dom = max(("encode_residual_kernel", "decode_residual_kernel"), key=lambda k: tk[k])
+    # algorithmic bytes per launch: int32 coefficient positions + 16 B per TU
+    # descriptor + bitstream bytes (written by the encoder / read by the decoder)
+    alg = 4 * r["n_co"] + 16 * r["n_tu"] + r["out_bytes"]
+    achieved = alg / (tk[dom] * 1e-3) / 1e9
+    sm_mhz = (r["clk"].get("sm_mhz") or 1965.0)
+    roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": facts.get(dom, {}).get("dram_bytes_per_launch"),
+            "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+            "kernel_ms": {k: round(v, 4) for k, v in tk.items()},
+            "note": "integer/latency-bound serial recurrence: see issue_roofline; HBM is not the binding resource"}
+    ipb = facts.get(dom, {}).get("warp_instr_per_bin")
+    issue = {"kernel": dom, "warp_instr_per_bin": ipb, "sm_count": 148, "sm_mhz": sm_mhz,
+             "mbins_s_achieved": r["enc_bins"] / (tk[dom] * 1e-3) / 1e6}
+    if ipb:
+        # 4 warp-instruction issue slots per SM per clock
+        bound = 148 * 4 * sm_mhz * 1e6 / ipb / 1e6
+        issue.update({"mbins_s_bound": bound, "frac": issue["mbins_s_achieved"] / bound})
+    line = {
+        "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_gpu": args.frames, "substreams_per_gpu": r["n_sub"],
+                   "tus_per_gpu": r["n_tu"], "coeff_positions_per_gpu": r["n_co"],
+                   "bins_per_step_per_gpu": 2 * r["enc_bins"], "bitstream_bytes_per_gpu": r["out_bytes"],
+                   "l2": "inputs larger than L2 (coefficient slab %.0f MB per pass)" % (4 * r["n_co"] / 1e6),
+                   "step": "encode_residual + pack + decode_residual"},
+        "encode_mbins_s": r["enc_bins"] / (tk["encode_residual_kernel"] + tk["pack"]) / 1e3,
+        "decode_mbins_s": r["enc_bins"] / tk["decode_residual_kernel"] / 1e3,
+        "output_mb_s": r["out_bytes"] / (tk["encode_residual_kernel"] + tk["pack"]) / 1e3,
+        "clocks": r["clk"], "gpu_launches": int(r["launches"]), "roofline": roof, "issue_roofline": issue,
+        "verified": "decode(encode(x)) == x and equal bin counts on the timed batch",
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if r["world"] == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = run_cpu_baseline(args, r)
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

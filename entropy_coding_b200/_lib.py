@@ -23,6 +23,9 @@ _SIGS = {
     "cabac_last_error": (C.c_char_p, [_P]),
     "cabac_version": (C.c_char_p, []),
     "cabac_launch_count": (C.c_uint64, [_P]),
+    "cabac_host_alloc": (_P, [_SZ]),
+    "cabac_host_free": (None, [_P]),
+    "cabac_encode_residual_packed": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P]),
     "cabac_ctx_init": (C.c_int, [_P, _P, _SZ, _P]),
     "cabac_ctx_init_dev": (C.c_int, [_P, _P, _SZ, _P]),
     "cabac_ctx_rates": (C.c_int, [_P]),

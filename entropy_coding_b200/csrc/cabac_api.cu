@@ -137,6 +137,15 @@ int cabac_sync(cabac_handle *h) {
 const char *cabac_last_error(cabac_handle *h) { return h ? h->err.c_str() : "null handle"; }
 uint64_t cabac_launch_count(cabac_handle *h) { return h ? h->launches : 0; }
 
+void *cabac_host_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+void cabac_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
 int cabac_ctx_rates(uint8_t *rates_out) {
   if (!rates_out) return CABAC_ERR_ARG;
   const unsigned char *win = cabac::hostInitTable(3);
@@ -409,6 +418,71 @@ int cabac_encode_residual(cabac_handle *h, const cabac_tu_desc *tus, const uint6
   return anySubstreamFailed(hst, n_sub);
 }
 
+int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                 const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                 size_t n_coeffs, const cabac_ctx_model *ctx_in, const uint64_t *out_offsets,
+                                 uint8_t *packed, size_t packed_cap, uint64_t *entry_points, uint32_t *out_sizes,
+                                 uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                 uint32_t *status) {
+  if (!h || !entry_points || (n_sub && (!tu_offsets || !params || !out_offsets || !packed)))
+    return badArg(h, "cabac_encode_residual_packed");
+  if (!n_sub) {
+    entry_points[0] = 0;
+    return CABAC_OK;
+  }
+  DeviceGuard g(h->device);
+  const size_t nTu = tu_offsets[n_sub], outCap = out_offsets[n_sub];
+  if (nTu && (!tus || !coeffs)) return badArg(h, "cabac_encode_residual_packed: tus/coeffs");
+  cabac_tu_desc *dTus;
+  uint64_t *dTuOff, *dOutOff, *dEntry;
+  cabac_substream_params *dP;
+  int32_t *dCoeffs;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dOut, *dTuFlags, *dPacked;
+  uint32_t *dSizes, *dBins, *dStatus;
+  Arena a(h);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dEntry, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCoeffs, n_coeffs * 4);
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dOut, outCap);
+  a.want((void **)&dPacked, outCap);
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dSizes, n_sub * 4);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  int rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
+                                     dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  rc = cabac_pack_dev(h, dOut, dOutOff, dSizes, n_sub, dPacked, dEntry);
+  if (rc) return rc;
+  D2H(entry_points, dEntry, (n_sub + 1) * 8);
+  D2H(out_sizes, dSizes, n_sub * 4);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(tu_flags, dTuFlags, nTu);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  const size_t total = entry_points[n_sub];
+  if (total > packed_cap) return badArg(h, "cabac_encode_residual_packed: packed_cap too small");
+  D2H(packed, dPacked, total);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
 int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const cabac_tu_desc *tus,
                           const uint64_t *tu_offsets, const cabac_substream_params *params, size_t n_sub,
                           const cabac_ctx_model *ctx_in, int32_t *coeffs, size_t n_coeffs, uint32_t *num_bins,
@@ -445,8 +519,8 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
   H2D(dIn, in, nIn);
-  // blocks no descriptor points at keep the caller's values
-  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  // positions no descriptor covers come back as zero
+  CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
   int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
                                      dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
   if (rc) return rc;

@@ -548,7 +548,8 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
 // ---------------------------------------------------------------------------
 // Single-CTA exclusive scan of the substream sizes (n_sub <= ~10^6: a few
 // dozen microseconds; the sizes are 4 bytes per substream).
-__global__ void __launch_bounds__(1024) entry_points_kernel(const uint32_t *__restrict__ sizes, size_t n,
+__global__ void __launch_bounds__(1024) entry_points_kernel(const uint32_t *__restrict__ sizes,
+                                                            const uint64_t *__restrict__ capOffsets, size_t n,
                                                             uint64_t *__restrict__ entry) {
   __shared__ uint64_t warpSums[32];
   __shared__ uint64_t carry;
@@ -557,7 +558,8 @@ __global__ void __launch_bounds__(1024) entry_points_kernel(const uint32_t *__re
   __syncthreads();
   for (size_t base = 0; base < n; base += blockDim.x) {
     const size_t i = base + threadIdx.x;
-    const uint64_t v = i < n ? sizes[i] : 0;
+    uint64_t v = i < n ? sizes[i] : 0;
+    if (i < n && v > capOffsets[i + 1] - capOffsets[i]) v = capOffsets[i + 1] - capOffsets[i];  // overflowed slab
     uint64_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -597,7 +599,8 @@ __global__ void __launch_bounds__(256) pack_kernel(const uint8_t *__restrict__ o
   for (size_t s = warp; s < n; s += nWarps) {
     const uint8_t *src = out + outOffsets[s];
     uint8_t *dst = packed + entry[s];
-    const uint32_t len = sizes[s];
+    uint32_t len = sizes[s];
+    if (len > outOffsets[s + 1] - outOffsets[s]) len = uint32_t(outOffsets[s + 1] - outOffsets[s]);
     // head: bytes up to the destination's 16-byte boundary
     uint32_t head = uint32_t((16 - (reinterpret_cast<uintptr_t>(dst) & 15u)) & 15u);
     if (head > len) head = len;
@@ -728,7 +731,7 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const uint8_t *in, 
 
 cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
                        const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints) {
-  entry_points_kernel<<<1, 1024, 0, s>>>(outSizes, nSub, entryPoints);
+  entry_points_kernel<<<1, 1024, 0, s>>>(outSizes, outOffsets, nSub, entryPoints);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess || nSub == 0) return e;
   int sms = 148;

@@ -57,6 +57,9 @@ class CabacEngine:
         if getattr(self, "h", None):
             self.lib.cabac_destroy(self.h)
             self.h = None
+            for p in getattr(self, "_pinned", []):
+                self.lib.cabac_host_free(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -81,6 +84,23 @@ class CabacEngine:
     @property
     def launch_count(self) -> int:
         return int(self.lib.cabac_launch_count(self.h))
+
+    # ---- pinned host buffers -------------------------------------------------
+    def host_array(self, n: int, dtype) -> np.ndarray:
+        """numpy array over page-locked memory (cabac_host_alloc); freed with the engine."""
+        dt = np.dtype(dtype)
+        p = self.lib.cabac_host_alloc(max(1, n * dt.itemsize))
+        if not p:
+            raise CabacError(-1, "cabac_host_alloc failed")
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(p)
+        buf = (C.c_uint8 * max(1, n * dt.itemsize)).from_address(p)
+        return np.frombuffer(buf, dtype=dt, count=n)
+
+    def pinned_copy(self, a: np.ndarray) -> np.ndarray:
+        out = self.host_array(a.size, a.dtype)
+        out[...] = a.reshape(-1)
+        return out
 
     # ---- tables -------------------------------------------------------------
     def ctx_rates(self) -> np.ndarray:
@@ -146,12 +166,35 @@ class CabacEngine:
             self._check(rc, status)
         return dict(out=out, sizes=sizes, num_bins=bins, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
 
+    def encode_residual_packed(self, tus, tu_offsets, params, coeffs, out_offsets, packed=None, ctx_in=None,
+                               want_ctx=False, raise_on_status=True):
+        """Encode + pack: returns the substreams concatenated in order plus the entry-point table."""
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        n = len(params)
+        if packed is None:
+            packed = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        entry = np.zeros(n + 1, np.uint64)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_residual_packed(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
+                                                   coeffs.size, _hp(ctx_in), _hp(out_offsets), _hp(packed),
+                                                   packed.size, _hp(entry), _hp(sizes), _hp(bins), _hp(tu_flags),
+                                                   _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(packed=packed[:int(entry[-1])], entry_points=entry, sizes=sizes, num_bins=bins,
+                    tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
     def decode_residual(self, data, in_offsets, tus, tu_offsets, params, n_coeffs, ctx_in=None, want_ctx=False,
-                        raise_on_status=True):
+                        raise_on_status=True, coeffs_out=None):
         data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
         tus, tu_offsets, params = _np(tus, TU_DT), _np(tu_offsets, np.uint64), _np(params, PARAMS_DT)
         n = len(params)
-        coeffs = np.zeros(n_coeffs, np.int32)
+        coeffs = np.zeros(n_coeffs, np.int32) if coeffs_out is None else coeffs_out
+        assert coeffs.dtype == np.int32 and coeffs.size >= n_coeffs and coeffs.flags.c_contiguous
         bins, bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
         tu_flags = np.zeros(len(tus), np.uint8)
         ctx_in = _np(ctx_in, CTX_DT)

@@ -165,6 +165,11 @@ const char *cabac_version(void);
 /* Number of kernel launches issued through this handle so far.              */
 uint64_t cabac_launch_count(cabac_handle *h);
 
+/* Page-locked host memory for the host-pointer entry points (any host pointer
+ * is accepted; pinned buffers let the H2D / D2H copies run at link speed).  */
+void *cabac_host_alloc(size_t bytes);
+void cabac_host_free(void *p);
+
 /* ---- (2) context initialisation ----------------------------------------- */
 /* Ctx::init(qp, initId) for n (qp, init_id) pairs, contexts.cpp:996-1015,
  * 893-901.  out: n * CABAC_NUM_CTX models.                                   */
@@ -250,11 +255,29 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus,
                               uint32_t *num_bins, uint8_t *tu_flags,
                               cabac_ctx_model *ctx_out, uint32_t *status);
 
+/* Host-pointer encode that returns what the slice writer consumes
+ * (EncSlice.cpp:2114-2125, EncGOP.cpp:3811-3824): the substreams compacted in
+ * order into `packed` plus the entry-point table, i.e. cabac_encode_residual
+ * followed by cabac_pack with a single D2H copy of the produced bytes.
+ * out_offsets describes the per-substream capacity of the DEVICE-side slab
+ * only; entry_points has n_sub + 1 entries; packed_cap bounds `packed`.     */
+int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus,
+                                 const uint64_t *tu_offsets,
+                                 const cabac_substream_params *params,
+                                 size_t n_sub, const int32_t *coeffs,
+                                 size_t n_coeffs, const cabac_ctx_model *ctx_in,
+                                 const uint64_t *out_offsets, uint8_t *packed,
+                                 size_t packed_cap, uint64_t *entry_points,
+                                 uint32_t *out_sizes, uint32_t *num_bins,
+                                 uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                 uint32_t *status);
+
 /* Mirror of the above.  The kernel zeroes each TU's coefficient block before
  * parsing (the reference requires the caller to pre-zero,
  * cabac_reader.cpp:2952-2953).  descriptor flag CABAC_TU_TS is ignored when
  * CABAC_TU_TS_ALLOWED is set (the flag is parsed) and otherwise supplies the
- * inferred value (cabac_reader.cpp:2738-2741).
+ * inferred value (cabac_reader.cpp:2738-2741).  The host-pointer flavour
+ * returns the whole slab: positions no descriptor covers come back as zero.
  */
 int cabac_decode_residual(cabac_handle *h, const uint8_t *in,
                           const uint64_t *in_offsets, const cabac_tu_desc *tus,

@@ -1419,11 +1419,13 @@ typedef struct {
   const uint64_t *inOffsets;
   const uint32_t *inSizes;
   uint64_t bins, bytes;
+  long *next; /* shared work counter: substreams are handed out dynamically */
 } Job;
 
 static void *job_run(void *arg) {
   Job *j = (Job *)arg;
-  for (long i = j->k; i < j->nSub; i += j->nthreads) {
+  for (long i = __atomic_fetch_add(j->next, 1, __ATOMIC_RELAXED); i < j->nSub;
+       i = __atomic_fetch_add(j->next, 1, __ATOMIC_RELAXED)) {
     const cabac_tu_desc *t = j->tus + j->tuOffsets[i];
     const long nt = (long)(j->tuOffsets[i + 1] - j->tuOffsets[i]);
     if (j->decode) {
@@ -1448,9 +1450,11 @@ static double run_jobs(Job *proto, int nthreads, uint64_t *bins, uint64_t *bytes
   Job *jobs = (Job *)calloc((size_t)nthreads, sizeof(Job));
   pthread_t *th = (pthread_t *)calloc((size_t)nthreads, sizeof(pthread_t));
   struct timespec t0, t1;
+  long next = 0;
   clock_gettime(CLOCK_MONOTONIC, &t0);
   for (int k = 0; k < nthreads; k++) {
     jobs[k] = *proto;
+    jobs[k].next = &next;
     jobs[k].k = k;
     jobs[k].nthreads = nthreads;
     pthread_create(&th[k], NULL, job_run, &jobs[k]);

@@ -388,8 +388,8 @@ long ref_decode_residual(const uint8_t *in, long nbytes,
 }
 
 // ---- timed batch runs for the CPU baseline --------------------------------
-// Substreams are statically interleaved over nthreads host threads, one coder
-// object per thread.  Returns wall seconds; totals via the out pointers.
+// Substreams are handed out dynamically (atomic counter) to nthreads host
+// threads, one coder object per call.  Returns wall seconds; totals via the out pointers.
 double ref_time_encode_residual(const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets,
                                 const cabac_substream_params *params,
@@ -400,12 +400,14 @@ double ref_time_encode_residual(const cabac_tu_desc *tus,
                                 uint32_t *outSizes) {
   ensureRom();
   std::atomic<uint64_t> bins{0}, bytes{0};
+  std::atomic<long> next{0};
   auto t0 = std::chrono::steady_clock::now();
   std::vector<std::thread> th;
   for (int k = 0; k < nthreads; k++) {
     th.emplace_back([&, k] {
       uint64_t b = 0, by = 0;
-      for (long i = k; i < nSub; i += nthreads) {
+      (void)k;
+      for (long i = next++; i < nSub; i = next++) {
         uint32_t nb = 0;
         uint8_t *o = out ? out + outOffsets[i] : nullptr;
         long cap = out ? (long)(outOffsets[i + 1] - outOffsets[i]) : 0;
@@ -435,11 +437,13 @@ double ref_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets,
                                 const cabac_substream_params *params,
                                 long nSub, int32_t *coeffs, int nthreads) {
   ensureRom();
+  std::atomic<long> next{0};
   auto t0 = std::chrono::steady_clock::now();
   std::vector<std::thread> th;
   for (int k = 0; k < nthreads; k++) {
     th.emplace_back([&, k] {
-      for (long i = k; i < nSub; i += nthreads) {
+      (void)k;
+      for (long i = next++; i < nSub; i = next++) {
         ref_decode_residual(in + inOffsets[i], (long)inSizes[i],
                             tus + tuOffsets[i],
                             (long)(tuOffsets[i + 1] - tuOffsets[i]), &params[i],
