@@ -230,7 +230,10 @@ def run_b200_arm(args):
     n_sub, n_tu, n_co = wl.n_sub, len(wl.tus), int(wl.coeffs.size)
     cap = wl.out_capacity()
     eng = E.CabacEngine(local_rank)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: kernels, copies and the timing events all go onto it
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     eng.set_stream(stream.cuda_stream)
 
     d_tus, d_tuoff = dev_bytes(dev, wl.tus), dev_bytes(dev, wl.tu_offsets)
