@@ -23,6 +23,9 @@ struct cabac_handle {
   // grow-only device scratch for the host-pointer entry points
   void *scratch = nullptr;
   size_t scratchBytes = 0;
+  // scheduler scratch (cost / order / cursor), grow-only
+  uint32_t *sched = nullptr;
+  size_t schedSubs = 0;
 };
 
 namespace {
@@ -74,6 +77,24 @@ struct Arena {
   }
 };
 
+// Scheduler scratch for n substreams.  Stream-ordered use only, so growing it
+// (free + malloc, both synchronising) is safe.
+cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
+  if (n > h->schedSubs) {
+    if (h->sched) cudaFree(h->sched);
+    h->sched = nullptr;
+    h->schedSubs = 0;
+    const size_t cap = n + (n >> 2) + 1024;
+    cudaError_t e = cudaMalloc(&h->sched, (2 * cap + 64) * sizeof(uint32_t));
+    if (e != cudaSuccess) return e;
+    h->schedSubs = cap;
+  }
+  sc.cursor = h->sched;
+  sc.cost = h->sched + 64;
+  sc.order = h->sched + 64 + h->schedSubs;
+  return cudaSuccess;
+}
+
 #define CK(call, what)                                   \
   do {                                                   \
     cudaError_t e__ = (call);                            \
@@ -117,6 +138,7 @@ void cabac_destroy(cabac_handle *h) {
   DeviceGuard g(h->device);
   cudaStreamSynchronize(h->stream);
   if (h->scratch) cudaFree(h->scratch);
+  if (h->sched) cudaFree(h->sched);
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
 }
@@ -178,10 +200,12 @@ int cabac_encode_bins_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t 
   if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)))
     return badArg(h, "cabac_encode_bins_dev");
   DeviceGuard g(h->device);
-  CK(cabac::launchEncodeBins(h->stream, h->device, cmds, cmd_offsets, params, n_sub, ctx_in, out, out_offsets,
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchEncodeBins(h->stream, h->device, sc, cmds, cmd_offsets, params, n_sub, ctx_in, out, out_offsets,
                              out_sizes, num_bins, ctx_out, status),
      "encode_bins_kernel");
-  h->launches += n_sub ? 1 : 0;
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
   return CABAC_OK;
 }
 
@@ -191,10 +215,12 @@ int cabac_decode_bins_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in
                           cabac_ctx_model *ctx_out, uint32_t *status) {
   if (!h || (n_sub && (!in || !in_offsets || !cmd_offsets || !params))) return badArg(h, "cabac_decode_bins_dev");
   DeviceGuard g(h->device);
-  CK(cabac::launchDecodeBins(h->stream, h->device, in, in_offsets, cmds, cmd_offsets, params, n_sub, ctx_in,
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchDecodeBins(h->stream, h->device, sc, in, in_offsets, cmds, cmd_offsets, params, n_sub, ctx_in,
                              values, bits_read, ctx_out, status),
      "decode_bins_kernel");
-  h->launches += n_sub ? 1 : 0;
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
   return CABAC_OK;
 }
 
@@ -206,10 +232,12 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!h || (n_sub && (!tu_offsets || !params || !out || !out_offsets || !out_sizes)))
     return badArg(h, "cabac_encode_residual_dev");
   DeviceGuard g(h->device);
-  CK(cabac::launchEncodeResidual(h->stream, h->device, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchEncodeResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
                                  out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
      "encode_residual_kernel");
-  h->launches += n_sub ? 1 : 0;
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
   return CABAC_OK;
 }
 
@@ -221,10 +249,12 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
   if (!h || (n_sub && (!in || !in_offsets || !tu_offsets || !params || !coeffs)))
     return badArg(h, "cabac_decode_residual_dev");
   DeviceGuard g(h->device);
-  CK(cabac::launchDecodeResidual(h->stream, h->device, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchDecodeResidual(h->stream, h->device, sc, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
                                  coeffs, num_bins, bits_read, tu_flags, ctx_out, status),
      "decode_residual_kernel");
-  h->launches += n_sub ? 1 : 0;
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
   return CABAC_OK;
 }
 

@@ -7,7 +7,7 @@
 
 #include <cstring>
 
-#include "cabac_residual.cuh"
+#include "cabac_lockstep.cuh"
 #include "cabac_kernels.h"
 
 namespace cabac {
@@ -23,6 +23,90 @@ namespace hosttab {
 constexpr int WARPS_PER_BLOCK = 4;
 
 __device__ __forceinline__ int clipQp(int qp) { return qp < 0 ? 0 : (qp > 63 ? 63 : qp); }
+
+// ---------------------------------------------------------------------------
+// Work distribution.  Substreams differ in length by orders of magnitude (a
+// QP0 CTU carries ~40x the bins of a QP51 one) and each is a serial chain, so
+// the makespan is set by when the longest ones START.  Every launch therefore
+// (1) estimates a cost per substream, (2) orders substreams longest-first with a
+// 256-bucket counting sort on a log-scale key, and (3) runs persistent warps
+// that pull the next substream from an atomic cursor (LPT list scheduling).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool nextSubstream(const uint32_t *__restrict__ order, uint32_t *cursor, size_t nSub,
+                                              int lane, size_t &sub) {
+  uint32_t i = 0;
+  if (lane == 0) i = atomicAdd(cursor, 1u);
+  i = __shfl_sync(FULL, i, 0);
+  if (i >= nSub) return false;
+  sub = order ? size_t(order[i]) : size_t(i);
+  return true;
+}
+
+// decode: bitstream bytes are an excellent proxy for bins
+__global__ void cost_bytes_kernel(const uint64_t *__restrict__ inOffsets, size_t n, uint32_t *__restrict__ cost) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const uint64_t b = inOffsets[i + 1] - inOffsets[i];
+    cost[i] = b > 0xFFFFFFFFull ? 0xFFFFFFFFu : uint32_t(b);
+  }
+}
+
+// encode: one streaming pass over the coefficients, ~2 bins per significant bit
+__global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__restrict__ tus,
+                                                         const uint64_t *__restrict__ tuOffsets,
+                                                         const int32_t *__restrict__ coeffs, size_t n,
+                                                         uint32_t *__restrict__ cost) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
+  for (size_t s = warp; s < n; s += nWarps) {
+    uint32_t c = 0;
+    for (uint64_t t = tuOffsets[s]; t < tuOffsets[s + 1]; t++) {
+      const cabac_tu_desc d = tus[t];
+      const int32_t *src = coeffs + d.coeff_offset;
+      const int total = 1 << (d.log2_w + d.log2_h);
+      if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
+        for (int i = lane * 4; i < total; i += 128) {
+          const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
+          c += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
+               (v.z ? 2 * (33 - __clz(abs(v.z))) : 0) + (v.w ? 2 * (33 - __clz(abs(v.w))) : 0);
+        }
+      } else {
+        for (int i = lane; i < total; i += 32) {
+          const int v = __ldg(src + i);
+          c += v ? 2 * (33 - __clz(abs(v))) : 0;
+        }
+      }
+      c += lane == 0 ? 8u + (uint32_t(total) >> 4) : 0u;
+    }
+    c = __reduce_add_sync(FULL, c);
+    if (lane == 0) cost[s] = c;
+  }
+}
+
+__device__ __forceinline__ uint32_t costKey(uint32_t c) {  // 3 mantissa bits under the leading one
+  if (c < 8) return c;
+  const int e = 31 - __clz(c);
+  return uint32_t(e - 2) * 8u + ((c >> (e - 3)) & 7u);  // 8..247
+}
+
+__global__ void __launch_bounds__(1024) lpt_order_kernel(const uint32_t *__restrict__ cost, size_t n,
+                                                         uint32_t *__restrict__ order, uint32_t *cursor) {
+  __shared__ uint32_t hist[256], start[256];
+  if (threadIdx.x < 256) hist[threadIdx.x] = 0;
+  if (threadIdx.x == 0) *cursor = 0;
+  __syncthreads();
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(&hist[costKey(cost[i])], 1u);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t acc = 0;
+    for (int b = 255; b >= 0; b--) {  // longest first
+      start[b] = acc;
+      acc += hist[b];
+    }
+  }
+  __syncthreads();
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) order[atomicAdd(&start[costKey(cost[i])], 1u)] = uint32_t(i);
+}
 
 // ---------------------------------------------------------------------------
 // K1: context initialisation (Ctx::init, contexts.cpp:996-1015)
@@ -103,12 +187,12 @@ encode_bins_kernel(const uint32_t *__restrict__ cmds, const uint64_t *__restrict
                    const cabac_ctx_model *__restrict__ ctxIn, uint8_t *__restrict__ out,
                    const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
                    uint32_t *__restrict__ numBins, cabac_ctx_model *__restrict__ ctxOut,
-                   uint32_t *__restrict__ status) {
+                   uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
   __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   BinsWarpSmem &sm = smem[wib];
-  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
-       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
     Encoder enc;
@@ -151,12 +235,12 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
                    const cabac_substream_params *__restrict__ params, size_t nSub,
                    const cabac_ctx_model *__restrict__ ctxIn, uint32_t *__restrict__ values,
                    uint32_t *__restrict__ bitsRead, cabac_ctx_model *__restrict__ ctxOut,
-                   uint32_t *__restrict__ status) {
+                   uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
   __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   BinsWarpSmem &sm = smem[wib];
-  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
-       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
     Decoder dec;
@@ -362,12 +446,12 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint8_t *__restrict__ out, const uint64_t *__restrict__ outOffsets,
                        uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
-                       uint32_t *__restrict__ status) {
+                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
   __shared__ EncWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   EncWarpSmem &sm = smem[wib];
-  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
-       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     loadCtx<true>(sm.ctx, p, ctxIn, sub, lane);
     Encoder enc;
@@ -483,8 +567,49 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
 // ---------------------------------------------------------------------------
 struct __align__(16) DecWarpSmem {
   int32_t tile[32 * 32];
-  uint32_t ctx[RCTX + 2];
+  uint4 ctx[RCTX];
 };
+
+// Residual contexts as 16-byte entries (see cabac_lockstep.cuh).
+__device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                      size_t sub, int lane) {
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int k = lane; k < RCTX; k += 32) {
+    const int id = rctx_inv(k);
+    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
+    if (imp) {
+      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+      ctx[k] = ctx_entry(m.state0, m.state1, win);
+    } else {
+      ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
+    }
+  }
+  __syncwarp();
+}
+
+__device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                       cabac_ctx_model *ctxOut, size_t sub, int lane) {
+  if (!ctxOut) return;
+  __syncwarp();
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    cabac_ctx_model m;
+    if (is_residual_ctx(id)) {
+      const uint32_t x = ctx[rctx(id)].x;
+      m.state0 = uint16_t(x >> 16);
+      m.state1 = uint16_t(x & 0xFFFFu);
+    } else if (imp) {
+      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else {
+      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
+      m.state0 = uint16_t(model_state0(w));
+      m.state1 = uint16_t(model_state1(w));
+    }
+    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+  }
+}
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
@@ -493,15 +618,15 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
                        const cabac_ctx_model *__restrict__ ctxIn, int32_t *__restrict__ coeffs,
                        uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
-                       uint32_t *__restrict__ status) {
+                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
   __shared__ DecWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   DecWarpSmem &sm = smem[wib];
-  for (size_t sub = size_t(blockIdx.x) * WARPS_PER_BLOCK + wib; sub < nSub;
-       sub += size_t(gridDim.x) * WARPS_PER_BLOCK) {
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtx<true>(sm.ctx, p, ctxIn, sub, lane);
-    Decoder dec;
+    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    LsDecoder dec;  // identical on every lane
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
     const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
     for (uint64_t t = t0; t < t1; t++) {
@@ -510,17 +635,15 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       const int n = g.tw * g.th;
       for (int i = lane; i < n; i += 32) sm.tile[i] = 0;
       __syncwarp();
-      if (lane == 0) {
-        // ts_flag, cabac_reader.cpp:2737-2752
-        bool ts = (d.flags & CABAC_TU_BDPCM) ? true : (d.flags & CABAC_TU_TS) != 0;
-        if (d.flags & CABAC_TU_TS_ALLOWED) ts = dec.decodeBin(sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0)) != 0;
-        uint32_t res = ts ? CABAC_TUR_TS : 0;
-        if (ts && !(p.flags & CABAC_SUB_TSRC_DISABLED))
-          decResidualTS(dec, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0);
-        else
-          res |= decResidualRegular(dec, sm.ctx, sm.tile, g, p.flags, ts);
-        if (tuFlags) tuFlags[t] = uint8_t(res);
-      }
+      // ts_flag, cabac_reader.cpp:2737-2752
+      bool ts = (d.flags & CABAC_TU_BDPCM) ? true : (d.flags & CABAC_TU_TS) != 0;
+      if (d.flags & CABAC_TU_TS_ALLOWED) ts = lsDecodeBin(dec, sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0)) != 0;
+      uint32_t res = ts ? CABAC_TUR_TS : 0;
+      if (ts && !(p.flags & CABAC_SUB_TSRC_DISABLED))
+        lsResidualTS(dec, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0);
+      else
+        res |= lsResidualRegular(dec, sm.ctx, sm.tile, g, p.flags, ts, lane);
+      if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
       __syncwarp();
       // write the block back (the zero-out region of 64-point blocks as zeros)
       int32_t *dst = coeffs + d.coeff_offset;
@@ -531,14 +654,15 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       }
       __syncwarp();
     }
+    if (p.flags & CABAC_SUB_TERMINATE)
+      if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
+    dec.checkOverrun();
     if (lane == 0) {
-      if (p.flags & CABAC_SUB_TERMINATE)
-        if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
       if (numBins) numBins[sub] = dec.nbins;
       if (bitsRead) bitsRead[sub] = dec.bitsRead();
       if (status) status[sub] = dec.status;
     }
-    storeCtx<true>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
     __syncwarp();
   }
 }
@@ -663,17 +787,37 @@ static void buildRom(ScanRom &r) {
 cudaError_t uploadRom() {
   ScanRom r;
   buildRom(r);
-  return cudaMemcpyToSymbol(g_rom, &r, sizeof(r));
+  cudaError_t e = cudaMemcpyToSymbol(g_rom, &r, sizeof(r));
+  if (e != cudaSuccess) return e;
+  uint32_t recip[256] = {0};
+  for (uint32_t range = 256; range <= 510; range++)
+    recip[range - 256] = uint32_t(((1ull << 34) + range - 1) / range);  // ceil(2^34 / range)
+  return cudaMemcpyToSymbol(c_recip, recip, sizeof(recip));
 }
 
 const unsigned char *hostInitTable(int row) { return hosttab::CABAC_CTX_INIT_TABLE[row]; }
 
-static int gridFor(size_t nSub, int device) {
-  int sms = 148;
+// Persistent grid: as many CTAs as can be resident (or fewer when there is less work).
+template <typename K>
+static int persistentGrid(K kernel, size_t nSub, int device) {
+  int sms = 148, perSm = 1;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, WARPS_PER_BLOCK * 32, 0) != cudaSuccess || perSm < 1)
+    perSm = 1;
   const size_t blocks = (nSub + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
-  const size_t cap = size_t(sms) * 32;  // more CTAs than can be resident: grid-stride picks up the rest
+  const size_t cap = size_t(sms) * perSm;
   return int(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+// cost -> longest-first order; resets the cursor.  `bytesCost` selects the decode estimate.
+static cudaError_t launchOrder(cudaStream_t s, const Sched &sc, size_t nSub) {
+  lpt_order_kernel<<<1, 1024, 0, s>>>(sc.cost, nSub, sc.order, sc.cursor);
+  return cudaGetLastError();
+}
+static int costGrid(size_t n, int perBlock) {
+  const size_t b = (n + perBlock - 1) / perBlock;
+  return int(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
 }
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
@@ -687,45 +831,59 @@ cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_para
   return cudaGetLastError();
 }
 
-cudaError_t launchEncodeBins(cudaStream_t s, int device, const uint32_t *cmds, const uint64_t *cmdOffsets,
-                             const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
-                             uint8_t *out, const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
-                             cabac_ctx_model *ctxOut, uint32_t *status) {
+cudaError_t launchEncodeBins(cudaStream_t s, int device, const Sched &sc, const uint32_t *cmds,
+                             const uint64_t *cmdOffsets, const cabac_substream_params *params, size_t nSub,
+                             const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
+                             uint32_t *outSizes, uint32_t *numBins, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  encode_bins_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      cmds, cmdOffsets, params, nSub, ctxIn, out, outOffsets, outSizes, numBins, ctxOut, status);
+  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cmdOffsets, nSub, sc.cost);  // commands per substream
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  encode_bins_kernel<<<persistentGrid(encode_bins_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      cmds, cmdOffsets, params, nSub, ctxIn, out, outOffsets, outSizes, numBins, ctxOut, status, sc.order, sc.cursor);
   return cudaGetLastError();
 }
 
-cudaError_t launchDecodeBins(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
-                             const uint32_t *cmds, const uint64_t *cmdOffsets,
+cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const uint8_t *in,
+                             const uint64_t *inOffsets, const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  decode_bins_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      in, inOffsets, cmds, cmdOffsets, params, nSub, ctxIn, values, bitsRead, ctxOut, status);
+  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cmdOffsets, nSub, sc.cost);
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  decode_bins_kernel<<<persistentGrid(decode_bins_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      in, inOffsets, cmds, cmdOffsets, params, nSub, ctxIn, values, bitsRead, ctxOut, status, sc.order, sc.cursor);
   return cudaGetLastError();
 }
 
-cudaError_t launchEncodeResidual(cudaStream_t s, int device, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
-                                 const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
-                                 const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
-                                 uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
-                                 cabac_ctx_model *ctxOut, uint32_t *status) {
+cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
+                                 const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
+                                 const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint8_t *out,
+                                 const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
+                                 uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  encode_residual_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut, status);
+  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost);
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  encode_residual_kernel<<<persistentGrid(encode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut, status,
+      sc.order, sc.cursor);
   return cudaGetLastError();
 }
 
-cudaError_t launchDecodeResidual(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
-                                 const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, const uint8_t *in,
+                                 const uint64_t *inOffsets, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                                  int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  decode_residual_kernel<<<gridFor(nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status);
+  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
+      sc.order, sc.cursor);
   return cudaGetLastError();
 }
 

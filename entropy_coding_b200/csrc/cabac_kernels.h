@@ -6,25 +6,34 @@
 
 namespace cabac {
 
+// Device scratch of the scheduler (owned by the handle): per-substream cost, the
+// longest-first order and the work cursor.  Kernels launched per call: 3.
+struct Sched {
+  uint32_t *cost;
+  uint32_t *order;
+  uint32_t *cursor;
+};
+constexpr int kLaunchesPerCodingCall = 3;
+
 cudaError_t uploadRom();
 const unsigned char *hostInitTable(int row);
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
                           cabac_ctx_model *out);
-cudaError_t launchEncodeBins(cudaStream_t s, int device, const uint32_t *cmds, const uint64_t *cmdOffsets,
+cudaError_t launchEncodeBins(cudaStream_t s, int device, const Sched &sc, const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                              uint8_t *out, const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
                              cabac_ctx_model *ctxOut, uint32_t *status);
-cudaError_t launchDecodeBins(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
                              const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status);
-cudaError_t launchEncodeResidual(cudaStream_t s, int device, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
                                  const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
                                  uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status);
-cudaError_t launchDecodeResidual(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
                                  const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                                  int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
