@@ -49,6 +49,12 @@ __host__ __device__ inline uint4 ctx_entry_init(int qp, uint32_t initVal, uint32
   return ctx_entry(uint32_t(s) << 8, uint32_t(s) << 8, win);
 }
 
+// Two stream bytes, zero beyond the end; by value so that no decoder state goes through memory.
+__device__ __noinline__ uint32_t lsFetchHalf(const uint8_t *in, uint32_t nbytes, uint32_t pos) {
+  if (pos + 2u <= nbytes) return (uint32_t(__ldg(in + pos)) << 8) | uint32_t(__ldg(in + pos + 1));
+  return pos < nbytes ? uint32_t(__ldg(in + pos)) << 8 : 0u;
+}
+
 struct LsDecoder {
   const uint8_t *in;
   uint32_t nbytes;
@@ -62,7 +68,7 @@ struct LsDecoder {
 
   __device__ __forceinline__ uint32_t byteAt(uint32_t i) const { return i < nbytes ? uint32_t(__ldg(in + i)) : 0u; }
   __device__ __forceinline__ void prefetch() {
-    nextHalf = (byteAt(pos) << 8) | byteAt(pos + 1);
+    nextHalf = lsFetchHalf(in, nbytes, pos);
     pos += 2;
   }
   // start(), arith_codec.cpp:60-66
@@ -112,7 +118,8 @@ struct LsDecoder {
     const uint32_t sr = rmps << 23;
     const bool isLps = hi >= sr;
     const uint32_t bin = mps ^ uint32_t(isLps);
-    const int n = isLps ? (__clz(lps | 7u) - 23) : int(rmps < 256u);
+    const int nLps = __clz(int(lps | 7u)) - 23, nMps = 1 - int(rmps >> 8);
+    const int n = isLps ? nLps : nMps;
     hi -= isLps ? sr : 0u;
     range = (isLps ? lps : rmps) << n;
     shiftIn(n);
@@ -146,7 +153,7 @@ struct LsDecoder {
     epCommit(n, q);
     return q;
   }
-  __device__ inline uint32_t epLong(uint32_t n) {  // any n <= 32, MSB-first like decodeBinsEP
+  __device__ __forceinline__ uint32_t epLong(uint32_t n) {  // any n <= 32, MSB-first like decodeBinsEP
     uint32_t v = 0;
     while (n > 16) {
       v = (v << 16) | ep(16);
@@ -155,38 +162,9 @@ struct LsDecoder {
     return (v << n) | ep(int(n));
   }
 
-  // decodeRemAbsEP(rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:153-179
-  __device__ __forceinline__ uint32_t remAbs(uint32_t rice) {
-    const uint32_t q16 = epPeek(16);
-    const uint32_t ones = uint32_t(__clz(int(~(q16 << 16))));  // leading ones of the 16-bin window
-    if (ones < 5u) {
-      const uint32_t n = ones + 1u + rice;
-      if (n <= 16u) {
-        const uint32_t bins = q16 >> (16u - n);
-        epCommit(int(n), bins);
-        return (ones << rice) + (bins & ((1u << rice) - 1u));
-      }
-      epCommit(int(ones + 1u), q16 >> (15u - ones));
-      return (ones << rice) + epLong(rice);
-    }
-    uint32_t prefix, len;
-    if (ones < 16u) {
-      prefix = ones;
-      len = prefix - 5u + rice;
-      const uint32_t n = prefix + 1u + len;
-      if (n <= 16u) {
-        const uint32_t bins = q16 >> (16u - n);
-        epCommit(int(n), bins);
-        return (((1u << (prefix - 5u)) + 4u) << rice) + (bins & ((1u << len) - 1u));
-      }
-      epCommit(int(prefix + 1u), q16 >> (15u - prefix));
-    } else {  // 16 ones: the prefix is 16 (a zero follows) or 17 (the limit, no terminator)
-      epCommit(16, 0xFFFFu);
-      prefix = 16u + ep(1);
-      len = prefix == 17u ? 15u : prefix - 5u + rice;
-    }
-    return (((1u << (prefix - 5u)) + 4u) << rice) + epLong(len);
-  }
+  // decodeRemAbsEP(rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:153-179.
+  // Fast path: the whole word (unary prefix, terminator, suffix) lies inside one 16-bin window.
+  __device__ __forceinline__ uint32_t remAbs(uint32_t rice);
 
   // decodeBinTrm, arith_codec.cpp:181-197
   __device__ __forceinline__ uint32_t decodeBinTrm() {
@@ -202,20 +180,56 @@ struct LsDecoder {
   }
 };
 
-// Out-of-line twins for the cold call sites (keeps the instruction footprint small).
-__device__ __noinline__ uint32_t lsDecodeBin(LsDecoder &d, uint4 *m) { return d.decodeBin(m); }
-__device__ __noinline__ uint32_t lsRemAbs(LsDecoder &d, uint32_t rice) { return d.remAbs(rice); }
+// Rare: words longer than 16 bins (large levels).  Out of line; the state round-trips through
+// local memory here only.
+__device__ __noinline__ uint32_t lsRemAbsSlow(LsDecoder &d, uint32_t rice, uint32_t q16, uint32_t ones) {
+  uint32_t prefix = ones, len;
+  if (ones < 16u) {
+    d.epCommit(int(ones + 1u), q16 >> (15u - ones));
+    len = ones < 5u ? rice : ones - 5u + rice;
+  } else {  // 16 ones: the prefix is 16 (a zero follows) or 17 (the limit, no terminator)
+    d.epCommit(16, 0xFFFFu);
+    prefix = 16u + d.ep(1);
+    len = prefix == 17u ? 15u : prefix - 5u + rice;
+  }
+  const uint32_t base = prefix < 5u ? prefix << rice : ((1u << (prefix - 5u)) + 4u) << rice;
+  return base + d.epLong(len);
+}
+__device__ __forceinline__ uint32_t LsDecoder::remAbs(uint32_t rice) {
+  const uint32_t q16 = epPeek(16);
+  const uint32_t ones = uint32_t(__clz(int(~(q16 << 16))));  // leading ones of the 16-bin window
+  const bool esc = ones >= 5u;
+  const uint32_t len = rice + (esc ? ones - 5u : 0u);
+  const uint32_t n = ones + 1u + len;
+  if (n > 16u) {  // copy in / copy out: the decoder's own address never escapes (it stays in registers)
+    LsDecoder tmp = *this;
+    const uint32_t r = lsRemAbsSlow(tmp, rice, q16, ones);
+    *this = tmp;
+    return r;
+  }
+  const uint32_t bins = q16 >> (16u - n);
+  epCommit(int(n), bins);
+  const uint32_t base = esc ? (1u << (ones - 5u)) + 4u : ones;
+  return (base << rice) + (bins & ((1u << len) - 1u));
+}
+#define lsDecodeBin(d, m) ((d).decodeBin(m))
+#define lsRemAbs(d, rice) ((d).remAbs(rice))
 
 // ---------------------------------------------------------------------------
 // last_sig_coeff, cabac_reader.cpp:2865-2940
 // ---------------------------------------------------------------------------
-__device__ inline int lsLastSigCoeff(LsDecoder &dec, uint4 *ctx, const TuGeom &g) {
-  uint32_t posX = 0, posY = 0;
-  const int bx = lastXBase(g.ch) + g.lastOffsetX, by = lastYBase(g.ch) + g.lastOffsetY;
-  for (; posX < uint32_t(g.maxLastX); posX++)
-    if (!lsDecodeBin(dec, ctx + bx + (posX >> g.lastShiftX))) break;
-  for (; posY < uint32_t(g.maxLastY); posY++)
-    if (!lsDecodeBin(dec, ctx + by + (posY >> g.lastShiftY))) break;
+__device__ __forceinline__ int lsLastSigCoeff(LsDecoder &dec, uint4 *ctx, const TuGeom &g) {
+  uint32_t posXY[2];
+#pragma unroll 1
+  for (int dim = 0; dim < 2; dim++) {  // one decodeBin site for both prefixes
+    const int base = dim ? lastYBase(g.ch) + g.lastOffsetY : lastXBase(g.ch) + g.lastOffsetX;
+    const int shift = dim ? g.lastShiftY : g.lastShiftX;
+    const uint32_t maxv = uint32_t(dim ? g.maxLastY : g.maxLastX);
+    uint32_t v = 0;
+    while (v < maxv && dec.decodeBin(ctx + base + (v >> shift))) v++;
+    if (dim) posXY[1] = v; else posXY[0] = v;
+  }
+  uint32_t posX = posXY[0], posY = posXY[1];
   if (posX > 3) posX = minInGroup(posX) + dec.ep(int((posX - 2) >> 1));
   if (posY > 3) posY = minInGroup(posY) + dec.ep(int((posY - 2) >> 1));
   return xyToScan(g, int(posX), int(posY));
@@ -234,7 +248,7 @@ __device__ __forceinline__ uint32_t lanePack(int s1, int np, int sa, int sigDiag
 // Regular residual, cabac_reader.cpp:2670-2735 + residual_coding_subblock :2948-3128.
 // All lanes call; returns CABAC_TUR_* flags.
 // ---------------------------------------------------------------------------
-__device__ __noinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g,
+__device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g,
                                                    uint32_t subFlags, bool ts, int lane) {
   uint32_t res = 0;
   const int scanPosLast = lsLastSigCoeff(dec, ctx, g);
@@ -328,15 +342,17 @@ __device__ __noinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx, i
       }
       int val = 0;
       if (sig) {
-        const uint32_t gt1 = dec.decodeBin(ctx + gtxFlagBase(g.ch + 2) + gtxOfs);
-        remRegBins--;
-        uint32_t par = 0, gt2 = 0;
-        if (gt1) {
-          par = dec.decodeBin(ctx + parFlagBase(g.ch) + gtxOfs);
-          gt2 = dec.decodeBin(ctx + gtxFlagBase(g.ch) + gtxOfs);
-          remRegBins -= 2;
+        // gt1, then par and gt2 when gt1 is set: one decodeBin site, three context sets
+        uint32_t gtBits = 0;  // bit 0 gt1, bit 1 par, bit 2 gt2
+#pragma unroll 1
+        for (int k = 0; k < 3; k++) {
+          const int base = k == 0 ? gtxFlagBase(g.ch + 2) : (k == 1 ? parFlagBase(g.ch) : gtxFlagBase(g.ch));
+          gtBits |= dec.decodeBin(ctx + base + gtxOfs) << k;
+          remRegBins--;
+          if (!gtBits) break;
         }
-        val = int(1 + par + gt1 + (gt2 << 1));
+        const uint32_t gt2 = gtBits >> 2;
+        val = int(1 + (gtBits & 1u) + ((gtBits >> 1) & 1u) + (gt2 << 1));
         nzMask |= 1u << p;
         remMask |= gt2 << p;
         if (lane == p) myVal = val;
@@ -401,7 +417,7 @@ __device__ __noinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx, i
 // residual_codingTS + subblockTS, cabac_reader.cpp:3130-3339
 // Lockstep flavour: every lane executes the same serial parse (transform-skip blocks are a
 // small share of the bins); tile stores are same-value broadcasts.
-__device__ __noinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g, bool bdpcm) {
+__device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g, bool bdpcm) {
   int remBins = ((g.w * g.h) * 7) >> 2;
   uint64_t sigGroups = 0;
   const int cgSize = 1 << g.log2cg;
