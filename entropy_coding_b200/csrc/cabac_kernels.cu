@@ -7,7 +7,7 @@
 
 #include <cstring>
 
-#include "cabac_lockstep.cuh"
+#include "cabac_lockstep_enc.cuh"
 #include "cabac_kernels.h"
 
 namespace cabac {
@@ -172,6 +172,47 @@ __device__ inline void storeCtx(const uint32_t *ctx, const cabac_substream_param
   }
 }
 
+// Residual contexts as 16-byte entries (see cabac_lockstep.cuh).
+__device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                      size_t sub, int lane) {
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int k = lane; k < RCTX; k += 32) {
+    const int id = rctx_inv(k);
+    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
+    if (imp) {
+      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+      ctx[k] = ctx_entry(m.state0, m.state1, win);
+    } else {
+      ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
+    }
+  }
+  __syncwarp();
+}
+
+__device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                       cabac_ctx_model *ctxOut, size_t sub, int lane) {
+  if (!ctxOut) return;
+  __syncwarp();
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    cabac_ctx_model m;
+    if (is_residual_ctx(id)) {
+      const uint32_t x = ctx[rctx(id)].x;
+      m.state0 = uint16_t(x >> 16);
+      m.state1 = uint16_t(x & 0xFFFFu);
+    } else if (imp) {
+      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else {
+      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
+      m.state0 = uint16_t(model_state0(w));
+      m.state1 = uint16_t(model_state1(w));
+    }
+    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // K2: bin-level encoder (recorded BinEncIf calls -> bytes)
 // ---------------------------------------------------------------------------
@@ -284,11 +325,11 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
 // K4: residual-level encoder
 // ---------------------------------------------------------------------------
 struct __align__(16) EncWarpSmem {
+  uint4 ctx[RCTX];
   uint8_t ring[STAGE_BYTES];
   int16_t tile[32 * 32];
-  uint32_t ctx[RCTX + 2];  // 232 words
   uint32_t queue[QUEUE_WORDS];
-  uint16_t cgMask[64];     // nonzero mask of every coefficient group, by scan index
+  uint16_t cgMask[64];  // nonzero mask of every coefficient group, by scan index
 };
 
 // Stages the coded region of a TU into the int16 tile (all lanes).  Returns
@@ -403,21 +444,27 @@ __device__ inline int binariseCG(uint32_t *queue, const int16_t *tile, const TuG
     }
   }
   nq += pass1Total;
-  // 2nd pass: abs_remainder of context-coded positions with |level| >= 4
+  // 2nd pass (abs_remainder of context-coded positions with |level| >= 4) and bypass-only positions
+  // (dec_abs_level): each Golomb-Rice word leaves its lane already packed as one or two EP strings
   const bool hasRem = inPass1 && a >= 4;
-  const uint32_t R = __ballot_sync(FULL, hasRem);
-  if (hasRem) queue[nq + __popc(R & above)] = CABAC_MK_REM((a - 4) >> 1, goRicePar(sumAll - 20));
-  nq += __popc(R);
-  // bypass-only positions: dec_abs_level
   const bool inPass3 = active && !inPass1;
-  const uint32_t M3 = activeMask & ~M1;
-  if (inPass3) {
+  uint32_t w0 = 0, w1 = 0;
+  int cnt = 0;
+  if (hasRem) {
+    cnt = lsRemWords(uint32_t(a - 4) >> 1, goRicePar(sumAll - 20), w0, w1);
+  } else if (inPass3) {
     const uint32_t rice = goRicePar(sumAll);
     const uint32_t pos0 = (st < 2 ? 1u : 2u) << rice;
     const uint32_t rem = a == 0 ? pos0 : (uint32_t(a) <= pos0 ? uint32_t(a) - 1u : uint32_t(a));
-    queue[nq + __popc(M3 & above)] = CABAC_MK_REM(rem, rice);
+    cnt = lsRemWords(rem, rice, w0, w1);
   }
-  nq += __popc(M3);
+  const uint32_t E1 = __ballot_sync(FULL, cnt >= 1), E2 = __ballot_sync(FULL, cnt == 2);
+  if (cnt) {
+    const int at = nq + __popc(E1 & above) + __popc(E2 & above);
+    queue[at] = w0;
+    if (cnt == 2) queue[at + 1] = w1;
+  }
+  nq += __popc(E1) + __popc(E2);
   // signs: first coded non-zero is the pattern's MSB
   uint32_t numSigns = __popc(Z);
   uint32_t mySign = (active && nz && v < 0) ? (1u << __popc(Z & ((1u << lane) - 1u))) : 0u;
@@ -439,6 +486,106 @@ __device__ inline int binariseCG(uint32_t *queue, const int16_t *tile, const TuG
   return nq;
 }
 
+// last_sig_coeff as command words, cabac_writer.cpp:2639-2722 (same words on every lane)
+__device__ __forceinline__ int pushLastSigCoeff(uint32_t *q, const TuGeom &g, int posX, int posY) {
+  const uint32_t gx = groupIdx(posX), gy = groupIdx(posY);
+  const int bx = lastXBase(g.ch) + g.lastOffsetX, by = lastYBase(g.ch) + g.lastOffsetY;
+  int n = 0;
+  uint32_t k;
+  for (k = 0; k < gx; k++) q[n++] = CABAC_MK_CTX(bx + (k >> g.lastShiftX), 1);
+  if (gx < uint32_t(g.maxLastX)) q[n++] = CABAC_MK_CTX(bx + (k >> g.lastShiftX), 0);
+  for (k = 0; k < gy; k++) q[n++] = CABAC_MK_CTX(by + (k >> g.lastShiftY), 1);
+  if (gy < uint32_t(g.maxLastY)) q[n++] = CABAC_MK_CTX(by + (k >> g.lastShiftY), 0);
+  if (gx > 3) {
+    const uint32_t nb = (gx - 2) >> 1;
+    q[n++] = CABAC_MK_EP((posX - minInGroup(gx)) & ((1u << nb) - 1u), nb);
+  }
+  if (gy > 3) {
+    const uint32_t nb = (gy - 2) >> 1;
+    q[n++] = CABAC_MK_EP((posY - minInGroup(gy)) & ((1u << nb) - 1u), nb);
+  }
+  return n;
+}
+
+// One coefficient group of a transform-skip block as command words
+// (residual_coding_subblockTS, cabac_writer.cpp:2924-3062).  Serial, identical on all lanes.
+__device__ __forceinline__ int produceTsCG(uint32_t *q, const int16_t *tile, const TuGeom &g, bool bdpcm,
+                                           const uint16_t *cgMask, int s, int &remBins, uint64_t &sigGroups) {
+  int n = 0;
+  const int cgSize = 1 << g.log2cg;
+  const int lastSubSet = g.numCG - 1;
+  const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
+  const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
+  const bool sig = cgMask[s] != 0;
+  if (sig) sigGroups |= 1ull << cgPos;
+  const int left = cgx > 0 ? int((sigGroups >> (cgPos - 1)) & 1) : 0;
+  const int above = cgy > 0 ? int((sigGroups >> (cgPos - g.wig)) & 1) : 0;
+  const uint64_t others = sigGroups & ~(1ull << lastSubSet);
+  if (s != lastSubSet || others != 0) {
+    q[n++] = CABAC_MK_CTX(R_TS_SIG_GROUP + left + above, sig);
+    if (!sig) return n;
+  }
+  const int minPos = s << g.log2cg, maxPos = minPos + cgSize - 1;
+  int numNonZero = 0, lastPass1 = -1, lastPass2 = -1;
+  int sp = minPos;
+  for (; sp <= maxPos && remBins >= 4; sp++) {
+    int x, y, l, a;
+    scanXY(g, sp, x, y);
+    const int v = tile[(y << g.log2tw) + x];
+    const uint32_t sigf = v != 0;
+    neighTS(tile, g, x, y, l, a);
+    if (numNonZero || sp != maxPos) {
+      q[n++] = CABAC_MK_CTX(R_TS_SIG_FLAG + (l != 0) + (a != 0), sigf);
+      remBins--;
+    }
+    if (sigf) {
+      q[n++] = CABAC_MK_CTX(signCtxTS(l, a, bdpcm), v < 0);
+      remBins--;
+      numNonZero++;
+      int rem = modCoeffTS(l, a, abs(v), bdpcm) - 1;
+      const uint32_t gt1 = rem != 0;
+      q[n++] = CABAC_MK_CTX(R_TS_LRG1_FLAG + (bdpcm ? 3 : (l != 0) + (a != 0)), gt1);
+      remBins--;
+      if (gt1) {
+        rem -= 1;
+        q[n++] = CABAC_MK_CTX(R_TS_PAR_FLAG, uint32_t(rem) & 1u);
+        remBins--;
+      }
+    }
+    lastPass1 = sp;
+  }
+  for (sp = minPos; sp <= maxPos && remBins >= 4; sp++) {
+    int x, y, l, a;
+    scanXY(g, sp, x, y);
+    neighTS(tile, g, x, y, l, a);
+    const int absLevel = modCoeffTS(l, a, abs(int(tile[(y << g.log2tw) + x])), bdpcm);
+    for (int cutoff = 2; cutoff <= 8; cutoff += 2) {
+      if (absLevel >= cutoff) {
+        q[n++] = CABAC_MK_CTX(R_TS_GTX_FLAG + (cutoff >> 1), absLevel >= cutoff + 2);
+        remBins--;
+      }
+    }
+    lastPass2 = sp;
+  }
+  for (sp = minPos; sp <= maxPos; sp++) {
+    int x, y, l, a;
+    scanXY(g, sp, x, y);
+    neighTS(tile, g, x, y, l, a);
+    const int cutoff = sp <= lastPass2 ? 10 : (sp <= lastPass1 ? 2 : 0);
+    const int v = tile[(y << g.log2tw) + x];
+    const int absLevel = modCoeffTS(l, a, abs(v), bdpcm || !cutoff);
+    if (absLevel >= cutoff) {
+      const uint32_t rem = sp <= lastPass1 ? uint32_t(absLevel - cutoff) >> 1 : uint32_t(absLevel);
+      uint32_t w0 = 0, w1 = 0;
+      const int cnt = lsRemWords(rem, 1, w0, w1);
+      q[n++] = w0;
+      if (cnt == 2) q[n++] = w1;
+      if (absLevel && sp > lastPass1) q[n++] = CABAC_MK_EP(v < 0, 1);
+    }
+  }
+  return n;
+}
+
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
@@ -453,111 +600,138 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtx<true>(sm.ctx, p, ctxIn, sub, lane);
-    Encoder enc;
+    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    LsEncoder enc;  // identical on every lane
     enc.start();
     enc.out.ring = sm.ring;
     enc.out.dst = out + outOffsets[sub];
     enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
     enc.out.n = 0;
     enc.out.flushed = 0;
+    enc.out.lane = lane;
     uint32_t st = 0;
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
-    const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
-    for (uint64_t t = t0; t < t1; t++) {
-      const cabac_tu_desc d = tus[t];
-      const TuGeom g = makeGeom(d);
-      const bool ts = (d.flags & CABAC_TU_TS) != 0;
-      const bool tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
-      uint32_t res = ts ? CABAC_TUR_TS : 0;
-      if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+    uint64_t t = tuOffsets[sub];
+    const uint64_t t1 = tuOffsets[sub + 1];
 
-      // ---- pre-scan: non-zero mask per coefficient group, last position ----
-      int lastCG = -1;
-      const int cgSize = 1 << g.log2cg;
-      const int perIter = 32 >> g.log2cg;  // coefficient groups handled per iteration
-      for (int s0 = 0; s0 < g.numCG; s0 += perIter) {
-        const int s = s0 + (lane >> g.log2cg), pl = lane & (cgSize - 1);
-        bool nz = false;
-        if (s < g.numCG) {
-          int x, y;
-          scanXY(g, (s << g.log2cg) + pl, x, y);
-          nz = sm.tile[(y << g.log2tw) + x] != 0;
+    // per-block producer state
+    bool inTu = false, tsPath = false, bdpcm = false;
+    cabac_tu_desc d;
+    TuGeom g;
+    uint32_t res = 0;
+    int lastCG = 0, scanPosLast = 0, s = 0, state = 0, remRegBins = 0, remBinsTS = 0;
+    uint64_t sigGroups = 0;
+
+    // Every iteration produces one batch of command words (block header and/or one coefficient
+    // group) and drains it through the single arithmetic-coder site.
+    for (;;) {
+      int nq = 0;
+      if (!inTu) {
+        if (t == t1) break;
+        d = tus[t];
+        g = makeGeom(d);
+        const bool ts = (d.flags & CABAC_TU_TS) != 0;
+        tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
+        bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
+        res = ts ? CABAC_TUR_TS : 0;
+        if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        // ---- pre-scan: non-zero mask per coefficient group, last position ----
+        lastCG = -1;
+        const int cgSize = 1 << g.log2cg;
+        const int perIter = 32 >> g.log2cg;  // coefficient groups handled per iteration
+        for (int s0 = 0; s0 < g.numCG; s0 += perIter) {
+          const int sc = s0 + (lane >> g.log2cg), pl = lane & (cgSize - 1);
+          bool nz = false;
+          if (sc < g.numCG) {
+            int x, y;
+            scanXY(g, (sc << g.log2cg) + pl, x, y);
+            nz = sm.tile[(y << g.log2tw) + x] != 0;
+          }
+          const uint32_t b = __ballot_sync(FULL, nz);
+          if (pl == 0 && sc < g.numCG)
+            sm.cgMask[sc] = uint16_t((b >> (lane & ~(cgSize - 1))) & ((1u << cgSize) - 1u));
+          if (b) lastCG = s0 + ((31 - __clz(b)) >> g.log2cg);
         }
-        const uint32_t b = __ballot_sync(FULL, nz);
-        if (pl == 0 && s < g.numCG) sm.cgMask[s] = uint16_t((b >> (lane & 31 & ~(cgSize - 1))) & ((1u << cgSize) - 1u));
-        if (b) lastCG = s0 + ((31 - __clz(b)) >> g.log2cg);
-      }
-      __syncwarp();
-      if (lastCG < 0) {  // "Coefficient coding called for empty TU", cabac_writer.cpp:2457
-        st |= CABAC_SS_EMPTY_TU;
-        if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
-        continue;
-      }
-      // ---- transform_skip_flag (ts_flag, cabac_writer.cpp:2527-2535) ----
-      if (lane == 0 && (d.flags & CABAC_TU_TS_ALLOWED)) enc.encodeBin(ts, sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0));
-      if (tsPath) {
-        if (lane == 0) encResidualTS(enc, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0, sm.cgMask);
         __syncwarp();
-      } else {
-        const int scanPosLast = (lastCG << g.log2cg) + (31 - __clz(uint32_t(sm.cgMask[lastCG])));
-        if (!ts && g.w >= 4 && g.h >= 4) {  // CUCtx side effects, cabac_writer.cpp:2460-2478
-          const int maxLfnstPos = ((g.h == 4 && g.w == 4) || (g.h == 8 && g.w == 8)) ? 7 : 15;
-          if (scanPosLast > maxLfnstPos) res |= CABAC_TUR_VIOLATES_LFNST;
-          if (scanPosLast >= 1) res |= CABAC_TUR_LFNST_LAST_POS;
+        if (lastCG < 0) {  // "Coefficient coding called for empty TU", cabac_writer.cpp:2457
+          st |= CABAC_SS_EMPTY_TU;
+          if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+          t++;
+          continue;
         }
-        if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
-        if (lane == 0) {
+        // transform_skip_flag (ts_flag, cabac_writer.cpp:2527-2535)
+        if (d.flags & CABAC_TU_TS_ALLOWED) sm.queue[nq++] = CABAC_MK_CTX(R_TS_FLAG + (g.comp ? 1 : 0), ts);
+        if (tsPath) {
+          s = 0;
+          remBinsTS = ((g.w * g.h) * 7) >> 2;
+        } else {
+          scanPosLast = (lastCG << g.log2cg) + (31 - __clz(uint32_t(sm.cgMask[lastCG])));
+          if (!ts && g.w >= 4 && g.h >= 4) {  // CUCtx side effects, cabac_writer.cpp:2460-2478
+            const int maxLfnstPos = ((g.h == 4 && g.w == 4) || (g.h == 8 && g.w == 8)) ? 7 : 15;
+            if (scanPosLast > maxLfnstPos) res |= CABAC_TUR_VIOLATES_LFNST;
+            if (scanPosLast >= 1) res |= CABAC_TUR_LFNST_LAST_POS;
+          }
+          if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
           int x, y;
           scanXY(g, scanPosLast, x, y);
-          encLastSigCoeff(enc, sm.ctx, g, x, y);
+          nq += pushLastSigCoeff(sm.queue + nq, g, x, y);
+          state = 0;
+          remRegBins = regBinLimit(g);
+          s = lastCG;
         }
-        int state = 0;
-        int remRegBins = regBinLimit(g);
-        uint64_t sigGroups = 0;
-        for (int s = lastCG; s >= 0; s--) {
-          const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
-          const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
-          const bool sig = sm.cgMask[s] != 0;
-          // initSubblock, context_modelling.cpp:81-106
-          if (sig) sigGroups |= 1ull << cgPos;
-          if (g.sbtZero) {
-            if ((g.h == 32 && cgy >= (16 >> g.log2cgh)) || (g.w == 32 && cgx >= (16 >> g.log2cgw))) continue;
-          }
+        sigGroups = 0;
+        inTu = true;
+        __syncwarp();
+      }
+      bool endTu;
+      if (tsPath) {
+        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups);
+        s++;
+        endTu = s == g.numCG;
+      } else {
+        const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
+        const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
+        const bool sig = sm.cgMask[s] != 0;
+        // initSubblock, context_modelling.cpp:81-106
+        if (sig) sigGroups |= 1ull << cgPos;
+        const bool zeroedOut = g.sbtZero && ((g.h == 32 && cgy >= (16 >> g.log2cgh)) ||
+                                             (g.w == 32 && cgx >= (16 >> g.log2cgw)));
+        if (!zeroedOut) {
           const bool codeSigGroup = s != lastCG && s != 0;
           const int right = (cgx + 1 < g.wig) ? int((sigGroups >> (cgPos + 1)) & 1) : 0;
           const int lower = (cgy + 1 < g.hig) ? int((sigGroups >> (cgPos + g.wig)) & 1) : 0;
           const int sigGroupCtx = R_SIG_GROUP + 2 * g.ch + (right | lower);
-          int nq;
           if (codeSigGroup && !sig) {
-            if (lane == 0) sm.queue[0] = CABAC_MK_CTX(sigGroupCtx, 0);
-            nq = 1;
-            __syncwarp();
+            sm.queue[nq++] = CABAC_MK_CTX(sigGroupCtx, 0);
           } else {
-            nq = binariseCG(sm.queue, sm.tile, g, lane, s, scanPosLast, codeSigGroup, sigGroupCtx, depQuant,
-                            signHiding, state, remRegBins);
+            nq += binariseCG(sm.queue + nq, sm.tile, g, lane, s, scanPosLast, codeSigGroup, sigGroupCtx, depQuant,
+                             signHiding, state, remRegBins);
             if (sig && g.comp == 0 && (cgy > 3 || cgx > 3)) res |= CABAC_TUR_VIOLATES_MTS;
           }
-          if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, nq);
-          __syncwarp();
-          if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
-            stage_flush(enc.out, lane, false);
         }
+        s--;
+        endTu = s < 0;
       }
-      if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
-      if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
-        stage_flush(enc.out, lane, false);
+      if (endTu) {
+        if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+        t++;
+        inTu = false;
+      }
+      __syncwarp();
+      lsDrain(enc, sm.ctx, sm.queue, nq);
+      if (enc.out.n - enc.out.flushed >= uint32_t(STAGE_BYTES / 2)) enc.out.flush(false);
+      __syncwarp();
     }
-    if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
-    stage_flush(enc.out, lane, true);
+    enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+    enc.out.flush(true);
     if (lane == 0) {
       if (enc.out.n > enc.out.cap) st |= CABAC_SS_OUT_OVERFLOW;
       outSizes[sub] = enc.out.n;
       if (numBins) numBins[sub] = enc.nbins;
       if (status) status[sub] = st;
     }
-    storeCtx<true>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
     __syncwarp();
   }
 }
@@ -569,47 +743,6 @@ struct __align__(16) DecWarpSmem {
   int32_t tile[32 * 32];
   uint4 ctx[RCTX];
 };
-
-// Residual contexts as 16-byte entries (see cabac_lockstep.cuh).
-__device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                      size_t sub, int lane) {
-  const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
-  for (int k = lane; k < RCTX; k += 32) {
-    const int id = rctx_inv(k);
-    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
-    if (imp) {
-      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
-      ctx[k] = ctx_entry(m.state0, m.state1, win);
-    } else {
-      ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
-    }
-  }
-  __syncwarp();
-}
-
-__device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                       cabac_ctx_model *ctxOut, size_t sub, int lane) {
-  if (!ctxOut) return;
-  __syncwarp();
-  const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
-  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
-    cabac_ctx_model m;
-    if (is_residual_ctx(id)) {
-      const uint32_t x = ctx[rctx(id)].x;
-      m.state0 = uint16_t(x >> 16);
-      m.state1 = uint16_t(x & 0xFFFFu);
-    } else if (imp) {
-      m = ctxIn[sub * CABAC_NUM_CTX + id];
-    } else {
-      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
-      m.state0 = uint16_t(model_state0(w));
-      m.state1 = uint16_t(model_state1(w));
-    }
-    ctxOut[sub * CABAC_NUM_CTX + id] = m;
-  }
-}
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,

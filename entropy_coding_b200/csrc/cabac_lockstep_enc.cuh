@@ -1,0 +1,228 @@
+// cabac_lockstep_enc.cuh - warp-lockstep CABAC encoder for sm_100a.
+//
+// The encoder's bins do not depend on the coder state, so a substream is coded in
+// two alternating steps per batch (a coefficient group, a last-position prefix, ...):
+//   produce : the warp binarises in parallel (one lane per scan position: template
+//             sums, context ids, Rice parameters, Golomb-Rice words already packed as
+//             EP bin strings) into a shared-memory queue of 32-bit command words
+//   drain   : ONE instance of the arithmetic coder in the whole kernel walks the
+//             queue, executed uniformly by all lanes (state in registers, the next
+//             command and its context entry are fetched one step ahead)
+// Exactly one encodeBin site keeps the hot loop inside the instruction cache, which
+// was the limiter of the first version (profiles/r1_b_ncu_details.txt).
+//
+// Arithmetic (arith_codec.cpp:329-582) is restated on a 64-bit `low`: up to 24 EP
+// bins enter in one multiply-add and bytes leave in a loop of writeOut steps; the
+// byte stream is identical because it only depends on the exact sum.
+#pragma once
+#include "cabac_lockstep.cuh"
+
+namespace cabac {
+
+// Output staging, uniform on all lanes: bytes go to a shared-memory ring and leave
+// for HBM as coalesced 16-byte stores.
+struct LsOut {
+  uint8_t *ring;  // shared, STAGE_BYTES, 16-byte aligned
+  uint8_t *dst;   // this substream's slab
+  uint32_t cap, n, flushed;
+  int lane;
+
+  __device__ __forceinline__ void flush(bool final) {
+    const uint32_t lim = n & ~15u;
+    __syncwarp();
+    if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+      for (uint32_t b = flushed + 16u * lane; b < lim; b += 512u) {
+        if (b + 16u <= cap) {
+          *reinterpret_cast<uint4 *>(dst + b) = *reinterpret_cast<const uint4 *>(ring + (b & (STAGE_BYTES - 1)));
+        } else {
+          for (uint32_t k = b; k < b + 16u && k < cap; k++) dst[k] = ring[k & (STAGE_BYTES - 1)];
+        }
+      }
+    } else {
+      for (uint32_t b = flushed + lane; b < lim; b += 32u)
+        if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
+    }
+    flushed = lim;
+    if (final) {
+      for (uint32_t b = lim + lane; b < n; b += 32u)
+        if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
+      flushed = n;
+    }
+    __syncwarp();
+  }
+  __device__ __forceinline__ void put(uint32_t byte) {
+    if (n - flushed >= uint32_t(STAGE_BYTES)) flush(false);  // long outstanding-0xFF run released at once
+    ring[n & (STAGE_BYTES - 1)] = uint8_t(byte);
+    n++;
+  }
+};
+
+struct LsEncoder {
+  uint64_t low;
+  uint32_t range, bufferedByte;
+  int numBuffered, bitsLeft;
+  uint32_t nbins;
+  LsOut out;
+
+  // start(), arith_codec.cpp:329-337
+  __device__ __forceinline__ void start() {
+    low = 0;
+    range = 510;
+    bufferedByte = 0xFF;
+    numBuffered = 0;
+    bitsLeft = 23;
+    nbins = 0;
+  }
+  // one writeOut() step, arith_codec.cpp:524-546
+  __device__ __forceinline__ void emitByte() {
+    const uint32_t lead = uint32_t(low >> (24 - bitsLeft));
+    bitsLeft += 8;
+    low &= (1ull << (32 - bitsLeft)) - 1ull;
+    if (lead == 0xFF) {
+      numBuffered++;
+    } else if (numBuffered > 0) {
+      const uint32_t carry = lead >> 8;
+      out.put((bufferedByte + carry) & 0xFF);
+      bufferedByte = lead & 0xFF;
+      const uint32_t fill = (0xFF + carry) & 0xFF;
+      while (numBuffered > 1) {
+        out.put(fill);
+        numBuffered--;
+      }
+    } else {
+      numBuffered = 1;
+      bufferedByte = lead;
+    }
+  }
+  __device__ __forceinline__ void flushBits() {
+    while (bitsLeft < 12) emitByte();
+  }
+  // TBinEncoder::encodeBin, arith_codec.cpp:553-582; returns the updated state word
+  __device__ __forceinline__ uint32_t encodeCtx(uint32_t bin, const uint4 e) {
+    const uint32_t q = ((e.x >> 16) + (e.x & 0xFFFFu)) >> 8;
+    const uint32_t mps = q >> 7;
+    const uint32_t qq = q ^ (0xFFu & (0u - mps));
+    const uint32_t lps = (((qq >> 2) * (range >> 5)) >> 1) + 4;
+    nbins++;
+    const uint32_t rmps = range - lps;
+    const bool isLps = bin != mps;
+    const int n = isLps ? __clz(int(lps | 7u)) - 23 : 1 - int(rmps >> 8);
+    low = (low + (isLps ? rmps : 0u)) << n;
+    range = (isLps ? lps : rmps) << n;
+    bitsLeft -= n;
+    const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
+    const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
+    return e.x - d0 - d1 + (bin ? e.y : 0u);
+  }
+  // encodeBinsEP, arith_codec.cpp:401-424, n <= 24 bins at once
+  __device__ __forceinline__ void ep(uint32_t bins, int n) {
+    low = (low << n) + uint64_t(range) * bins;
+    bitsLeft -= n;
+    nbins += uint32_t(n);
+  }
+  // encodeBinTrm, arith_codec.cpp:460-478
+  __device__ __forceinline__ void trm(uint32_t bin) {
+    nbins++;
+    range -= 2;
+    if (bin) {
+      low = (low + range) << 7;
+      range = 256;
+      bitsLeft -= 7;
+    } else if (range < 256) {
+      low <<= 1;
+      range <<= 1;
+      bitsLeft--;
+    }
+    flushBits();
+  }
+  // finish(), arith_codec.cpp:339-357, then optionally writeByteAlignment(), bit_stream.cpp:152-155.
+  // Without `terminate` the tail bits stay in `low` (nothing is emitted), as the reference
+  // leaves them in the coder until finish().
+  __device__ __forceinline__ void finish(bool terminate, bool align) {
+    uint32_t tail = 0, ntail = 0;  // bits an OutputBitstream would still hold
+    if (terminate) {
+      trm(1);
+      if (low >> (32 - bitsLeft)) {
+        out.put((bufferedByte + 1) & 0xFF);
+        while (numBuffered > 1) {
+          out.put(0x00);
+          numBuffered--;
+        }
+        low -= 1ull << (32 - bitsLeft);
+      } else {
+        if (numBuffered > 0) out.put(bufferedByte & 0xFF);
+        while (numBuffered > 1) {
+          out.put(0xFF);
+          numBuffered--;
+        }
+      }
+      tail = uint32_t(low >> 8);
+      ntail = uint32_t(24 - bitsLeft);
+    }
+    if (align) {
+      tail = (tail << 1) | 1u;  // stop bit
+      ntail += 1;
+    }
+    while (ntail >= 8) {
+      out.put((tail >> (ntail - 8)) & 0xFF);
+      ntail -= 8;
+    }
+    if (align && ntail) out.put((tail << (8 - ntail)) & 0xFF);
+  }
+};
+
+// The single arithmetic-coder site: walks n command words (CTX / EP kinds).
+__device__ __forceinline__ void lsDrain(LsEncoder &enc, uint4 *ctx, const uint32_t *queue, int n) {
+  if (n <= 0) return;
+  uint32_t w = queue[0];
+  uint4 e = ctx[(w >> 29) ? 0u : (w & 511u)];
+#pragma unroll 1
+  for (int i = 0; i < n; i++) {
+    // one step ahead: the next command and (speculatively) its context entry
+    const uint32_t wn = queue[min(i + 1, n - 1)];
+    const uint32_t idxn = (wn >> 29) ? 0u : (wn & 511u);
+    uint4 en = ctx[idxn];
+    if ((w >> 29) == CABAC_CMD_CTX) {
+      const uint32_t idx = w & 511u;
+      const uint32_t nx = enc.encodeCtx((w >> 9) & 1u, e);
+      ctx[idx].x = nx;
+      if (idxn == idx) en.x = nx;  // the entry fetched ahead was the one just updated
+    } else {
+      enc.ep(w & 0xFFFFFFu, int((w >> 24) & 31u));
+    }
+    enc.flushBits();
+    w = wn;
+    e = en;
+  }
+}
+
+// encodeRemAbsEP(v, rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:426-458, as one or
+// two EP command words (prefix and suffix concatenated when they fit 24 bins).  Returns the count.
+__device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w0, uint32_t &w1) {
+  const uint32_t mask = (1u << rice) - 1u;
+  if (v < (5u << rice)) {
+    const uint32_t len = (v >> rice) + 1u;
+    w0 = CABAC_MK_EP((((1u << len) - 2u) << rice) | (v & mask), len + rice);
+    return 1;
+  }
+  const uint32_t code = (v >> rice) - 5u;
+  uint32_t prefix, suffixLen;
+  if (code >= ((1u << 12) - 1u)) {
+    prefix = 12;
+    suffixLen = 15;
+  } else {
+    prefix = 31 - __clz(int(code + 1u));  // smallest p with code <= 2^(p+1) - 2
+    suffixLen = prefix + rice + 1u;
+  }
+  const uint32_t total = prefix + 5u;
+  const uint32_t suffix = ((code - ((1u << prefix) - 1u)) << rice) | (v & mask);
+  if (total + suffixLen <= 24u) {
+    w0 = CABAC_MK_EP((((1u << total) - 1u) << suffixLen) | suffix, total + suffixLen);
+    return 1;
+  }
+  w0 = CABAC_MK_EP((1u << total) - 1u, total);
+  w1 = CABAC_MK_EP(suffix, suffixLen);
+  return 2;
+}
+
+}  // namespace cabac

@@ -224,7 +224,7 @@ __device__ __forceinline__ int gtxCtxOffset(const TuGeom &g, int sumAbs1, int nu
 // ---------------------------------------------------------------------------
 // Encoder: command queue drained by lane 0
 // ---------------------------------------------------------------------------
-constexpr int QUEUE_WORDS = 96;
+constexpr int QUEUE_WORDS = 192;  // worst case: one transform-skip group (178 words)
 
 __device__ __noinline__ uint32_t drainQueue(Encoder &enc, uint32_t *ctx, const uint32_t *queue, int n) {
   uint32_t status = 0;
