@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -26,6 +27,11 @@ struct cabac_handle {
   // scheduler scratch (cost / order / cursor), grow-only
   uint32_t *sched = nullptr;
   size_t schedSubs = 0;
+  // resolved command words of the two-stage residual encoder, grow-only
+  uint32_t *cmdBuf = nullptr;
+  size_t cmdCapWords = 0;
+  uint64_t *pinnedTotal = nullptr;  // page-locked landing spot for the slab size read-back
+  int encoderMode = CABAC_ENCODER_AUTO;
 };
 
 namespace {
@@ -85,15 +91,25 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     h->sched = nullptr;
     h->schedSubs = 0;
     const size_t cap = n + (n >> 2) + 1024;
-    cudaError_t e = cudaMalloc(&h->sched, (2 * cap + 64) * sizeof(uint32_t));
+    cudaError_t e = cudaMalloc(&h->sched, (7 * cap + 64 + 2) * sizeof(uint32_t));
     if (e != cudaSuccess) return e;
     h->schedSubs = cap;
   }
+  const size_t cap = h->schedSubs;
   sc.cursor = h->sched;
-  sc.cost = h->sched + 64;
-  sc.order = h->sched + 64 + h->schedSubs;
+  sc.cmdOffsets = reinterpret_cast<uint64_t *>(h->sched + 64);  // 2 * (cap + 1) words, 8-byte aligned
+  uint32_t *p = h->sched + 64 + 2 * (cap + 1);
+  sc.cost = p;
+  sc.order = p + cap;
+  sc.capWords = p + 2 * cap;
+  sc.cmdCounts = p + 3 * cap;
+  sc.statusScratch = p + 4 * cap;
+  sc.cmdBuf = h->cmdBuf;
   return cudaSuccess;
 }
+
+// From this many substreams on, stage D (32 substreams per warp) fills the machine.
+constexpr size_t kTwoStageMinSubstreams = 32768;
 
 #define CK(call, what)                                   \
   do {                                                   \
@@ -130,6 +146,10 @@ cabac_handle *cabac_create(int device) {
     return nullptr;
   }
   h->stream = h->ownStream;
+  if (const char *m = getenv("CABAC_B200_ENCODER")) {
+    if (!strcmp(m, "fused")) h->encoderMode = CABAC_ENCODER_FUSED;
+    if (!strcmp(m, "two_stage")) h->encoderMode = CABAC_ENCODER_TWO_STAGE;
+  }
   return h;
 }
 
@@ -139,6 +159,8 @@ void cabac_destroy(cabac_handle *h) {
   cudaStreamSynchronize(h->stream);
   if (h->scratch) cudaFree(h->scratch);
   if (h->sched) cudaFree(h->sched);
+  if (h->cmdBuf) cudaFree(h->cmdBuf);
+  if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
 }
@@ -146,6 +168,12 @@ void cabac_destroy(cabac_handle *h) {
 int cabac_set_stream(cabac_handle *h, void *cuda_stream) {
   if (!h) return CABAC_ERR_ARG;
   h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->ownStream;
+  return CABAC_OK;
+}
+
+int cabac_set_encoder_mode(cabac_handle *h, int mode) {
+  if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_TWO_STAGE) return CABAC_ERR_ARG;
+  h->encoderMode = mode;
   return CABAC_OK;
 }
 
@@ -232,12 +260,36 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!h || (n_sub && (!tu_offsets || !params || !out || !out_offsets || !out_sizes)))
     return badArg(h, "cabac_encode_residual_dev");
   DeviceGuard g(h->device);
+  if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  CK(cabac::launchEncodeResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
-                                 out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
-     "encode_residual_kernel");
-  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs), "encode prepare kernels");
+  // Few long substreams: one warp per substream, fused.  Many substreams: the two-stage coder,
+  // whose interval stage runs one substream per thread.
+  sc.twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
+  if (sc.twoStage) {
+    // The command slab is sized from the descriptors, which live on the device: read the total
+    // back (8 bytes; the one synchronisation point of this call) and grow the slab if needed.
+    if (!h->pinnedTotal) CK(cudaHostAlloc(&h->pinnedTotal, sizeof(uint64_t), cudaHostAllocDefault), "pinned alloc");
+    CK(cudaMemcpyAsync(h->pinnedTotal, sc.cmdOffsets + n_sub, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream),
+       "slab size read-back");
+    CK(cudaStreamSynchronize(h->stream), "sync");
+    const size_t needWords = size_t(*h->pinnedTotal);
+    if (needWords > h->cmdCapWords) {
+      if (h->cmdBuf) cudaFree(h->cmdBuf);
+      h->cmdBuf = nullptr;
+      h->cmdCapWords = 0;
+      const size_t words = needWords + (needWords >> 3) + 1024;
+      CK(cudaMalloc(&h->cmdBuf, words * sizeof(uint32_t)), "command slab alloc");
+      h->cmdCapWords = words;
+    }
+  }
+  sc.cmdBuf = h->cmdBuf;
+  CK(cabac::launchEncodeResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out, out_offsets,
+                                 out_sizes, num_bins, tu_flags, ctx_out, status),
+     "encode_residual kernels");
+  h->launches += sc.twoStage ? 5 : 4;  // cost+capacity, order, slab scan, then fused | stage P + stage D
   return CABAC_OK;
 }
 

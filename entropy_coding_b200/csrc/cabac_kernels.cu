@@ -50,20 +50,33 @@ __global__ void cost_bytes_kernel(const uint64_t *__restrict__ inOffsets, size_t
   }
 }
 
+// Upper bound of the command words one block can produce: header <= 23,
+// <= 2 per coefficient group (group flag, sign word), context-coded words <= 1.75 A + 8 (the
+// regular-bin budget), <= 3 per coefficient of Golomb-Rice / sign words in the bypass passes.
+__device__ __forceinline__ uint32_t tuCmdCapacity(const cabac_tu_desc &d) {
+  const uint32_t lw = d.log2_w < 5 ? d.log2_w : 5, lh = d.log2_h < 5 ? d.log2_h : 5;
+  const uint32_t area = 1u << (lw + lh);
+  const uint32_t log2cg = (lw >= 2 && lh >= 2) ? 4u : ((lw + lh <= 3) ? 2u : 4u);
+  const uint32_t numCG = area >> log2cg ? area >> log2cg : 1u;
+  return 5u * area + 2u * numCG + 32u;
+}
+
 // encode: one streaming pass over the coefficients, ~2 bins per significant bit
 __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__restrict__ tus,
                                                          const uint64_t *__restrict__ tuOffsets,
                                                          const int32_t *__restrict__ coeffs, size_t n,
-                                                         uint32_t *__restrict__ cost) {
+                                                         uint32_t *__restrict__ cost,
+                                                         uint32_t *__restrict__ capWords) {
   const int lane = threadIdx.x & 31;
   const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
   for (size_t s = warp; s < n; s += nWarps) {
-    uint32_t c = 0;
+    uint32_t c = 0, cap = 0;
     for (uint64_t t = tuOffsets[s]; t < tuOffsets[s + 1]; t++) {
       const cabac_tu_desc d = tus[t];
       const int32_t *src = coeffs + d.coeff_offset;
       const int total = 1 << (d.log2_w + d.log2_h);
+      cap += tuCmdCapacity(d);
       if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
         for (int i = lane * 4; i < total; i += 128) {
           const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
@@ -79,7 +92,10 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
       c += lane == 0 ? 8u + (uint32_t(total) >> 4) : 0u;
     }
     c = __reduce_add_sync(FULL, c);
-    if (lane == 0) cost[s] = c;
+    if (lane == 0) {
+      cost[s] = c;
+      if (capWords) capWords[s] = (cap + 3u) & ~3u;  // keeps every substream's slab 16-byte aligned
+    }
   }
 }
 
@@ -326,7 +342,6 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
 // ---------------------------------------------------------------------------
 struct __align__(16) EncWarpSmem {
   uint4 ctx[RCTX];
-  uint8_t ring[STAGE_BYTES];
   int16_t tile[32 * 32];
   uint32_t queue[QUEUE_WORDS];
   uint16_t cgMask[64];  // nonzero mask of every coefficient group, by scan index
@@ -586,6 +601,18 @@ __device__ __forceinline__ int produceTsCG(uint32_t *q, const int16_t *tile, con
   return n;
 }
 
+// ---------------------------------------------------------------------------
+// K4a: fused lockstep encoder (produce + drain in one kernel, one warp per substream).
+// Chosen for batches with few, long substreams (see launchEncodeResidual).
+// ---------------------------------------------------------------------------
+struct __align__(16) FusedEncWarpSmem {
+  uint4 ctx[RCTX];
+  uint8_t ring[STAGE_BYTES];
+  int16_t tile[32 * 32];
+  uint32_t queue[QUEUE_WORDS];
+  uint16_t cgMask[64];
+};
+
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
@@ -594,9 +621,9 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
-  __shared__ EncWarpSmem smem[WARPS_PER_BLOCK];
+  __shared__ FusedEncWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  EncWarpSmem &sm = smem[wib];
+  FusedEncWarpSmem &sm = smem[wib];
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
@@ -737,6 +764,233 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
 }
 
 // ---------------------------------------------------------------------------
+// K4b: two-stage encoder, stage P (binarise + resolve probabilities -> command words in HBM)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+produce_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
+                        const cabac_substream_params *__restrict__ params, size_t nSub,
+                        const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
+                        uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
+                        uint32_t *__restrict__ cmdCounts, uint8_t *__restrict__ tuFlags,
+                        cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
+                        const uint32_t *__restrict__ order, uint32_t *cursor) {
+  __shared__ EncWarpSmem smem[WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  EncWarpSmem &sm = smem[wib];
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
+    const cabac_substream_params p = params[sub];
+    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    uint32_t *cmdBase = cmds + cmdOffsets[sub];  // this substream's resolved command words
+    uint32_t cmdN = 0;
+    uint32_t st = 0;
+    const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
+    const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
+    uint64_t t = tuOffsets[sub];
+    const uint64_t t1 = tuOffsets[sub + 1];
+
+    // per-block producer state
+    bool inTu = false, tsPath = false, bdpcm = false;
+    cabac_tu_desc d;
+    TuGeom g;
+    uint32_t res = 0;
+    int lastCG = 0, scanPosLast = 0, s = 0, state = 0, remRegBins = 0, remBinsTS = 0;
+    uint64_t sigGroups = 0;
+
+    // Every iteration produces one batch of command words (block header and/or one coefficient
+    // group), resolves its probabilities and appends it to the substream's slab.
+    for (;;) {
+      int nq = 0;
+      if (!inTu) {
+        if (t == t1) break;
+        d = tus[t];
+        g = makeGeom(d);
+        const bool ts = (d.flags & CABAC_TU_TS) != 0;
+        tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
+        bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
+        res = ts ? CABAC_TUR_TS : 0;
+        if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        // ---- pre-scan: non-zero mask per coefficient group, last position ----
+        lastCG = -1;
+        const int cgSize = 1 << g.log2cg;
+        const int perIter = 32 >> g.log2cg;  // coefficient groups handled per iteration
+        for (int s0 = 0; s0 < g.numCG; s0 += perIter) {
+          const int sc = s0 + (lane >> g.log2cg), pl = lane & (cgSize - 1);
+          bool nz = false;
+          if (sc < g.numCG) {
+            int x, y;
+            scanXY(g, (sc << g.log2cg) + pl, x, y);
+            nz = sm.tile[(y << g.log2tw) + x] != 0;
+          }
+          const uint32_t b = __ballot_sync(FULL, nz);
+          if (pl == 0 && sc < g.numCG)
+            sm.cgMask[sc] = uint16_t((b >> (lane & ~(cgSize - 1))) & ((1u << cgSize) - 1u));
+          if (b) lastCG = s0 + ((31 - __clz(b)) >> g.log2cg);
+        }
+        __syncwarp();
+        if (lastCG < 0) {  // "Coefficient coding called for empty TU", cabac_writer.cpp:2457
+          st |= CABAC_SS_EMPTY_TU;
+          if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+          t++;
+          continue;
+        }
+        // transform_skip_flag (ts_flag, cabac_writer.cpp:2527-2535)
+        if (d.flags & CABAC_TU_TS_ALLOWED) sm.queue[nq++] = CABAC_MK_CTX(R_TS_FLAG + (g.comp ? 1 : 0), ts);
+        if (tsPath) {
+          s = 0;
+          remBinsTS = ((g.w * g.h) * 7) >> 2;
+        } else {
+          scanPosLast = (lastCG << g.log2cg) + (31 - __clz(uint32_t(sm.cgMask[lastCG])));
+          if (!ts && g.w >= 4 && g.h >= 4) {  // CUCtx side effects, cabac_writer.cpp:2460-2478
+            const int maxLfnstPos = ((g.h == 4 && g.w == 4) || (g.h == 8 && g.w == 8)) ? 7 : 15;
+            if (scanPosLast > maxLfnstPos) res |= CABAC_TUR_VIOLATES_LFNST;
+            if (scanPosLast >= 1) res |= CABAC_TUR_LFNST_LAST_POS;
+          }
+          if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
+          int x, y;
+          scanXY(g, scanPosLast, x, y);
+          nq += pushLastSigCoeff(sm.queue + nq, g, x, y);
+          state = 0;
+          remRegBins = regBinLimit(g);
+          s = lastCG;
+        }
+        sigGroups = 0;
+        inTu = true;
+        __syncwarp();
+      }
+      bool endTu;
+      if (tsPath) {
+        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups);
+        s++;
+        endTu = s == g.numCG;
+      } else {
+        const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
+        const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
+        const bool sig = sm.cgMask[s] != 0;
+        // initSubblock, context_modelling.cpp:81-106
+        if (sig) sigGroups |= 1ull << cgPos;
+        const bool zeroedOut = g.sbtZero && ((g.h == 32 && cgy >= (16 >> g.log2cgh)) ||
+                                             (g.w == 32 && cgx >= (16 >> g.log2cgw)));
+        if (!zeroedOut) {
+          const bool codeSigGroup = s != lastCG && s != 0;
+          const int right = (cgx + 1 < g.wig) ? int((sigGroups >> (cgPos + 1)) & 1) : 0;
+          const int lower = (cgy + 1 < g.hig) ? int((sigGroups >> (cgPos + g.wig)) & 1) : 0;
+          const int sigGroupCtx = R_SIG_GROUP + 2 * g.ch + (right | lower);
+          if (codeSigGroup && !sig) {
+            sm.queue[nq++] = CABAC_MK_CTX(sigGroupCtx, 0);
+          } else {
+            nq += binariseCG(sm.queue + nq, sm.tile, g, lane, s, scanPosLast, codeSigGroup, sigGroupCtx, depQuant,
+                             signHiding, state, remRegBins);
+            if (sig && g.comp == 0 && (cgy > 3 || cgx > 3)) res |= CABAC_TUR_VIOLATES_MTS;
+          }
+        }
+        s--;
+        endTu = s < 0;
+      }
+      if (endTu) {
+        if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+        t++;
+        inTu = false;
+      }
+      __syncwarp();
+      lsResolveQueue(sm.ctx, sm.queue, nq, lane);
+      for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
+      cmdN += uint32_t(nq);
+      __syncwarp();
+    }
+    if (lane == 0) {
+      cmdCounts[sub] = cmdN;
+      status[sub] = st;
+    }
+    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K4b: stage D, the interval coder.  One THREAD per substream (32 per warp, neighbours in
+// the longest-first order, so lanes of a warp carry similar lengths).  Resolved command
+// words are staged global -> shared with 16-byte cp.async, double buffered: per 32-word
+// chunk lane L fetches quarter (L & 7) of substream 4r + (L >> 3), r = 0..7.
+// ---------------------------------------------------------------------------
+constexpr int RC_WARPS = 4;
+constexpr int RC_ROW = 36;  // words per staged row: 32 + padding, rows stay 16-byte aligned
+
+__device__ __forceinline__ void cpAsync16(void *smemDst, const void *gmemSrc) {
+  const uint32_t d = uint32_t(__cvta_generic_to_shared(smemDst));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmemSrc) : "memory");
+}
+
+__global__ void __launch_bounds__(RC_WARPS * 32)
+range_code_kernel(const uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
+                  const uint32_t *__restrict__ cmdCounts, const cabac_substream_params *__restrict__ params,
+                  size_t nSub, uint8_t *__restrict__ out, const uint64_t *__restrict__ outOffsets,
+                  uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins, uint32_t *__restrict__ status,
+                  const uint32_t *__restrict__ order) {
+  __shared__ __align__(16) uint32_t stage[RC_WARPS][2][32 * RC_ROW];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const size_t slot = (size_t(blockIdx.x) * RC_WARPS + wib) * 32 + lane;
+  const bool valid = slot < nSub;
+  const size_t sub = valid ? (order ? size_t(order[slot]) : slot) : 0;
+  const uint32_t count = valid ? cmdCounts[sub] : 0u;
+  const uint32_t *src = cmds + (valid ? cmdOffsets[sub] : 0);
+  const cabac_substream_params p = valid ? params[sub] : cabac_substream_params{0, 0, 0, 0};
+  RangeCoder enc;
+  enc.start(out + (valid ? outOffsets[sub] : 0), valid ? uint32_t(outOffsets[sub + 1] - outOffsets[sub]) : 0u);
+  const uint32_t maxCount = __reduce_max_sync(FULL, count);
+  const uint32_t nChunks = (maxCount + 31u) >> 5;
+  uint32_t *st = stage[wib][0];
+
+  auto fetch = [&](uint32_t chunk) {
+    uint32_t *dst = st + (chunk & 1u) * (32 * RC_ROW);
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+      const int j = 4 * r + (lane >> 3);
+      const uint32_t cj = __shfl_sync(FULL, count, j);
+      const uint64_t pj = __shfl_sync(FULL, reinterpret_cast<uint64_t>(src), j);
+      const uint32_t w0 = chunk * 32u + uint32_t(lane & 7) * 4u;
+      if (w0 < cj) cpAsync16(dst + j * RC_ROW + (lane & 7) * 4, reinterpret_cast<const uint32_t *>(pj) + w0);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  if (nChunks) fetch(0);
+  for (uint32_t c = 0; c < nChunks; c++) {
+    if (c + 1 < nChunks) {
+      fetch(c + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncwarp();
+    const uint32_t *row = st + (c & 1u) * (32 * RC_ROW) + lane * RC_ROW;
+    const uint32_t lim = min(32u, maxCount - c * 32u);
+#pragma unroll 1
+    for (uint32_t i = 0; i < lim; i++) {
+      if (c * 32u + i < count) {
+        const uint32_t w = row[i];
+        const uint32_t kind = w >> 29;
+        if (kind <= CABAC_CMD_EP) {
+          enc.step(w);  // branch-free for the two hot kinds, so mixed lanes do not serialise
+        } else if (kind == CABAC_CMD_TRM) {
+          enc.trm(w & 1u);
+        } else {  // CABAC_CMD_ALIGN
+          enc.range = 256;
+        }
+        enc.flushBits();
+      }
+    }
+    __syncwarp();
+  }
+  if (valid) {
+    const uint32_t total = enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+    outSizes[sub] = total;
+    if (numBins) numBins[sub] = enc.nbins;
+    if (total > enc.cap && status) status[sub] |= CABAC_SS_OUT_OVERFLOW;
+  }
+}
+
+// ---------------------------------------------------------------------------
 // K5: residual-level decoder
 // ---------------------------------------------------------------------------
 struct __align__(16) DecWarpSmem {
@@ -816,7 +1070,8 @@ __global__ void __launch_bounds__(1024) entry_points_kernel(const uint32_t *__re
   for (size_t base = 0; base < n; base += blockDim.x) {
     const size_t i = base + threadIdx.x;
     uint64_t v = i < n ? sizes[i] : 0;
-    if (i < n && v > capOffsets[i + 1] - capOffsets[i]) v = capOffsets[i + 1] - capOffsets[i];  // overflowed slab
+    if (capOffsets && i < n && v > capOffsets[i + 1] - capOffsets[i])
+      v = capOffsets[i + 1] - capOffsets[i];  // overflowed slab
     uint64_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -990,18 +1245,41 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
   return cudaGetLastError();
 }
 
+// Residual encode, part 1: per-substream cost and command-slab capacity, longest-first order,
+// slab offsets (exclusive scan; cmdOffsets[nSub] = words the slab must hold).
+cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
+                                const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs) {
+  (void)device;
+  if (nSub == 0) return cudaSuccess;
+  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords);
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
+  return cudaGetLastError();
+}
+
+// Part 2: stage P (binarise + resolve probabilities -> command words) and stage D (interval coder).
 cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                  const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
                                  const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint8_t *out,
                                  const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
                                  uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost);
-  cudaError_t e = launchOrder(s, sc, nSub);
+  if (!sc.twoStage) {
+    encode_residual_kernel<<<persistentGrid(encode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+        tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
+        status ? status : sc.statusScratch, sc.order, sc.cursor);
+    return cudaGetLastError();
+  }
+  produce_residual_kernel<<<persistentGrid(produce_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
+      status ? status : sc.statusScratch, sc.order, sc.cursor);
+  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  encode_residual_kernel<<<persistentGrid(encode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut, status,
-      sc.order, sc.cursor);
+  const size_t perBlock = RC_WARPS * 32;
+  range_code_kernel<<<unsigned((nSub + perBlock - 1) / perBlock), RC_WARPS * 32, 0, s>>>(
+      sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, params, nSub, out, outOffsets, outSizes, numBins,
+      status ? status : sc.statusScratch, sc.order);
   return cudaGetLastError();
 }
 

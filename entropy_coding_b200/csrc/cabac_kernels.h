@@ -12,6 +12,13 @@ struct Sched {
   uint32_t *cost;
   uint32_t *order;
   uint32_t *cursor;
+  // residual encode (two-stage): command-slab bookkeeping
+  uint32_t *capWords;       // [n]   upper bound of command words per substream
+  uint32_t *cmdCounts;      // [n]   words stage P produced
+  uint32_t *statusScratch;  // [n]   when the caller passes no status array
+  uint64_t *cmdOffsets;     // [n+1] slab offsets (words); [n] = total
+  uint32_t *cmdBuf;         // the slab
+  bool twoStage;            // residual encode: stage P + stage D instead of the fused lockstep kernel
 };
 constexpr int kLaunchesPerCodingCall = 3;
 
@@ -28,6 +35,8 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
                              const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status);
+cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
+                                const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs);
 cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
                                  const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,

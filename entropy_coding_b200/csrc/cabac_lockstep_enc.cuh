@@ -21,7 +21,7 @@ namespace cabac {
 
 // Output staging, uniform on all lanes: bytes go to a shared-memory ring and leave
 // for HBM as coalesced 16-byte stores.
-struct LsOut {
+struct LsOut {  // (kept for the single-kernel lockstep variant)
   uint8_t *ring;  // shared, STAGE_BYTES, 16-byte aligned
   uint8_t *dst;   // this substream's slab
   uint32_t cap, n, flushed;
@@ -57,12 +57,47 @@ struct LsOut {
   }
 };
 
-struct LsEncoder {
+// Stage D output: one byte stream per LANE, assembled in a register and stored as aligned words.
+struct LaneOut {
+  uint8_t *dst;
+  uint32_t cap, n, acc;
+  bool aligned;
+  __device__ __forceinline__ void init(uint8_t *p, uint32_t c) {
+    dst = p;
+    cap = c;
+    n = 0;
+    acc = 0;
+    aligned = (reinterpret_cast<uintptr_t>(p) & 3u) == 0;
+  }
+  __device__ __forceinline__ void put(uint32_t byte) {
+    acc = (acc >> 8) | (byte << 24);
+    n++;
+    if (aligned) {
+      if ((n & 3u) == 0 && n <= cap) *reinterpret_cast<uint32_t *>(dst + n - 4) = acc;
+    } else if (n <= cap) {
+      dst[n - 1] = uint8_t(byte);
+    }
+  }
+  __device__ __forceinline__ void finish() {  // the bytes still in `acc`
+    if (!aligned) return;
+    const uint32_t rem = n & 3u;
+    const uint32_t v = acc >> (8u * (4u - rem));
+    for (uint32_t k = 0; k < rem; k++)
+      if (n - rem + k < cap) dst[n - rem + k] = uint8_t(v >> (8u * k));
+    // a word that crossed `cap` was not stored: write its in-range head byte-wise
+    if (rem == 0 && n > cap && (n - 4) < cap)
+      for (uint32_t k = 0; n - 4 + k < cap; k++) dst[n - 4 + k] = uint8_t(acc >> (8u * k));
+  }
+};
+
+
+template <typename Out>
+struct ArithEncoder {
   uint64_t low;
   uint32_t range, bufferedByte;
   int numBuffered, bitsLeft;
   uint32_t nbins;
-  LsOut out;
+  Out out;
 
   // start(), arith_codec.cpp:329-337
   __device__ __forceinline__ void start() {
@@ -113,6 +148,32 @@ struct LsEncoder {
     const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
     const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
     return e.x - d0 - d1 + (bin ? e.y : 0u);
+  }
+  // the same with the probability already resolved by stage P: k = LPS table row, isLps
+  __device__ __forceinline__ void encodeResolved(uint32_t k, bool isLps) {
+    const uint32_t lps = ((k * (range >> 5)) >> 1) + 4;
+    nbins++;
+    const uint32_t rmps = range - lps;
+    const int n = isLps ? __clz(int(lps | 7u)) - 23 : 1 - int(rmps >> 8);
+    low = (low + (isLps ? rmps : 0u)) << n;
+    range = (isLps ? lps : rmps) << n;
+    bitsLeft -= n;
+  }
+  // One resolved CTX word or one EP word, without a branch between the two:
+  //   (low + x) << n == (low << n) + (x << n), so both kinds are low = (low << n) + addend.
+  __device__ __forceinline__ void step(uint32_t w) {
+    const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+    const bool isLps = (w >> 6) & 1u;
+    const uint32_t epN = (w >> 24) & 31u;
+    const uint32_t lps = (((w & 63u) * (range >> 5)) >> 1) + 4;
+    const uint32_t rmps = range - lps;
+    const uint32_t nCtx = isLps ? uint32_t(__clz(int(lps | 7u)) - 23) : 1u - (rmps >> 8);
+    const uint32_t n = isCtx ? nCtx : epN;
+    const uint64_t add = isCtx ? uint64_t(isLps ? rmps << nCtx : 0u) : uint64_t(range) * (w & 0xFFFFFFu);
+    range = isCtx ? (isLps ? lps : rmps) << nCtx : range;
+    low = (low << n) + add;
+    bitsLeft -= int(n);
+    nbins += isCtx ? 1u : epN;
   }
   // encodeBinsEP, arith_codec.cpp:401-424, n <= 24 bins at once
   __device__ __forceinline__ void ep(uint32_t bins, int n) {
@@ -171,6 +232,9 @@ struct LsEncoder {
   }
 };
 
+typedef ArithEncoder<LsOut> LsEncoder;
+typedef ArithEncoder<LaneOut> LaneEncoder;
+
 // The single arithmetic-coder site: walks n command words (CTX / EP kinds).
 __device__ __forceinline__ void lsDrain(LsEncoder &enc, uint4 *ctx, const uint32_t *queue, int n) {
   if (n <= 0) return;
@@ -224,5 +288,193 @@ __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w
   w1 = CABAC_MK_EP(suffix, suffixLen);
   return 2;
 }
+
+
+// ===========================================================================
+// Two-stage encoder.  The bins of an encoder do not depend on the coder state, and
+// the probability a context-coded bin is coded with depends only on the earlier
+// bins of the SAME context.  So everything except the interval recurrence is done
+// by the substream's warp in parallel (stage P), which leaves "resolved" command
+// words in HBM; stage D is a pure interval coder with one THREAD per substream:
+// 32 substreams per warp-instruction, no context table, no model update.
+//
+// Resolved word: kind in bits 31..29 as in cabac_b200.h; a CTX word carries
+//   bits 0..5 = (q ^ mps-mask) >> 2  (the LPS table row, BinProbModel_Std::getLPS, contexts.cpp:945-950)
+//   bit  6    = 1 when the bin is the LPS
+// ===========================================================================
+
+// Stage P, probability modelling of one queue (in place).  Lane i owns command i of each
+// 32-command slice; commands that share a context are serialised by their rank among
+// the slice's users of that context (match_any), everything else runs in parallel.
+__device__ __forceinline__ void lsResolveQueue(uint4 *ctx, uint32_t *queue, int n, int lane) {
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    uint32_t w = i < n ? queue[i] : (uint32_t(CABAC_CMD_EP) << 29);
+    const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+    const uint32_t idx = w & 511u, bin = (w >> 9) & 1u;
+    const uint32_t peers = __match_any_sync(FULL, isCtx ? idx : (0x8000u | uint32_t(lane)));
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int rounds = __reduce_max_sync(FULL, isCtx ? rank : 0);
+    for (int r = 0; r <= rounds; r++) {
+      if (isCtx && rank == r) {
+        const uint4 e = ctx[idx];
+        const uint32_t q = ((e.x >> 16) + (e.x & 0xFFFFu)) >> 8;
+        const uint32_t mps = q >> 7;
+        const uint32_t qq = q ^ (0xFFu & (0u - mps));
+        const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
+        const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
+        ctx[idx].x = e.x - d0 - d1 + (bin ? e.y : 0u);
+        w = (qq >> 2) | ((bin ^ mps) << 6);
+      }
+      __syncwarp();
+    }
+    if (i < n) queue[i] = w;
+  }
+  __syncwarp();
+}
+
+
+// ---------------------------------------------------------------------------
+// Stage D coder: interval recurrence + byte output for ONE substream per lane.
+//
+// Output bytes are assembled big-endian in a 64-bit register that always keeps the most
+// recent 4..7 bytes pending, so a carry out of `low` is a plain integer add on the pending
+// bytes (the reference holds one byte + a count of 0xFF bytes for the same purpose,
+// arith_codec.cpp:524-546).  Only a carry through >= 4 pending 0xFF bytes has to patch bytes
+// already stored in the slab (carrySlow).  `vtmPending` tracks m_numBufferedBytes so that a
+// substream that is NOT terminated reports exactly the bytes the reference would have written.
+// ---------------------------------------------------------------------------
+struct RangeCoder {
+  uint64_t low, acc;
+  uint32_t range, nbins;
+  int bitsLeft;
+  uint32_t cnt;         // bytes pending in acc (0..7)
+  uint32_t n;           // bytes stored to the slab
+  uint32_t vtmPending;  // m_numBufferedBytes of the reference coder
+  uint8_t *dst;
+  uint32_t cap;
+
+  __device__ __forceinline__ void start(uint8_t *p, uint32_t c) {
+    low = 0;
+    acc = 0;
+    range = 510;
+    nbins = 0;
+    bitsLeft = 23;
+    cnt = 0;
+    n = 0;
+    vtmPending = 0;
+    dst = p;
+    cap = c;
+  }
+  __device__ __forceinline__ void storeByte(uint32_t at, uint32_t b) {
+    if (at < cap) dst[at] = uint8_t(b);
+  }
+  // carry out of all pending bytes: increment the stored bytes backwards (essentially never)
+  __device__ __noinline__ static void carrySlow(uint8_t *dst, uint32_t cap, uint32_t n) {
+    while (n > 0) {
+      n--;
+      if (n >= cap) continue;
+      const uint8_t b = uint8_t(dst[n] + 1);
+      dst[n] = b;
+      if (b != 0) break;
+    }
+  }
+  __device__ __forceinline__ void spill4() {  // oldest 4 of 8 pending bytes -> slab
+    const uint32_t be = uint32_t(acc >> 32);
+    if ((reinterpret_cast<uintptr_t>(dst) & 3u) == 0 && n + 4u <= cap) {
+      *reinterpret_cast<uint32_t *>(dst + n) = __byte_perm(be, 0, 0x0123);
+    } else {
+      storeByte(n, be >> 24);
+      storeByte(n + 1, (be >> 16) & 0xFF);
+      storeByte(n + 2, (be >> 8) & 0xFF);
+      storeByte(n + 3, be & 0xFF);
+    }
+    n += 4;
+    acc &= 0xFFFFFFFFull;
+    cnt = 4;
+  }
+  __device__ __forceinline__ void addCarry(uint32_t carry) {
+    acc += carry;
+    if (cnt < 8 && (acc >> (8 * cnt))) {  // rippled through every pending byte
+      acc &= (1ull << (8 * cnt)) - 1ull;
+      carrySlow(dst, cap, n);
+    }
+  }
+  // one writeOut() step, arith_codec.cpp:524-546
+  __device__ __forceinline__ void emitByte() {
+    const int s = 24 - bitsLeft;
+    const uint32_t lead = uint32_t(low >> s);
+    low -= uint64_t(lead) << s;
+    bitsLeft += 8;
+    addCarry(lead >> 8);
+    acc = (acc << 8) | (lead & 0xFFu);
+    cnt++;
+    vtmPending = lead == 0xFFu ? vtmPending + 1u : 1u;
+    if (cnt == 8) spill4();
+  }
+  __device__ __forceinline__ void flushBits() {
+    while (bitsLeft < 12) emitByte();
+  }
+  // One resolved CTX word or one EP word, without a branch between the two:
+  //   (low + x) << n == (low << n) + (x << n), so both kinds are low = (low << n) + addend.
+  __device__ __forceinline__ void step(uint32_t w) {
+    const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+    const bool isLps = (w >> 6) & 1u;
+    const uint32_t epN = (w >> 24) & 31u;
+    const uint32_t lps = (((w & 63u) * (range >> 5)) >> 1) + 4;
+    const uint32_t rmps = range - lps;
+    const uint32_t nCtx = isLps ? uint32_t(__clz(int(lps | 7u)) - 23) : 1u - (rmps >> 8);
+    const uint32_t n_ = isCtx ? nCtx : epN;
+    const uint64_t add = isCtx ? uint64_t(isLps ? rmps << nCtx : 0u) : uint64_t(range) * (w & 0xFFFFFFu);
+    range = isCtx ? (isLps ? lps : rmps) << nCtx : range;
+    low = (low << n_) + add;
+    bitsLeft -= int(n_);
+    nbins += isCtx ? 1u : epN;
+  }
+  // encodeBinTrm, arith_codec.cpp:460-478
+  __device__ __forceinline__ void trm(uint32_t bin) {
+    nbins++;
+    range -= 2;
+    if (bin) {
+      low = (low + range) << 7;
+      range = 256;
+      bitsLeft -= 7;
+    } else if (range < 256) {
+      low <<= 1;
+      range <<= 1;
+      bitsLeft--;
+    }
+    flushBits();
+  }
+  // finish() + writeByteAlignment() (arith_codec.cpp:339-357, bit_stream.cpp:152-155); returns the
+  // substream's byte count.  Without `terminate` only the bytes the reference coder would already
+  // have handed to its OutputBitstream are reported (the buffered byte and its 0xFF run stay back).
+  __device__ __forceinline__ uint32_t finish(bool terminate, bool align) {
+    uint32_t tail = 0, ntail = 0;
+    uint32_t keepBack = vtmPending;
+    if (terminate) {
+      trm(1);
+      const uint32_t carry = uint32_t(low >> (32 - bitsLeft));
+      addCarry(carry);
+      low -= uint64_t(carry) << (32 - bitsLeft);
+      tail = uint32_t(low >> 8);
+      ntail = uint32_t(24 - bitsLeft);
+      keepBack = 0;
+    }
+    if (align) {
+      tail = (tail << 1) | 1u;  // stop bit
+      ntail += 1;
+    }
+    // pending bytes, oldest first
+    for (uint32_t k = cnt; k > 0; k--) storeByte(n + (cnt - k), uint32_t(acc >> (8 * (k - 1))) & 0xFFu);
+    uint32_t total = n + cnt - keepBack;
+    while (ntail >= 8) {
+      storeByte(total++, (tail >> (ntail - 8)) & 0xFF);
+      ntail -= 8;
+    }
+    if (align && ntail) storeByte(total++, (tail << (8 - ntail)) & 0xFF);
+    return total;
+  }
+};
 
 }  // namespace cabac

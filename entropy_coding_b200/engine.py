@@ -78,6 +78,10 @@ class CabacEngine:
     def set_stream(self, cuda_stream_ptr: int | None):
         self._check(self.lib.cabac_set_stream(self.h, C.c_void_p(cuda_stream_ptr or 0)))
 
+    def set_encoder_mode(self, mode: int):
+        """0 = auto, 1 = fused lockstep kernel, 2 = two-stage (stage P + stage D)."""
+        self._check(self.lib.cabac_set_encoder_mode(self.h, int(mode)))
+
     def sync(self):
         self._check(self.lib.cabac_sync(self.h))
 

@@ -160,6 +160,13 @@ void cabac_destroy(cabac_handle *h);
  * the handle's own stream.                                                  */
 int cabac_set_stream(cabac_handle *h, void *cuda_stream);
 int cabac_sync(cabac_handle *h);
+/* Residual encoder variant.  AUTO picks by batch shape: FUSED = one warp per
+ * substream does binarisation and arithmetic coding (few, long substreams);
+ * TWO_STAGE = warps binarise and resolve probabilities into command words,
+ * then one thread per substream runs the interval coder (many substreams).
+ * Both are byte-identical.  Also settable with CABAC_B200_ENCODER=fused|two_stage. */
+enum { CABAC_ENCODER_AUTO = 0, CABAC_ENCODER_FUSED = 1, CABAC_ENCODER_TWO_STAGE = 2 };
+int cabac_set_encoder_mode(cabac_handle *h, int mode);
 const char *cabac_last_error(cabac_handle *h);
 const char *cabac_version(void);
 /* Number of kernel launches issued through this handle so far.              */

@@ -212,6 +212,42 @@ def test_residual_random_vs_oracle(engine, oracle, seed, flags, kw):
             assert (od[0][lo:hi] == d["coeffs"][lo:hi]).all() and od[1] == int(d["bits_read"][i])
 
 
+@pytest.mark.parametrize("mode", [1, 2], ids=["fused", "two_stage"])
+@pytest.mark.parametrize("seed,flags,kw", [
+    (301, None, {}),
+    (302, T | SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3, "bdpcm_fraction": 0.1}),
+    (303, SUB_DEP_QUANT, {"preset": "qp0", "tus_per_sub": (1, 4)}),        # not terminated: bytes held back
+    (304, SUB_ALIGN, {"preset": "qp32"}),
+    (305, T, {"preset": "qp0", "tus_per_sub": (20, 40), "ts_fraction": 0.0}),
+])
+def test_residual_encoder_variants(engine, oracle, mode, seed, flags, kw):
+    """Both residual encoders (fused lockstep kernel, two-stage P + D) against the oracle, byte for byte."""
+    engine.set_encoder_mode(mode)
+    try:
+        wl = W.random_substreams(70, seed, flags=flags, **kw)
+        r, outs = run_residual(engine, wl)
+        assert not r["status"].any()
+        for i in range(wl.n_sub):
+            a, b, lo, hi = sub_range(wl, i)
+            p = wl.params[i]
+            eb, nb, tuf, ectx = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]),
+                                                       int(p["flags"]), want_ctx=True)
+            assert outs[i].tobytes() == eb.tobytes(), (mode, seed, i)
+            assert int(r["num_bins"][i]) == nb and (r["tu_flags"][a:b] == tuf).all()
+            assert (r["ctx_out"][i] == ectx).all()
+        # overflow is reported, sizes stay exact, the in-capacity prefix is intact
+        small = offsets_of([48] * wl.n_sub, align=16)
+        r2 = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, small, raise_on_status=False)
+        assert (r2["sizes"] == r["sizes"]).all()
+        over = r["sizes"] > 48
+        assert ((r2["status"] & SS_OUT_OVERFLOW) != 0)[over].all() and not r2["status"][~over].any()
+        for i in range(wl.n_sub):
+            k = min(48, int(r["sizes"][i]))
+            assert r2["out"][int(small[i]):int(small[i]) + k].tobytes() == outs[i][:k].tobytes()
+    finally:
+        engine.set_encoder_mode(0)
+
+
 def test_residual_all_shapes_single_coeff(engine, oracle):
     """Every block shape 2..64 x 2..64, one level at DC / at the last coded column, extreme magnitudes."""
     tus, coeffs, cur = [], [], 0
