@@ -33,6 +33,8 @@ _SIGS = {
     "cabac_ctx_init_table": (C.c_int, [C.c_int, _P]),
     "cabac_encode_bins": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_encode_bins_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_stream": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_stream_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_decode_bins": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P]),
     "cabac_decode_bins_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P]),
     "cabac_encode_residual": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),

@@ -108,6 +108,29 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
   return cudaSuccess;
 }
 
+// Reads the command-slab size the prepare kernels computed (8 bytes; the one synchronisation
+// point of a two-stage encode call) and grows the slab if needed.
+cudaError_t ensureCmdSlab(cabac_handle *h, cabac::Sched &sc, size_t n_sub) {
+  cudaError_t e;
+  if (!h->pinnedTotal && (e = cudaHostAlloc(&h->pinnedTotal, sizeof(uint64_t), cudaHostAllocDefault)) != cudaSuccess)
+    return e;
+  if ((e = cudaMemcpyAsync(h->pinnedTotal, sc.cmdOffsets + n_sub, sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                           h->stream)) != cudaSuccess)
+    return e;
+  if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return e;
+  const size_t needWords = size_t(*h->pinnedTotal);
+  if (needWords > h->cmdCapWords) {
+    if (h->cmdBuf) cudaFree(h->cmdBuf);
+    h->cmdBuf = nullptr;
+    h->cmdCapWords = 0;
+    const size_t words = needWords + (needWords >> 3) + 1024;
+    if ((e = cudaMalloc(&h->cmdBuf, words * sizeof(uint32_t))) != cudaSuccess) return e;
+    h->cmdCapWords = words;
+  }
+  sc.cmdBuf = h->cmdBuf;
+  return cudaSuccess;
+}
+
 // From this many substreams on, stage D (32 substreams per warp) fills the machine.
 constexpr size_t kTwoStageMinSubstreams = 32768;
 
@@ -221,20 +244,20 @@ int cabac_ctx_init_dev(cabac_handle *h, const cabac_substream_params *params, si
   return CABAC_OK;
 }
 
+int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                            const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                            const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                            const cabac_ctx_model *ctx_in, uint8_t *out, const uint64_t *out_offsets,
+                            uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                            uint32_t *status);
+
+// A recorded bin stream is a command stream without TU markers.
 int cabac_encode_bins_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
                           const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
                           uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
                           cabac_ctx_model *ctx_out, uint32_t *status) {
-  if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)))
-    return badArg(h, "cabac_encode_bins_dev");
-  DeviceGuard g(h->device);
-  cabac::Sched sc;
-  CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  CK(cabac::launchEncodeBins(h->stream, h->device, sc, cmds, cmd_offsets, params, n_sub, ctx_in, out, out_offsets,
-                             out_sizes, num_bins, ctx_out, status),
-     "encode_bins_kernel");
-  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
-  return CABAC_OK;
+  return cabac_encode_stream_dev(h, cmds, cmd_offsets, nullptr, nullptr, params, n_sub, nullptr, ctx_in, out,
+                                 out_offsets, out_sizes, num_bins, nullptr, ctx_out, status);
 }
 
 int cabac_decode_bins_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const uint32_t *cmds,
@@ -263,33 +286,40 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs), "encode prepare kernels");
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, nullptr), "encode prepare kernels");
   // Few long substreams: one warp per substream, fused.  Many substreams: the two-stage coder,
   // whose interval stage runs one substream per thread.
   sc.twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
                 (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
-  if (sc.twoStage) {
-    // The command slab is sized from the descriptors, which live on the device: read the total
-    // back (8 bytes; the one synchronisation point of this call) and grow the slab if needed.
-    if (!h->pinnedTotal) CK(cudaHostAlloc(&h->pinnedTotal, sizeof(uint64_t), cudaHostAllocDefault), "pinned alloc");
-    CK(cudaMemcpyAsync(h->pinnedTotal, sc.cmdOffsets + n_sub, sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream),
-       "slab size read-back");
-    CK(cudaStreamSynchronize(h->stream), "sync");
-    const size_t needWords = size_t(*h->pinnedTotal);
-    if (needWords > h->cmdCapWords) {
-      if (h->cmdBuf) cudaFree(h->cmdBuf);
-      h->cmdBuf = nullptr;
-      h->cmdCapWords = 0;
-      const size_t words = needWords + (needWords >> 3) + 1024;
-      CK(cudaMalloc(&h->cmdBuf, words * sizeof(uint32_t)), "command slab alloc");
-      h->cmdCapWords = words;
-    }
-  }
+  if (sc.twoStage) CK(ensureCmdSlab(h, sc, n_sub), "command slab");
   sc.cmdBuf = h->cmdBuf;
   CK(cabac::launchEncodeResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out, out_offsets,
                                  out_sizes, num_bins, tu_flags, ctx_out, status),
      "encode_residual kernels");
   h->launches += sc.twoStage ? 5 : 4;  // cost+capacity, order, slab scan, then fused | stage P + stage D
+  return CABAC_OK;
+}
+
+int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                            const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                            const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                            const cabac_ctx_model *ctx_in, uint8_t *out, const uint64_t *out_offsets,
+                            uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                            uint32_t *status) {
+  if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)) || (tus && !tu_offsets))
+    return badArg(h, "cabac_encode_stream_dev");
+  DeviceGuard g(h->device);
+  if (!n_sub) return CABAC_OK;
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  sc.twoStage = true;
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, cmd_offsets),
+     "encode prepare kernels");
+  CK(ensureCmdSlab(h, sc, n_sub), "command slab");
+  CK(cabac::launchEncodeStream(h->stream, h->device, sc, cmds, cmd_offsets, tus, tu_offsets, params, n_sub, coeffs,
+                               ctx_in, out, out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
+     "encode_stream kernels");
+  h->launches += 5;
   return CABAC_OK;
 }
 
@@ -351,49 +381,71 @@ int cabac_ctx_init(cabac_handle *h, const cabac_substream_params *params, size_t
   return CABAC_OK;
 }
 
-int cabac_encode_bins(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
-                      const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
-                      uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
-                      cabac_ctx_model *ctx_out, uint32_t *status) {
+int cabac_encode_stream(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets, const cabac_tu_desc *tus,
+                        const uint64_t *tu_offsets, const cabac_substream_params *params, size_t n_sub,
+                        const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in, uint8_t *out,
+                        const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags,
+                        cabac_ctx_model *ctx_out, uint32_t *status) {
   if (!h || (n_sub && (!cmd_offsets || !params || !out || !out_offsets || !out_sizes)))
-    return badArg(h, "cabac_encode_bins");
+    return badArg(h, "cabac_encode_stream");
   if (!n_sub) return CABAC_OK;
   DeviceGuard g(h->device);
   const size_t nCmd = cmd_offsets[n_sub], outCap = out_offsets[n_sub];
+  const size_t nTu = tu_offsets ? tu_offsets[n_sub] : 0;
+  if ((nCmd && !cmds) || (nTu && (!tus || !coeffs))) return badArg(h, "cabac_encode_stream: cmds/tus/coeffs");
   uint32_t *dCmds, *dSizes, *dBins, *dStatus;
-  uint64_t *dCmdOff, *dOutOff;
+  uint64_t *dCmdOff, *dOutOff, *dTuOff;
+  cabac_tu_desc *dTus;
+  int32_t *dCoeffs;
   cabac_substream_params *dP;
   cabac_ctx_model *dCin, *dCout;
-  uint8_t *dOut;
+  uint8_t *dOut, *dTuFlags;
   Arena a(h);
   a.want((void **)&dCmds, nCmd * 4);
   a.want((void **)&dCmdOff, (n_sub + 1) * 8);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dCoeffs, nTu ? n_coeffs * 4 : 0);
   a.want((void **)&dOutOff, (n_sub + 1) * 8);
   a.want((void **)&dP, n_sub * sizeof(*params));
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
   a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dOut, outCap);
+  a.want((void **)&dTuFlags, nTu);
   a.want((void **)&dSizes, n_sub * 4);
   a.want((void **)&dBins, n_sub * 4);
   a.want((void **)&dStatus, n_sub * 4);
   CK(a.commit(), "scratch alloc");
   H2D(dCmds, cmds, nCmd * 4);
   H2D(dCmdOff, cmd_offsets, (n_sub + 1) * 8);
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  if (nTu) H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  if (nTu) H2D(dCoeffs, coeffs, n_coeffs * 4);
   H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
   H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
-  int rc = cabac_encode_bins_dev(h, dCmds, dCmdOff, dP, n_sub, ctx_in ? dCin : nullptr, dOut, dOutOff, dSizes,
-                                 dBins, ctx_out ? dCout : nullptr, dStatus);
+  int rc = cabac_encode_stream_dev(h, dCmds, dCmdOff, nTu ? dTus : nullptr, nTu ? dTuOff : nullptr, dP, n_sub,
+                                   nTu ? dCoeffs : nullptr, ctx_in ? dCin : nullptr, dOut, dOutOff, dSizes, dBins,
+                                   nTu ? dTuFlags : nullptr, ctx_out ? dCout : nullptr, dStatus);
   if (rc) return rc;
   D2H(out, dOut, outCap);
   D2H(out_sizes, dSizes, n_sub * 4);
   D2H(num_bins, dBins, n_sub * 4);
+  D2H(tu_flags, dTuFlags, nTu);
   D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
   std::vector<uint32_t> st(status ? 0 : n_sub);
   uint32_t *hst = status ? status : st.data();
   D2H(hst, dStatus, n_sub * 4);
   CK(cudaStreamSynchronize(h->stream), "sync");
   return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_encode_bins(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                      const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
+                      uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                      cabac_ctx_model *ctx_out, uint32_t *status) {
+  return cabac_encode_stream(h, cmds, cmd_offsets, nullptr, nullptr, params, n_sub, nullptr, 0, ctx_in, out,
+                             out_offsets, out_sizes, num_bins, nullptr, ctx_out, status);
 }
 
 int cabac_decode_bins(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const uint32_t *cmds,

@@ -66,13 +66,19 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          const uint64_t *__restrict__ tuOffsets,
                                                          const int32_t *__restrict__ coeffs, size_t n,
                                                          uint32_t *__restrict__ cost,
-                                                         uint32_t *__restrict__ capWords) {
+                                                         uint32_t *__restrict__ capWords,
+                                                         const uint64_t *__restrict__ rawOffsets) {
   const int lane = threadIdx.x & 31;
   const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
   for (size_t s = warp; s < n; s += nWarps) {
     uint32_t c = 0, cap = 0;
-    for (uint64_t t = tuOffsets[s]; t < tuOffsets[s + 1]; t++) {
+    if (rawOffsets) {  // recorded commands: one word each, REM commands may become two
+      const uint32_t nRaw = uint32_t(rawOffsets[s + 1] - rawOffsets[s]);
+      cap = 2u * nRaw;
+      c = lane == 0 ? nRaw : 0u;
+    }
+    for (uint64_t t = tus ? tuOffsets[s] : 0, te = tus ? tuOffsets[s + 1] : 0; t < te; t++) {
       const cabac_tu_desc d = tus[t];
       const int32_t *src = coeffs + d.coeff_offset;
       const int total = 1 << (d.log2_w + d.log2_h);
@@ -229,6 +235,33 @@ __device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_p
   }
 }
 
+// All 379 contexts (recorded command streams address them by their reference ids).
+__device__ inline void loadCtxEntriesFull(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                          size_t sub, int lane) {
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
+    if (imp) {
+      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+      ctx[id] = ctx_entry(m.state0, m.state1, win);
+    } else {
+      ctx[id] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
+    }
+  }
+  __syncwarp();
+}
+__device__ inline void storeCtxEntriesFull(const uint4 *ctx, cabac_ctx_model *ctxOut, size_t sub, int lane) {
+  if (!ctxOut) return;
+  __syncwarp();
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    cabac_ctx_model m;
+    m.state0 = uint16_t(ctx[id].x >> 16);
+    m.state1 = uint16_t(ctx[id].x & 0xFFFFu);
+    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // K2: bin-level encoder (recorded BinEncIf calls -> bytes)
 // ---------------------------------------------------------------------------
@@ -340,8 +373,9 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
 // ---------------------------------------------------------------------------
 // K4: residual-level encoder
 // ---------------------------------------------------------------------------
-struct __align__(16) EncWarpSmem {
-  uint4 ctx[RCTX];
+template <int kNumCtx>
+struct __align__(16) EncWarpSmemT {
+  uint4 ctx[kNumCtx];
   int16_t tile[32 * 32];
   uint32_t queue[QUEUE_WORDS];
   uint16_t cgMask[64];  // nonzero mask of every coefficient group, by scan index
@@ -766,28 +800,40 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
 // ---------------------------------------------------------------------------
 // K4b: two-stage encoder, stage P (binarise + resolve probabilities -> command words in HBM)
 // ---------------------------------------------------------------------------
+// kStream = false: the substream is its TU list (cabac_encode_residual).
+// kStream = true : the substream is a recorded command stream (cabac_encode_stream): BinEncIf calls
+//                  with raw context ids, and CABAC_CMD_TU markers that each code the next TU of the
+//                  substream's list (CABACWriter::residual_coding in the middle of other syntax).
+template <bool kStream>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
-produce_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
-                        const cabac_substream_params *__restrict__ params, size_t nSub,
-                        const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
-                        uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
-                        uint32_t *__restrict__ cmdCounts, uint8_t *__restrict__ tuFlags,
-                        cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
-                        const uint32_t *__restrict__ order, uint32_t *cursor) {
-  __shared__ EncWarpSmem smem[WARPS_PER_BLOCK];
+produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict__ rawOffsets,
+               const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
+               const cabac_substream_params *__restrict__ params, size_t nSub,
+               const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
+               uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
+               uint32_t *__restrict__ cmdCounts, uint8_t *__restrict__ tuFlags,
+               cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
+               const uint32_t *__restrict__ order, uint32_t *cursor) {
+  typedef EncWarpSmemT<kStream ? CABAC_NUM_CTX : RCTX> Smem;
+  __shared__ Smem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  EncWarpSmem &sm = smem[wib];
+  Smem &sm = smem[wib];
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    if (kStream)
+      loadCtxEntriesFull(sm.ctx, p, ctxIn, sub, lane);
+    else
+      loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    uint64_t rc = kStream ? rawOffsets[sub] : 0;
+    const uint64_t rc1 = kStream ? rawOffsets[sub + 1] : 0;
     uint32_t *cmdBase = cmds + cmdOffsets[sub];  // this substream's resolved command words
     uint32_t cmdN = 0;
     uint32_t st = 0;
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
-    uint64_t t = tuOffsets[sub];
-    const uint64_t t1 = tuOffsets[sub + 1];
+    uint64_t t = tus ? tuOffsets[sub] : 0;
+    const uint64_t t1 = tus ? tuOffsets[sub + 1] : 0;
 
     // per-block producer state
     bool inTu = false, tsPath = false, bdpcm = false;
@@ -798,11 +844,61 @@ produce_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *_
     uint64_t sigGroups = 0;
 
     // Every iteration produces one batch of command words (block header and/or one coefficient
-    // group), resolves its probabilities and appends it to the substream's slab.
+    // group, or a run of recorded bin commands), resolves its probabilities and appends it to the
+    // substream's slab.
     for (;;) {
       int nq = 0;
       if (!inTu) {
-        if (t == t1) break;
+        if (kStream) {
+          if (rc == rc1) break;
+          // up to 32 recorded commands, stopping at the next TU marker
+          const bool have = rc + lane < rc1;
+          const uint32_t w = have ? rawCmds[rc + lane] : (uint32_t(CABAC_CMD_TU) << 29);
+          const uint32_t kind = w >> 29;
+          const uint32_t stop = __ballot_sync(FULL, kind == CABAC_CMD_TU);
+          const int nRaw = stop ? __ffs(int(stop)) - 1 : 32;
+          if (nRaw > 0) {
+            // REM -> one or two EP words; everything else is copied (CTX words keep raw context ids)
+            uint32_t w0 = w, w1 = 0;
+            int cnt = lane < nRaw ? 1 : 0;
+            if (cnt && kind == CABAC_CMD_REM) {
+              const uint32_t rice = (w >> 24) & 31u;
+              if (rice > 12u) {  // suffix words must fit 24 bins
+                st |= CABAC_SS_BAD_CMD;
+                w0 = CABAC_MK_EP(0, 0);
+              } else {
+                cnt = lsRemWords(w & 0xFFFFFFu, rice, w0, w1);
+              }
+            } else if (cnt && (kind > CABAC_CMD_ALIGN || (kind == CABAC_CMD_EP && ((w >> 24) & 31u) > 24u) ||
+                               (kind == CABAC_CMD_CTX && (w & 511u) >= CABAC_NUM_CTX))) {
+              st |= CABAC_SS_BAD_CMD;
+              w0 = CABAC_MK_EP(0, 0);
+            }
+            const uint32_t below = (1u << lane) - 1u;
+            const uint32_t E1 = __ballot_sync(FULL, cnt >= 1), E2 = __ballot_sync(FULL, cnt == 2);
+            if (cnt) {
+              const int at = __popc(E1 & below) + __popc(E2 & below);
+              sm.queue[at] = w0;
+              if (cnt == 2) sm.queue[at + 1] = w1;
+            }
+            nq = __popc(E1) + __popc(E2);
+            st = __reduce_or_sync(FULL, st);
+            rc += uint64_t(nRaw);
+            __syncwarp();
+            lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+            for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
+            cmdN += uint32_t(nq);
+            __syncwarp();
+            continue;
+          }
+          rc++;  // a TU marker: code the next transform unit of the substream's list
+          if (t == t1) {
+            st |= CABAC_SS_BAD_CMD;
+            continue;
+          }
+        } else if (t == t1) {
+          break;
+        }
         d = tus[t];
         g = makeGeom(d);
         const bool ts = (d.flags & CABAC_TU_TS) != 0;
@@ -893,7 +989,7 @@ produce_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *_
         inTu = false;
       }
       __syncwarp();
-      lsResolveQueue(sm.ctx, sm.queue, nq, lane);
+      lsResolveQueue<kStream>(sm.ctx, sm.queue, nq, lane);  // the TU producers emit compact context ids
       for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
       cmdN += uint32_t(nq);
       __syncwarp();
@@ -902,7 +998,10 @@ produce_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *_
       cmdCounts[sub] = cmdN;
       status[sub] = st;
     }
-    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    if (kStream)
+      storeCtxEntriesFull(sm.ctx, ctxOut, sub, lane);
+    else
+      storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
     __syncwarp();
   }
 }
@@ -1248,10 +1347,11 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
 // Residual encode, part 1: per-substream cost and command-slab capacity, longest-first order,
 // slab offsets (exclusive scan; cmdOffsets[nSub] = words the slab must hold).
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
-                                const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs) {
+                                const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
+                                const uint64_t *rawOffsets) {
   (void)device;
   if (nSub == 0) return cudaSuccess;
-  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords);
+  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
@@ -1271,9 +1371,29 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
         status ? status : sc.statusScratch, sc.order, sc.cursor);
     return cudaGetLastError();
   }
-  produce_residual_kernel<<<persistentGrid(produce_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
+  produce_kernel<false><<<persistentGrid(produce_kernel<false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      nullptr, nullptr, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
       status ? status : sc.statusScratch, sc.order, sc.cursor);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const size_t perBlock = RC_WARPS * 32;
+  range_code_kernel<<<unsigned((nSub + perBlock - 1) / perBlock), RC_WARPS * 32, 0, s>>>(
+      sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, params, nSub, out, outOffsets, outSizes, numBins,
+      status ? status : sc.statusScratch, sc.order);
+  return cudaGetLastError();
+}
+
+// Recorded command streams (BinEncIf calls + TU markers): stage P in stream mode, then stage D.
+cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, const uint32_t *rawCmds,
+                               const uint64_t *rawOffsets, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                               const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
+                               const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
+                               uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
+                               uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  produce_kernel<true><<<persistentGrid(produce_kernel<true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts,
+      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.order, sc.cursor);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;

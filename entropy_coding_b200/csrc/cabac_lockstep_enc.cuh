@@ -306,12 +306,15 @@ __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w
 // Stage P, probability modelling of one queue (in place).  Lane i owns command i of each
 // 32-command slice; commands that share a context are serialised by their rank among
 // the slice's users of that context (match_any), everything else runs in parallel.
+// kTranslate: the words carry the residual kernels' compact context ids while `ctx` is the full
+// 379-entry table.
+template <bool kTranslate>
 __device__ __forceinline__ void lsResolveQueue(uint4 *ctx, uint32_t *queue, int n, int lane) {
   for (int base = 0; base < n; base += 32) {
     const int i = base + lane;
     uint32_t w = i < n ? queue[i] : (uint32_t(CABAC_CMD_EP) << 29);
     const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
-    const uint32_t idx = w & 511u, bin = (w >> 9) & 1u;
+    const uint32_t idx = kTranslate ? uint32_t(rctx_inv(int(w & 511u))) : (w & 511u), bin = (w >> 9) & 1u;
     const uint32_t peers = __match_any_sync(FULL, isCtx ? idx : (0x8000u | uint32_t(lane)));
     const int rank = __popc(peers & ((1u << lane) - 1u));
     const int rounds = __reduce_max_sync(FULL, isCtx ? rank : 0);

@@ -138,6 +138,25 @@ class CabacEngine:
             self._check(rc, status)
         return dict(out=out, sizes=sizes, num_bins=bins, status=status, ctx_out=ctx_out)
 
+    def encode_stream(self, cmds, cmd_offsets, tus, tu_offsets, params, coeffs, out_offsets, ctx_in=None,
+                      want_ctx=False, raise_on_status=True):
+        """Recorded command streams with CABAC_CMD_TU markers (the CABACWriter seam)."""
+        cmds, cmd_offsets = _np(cmds, np.uint32), _np(cmd_offsets, np.uint64)
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        n = len(params)
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_stream(self.h, _hp(cmds), _hp(cmd_offsets), _hp(tus), _hp(tu_offsets), _hp(params),
+                                          n, _hp(coeffs), coeffs.size, _hp(ctx_in), _hp(out), _hp(out_offsets),
+                                          _hp(sizes), _hp(bins), _hp(tu_flags), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
     def decode_bins(self, data, in_offsets, cmds, cmd_offsets, params, ctx_in=None, want_ctx=False,
                     raise_on_status=True):
         data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)

@@ -22,7 +22,7 @@ SUB_TERMINATE, SUB_ALIGN, SUB_CTX_IN = 8, 16, 32
 TU_TS, TU_TS_ALLOWED, TU_BDPCM, TU_SBT_ZEROOUT = 1, 2, 4, 8
 TUR_TS, TUR_VIOLATES_LFNST, TUR_LFNST_LAST_POS, TUR_MTS_LAST_POS, TUR_VIOLATES_MTS = 1, 2, 4, 8, 16
 # command kinds
-CMD_CTX, CMD_EP, CMD_REM, CMD_TRM, CMD_ALIGN = 0, 1, 2, 3, 4
+CMD_CTX, CMD_EP, CMD_REM, CMD_TRM, CMD_ALIGN, CMD_TU = 0, 1, 2, 3, 4, 5
 
 
 def mk_ctx(ctx: int, b: int) -> int:
@@ -43,3 +43,7 @@ def mk_trm(b: int) -> int:
 
 def mk_align() -> int:
     return CMD_ALIGN << 29
+
+
+def mk_tu() -> int:
+    return CMD_TU << 29

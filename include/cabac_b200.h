@@ -95,7 +95,8 @@ typedef struct cabac_substream_params {
  *   EP    : bits 28..24 = n (0..24), 23..0 = bins encodeBinsEP / decodeBinsEP
  *           (encodeBinEP(b) == EP with n = 1; longer runs are split by the
  *            recorder, which is arithmetically identical)
- *   REM   : bits 28..24 = rice, 23..0 = value     encodeRemAbsEP(v, rice, 5, 15)
+ *   REM   : bits 28..24 = rice (0..12), 23..0 = value
+ *                                                 encodeRemAbsEP(v, rice, 5, 15)
  *   TRM   : bit 0 = bin                           encodeBinTrm / decodeBinTrm
  *   ALIGN :                                       align()  (m_Range = 256)
  */
@@ -104,7 +105,9 @@ enum {
   CABAC_CMD_EP = 1,
   CABAC_CMD_REM = 2,
   CABAC_CMD_TRM = 3,
-  CABAC_CMD_ALIGN = 4
+  CABAC_CMD_ALIGN = 4,
+  CABAC_CMD_TU = 5 /* cabac_encode_stream only: residual_coding() of the
+                      substream's next TU descriptor                        */
 };
 #define CABAC_CMD_KIND(w) ((uint32_t)(w) >> 29)
 #define CABAC_MK_CTX(ctx, bin) \
@@ -115,6 +118,7 @@ enum {
   (((uint32_t)CABAC_CMD_REM << 29) | (((uint32_t)(rice) & 31u) << 24) | ((uint32_t)(value) & 0xFFFFFFu))
 #define CABAC_MK_TRM(bin) (((uint32_t)CABAC_CMD_TRM << 29) | ((uint32_t)(bin) & 1u))
 #define CABAC_MK_ALIGN() ((uint32_t)CABAC_CMD_ALIGN << 29)
+#define CABAC_MK_TU() ((uint32_t)CABAC_CMD_TU << 29)
 
 /* ---- flat transform-unit descriptor (residual level) --------------------- */
 /* Replaces the (TransformUnit&, ComponentID) argument pair of
@@ -261,6 +265,35 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus,
                               const uint64_t *out_offsets, uint32_t *out_sizes,
                               uint32_t *num_bins, uint8_t *tu_flags,
                               cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* ---- (1)+(3) recorded command streams ------------------------------------- */
+/* The full CABACWriter seam: a substream is the recorded sequence of BinEncIf
+ * calls its syntax writer made (command words as above, raw context ids) with
+ * a CABAC_CMD_TU marker wherever the writer called residual_coding(); marker k
+ * of substream i codes TU tus[tu_offsets[i] + k].  This is how coding_tree /
+ * coding_unit / cbf / intra-mode bins recorded on the host interleave with
+ * device-side residual binarisation.  Arguments as in
+ * cabac_encode_bins + cabac_encode_residual; tus / tu_offsets / coeffs may be
+ * NULL when no substream contains a marker.                                  */
+int cabac_encode_stream(cabac_handle *h, const uint32_t *cmds,
+                        const uint64_t *cmd_offsets, const cabac_tu_desc *tus,
+                        const uint64_t *tu_offsets,
+                        const cabac_substream_params *params, size_t n_sub,
+                        const int32_t *coeffs, size_t n_coeffs,
+                        const cabac_ctx_model *ctx_in, uint8_t *out,
+                        const uint64_t *out_offsets, uint32_t *out_sizes,
+                        uint32_t *num_bins, uint8_t *tu_flags,
+                        cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds,
+                            const uint64_t *cmd_offsets,
+                            const cabac_tu_desc *tus,
+                            const uint64_t *tu_offsets,
+                            const cabac_substream_params *params, size_t n_sub,
+                            const int32_t *coeffs,
+                            const cabac_ctx_model *ctx_in, uint8_t *out,
+                            const uint64_t *out_offsets, uint32_t *out_sizes,
+                            uint32_t *num_bins, uint8_t *tu_flags,
+                            cabac_ctx_model *ctx_out, uint32_t *status);
 
 /* Host-pointer encode that returns what the slice writer consumes
  * (EncSlice.cpp:2114-2125, EncGOP.cpp:3811-3824): the substreams compacted in

@@ -1383,6 +1383,37 @@ long orc_encode_residual(const cabac_tu_desc *tus, long ntu, const cabac_substre
   return enc_end(&e, p, &ct, numBins, ctxOut);
 }
 
+/* Recorded command stream with CABAC_CMD_TU markers (cabac_encode_stream): the BinEncIf calls of a
+ * CABACWriter interleaved with its residual_coding() calls, on one coder object. */
+long orc_encode_stream(const uint32_t *cmds, long ncmd, const cabac_tu_desc *tus, long ntu,
+                       const cabac_substream_params *p, const int32_t *coeffs, const cabac_ctx_model *ctxIn,
+                       uint8_t *out, long cap, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut) {
+  CtxTab ct;
+  Enc e;
+  long t = 0;
+  ctx_begin(&ct, p, ctxIn);
+  enc_start(&e, out, cap);
+  for (long i = 0; i < ncmd; i++) {
+    const uint32_t w = cmds[i];
+    switch (CABAC_CMD_KIND(w)) {
+      case CABAC_CMD_CTX: enc_bin(&e, &ct, (w >> 9) & 1, w & 511); break;
+      case CABAC_CMD_EP: enc_bins_ep(&e, w & 0xFFFFFF, (w >> 24) & 31); break;
+      case CABAC_CMD_REM: enc_rem_abs(&e, w & 0xFFFFFF, (w >> 24) & 31, 5, 15); break;
+      case CABAC_CMD_TRM: enc_trm(&e, w & 1); break;
+      case CABAC_CMD_ALIGN: e.range = 256; break;
+      case CABAC_CMD_TU: {
+        if (t >= ntu) return -1;
+        const unsigned st = w_residual_coding(&e, &ct, &tus[t], coeffs, p->flags, tuFlags ? &tuFlags[t] : NULL);
+        if (st) return -(long)st;
+        t++;
+        break;
+      }
+      default: return -1;
+    }
+  }
+  return enc_end(&e, p, &ct, numBins, ctxOut);
+}
+
 long orc_decode_residual(const uint8_t *in, long nbytes, const cabac_tu_desc *tus, long ntu,
                          const cabac_substream_params *p, const cabac_ctx_model *ctxIn, int32_t *coeffs,
                          uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status, int useMTS) {

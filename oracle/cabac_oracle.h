@@ -25,6 +25,9 @@ long orc_decode_bins(const uint8_t *in, long nbytes, const uint32_t *cmds, long 
 long orc_encode_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
                          const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint8_t *out, long cap,
                          uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut, int useMTS);
+long orc_encode_stream(const uint32_t *cmds, long ncmd, const cabac_tu_desc *tus, long ntu,
+                       const cabac_substream_params *p, const int32_t *coeffs, const cabac_ctx_model *ctxIn,
+                       uint8_t *out, long cap, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut);
 long orc_decode_residual(const uint8_t *in, long nbytes, const cabac_tu_desc *tus, long ntu,
                          const cabac_substream_params *p, const cabac_ctx_model *ctxIn, int32_t *coeffs,
                          uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status, int useMTS);

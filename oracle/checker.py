@@ -34,7 +34,7 @@ assert PARAMS_DT.itemsize == 4 and TU_DT.itemsize == 16 and CTX_DT.itemsize == 4
 SUB_DEP_QUANT, SUB_SIGN_HIDING, SUB_TSRC_DISABLED = 1, 2, 4
 SUB_TERMINATE, SUB_ALIGN, SUB_CTX_IN = 8, 16, 32
 TU_TS, TU_TS_ALLOWED, TU_BDPCM, TU_SBT_ZEROOUT = 1, 2, 4, 8
-CMD_CTX, CMD_EP, CMD_REM, CMD_TRM, CMD_ALIGN = 0, 1, 2, 3, 4
+CMD_CTX, CMD_EP, CMD_REM, CMD_TRM, CMD_ALIGN, CMD_TU = 0, 1, 2, 3, 4, 5
 
 
 def mk_ctx(ctx, b):
@@ -55,6 +55,10 @@ def mk_trm(b):
 
 def mk_align():
     return CMD_ALIGN << 29
+
+
+def mk_tu():
+    return CMD_TU << 29
 
 
 def _ptr(a):
@@ -88,7 +92,7 @@ class Checker:
                 self.lib = C.CDLL(path)
             finally:
                 os.chdir(cwd)
-        for name in ("encode_bins", "decode_bins", "encode_residual", "decode_residual"):
+        for name in ("encode_bins", "decode_bins", "encode_residual", "decode_residual", "encode_stream"):
             getattr(self.lib, self.pfx + name).restype = C.c_long
         for name in ("time_encode_residual", "time_decode_residual"):
             getattr(self.lib, self.pfx + name).restype = C.c_double
@@ -162,6 +166,25 @@ class Checker:
         n = self._f("encode_residual")(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in),
                                        _ptr(out), C.c_long(cap), _ptr(nb), _ptr(tuf), _ptr(ctx_out),
                                        C.c_int(int(use_mts)))
+        assert 0 <= n <= cap, n
+        res = (out[:n].copy(), int(nb[0]), tuf)
+        return res + (ctx_out,) if want_ctx else res
+
+    def encode_stream(self, cmds, tus, coeffs, qp, init_id, flags, ctx_in=None, want_ctx=False, cap=None):
+        """Recorded commands with CMD_TU markers (marker k codes tus[k])."""
+        cmds = np.ascontiguousarray(cmds, np.uint32)
+        tus = np.ascontiguousarray(tus, TU_DT)
+        coeffs = np.ascontiguousarray(coeffs, np.int32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        cap = cap or (coeffs.size * 5 + 64 * len(tus) + 5 * len(cmds) + 64)
+        out = np.zeros(cap, np.uint8)
+        nb = np.zeros(1, np.uint32)
+        tuf = np.zeros(len(tus), np.uint8)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        n = self._f("encode_stream")(_ptr(cmds), C.c_long(len(cmds)), _ptr(tus), C.c_long(len(tus)), _ptr(p),
+                                     _ptr(coeffs), _ptr(ctx_in), _ptr(out), C.c_long(cap), _ptr(nb), _ptr(tuf),
+                                     _ptr(ctx_out))
         assert 0 <= n <= cap, n
         res = (out[:n].copy(), int(nb[0]), tuf)
         return res + (ctx_out,) if want_ctx else res

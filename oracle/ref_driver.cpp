@@ -346,6 +346,54 @@ long ref_encode_residual(const cabac_tu_desc *tus, long ntu,
   return copyOut(bs, out, cap);
 }
 
+// Recorded command stream with CABAC_CMD_TU markers: BinEncIf calls and
+// CABACWriter::residual_coding calls interleaved on one coder, as the
+// reference's slice writer issues them.
+long ref_encode_stream(const uint32_t *cmds, long ncmd, const cabac_tu_desc *tus,
+                       long ntu, const cabac_substream_params *p,
+                       const int32_t *coeffs, const cabac_ctx_model *ctxIn,
+                       uint8_t *out, long cap, uint32_t *numBins,
+                       uint8_t *tuFlags, cabac_ctx_model *ctxOut) {
+  Harness hs(*p, false);
+  BinEncoder_Std enc;
+  CABACWriter wr(enc);
+  OutputBitstream bs;
+  wr.initBitstream(&bs);
+  enc.reset(p->qp, p->init_id);
+  enc.riceStatReset(10);
+  if ((p->flags & CABAC_SUB_CTX_IN) && ctxIn) importCtx(enc, ctxIn);
+  long t = 0;
+  for (long i = 0; i < ncmd; i++) {
+    const uint32_t w = cmds[i];
+    switch (CABAC_CMD_KIND(w)) {
+      case CABAC_CMD_CTX: enc.encodeBin((w >> 9) & 1, w & 511); break;
+      case CABAC_CMD_EP: enc.encodeBinsEP(w & 0xFFFFFF, (w >> 24) & 31); break;
+      case CABAC_CMD_REM:
+        enc.encodeRemAbsEP(w & 0xFFFFFF, (w >> 24) & 31, 5, 15);
+        break;
+      case CABAC_CMD_TRM: enc.encodeBinTrm(w & 1); break;
+      case CABAC_CMD_ALIGN: enc.align(); break;
+      case CABAC_CMD_TU: {
+        if (t >= ntu) return -1;
+        TuPair tp;
+        makeTu(tp, hs, tus[t], const_cast<TCoeff *>(coeffs));
+        applyTsAllowed(tp, tus[t], false);
+        CUCtx cuCtx(p->qp);
+        wr.residual_coding(tp.tu, ComponentID(tus[t].comp_id), &cuCtx);
+        if (tuFlags) tuFlags[t] = tuResultFlags(cuCtx, tp.tu, tus[t].comp_id);
+        t++;
+        break;
+      }
+      default: return -1;
+    }
+  }
+  if (p->flags & CABAC_SUB_TERMINATE) wr.end_of_slice();
+  if (p->flags & CABAC_SUB_ALIGN) bs.writeByteAlignment();
+  if (numBins) *numBins = enc.getNumBins();
+  if (ctxOut) exportCtx(enc, ctxOut);
+  return copyOut(bs, out, cap);
+}
+
 long ref_decode_residual(const uint8_t *in, long nbytes,
                          const cabac_tu_desc *tus, long ntu,
                          const cabac_substream_params *p,

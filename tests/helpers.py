@@ -28,6 +28,28 @@ def random_cmds(rng, n, with_align=False):
     return np.asarray(cmds, np.uint32)
 
 
+def mixed_stream(rng, n_tu, raw_per_gap=(0, 40)):
+    """Recorded commands (non-residual ctx ids 0..85, EP, REM, trm(0)) with one TU marker per TU."""
+    from entropy_coding_b200.types import mk_tu
+    cmds = []
+    for _ in range(n_tu):
+        for _ in range(int(rng.integers(raw_per_gap[0], raw_per_gap[1] + 1))):
+            k = rng.random()
+            if k < 0.7:
+                cmds.append(mk_ctx(int(rng.integers(0, 86)), int(rng.random() < 0.3)))
+            elif k < 0.85:
+                nb = int(rng.integers(1, 25))
+                cmds.append(mk_ep(int(rng.integers(0, 1 << nb)), nb))
+            elif k < 0.95:
+                cmds.append(mk_rem(int(rng.integers(0, 3000)), int(rng.integers(0, 4))))
+            else:
+                cmds.append(mk_trm(0))
+        cmds.append(mk_tu())
+    for _ in range(int(rng.integers(0, 6))):
+        cmds.append(mk_ctx(int(rng.integers(292, 357)), int(rng.integers(2))))
+    return np.asarray(cmds, np.uint32)
+
+
 def expected_values(cmds):
     """What decoding a stream must return for every command (no ALIGN inside)."""
     cmds = np.asarray(cmds, np.uint32)

@@ -9,7 +9,7 @@ from entropy_coding_b200 import workload as W
 from entropy_coding_b200.types import (CTX_DT, PARAMS_DT, SS_EMPTY_TU, SS_OUT_OVERFLOW, SUB_ALIGN, SUB_CTX_IN,
                                        SUB_DEP_QUANT, SUB_SIGN_HIDING, SUB_TERMINATE, SUB_TSRC_DISABLED, TU_DT,
                                        mk_ctx, mk_ep, mk_trm)
-from helpers import T, ctx_pairs, expected_values, random_cmds, sub_range
+from helpers import T, ctx_pairs, expected_values, mixed_stream, random_cmds, sub_range
 
 pytestmark = pytest.mark.gpu
 
@@ -246,6 +246,33 @@ def test_residual_encoder_variants(engine, oracle, mode, seed, flags, kw):
             assert r2["out"][int(small[i]):int(small[i]) + k].tobytes() == outs[i][:k].tobytes()
     finally:
         engine.set_encoder_mode(0)
+
+
+@pytest.mark.parametrize("seed,flags", [(401, T | SUB_DEP_QUANT), (402, T | SUB_SIGN_HIDING), (403, SUB_DEP_QUANT)])
+def test_stream_mixed_vs_oracle(engine, oracle, seed, flags):
+    """cabac_encode_stream: recorded BinEncIf calls interleaved with residual_coding() markers."""
+    rng = np.random.default_rng(seed)
+    wl = W.random_substreams(48, seed, flags=flags, tus_per_sub=(0, 9), ts_fraction=0.2)
+    streams = [mixed_stream(rng, int(wl.tu_offsets[i + 1] - wl.tu_offsets[i])) for i in range(wl.n_sub)]
+    coff = offsets_of([len(c) for c in streams])
+    cap = offsets_of([5 * len(c) + 64 for c in streams], align=16) + wl.out_capacity(bytes_per_coeff=5.0)
+    r = engine.encode_stream(np.concatenate(streams), coff, wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap,
+                             want_ctx=True)
+    outs = split(r["out"], cap, r["sizes"])
+    assert not r["status"].any()
+    for i in range(wl.n_sub):
+        a, b = int(wl.tu_offsets[i]), int(wl.tu_offsets[i + 1])
+        p = wl.params[i]
+        eb, nb, tuf, ectx = oracle.encode_stream(streams[i], wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]),
+                                                 int(p["flags"]), want_ctx=True)
+        assert outs[i].tobytes() == eb.tobytes(), (seed, i)
+        assert int(r["num_bins"][i]) == nb and (r["tu_flags"][a:b] == tuf).all()
+        assert (r["ctx_out"][i] == ectx).all()
+    # a marker without a TU left is a malformed stream
+    bad = engine.encode_stream(np.asarray([W.types.mk_tu()] if hasattr(W, "types") else [5 << 29], np.uint32),
+                               offsets_of([1]), np.zeros(0, TU_DT), np.zeros(2, np.uint64), wl.params[:1],
+                               np.zeros(1, np.int32), offsets_of([64]), raise_on_status=False)
+    assert int(bad["status"][0]) & 4
 
 
 def test_residual_all_shapes_single_coeff(engine, oracle):

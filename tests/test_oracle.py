@@ -169,3 +169,19 @@ def test_oracle_edge_cases(oracle):
     out, nb, tuf = oracle.encode_residual(tus, coeffs, 0, 2, T | SUB_DEP_QUANT)
     dec, bits, tuf2, st = oracle.decode_residual(out, tus, 16, 0, 2, T | SUB_DEP_QUANT)
     assert st == 0 and (dec == coeffs).all()
+
+
+def test_stream_oracle_vs_reference(oracle, ref):
+    """Mixed command streams (BinEncIf calls + residual_coding markers): restatement == compiled reference."""
+    from entropy_coding_b200 import workload as W
+    from helpers import mixed_stream
+    rng = np.random.default_rng(77)
+    wl = W.random_substreams(24, 77, tus_per_sub=(0, 7), ts_fraction=0.2)
+    for i in range(wl.n_sub):
+        a, b = int(wl.tu_offsets[i]), int(wl.tu_offsets[i + 1])
+        cmds = mixed_stream(rng, b - a)
+        p = wl.params[i]
+        args = (cmds, wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
+        ro, rr = oracle.encode_stream(*args, want_ctx=True), ref.encode_stream(*args, want_ctx=True)
+        assert ro[0].tobytes() == rr[0].tobytes() and ro[1] == rr[1]
+        assert (ro[2] == rr[2]).all() and (ro[3] == rr[3]).all()
