@@ -148,52 +148,6 @@ __global__ void ctx_init_kernel(const cabac_substream_params *__restrict__ param
   }
 }
 
-// Loads the warp's models: full table (379) or the residual subset (230).
-template <bool kResidualOnly>
-__device__ inline void loadCtx(uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                               size_t sub, int lane) {
-  const int qp = clipQp(p.qp);
-  constexpr int N = kResidualOnly ? RCTX : CABAC_NUM_CTX;
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
-  for (int k = lane; k < N; k += 32) {
-    const int id = kResidualOnly ? rctx_inv(k) : k;
-    const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
-    uint32_t w;
-    if (imp) {
-      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
-      w = model_pack(m.state0, m.state1, win);
-    } else {
-      w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
-    }
-    ctx[k] = w;
-  }
-  __syncwarp();
-}
-
-template <bool kResidualOnly>
-__device__ inline void storeCtx(const uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                cabac_ctx_model *ctxOut, size_t sub, int lane) {
-  if (!ctxOut) return;
-  __syncwarp();
-  const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
-  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
-    cabac_ctx_model m;
-    if (!kResidualOnly || is_residual_ctx(id)) {
-      const uint32_t w = ctx[kResidualOnly ? rctx(id) : id];
-      m.state0 = uint16_t(model_state0(w));
-      m.state1 = uint16_t(model_state1(w));
-    } else if (imp) {
-      m = ctxIn[sub * CABAC_NUM_CTX + id];
-    } else {
-      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
-      m.state0 = uint16_t(model_state0(w));
-      m.state1 = uint16_t(model_state1(w));
-    }
-    ctxOut[sub * CABAC_NUM_CTX + id] = m;
-  }
-}
-
 // Residual contexts as 16-byte entries (see cabac_lockstep.cuh).
 __device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
                                       size_t sub, int lane) {
@@ -263,62 +217,15 @@ __device__ inline void storeCtxEntriesFull(const uint4 *ctx, cabac_ctx_model *ct
 }
 
 // ---------------------------------------------------------------------------
-// K2: bin-level encoder (recorded BinEncIf calls -> bytes)
+// K2: bin-level encoding is cabac_encode_stream without TU markers (stage P in stream mode +
+//     stage D, below).
+// K3: bin-level decoder with a known call skeleton (test vehicle: the context of every bin is
+//     given by the command words).  Lockstep: every lane runs the same decoder.
 // ---------------------------------------------------------------------------
-struct __align__(16) BinsWarpSmem {
-  uint8_t ring[STAGE_BYTES];
-  uint32_t ctx[CABAC_NUM_CTX + 5];  // 384 words
-  uint32_t queue[32];
+struct __align__(16) BinsDecWarpSmem {
+  uint4 ctx[CABAC_NUM_CTX];
 };
 
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
-encode_bins_kernel(const uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
-                   const cabac_substream_params *__restrict__ params, size_t nSub,
-                   const cabac_ctx_model *__restrict__ ctxIn, uint8_t *__restrict__ out,
-                   const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
-                   uint32_t *__restrict__ numBins, cabac_ctx_model *__restrict__ ctxOut,
-                   uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
-  __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  BinsWarpSmem &sm = smem[wib];
-  size_t sub;
-  while (nextSubstream(order, cursor, nSub, lane, sub)) {
-    const cabac_substream_params p = params[sub];
-    loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
-    Encoder enc;
-    enc.start();
-    enc.out.ring = sm.ring;
-    enc.out.dst = out + outOffsets[sub];
-    enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
-    enc.out.n = 0;
-    enc.out.flushed = 0;
-    uint32_t st = 0;
-    const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
-    for (uint64_t c = c0; c < c1; c += 32) {
-      const int n = (c1 - c) < 32 ? int(c1 - c) : 32;
-      if (lane < n) sm.queue[lane] = cmds[c + lane];
-      __syncwarp();
-      if (lane == 0) st |= drainQueue(enc, sm.ctx, sm.queue, n);
-      __syncwarp();
-      if (__shfl_sync(FULL, enc.out.n - enc.out.flushed, 0) >= uint32_t(STAGE_BYTES / 2))
-        stage_flush(enc.out, lane, false);
-    }
-    if (lane == 0) enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
-    stage_flush(enc.out, lane, true);
-    if (lane == 0) {
-      if (enc.out.n > enc.out.cap) st |= CABAC_SS_OUT_OVERFLOW;
-      outSizes[sub] = enc.out.n;
-      if (numBins) numBins[sub] = enc.nbins;
-      if (status) status[sub] = st;
-    }
-    storeCtx<false>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
-    __syncwarp();
-  }
-}
-
-// ---------------------------------------------------------------------------
-// K3: bin-level decoder with a known call skeleton
-// ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
                    const uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
@@ -326,46 +233,41 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
                    const cabac_ctx_model *__restrict__ ctxIn, uint32_t *__restrict__ values,
                    uint32_t *__restrict__ bitsRead, cabac_ctx_model *__restrict__ ctxOut,
                    uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
-  __shared__ BinsWarpSmem smem[WARPS_PER_BLOCK];
+  __shared__ BinsDecWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  BinsWarpSmem &sm = smem[wib];
+  BinsDecWarpSmem &sm = smem[wib];
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtx<false>(sm.ctx, p, ctxIn, sub, lane);
-    Decoder dec;
+    loadCtxEntriesFull(sm.ctx, p, ctxIn, sub, lane);
+    LsDecoder dec;
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
     const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
-    for (uint64_t c = c0; c < c1; c += 32) {
-      const int n = (c1 - c) < 32 ? int(c1 - c) : 32;
-      if (lane < n) sm.queue[lane] = cmds[c + lane];
-      __syncwarp();
-      if (lane == 0) {
-        for (int i = 0; i < n; i++) {
-          const uint32_t w = sm.queue[i];
-          uint32_t v = 0;
-          switch (CABAC_CMD_KIND(w)) {
-            case CABAC_CMD_CTX: v = dec.decodeBin(sm.ctx + (w & 511u)); break;
-            case CABAC_CMD_EP: v = dec.decodeBinsEP((w >> 24) & 31u); break;
-            case CABAC_CMD_REM: v = dec.decodeRemAbsEP((w >> 24) & 31u); break;
-            case CABAC_CMD_TRM: v = dec.decodeBinTrm(); break;
-            case CABAC_CMD_ALIGN: dec.range = 256; break;
-            default: dec.status |= CABAC_SS_BAD_CMD; break;
-          }
-          sm.queue[i] = v;
-        }
+#pragma unroll 1
+    for (uint64_t c = c0; c < c1; c++) {
+      const uint32_t w = cmds[c];
+      uint32_t v = 0;
+      switch (CABAC_CMD_KIND(w)) {
+        case CABAC_CMD_CTX:
+          if ((w & 511u) < CABAC_NUM_CTX) v = dec.decodeBin(sm.ctx + (w & 511u));
+          else dec.status |= CABAC_SS_BAD_CMD;
+          break;
+        case CABAC_CMD_EP: v = dec.epLong((w >> 24) & 31u); break;
+        case CABAC_CMD_REM: v = dec.remAbs((w >> 24) & 31u); break;
+        case CABAC_CMD_TRM: v = dec.decodeBinTrm(); break;
+        case CABAC_CMD_ALIGN: dec.range = 256; break;
+        default: dec.status |= CABAC_SS_BAD_CMD; break;
       }
-      __syncwarp();
-      if (values && lane < n) values[c + lane] = sm.queue[lane];
-      __syncwarp();
+      if (values && lane == 0) values[c] = v;
     }
+    if (p.flags & CABAC_SUB_TERMINATE)
+      if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
+    dec.checkOverrun();
     if (lane == 0) {
-      if (p.flags & CABAC_SUB_TERMINATE)
-        if (!dec.decodeBinTrm()) dec.status |= CABAC_SS_NO_TERMINATE;
       if (bitsRead) bitsRead[sub] = dec.bitsRead();
       if (status) status[sub] = dec.status;
     }
-    storeCtx<false>(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    storeCtxEntriesFull(sm.ctx, ctxOut, sub, lane);
     __syncwarp();
   }
 }
@@ -1315,19 +1217,6 @@ cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_para
   const size_t wantBlocks = (total + 255) / 256;
   const int blocks = int(wantBlocks < size_t(148 * 16) ? wantBlocks : size_t(148 * 16));
   ctx_init_kernel<<<blocks, 256, 0, s>>>(params, n, out);
-  return cudaGetLastError();
-}
-
-cudaError_t launchEncodeBins(cudaStream_t s, int device, const Sched &sc, const uint32_t *cmds,
-                             const uint64_t *cmdOffsets, const cabac_substream_params *params, size_t nSub,
-                             const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
-                             uint32_t *outSizes, uint32_t *numBins, cabac_ctx_model *ctxOut, uint32_t *status) {
-  if (nSub == 0) return cudaSuccess;
-  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cmdOffsets, nSub, sc.cost);  // commands per substream
-  cudaError_t e = launchOrder(s, sc, nSub);
-  if (e != cudaSuccess) return e;
-  encode_bins_kernel<<<persistentGrid(encode_bins_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      cmds, cmdOffsets, params, nSub, ctxIn, out, outOffsets, outSizes, numBins, ctxOut, status, sc.order, sc.cursor);
   return cudaGetLastError();
 }
 

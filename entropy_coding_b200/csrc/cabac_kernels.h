@@ -27,10 +27,6 @@ const unsigned char *hostInitTable(int row);
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
                           cabac_ctx_model *out);
-cudaError_t launchEncodeBins(cudaStream_t s, int device, const Sched &sc, const uint32_t *cmds, const uint64_t *cmdOffsets,
-                             const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
-                             uint8_t *out, const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins,
-                             cabac_ctx_model *ctxOut, uint32_t *status);
 cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
                              const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,

@@ -21,75 +21,47 @@ namespace cabac {
 
 // Output staging, uniform on all lanes: bytes go to a shared-memory ring and leave
 // for HBM as coalesced 16-byte stores.
-struct LsOut {  // (kept for the single-kernel lockstep variant)
+// All arguments by value and out of line: one copy of the flush code in the kernel, and the
+// encoder state never has its address taken (it stays in registers).  Returns the new `flushed`.
+__device__ __noinline__ uint32_t lsFlushRing(const uint8_t *ring, uint8_t *dst, uint32_t cap, uint32_t n,
+                                             uint32_t flushed, int lane, bool final) {
+  const uint32_t lim = n & ~15u;
+  __syncwarp();
+  if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+    for (uint32_t b = flushed + 16u * lane; b < lim; b += 512u) {
+      if (b + 16u <= cap) {
+        *reinterpret_cast<uint4 *>(dst + b) = *reinterpret_cast<const uint4 *>(ring + (b & (STAGE_BYTES - 1)));
+      } else {
+        for (uint32_t k = b; k < b + 16u && k < cap; k++) dst[k] = ring[k & (STAGE_BYTES - 1)];
+      }
+    }
+  } else {
+    for (uint32_t b = flushed + lane; b < lim; b += 32u)
+      if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
+  }
+  uint32_t done = lim;
+  if (final) {
+    for (uint32_t b = lim + lane; b < n; b += 32u)
+      if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
+    done = n;
+  }
+  __syncwarp();
+  return done;
+}
+
+struct LsOut {  // output staging of the fused lockstep encoder, uniform on all lanes
   uint8_t *ring;  // shared, STAGE_BYTES, 16-byte aligned
   uint8_t *dst;   // this substream's slab
   uint32_t cap, n, flushed;
   int lane;
 
-  __device__ __forceinline__ void flush(bool final) {
-    const uint32_t lim = n & ~15u;
-    __syncwarp();
-    if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
-      for (uint32_t b = flushed + 16u * lane; b < lim; b += 512u) {
-        if (b + 16u <= cap) {
-          *reinterpret_cast<uint4 *>(dst + b) = *reinterpret_cast<const uint4 *>(ring + (b & (STAGE_BYTES - 1)));
-        } else {
-          for (uint32_t k = b; k < b + 16u && k < cap; k++) dst[k] = ring[k & (STAGE_BYTES - 1)];
-        }
-      }
-    } else {
-      for (uint32_t b = flushed + lane; b < lim; b += 32u)
-        if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
-    }
-    flushed = lim;
-    if (final) {
-      for (uint32_t b = lim + lane; b < n; b += 32u)
-        if (b < cap) dst[b] = ring[b & (STAGE_BYTES - 1)];
-      flushed = n;
-    }
-    __syncwarp();
-  }
+  __device__ __forceinline__ void flush(bool final) { flushed = lsFlushRing(ring, dst, cap, n, flushed, lane, final); }
   __device__ __forceinline__ void put(uint32_t byte) {
     if (n - flushed >= uint32_t(STAGE_BYTES)) flush(false);  // long outstanding-0xFF run released at once
     ring[n & (STAGE_BYTES - 1)] = uint8_t(byte);
     n++;
   }
 };
-
-// Stage D output: one byte stream per LANE, assembled in a register and stored as aligned words.
-struct LaneOut {
-  uint8_t *dst;
-  uint32_t cap, n, acc;
-  bool aligned;
-  __device__ __forceinline__ void init(uint8_t *p, uint32_t c) {
-    dst = p;
-    cap = c;
-    n = 0;
-    acc = 0;
-    aligned = (reinterpret_cast<uintptr_t>(p) & 3u) == 0;
-  }
-  __device__ __forceinline__ void put(uint32_t byte) {
-    acc = (acc >> 8) | (byte << 24);
-    n++;
-    if (aligned) {
-      if ((n & 3u) == 0 && n <= cap) *reinterpret_cast<uint32_t *>(dst + n - 4) = acc;
-    } else if (n <= cap) {
-      dst[n - 1] = uint8_t(byte);
-    }
-  }
-  __device__ __forceinline__ void finish() {  // the bytes still in `acc`
-    if (!aligned) return;
-    const uint32_t rem = n & 3u;
-    const uint32_t v = acc >> (8u * (4u - rem));
-    for (uint32_t k = 0; k < rem; k++)
-      if (n - rem + k < cap) dst[n - rem + k] = uint8_t(v >> (8u * k));
-    // a word that crossed `cap` was not stored: write its in-range head byte-wise
-    if (rem == 0 && n > cap && (n - 4) < cap)
-      for (uint32_t k = 0; n - 4 + k < cap; k++) dst[n - 4 + k] = uint8_t(acc >> (8u * k));
-  }
-};
-
 
 template <typename Out>
 struct ArithEncoder {
@@ -233,7 +205,6 @@ struct ArithEncoder {
 };
 
 typedef ArithEncoder<LsOut> LsEncoder;
-typedef ArithEncoder<LaneOut> LaneEncoder;
 
 // The single arithmetic-coder site: walks n command words (CTX / EP kinds).
 __device__ __forceinline__ void lsDrain(LsEncoder &enc, uint4 *ctx, const uint32_t *queue, int n) {
