@@ -1,0 +1,301 @@
+// tests/dropin/dropin_main.cpp - drop-in proof (TEST, built into oracle/_ref/dropin_test).
+//
+// The reference's OWN CABACWriter / CABACReader and data model (compiled unmodified from
+// /root/reference/src) run on top of the shims of entropy_coding_b200/host/:
+//   A  reference : CABACWriter(BinEncoder_Std)                         -> bytes_ref
+//   B1 bin seam  : CABACWriter(GpuBinEncoder), residual_coding on host -> recorded bins -> GPU
+//   B2 TU seam   : GpuBinEncoder::residual_coding markers              -> binarisation on GPU
+//   C  decode    : GpuResidualReader on bytes_ref -> coefficients, mtsIdx, CUCtx flags,
+//                  compared with CABACReader(BinDecoder_Std) on the same bytes
+// All of B1, B2 must equal A byte for byte (after the caller's writeByteAlignment), with equal
+// getNumBins() and final contexts; C must return what the reference's reader returns (= the
+// encoder's input wherever sign hiding is off).
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+
+#include "gpu_bin_encoder.hpp"
+#include "gpu_residual_reader.hpp"
+#include "ref_harness.hpp"
+
+using namespace ref_harness;
+using namespace cabac_b200;
+
+namespace {
+
+struct SubSpec {
+  cabac_substream_params p;
+  std::vector<cabac_tu_desc> tus;
+};
+
+int g_fail = 0;
+#define EXPECT(cond, ...)                       \
+  do {                                          \
+    if (!(cond)) {                              \
+      if (g_fail++ < 10) {                      \
+        fprintf(stderr, "MISMATCH: " __VA_ARGS__); \
+        fprintf(stderr, "\n");                  \
+      }                                         \
+    }                                           \
+  } while (0)
+
+void fillCoeffs(std::mt19937 &rng, int32_t *c, int w, int h, int density, bool ts) {
+  std::uniform_int_distribution<int> u(0, 999);
+  bool any = false;
+  for (int y = 0; y < h; y++)
+    for (int x = 0; x < w; x++) {
+      int v = 0;
+      const int thr = ts ? density * 8 : density * 40 / (1 + x + y);
+      if (u(rng) < thr) {
+        const int r = u(rng);
+        v = r < 600 ? 1 : (r < 850 ? 2 + u(rng) % 4 : (r < 990 ? 6 + u(rng) % 60 : 100 + u(rng) % 20000));
+        if (u(rng) & 1) v = -v;
+      }
+      if (x >= 32 || y >= 32) v = 0;  // VVC zeroes a 64-sized dimension beyond 32 (context_modelling.cpp:7-79)
+      c[y * w + x] = v;
+      any |= v != 0;
+    }
+  if (!any) c[0] = (u(rng) & 1) ? 1 : -3;
+}
+
+// non-residual syntax the slice writer interleaves: raw BinEncIf calls on arbitrary contexts
+void sideBins(BinEncIf &e, std::mt19937 &rng) {
+  std::uniform_int_distribution<int> u(0, 1 << 20);
+  const int n = u(rng) % 6;
+  for (int i = 0; i < n; i++) e.encodeBin(u(rng) & 1, u(rng) % Ctx::NumberOfContexts);
+  if (u(rng) % 3 == 0) e.encodeBinEP(u(rng) & 1);
+  if (u(rng) % 3 == 0) {
+    const unsigned nb = 1 + u(rng) % 32;
+    e.encodeBinsEP(nb == 32 ? unsigned(u(rng)) * 4099u : unsigned(u(rng)) & ((1u << nb) - 1), nb);
+  }
+  if (u(rng) % 4 == 0) e.encodeRemAbsEP(u(rng) % 3000, u(rng) % 4, 5, 15);
+  if (u(rng) % 9 == 0) e.encodeBinTrm(0);
+}
+
+std::vector<uint8_t> closeSubstream(OutputBitstream &bs) {
+  bs.writeByteAlignment();  // what EncSlice.cpp:2114 does after end_of_slice
+  return bs.getFIFO();
+}
+
+bool sameCtx(const Ctx &a, const Ctx &b) {
+  const auto &sa = static_cast<const CtxStore<BinProbModel_Std> &>(a);
+  const auto &sb = static_cast<const CtxStore<BinProbModel_Std> &>(b);
+  for (unsigned k = 0; k < Ctx::NumberOfContexts; k++)
+    if (sa[k].getState0() != sb[k].getState0() || sa[k].getState1() != sb[k].getState1()) return false;
+  return true;
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+  const int nSub = argc > 1 ? atoi(argv[1]) : 96;
+  const unsigned seed = argc > 2 ? unsigned(atoi(argv[2])) : 7u;
+  std::mt19937 rng(seed);
+  std::uniform_int_distribution<int> u(0, 1 << 20);
+
+  // ---- workload ----
+  std::vector<SubSpec> subs(nSub);
+  std::vector<int32_t> slab;
+  for (SubSpec &s : subs) {
+    const int qps[3] = {0, 32, 51};
+    s.p.qp = int8_t(qps[u(rng) % 3]);
+    s.p.init_id = uint8_t(u(rng) % 3);
+    s.p.flags = uint8_t((u(rng) & 1 ? CABAC_SUB_DEP_QUANT : 0));
+    if (!(s.p.flags & CABAC_SUB_DEP_QUANT) && (u(rng) & 1)) s.p.flags |= CABAC_SUB_SIGN_HIDING;
+    s.p.reserved = 0;
+    const int ntu = 1 + u(rng) % 12;
+    for (int t = 0; t < ntu; t++) {
+      cabac_tu_desc d{};
+      d.comp_id = uint8_t(u(rng) % 3);
+      d.log2_w = uint8_t(2 + u(rng) % (d.comp_id ? 4 : 5));
+      d.log2_h = uint8_t(2 + u(rng) % (d.comp_id ? 4 : 5));
+      const bool tsOk = d.log2_w <= 5 && d.log2_h <= 5;
+      const int r = u(rng) % 10;
+      d.flags = 0;
+      if (tsOk && r < 3) d.flags = CABAC_TU_TS_ALLOWED | (r < 2 ? CABAC_TU_TS : 0);
+      if (tsOk && r == 3) d.flags = CABAC_TU_BDPCM | CABAC_TU_TS;
+      d.coeff_offset = slab.size();
+      const int w = 1 << d.log2_w, h = 1 << d.log2_h;
+      slab.resize(slab.size() + size_t(w) * h);
+      fillCoeffs(rng, &slab[d.coeff_offset], w, h, 1 + u(rng) % 20, (d.flags & CABAC_TU_TS) != 0);
+      s.tus.push_back(d);
+    }
+  }
+
+  Engine eng(0);
+  GpuEncodeSession sessBins(eng), sessTu(eng);
+  std::vector<std::unique_ptr<GpuBinEncoder>> encB1, encB2;
+  std::vector<std::unique_ptr<OutputBitstream>> bsB1, bsB2;
+  std::vector<std::vector<uint8_t>> bytesRef(nSub);
+  std::vector<uint32_t> binsRef(nSub);
+  std::vector<std::unique_ptr<BinEncoder_Std>> encRef;
+  std::vector<std::vector<uint8_t>> flagsRef(nSub);
+
+  for (int i = 0; i < nSub; i++) {
+    const SubSpec &s = subs[i];
+    Harness hs(s.p, false);
+    const unsigned sideSeed = u(rng);
+    // three coders, same calls
+    encRef.emplace_back(new BinEncoder_Std());
+    encB1.emplace_back(new GpuBinEncoder(sessBins));
+    encB2.emplace_back(new GpuBinEncoder(sessTu));
+    bsB1.emplace_back(new OutputBitstream());
+    bsB2.emplace_back(new OutputBitstream());
+    OutputBitstream bsRef;
+    BinEncIf *coder[3] = {encRef.back().get(), encB1.back().get(), encB2.back().get()};
+    OutputBitstream *bs[3] = {&bsRef, bsB1.back().get(), bsB2.back().get()};
+    for (int v = 0; v < 3; v++) {
+      CABACWriter wr(*coder[v]);  // the reference's writer, unchanged (cabac_writer.hpp:16-18)
+      wr.initBitstream(bs[v]);
+      coder[v]->reset(s.p.qp, s.p.init_id);
+      if (v) static_cast<GpuBinEncoder *>(coder[v])->setSliceTools(s.p.flags & CABAC_SUB_DEP_QUANT,
+                                                                  s.p.flags & CABAC_SUB_SIGN_HIDING, false);
+      std::mt19937 sideRng(sideSeed);
+      for (size_t t = 0; t < s.tus.size(); t++) {
+        sideBins(*coder[v], sideRng);
+        TuPair tp;
+        makeTu(tp, hs, s.tus[t], slab.data());
+        applyTsAllowed(tp, s.tus[t], false);
+        CUCtx cuCtx(s.p.qp);
+        if (v == 2) {
+          static_cast<GpuBinEncoder *>(coder[v])->residual_coding(tp.tu, ComponentID(s.tus[t].comp_id), nullptr);
+        } else {
+          wr.residual_coding(tp.tu, ComponentID(s.tus[t].comp_id), &cuCtx);
+        }
+        if (v == 0) {
+          uint8_t f = 0;
+          if (tp.tu.mtsIdx[s.tus[t].comp_id] == MTS_SKIP) f |= CABAC_TUR_TS;
+          if (cuCtx.violatesLfnstConstrained[toChannelType(ComponentID(s.tus[t].comp_id))]) f |= CABAC_TUR_VIOLATES_LFNST;
+          if (cuCtx.lfnstLastScanPos) f |= CABAC_TUR_LFNST_LAST_POS;
+          if (cuCtx.mtsLastScanPos) f |= CABAC_TUR_MTS_LAST_POS;
+          if (cuCtx.violatesMtsCoeffConstraint) f |= CABAC_TUR_VIOLATES_MTS;
+          flagsRef[i].push_back(f);
+        }
+      }
+      wr.end_of_slice();  // encodeBinTrm(1) + finish(), cabac_writer.cpp:104-107
+    }
+    binsRef[i] = encRef.back()->getNumBins();
+    bytesRef[i] = closeSubstream(bsRef);
+  }
+  sessBins.flush();
+  sessTu.flush();
+
+  size_t totalBytes = 0, totalBins = 0;
+  for (int i = 0; i < nSub; i++) {
+    const std::vector<uint8_t> b1 = closeSubstream(*bsB1[i]), b2 = closeSubstream(*bsB2[i]);
+    EXPECT(b1 == bytesRef[i], "substream %d: bin-seam bytes differ (%zu vs %zu)", i, b1.size(), bytesRef[i].size());
+    EXPECT(b2 == bytesRef[i], "substream %d: TU-seam bytes differ (%zu vs %zu)", i, b2.size(), bytesRef[i].size());
+    if (b2 != bytesRef[i] && g_fail < 10) {
+      fprintf(stderr, "  qp %d init %d flags %u:", subs[i].p.qp, subs[i].p.init_id, subs[i].p.flags);
+      for (const cabac_tu_desc &d : subs[i].tus) fprintf(stderr, " [c%u %ux%u f%u]", d.comp_id, 1u << d.log2_w, 1u << d.log2_h, d.flags);
+      fprintf(stderr, "\n");
+    }
+    EXPECT(encB1[i]->getNumBins() == binsRef[i], "substream %d: bin-seam getNumBins %u vs %u", i, encB1[i]->getNumBins(), binsRef[i]);
+    EXPECT(encB2[i]->getNumBins() == binsRef[i], "substream %d: TU-seam getNumBins %u vs %u", i, encB2[i]->getNumBins(), binsRef[i]);
+    EXPECT(sameCtx(*encB1[i], *encRef[i]), "substream %d: bin-seam final contexts differ", i);
+    EXPECT(sameCtx(*encB2[i], *encRef[i]), "substream %d: TU-seam final contexts differ", i);
+    totalBytes += bytesRef[i].size();
+    totalBins += binsRef[i];
+  }
+
+  // ---- C: decode the reference's residual-only bitstreams through GpuResidualReader ----
+  {
+    GpuResidualReader rd(eng);
+    std::vector<std::unique_ptr<Harness>> hss;
+    std::vector<std::unique_ptr<TuPair>> tps;
+    std::vector<CUCtx> ctxs;
+    std::vector<int32_t> decoded(slab.size(), 0x5a5a5a5a), decodedRef(slab.size(), 0);
+    std::vector<std::vector<uint8_t>> resBytes(nSub);
+    size_t nTu = 0;
+    for (const SubSpec &s : subs) nTu += s.tus.size();
+    ctxs.reserve(nTu);
+    std::vector<uint8_t> wantFlags;
+    for (int i = 0; i < nSub; i++) {
+      const SubSpec &s = subs[i];
+      hss.emplace_back(new Harness(s.p, false));
+      BinEncoder_Std enc;
+      CABACWriter wr(enc);
+      OutputBitstream bs;
+      wr.initBitstream(&bs);
+      enc.reset(s.p.qp, s.p.init_id);
+      for (const cabac_tu_desc &d : s.tus) {
+        TuPair tp;
+        makeTu(tp, *hss.back(), d, slab.data());
+        applyTsAllowed(tp, d, false);
+        wr.residual_coding(tp.tu, ComponentID(d.comp_id), nullptr);
+      }
+      wr.end_of_slice();
+      resBytes[i] = closeSubstream(bs);
+      {  // what the reference's own reader returns (random levels ignore the sign-hiding parity rule,
+         // so with SBH the decoded signs legitimately differ from the encoder's input)
+        BinDecoder_Std dec;
+        CABACReader rr(dec);
+        InputBitstream ibs;
+        ibs.getFifo() = resBytes[i];
+        ibs.getFifo().resize(resBytes[i].size() + 8, 0);
+        rr.initBitstream(&ibs);
+        dec.reset(s.p.qp, s.p.init_id);
+        for (const cabac_tu_desc &d : s.tus) {
+          TuPair tp;
+          makeTu(tp, *hss.back(), d, decodedRef.data());
+          applyTsAllowed(tp, d, false);
+          if (d.flags & CABAC_TU_TS_ALLOWED) tp.tu.mtsIdx[d.comp_id] = MTS_DCT2_DCT2;
+          CUCtx cc(int(s.p.qp));
+          rr.residual_coding(tp.tu, ComponentID(d.comp_id), cc);
+        }
+        if (!(s.p.flags & CABAC_SUB_SIGN_HIDING))
+          for (const cabac_tu_desc &d : s.tus)
+            for (size_t k = 0; k < (size_t(1) << (d.log2_w + d.log2_h)); k++)
+              EXPECT(decodedRef[d.coeff_offset + k] == slab[d.coeff_offset + k], "reference decode != input (sub %d)", i);
+      }
+      rd.beginSubstream(resBytes[i].data(), resBytes[i].size(), s.p.qp, s.p.init_id, s.p.flags & CABAC_SUB_DEP_QUANT,
+                        s.p.flags & CABAC_SUB_SIGN_HIDING, false, true);
+      for (size_t t = 0; t < s.tus.size(); t++) {
+        const cabac_tu_desc &d = s.tus[t];
+        tps.emplace_back(new TuPair());
+        makeTu(*tps.back(), *hss.back(), d, decoded.data());
+        applyTsAllowed(*tps.back(), d, false);
+        // the parser must derive the flag itself when it is coded
+        if (d.flags & CABAC_TU_TS_ALLOWED) tps.back()->tu.mtsIdx[d.comp_id] = MTS_DCT2_DCT2;
+        ctxs.emplace_back(int(s.p.qp));
+        rd.residual_coding(tps.back()->tu, ComponentID(d.comp_id), &ctxs.back());
+        wantFlags.push_back(flagsRef[i][t]);
+      }
+    }
+    rd.flush();
+    EXPECT(decoded == decodedRef, "decoded coefficients differ from the reference reader's");
+    if (decoded != decodedRef) {
+      int shown = 0;
+      for (int i = 0; i < nSub && shown < 6; i++)
+        for (const cabac_tu_desc &d : subs[i].tus) {
+          const size_t n = size_t(1) << (d.log2_w + d.log2_h);
+          size_t bad = 0, first = 0;
+          for (size_t k = 0; k < n; k++)
+            if (decoded[d.coeff_offset + k] != decodedRef[d.coeff_offset + k] && !bad++) first = k;
+          if (bad && shown++ < 6)
+            fprintf(stderr, "  sub %d [c%u %ux%u f%u] %zu bad, first at %zu: got %d want %d\n", i, d.comp_id, 1u << d.log2_w,
+                    1u << d.log2_h, d.flags, bad, first, decoded[d.coeff_offset + first], decodedRef[d.coeff_offset + first]);
+        }
+    }
+    size_t k = 0;
+    for (int i = 0; i < nSub; i++)
+      for (size_t t = 0; t < subs[i].tus.size(); t++, k++) {
+        const int comp = subs[i].tus[t].comp_id;
+        uint8_t f = 0;
+        if (tps[k]->tu.mtsIdx[comp] == MTS_SKIP) f |= CABAC_TUR_TS;
+        if (ctxs[k].violatesLfnstConstrained[toChannelType(ComponentID(comp))]) f |= CABAC_TUR_VIOLATES_LFNST;
+        if (ctxs[k].lfnstLastScanPos) f |= CABAC_TUR_LFNST_LAST_POS;
+        if (ctxs[k].mtsLastScanPos) f |= CABAC_TUR_MTS_LAST_POS;
+        if (ctxs[k].violatesMtsCoeffConstraint) f |= CABAC_TUR_VIOLATES_MTS;
+        EXPECT(f == wantFlags[k], "substream %d TU %zu: decoder side flags %u vs %u", i, t, f, wantFlags[k]);
+      }
+  }
+
+  if (g_fail) {
+    fprintf(stderr, "DROPIN FAILED: %d mismatches\n", g_fail);
+    return 1;
+  }
+  printf("DROPIN OK substreams=%d bins=%zu bytes=%zu launches=%llu\n", nSub, totalBins, totalBytes,
+         (unsigned long long)cabac_launch_count(eng.get()));
+  return 0;
+}
