@@ -32,6 +32,17 @@ struct cabac_handle {
   size_t cmdCapWords = 0;
   uint64_t *pinnedTotal = nullptr;  // page-locked landing spot for the slab size read-back
   int encoderMode = CABAC_ENCODER_AUTO;
+  // chunked pipeline of the host-pointer residual entry points: PCIe copies of the coefficient
+  // slab overlap coding (one copy stream; one compute stream per chunk, so a chunk's long substreams never
+  // hold back the chunks behind it)
+  static constexpr int kMaxChunks = 16;
+  int pipeChunks = 8;
+  size_t pipeMinCoeffs = size_t(8) << 20, pipeMinSubstreams = 512;  // below: one copy, one launch
+  cudaStream_t copyStream = nullptr, compStream[kMaxChunks] = {};
+  cudaEvent_t evCopy[kMaxChunks] = {}, evDone[kMaxChunks] = {}, evJoin = nullptr;
+  bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
+  cudaEvent_t evT0 = nullptr;
+  uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
 };
 
 namespace {
@@ -131,6 +142,69 @@ cudaError_t ensureCmdSlab(cabac_handle *h, cabac::Sched &sc, size_t n_sub) {
   return cudaSuccess;
 }
 
+// Streams / events / pinned landing area of the chunked pipeline (created on first use).
+cudaError_t ensurePipe(cabac_handle *h) {
+  if (h->copyStream) return cudaSuccess;
+  cudaError_t e;
+  if ((e = cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking)) != cudaSuccess) return e;
+  for (int i = 0; i < cabac_handle::kMaxChunks; i++)
+    if ((e = cudaStreamCreateWithFlags(&h->compStream[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+  for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
+    const unsigned fl = h->trace ? cudaEventDefault : cudaEventDisableTiming;
+    if ((e = cudaEventCreateWithFlags(&h->evCopy[i], fl)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&h->evDone[i], fl)) != cudaSuccess) return e;
+  }
+  if (h->trace && (e = cudaEventCreate(&h->evT0)) != cudaSuccess) return e;
+  if ((e = cudaEventCreateWithFlags(&h->evJoin, h->trace ? cudaEventDefault : cudaEventDisableTiming)) != cudaSuccess) return e;
+  return cudaHostAlloc(&h->pinnedRanges, (3 * cabac_handle::kMaxChunks + 2) * sizeof(uint64_t), cudaHostAllocDefault);
+}
+
+void traceChunks(cabac_handle *h, const char *what, int K, bool copyFirst) {
+  if (!h->trace) return;
+  fprintf(stderr, "[cabac_b200 trace] %s: %d chunks, ms since pipeline start (%s):", what, K,
+          copyFirst ? "H2D done / coded" : "decoded");
+  for (int k = 0; k < K; k++) {
+    float a = 0, b = 0;
+    if (copyFirst) cudaEventElapsedTime(&a, h->evT0, h->evCopy[k]);
+    cudaEventElapsedTime(&b, h->evT0, h->evDone[k]);
+    if (copyFirst) fprintf(stderr, " %.1f/%.1f", a, b); else fprintf(stderr, " %.1f", b);
+  }
+  float j = 0;
+  cudaEventElapsedTime(&j, h->evT0, h->evJoin);
+  fprintf(stderr, " | joined %.1f\n", j);
+}
+
+// Splits n_sub substreams into <= want chunks of about equal TU count (tu_offsets is a host array).
+int planChunks(const uint64_t *tu_offsets, size_t n_sub, int want, uint32_t *start) {
+  const uint64_t nTu = tu_offsets[n_sub] - tu_offsets[0];
+  int k = 0;
+  start[0] = 0;
+  for (int c = 1; c < want; c++) {
+    const uint64_t target = tu_offsets[0] + nTu * uint64_t(c) / uint64_t(want);
+    size_t lo = start[k], hi = n_sub;  // first substream whose TUs begin at or after the target
+    while (lo < hi) {
+      const size_t mid = (lo + hi) / 2;
+      if (tu_offsets[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    if (lo > start[k] && lo < n_sub) start[++k] = uint32_t(lo);
+  }
+  start[++k] = uint32_t(n_sub);
+  return k;
+}
+
+cabac::Sched chunkSched(const cabac::Sched &base, size_t s0, int k) {
+  cabac::Sched c = base;
+  c.cost += s0;
+  c.order += s0;
+  c.capWords += s0;
+  c.cmdCounts += s0;
+  c.statusScratch += s0;
+  c.cmdOffsets += s0 + size_t(k);
+  c.cursor = base.cursor + k;
+  c.twoStage = false;
+  return c;
+}
+
 // From this many substreams on, stage D (32 substreams per warp) fills the machine.
 constexpr size_t kTwoStageMinSubstreams = 32768;
 
@@ -169,6 +243,13 @@ cabac_handle *cabac_create(int device) {
     return nullptr;
   }
   h->stream = h->ownStream;
+  if (const char *c = getenv("CABAC_B200_PIPE_CHUNKS")) {  // 1 disables the chunked copy/compute pipeline
+    const int v = atoi(c);
+    if (v >= 1 && v <= cabac_handle::kMaxChunks) h->pipeChunks = v;
+  }
+  if (const char *c = getenv("CABAC_B200_TRACE")) h->trace = atoi(c) != 0;
+  if (const char *c = getenv("CABAC_B200_PIPE_MIN_COEFFS")) h->pipeMinCoeffs = size_t(atoll(c));
+  if (const char *c = getenv("CABAC_B200_PIPE_MIN_SUBSTREAMS")) h->pipeMinSubstreams = size_t(atoll(c));
   if (const char *m = getenv("CABAC_B200_ENCODER")) {
     if (!strcmp(m, "fused")) h->encoderMode = CABAC_ENCODER_FUSED;
     if (!strcmp(m, "two_stage")) h->encoderMode = CABAC_ENCODER_TWO_STAGE;
@@ -184,6 +265,15 @@ void cabac_destroy(cabac_handle *h) {
   if (h->sched) cudaFree(h->sched);
   if (h->cmdBuf) cudaFree(h->cmdBuf);
   if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
+  if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
+  for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
+    if (h->evCopy[i]) cudaEventDestroy(h->evCopy[i]);
+    if (h->evDone[i]) cudaEventDestroy(h->evDone[i]);
+  }
+  if (h->evJoin) cudaEventDestroy(h->evJoin);
+  if (h->copyStream) cudaStreamDestroy(h->copyStream);
+  for (int i = 0; i < cabac_handle::kMaxChunks; i++)
+    if (h->compStream[i]) cudaStreamDestroy(h->compStream[i]);
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
 }
@@ -568,7 +658,8 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   const size_t nTu = tu_offsets[n_sub], outCap = out_offsets[n_sub];
   if (nTu && (!tus || !coeffs)) return badArg(h, "cabac_encode_residual_packed: tus/coeffs");
   cabac_tu_desc *dTus;
-  uint64_t *dTuOff, *dOutOff, *dEntry;
+  uint64_t *dTuOff, *dOutOff, *dEntry, *dRanges;
+  uint32_t *dChunkStart;
   cabac_substream_params *dP;
   int32_t *dCoeffs;
   cabac_ctx_model *dCin, *dCout;
@@ -579,6 +670,8 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   a.want((void **)&dTuOff, (n_sub + 1) * 8);
   a.want((void **)&dOutOff, (n_sub + 1) * 8);
   a.want((void **)&dEntry, (n_sub + 1) * 8);
+  a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
+  a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, n_sub * sizeof(*params));
   a.want((void **)&dCoeffs, n_coeffs * 4);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
@@ -594,11 +687,66 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
   H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
   H2D(dP, params, n_sub * sizeof(*params));
-  H2D(dCoeffs, coeffs, n_coeffs * 4);
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
-  int rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
-                                     dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
-  if (rc) return rc;
+  int rc;
+  const bool twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                        (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
+  if (h->pipeChunks > 1 && !twoStage && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+    // ---- chunked pipeline: the slab crosses PCIe chunk by chunk while earlier chunks are coded ----
+    CK(ensurePipe(h), "pipeline streams");
+    uint64_t *hr = h->pinnedRanges;
+    uint32_t *hStart = reinterpret_cast<uint32_t *>(hr + 2 * cabac_handle::kMaxChunks);
+    const int K = planChunks(tu_offsets, n_sub, h->pipeChunks, hStart);
+    for (int k = 0; k < K; k++) {
+      hr[2 * k] = ~0ull;
+      hr[2 * k + 1] = 0;
+    }
+    H2D(dRanges, hr, 2 * K * sizeof(uint64_t));
+    H2D(dChunkStart, hStart, (K + 1) * sizeof(uint32_t));
+    CK(cabac::launchCoeffRanges(h->stream, dTus, dTuOff, dChunkStart, K, dRanges), "coeff_range_kernel");
+    h->launches += 1;
+    D2H(hr, dRanges, 2 * K * sizeof(uint64_t));
+    CK(cudaStreamSynchronize(h->stream), "sync");  // descriptors are resident from here on
+    uint64_t cur = ~0ull;
+    for (int k = 0; k < K; k++) {
+      if (hr[2 * k + 1] > n_coeffs) return badArg(h, "cabac_encode_residual_packed: descriptor beyond n_coeffs");
+      if (hr[2 * k] < cur) cur = hr[2 * k];
+    }
+    cabac::Sched base;
+    CK(schedFor(h, n_sub, base), "scheduler scratch");
+    if (h->trace) CK(cudaEventRecord(h->evT0, h->copyStream), "event");
+    for (int k = 0; k < K; k++) {
+      const uint64_t hi = hr[2 * k + 1];
+      if (hi > cur) {  // everything below `cur` is already on its way: any slab layout stays correct
+        CK(cudaMemcpyAsync(dCoeffs + cur, coeffs + cur, (hi - cur) * 4, cudaMemcpyHostToDevice, h->copyStream),
+           "H2D copy");
+        cur = hi;
+      }
+      CK(cudaEventRecord(h->evCopy[k], h->copyStream), "event");
+      cudaStream_t cs = h->compStream[k];
+      CK(cudaStreamWaitEvent(cs, h->evCopy[k], 0), "event wait");
+      const size_t s0 = hStart[k], nk = hStart[k + 1] - s0;
+      cabac::Sched sc = chunkSched(base, s0, k);
+      CK(cabac::launchEncodePrepare(cs, h->device, sc, dTus, dTuOff + s0, nk, dCoeffs, nullptr), "encode prepare kernels");
+      CK(cabac::launchEncodeResidual(cs, h->device, sc, dTus, dTuOff + s0, dP + s0, nk, dCoeffs,
+                                     ctx_in ? dCin + s0 * CABAC_NUM_CTX : nullptr, dOut, dOutOff + s0, dSizes + s0,
+                                     dBins + s0, dTuFlags, ctx_out ? dCout + s0 * CABAC_NUM_CTX : nullptr, dStatus + s0),
+         "encode_residual kernels");
+      h->launches += 4;
+      CK(cudaEventRecord(h->evDone[k], cs), "event");
+    }
+    for (int k = 0; k < K; k++) CK(cudaStreamWaitEvent(h->stream, h->evDone[k], 0), "event wait");
+    if (h->trace) {
+      CK(cudaEventRecord(h->evJoin, h->stream), "event");
+      CK(cudaStreamSynchronize(h->stream), "sync");
+      traceChunks(h, "encode_residual_packed", K, true);
+    }
+  } else {
+    H2D(dCoeffs, coeffs, n_coeffs * 4);
+    rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
+                                   dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+    if (rc) return rc;
+  }
   rc = cabac_pack_dev(h, dOut, dOutOff, dSizes, n_sub, dPacked, dEntry);
   if (rc) return rc;
   D2H(entry_points, dEntry, (n_sub + 1) * 8);
@@ -627,7 +775,8 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   DeviceGuard g(h->device);
   const size_t nTu = tu_offsets[n_sub], nIn = in_offsets[n_sub];
   cabac_tu_desc *dTus;
-  uint64_t *dTuOff, *dInOff;
+  uint64_t *dTuOff, *dInOff, *dRanges;
+  uint32_t *dChunkStart;
   cabac_substream_params *dP;
   int32_t *dCoeffs;
   cabac_ctx_model *dCin, *dCout;
@@ -637,6 +786,8 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   a.want((void **)&dTus, nTu * sizeof(*tus));
   a.want((void **)&dTuOff, (n_sub + 1) * 8);
   a.want((void **)&dInOff, (n_sub + 1) * 8);
+  a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
+  a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, n_sub * sizeof(*params));
   a.want((void **)&dCoeffs, n_coeffs * 4);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
@@ -655,10 +806,64 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   H2D(dIn, in, nIn);
   // positions no descriptor covers come back as zero
   CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
-  int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
-                                     dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
-  if (rc) return rc;
-  D2H(coeffs, dCoeffs, n_coeffs * 4);
+  if (h->pipeChunks > 1 && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+    // ---- chunked pipeline: finished coefficient ranges leave over PCIe while later chunks decode ----
+    CK(ensurePipe(h), "pipeline streams");
+    uint64_t *hr = h->pinnedRanges;
+    uint32_t *hStart = reinterpret_cast<uint32_t *>(hr + 2 * cabac_handle::kMaxChunks);
+    const int K = planChunks(tu_offsets, n_sub, h->pipeChunks, hStart);
+    for (int k = 0; k < K; k++) {
+      hr[2 * k] = ~0ull;
+      hr[2 * k + 1] = 0;
+    }
+    H2D(dRanges, hr, 2 * K * sizeof(uint64_t));
+    H2D(dChunkStart, hStart, (K + 1) * sizeof(uint32_t));
+    CK(cabac::launchCoeffRanges(h->stream, dTus, dTuOff, dChunkStart, K, dRanges), "coeff_range_kernel");
+    h->launches += 1;
+    D2H(hr, dRanges, 2 * K * sizeof(uint64_t));
+    CK(cudaStreamSynchronize(h->stream), "sync");  // inputs resident, slab zeroed
+    uint64_t sufMin[cabac_handle::kMaxChunks + 1];
+    sufMin[K] = n_coeffs;
+    for (int k = K - 1; k >= 0; k--) {
+      if (hr[2 * k + 1] > n_coeffs) return badArg(h, "cabac_decode_residual: descriptor beyond n_coeffs");
+      sufMin[k] = hr[2 * k] < sufMin[k + 1] ? hr[2 * k] : sufMin[k + 1];
+    }
+    cabac::Sched base;
+    CK(schedFor(h, n_sub, base), "scheduler scratch");
+    uint64_t cur = 0;
+    if (h->trace) CK(cudaEventRecord(h->evT0, h->compStream[0]), "event");
+    for (int k = 0; k < K; k++) {
+      cudaStream_t cs = h->compStream[k];
+      const size_t s0 = hStart[k], nk = hStart[k + 1] - s0;
+      cabac::Sched sc = chunkSched(base, s0, k);
+      CK(cabac::launchDecodeResidual(cs, h->device, sc, dIn, dInOff + s0, dTus, dTuOff + s0, dP + s0, nk,
+                                     ctx_in ? dCin + s0 * CABAC_NUM_CTX : nullptr, dCoeffs, dBins + s0, dBits + s0,
+                                     dTuFlags, ctx_out ? dCout + s0 * CABAC_NUM_CTX : nullptr, dStatus + s0),
+         "decode_residual_kernel");
+      h->launches += cabac::kLaunchesPerCodingCall;
+      CK(cudaEventRecord(h->evDone[k], cs), "event");
+      // chunks 0..k are complete once the copy stream has passed evDone[0..k]; no later chunk
+      // writes below sufMin[k + 1]
+      CK(cudaStreamWaitEvent(h->copyStream, h->evDone[k], 0), "event wait");
+      const uint64_t safe = sufMin[k + 1];
+      if (safe > cur) {
+        CK(cudaMemcpyAsync(coeffs + cur, dCoeffs + cur, (safe - cur) * 4, cudaMemcpyDeviceToHost, h->copyStream),
+           "D2H copy");
+        cur = safe;
+      }
+    }
+    CK(cudaEventRecord(h->evJoin, h->copyStream), "event");
+    CK(cudaStreamWaitEvent(h->stream, h->evJoin, 0), "event wait");
+    if (h->trace) {
+      CK(cudaStreamSynchronize(h->stream), "sync");
+      traceChunks(h, "decode_residual", K, false);
+    }
+  } else {
+    int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
+                                       dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+    if (rc) return rc;
+    D2H(coeffs, dCoeffs, n_coeffs * 4);
+  }
   D2H(num_bins, dBins, n_sub * 4);
   D2H(bits_read, dBits, n_sub * 4);
   D2H(tu_flags, dTuFlags, nTu);

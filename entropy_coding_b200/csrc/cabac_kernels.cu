@@ -458,10 +458,28 @@ __device__ __forceinline__ int pushLastSigCoeff(uint32_t *q, const TuGeom &g, in
   return n;
 }
 
+// Exclusive prefix sum over the 16 lanes of a coefficient group (lanes >= 16 contribute 0 and
+// receive the total); `total` is the group's sum on every lane.
+__device__ __forceinline__ int cgExclusiveScan(int v, int lane, int &total) {
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const int t = __shfl_up_sync(FULL, inc, o);
+    if ((lane & 15) >= o) inc += t;
+  }
+  total = __shfl_sync(FULL, inc, 15);
+  return inc - v;
+}
+
 // One coefficient group of a transform-skip block as command words
-// (residual_coding_subblockTS, cabac_writer.cpp:2924-3062).  Serial, identical on all lanes.
+// (residual_coding_subblockTS, cabac_writer.cpp:2924-3062).  The encoder knows every level up
+// front, so lane k binarises scan position minPos + k on its own: contexts come from the original
+// left / above neighbours, and the only serial quantities - the context-coded bin budget that ends
+// pass 1 / pass 2 and each word's slot in the queue - are prefix sums over the lanes.
+// Returns the word count (uniform).
 __device__ __forceinline__ int produceTsCG(uint32_t *q, const int16_t *tile, const TuGeom &g, bool bdpcm,
-                                           const uint16_t *cgMask, int s, int &remBins, uint64_t &sigGroups) {
+                                           const uint16_t *cgMask, int s, int &remBins, uint64_t &sigGroups,
+                                           int lane) {
   int n = 0;
   const int cgSize = 1 << g.log2cg;
   const int lastSubSet = g.numCG - 1;
@@ -473,67 +491,74 @@ __device__ __forceinline__ int produceTsCG(uint32_t *q, const int16_t *tile, con
   const int above = cgy > 0 ? int((sigGroups >> (cgPos - g.wig)) & 1) : 0;
   const uint64_t others = sigGroups & ~(1ull << lastSubSet);
   if (s != lastSubSet || others != 0) {
-    q[n++] = CABAC_MK_CTX(R_TS_SIG_GROUP + left + above, sig);
+    if (lane == 0) q[0] = CABAC_MK_CTX(R_TS_SIG_GROUP + left + above, sig);
+    n = 1;
     if (!sig) return n;
   }
-  const int minPos = s << g.log2cg, maxPos = minPos + cgSize - 1;
-  int numNonZero = 0, lastPass1 = -1, lastPass2 = -1;
-  int sp = minPos;
-  for (; sp <= maxPos && remBins >= 4; sp++) {
-    int x, y, l, a;
-    scanXY(g, sp, x, y);
-    const int v = tile[(y << g.log2tw) + x];
-    const uint32_t sigf = v != 0;
-    neighTS(tile, g, x, y, l, a);
-    if (numNonZero || sp != maxPos) {
-      q[n++] = CABAC_MK_CTX(R_TS_SIG_FLAG + (l != 0) + (a != 0), sigf);
-      remBins--;
-    }
-    if (sigf) {
-      q[n++] = CABAC_MK_CTX(signCtxTS(l, a, bdpcm), v < 0);
-      remBins--;
-      numNonZero++;
-      int rem = modCoeffTS(l, a, abs(v), bdpcm) - 1;
-      const uint32_t gt1 = rem != 0;
-      q[n++] = CABAC_MK_CTX(R_TS_LRG1_FLAG + (bdpcm ? 3 : (l != 0) + (a != 0)), gt1);
-      remBins--;
-      if (gt1) {
-        rem -= 1;
-        q[n++] = CABAC_MK_CTX(R_TS_PAR_FLAG, uint32_t(rem) & 1u);
-        remBins--;
-      }
-    }
-    lastPass1 = sp;
-  }
-  for (sp = minPos; sp <= maxPos && remBins >= 4; sp++) {
-    int x, y, l, a;
-    scanXY(g, sp, x, y);
-    neighTS(tile, g, x, y, l, a);
-    const int absLevel = modCoeffTS(l, a, abs(int(tile[(y << g.log2tw) + x])), bdpcm);
-    for (int cutoff = 2; cutoff <= 8; cutoff += 2) {
-      if (absLevel >= cutoff) {
-        q[n++] = CABAC_MK_CTX(R_TS_GTX_FLAG + (cutoff >> 1), absLevel >= cutoff + 2);
-        remBins--;
-      }
-    }
-    lastPass2 = sp;
-  }
-  for (sp = minPos; sp <= maxPos; sp++) {
-    int x, y, l, a;
-    scanXY(g, sp, x, y);
-    neighTS(tile, g, x, y, l, a);
-    const int cutoff = sp <= lastPass2 ? 10 : (sp <= lastPass1 ? 2 : 0);
-    const int v = tile[(y << g.log2tw) + x];
-    const int absLevel = modCoeffTS(l, a, abs(v), bdpcm || !cutoff);
-    if (absLevel >= cutoff) {
-      const uint32_t rem = sp <= lastPass1 ? uint32_t(absLevel - cutoff) >> 1 : uint32_t(absLevel);
-      uint32_t w0 = 0, w1 = 0;
-      const int cnt = lsRemWords(rem, 1, w0, w1);
-      q[n++] = w0;
-      if (cnt == 2) q[n++] = w1;
-      if (absLevel && sp > lastPass1) q[n++] = CABAC_MK_EP(v < 0, 1);
+  const bool active = lane < cgSize;
+  const int k = lane & (cgSize - 1);
+  int x, y, l, a;
+  scanXY(g, (s << g.log2cg) + k, x, y);
+  const int v = active ? int(tile[(y << g.log2tw) + x]) : 0;
+  neighTS(tile, g, x, y, l, a);
+  const int absV = abs(v);
+  const int mod = modCoeffTS(l, a, absV, bdpcm);  // level after prediction from the neighbours
+  const uint32_t nzMask = uint32_t(cgMask[s]);
+  // ---- pass 1: sig, sign, gt1, par ----
+  const bool sigCoded = active && ((nzMask & ((1u << k) - 1u)) != 0 || k != cgSize - 1);
+  const int gt1 = mod > 1;
+  const int c1 = active ? int(sigCoded) + (v ? 2 + gt1 : 0) : 0;
+  int tot1, tot2, tot3;
+  const int ex1 = cgExclusiveScan(c1, lane, tot1);
+  const bool inP1 = active && remBins - ex1 >= 4;
+  const uint32_t p1Mask = __ballot_sync(FULL, inP1);  // a prefix of the group's positions
+  const int nP1 = __popc(p1Mask);
+  if (inP1) {
+    uint32_t *w = q + n + ex1;
+    const int nb = (l != 0) + (a != 0);
+    if (sigCoded) *w++ = CABAC_MK_CTX(R_TS_SIG_FLAG + nb, v != 0);
+    if (v) {
+      *w++ = CABAC_MK_CTX(signCtxTS(l, a, bdpcm), v < 0);
+      *w++ = CABAC_MK_CTX(R_TS_LRG1_FLAG + (bdpcm ? 3 : nb), gt1);
+      if (gt1) *w++ = CABAC_MK_CTX(R_TS_PAR_FLAG, uint32_t(mod - 2) & 1u);
     }
   }
+  const int used1 = nP1 == cgSize ? tot1 : __shfl_sync(FULL, ex1, nP1 & 31);  // bins of positions 0..nP1-1
+  n += used1;
+  remBins -= used1;
+  // ---- pass 2: greater-than-2/4/6/8 flags ----
+  const int c2 = active ? min(mod >> 1, 4) : 0;
+  const int ex2 = cgExclusiveScan(c2, lane, tot2);
+  const bool inP2 = active && remBins - ex2 >= 4;
+  const int nP2 = __popc(__ballot_sync(FULL, inP2));
+  if (inP2) {
+    uint32_t *w = q + n + ex2;
+    for (int cutoff = 2; cutoff <= 8 && mod >= cutoff; cutoff += 2)
+      *w++ = CABAC_MK_CTX(R_TS_GTX_FLAG + (cutoff >> 1), mod >= cutoff + 2);
+  }
+  const int used2 = nP2 == cgSize ? tot2 : __shfl_sync(FULL, ex2, nP2 & 31);
+  n += used2;
+  remBins -= used2;
+  // ---- pass 3: bypass remainders (+ bypass signs of positions pass 1 did not reach) ----
+  const int cutoff = k < nP2 ? 10 : (k < nP1 ? 2 : 0);
+  const int absLevel = cutoff ? mod : (bdpcm ? mod : absV);  // modCoeffTS(l, a, |v|, bdpcm || !cutoff)
+  uint32_t w0 = 0, w1 = 0;
+  int cnt = 0;
+  bool signWord = false;
+  if (active && absLevel >= cutoff) {
+    const uint32_t rem = k < nP1 ? uint32_t(absLevel - cutoff) >> 1 : uint32_t(absLevel);
+    cnt = lsRemWords(rem, 1, w0, w1);
+    signWord = absLevel && k >= nP1;
+  }
+  const int c3 = cnt + int(signWord);
+  const int ex3 = cgExclusiveScan(c3, lane, tot3);
+  if (c3) {
+    uint32_t *w = q + n + ex3;
+    *w++ = w0;
+    if (cnt == 2) *w++ = w1;
+    if (signWord) *w++ = CABAC_MK_EP(v < 0, 1);
+  }
+  n += tot3;
   return n;
 }
 
@@ -649,7 +674,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       }
       bool endTu;
       if (tsPath) {
-        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups);
+        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups, lane);
         s++;
         endTu = s == g.numCG;
       } else {
@@ -858,7 +883,7 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
       }
       bool endTu;
       if (tsPath) {
-        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups);
+        nq += produceTsCG(sm.queue + nq, sm.tile, g, bdpcm, sm.cgMask, s, remBinsTS, sigGroups, lane);
         s++;
         endTu = s == g.numCG;
       } else {
@@ -1028,7 +1053,7 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       if (d.flags & CABAC_TU_TS_ALLOWED) ts = lsDecodeBin(dec, sm.ctx + R_TS_FLAG + (g.comp ? 1 : 0)) != 0;
       uint32_t res = ts ? CABAC_TUR_TS : 0;
       if (ts && !(p.flags & CABAC_SUB_TSRC_DISABLED))
-        lsResidualTS(dec, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0);
+        lsResidualTS(dec, sm.ctx, sm.tile, g, (d.flags & CABAC_TU_BDPCM) != 0, lane);
       else
         res |= lsResidualRegular(dec, sm.ctx, sm.tile, g, p.flags, ts, lane);
       if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
@@ -1304,6 +1329,43 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
       sc.order, sc.cursor);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Coefficient range [lo, hi) (TCoeff units) the TUs of each chunk of substreams touch:
+// lets the host-pointer entry points stream the slab over PCIe chunk by chunk while earlier
+// chunks are already being coded.  ranges[2k] = lo, ranges[2k+1] = hi; pre-set to ~0 / 0.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) coeff_range_kernel(const cabac_tu_desc *__restrict__ tus,
+                                                          const uint64_t *__restrict__ tuOffsets,
+                                                          const uint32_t *__restrict__ chunkStart,
+                                                          unsigned long long *__restrict__ ranges) {
+  const int k = blockIdx.y;
+  const uint64_t t0 = tuOffsets[chunkStart[k]], t1 = tuOffsets[chunkStart[k + 1]];
+  unsigned long long lo = ~0ull, hi = 0;
+  for (uint64_t t = t0 + blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; t < t1; t += uint64_t(gridDim.x) * blockDim.x) {
+    const cabac_tu_desc d = tus[t];
+    const unsigned long long a = d.coeff_offset, b = a + (1ull << (d.log2_w + d.log2_h));
+    lo = a < lo ? a : lo;
+    hi = b > hi ? b : hi;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long l2 = __shfl_xor_sync(FULL, lo, o), h2 = __shfl_xor_sync(FULL, hi, o);
+    lo = l2 < lo ? l2 : lo;
+    hi = h2 > hi ? h2 : hi;
+  }
+  if ((threadIdx.x & 31) == 0 && hi) {
+    atomicMin(ranges + 2 * k, lo);
+    atomicMax(ranges + 2 * k + 1, hi);
+  }
+}
+
+cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                              const uint32_t *chunkStart, int nChunks, uint64_t *ranges) {
+  if (nChunks <= 0) return cudaSuccess;
+  coeff_range_kernel<<<dim3(64, nChunks), 256, 0, s>>>(tus, tuOffsets, chunkStart,
+                                                        reinterpret_cast<unsigned long long *>(ranges));
   return cudaGetLastError();
 }
 

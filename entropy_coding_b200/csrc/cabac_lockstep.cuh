@@ -237,11 +237,12 @@ __device__ __forceinline__ int lsLastSigCoeff(LsDecoder &dec, uint4 *ctx, const 
 
 // Template state of the scan position a lane owns -> the context offsets / Rice
 // parameters that position will need (R3-R5 of SURVEY.md section 8a).
-//   bits 0..3 sig offset, 4..8 gtx offset, 9..10 Rice (2nd pass), 11..12 Rice (bypass pass)
-__device__ __forceinline__ uint32_t lanePack(int s1, int np, int sa, int sigDiag, int gtxDiag) {
+//   bits 0..3 sig offset, 4..8 gtx offset.  (The Rice parameters of the 2nd / bypass pass come from
+//   the owner lane's absolute sum directly: one shuffle + one goRicePar per remainder.)
+__device__ __forceinline__ uint32_t lanePack(int s1, int np, int sigDiag, int gtxDiag) {
   const uint32_t sig = uint32_t(min((s1 + 1) >> 1, 3) + sigDiag);
   const uint32_t gtx = uint32_t(min(s1 - np, 4) + 1 + gtxDiag);
-  return sig | (gtx << 4) | (goRicePar(sa - 20) << 9) | (goRicePar(sa) << 11);
+  return sig | (gtx << 4);
 }
 
 // ---------------------------------------------------------------------------
@@ -322,7 +323,7 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
       }
     }
     int myVal = 0;
-    uint32_t myInfo = lanePack(s1, np, sa, sigDiag, gtxDiag);
+    uint32_t myInfo = lanePack(s1, np, sigDiag, gtxDiag);
     const int P0 = isLast ? scanPosLast - (s << g.log2cg) : cgSize - 1;
     const int inferSigPos = isLast ? P0 : (s != 0 ? 0 : -1);
     uint32_t nzMask = 0, remMask = 0;
@@ -364,7 +365,7 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
       }
       if (depQuant) state = stateStep(state, val & 1);
       if (boundary && p > 0) {
-        myInfo = lanePack(s1, np, sa, sigDiag, gtxDiag);
+        myInfo = lanePack(s1, np, sigDiag, gtxDiag);
         infoNext = __shfl_sync(FULL, myInfo, p - 1);
       }
       info = infoNext;
@@ -375,13 +376,13 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
     while (visit) {
       const int j = 31 - __clz(int(visit));
       visit &= ~(1u << j);
-      const uint32_t inf = __shfl_sync(FULL, lanePack(s1, np, sa, sigDiag, gtxDiag), j);
+      const int saj = __shfl_sync(FULL, sa, j);  // templateAbsSum of position j, context_modelling.hpp:135-157
       if (j > cut) {
-        const int add = int(dec.remAbs((inf >> 9) & 3u) << 1);
+        const int add = int(dec.remAbs(goRicePar(saj - 20)) << 1);
         if (lane == j) myVal += add;
         if ((tmask >> j) & 1u) sa += add;
       } else {
-        const uint32_t rice = (inf >> 11) & 3u;
+        const uint32_t rice = goRicePar(saj);
         const uint32_t pos0 = (state < 2 ? 1u : 2u) << rice;
         const uint32_t rem = dec.remAbs(rice);
         const int val = int(rem == pos0 ? 0u : (rem < pos0 ? rem + 1u : rem));
@@ -417,7 +418,8 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
 // residual_codingTS + subblockTS, cabac_reader.cpp:3130-3339
 // Lockstep flavour: every lane executes the same serial parse (transform-skip blocks are a
 // small share of the bins); tile stores are same-value broadcasts.
-__device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g, bool bdpcm) {
+__device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t *tile, const TuGeom &g, bool bdpcm,
+                                             int lane) {
   int remBins = ((g.w * g.h) * 7) >> 2;
   uint64_t sigGroups = 0;
   const int cgSize = 1 << g.log2cg;
@@ -434,15 +436,24 @@ __device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t
     if (!sigGroup) continue;
     sigGroups |= 1ull << cgPos;
     const int minPos = s << g.log2cg, maxPos = minPos + cgSize - 1;
+    // lane k owns scan position minPos + k: tile index | has-left << 16 | has-above << 17, fetched by
+    // shuffle in the passes below (keeps the scan-table loads off the per-bin dependent chain)
+    uint32_t myPos;
+    {
+      int x, y;
+      scanXY(g, minPos + (lane & (cgSize - 1)), x, y);
+      myPos = uint32_t((y << g.log2tw) + x) | (x > 0 ? 1u << 16 : 0u) | (y > 0 ? 1u << 17 : 0u);
+    }
+#define TS_POS(sp, ti, l, a)                                              \
+  const uint32_t pk_ = __shfl_sync(FULL, myPos, (sp) - minPos);           \
+  const int ti = int(pk_ & 0xFFFFu);                                      \
+  const int l = (pk_ >> 16) & 1u ? tile[ti - 1] : 0;                      \
+  const int a = (pk_ >> 17) & 1u ? tile[ti - g.tw] : 0;
     int numNonZero = 0, lastPass1 = -1, lastPass2 = -1;
-    uint32_t signPattern = 0;
-    uint16_t sigIdx[16];
+    uint32_t signMask = 0;  // bit k: position minPos + k is negative (coded signs arrive in ascending position order)
     int sp = minPos;
     for (; sp <= maxPos && remBins >= 4; sp++) {
-      int x, y, l, a;
-      scanXY(g, sp, x, y);
-      const int ti = (y << g.log2tw) + x;
-      neighTS(tile, g, x, y, l, a);
+      TS_POS(sp, ti, l, a)
       bool sig = (!numNonZero && sp == maxPos);
       if (!sig) {
         sig = lsDecodeBin(dec, ctx + R_TS_SIG_FLAG + (l != 0) + (a != 0));
@@ -451,8 +462,8 @@ __device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t
       if (sig) {
         const uint32_t sign = lsDecodeBin(dec, ctx + signCtxTS(l, a, bdpcm));
         remBins--;
-        signPattern += sign << numNonZero;
-        sigIdx[numNonZero++] = uint16_t(ti);
+        signMask |= sign << (sp - minPos);
+        numNonZero++;
         const uint32_t gt1 = lsDecodeBin(dec, ctx + R_TS_LRG1_FLAG + (bdpcm ? 3 : (l != 0) + (a != 0)));
         remBins--;
         uint32_t par = 0;
@@ -465,9 +476,7 @@ __device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t
       lastPass1 = sp;
     }
     for (sp = minPos; sp <= maxPos && remBins >= 4; sp++) {
-      int x, y;
-      scanXY(g, sp, x, y);
-      const int ti = (y << g.log2tw) + x;
+      const int ti = int(__shfl_sync(FULL, myPos, sp - minPos) & 0xFFFFu);
       int t = abs(tile[ti]);
       for (int cutoff = 2; cutoff <= 8; cutoff += 2) {
         if (t >= cutoff) {
@@ -479,34 +488,31 @@ __device__ __forceinline__ void lsResidualTS(LsDecoder &dec, uint4 *ctx, int32_t
       lastPass2 = sp;
     }
     for (sp = minPos; sp <= maxPos; sp++) {
-      int x, y;
-      scanXY(g, sp, x, y);
-      const int ti = (y << g.log2tw) + x;
+      TS_POS(sp, ti, l, a)
       const int cutoff = sp <= lastPass2 ? 10 : (sp <= lastPass1 ? 2 : 0);
       int t = abs(tile[ti]);
       if (t >= cutoff) {
         const int rem = int(lsRemAbs(dec, 1));
         t += (sp <= lastPass1) ? (rem << 1) : rem;
         if (t && sp > lastPass1) {
-          const uint32_t sign = dec.ep(1);
-          signPattern += sign << numNonZero;
-          sigIdx[numNonZero++] = uint16_t(ti);
+          signMask |= dec.ep(1) << (sp - minPos);
         }
       }
-      if (!bdpcm && cutoff && t > 0) {
-        int l, a;
-        neighTS(tile, g, x, y, l, a);
-        t = decModCoeffTS(l, a, t);
-      }
+      if (!bdpcm && cutoff && t > 0) t = decModCoeffTS(l, a, t);
       tile[ti] = t;
     }
-    for (int k = 0; k < numNonZero; k++) {
-      const int a = tile[sigIdx[k]];
-      const int v = (signPattern & 1u) ? -a : a;
-      tile[sigIdx[k]] = v;
-      signPattern >>= 1;
-      if (v < -32768 || v > 32767) dec.status |= CABAC_SS_COEFF_RANGE;
+#undef TS_POS
+    // signs: one position per lane
+    __syncwarp();
+    int v = 0;
+    if (lane < cgSize) {
+      const int ti = int(myPos & 0xFFFFu);
+      const int a = tile[ti];
+      v = (signMask >> lane) & 1u ? -a : a;
+      tile[ti] = v;
     }
+    if (__any_sync(FULL, v < -32768 || v > 32767)) dec.status |= CABAC_SS_COEFF_RANGE;
+    __syncwarp();
   }
 }
 

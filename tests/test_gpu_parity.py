@@ -360,3 +360,58 @@ def test_full_size_round_trip_and_checksum(engine, oracle):
         p = wl.params[i]
         eb, nb, _ = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
         assert outs[i].tobytes() == eb.tobytes() and nb == int(r["num_bins"][i])
+
+
+# ---------------------------------------------------------------- chunked copy/compute pipeline
+@pytest.mark.parametrize("layout", ["ordered", "shuffled"])
+def test_pipelined_host_path_matches_single_launch(monkeypatch, oracle, layout):
+    """cabac_encode_residual_packed / cabac_decode_residual stream the coefficient slab over PCIe in
+    chunks while earlier chunks are coded.  Results must equal the one-copy-one-launch path for any
+    slab layout (TU blocks in substream order or scattered, with gaps no descriptor covers)."""
+    import entropy_coding_b200 as E
+    wl = W.random_substreams(700, 321, tus_per_sub=(2, 9))
+    tus, coeffs = wl.tus.copy(), wl.coeffs
+    if layout == "shuffled":  # scatter the TU blocks over a larger slab, leaving holes
+        rng = np.random.default_rng(5)
+        sizes = 1 << (tus["log2_w"].astype(np.int64) + tus["log2_h"].astype(np.int64))
+        perm = rng.permutation(len(tus))
+        gaps = rng.integers(0, 64, len(tus)) * 4
+        new_off = np.zeros(len(tus), np.int64)
+        new_off[perm] = np.concatenate([[0], np.cumsum(sizes[perm] + gaps[perm])[:-1]]) + 16
+        total = int((new_off + sizes).max()) + 32
+        slab = np.zeros(total, np.int32)
+        for t in range(len(tus)):
+            o, n = int(tus["coeff_offset"][t]), int(sizes[t])
+            slab[int(new_off[t]):int(new_off[t]) + n] = coeffs[o:o + n]
+        tus["coeff_offset"] = new_off.astype(np.uint64)
+        coeffs = slab
+    cap = wl.out_capacity(bytes_per_coeff=5.0)
+    results = {}
+    for name, chunks in (("single", "1"), ("pipelined", "6")):
+        monkeypatch.setenv("CABAC_B200_PIPE_CHUNKS", chunks)
+        monkeypatch.setenv("CABAC_B200_PIPE_MIN_COEFFS", "1")
+        monkeypatch.setenv("CABAC_B200_PIPE_MIN_SUBSTREAMS", "1")
+        eng = E.CabacEngine(0)
+        n0 = eng.launch_count
+        r = eng.encode_residual_packed(tus, wl.tu_offsets, wl.params, coeffs, cap, want_ctx=True)
+        n1 = eng.launch_count
+        d = eng.decode_residual(r["packed"], r["entry_points"], tus, wl.tu_offsets, wl.params, coeffs.size,
+                                want_ctx=True)
+        results[name] = (r, d, n1 - n0, eng.launch_count - n1)
+        eng.close()
+    (r1, d1, le1, ld1), (r2, d2, le2, ld2) = results["single"], results["pipelined"]
+    assert le2 > le1 and ld2 > ld1, "the pipelined path did not run"
+    assert r1["packed"].tobytes() == r2["packed"].tobytes()
+    for k in ("entry_points", "sizes", "num_bins", "tu_flags"):
+        assert (r1[k] == r2[k]).all(), k
+    assert (ctx_pairs(r1["ctx_out"]) == ctx_pairs(r2["ctx_out"])).all() and (ctx_pairs(d1["ctx_out"]) == ctx_pairs(d2["ctx_out"])).all()
+    assert (d1["coeffs"] == d2["coeffs"]).all() and (d2["coeffs"] == coeffs).all()
+    for k in ("num_bins", "bits_read", "tu_flags"):
+        assert (d1[k] == d2[k]).all(), k
+    # and against the oracle on a sample
+    ep = r2["entry_points"]
+    for i in range(0, wl.n_sub, 70):
+        a, b = int(wl.tu_offsets[i]), int(wl.tu_offsets[i + 1])
+        p = wl.params[i]
+        eb, nb, _ = oracle.encode_residual(tus[a:b], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
+        assert r2["packed"][int(ep[i]):int(ep[i + 1])].tobytes() == eb.tobytes() and nb == int(r2["num_bins"][i])
