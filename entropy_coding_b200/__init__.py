@@ -6,6 +6,6 @@ face of that ABI plus the synthetic-workload generator used by tests and
 bench.py.  There is no CPU implementation in here.
 """
 from .engine import CabacEngine, CabacError  # noqa: F401
-from . import types, workload  # noqa: F401
+from . import sharding, types, workload  # noqa: F401
 
-__all__ = ["CabacEngine", "CabacError", "types", "workload"]
+__all__ = ["CabacEngine", "CabacError", "sharding", "types", "workload"]

@@ -32,6 +32,7 @@ struct cabac_handle {
   size_t cmdCapWords = 0;
   uint64_t *pinnedTotal = nullptr;  // page-locked landing spot for the slab size read-back
   int encoderMode = CABAC_ENCODER_AUTO;
+  bool fusedResolve = true;  // CABAC_B200_FUSED_RESOLVE=0 selects the classic single-site drain
   // chunked pipeline of the host-pointer residual entry points: PCIe copies of the coefficient
   // slab overlap coding (one copy stream; one compute stream per chunk, so a chunk's long substreams never
   // hold back the chunks behind it)
@@ -116,6 +117,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
   sc.cmdCounts = p + 3 * cap;
   sc.statusScratch = p + 4 * cap;
   sc.cmdBuf = h->cmdBuf;
+  sc.fusedResolve = h->fusedResolve;
   return cudaSuccess;
 }
 
@@ -247,6 +249,7 @@ cabac_handle *cabac_create(int device) {
     const int v = atoi(c);
     if (v >= 1 && v <= cabac_handle::kMaxChunks) h->pipeChunks = v;
   }
+  if (const char *c = getenv("CABAC_B200_FUSED_RESOLVE")) h->fusedResolve = atoi(c) != 0;
   if (const char *c = getenv("CABAC_B200_TRACE")) h->trace = atoi(c) != 0;
   if (const char *c = getenv("CABAC_B200_PIPE_MIN_COEFFS")) h->pipeMinCoeffs = size_t(atoll(c));
   if (const char *c = getenv("CABAC_B200_PIPE_MIN_SUBSTREAMS")) h->pipeMinSubstreams = size_t(atoll(c));

@@ -574,6 +574,9 @@ struct __align__(16) FusedEncWarpSmem {
   uint16_t cgMask[64];
 };
 
+// kResolve: probabilities of a batch are resolved lane-parallel (lsResolveQueue) before the serial
+// walk, which then only carries the interval recurrence.
+template <bool kResolve>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
@@ -707,7 +710,12 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         inTu = false;
       }
       __syncwarp();
-      lsDrain(enc, sm.ctx, sm.queue, nq);
+      if (kResolve) {
+        lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+        lsDrainResolved(enc, sm.queue, nq);
+      } else {
+        lsDrain(enc, sm.ctx, sm.queue, nq);
+      }
       if (enc.out.n - enc.out.flushed >= uint32_t(STAGE_BYTES / 2)) enc.out.flush(false);
       __syncwarp();
     }
@@ -1280,9 +1288,14 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
   if (!sc.twoStage) {
-    encode_residual_kernel<<<persistentGrid(encode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-        tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-        status ? status : sc.statusScratch, sc.order, sc.cursor);
+    if (sc.fusedResolve)
+      encode_residual_kernel<true><<<persistentGrid(encode_residual_kernel<true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
+          status ? status : sc.statusScratch, sc.order, sc.cursor);
+    else
+      encode_residual_kernel<false><<<persistentGrid(encode_residual_kernel<false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
+          status ? status : sc.statusScratch, sc.order, sc.cursor);
     return cudaGetLastError();
   }
   produce_kernel<false><<<persistentGrid(produce_kernel<false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(

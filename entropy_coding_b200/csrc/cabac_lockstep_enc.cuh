@@ -231,6 +231,20 @@ __device__ __forceinline__ void lsDrain(LsEncoder &enc, uint4 *ctx, const uint32
   }
 }
 
+// The same walk over words whose probabilities were already resolved in parallel
+// (lsResolveQueue below): only the interval recurrence is left on the serial path.
+__device__ __forceinline__ void lsDrainResolved(LsEncoder &enc, const uint32_t *queue, int n) {
+  if (n <= 0) return;
+  uint32_t w = queue[0];
+#pragma unroll 1
+  for (int i = 0; i < n; i++) {
+    const uint32_t wn = queue[min(i + 1, n - 1)];
+    enc.step(w);
+    enc.flushBits();
+    w = wn;
+  }
+}
+
 // encodeRemAbsEP(v, rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:426-458, as one or
 // two EP command words (prefix and suffix concatenated when they fit 24 bins).  Returns the count.
 __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w0, uint32_t &w1) {

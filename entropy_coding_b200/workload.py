@@ -197,3 +197,23 @@ def frames_as_ctu_substreams(n_frames: int, width: int, height: int, seed0: int 
         params[i] = (qp, iid, fl, 0)
     return Workload(np.concatenate(tus), np.asarray(offs, np.uint64), params, np.concatenate(co),
                     f"{width}x{height}-AI-{n_frames}f-{'frame' if per_frame else 'ctu'}-substreams")
+
+
+def frames_as_ctu_rows(n_frames: int, width: int, height: int, seed0: int = 1000, ctu: int = 128, **kw):
+    """WPP layout (BASELINE.json configs[3]): one substream per CTU ROW, rows of a frame consecutive.
+
+    Returns (workload, rows_per_frame, first_ctu_tus) where first_ctu_tus[i] is the number of TUs of
+    row i's first CTU - the point after which the row below picks up its contexts
+    (VTM EncSlice.cpp:2085-2089).  The slice QP of a frame is that of its first CTU.
+    """
+    wl = frames_as_ctu_substreams(n_frames, width, height, seed0=seed0, ctu=ctu, **kw)
+    cpr = (width + ctu - 1) // ctu
+    rows = (height + ctu - 1) // ctu
+    assert wl.n_sub == n_frames * rows * cpr
+    off = wl.tu_offsets.astype(np.int64)
+    first = (off[1::cpr] - off[0::cpr][:len(off[1::cpr])]).astype(np.int64)
+    params = wl.params[0::cpr].copy()
+    for f in range(n_frames):  # one slice QP per frame
+        params[f * rows:(f + 1) * rows] = params[f * rows]
+    return (Workload(wl.tus, wl.tu_offsets[0::cpr].copy(), params, wl.coeffs,
+                     f"{width}x{height}-WPP-{n_frames}f-row-substreams"), rows, first)
