@@ -5,6 +5,8 @@
 // a command queue and an output staging ring (see cabac_device.cuh).
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include <cstring>
 
 #include "cabac_lockstep_enc.cuh"
@@ -21,6 +23,15 @@ namespace hosttab {
 }
 
 constexpr int WARPS_PER_BLOCK = 4;
+// resident CTAs per SM the register allocation of the two hot kernels is held to (occupancy sweep in
+// 5 CTAs = 20 warps per SM is the measured optimum of both; tighter register
+// caps cost more in extra instructions than the added warps return)
+#ifndef ENC_MIN_CTAS
+#define ENC_MIN_CTAS 5
+#endif
+#ifndef DEC_MIN_CTAS
+#define DEC_MIN_CTAS 5
+#endif
 
 __device__ __forceinline__ int clipQp(int qp) { return qp < 0 ? 0 : (qp > 63 ? 63 : qp); }
 
@@ -577,7 +588,7 @@ struct __align__(16) FusedEncWarpSmem {
 // kResolve: probabilities of a batch are resolved lane-parallel (lsResolveQueue) before the serial
 // walk, which then only carries the interval recurrence.
 template <bool kResolve>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, ENC_MIN_CTAS)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
                        const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
@@ -592,14 +603,21 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
-    LsEncoder enc;  // identical on every lane
-    enc.start();
-    enc.out.ring = sm.ring;
-    enc.out.dst = out + outOffsets[sub];
-    enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
-    enc.out.n = 0;
-    enc.out.flushed = 0;
-    enc.out.lane = lane;
+    // identical on every lane; only the coder of this instantiation survives dead-code elimination
+    LsEncoder enc;
+    LsCoder rc;
+    if constexpr (kResolve) {
+      rc.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane,
+               (p.flags & CABAC_SUB_TERMINATE) != 0);
+    } else {
+      enc.start();
+      enc.out.ring = sm.ring;
+      enc.out.dst = out + outOffsets[sub];
+      enc.out.cap = uint32_t(outOffsets[sub + 1] - outOffsets[sub]);
+      enc.out.n = 0;
+      enc.out.flushed = 0;
+      enc.out.lane = lane;
+    }
     uint32_t st = 0;
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
@@ -710,21 +728,31 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         inTu = false;
       }
       __syncwarp();
-      if (kResolve) {
-        lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
-        lsDrainResolved(enc, sm.queue, nq);
+      if constexpr (kResolve) {
+        rc.nbins += lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+        lsWalkResolved(rc, sm.queue, nq);
       } else {
         lsDrain(enc, sm.ctx, sm.queue, nq);
+        if (enc.out.n - enc.out.flushed >= uint32_t(STAGE_BYTES / 2)) enc.out.flush(false);
       }
-      if (enc.out.n - enc.out.flushed >= uint32_t(STAGE_BYTES / 2)) enc.out.flush(false);
       __syncwarp();
     }
-    enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
-    enc.out.flush(true);
+    uint32_t total, cap, nb;
+    if constexpr (kResolve) {
+      total = rc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+      cap = rc.cap;
+      nb = rc.nbins;
+    } else {
+      enc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+      enc.out.flush(true);
+      total = enc.out.n;
+      cap = enc.out.cap;
+      nb = enc.nbins;
+    }
     if (lane == 0) {
-      if (enc.out.n > enc.out.cap) st |= CABAC_SS_OUT_OVERFLOW;
-      outSizes[sub] = enc.out.n;
-      if (numBins) numBins[sub] = enc.nbins;
+      if (total > cap) st |= CABAC_SS_OUT_OVERFLOW;
+      outSizes[sub] = total;
+      if (numBins) numBins[sub] = nb;
       if (status) status[sub] = st;
     }
     storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
@@ -1032,7 +1060,7 @@ struct __align__(16) DecWarpSmem {
   uint4 ctx[RCTX];
 };
 
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, DEC_MIN_CTAS)
 decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
                        const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
@@ -1227,6 +1255,11 @@ static int persistentGrid(K kernel, size_t nSub, int device) {
   cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, WARPS_PER_BLOCK * 32, 0) != cudaSuccess || perSm < 1)
     perSm = 1;
+  static const int maxPerSm = [] {  // experiment knob: CABAC_B200_CTAS_PER_SM caps the resident CTAs per SM
+    const char *e = getenv("CABAC_B200_CTAS_PER_SM");
+    return e ? atoi(e) : 0;
+  }();
+  if (maxPerSm > 0 && perSm > maxPerSm) perSm = maxPerSm;
   const size_t blocks = (nSub + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
   const size_t cap = size_t(sms) * perSm;
   return int(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));

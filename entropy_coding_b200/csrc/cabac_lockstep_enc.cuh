@@ -245,6 +245,207 @@ __device__ __forceinline__ void lsDrainResolved(LsEncoder &enc, const uint32_t *
   }
 }
 
+// ---------------------------------------------------------------------------
+// LsCoder: the interval coder of the fused kernel's resolved walk, uniform on all lanes.
+//
+// Same arithmetic as ArithEncoder (arith_codec.cpp:329-582 on a 64-bit `low`), organised for the
+// fewest instructions per word on the serial path:
+//   * finished bytes leave `low` three to five at a time (when bitsLeft < -4) instead of one per
+//     writeOut: until then a carry is an ordinary add inside the 64-bit register;
+//   * emitted bytes wait big-endian in `acc` (4..7 most recent bytes), where a late carry is again
+//     a plain integer add; only a carry through all pending bytes patches stored bytes (carrySlow);
+//   * groups of 4 bytes go to the shared-memory ring and from there to HBM as 16-byte stores;
+//   * bins are counted by the parallel resolve step, not here.
+// `vtmPending` mirrors m_numBufferedBytes so that a substream that is NOT terminated reports
+// exactly the bytes the reference coder would already have handed to its OutputBitstream.
+// ---------------------------------------------------------------------------
+__device__ __noinline__ void lsCarrySlow(uint8_t *ring, uint8_t *dst, uint32_t cap, uint32_t n, uint32_t flushed,
+                                         int lane) {
+  __syncwarp();
+  if (lane == 0) {
+    while (n > 0) {
+      n--;
+      uint8_t b;
+      if (n >= flushed) {
+        b = uint8_t(ring[n & (STAGE_BYTES - 1)] + 1);
+        ring[n & (STAGE_BYTES - 1)] = b;
+      } else if (n < cap) {
+        b = uint8_t(dst[n] + 1);
+        dst[n] = b;
+      } else {
+        continue;
+      }
+      if (b != 0) break;
+    }
+  }
+  __syncwarp();
+}
+
+struct LsCoder {
+  uint64_t low, acc;
+  uint32_t range;
+  int bitsLeft;
+  uint32_t cnt;         // bytes pending in acc (0..7)
+  uint32_t n;           // bytes handed to the ring so far (multiple of 4 until finish)
+  uint32_t flushed;     // bytes of the ring already stored to HBM
+  uint32_t vtmPending;  // m_numBufferedBytes of the reference coder
+  uint32_t nbins;
+  int lazyBelow;        // bytes leave `low` when bitsLeft drops below this
+  uint8_t *ring, *dst;
+  uint32_t cap;
+  int lane;
+
+  // `terminated`: the substream ends with finish(), so nobody observes the reference's outstanding-
+  // byte count and finished bits may wait in `low` (lazy emission).  Otherwise bytes leave one per
+  // writeOut() exactly as in the reference, which keeps `vtmPending` exact.
+  __device__ __forceinline__ void start(uint8_t *ring_, uint8_t *dst_, uint32_t cap_, int lane_, bool terminated) {
+    lazyBelow = terminated ? -4 : 12;
+    low = 0;
+    acc = 0;
+    range = 510;
+    bitsLeft = 23;
+    cnt = 0;
+    n = 0;
+    flushed = 0;
+    vtmPending = 0;
+    nbins = 0;
+    ring = ring_;
+    dst = dst_;
+    cap = cap_;
+    lane = lane_;
+  }
+  __device__ __forceinline__ void flushRing(bool final) { flushed = lsFlushRing(ring, dst, cap, n, flushed, lane, final); }
+  __device__ __forceinline__ void spill4() {  // oldest 4 of the pending bytes -> ring
+    const uint32_t be = uint32_t(acc >> (8 * (cnt - 4)));
+    *reinterpret_cast<uint32_t *>(ring + (n & (STAGE_BYTES - 1))) = __byte_perm(be, 0, 0x0123);
+    n += 4;
+    cnt -= 4;
+    acc &= (1ull << (8 * cnt)) - 1ull;
+    if (n - flushed >= uint32_t(STAGE_BYTES / 2)) flushRing(false);
+  }
+  __device__ __forceinline__ void addCarry(uint32_t carry) {
+    acc += carry;
+    if (cnt < 8 && (acc >> (8 * cnt))) {  // rippled through every pending byte
+      acc &= (1ull << (8 * cnt)) - 1ull;
+      lsCarrySlow(ring, dst, cap, n, flushed, lane);
+    }
+  }
+  // k writeOut() steps at once (arith_codec.cpp:524-546), 1 <= k <= 5, cnt <= 3 on entry
+  __device__ __forceinline__ void emitBytes(uint32_t k) {
+    const int s = 24 - bitsLeft - 8 * int(k - 1);
+    const uint64_t chunk = low >> s;  // carry bit + k bytes
+    low -= chunk << s;
+    bitsLeft += 8 * int(k);
+    while (cnt + k > 8) spill4();
+    const uint32_t carry = uint32_t(chunk >> (8 * k));
+    addCarry(carry);
+    const uint64_t bytes = chunk & ((1ull << (8 * k)) - 1ull);
+    acc = (acc << (8 * k)) | bytes;
+    cnt += k;
+    // m_numBufferedBytes: a lead byte of exactly 0xFF (no carry) extends the outstanding run, anything
+    // else restarts it at 1 (exact for k == 1, i.e. whenever the count is observable)
+    const uint32_t t = min(uint32_t(__ffsll(~(long long)bytes) - 1) >> 3, k);
+    vtmPending = t == k ? (carry ? k : vtmPending + k) : t + 1u;
+    if (cnt == 8) spill4();
+  }
+  // everything the reference has written by now: back to bitsLeft >= 12
+  __device__ __forceinline__ void flushBits() {
+    if (bitsLeft < 12) emitBytes(uint32_t(19 - bitsLeft) >> 3);
+  }
+  // lazy variant used inside the walk: lets up to 16 + 24 finished bits wait in `low`
+  __device__ __forceinline__ void flushLazy() {
+    if (bitsLeft < lazyBelow) emitBytes(uint32_t(19 - bitsLeft) >> 3);
+  }
+  // resolved context-coded word: bits 0..5 LPS table row, bit 6 "bin is the LPS"
+  __device__ __forceinline__ void ctxWord(uint32_t w) {
+    const uint32_t lps = (((w & 63u) * (range >> 5)) >> 1) + 4;
+    const uint32_t rmps = range - lps;
+    const bool isLps = (w & 64u) != 0;
+    const uint32_t nr = isLps ? lps : rmps;  // rmps >= 128, so one normalisation rule serves both
+    const int sh = __clz(int(nr | 7u)) - 23;
+    low = (low + (isLps ? rmps : 0u)) << sh;
+    range = nr << sh;
+    bitsLeft -= sh;
+  }
+  __device__ __forceinline__ void epWord(uint32_t w) {  // encodeBinsEP, <= 24 bins
+    const int k = int((w >> 24) & 31u);
+    low = (low << k) + uint64_t(range) * (w & 0xFFFFFFu);
+    bitsLeft -= k;
+  }
+  // encodeBinTrm, arith_codec.cpp:460-478
+  __device__ __forceinline__ void trm(uint32_t bin) {
+    nbins++;
+    range -= 2;
+    if (bin) {
+      low = (low + range) << 7;
+      range = 256;
+      bitsLeft -= 7;
+    } else if (range < 256) {
+      low <<= 1;
+      range <<= 1;
+      bitsLeft--;
+    }
+    flushBits();
+  }
+  __device__ __forceinline__ void putAt(uint32_t at, uint32_t b) {
+    if (at >= flushed) ring[at & (STAGE_BYTES - 1)] = uint8_t(b);
+    else if (at < cap && lane == 0) dst[at] = uint8_t(b);
+  }
+  // finish() + writeByteAlignment() (arith_codec.cpp:339-357, bit_stream.cpp:152-155); returns the byte
+  // count and stores everything.  Without `terminate` only the bytes the reference coder would already
+  // have written are reported (its buffered byte and 0xFF run stay back).
+  __device__ __forceinline__ uint32_t finish(bool terminate, bool align) {
+    flushBits();
+    uint32_t tail = 0, ntail = 0;
+    uint32_t keepBack = vtmPending;
+    if (terminate) {
+      trm(1);
+      const uint32_t carry = uint32_t(low >> (32 - bitsLeft));
+      addCarry(carry);
+      low -= uint64_t(carry) << (32 - bitsLeft);
+      tail = uint32_t(low >> 8);
+      ntail = uint32_t(24 - bitsLeft);
+      keepBack = 0;
+    }
+    if (align) {
+      tail = (tail << 1) | 1u;  // stop bit
+      ntail += 1;
+    }
+    if (n + cnt - flushed > uint32_t(STAGE_BYTES) - 8u) flushRing(false);
+    for (uint32_t k = cnt; k > 0; k--) {  // pending bytes, oldest first
+      ring[n & (STAGE_BYTES - 1)] = uint8_t(acc >> (8 * (k - 1)));
+      n++;
+    }
+    cnt = 0;
+    uint32_t total = n - keepBack;
+    while (ntail >= 8) {
+      putAt(total++, (tail >> (ntail - 8)) & 0xFF);
+      ntail -= 8;
+    }
+    if (align && ntail) putAt(total++, (tail << (8 - ntail)) & 0xFF);
+    if (total < flushed) flushed = total;  // nothing beyond `total` is reported
+    n = total;
+    flushRing(true);
+    return total;
+  }
+};
+
+// The walk over resolved words on an LsCoder: a uniform branch per word (all lanes hold the same
+// word), one lazy byte-emission test; the queue is read one word ahead.
+__device__ __forceinline__ void lsWalkResolved(LsCoder &enc, const uint32_t *queue, int n) {
+  if (n <= 0) return;
+  const uint32_t *q = queue, *end = queue + n;
+  uint32_t w = *q;
+#pragma unroll 1
+  do {
+    q++;
+    const uint32_t wn = *q;  // queue[n] is readable (QUEUE_WORDS leaves a spare slot)
+    if ((w >> 29) == CABAC_CMD_CTX) enc.ctxWord(w); else enc.epWord(w);
+    enc.flushLazy();
+    w = wn;
+  } while (q != end);
+}
+
 // encodeRemAbsEP(v, rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:426-458, as one or
 // two EP command words (prefix and suffix concatenated when they fit 24 bins).  Returns the count.
 __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w0, uint32_t &w1) {
@@ -294,7 +495,8 @@ __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w
 // kTranslate: the words carry the residual kernels' compact context ids while `ctx` is the full
 // 379-entry table.
 template <bool kTranslate>
-__device__ __forceinline__ void lsResolveQueue(uint4 *ctx, uint32_t *queue, int n, int lane) {
+__device__ __forceinline__ uint32_t lsResolveQueue(uint4 *ctx, uint32_t *queue, int n, int lane) {
+  uint32_t bins = 0;  // BinCounter::getAll() of the CTX / EP words (uniform)
   for (int base = 0; base < n; base += 32) {
     const int i = base + lane;
     uint32_t w = i < n ? queue[i] : (uint32_t(CABAC_CMD_EP) << 29);
@@ -317,8 +519,10 @@ __device__ __forceinline__ void lsResolveQueue(uint4 *ctx, uint32_t *queue, int 
       __syncwarp();
     }
     if (i < n) queue[i] = w;
+    bins += __reduce_add_sync(FULL, i < n ? (isCtx ? 1u : ((w >> 29) == CABAC_CMD_EP ? (w >> 24) & 31u : 0u)) : 0u);
   }
   __syncwarp();
+  return bins;
 }
 
 

@@ -415,3 +415,58 @@ def test_pipelined_host_path_matches_single_launch(monkeypatch, oracle, layout):
         p = wl.params[i]
         eb, nb, _ = oracle.encode_residual(tus[a:b], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
         assert r2["packed"][int(ep[i]):int(ep[i + 1])].tobytes() == eb.tobytes() and nb == int(r2["num_bins"][i])
+
+
+# ---------------------------------------------------------------- configs[4]: decode sweep
+def _tiny_substreams(n_sub, seed):
+    """Many short substreams (1-3 small TUs each), mixed QP presets, built without a Python loop per TU."""
+    rng = np.random.default_rng(seed)
+    ntu = rng.integers(1, 4, n_sub)
+    tu_offsets = np.concatenate([[0], np.cumsum(ntu)]).astype(np.uint64)
+    n = int(tu_offsets[-1])
+    tus = np.zeros(n, TU_DT)
+    tus["log2_w"], tus["log2_h"] = rng.integers(2, 4, n), rng.integers(2, 4, n)
+    tus["comp_id"] = rng.integers(0, 3, n)
+    tus["flags"] = np.where(rng.random(n) < 0.15, 3, 2)  # TS allowed, 15 % transform skip
+    area = 1 << (tus["log2_w"].astype(np.int64) + tus["log2_h"].astype(np.int64))
+    tus["coeff_offset"] = np.concatenate([[0], np.cumsum(area)[:-1]]).astype(np.uint64)
+    total = int(area.sum())
+    scale = np.repeat(rng.choice([0.6, 2.5, 30.0], n), area)
+    coeffs = np.rint(rng.laplace(0, 1, total) * scale).astype(np.int32)
+    first = tus["coeff_offset"].astype(np.int64)
+    empty = np.add.reduceat(np.abs(coeffs), first) == 0
+    coeffs[first[empty]] = 1  # residual_coding is only called for coded blocks
+    params = np.zeros(n_sub, PARAMS_DT)
+    params["qp"] = rng.choice([0, 32, 51], n_sub)
+    params["init_id"] = rng.integers(0, 3, n_sub)
+    params["flags"] = SUB_DEP_QUANT | T
+    return W.Workload(tus, tu_offsets, params, coeffs, f"tiny-{n_sub}")
+
+
+@pytest.mark.parametrize("n_sub", [10_000, 40_000])
+def test_decode_sweep_many_substreams(engine, oracle, n_sub):
+    """10^4 .. 4x10^4 independent substreams of mixed QP per launch (40 000 also crosses the threshold
+    where the AUTO encoder switches to the two-stage coder): GPU decode of GPU bitstreams round-trips,
+    a sample of substreams equals the oracle byte for byte, and the oracle's bitstreams decode."""
+    wl = _tiny_substreams(n_sub, 42 + n_sub)
+    cap = wl.out_capacity(bytes_per_coeff=6.0, slack=64)
+    n0 = engine.launch_count
+    r = engine.encode_residual_packed(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap)
+    assert engine.launch_count - n0 == (7 if n_sub >= 32768 else 6)  # two-stage = one more launch
+    ep = r["entry_points"]
+    d = engine.decode_residual(r["packed"], ep, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size)
+    assert (d["coeffs"] == wl.coeffs).all() and (d["num_bins"] == r["num_bins"]).all()
+    sample = range(0, n_sub, n_sub // 50)
+    blobs = []
+    for i in sample:
+        a, b = int(wl.tu_offsets[i]), int(wl.tu_offsets[i + 1])
+        p = wl.params[i]
+        eb, nb, _ = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]),
+                                           cap=4096)
+        assert r["packed"][int(ep[i]):int(ep[i + 1])].tobytes() == eb.tobytes() and nb == int(r["num_bins"][i])
+        blobs.append(eb)
+    # decode-only leg on bitstreams produced by the CPU reference restatement
+    sub = wl.subset(list(sample))
+    d2 = engine.decode_residual(np.concatenate(blobs), offsets_of([len(b) for b in blobs]), sub.tus, sub.tu_offsets,
+                                sub.params, sub.coeffs.size)
+    assert (d2["coeffs"] == sub.coeffs).all()
