@@ -41,6 +41,8 @@ struct cabac_handle {
   size_t pipeMinCoeffs = size_t(8) << 20, pipeMinSubstreams = 512;  // below: one copy, one launch
   cudaStream_t copyStream = nullptr, compStream[kMaxChunks] = {};
   cudaEvent_t evCopy[kMaxChunks] = {}, evDone[kMaxChunks] = {}, evJoin = nullptr;
+  void *epbScratch = nullptr;  // tile counts / bases of the emulation-prevention pass, grow-only
+  size_t epbTiles = 0;
   bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
   cudaEvent_t evT0 = nullptr;
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
@@ -269,6 +271,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->cmdBuf) cudaFree(h->cmdBuf);
   if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
+  if (h->epbScratch) cudaFree(h->epbScratch);
   for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
     if (h->evCopy[i]) cudaEventDestroy(h->evCopy[i]);
     if (h->evDone[i]) cudaEventDestroy(h->evDone[i]);
@@ -441,6 +444,36 @@ int cabac_pack_dev(cabac_handle *h, const uint8_t *out, const uint64_t *out_offs
   CK(cabac::launchPack(h->stream, h->device, out, out_offsets, out_sizes, n_sub, packed, entry_points),
      "pack kernels");
   h->launches += n_sub ? 2 : 1;
+  return CABAC_OK;
+}
+
+int cabac_count_emulations_dev(cabac_handle *h, const uint8_t *data, const uint64_t *offsets, size_t n_seg,
+                               uint32_t *counts) {
+  if (!h || (n_seg && (!data || !offsets || !counts))) return badArg(h, "cabac_count_emulations_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchEmulationCount(h->stream, data, offsets, n_seg, counts), "emulation_count_kernel");
+  h->launches += n_seg ? 1 : 0;
+  return CABAC_OK;
+}
+
+int cabac_insert_emulation_prevention_dev(cabac_handle *h, const uint8_t *rbsp, size_t n, uint8_t *out,
+                                          size_t out_cap, uint64_t *out_size) {
+  if (!h || !out_size || (n && (!rbsp || !out))) return badArg(h, "cabac_insert_emulation_prevention_dev");
+  DeviceGuard g(h->device);
+  const size_t tiles = cabac::emulationTiles(n);
+  if (tiles > h->epbTiles) {
+    if (h->epbScratch) cudaFree(h->epbScratch);
+    h->epbScratch = nullptr;
+    h->epbTiles = 0;
+    const size_t cap = tiles + (tiles >> 2) + 256;
+    CK(cudaMalloc(&h->epbScratch, cap * 4 + (cap + 1) * 8 + 16), "emulation scratch");
+    h->epbTiles = cap;
+  }
+  uint64_t *tileBase = static_cast<uint64_t *>(h->epbScratch);
+  uint32_t *tileCounts = reinterpret_cast<uint32_t *>(tileBase + h->epbTiles + 1);
+  CK(cabac::launchEmulationInsert(h->stream, rbsp, n, tileCounts, tileBase, out, out_cap, out_size),
+     "emulation insert kernels");
+  h->launches += n ? 3 : 0;
   return CABAC_OK;
 }
 
@@ -904,6 +937,52 @@ int cabac_pack(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets,
   if (rc) return rc;
   D2H(packed, dPacked, total);
   D2H(entry_points, dEntry, (n_sub + 1) * 8);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
+int cabac_count_emulations(cabac_handle *h, const uint8_t *data, const uint64_t *offsets, size_t n_seg,
+                           uint32_t *counts) {
+  if (!h || (n_seg && (!data || !offsets || !counts))) return badArg(h, "cabac_count_emulations");
+  if (!n_seg) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nBytes = offsets[n_seg];
+  uint8_t *dData;
+  uint64_t *dOff;
+  uint32_t *dCnt;
+  Arena a(h);
+  a.want((void **)&dData, nBytes);
+  a.want((void **)&dOff, (n_seg + 1) * 8);
+  a.want((void **)&dCnt, n_seg * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dData, data, nBytes);
+  H2D(dOff, offsets, (n_seg + 1) * 8);
+  int rc = cabac_count_emulations_dev(h, dData, dOff, n_seg, dCnt);
+  if (rc) return rc;
+  D2H(counts, dCnt, n_seg * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
+int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp, size_t n, uint8_t *out, size_t out_cap,
+                                      uint64_t *out_size) {
+  if (!h || !out_size || (n && (!rbsp || !out))) return badArg(h, "cabac_insert_emulation_prevention");
+  DeviceGuard g(h->device);
+  const size_t worst = n + n / 2 + 1;
+  uint8_t *dIn, *dOut;
+  uint64_t *dSize;
+  Arena a(h);
+  a.want((void **)&dIn, n);
+  a.want((void **)&dOut, worst);
+  a.want((void **)&dSize, 8);
+  CK(a.commit(), "scratch alloc");
+  H2D(dIn, rbsp, n);
+  int rc = cabac_insert_emulation_prevention_dev(h, dIn, n, dOut, worst, dSize);
+  if (rc) return rc;
+  D2H(out_size, dSize, 8);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  if (*out_size > out_cap) return badArg(h, "cabac_insert_emulation_prevention: out_cap too small");
+  D2H(out, dOut, size_t(*out_size));
   CK(cudaStreamSynchronize(h->stream), "sync");
   return CABAC_OK;
 }

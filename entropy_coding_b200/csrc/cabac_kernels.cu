@@ -1415,6 +1415,125 @@ cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const ui
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------
+// K7: start-code emulation (the step right after the path).
+//   count : OutputBitstream::countStartCodeEmulations per substream (bit_stream.cpp:157-181) -
+//           the term VTM adds to every entry-point offset (EncGOP.cpp:3811-3830)
+//   insert: writeNaluContent (VTM Lib/EncoderLib/NALwrite.cpp:67-126): an emulation_prevention_
+//           three_byte before every byte <= 3 that follows two zero bytes, the zero count
+//           restarting after each insertion; a trailing zero byte gets a final 0x03.
+// Both are per-byte decisions once the zero run in front of a byte is known: in a run of L zeros
+// the sequential rule inserts before the run's bytes 2, 4, 6 ... and before a following byte <= 3
+// iff L >= 2 and L is even.  Arithmetic-coded bytes rarely hold zero runs, so each candidate byte
+// simply walks back over the zeros in front of it.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool epbBefore(const uint8_t *__restrict__ data, uint64_t s0, uint64_t i) {
+  if (data[i] > 3) return false;
+  uint64_t j = i;
+  while (j > s0 && data[j - 1] == 0) j--;
+  const uint64_t run = i - j;
+  return run >= 2 && (run & 1) == 0;
+}
+
+// one warp per segment
+__global__ void __launch_bounds__(256) emulation_count_kernel(const uint8_t *__restrict__ data,
+                                                              const uint64_t *__restrict__ offsets, size_t nSeg,
+                                                              uint32_t *__restrict__ counts) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
+  for (size_t sgm = warp; sgm < nSeg; sgm += nWarps) {
+    const uint64_t a = offsets[sgm], b = offsets[sgm + 1];
+    uint32_t c = 0;
+    // "end() - 1 prevents finding a trailing two byte sequence" is automatic: a flagged byte exists
+    for (uint64_t i = a + lane; i < b; i += 32) c += epbBefore(data, a, i) ? 1u : 0u;
+    c = __reduce_add_sync(FULL, c);
+    if (lane == 0) counts[sgm] = c;
+  }
+}
+
+constexpr int EPB_PER_THREAD = 16;
+constexpr int EPB_TILE = 256 * EPB_PER_THREAD;
+
+// pass A: insertions per 4 KiB tile
+__global__ void __launch_bounds__(256) emulation_tile_count_kernel(const uint8_t *__restrict__ data, uint64_t n,
+                                                                   uint32_t *__restrict__ tileCounts) {
+  const uint64_t base = uint64_t(blockIdx.x) * EPB_TILE + uint64_t(threadIdx.x) * EPB_PER_THREAD;
+  uint32_t c = 0;
+  for (int k = 0; k < EPB_PER_THREAD; k++)
+    if (base + k < n) c += epbBefore(data, 0, base + k) ? 1u : 0u;
+  __shared__ uint32_t ws[8];
+  c = __reduce_add_sync(FULL, c);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; w++) t += ws[w];
+    tileCounts[blockIdx.x] = t;
+  }
+}
+
+// pass B: copy with insertions; tileBase = exclusive scan of the tile counts
+__global__ void __launch_bounds__(256) emulation_insert_kernel(const uint8_t *__restrict__ data, uint64_t n,
+                                                               const uint64_t *__restrict__ tileBase,
+                                                               uint8_t *__restrict__ out, uint64_t outCap,
+                                                               uint64_t *__restrict__ outSize) {
+  const uint64_t base = uint64_t(blockIdx.x) * EPB_TILE + uint64_t(threadIdx.x) * EPB_PER_THREAD;
+  uint32_t mask = 0;
+  for (int k = 0; k < EPB_PER_THREAD; k++)
+    if (base + k < n && epbBefore(data, 0, base + k)) mask |= 1u << k;
+  const uint32_t c = __popc(mask);
+  // block-wide exclusive scan of c
+  __shared__ uint32_t ws[8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(FULL, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) ws[w] = inc;
+  __syncthreads();
+  uint32_t before = inc - c;
+  for (int k = 0; k < w; k++) before += ws[k];
+  uint64_t o = base + tileBase[blockIdx.x] + before;
+  for (int k = 0; k < EPB_PER_THREAD && base + k < n; k++) {
+    if ((mask >> k) & 1u) {
+      if (o < outCap) out[o] = 3;
+      o++;
+    }
+    if (o < outCap) out[o] = data[base + k];
+    o++;
+  }
+  if (n > 0 && base <= n - 1 && n - 1 < base + EPB_PER_THREAD) {  // the thread that owns the last byte
+    if (data[n - 1] == 0) {  // 7.4.1.1: a final 0x03 after a trailing zero byte
+      if (o < outCap) out[o] = 3;
+      o++;
+    }
+    *outSize = o;
+  }
+}
+
+cudaError_t launchEmulationCount(cudaStream_t s, const uint8_t *data, const uint64_t *offsets, size_t nSeg,
+                                 uint32_t *counts) {
+  if (nSeg == 0) return cudaSuccess;
+  emulation_count_kernel<<<costGrid(nSeg, 8), 256, 0, s>>>(data, offsets, nSeg, counts);
+  return cudaGetLastError();
+}
+
+size_t emulationTiles(size_t n) { return (n + EPB_TILE - 1) / EPB_TILE; }
+
+// tileCounts: emulationTiles(n) u32, tileBase: emulationTiles(n) + 1 u64 (device scratch)
+cudaError_t launchEmulationInsert(cudaStream_t s, const uint8_t *data, size_t n, uint32_t *tileCounts,
+                                  uint64_t *tileBase, uint8_t *out, size_t outCap, uint64_t *outSize) {
+  if (n == 0) return cudaMemsetAsync(outSize, 0, sizeof(uint64_t), s);
+  const size_t tiles = emulationTiles(n);
+  emulation_tile_count_kernel<<<unsigned(tiles), 256, 0, s>>>(data, n, tileCounts);
+  entry_points_kernel<<<1, 1024, 0, s>>>(tileCounts, nullptr, tiles, tileBase);
+  emulation_insert_kernel<<<unsigned(tiles), 256, 0, s>>>(data, n, tileBase, out, outCap, outSize);
+  return cudaGetLastError();
+}
+
 cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
                        const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints) {
   entry_points_kernel<<<1, 1024, 0, s>>>(outSizes, outOffsets, nSub, entryPoints);

@@ -54,6 +54,11 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
 // per-chunk coefficient ranges: chunk k = substreams [chunkStart[k], chunkStart[k+1]); device pointers
 cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                               const uint32_t *chunkStart, int nChunks, uint64_t *ranges);
+cudaError_t launchEmulationCount(cudaStream_t s, const uint8_t *data, const uint64_t *offsets, size_t nSeg,
+                                 uint32_t *counts);
+size_t emulationTiles(size_t n);
+cudaError_t launchEmulationInsert(cudaStream_t s, const uint8_t *data, size_t n, uint32_t *tileCounts,
+                                  uint64_t *tileBase, uint8_t *out, size_t outCap, uint64_t *outSize);
 cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
                        const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints);
 

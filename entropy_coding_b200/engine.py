@@ -229,6 +229,23 @@ class CabacEngine:
             self._check(rc, status)
         return dict(coeffs=coeffs, num_bins=bins, bits_read=bits, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
 
+    def count_emulations(self, data, offsets):
+        """countStartCodeEmulations per segment (reference bit_stream.cpp:157-181)."""
+        data, offsets = _np(data, np.uint8), _np(offsets, np.uint64)
+        n = len(offsets) - 1
+        counts = np.zeros(n, np.uint32)
+        self._check(self.lib.cabac_count_emulations(self.h, _hp(data), _hp(offsets), n, _hp(counts)))
+        return counts
+
+    def insert_emulation_prevention(self, rbsp):
+        """RBSP -> NAL payload bytes (VTM NALwrite.cpp:67-126)."""
+        rbsp = _np(rbsp, np.uint8)
+        out = np.zeros(rbsp.size + rbsp.size // 2 + 1, np.uint8)
+        size = np.zeros(1, np.uint64)
+        self._check(self.lib.cabac_insert_emulation_prevention(self.h, _hp(rbsp), rbsp.size, _hp(out), out.size,
+                                                               _hp(size)))
+        return out[:int(size[0])]
+
     def pack(self, out, out_offsets, sizes):
         out, out_offsets, sizes = _np(out, np.uint8), _np(out_offsets, np.uint64), _np(sizes, np.uint32)
         n = len(sizes)

@@ -352,6 +352,29 @@ int cabac_pack(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets,
                const uint32_t *out_sizes, size_t n_sub, uint8_t *packed,
                size_t packed_cap, uint64_t *entry_points);
 
+/* ---- start-code emulation: the step right after the path ------------------- */
+/* counts[i] = OutputBitstream::countStartCodeEmulations() of segment
+ * data[offsets[i] .. offsets[i+1]) (bit_stream.cpp:157-181): the number of
+ * emulation_prevention_three_bytes the NAL writer will insert into substream i,
+ * which VTM adds to the substream's entry-point offset (EncGOP.cpp:3811-3830). */
+int cabac_count_emulations_dev(cabac_handle *h, const uint8_t *data,
+                               const uint64_t *offsets, size_t n_seg,
+                               uint32_t *counts);
+int cabac_count_emulations(cabac_handle *h, const uint8_t *data,
+                           const uint64_t *offsets, size_t n_seg,
+                           uint32_t *counts);
+/* RBSP -> NAL payload: inserts 0x03 before every byte <= 3 that follows two
+ * zero bytes (zero count restarting after each insertion) and after a trailing
+ * zero byte - writeNaluContent, VTM Lib/EncoderLib/NALwrite.cpp:67-126.
+ * out must hold up to n + n/2 + 1 bytes; *out_size receives the length
+ * (device memory for the _dev flavour).                                      */
+int cabac_insert_emulation_prevention_dev(cabac_handle *h, const uint8_t *rbsp,
+                                          size_t n, uint8_t *out,
+                                          size_t out_cap, uint64_t *out_size);
+int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp,
+                                      size_t n, uint8_t *out, size_t out_cap,
+                                      uint64_t *out_size);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1538,3 +1538,44 @@ double orc_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets, co
   j.inSizes = inSizes;
   return run_jobs(&j, nthreads, NULL, NULL);
 }
+
+/* ---- start-code emulation ----------------------------------------- */
+/* OutputBitstream::countStartCodeEmulations, src/common/bit_stream.cpp:157-181: repeatedly find the
+ * next pair of zero bytes that is followed by another byte (the search stops one byte short of the
+ * end); when that byte is <= 3 count one emulation and continue the search AT that byte. */
+long orc_count_emulations(const uint8_t *d, long n) {
+  long cnt = 0, it = 0;
+  while (it < n) {
+    long found = it;
+    for (;;) {
+      long p = found; /* search_n(found, end - 1, 2, 0): both zeros inside [found, n - 1) */
+      while (p + 1 <= n - 2 && !(d[p] == 0 && d[p + 1] == 0)) p++;
+      if (p + 1 > n - 2) p = n - 1; /* not found: search_n returns its `last` = end - 1 */
+      found = p + 1;
+      if (found >= n) { found = n; break; }
+      found++;
+      if (d[found] <= 3) break;
+    }
+    it = found;
+    if (found != n) cnt++;
+  }
+  return cnt;
+}
+
+/* writeNaluContent, VVCSoftware_VTM/source/Lib/EncoderLib/NALwrite.cpp:67-126 (the VTM submodule;
+ * not part of the reference's src/): RBSP -> NAL payload.  Returns the output length. */
+long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out) {
+  long o = 0;
+  int zeroCount = 0;
+  for (long i = 0; i < n; i++) {
+    const uint8_t v = in[i];
+    if (zeroCount == 2 && v <= 3) {
+      out[o++] = 3;
+      zeroCount = 0;
+    }
+    if (v == 0) zeroCount++; else zeroCount = 0;
+    out[o++] = v;
+  }
+  if (zeroCount > 0) out[o++] = 3;
+  return o;
+}

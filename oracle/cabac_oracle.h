@@ -39,4 +39,6 @@ double orc_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets, co
                                 const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                 const cabac_substream_params *params, long nSub, int32_t *coeffs,
                                 int nthreads);
+long orc_count_emulations(const uint8_t *d, long n);
+long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out);
 #endif

@@ -122,6 +122,21 @@ class Checker:
         self._f("ctx_offsets")(_ptr(out))
         return out
 
+    # ---- start-code emulation ----------------------------------------------
+    def count_emulations(self, data) -> int:
+        data = np.ascontiguousarray(data, np.uint8)
+        f = self._f("count_emulations")
+        f.restype = C.c_long
+        return int(f(_ptr(data), C.c_long(data.size)))
+
+    def insert_emulation_prevention(self, data) -> np.ndarray:
+        """Oracle only (the function lives in the VTM submodule, not in the reference's src/)."""
+        data = np.ascontiguousarray(data, np.uint8)
+        out = np.zeros(data.size + data.size // 2 + 2, np.uint8)
+        f = self.lib.orc_insert_emulation_prevention
+        f.restype = C.c_long
+        return out[:int(f(_ptr(data), C.c_long(data.size), _ptr(out)))].copy()
+
     # ---- bin level --------------------------------------------------------
     def encode_bins(self, cmds, qp, init_id, flags=SUB_TERMINATE | SUB_ALIGN, ctx_in=None,
                     want_ctx=False, cap=None):

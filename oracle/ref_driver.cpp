@@ -391,4 +391,11 @@ double ref_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets,
   return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// The reference's own OutputBitstream::countStartCodeEmulations (bit_stream.cpp:157-181).
+long ref_count_emulations(const uint8_t *d, long n) {
+  OutputBitstream bs;
+  bs.getFIFO().assign(d, d + n);
+  return bs.countStartCodeEmulations();
+}
+
 }  // extern "C"
