@@ -118,10 +118,12 @@ struct LsDecoder {
     const uint32_t sr = rmps << 23;
     const bool isLps = hi >= sr;
     const uint32_t bin = mps ^ uint32_t(isLps);
-    const int nLps = __clz(int(lps | 7u)) - 23, nMps = 1 - int(rmps >> 8);
-    const int n = isLps ? nLps : nMps;
+    // one normalisation rule for both paths: rmps >= 128, so clz gives 0 / 1 for the MPS path and
+    // the renormTab value (contexts.cpp:787-789) for the LPS path
+    const uint32_t nr = isLps ? lps : rmps;
+    const int n = __clz(int(nr | 7u)) - 23;
     hi -= isLps ? sr : 0u;
-    range = (isLps ? lps : rmps) << n;
+    range = nr << n;
     shiftIn(n);
     // update
     const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);

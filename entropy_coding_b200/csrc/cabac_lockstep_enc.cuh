@@ -336,16 +336,21 @@ struct LsCoder {
     const uint64_t chunk = low >> s;  // carry bit + k bytes
     low -= chunk << s;
     bitsLeft += 8 * int(k);
-    while (cnt + k > 8) spill4();
+    if (cnt + k > 8) spill4();  // cnt <= 7, k <= 5: one spill always makes room
     const uint32_t carry = uint32_t(chunk >> (8 * k));
     addCarry(carry);
     const uint64_t bytes = chunk & ((1ull << (8 * k)) - 1ull);
     acc = (acc << (8 * k)) | bytes;
     cnt += k;
-    // m_numBufferedBytes: a lead byte of exactly 0xFF (no carry) extends the outstanding run, anything
-    // else restarts it at 1 (exact for k == 1, i.e. whenever the count is observable)
-    const uint32_t t = min(uint32_t(__ffsll(~(long long)bytes) - 1) >> 3, k);
-    vtmPending = t == k ? (carry ? k : vtmPending + k) : t + 1u;
+    if (lazyBelow == 12) {
+      // m_numBufferedBytes, only observable when the substream is not terminated: a lead byte of
+      // exactly 0xFF (no carry) extends the outstanding run, anything else restarts it at 1.  Exact
+      // whenever bytes leave one at a time; a packed EP word can release up to 3 at once, where the
+      // reference's 8-bin steps (arith_codec.cpp:401-424) may see a carry arrive one byte later -
+      // the byte stream is unaffected, only this interim count can then differ.
+      const uint32_t t = min(uint32_t(__ffsll(~(long long)bytes) - 1) >> 3, k);
+      vtmPending = t == k ? (carry ? k : vtmPending + k) : t + 1u;
+    }
     if (cnt == 8) spill4();
   }
   // everything the reference has written by now: back to bitsLeft >= 12
