@@ -32,6 +32,8 @@ struct cabac_handle {
   size_t cmdCapWords = 0;
   uint64_t *pinnedTotal = nullptr;  // page-locked landing spot for the slab size read-back
   int encoderMode = CABAC_ENCODER_AUTO;
+  bool zeroCopy = true;      // CABAC_B200_ZERO_COPY=0: always stage pinned host slabs through device memory
+  bool areaCostNext = false; // next residual encode: schedule from areas, do not read the slab (zero-copy)
   bool fusedResolve = true;  // CABAC_B200_FUSED_RESOLVE=0 selects the classic single-site drain
   // chunked pipeline of the host-pointer residual entry points: PCIe copies of the coefficient
   // slab overlap coding (one copy stream; one compute stream per chunk, so a chunk's long substreams never
@@ -146,6 +148,19 @@ cudaError_t ensureCmdSlab(cabac_handle *h, cabac::Sched &sc, size_t n_sub) {
   return cudaSuccess;
 }
 
+// Page-locked, device-mapped host memory (cudaHostAlloc / cudaHostRegister under UVA): kernels can
+// read and write it directly over PCIe.  Returns the device alias, or nullptr for any other pointer.
+void *mappedHostAlias(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return (a.type == cudaMemoryTypeHost && a.devicePointer) ? a.devicePointer : nullptr;
+}
+// Zero-copy pays when the slab is large against the per-TU PCIe round trip.
+constexpr size_t kZeroCopyMinCoeffs = size_t(4) << 20;
+
 // Streams / events / pinned landing area of the chunked pipeline (created on first use).
 cudaError_t ensurePipe(cabac_handle *h) {
   if (h->copyStream) return cudaSuccess;
@@ -251,6 +266,7 @@ cabac_handle *cabac_create(int device) {
     const int v = atoi(c);
     if (v >= 1 && v <= cabac_handle::kMaxChunks) h->pipeChunks = v;
   }
+  if (const char *c = getenv("CABAC_B200_ZERO_COPY")) h->zeroCopy = atoi(c) != 0;
   if (const char *c = getenv("CABAC_B200_FUSED_RESOLVE")) h->fusedResolve = atoi(c) != 0;
   if (const char *c = getenv("CABAC_B200_TRACE")) h->trace = atoi(c) != 0;
   if (const char *c = getenv("CABAC_B200_PIPE_MIN_COEFFS")) h->pipeMinCoeffs = size_t(atoll(c));
@@ -382,7 +398,11 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, nullptr), "encode prepare kernels");
+  const bool areaCost = h->areaCostNext;
+  h->areaCostNext = false;
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, areaCost ? nullptr : coeffs, nullptr,
+                                params),
+     "encode prepare kernels");
   // Few long substreams: one warp per substream, fused.  Many substreams: the two-stage coder,
   // whose interval stage runs one substream per thread.
   sc.twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
@@ -709,7 +729,11 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, n_sub * sizeof(*params));
-  a.want((void **)&dCoeffs, n_coeffs * 4);
+  const bool twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                        (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
+  const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && n_coeffs >= kZeroCopyMinCoeffs)
+                                ? static_cast<const int32_t *>(mappedHostAlias(coeffs)) : nullptr;
+  a.want((void **)&dCoeffs, zcCoeffs ? 0 : n_coeffs * 4);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
   a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dOut, outCap);
@@ -725,9 +749,15 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
   int rc;
-  const bool twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
-                        (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
-  if (h->pipeChunks > 1 && !twoStage && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+  if (zcCoeffs) {
+    // ---- zero-copy: the kernel reads every TU block straight from pinned host memory (each
+    // coefficient crosses PCIe exactly once, under the coding of the other warps); the schedule comes
+    // from block areas and QPs instead of a pass over the slab ----
+    h->areaCostNext = true;
+    rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, zcCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
+                                   dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+    if (rc) return rc;
+  } else if (h->pipeChunks > 1 && !twoStage && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
     // ---- chunked pipeline: the slab crosses PCIe chunk by chunk while earlier chunks are coded ----
     CK(ensurePipe(h), "pipeline streams");
     uint64_t *hr = h->pinnedRanges;
@@ -825,7 +855,9 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, n_sub * sizeof(*params));
-  a.want((void **)&dCoeffs, n_coeffs * 4);
+  int32_t *zcCandidate = (h->zeroCopy && n_coeffs >= kZeroCopyMinCoeffs)
+                             ? static_cast<int32_t *>(mappedHostAlias(coeffs)) : nullptr;
+  a.want((void **)&dCoeffs, n_coeffs * 4);  // kept even for a zero-copy candidate: the coverage check may refuse
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
   a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dIn, nIn);
@@ -841,8 +873,33 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
   H2D(dIn, in, nIn);
   // positions no descriptor covers come back as zero
-  CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
-  if (h->pipeChunks > 1 && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+  // ---- zero-copy: when the descriptors tile the whole slab (their areas sum to n_coeffs over the
+  // range [0, n_coeffs)), every position is written by the kernel itself, so it can store straight into
+  // the caller's pinned host slab: no device slab, no memset, no D2H copy ----
+  int32_t *zcCoeffs = nullptr;
+  if (zcCandidate) {
+    CK(ensurePipe(h), "pipeline streams");  // owns the pinned landing area used below
+    uint64_t *hr = h->pinnedRanges;
+    uint32_t *hStart = reinterpret_cast<uint32_t *>(hr + 2 * cabac_handle::kMaxChunks);
+    hStart[0] = 0;
+    hStart[1] = uint32_t(n_sub);
+    hr[0] = ~0ull;
+    hr[1] = 0;
+    hr[2] = 0;
+    H2D(dRanges, hr, 3 * sizeof(uint64_t));
+    H2D(dChunkStart, hStart, 2 * sizeof(uint32_t));
+    CK(cabac::launchCoeffRanges(h->stream, dTus, dTuOff, dChunkStart, 1, dRanges, dRanges + 2), "coeff_range_kernel");
+    h->launches += 1;
+    D2H(hr, dRanges, 3 * sizeof(uint64_t));
+    CK(cudaStreamSynchronize(h->stream), "sync");
+    if (hr[0] == 0 && hr[1] == n_coeffs && hr[2] == n_coeffs) zcCoeffs = zcCandidate;
+  }
+  if (zcCoeffs) {
+    int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, zcCoeffs,
+                                       dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
+    if (rc) return rc;
+  } else if (h->pipeChunks > 1 && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
     // ---- chunked pipeline: finished coefficient ranges leave over PCIe while later chunks decode ----
     CK(ensurePipe(h), "pipeline streams");
     uint64_t *hr = h->pinnedRanges;
@@ -895,6 +952,7 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
       traceChunks(h, "decode_residual", K, false);
     }
   } else {
+    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
     int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
                                        dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;

@@ -78,7 +78,8 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          const int32_t *__restrict__ coeffs, size_t n,
                                                          uint32_t *__restrict__ cost,
                                                          uint32_t *__restrict__ capWords,
-                                                         const uint64_t *__restrict__ rawOffsets) {
+                                                         const uint64_t *__restrict__ rawOffsets,
+                                                         const cabac_substream_params *__restrict__ params) {
   const int lane = threadIdx.x & 31;
   const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
@@ -94,6 +95,16 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
       const int32_t *src = coeffs + d.coeff_offset;
       const int total = 1 << (d.log2_w + d.log2_h);
       cap += tuCmdCapacity(d);
+      if (!coeffs) {
+        // zero-copy launches (the slab stays in pinned host memory): no pass over the coefficients;
+        // estimate from the block area, the slice QP (bins per coefficient fall ~4x per 20 QP steps)
+        // and transform skip (no frequency decay: ~1.5x the bins)
+        if (lane == 0) {
+          const int q = 70 - int(params ? params[s].qp : 32);
+          c += (uint32_t(total) * uint32_t(q * q) >> 6) * ((d.flags & CABAC_TU_TS) ? 3u : 2u);
+        }
+        continue;
+      }
       if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
         for (int i = lane * 4; i < total; i += 128) {
           const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
@@ -1303,10 +1314,11 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
 // slab offsets (exclusive scan; cmdOffsets[nSub] = words the slab must hold).
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
-                                const uint64_t *rawOffsets) {
+                                const uint64_t *rawOffsets, const cabac_substream_params *params) {
   (void)device;
   if (nSub == 0) return cudaSuccess;
-  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets);
+  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
+                                                     params);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
@@ -1386,15 +1398,21 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
 __global__ void __launch_bounds__(256) coeff_range_kernel(const cabac_tu_desc *__restrict__ tus,
                                                           const uint64_t *__restrict__ tuOffsets,
                                                           const uint32_t *__restrict__ chunkStart,
-                                                          unsigned long long *__restrict__ ranges) {
+                                                          unsigned long long *__restrict__ ranges,
+                                                          unsigned long long *__restrict__ areaSums) {
   const int k = blockIdx.y;
   const uint64_t t0 = tuOffsets[chunkStart[k]], t1 = tuOffsets[chunkStart[k + 1]];
-  unsigned long long lo = ~0ull, hi = 0;
+  unsigned long long lo = ~0ull, hi = 0, sum = 0;
   for (uint64_t t = t0 + blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; t < t1; t += uint64_t(gridDim.x) * blockDim.x) {
     const cabac_tu_desc d = tus[t];
     const unsigned long long a = d.coeff_offset, b = a + (1ull << (d.log2_w + d.log2_h));
     lo = a < lo ? a : lo;
     hi = b > hi ? b : hi;
+    sum += b - a;
+  }
+  if (areaSums) {
+    sum = __reduce_add_sync(FULL, uint32_t(sum)) + (uint64_t(__reduce_add_sync(FULL, uint32_t(sum >> 32))) << 32);
+    if ((threadIdx.x & 31) == 0 && sum) atomicAdd(areaSums + k, sum);
   }
   for (int o = 16; o > 0; o >>= 1) {
     const unsigned long long l2 = __shfl_xor_sync(FULL, lo, o), h2 = __shfl_xor_sync(FULL, hi, o);
@@ -1408,10 +1426,11 @@ __global__ void __launch_bounds__(256) coeff_range_kernel(const cabac_tu_desc *_
 }
 
 cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
-                              const uint32_t *chunkStart, int nChunks, uint64_t *ranges) {
+                              const uint32_t *chunkStart, int nChunks, uint64_t *ranges, uint64_t *areaSums) {
   if (nChunks <= 0) return cudaSuccess;
   coeff_range_kernel<<<dim3(64, nChunks), 256, 0, s>>>(tus, tuOffsets, chunkStart,
-                                                        reinterpret_cast<unsigned long long *>(ranges));
+                                                        reinterpret_cast<unsigned long long *>(ranges),
+                                                        reinterpret_cast<unsigned long long *>(areaSums));
   return cudaGetLastError();
 }
 

@@ -34,7 +34,7 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status);
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
-                                const uint64_t *rawOffsets);
+                                const uint64_t *rawOffsets, const cabac_substream_params *params = nullptr);
 cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, const uint32_t *rawCmds,
                                const uint64_t *rawOffsets, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
@@ -53,7 +53,8 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  cabac_ctx_model *ctxOut, uint32_t *status);
 // per-chunk coefficient ranges: chunk k = substreams [chunkStart[k], chunkStart[k+1]); device pointers
 cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
-                              const uint32_t *chunkStart, int nChunks, uint64_t *ranges);
+                              const uint32_t *chunkStart, int nChunks, uint64_t *ranges,
+                              uint64_t *areaSums = nullptr);
 cudaError_t launchEmulationCount(cudaStream_t s, const uint8_t *data, const uint64_t *offsets, size_t nSeg,
                                  uint32_t *counts);
 size_t emulationTiles(size_t n);
