@@ -362,7 +362,7 @@ def run_e2e(args, r):
     return {"value": r["all_bins"] * args.steps / float(tt) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(tt) / args.steps,
             "gpu_launches": int(eng.launch_count - launches0),
-            "api": "cabac_encode_residual_packed + cabac_decode_residual (host pointers, pinned)"}
+            "api": "cabac_encode_residual_packed + cabac_decode_residual (host pointers; pinned slabs are read / written by the kernels directly over PCIe)"}
 
 
 def run_cpu_baseline(args, r):
@@ -433,5 +433,17 @@ def main():
     print(json.dumps(line), flush=True)
 
 
+def _shutdown():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    finally:
+        _shutdown()

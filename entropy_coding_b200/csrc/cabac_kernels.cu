@@ -329,6 +329,47 @@ __device__ inline bool loadTile(int16_t *tile, const int32_t *__restrict__ src, 
   return __all_sync(FULL, ok);
 }
 
+// Asynchronous variant for the fused encoder: the coded part (<= 32 x 32) of the NEXT block is
+// fetched with cp.async into a raw int32 staging tile while the current block is coded, so the
+// HBM - or, for zero-copy launches, PCIe - round trip of a block never sits on the warp's serial path.
+__device__ __forceinline__ void prefetchBlock(int32_t *raw, const int32_t *__restrict__ src, const cabac_tu_desc &d,
+                                              int lane) {
+  const int log2w = d.log2_w, log2tw = min(int(d.log2_w), 5), log2th = min(int(d.log2_h), 5);
+  const uint32_t dst = uint32_t(__cvta_generic_to_shared(raw));
+  if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+    const int total = 1 << (log2tw + log2th - 2);  // 16-byte units
+    for (int u = lane; u < total; u += 32) {
+      const int y = u >> (log2tw - 2), x = (u & ((1 << (log2tw - 2)) - 1)) << 2;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + uint32_t(u) * 16u),
+                   "l"(src + (size_t(y) << log2w) + x)
+                   : "memory");
+    }
+  } else {
+    const int total = 1 << (log2tw + log2th);
+    for (int i = lane; i < total; i += 32) {
+      const int y = i >> log2tw, x = i & ((1 << log2tw) - 1);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + uint32_t(i) * 4u),
+                   "l"(src + (size_t(y) << log2w) + x)
+                   : "memory");
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// waits for the staged block and narrows it into the int16 tile; false when a level is out of range
+__device__ __forceinline__ bool takeBlock(int16_t *tile, const int32_t *raw, const TuGeom &g, int lane) {
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+  bool ok = true;
+  const int n = g.tw * g.th;
+  for (int i = lane * 4; i < n; i += 128) {
+    const int4 v = *reinterpret_cast<const int4 *>(raw + i);
+    ok &= (v.x == int16_t(v.x)) & (v.y == int16_t(v.y)) & (v.z == int16_t(v.z)) & (v.w == int16_t(v.w));
+    *reinterpret_cast<short4 *>(tile + i) = make_short4(short(v.x), short(v.y), short(v.z), short(v.w));
+  }
+  __syncwarp();
+  return __all_sync(FULL, ok);
+}
+
 // One regular-residual coefficient group, binarised by lanes 0..cgSize-1
 // (residual_coding_subblock, cabac_writer.cpp:2724-2872).  Returns the number
 // of command words written to `queue`.  All lanes must call.
@@ -591,6 +632,7 @@ __device__ __forceinline__ int produceTsCG(uint32_t *q, const int16_t *tile, con
 struct __align__(16) FusedEncWarpSmem {
   uint4 ctx[RCTX];
   uint8_t ring[STAGE_BYTES];
+  int32_t raw[32 * 32];  // cp.async landing tile of the next block
   int16_t tile[32 * 32];
   uint32_t queue[QUEUE_WORDS];
   uint16_t cgMask[64];
@@ -634,6 +676,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
     uint64_t t = tuOffsets[sub];
     const uint64_t t1 = tuOffsets[sub + 1];
+    if (t < t1) prefetchBlock(sm.raw, coeffs + tus[t].coeff_offset, tus[t], lane);
 
     // per-block producer state
     bool inTu = false, tsPath = false, bdpcm = false;
@@ -655,7 +698,11 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
         bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
         res = ts ? CABAC_TUR_TS : 0;
-        if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        if (!takeBlock(sm.tile, sm.raw, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        if (t + 1 < t1) {
+          const cabac_tu_desc dn = tus[t + 1];
+          prefetchBlock(sm.raw, coeffs + dn.coeff_offset, dn, lane);
+        }
         // ---- pre-scan: non-zero mask per coefficient group, last position ----
         lastCG = -1;
         const int cgSize = 1 << g.log2cg;
