@@ -411,6 +411,18 @@ def main():
         # 4 warp-instruction issue slots per SM per clock
         bound = 148 * 4 * sm_mhz * 1e6 / ipb / 1e6
         issue.update({"mbins_s_bound": bound, "frac": issue["mbins_s_achieved"] / bound})
+    per_kernel = {}
+    for k in ("encode_residual_kernel", "decode_residual_kernel"):
+        f = facts.get(k, {})
+        if f.get("warp_instr_per_bin"):
+            b = 148 * 4 * sm_mhz * 1e6 / f["warp_instr_per_bin"] / 1e6
+            a = r["enc_bins"] / (tk[k] * 1e-3) / 1e6
+            per_kernel[k] = {"warp_instr_per_bin": f["warp_instr_per_bin"], "mbins_s_achieved": a, "mbins_s_bound": b,
+                             "frac": a / b, "issue_active_pct_ncu": f.get("issue_active_pct"),
+                             "shared_bank_conflicts_ncu": f.get("shared_bank_conflicts"),
+                             "dram_bytes_ncu": f.get("dram_bytes_per_launch")}
+    issue["kernels"] = per_kernel
+    issue["source"] = "instructions per bin, issue activity, bank conflicts and DRAM bytes: profiles/kernel_facts.json (ncu)"
     line = {
         "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
