@@ -329,6 +329,12 @@ __device__ inline bool loadTile(int16_t *tile, const int32_t *__restrict__ src, 
   return __all_sync(FULL, ok);
 }
 
+// Blocks of one shape and component share their geometry: consecutive descriptors usually do.
+__device__ __forceinline__ uint32_t geomKey(const cabac_tu_desc &d) {
+  return uint32_t(d.log2_w) | (uint32_t(d.log2_h) << 8) | (uint32_t(d.comp_id) << 16) |
+         (uint32_t(d.flags & CABAC_TU_SBT_ZEROOUT) << 24);
+}
+
 // Asynchronous variant for the fused encoder: the coded part (<= 32 x 32) of the NEXT block is
 // fetched with cp.async into a raw int32 staging tile while the current block is coded, so the
 // HBM - or, for zero-copy launches, PCIe - round trip of a block never sits on the warp's serial path.
@@ -682,6 +688,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     bool inTu = false, tsPath = false, bdpcm = false;
     cabac_tu_desc d;
     TuGeom g;
+    uint32_t gKey = ~0u;
     uint32_t res = 0;
     int lastCG = 0, scanPosLast = 0, s = 0, state = 0, remRegBins = 0, remBinsTS = 0;
     uint64_t sigGroups = 0;
@@ -693,7 +700,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       if (!inTu) {
         if (t == t1) break;
         d = tus[t];
-        g = makeGeom(d);
+        if (geomKey(d) != gKey) {
+          g = makeGeom(d);
+          gKey = geomKey(d);
+        }
         const bool ts = (d.flags & CABAC_TU_TS) != 0;
         tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
         bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
@@ -860,6 +870,7 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
     bool inTu = false, tsPath = false, bdpcm = false;
     cabac_tu_desc d;
     TuGeom g;
+    uint32_t gKey = ~0u;
     uint32_t res = 0;
     int lastCG = 0, scanPosLast = 0, s = 0, state = 0, remRegBins = 0, remBinsTS = 0;
     uint64_t sigGroups = 0;
@@ -921,7 +932,10 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
           break;
         }
         d = tus[t];
-        g = makeGeom(d);
+        if (geomKey(d) != gKey) {
+          g = makeGeom(d);
+          gKey = geomKey(d);
+        }
         const bool ts = (d.flags & CABAC_TU_TS) != 0;
         tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
         bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
