@@ -428,14 +428,16 @@ int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds, const uint64_
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  sc.twoStage = true;
+  // Few long substreams (slices, frames): one warp each, fused.  Many: stage P + stage D (one thread each).
+  sc.twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
   CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, cmd_offsets),
      "encode prepare kernels");
-  CK(ensureCmdSlab(h, sc, n_sub), "command slab");
+  if (sc.twoStage) CK(ensureCmdSlab(h, sc, n_sub), "command slab");
   CK(cabac::launchEncodeStream(h->stream, h->device, sc, cmds, cmd_offsets, tus, tu_offsets, params, n_sub, coeffs,
                                ctx_in, out, out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
      "encode_stream kernels");
-  h->launches += 5;
+  h->launches += sc.twoStage ? 5 : 4;
   return CABAC_OK;
 }
 

@@ -300,6 +300,7 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
 template <int kNumCtx>
 struct __align__(16) EncWarpSmemT {
   uint4 ctx[kNumCtx];
+  uint8_t ring[STAGE_BYTES];  // output staging of the fused variant
   int16_t tile[32 * 32];
   uint32_t queue[QUEUE_WORDS];
   uint16_t cgMask[64];  // nonzero mask of every coefficient group, by scan index
@@ -835,7 +836,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
 // kStream = true : the substream is a recorded command stream (cabac_encode_stream): BinEncIf calls
 //                  with raw context ids, and CABAC_CMD_TU markers that each code the next TU of the
 //                  substream's list (CABACWriter::residual_coding in the middle of other syntax).
-template <bool kStream>
+// kFused   = true : the resolved words of every batch are walked at once by the warp's own LsCoder
+//                   (few, long substreams: slices, frames) and the bytes leave through the ring;
+//                   cmds / cmdOffsets / cmdCounts are unused.
+template <bool kStream, bool kFused>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict__ rawOffsets,
                const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
@@ -844,7 +848,9 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
                uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets,
                uint32_t *__restrict__ cmdCounts, uint8_t *__restrict__ tuFlags,
                cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
-               const uint32_t *__restrict__ order, uint32_t *cursor) {
+               const uint32_t *__restrict__ order, uint32_t *cursor, uint8_t *__restrict__ out,
+               const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
+               uint32_t *__restrict__ numBins) {
   typedef EncWarpSmemT<kStream ? CABAC_NUM_CTX : RCTX> Smem;
   __shared__ Smem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -858,9 +864,13 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
       loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
     uint64_t rc = kStream ? rawOffsets[sub] : 0;
     const uint64_t rc1 = kStream ? rawOffsets[sub + 1] : 0;
-    uint32_t *cmdBase = cmds + cmdOffsets[sub];  // this substream's resolved command words
+    uint32_t *cmdBase = kFused ? nullptr : cmds + cmdOffsets[sub];  // this substream's resolved command words
     uint32_t cmdN = 0;
     uint32_t st = 0;
+    LsCoder coder;
+    if constexpr (kFused)
+      coder.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane,
+               (p.flags & CABAC_SUB_TERMINATE) != 0);
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
     uint64_t t = tus ? tuOffsets[sub] : 0;
@@ -917,9 +927,14 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
             st = __reduce_or_sync(FULL, st);
             rc += uint64_t(nRaw);
             __syncwarp();
-            lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
-            for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
-            cmdN += uint32_t(nq);
+            const uint32_t nb = lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+            if constexpr (kFused) {
+              coder.nbins += nb;
+              lsWalkResolvedAny(coder, sm.queue, nq);
+            } else {
+              for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
+              cmdN += uint32_t(nq);
+            }
             __syncwarp();
             continue;
           }
@@ -1024,12 +1039,25 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
         inTu = false;
       }
       __syncwarp();
-      lsResolveQueue<kStream>(sm.ctx, sm.queue, nq, lane);  // the TU producers emit compact context ids
-      for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
-      cmdN += uint32_t(nq);
+      const uint32_t nb = lsResolveQueue<kStream>(sm.ctx, sm.queue, nq, lane);  // the TU producers emit compact context ids
+      if constexpr (kFused) {
+        coder.nbins += nb;
+        lsWalkResolved(coder, sm.queue, nq);
+      } else {
+        for (int i = lane; i < nq; i += 32) cmdBase[cmdN + i] = sm.queue[i];
+        cmdN += uint32_t(nq);
+      }
       __syncwarp();
     }
-    if (lane == 0) {
+    if constexpr (kFused) {
+      const uint32_t total = coder.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+      if (lane == 0) {
+        if (total > coder.cap) st |= CABAC_SS_OUT_OVERFLOW;
+        outSizes[sub] = total;
+        if (numBins) numBins[sub] = coder.nbins;
+        status[sub] = st;
+      }
+    } else if (lane == 0) {
       cmdCounts[sub] = cmdN;
       status[sub] = st;
     }
@@ -1404,9 +1432,9 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
           status ? status : sc.statusScratch, sc.order, sc.cursor);
     return cudaGetLastError();
   }
-  produce_kernel<false><<<persistentGrid(produce_kernel<false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+  produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       nullptr, nullptr, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor);
+      status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;
@@ -1424,9 +1452,15 @@ cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, cons
                                uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
                                uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  produce_kernel<true><<<persistentGrid(produce_kernel<true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+  if (!sc.twoStage) {  // few, long substreams: one warp each, bytes straight out of the producer kernel
+    produce_kernel<true, true><<<persistentGrid(produce_kernel<true, true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+        rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, tuFlags, ctxOut,
+        status ? status : sc.statusScratch, sc.order, sc.cursor, out, outOffsets, outSizes, numBins);
+    return cudaGetLastError();
+  }
+  produce_kernel<true, false><<<persistentGrid(produce_kernel<true, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts,
-      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.order, sc.cursor);
+      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;

@@ -451,6 +451,32 @@ __device__ __forceinline__ void lsWalkResolved(LsCoder &enc, const uint32_t *que
   } while (q != end);
 }
 
+// The walk for recorded streams: besides resolved CTX / EP words they carry the rare kinds of
+// BinEncIf (terminating bins, align()).
+__device__ __forceinline__ void lsWalkResolvedAny(LsCoder &enc, const uint32_t *queue, int n) {
+  if (n <= 0) return;
+  const uint32_t *q = queue, *end = queue + n;
+  uint32_t w = *q;
+#pragma unroll 1
+  do {
+    q++;
+    const uint32_t wn = *q;
+    const uint32_t kind = w >> 29;
+    if (kind == CABAC_CMD_CTX) {
+      enc.ctxWord(w);
+    } else if (kind == CABAC_CMD_EP) {
+      enc.epWord(w);
+    } else if (kind == CABAC_CMD_TRM) {
+      enc.flushBits();  // encodeBinTrm works on the eager state (arith_codec.cpp:460-478)
+      enc.trm(w & 1u);
+    } else {  // CABAC_CMD_ALIGN: align(), arith_codec.cpp:480
+      enc.range = 256;
+    }
+    enc.flushLazy();
+    w = wn;
+  } while (q != end);
+}
+
 // encodeRemAbsEP(v, rice, cutoff = 5, maxLog2TrDynamicRange = 15), arith_codec.cpp:426-458, as one or
 // two EP command words (prefix and suffix concatenated when they fit 24 bins).  Returns the count.
 __device__ __forceinline__ int lsRemWords(uint32_t v, uint32_t rice, uint32_t &w0, uint32_t &w1) {

@@ -14,6 +14,14 @@ from helpers import T, ctx_pairs, expected_values, mixed_stream, random_cmds, su
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=[0, 2], ids=["auto_fused", "two_stage"])
+def stream_mode(request, engine):
+    """Recorded streams run on the fused lockstep coder (AUTO below 32 768 substreams) and on stage P + stage D."""
+    engine.set_encoder_mode(request.param)
+    yield request.param
+    engine.set_encoder_mode(0)
+
+
 def offsets_of(lengths, align=1):
     lengths = (np.asarray(lengths, np.int64) + align - 1) // align * align
     return np.concatenate([[0], np.cumsum(lengths)]).astype(np.uint64)
@@ -43,6 +51,7 @@ def test_ctx_init_matches_golden_and_oracle(engine, oracle):
     assert (engine.ctx_rates() == g["rates"]).all()
 
 
+@pytest.mark.usefixtures("stream_mode")
 # ---------------------------------------------------------------- (1) bin level
 def test_kats_on_gpu(engine):
     g = load_golden("kat")
@@ -62,6 +71,7 @@ def test_kats_on_gpu(engine):
     assert not r["status"].any()
 
 
+@pytest.mark.usefixtures("stream_mode")
 def test_bins_golden_on_gpu(engine):
     g = load_golden("bins")
     n = int(g["n"][0])
@@ -89,6 +99,7 @@ def test_bins_golden_on_gpu(engine):
         assert (ctx_pairs(d["ctx_out"][i]) == g[f"ctx{i}"]).all()
 
 
+@pytest.mark.usefixtures("stream_mode")
 def test_bins_random_vs_oracle(engine, oracle):
     rng = np.random.default_rng(2024)
     n = 300
@@ -114,6 +125,7 @@ def test_bins_random_vs_oracle(engine, oracle):
     assert (d["bits_read"] <= 8 * r["sizes"]).all()
 
 
+@pytest.mark.usefixtures("stream_mode")
 def test_bins_ctx_handoff(engine, oracle):
     """Encoding in two launches with exported/imported contexts (WPP-style hand-off) keeps the models exact."""
     rng = np.random.default_rng(5)
@@ -130,6 +142,7 @@ def test_bins_ctx_handoff(engine, oracle):
     assert r2["out"][:r2["sizes"][0]].tobytes() == eb.tobytes() and (r2["ctx_out"][0] == ectx2).all()
 
 
+@pytest.mark.usefixtures("stream_mode")
 def test_long_ff_run_and_overflow(engine, oracle):
     """Carry propagation through a long outstanding-byte run (numBufferedBytes), and the overflow status."""
     cmds = np.asarray([mk_ctx(246, 1)] * 300 + [mk_ep(1, 1)] * 3000 + [mk_trm(0)], np.uint32)
@@ -248,6 +261,7 @@ def test_residual_encoder_variants(engine, oracle, mode, seed, flags, kw):
         engine.set_encoder_mode(0)
 
 
+@pytest.mark.usefixtures("stream_mode")
 @pytest.mark.parametrize("seed,flags", [(401, T | SUB_DEP_QUANT), (402, T | SUB_SIGN_HIDING), (403, SUB_DEP_QUANT)])
 def test_stream_mixed_vs_oracle(engine, oracle, seed, flags):
     """cabac_encode_stream: recorded BinEncIf calls interleaved with residual_coding() markers."""
