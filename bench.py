@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=64, help="frames per GPU (64 = the BASELINE config)")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--substreams", default="ctu", choices=["ctu", "frame"],
+                    help="ctu: one substream per 128x128 CTU (the bench line); frame: one per frame (64 long slices, latency-bound)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-frames", type=int, default=16)
@@ -152,7 +154,7 @@ def run_reference_arm(args):
     chk, kind = cpu_checker()
     threads = host_threads()
     frames = max(1, min(args.cpu_sample_frames, args.frames))
-    wl = W.frames_as_ctu_substreams(frames, args.width, args.height, seed0=1000)
+    wl = W.frames_as_ctu_substreams(frames, args.width, args.height, seed0=1000, per_frame=args.substreams == "frame")
     for _ in range(max(1, args.warmup)):
         cpu_pass(chk, wl, threads)
     t_enc = t_dec = 0.0
@@ -226,7 +228,8 @@ def run_b200_arm(args):
         torch.cuda.synchronize()
 
     # ---- workload: this rank's 64 frames (weak scaling: different frames per rank) ----
-    wl = W.frames_as_ctu_substreams(args.frames, args.width, args.height, seed0=1000 + rank * args.frames)
+    wl = W.frames_as_ctu_substreams(args.frames, args.width, args.height, seed0=1000 + rank * args.frames,
+                                    per_frame=args.substreams == "frame")
     n_sub, n_tu, n_co = wl.n_sub, len(wl.tus), int(wl.coeffs.size)
     cap = wl.out_capacity()
     eng = E.CabacEngine(local_rank)
@@ -427,7 +430,9 @@ def main():
         "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_gpu": args.frames, "substreams_per_gpu": r["n_sub"],
+        "config": {"workload": WORKLOAD if args.substreams == "ctu" else WORKLOAD.replace(
+                       "one substream per 128x128 CTU (8640 substreams/GPU)", "one substream per frame"),
+                   "frames_per_gpu": args.frames, "substreams_per_gpu": r["n_sub"],
                    "tus_per_gpu": r["n_tu"], "coeff_positions_per_gpu": r["n_co"],
                    "bins_per_step_per_gpu": 2 * r["enc_bins"], "bitstream_bytes_per_gpu": r["out_bytes"],
                    "l2": "inputs larger than L2 (coefficient slab %.0f MB per pass)" % (4 * r["n_co"] / 1e6),

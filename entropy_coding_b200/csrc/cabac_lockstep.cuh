@@ -287,6 +287,10 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
   int remRegBins = regBinLimit(g);
   uint64_t sigGroups = 0;
   const int lastCG = scanPosLast >> g.log2cg;
+  // context-set bases of this block, fixed for all its bins: gt1 | par << 10 | gt2 << 20
+  const int sigBase0 = sigFlagBase(g.ch, 0);
+  const uint32_t gtPack = uint32_t(gtxFlagBase(g.ch + 2)) | (uint32_t(parFlagBase(g.ch)) << 10) |
+                          (uint32_t(gtxFlagBase(g.ch)) << 20);
   for (int s = lastCG; s >= 0; s--) {
     const uint32_t c = __ldg(&g_rom.cgScan[g.lwig][g.lhig][s]);
     const int cgx = c & 15, cgy = c >> 4, cgPos = cgy * g.wig + cgx;
@@ -340,17 +344,18 @@ __device__ __forceinline__ uint32_t lsResidualRegular(LsDecoder &dec, uint4 *ctx
       bool sig = nzMask == 0 && p == inferSigPos;
       const int gtxOfs = (isLast && p == P0) ? 0 : int((info >> 4) & 31u);
       if (!sig) {
-        sig = dec.decodeBin(ctx + sigFlagBase(g.ch, max(0, state - 1)) + int(info & 15u)) != 0;
+        sig = dec.decodeBin(ctx + sigBase0 + 20 * max(0, state - 1) + int(info & 15u)) != 0;
         remRegBins--;
       }
       int val = 0;
       if (sig) {
         // gt1, then par and gt2 when gt1 is set: one decodeBin site, three context sets
         uint32_t gtBits = 0;  // bit 0 gt1, bit 1 par, bit 2 gt2
+        uint32_t gp = gtPack;
 #pragma unroll 1
         for (int k = 0; k < 3; k++) {
-          const int base = k == 0 ? gtxFlagBase(g.ch + 2) : (k == 1 ? parFlagBase(g.ch) : gtxFlagBase(g.ch));
-          gtBits |= dec.decodeBin(ctx + base + gtxOfs) << k;
+          gtBits |= dec.decodeBin(ctx + (gp & 1023u) + gtxOfs) << k;
+          gp >>= 10;
           remRegBins--;
           if (!gtBits) break;
         }
