@@ -26,6 +26,7 @@
 
 #define CABAC_CTX_TABLE_QUALIFIER static const
 #include "ctx_tables.inc"
+#include "frac_bits.inc"
 
 /* ------------------------------------------------------------------------- */
 /* context-set offsets: positional in src/common/contexts.cpp:77-770          */
@@ -180,6 +181,10 @@ typedef struct {
   uint32_t low, range, bufferedByte;
   int32_t numBuffered, bitsLeft;
   uint32_t nbins;
+  /* estimate mode = the reference's BitEstimator_Std behind the same BinEncIf calls
+   * (arith_codec.cpp:603-711): no interval, no bytes; 15-bit fixed-point bits are summed */
+  int est;
+  uint64_t estBits;
 } Enc;
 
 /* start, arith_codec.cpp:329-337 */
@@ -220,6 +225,12 @@ static void enc_write_out(Enc *e) {
 static void enc_bin(Enc *e, CtxTab *c, unsigned bin, unsigned ctxId) {
   cabac_ctx_model *m = &c->m[ctxId];
   e->nbins++;
+  if (e->est) { /* estFracBitsUpdate, contexts.cpp:922-929: table[state()][bin], then update */
+    const unsigned q = ((unsigned)m->state0 + m->state1) >> 8;
+    e->estBits += CABAC_FRAC_BITS[2 * q + (bin & 1)];
+    mdl_update(m, c->rate[ctxId], bin);
+    return;
+  }
   const unsigned lps = mdl_lps(m, e->range);
   e->range -= lps;
   if (bin != mdl_mps(m)) {
@@ -242,6 +253,10 @@ static void enc_bin(Enc *e, CtxTab *c, unsigned bin, unsigned ctxId) {
  * same arithmetic with range == 256 and the same 8-bin chunking) */
 static void enc_bins_ep(Enc *e, unsigned bins, unsigned n) {
   e->nbins += n;
+  if (e->est) { /* estFracBitsEP(numBins) = numBins << SCALE_BITS, contexts.cpp:880-884 */
+    e->estBits += (uint64_t)n << 15;
+    return;
+  }
   /* the aligned variant masks every chunk to its width (:513-514); only visible
    * for out-of-contract input (bins >= 2^n) */
   if (e->range == 256 && n < 32) bins &= (1u << n) - 1;
@@ -291,6 +306,10 @@ static void enc_rem_abs(Enc *e, unsigned v, unsigned rice, unsigned cutoff, int 
 /* encodeBinTrm, arith_codec.cpp:460-478 */
 static void enc_trm(Enc *e, unsigned bin) {
   e->nbins++;
+  if (e->est) { /* estFracBitsTrm, contexts.cpp:931-933 */
+    e->estBits += bin ? 0x3bfbb : 0x0010c;
+    return;
+  }
   e->range -= 2;
   if (bin) {
     e->low += e->range;
@@ -1381,6 +1400,28 @@ long orc_encode_residual(const cabac_tu_desc *tus, long ntu, const cabac_substre
     if (st) return -(long)st;
   }
   return enc_end(&e, p, &ct, numBins, ctxOut);
+}
+
+/* m_binFracBits[256][2] flattened (contexts.cpp:791-878), generated by gen_tables.py */
+void orc_frac_bits(uint32_t *out) { memcpy(out, CABAC_FRAC_BITS, sizeof(CABAC_FRAC_BITS)); }
+
+/* RDO bit estimate of a TU list: CABACWriter::residual_coding on BitEstimator_Std.  Returns
+ * getEstFracBits(); estPerTu[t] = the running estimate after TU t. */
+uint64_t orc_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                               const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
+                               uint64_t *estPerTu) {
+  CtxTab ct;
+  Enc e;
+  uint8_t dummy[8];
+  ctx_begin(&ct, p, ctxIn);
+  enc_start(&e, dummy, 0);
+  e.est = 1;
+  for (long t = 0; t < ntu; t++) {
+    if (w_residual_coding(&e, &ct, &tus[t], coeffs, p->flags, NULL)) return ~0ull;
+    if (estPerTu) estPerTu[t] = e.estBits;
+  }
+  if (ctxOut) memcpy(ctxOut, ct.m, sizeof(ct.m));
+  return e.estBits;
 }
 
 /* Recorded command stream with CABAC_CMD_TU markers (cabac_encode_stream): the BinEncIf calls of a

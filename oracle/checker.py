@@ -185,6 +185,27 @@ class Checker:
         res = (out[:n].copy(), int(nb[0]), tuf)
         return res + (ctx_out,) if want_ctx else res
 
+    def frac_bits(self) -> np.ndarray:
+        """BinProbModelBase::m_binFracBits flattened [state][bin] (contexts.cpp:791-878)."""
+        out = np.zeros(512, np.uint32)
+        self._f("frac_bits")(_ptr(out))
+        return out
+
+    def estimate_residual(self, tus, coeffs, qp, init_id, flags=0, ctx_in=None, want_ctx=False):
+        """BitEstimator_Std behind CABACWriter::residual_coding: (total, per-TU running totals[, ctx])."""
+        tus = np.ascontiguousarray(tus, TU_DT)
+        coeffs = np.ascontiguousarray(coeffs, np.int32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        per_tu = np.zeros(len(tus), np.uint64)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT) if want_ctx else None
+        f = self._f("estimate_residual")
+        f.restype = C.c_uint64
+        tot = int(f(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in), _ptr(ctx_out),
+                    _ptr(per_tu)))
+        assert tot != 0xFFFFFFFFFFFFFFFF
+        return (tot, per_tu, ctx_out) if want_ctx else (tot, per_tu)
+
     def encode_stream(self, cmds, tus, coeffs, qp, init_id, flags, ctx_in=None, want_ctx=False, cap=None):
         """Recorded commands with CMD_TU markers (marker k codes tus[k])."""
         cmds = np.ascontiguousarray(cmds, np.uint32)

@@ -398,4 +398,36 @@ long ref_count_emulations(const uint8_t *d, long n) {
   return bs.countStartCodeEmulations();
 }
 
+// ProbModelTables::m_binFracBits (contexts.cpp:791-878) through the public accessor: out[2 * q + bin].
+void ref_frac_bits(uint32_t *out) {
+  for (unsigned q = 0; q < 256; q++) {
+    BinProbModel_Std m(uint16_t(q << 7), uint16_t(q << 7), 0x58);  // state() = (s0 + s1) >> 8 = q
+    const BinFracBits f = m.getFracBitsArray();
+    out[2 * q] = f.intBits[0];
+    out[2 * q + 1] = f.intBits[1];
+  }
+}
+
+// RDO estimation of a TU list: CABACWriter::residual_coding on the reference's BitEstimator_Std
+// (arith_codec.cpp:603-711).  Returns getEstFracBits(); estPerTu[t] = the estimate after TU t.
+uint64_t ref_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                               const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
+                               uint64_t *estPerTu) {
+  Harness hs(*p, false);
+  BitEstimator_Std est;
+  CABACWriter wr(est);
+  est.reset(p->qp, p->init_id);
+  if ((p->flags & CABAC_SUB_CTX_IN) && ctxIn) importCtx(est, ctxIn);
+  for (long t = 0; t < ntu; t++) {
+    TuPair tp;
+    makeTu(tp, hs, tus[t], const_cast<TCoeff *>(coeffs));
+    applyTsAllowed(tp, tus[t], false);
+    CUCtx cuCtx(p->qp);
+    wr.residual_coding(tp.tu, ComponentID(tus[t].comp_id), &cuCtx);
+    if (estPerTu) estPerTu[t] = est.getEstFracBits();
+  }
+  if (ctxOut) exportCtx(est, ctxOut);
+  return est.getEstFracBits();
+}
+
 }  // extern "C"

@@ -185,3 +185,31 @@ def test_stream_oracle_vs_reference(oracle, ref):
         ro, rr = oracle.encode_stream(*args, want_ctx=True), ref.encode_stream(*args, want_ctx=True)
         assert ro[0].tobytes() == rr[0].tobytes() and ro[1] == rr[1]
         assert (ro[2] == rr[2]).all() and (ro[3] == rr[3]).all()
+
+
+# ---- the RDO bit estimator (BitEstimator_Std behind the same writer) ----
+def test_frac_bits_table_vs_ref(oracle, ref):
+    assert (oracle.frac_bits() == ref.frac_bits()).all()
+
+
+@pytest.mark.parametrize("seed,flags,kw", [
+    (201, None, {}),
+    (202, SUB_SIGN_HIDING, {}),
+    (203, SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3}),
+    (204, SUB_DEP_QUANT | SUB_TSRC_DISABLED, {"ts_fraction": 0.4, "bdpcm_fraction": 0.1}),
+])
+def test_oracle_vs_ref_estimate(oracle, ref, seed, flags, kw):
+    wl = W.random_substreams(10, seed, flags=flags, **kw)
+    for i in range(wl.n_sub):
+        a, b, _, _ = sub_range(wl, i)
+        p = wl.params[i]
+        args = (int(p["qp"]), int(p["init_id"]), int(p["flags"]))
+        r = ref.estimate_residual(wl.tus[a:b], wl.coeffs, *args, want_ctx=True)
+        o = oracle.estimate_residual(wl.tus[a:b], wl.coeffs, *args, want_ctx=True)
+        assert r[0] == o[0] and (r[1] == o[1]).all() and (r[2] == o[2]).all()
+        # the estimator leaves the contexts exactly where the real encoder does
+        e = oracle.encode_residual(wl.tus[a:b], wl.coeffs, *args, want_ctx=True)
+        assert (e[3] == o[2]).all()
+        # and its estimate tracks the real payload (15-bit fixed point) to within the coder's slack
+        bits = o[0] / 32768.0
+        assert abs(bits - 8 * len(e[0])) <= 0.02 * 8 * len(e[0]) + 64
