@@ -41,6 +41,9 @@ _SIGS = {
     "cabac_encode_residual_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_decode_residual": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
     "cabac_decode_residual_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_estimate_residual_bits": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_estimate_residual_bits_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_frac_bits_table": (C.c_int, [_P]),
     "cabac_count_emulations": (C.c_int, [_P, _P, _P, _SZ, _P]),
     "cabac_count_emulations_dev": (C.c_int, [_P, _P, _P, _SZ, _P]),
     "cabac_insert_emulation_prevention": (C.c_int, [_P, _P, _SZ, _P, _SZ, _P]),

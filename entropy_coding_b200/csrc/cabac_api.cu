@@ -347,6 +347,12 @@ int cabac_ctx_init_table(int row, uint8_t *table_out) {
   return CABAC_OK;
 }
 
+int cabac_frac_bits_table(uint32_t *table_out) {
+  if (!table_out) return CABAC_ERR_ARG;
+  memcpy(table_out, cabac::hostFracBits(), 512 * sizeof(uint32_t));
+  return CABAC_OK;
+}
+
 // ---- device-pointer entry points -----------------------------------------
 int cabac_ctx_init_dev(cabac_handle *h, const cabac_substream_params *params, size_t n, cabac_ctx_model *out) {
   if (!h || (n && (!params || !out))) return badArg(h, "cabac_ctx_init_dev");
@@ -438,6 +444,26 @@ int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds, const uint64_
                                ctx_in, out, out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status),
      "encode_stream kernels");
   h->launches += sc.twoStage ? 5 : 4;
+  return CABAC_OK;
+}
+
+int cabac_estimate_residual_bits_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                     const cabac_ctx_model *ctx_in, uint64_t *est_bits, uint64_t *est_per_tu,
+                                     uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                     uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits_dev");
+  DeviceGuard g(h->device);
+  if (!n_sub) return CABAC_OK;
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  sc.twoStage = false;
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, nullptr, params),
+     "estimate prepare kernels");
+  CK(cabac::launchEstimateResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, est_bits,
+                                   est_per_tu, num_bins, tu_flags, ctx_out, status),
+     "estimate_residual kernel");
+  h->launches += 4;  // cost, order, slab scan (shared prepare), estimate
   return CABAC_OK;
 }
 
@@ -696,6 +722,57 @@ int cabac_encode_residual(cabac_handle *h, const cabac_tu_desc *tus, const uint6
     if (nb) CK(cudaMemcpyAsync(out + out_offsets[i], dOut + out_offsets[i], nb, cudaMemcpyDeviceToHost, h->stream),
                "D2H copy");
   }
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                 const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                 size_t n_coeffs, const cabac_ctx_model *ctx_in, uint64_t *est_bits,
+                                 uint64_t *est_per_tu, uint32_t *num_bins, uint8_t *tu_flags,
+                                 cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nTu = tu_offsets[n_sub];
+  if (nTu && (!tus || !coeffs)) return badArg(h, "cabac_estimate_residual_bits: tus/coeffs");
+  cabac_tu_desc *dTus;
+  uint64_t *dTuOff, *dEst, *dPerTu;
+  cabac_substream_params *dP;
+  int32_t *dCoeffs;
+  cabac_ctx_model *dCin, *dCout;
+  uint8_t *dTuFlags;
+  uint32_t *dBins, *dStatus;
+  Arena a(h);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dEst, n_sub * 8);
+  a.want((void **)&dPerTu, est_per_tu ? nTu * 8 : 0);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dCoeffs, n_coeffs * 4);
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  int rc = cabac_estimate_residual_bits_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dEst,
+                                            est_per_tu ? dPerTu : nullptr, dBins, dTuFlags,
+                                            ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  D2H(est_bits, dEst, n_sub * 8);
+  D2H(est_per_tu, dPerTu, nTu * 8);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(tu_flags, dTuFlags, nTu);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
   CK(cudaStreamSynchronize(h->stream), "sync");
   return anySubstreamFailed(hst, n_sub);
 }

@@ -17,9 +17,15 @@ namespace cabac {
 #define CABAC_CTX_TABLE_QUALIFIER __device__ __constant__
 #include "cabac_ctx_tables.inc"
 #undef CABAC_CTX_TABLE_QUALIFIER
+// m_binFracBits of the bit estimator: indexed per lane (divergent), so it lives in global memory
+// behind L1 rather than in the constant bank
+#define CABAC_CTX_TABLE_QUALIFIER __device__ const
+#include "cabac_frac_bits.inc"
+#undef CABAC_CTX_TABLE_QUALIFIER
 #define CABAC_CTX_TABLE_QUALIFIER static const
 namespace hosttab {
 #include "cabac_ctx_tables.inc"
+#include "cabac_frac_bits.inc"
 }
 
 constexpr int WARPS_PER_BLOCK = 4;
@@ -645,9 +651,15 @@ struct __align__(16) FusedEncWarpSmem {
   uint16_t cgMask[64];
 };
 
-// kResolve: probabilities of a batch are resolved lane-parallel (lsResolveQueue) before the serial
-// walk, which then only carries the interval recurrence.
-template <bool kResolve>
+// kMode FUSED_RESOLVE : probabilities of a batch are resolved lane-parallel (lsResolveQueue) before the
+//                       serial walk, which then only carries the interval recurrence.
+//       FUSED_LEGACY  : lsDrain codes the raw words (model + interval on the serial path).
+//       FUSED_ESTIMATE: the RDO bit estimator (CABACWriter on BitEstimator_Std): the same binarisation
+//                       and model walk, no interval coder; 15-bit fixed-point bits per substream
+//                       (estBits) and the running total after every TU (estPerTu).  out / outOffsets /
+//                       outSizes are unused.
+enum { FUSED_LEGACY = 0, FUSED_RESOLVE = 1, FUSED_ESTIMATE = 2 };
+template <int kMode>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, ENC_MIN_CTAS)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
@@ -655,7 +667,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint8_t *__restrict__ out, const uint64_t *__restrict__ outOffsets,
                        uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
-                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
+                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
+                       uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu) {
+  constexpr bool kResolve = kMode == FUSED_RESOLVE;
+  constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
   __shared__ FusedEncWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   FusedEncWarpSmem &sm = smem[wib];
@@ -666,7 +681,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     // identical on every lane; only the coder of this instantiation survives dead-code elimination
     LsEncoder enc;
     LsCoder rc;
-    if constexpr (kResolve) {
+    uint64_t est = 0;
+    uint32_t estBins = 0;
+    if constexpr (kEstimate) {
+    } else if constexpr (kResolve) {
       rc.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane,
                (p.flags & CABAC_SUB_TERMINATE) != 0);
     } else {
@@ -735,6 +753,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         if (lastCG < 0) {  // "Coefficient coding called for empty TU", cabac_writer.cpp:2457
           st |= CABAC_SS_EMPTY_TU;
           if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
+          if constexpr (kEstimate)
+            if (estPerTu && lane == 0) estPerTu[t] = est;
           t++;
           continue;
         }
@@ -797,7 +817,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         inTu = false;
       }
       __syncwarp();
-      if constexpr (kResolve) {
+      if constexpr (kEstimate) {
+        est += lsEstimateQueue(sm.ctx, sm.queue, nq, lane, CABAC_FRAC_BITS, estBins);
+        if (endTu && estPerTu && lane == 0) estPerTu[t - 1] = est;
+      } else if constexpr (kResolve) {
         rc.nbins += lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
         lsWalkResolved(rc, sm.queue, nq);
       } else {
@@ -807,7 +830,11 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       __syncwarp();
     }
     uint32_t total, cap, nb;
-    if constexpr (kResolve) {
+    if constexpr (kEstimate) {
+      total = cap = 0;
+      nb = estBins;
+      if (lane == 0) estBits[sub] = est;
+    } else if constexpr (kResolve) {
       total = rc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
       cap = rc.cap;
       nb = rc.nbins;
@@ -820,7 +847,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     }
     if (lane == 0) {
       if (total > cap) st |= CABAC_SS_OUT_OVERFLOW;
-      outSizes[sub] = total;
+      if constexpr (!kEstimate) outSizes[sub] = total;
       if (numBins) numBins[sub] = nb;
       if (status) status[sub] = st;
     }
@@ -1346,6 +1373,7 @@ cudaError_t uploadRom() {
 }
 
 const unsigned char *hostInitTable(int row) { return hosttab::CABAC_CTX_INIT_TABLE[row]; }
+const unsigned int *hostFracBits() { return hosttab::CABAC_FRAC_BITS; }
 
 // Persistent grid: as many CTAs as can be resident (or fewer when there is less work).
 template <typename K>
@@ -1423,13 +1451,13 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
   if (nSub == 0) return cudaSuccess;
   if (!sc.twoStage) {
     if (sc.fusedResolve)
-      encode_residual_kernel<true><<<persistentGrid(encode_residual_kernel<true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor);
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
     else
-      encode_residual_kernel<false><<<persistentGrid(encode_residual_kernel<false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      encode_residual_kernel<FUSED_LEGACY><<<persistentGrid(encode_residual_kernel<FUSED_LEGACY>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor);
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
     return cudaGetLastError();
   }
   produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
@@ -1441,6 +1469,19 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
   range_code_kernel<<<unsigned((nSub + perBlock - 1) / perBlock), RC_WARPS * 32, 0, s>>>(
       sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, params, nSub, out, outOffsets, outSizes, numBins,
       status ? status : sc.statusScratch, sc.order);
+  return cudaGetLastError();
+}
+
+// RDO bit estimate of TU lists (BitEstimator_Std): the fused kernel without its interval coder.
+cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
+                                   const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
+                                   const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint64_t *estBits,
+                                   uint64_t *estPerTu, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
+                                   uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  encode_residual_kernel<FUSED_ESTIMATE><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,
+      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu);
   return cudaGetLastError();
 }
 

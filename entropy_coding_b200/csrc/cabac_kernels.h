@@ -25,6 +25,7 @@ constexpr int kLaunchesPerCodingCall = 3;
 
 cudaError_t uploadRom();
 const unsigned char *hostInitTable(int row);
+const unsigned int *hostFracBits();
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
                           cabac_ctx_model *out);
@@ -46,6 +47,11 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
                                  uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status);
+cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
+                                   const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
+                                   const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint64_t *estBits,
+                                   uint64_t *estPerTu, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
+                                   uint32_t *status);
 cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
                                  const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,

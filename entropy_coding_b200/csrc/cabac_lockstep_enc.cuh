@@ -557,6 +557,47 @@ __device__ __forceinline__ uint32_t lsResolveQueue(uint4 *ctx, uint32_t *queue, 
 }
 
 
+// The RDO bit estimator (BitEstimator_Std, arith_codec.cpp:603-711) over one queue: the same
+// rank-serialised model walk as lsResolveQueue, but what leaves is the 15-bit fixed-point cost of the
+// words - m_binFracBits[state()][bin] for a context-coded bin BEFORE its update (estFracBitsUpdate,
+// contexts.cpp:922-925), numBins << SCALE_BITS for bypass bins (estFracBitsEP, contexts.cpp:882-884).
+// There is no interval and no serial walk.  Returns the (uniform) cost; `bins` as lsResolveQueue.
+__device__ __forceinline__ uint64_t lsEstimateQueue(uint4 *ctx, const uint32_t *queue, int n, int lane,
+                                                    const uint32_t *__restrict__ fracBits, uint32_t &bins) {
+  uint32_t cost = 0;  // this lane's share; <= 2 words of <= 2^20 per slice, queues are << 2^10 slices
+  uint32_t nb = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    const uint32_t w = i < n ? queue[i] : (uint32_t(CABAC_CMD_EP) << 29);
+    const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+    const uint32_t idx = w & 511u, bin = (w >> 9) & 1u;
+    const uint32_t peers = __match_any_sync(FULL, isCtx ? idx : (0x8000u | uint32_t(lane)));
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int rounds = __reduce_max_sync(FULL, isCtx ? rank : 0);
+    for (int r = 0; r <= rounds; r++) {
+      if (isCtx && rank == r) {
+        const uint4 e = ctx[idx];
+        const uint32_t q = ((e.x >> 16) + (e.x & 0xFFFFu)) >> 8;
+        const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
+        const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
+        ctx[idx].x = e.x - d0 - d1 + (bin ? e.y : 0u);
+        cost += __ldg(&fracBits[2u * q + bin]);
+        nb++;
+      }
+      __syncwarp();
+    }
+    if (!isCtx && (w >> 29) == CABAC_CMD_EP) {
+      const uint32_t k = (w >> 24) & 31u;
+      cost += k << 15;
+      nb += k;
+    }
+  }
+  __syncwarp();
+  bins += __reduce_add_sync(FULL, nb);
+  // 64-bit sum of the lanes' 32-bit shares
+  return uint64_t(__reduce_add_sync(FULL, cost & 0xFFFFu)) + (uint64_t(__reduce_add_sync(FULL, cost >> 16)) << 16);
+}
+
 // ---------------------------------------------------------------------------
 // Stage D coder: interval recurrence + byte output for ONE substream per lane.
 //

@@ -117,6 +117,12 @@ class CabacEngine:
         self._check(self.lib.cabac_ctx_init_table(row, _hp(out)))
         return out
 
+    def frac_bits_table(self) -> np.ndarray:
+        """m_binFracBits as [2 * state + bin] (contexts.cpp:791-878)."""
+        out = np.zeros(512, np.uint32)
+        self._check(self.lib.cabac_frac_bits_table(_hp(out)))
+        return out
+
     def ctx_init(self, params) -> np.ndarray:
         params = _np(params, PARAMS_DT)
         out = np.zeros((len(params), NUM_CTX), CTX_DT)
@@ -188,6 +194,26 @@ class CabacEngine:
         if rc != ERR_SUBSTREAM or raise_on_status:
             self._check(rc, status)
         return dict(out=out, sizes=sizes, num_bins=bins, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    def estimate_residual_bits(self, tus, tu_offsets, params, coeffs, ctx_in=None, want_ctx=False,
+                               want_per_tu=True, raise_on_status=True):
+        """CABACWriter::residual_coding on BitEstimator_Std for every TU list (candidate) of the batch:
+        est_bits in 1/32768 bit per list and, per TU, the running total after it."""
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs = _np(params, PARAMS_DT), _np(coeffs, np.int32)
+        n = len(params)
+        est, bins, status = np.zeros(n, np.uint64), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        per_tu = np.zeros(len(tus), np.uint64) if want_per_tu else None
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_estimate_residual_bits(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
+                                                   coeffs.size, _hp(ctx_in), _hp(est), _hp(per_tu), _hp(bins),
+                                                   _hp(tu_flags), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(est_bits=est, est_per_tu=per_tu, num_bins=bins, tu_flags=tu_flags, status=status,
+                    ctx_out=ctx_out)
 
     def encode_residual_packed(self, tus, tu_offsets, params, coeffs, out_offsets, packed=None, ctx_in=None,
                                want_ctx=False, raise_on_status=True):
@@ -263,6 +289,13 @@ class CabacEngine:
                                                        _dp(coeffs), _dp(ctx_in), _dp(out), _dp(out_offsets),
                                                        _dp(out_sizes), _dp(num_bins), _dp(tu_flags), _dp(ctx_out),
                                                        _dp(status)))
+
+    def estimate_residual_bits_dev(self, tus, tu_offsets, params, n_sub, coeffs, est_bits, est_per_tu=None,
+                                   num_bins=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_estimate_residual_bits_dev(self.h, _dp(tus), _dp(tu_offsets), _dp(params), n_sub,
+                                                              _dp(coeffs), _dp(ctx_in), _dp(est_bits),
+                                                              _dp(est_per_tu), _dp(num_bins), _dp(tu_flags),
+                                                              _dp(ctx_out), _dp(status)))
 
     def decode_residual_dev(self, data, in_offsets, tus, tu_offsets, params, n_sub, coeffs, num_bins=None,
                             bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):

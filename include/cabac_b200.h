@@ -352,6 +352,40 @@ int cabac_pack(cabac_handle *h, const uint8_t *out, const uint64_t *out_offsets,
                const uint32_t *out_sizes, size_t n_sub, uint8_t *packed,
                size_t packed_cap, uint64_t *entry_points);
 
+/* ---- RDO bit estimation: the encoder-side caller of the path ---------------- */
+/* CABACWriter::residual_coding() (cabac_writer.cpp:2438-2585) over a TU list with the
+ * writer bound to a BitEstimator_Std (arith_codec.hpp:189-259, arith_codec.cpp:603-711)
+ * instead of the arithmetic coder - what an encoder's rate-distortion search calls
+ * to price a candidate.  est_bits[i] = getEstFracBits() of substream i after its last
+ * TU, in 1/32768 bit (SCALE_BITS = 15): m_binFracBits[state()][bin] per context-coded
+ * bin (contexts.cpp:791-878, 922-929), 1 << 15 per bypass bin (contexts.cpp:880-884).
+ * est_per_tu (nullable) [n_tu] = the running total after each TU, i.e. the value an
+ * encoder reads between two residual_coding() calls.  Contexts evolve exactly as in
+ * cabac_encode_residual; CABAC_SUB_TERMINATE / CABAC_SUB_ALIGN are ignored (the
+ * estimator has neither; num_bins therefore counts the residual syntax only, one less
+ * than cabac_encode_residual's for a terminated substream).  num_bins / tu_flags /
+ * ctx_out / status nullable.
+ * One launch prices every candidate list of a batch: n_sub is the number of
+ * candidates, ctx_in their (shared or individual) starting contexts. */
+int cabac_estimate_residual_bits_dev(cabac_handle *h, const cabac_tu_desc *tus,
+                                     const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params,
+                                     size_t n_sub, const int32_t *coeffs,
+                                     const cabac_ctx_model *ctx_in,
+                                     uint64_t *est_bits, uint64_t *est_per_tu,
+                                     uint32_t *num_bins, uint8_t *tu_flags,
+                                     cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus,
+                                 const uint64_t *tu_offsets,
+                                 const cabac_substream_params *params,
+                                 size_t n_sub, const int32_t *coeffs,
+                                 size_t n_coeffs, const cabac_ctx_model *ctx_in,
+                                 uint64_t *est_bits, uint64_t *est_per_tu,
+                                 uint32_t *num_bins, uint8_t *tu_flags,
+                                 cabac_ctx_model *ctx_out, uint32_t *status);
+/* m_binFracBits flattened as table_out[2 * state + bin], 512 entries. */
+int cabac_frac_bits_table(uint32_t *table_out);
+
 /* ---- start-code emulation: the step right after the path ------------------- */
 /* counts[i] = OutputBitstream::countStartCodeEmulations() of segment
  * data[offsets[i] .. offsets[i+1]) (bit_stream.cpp:157-181): the number of

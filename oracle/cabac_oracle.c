@@ -1409,8 +1409,9 @@ void orc_frac_bits(uint32_t *out) { memcpy(out, CABAC_FRAC_BITS, sizeof(CABAC_FR
  * getEstFracBits(); estPerTu[t] = the running estimate after TU t. */
 uint64_t orc_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
                                const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
-                               uint64_t *estPerTu) {
+                               uint64_t *estPerTu, int useMTS) {
   CtxTab ct;
+  (void)useMTS; /* the reference harness needs it to set up its SPS; the TU descriptors carry the effect */
   Enc e;
   uint8_t dummy[8];
   ctx_begin(&ct, p, ctxIn);

@@ -42,7 +42,7 @@ double orc_time_decode_residual(const uint8_t *in, const uint64_t *inOffsets, co
 void orc_frac_bits(uint32_t *out);
 uint64_t orc_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
                                const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
-                               uint64_t *estPerTu);
+                               uint64_t *estPerTu, int useMTS);
 long orc_count_emulations(const uint8_t *d, long n);
 long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out);
 #endif

@@ -191,7 +191,7 @@ class Checker:
         self._f("frac_bits")(_ptr(out))
         return out
 
-    def estimate_residual(self, tus, coeffs, qp, init_id, flags=0, ctx_in=None, want_ctx=False):
+    def estimate_residual(self, tus, coeffs, qp, init_id, flags=0, ctx_in=None, want_ctx=False, use_mts=False):
         """BitEstimator_Std behind CABACWriter::residual_coding: (total, per-TU running totals[, ctx])."""
         tus = np.ascontiguousarray(tus, TU_DT)
         coeffs = np.ascontiguousarray(coeffs, np.int32)
@@ -202,7 +202,7 @@ class Checker:
         f = self._f("estimate_residual")
         f.restype = C.c_uint64
         tot = int(f(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in), _ptr(ctx_out),
-                    _ptr(per_tu)))
+                    _ptr(per_tu), C.c_int(int(use_mts))))
         assert tot != 0xFFFFFFFFFFFFFFFF
         return (tot, per_tu, ctx_out) if want_ctx else (tot, per_tu)
 

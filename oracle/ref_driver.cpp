@@ -412,8 +412,8 @@ void ref_frac_bits(uint32_t *out) {
 // (arith_codec.cpp:603-711).  Returns getEstFracBits(); estPerTu[t] = the estimate after TU t.
 uint64_t ref_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
                                const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
-                               uint64_t *estPerTu) {
-  Harness hs(*p, false);
+                               uint64_t *estPerTu, int useMTS) {
+  Harness hs(*p, useMTS != 0);
   BitEstimator_Std est;
   CABACWriter wr(est);
   est.reset(p->qp, p->init_id);
@@ -421,7 +421,7 @@ uint64_t ref_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_s
   for (long t = 0; t < ntu; t++) {
     TuPair tp;
     makeTu(tp, hs, tus[t], const_cast<TCoeff *>(coeffs));
-    applyTsAllowed(tp, tus[t], false);
+    applyTsAllowed(tp, tus[t], useMTS != 0);
     CUCtx cuCtx(p->qp);
     wr.residual_coding(tp.tu, ComponentID(tus[t].comp_id), &cuCtx);
     if (estPerTu) estPerTu[t] = est.getEstFracBits();

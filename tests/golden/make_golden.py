@@ -150,6 +150,22 @@ def main():
         print(name, wl.n_sub, "substreams", len(wl.tus), "TUs", sum(m[0] for m in metas), "bins")
     out["names"] = np.asarray(names)
     np.savez_compressed(os.path.join(HERE, "residual.npz"), **out)
+    # ---- RDO bit estimates of the same residual cases (BitEstimator_Std behind CABACWriter) ----
+    est = {}
+    for (name, _, _, use_mts) in cases:
+        tus, offs, params, coeffs = (out[f"{name}_{k}"] for k in ("tus", "tu_offsets", "params", "coeffs"))
+        totals, per_tu = [], []
+        for i in range(len(params)):
+            a, b = int(offs[i]), int(offs[i + 1])
+            p = params[i]
+            tot, pt = ref.estimate_residual(tus[a:b], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]),
+                                            use_mts=use_mts)
+            totals.append(tot)
+            per_tu.append(pt)
+        est[f"{name}_est_bits"] = np.asarray(totals, np.uint64)
+        est[f"{name}_est_per_tu"] = np.concatenate(per_tu)
+    est["frac_bits"] = ref.frac_bits()
+    np.savez_compressed(os.path.join(HERE, "estimate.npz"), **est)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

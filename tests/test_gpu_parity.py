@@ -519,3 +519,96 @@ def test_zero_copy_host_path_matches_staged(monkeypatch, oracle):
         p = wl.params[i]
         eb, nb, _ = oracle.encode_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
         assert r1["packed"][int(ep[i]):int(ep[i + 1])].tobytes() == eb.tobytes() and nb == int(r1["num_bins"][i])
+
+
+# ---------------------------------------------------------------- RDO bit estimator
+def test_frac_bits_table(engine, oracle):
+    assert (engine.frac_bits_table() == oracle.frac_bits()).all()
+
+
+def test_estimate_golden_on_gpu(engine):
+    g, e = load_golden("residual"), load_golden("estimate")
+    assert (engine.frac_bits_table() == e["frac_bits"]).all()
+    for name in g["names"]:
+        r = engine.estimate_residual_bits(g[f"{name}_tus"], g[f"{name}_tu_offsets"], g[f"{name}_params"],
+                                          g[f"{name}_coeffs"])
+        assert (r["est_bits"] == e[f"{name}_est_bits"]).all(), name
+        assert (r["est_per_tu"] == e[f"{name}_est_per_tu"]).all(), name
+        assert (r["tu_flags"] == g[f"{name}_tu_flags"]).all()
+
+
+@pytest.mark.parametrize("seed,flags,kw", [
+    (601, None, {}),
+    (602, SUB_SIGN_HIDING, {}),
+    (603, T | SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3}),
+    (604, SUB_DEP_QUANT | SUB_TSRC_DISABLED, {"ts_fraction": 0.4, "bdpcm_fraction": 0.1}),
+    (605, SUB_DEP_QUANT, {"sbt_fraction": 0.2}),
+    (606, None, {"preset": "qp0", "tus_per_sub": (1, 3)}),
+    (607, None, {"preset": "qp51", "tus_per_sub": (30, 60)}),
+])
+def test_estimate_vs_oracle(engine, oracle, seed, flags, kw):
+    """cabac_estimate_residual_bits == BitEstimator_Std behind the writer: totals, per-TU running totals,
+    bins, TU side effects and the contexts it leaves."""
+    wl = W.random_substreams(40, seed, flags=flags, **kw)
+    r = engine.estimate_residual_bits(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, want_ctx=True)
+    assert not r["status"].any()
+    enc, _ = run_residual(engine, wl)
+    for i in range(wl.n_sub):
+        a, b, _, _ = sub_range(wl, i)
+        p = wl.params[i]
+        tot, per_tu, ectx = oracle.estimate_residual(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]),
+                                                     int(p["flags"]), want_ctx=True)
+        assert int(r["est_bits"][i]) == tot, (seed, i)
+        assert (r["est_per_tu"][a:b] == per_tu).all()
+        assert (r["ctx_out"][i] == ectx).all()
+    # the estimator and the real coder agree on everything but the bytes
+    trm = (wl.params["flags"] & SUB_TERMINATE) != 0  # the coder's count includes its terminating bin
+    assert (r["num_bins"] + trm == enc["num_bins"]).all() and (r["tu_flags"] == enc["tu_flags"]).all()
+    assert (r["ctx_out"] == enc["ctx_out"]).all()
+
+
+def test_estimate_ctx_handoff_and_candidates(engine, oracle):
+    """RDO use: many candidate TU lists priced from ONE saved context set (ctx_in), and an estimate
+    continued across two calls equals the estimate of the concatenation."""
+    wl = W.random_substreams(24, 611, flags=SUB_DEP_QUANT, tus_per_sub=(4, 9))
+    full = engine.estimate_residual_bits(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, want_ctx=True)
+    # split every list in two: first halves, then second halves starting from the contexts of the first
+    mid = (wl.tu_offsets[:-1] + (wl.tu_offsets[1:] - wl.tu_offsets[:-1]) // 2).astype(np.uint64)
+    order1 = np.concatenate([np.arange(int(wl.tu_offsets[i]), int(mid[i])) for i in range(wl.n_sub)])
+    order2 = np.concatenate([np.arange(int(mid[i]), int(wl.tu_offsets[i + 1])) for i in range(wl.n_sub)])
+    off1 = offsets_of(mid - wl.tu_offsets[:-1])
+    off2 = offsets_of(wl.tu_offsets[1:] - mid)
+    h1 = engine.estimate_residual_bits(wl.tus[order1], off1, wl.params, wl.coeffs, want_ctx=True)
+    p2 = wl.params.copy()
+    p2["flags"] |= SUB_CTX_IN
+    h2 = engine.estimate_residual_bits(wl.tus[order2], off2, p2, wl.coeffs, ctx_in=h1["ctx_out"], want_ctx=True)
+    assert (h1["est_bits"] + h2["est_bits"] == full["est_bits"]).all()
+    assert (h2["ctx_out"] == full["ctx_out"]).all()
+    # the same candidate priced n times from one context set gives one answer, equal to the oracle's
+    k = 7
+    a, b, _, _ = sub_range(wl, k)
+    n = 300
+    tus = np.tile(wl.tus[a:b], n)
+    offs = (np.arange(n + 1) * (b - a)).astype(np.uint64)
+    params = np.repeat(p2[k:k + 1], n)
+    ctx = np.repeat(h1["ctx_out"][k:k + 1], n, axis=0)
+    r = engine.estimate_residual_bits(tus, offs, params, wl.coeffs, ctx_in=ctx)
+    tot, _ = oracle.estimate_residual(wl.tus[a:b], wl.coeffs, int(p2[k]["qp"]), int(p2[k]["init_id"]),
+                                      int(p2[k]["flags"]), ctx_in=h1["ctx_out"][k])
+    assert (r["est_bits"] == tot).all()
+
+
+def test_estimate_empty_tu_and_empty_batch(engine):
+    tus = np.zeros(2, TU_DT)
+    tus["log2_w"], tus["log2_h"] = 3, 3
+    tus["coeff_offset"] = [0, 64]
+    coeffs = np.zeros(128, np.int32)
+    coeffs[64 + 5] = 3
+    params = np.zeros(1, PARAMS_DT)
+    params["qp"] = 32
+    r = engine.estimate_residual_bits(tus, np.array([0, 2], np.uint64), params, coeffs, raise_on_status=False)
+    assert int(r["status"][0]) & SS_EMPTY_TU
+    assert int(r["est_per_tu"][0]) == 0 and int(r["est_per_tu"][1]) == int(r["est_bits"][0]) > 0
+    r = engine.estimate_residual_bits(np.zeros(0, TU_DT), np.zeros(1, np.uint64), np.zeros(0, PARAMS_DT),
+                                      np.zeros(0, np.int32))
+    assert r["est_bits"].size == 0

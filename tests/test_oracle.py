@@ -213,3 +213,17 @@ def test_oracle_vs_ref_estimate(oracle, ref, seed, flags, kw):
         # and its estimate tracks the real payload (15-bit fixed point) to within the coder's slack
         bits = o[0] / 32768.0
         assert abs(bits - 8 * len(e[0])) <= 0.02 * 8 * len(e[0]) + 64
+
+
+def test_estimate_golden(oracle):
+    """The oracle's estimator against the reference-generated estimate.npz (BitEstimator_Std totals)."""
+    g, e = load_golden("residual"), load_golden("estimate")
+    assert (oracle.frac_bits() == e["frac_bits"]).all()
+    for name in g["names"]:
+        tus, offs, params, coeffs = g[f"{name}_tus"], g[f"{name}_tu_offsets"], g[f"{name}_params"], g[f"{name}_coeffs"]
+        for i in range(len(params)):
+            a, b = int(offs[i]), int(offs[i + 1])
+            p = params[i]
+            tot, per_tu = oracle.estimate_residual(tus[a:b], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
+            assert tot == int(e[f"{name}_est_bits"][i]), (name, i)
+            assert (per_tu == e[f"{name}_est_per_tu"][a:b]).all()
