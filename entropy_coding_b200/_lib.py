@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcabac_b200.so")
+LIB_PATH = os.environ.get("CABAC_B200_LIB") or os.path.join(HERE, "libcabac_b200.so")  # env: dev A/B builds
 
 _lib = None
 

@@ -122,6 +122,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
   sc.statusScratch = p + 4 * cap;
   sc.cmdBuf = h->cmdBuf;
   sc.fusedResolve = h->fusedResolve;
+  sc.warpSpecialised = h->encoderMode == CABAC_ENCODER_WARP_SPECIALISED;
   return cudaSuccess;
 }
 
@@ -274,6 +275,7 @@ cabac_handle *cabac_create(int device) {
   if (const char *m = getenv("CABAC_B200_ENCODER")) {
     if (!strcmp(m, "fused")) h->encoderMode = CABAC_ENCODER_FUSED;
     if (!strcmp(m, "two_stage")) h->encoderMode = CABAC_ENCODER_TWO_STAGE;
+    if (!strcmp(m, "warp_specialised")) h->encoderMode = CABAC_ENCODER_WARP_SPECIALISED;
   }
   return h;
 }
@@ -307,7 +309,7 @@ int cabac_set_stream(cabac_handle *h, void *cuda_stream) {
 }
 
 int cabac_set_encoder_mode(cabac_handle *h, int mode) {
-  if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_TWO_STAGE) return CABAC_ERR_ARG;
+  if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_WARP_SPECIALISED) return CABAC_ERR_ARG;
   h->encoderMode = mode;
   return CABAC_OK;
 }

@@ -658,9 +658,32 @@ struct __align__(16) FusedEncWarpSmem {
 //                       and model walk, no interval coder; 15-bit fixed-point bits per substream
 //                       (estBits) and the running total after every TU (estPerTu).  out / outOffsets /
 //                       outSizes are unused.
-enum { FUSED_LEGACY = 0, FUSED_RESOLVE = 1, FUSED_ESTIMATE = 2 };
+//       FUSED_WS      : warp-specialised: WS_PRODUCERS producer warps per CTA binarise and resolve; ONE
+//                       walker warp runs the range recurrence of all of them, one per lane; the
+//                       producers then fold their words into `low` in lane-parallel groups
+//                       (cabac_lockstep_enc.cuh, "Warp-specialised fused encoder").
+enum { FUSED_LEGACY = 0, FUSED_RESOLVE = 1, FUSED_ESTIMATE = 2, FUSED_WS = 3 };
+constexpr int WS_THREADS = (WS_PRODUCERS + 1) * 32;
+#ifndef CABAC_WS_MIN_CTAS
+#define CABAC_WS_MIN_CTAS 1
+#endif
+constexpr int WS_MIN_CTAS = CABAC_WS_MIN_CTAS;
+constexpr size_t WS_SMEM_BYTES = WS_PRODUCERS * (sizeof(FusedEncWarpSmem) + sizeof(WsChannel));
+
+template <bool kWs>
+__device__ __forceinline__ FusedEncWarpSmem &fusedEncSmem(int wib) {
+  if constexpr (kWs) {
+    extern __shared__ __align__(16) unsigned char wsDynSmem[];
+    return reinterpret_cast<FusedEncWarpSmem *>(wsDynSmem)[wib];
+  } else {
+    __shared__ FusedEncWarpSmem smem[WARPS_PER_BLOCK];
+    return smem[wib];
+  }
+}
+
 template <int kMode>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, ENC_MIN_CTAS)
+__global__ void __launch_bounds__(kMode == FUSED_WS ? WS_THREADS : WARPS_PER_BLOCK * 32,
+                                  kMode == FUSED_WS ? WS_MIN_CTAS : ENC_MIN_CTAS)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
                        const cabac_substream_params *__restrict__ params, size_t nSub,
                        const int32_t *__restrict__ coeffs, const cabac_ctx_model *__restrict__ ctxIn,
@@ -671,19 +694,59 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu) {
   constexpr bool kResolve = kMode == FUSED_RESOLVE;
   constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
-  __shared__ FusedEncWarpSmem smem[WARPS_PER_BLOCK];
+  constexpr bool kWs = kMode == FUSED_WS;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  FusedEncWarpSmem &sm = smem[wib];
+  WsChannel *chan = nullptr;
+  uint32_t chHead = 0, drained = 0;
+  if constexpr (kWs) {
+    WsChannel *chans = reinterpret_cast<WsChannel *>(&fusedEncSmem<true>(WS_PRODUCERS));
+    if (threadIdx.x < WS_PRODUCERS) chans[threadIdx.x].head = chans[threadIdx.x].tail = chans[threadIdx.x].want = 0;
+    __syncthreads();
+    if (wib == WS_PRODUCERS) {
+      wsWalk(chans, lane);
+      return;
+    }
+    chan = chans + wib;
+  }
+  FusedEncWarpSmem &sm = fusedEncSmem<kWs>(wib);
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    if constexpr (kWs) {  // the ring is empty here: every substream ends fully drained
+      wsPushWord(*chan, chHead, WS_MK_CTL(WS_OP_START), lane);
+      drained = chHead;
+    }
     // identical on every lane; only the coder of this instantiation survives dead-code elimination
     LsEncoder enc;
     LsCoder rc;
     uint64_t est = 0;
     uint32_t estBins = 0;
+    const bool wsSingle = !(p.flags & CABAC_SUB_TERMINATE);
+    // words [drained, chHead) are in the ring; drain 32 at a time once the walker has passed them.
+    // minFree: words the next push needs (waits for the walker only when the ring lacks that room)
+    auto wsDrain = [&](uint32_t minFree, bool all) {
+      for (;;) {
+        const uint32_t pending = chHead - drained;
+        const bool must = all ? pending != 0 : pending + minFree > WS_RING;
+        if (!must && pending < 32u) break;
+        const uint32_t m = min(32u, pending);
+        uint32_t spins = 0;
+        while (int32_t(wsLoad(&chan->tail) - drained) < int32_t(m)) {  // signed: the walker may not have passed START yet
+          if (!must) return;
+          if (spins == 0 && lane == 0) wsStore(&chan->want, 1u);
+          __nanosleep(32);
+          if (++spins > WS_SPIN_LIMIT) __trap();
+        }
+        if (spins && lane == 0) wsStore(&chan->want, 0u);
+        wsDrainSlice(rc, *chan, drained, int(m), lane, wsSingle);
+        drained += m;
+      }
+    };
     if constexpr (kEstimate) {
+    } else if constexpr (kWs) {
+      rc.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane, false);
+      rc.trackPending = wsSingle;  // eager emission either way; the outstanding-byte count only when observable
     } else if constexpr (kResolve) {
       rc.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane,
                (p.flags & CABAC_SUB_TERMINATE) != 0);
@@ -820,6 +883,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       if constexpr (kEstimate) {
         est += lsEstimateQueue(sm.ctx, sm.queue, nq, lane, CABAC_FRAC_BITS, estBins);
         if (endTu && estPerTu && lane == 0) estPerTu[t - 1] = est;
+      } else if constexpr (kWs) {
+        rc.nbins += lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+        wsDrain(uint32_t(nq), false);
+        if (nq) wsPush(*chan, chHead, sm.queue, nq, lane);
       } else if constexpr (kResolve) {
         rc.nbins += lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
         lsWalkResolved(rc, sm.queue, nq);
@@ -834,6 +901,15 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       total = cap = 0;
       nb = estBins;
       if (lane == 0) estBits[sub] = est;
+    } else if constexpr (kWs) {
+      // a no-op word (EP, 0 bins) whose recorded range is the one finish() continues from
+      wsDrain(1, false);
+      wsPushWord(*chan, chHead, uint32_t(CABAC_CMD_EP) << 29, lane);
+      wsDrain(0, true);
+      rc.range = chan->rng[(chHead - 1u) & (WS_RING - 1u)];
+      total = rc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
+      cap = rc.cap;
+      nb = rc.nbins;
     } else if constexpr (kResolve) {
       total = rc.finish((p.flags & CABAC_SUB_TERMINATE) != 0, (p.flags & CABAC_SUB_ALIGN) != 0);
       cap = rc.cap;
@@ -853,6 +929,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     }
     storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
     __syncwarp();
+  }
+  if constexpr (kWs) {  // nobody waits for EXIT to be taken: mark the channel urgent for good
+    if (lane == 0) wsStore(&chan->want, 1u);
+    wsPushWord(*chan, chHead, WS_MK_CTL(WS_OP_EXIT), lane);
   }
 }
 
@@ -1450,6 +1530,19 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  uint8_t *tuFlags, cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
   if (!sc.twoStage) {
+    if (sc.warpSpecialised && nSub < (size_t(1) << 27)) {
+      static const cudaError_t attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS>,
+                                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                           int(WS_SMEM_BYTES));
+      if (attr != cudaSuccess) return attr;
+      int sms = 148;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+      const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
+      encode_residual_kernel<FUSED_WS><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(
+          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
+      return cudaGetLastError();
+    }
     if (sc.fusedResolve)
       encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,

@@ -18,6 +18,7 @@ struct Sched {
   uint32_t *statusScratch;  // [n]   when the caller passes no status array
   uint64_t *cmdOffsets;     // [n+1] slab offsets (words); [n] = total
   uint32_t *cmdBuf;         // the slab
+  bool warpSpecialised = false;  // fused kernel: producer warps + one walker warp per CTA (FUSED_WS)
   bool fusedResolve = false;  // fused kernel: resolve probabilities lane-parallel before the serial walk
   bool twoStage;            // residual encode: stage P + stage D instead of the fused lockstep kernel
 };

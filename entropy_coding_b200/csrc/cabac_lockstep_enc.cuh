@@ -291,6 +291,7 @@ struct LsCoder {
   uint32_t vtmPending;  // m_numBufferedBytes of the reference coder
   uint32_t nbins;
   int lazyBelow;        // bytes leave `low` when bitsLeft drops below this
+  bool trackPending;    // keep vtmPending (substream not terminated)
   uint8_t *ring, *dst;
   uint32_t cap;
   int lane;
@@ -300,6 +301,7 @@ struct LsCoder {
   // writeOut() exactly as in the reference, which keeps `vtmPending` exact.
   __device__ __forceinline__ void start(uint8_t *ring_, uint8_t *dst_, uint32_t cap_, int lane_, bool terminated) {
     lazyBelow = terminated ? -4 : 12;
+    trackPending = !terminated;
     low = 0;
     acc = 0;
     range = 510;
@@ -342,7 +344,7 @@ struct LsCoder {
     const uint64_t bytes = chunk & ((1ull << (8 * k)) - 1ull);
     acc = (acc << (8 * k)) | bytes;
     cnt += k;
-    if (lazyBelow == 12) {
+    if (trackPending) {
       // m_numBufferedBytes, only observable when the substream is not terminated: a lead byte of
       // exactly 0xFF (no carry) extends the outstanding run, anything else restarts it at 1.  Exact
       // whenever bytes leave one at a time; a packed EP word can release up to 3 at once, where the
@@ -740,5 +742,195 @@ struct RangeCoder {
     return total;
   }
 };
+
+// ===========================================================================
+// Warp-specialised fused encoder.
+//
+// Of the interval coder only the RANGE recurrence is inherently serial: range' = f(range, word), nine
+// bits of state, ~10 instructions.  `low` is a sum of shifted addends - associative - so it can be
+// accumulated in groups by the lanes of a warp once the range each word saw is known.
+//
+//   producer warp (one substream): binarise -> resolve probabilities -> push resolved words into
+//       its ring in shared memory                                    (all lane-parallel)
+//   walker warp (one per CTA): lane j runs the range recurrence of producer j's ring and leaves
+//       the range every word saw next to it            (serial, but WS_PRODUCERS chains per warp-
+//       instruction instead of one)
+//   producer warp again: 32 words at a time, lanes compute (shift, addend) from (word, range), a prefix
+//       sum groups consecutive words into <= 39-bit pieces ("low = (low << K) + C"), and the warp's
+//       LsCoder takes one group - two to five output bytes - per serial step.
+// ===========================================================================
+#ifndef CABAC_WS_PRODUCERS
+#define CABAC_WS_PRODUCERS 16
+#endif
+#ifndef CABAC_WS_WINDOW_BITS
+#define CABAC_WS_WINDOW_BITS 4
+#endif
+constexpr int WS_PRODUCERS = CABAC_WS_PRODUCERS;
+constexpr uint32_t WS_RING = 256;    // words per channel (> QUEUE_WORDS + one drain slice)
+constexpr uint32_t WS_KIND_CTL = 6;  // control word: bits 28..27 = op
+constexpr uint32_t WS_OP_START = 0;  // new substream: range = 510
+constexpr uint32_t WS_OP_EXIT = 2;
+constexpr uint32_t WS_SPIN_LIMIT = 1u << 24;  // x >= 32 ns: a stuck hand-off traps instead of hanging the GPU
+#define WS_MK_CTL(op) ((WS_KIND_CTL << 29) | (uint32_t(op) << 27))
+
+struct __align__(16) WsChannel {
+  uint32_t ring[WS_RING];  // resolved words
+  uint16_t rng[WS_RING];   // m_Range each word saw (written by the walker)
+  uint2 pieces[32];        // (K, C) pieces of the slice being drained (producer only)
+  uint32_t head;           // words published by the producer (free-running)
+  uint32_t tail;           // words the walker has passed (free-running)
+  uint32_t want;           // the producer is waiting for the walker
+  uint32_t pad;
+};
+
+// Head / tail hand-off inside one CTA: shared-memory accesses of a warp are performed in program
+// order, so volatile accesses (no reordering by the compiler) are enough; no fence is needed.
+__device__ __forceinline__ uint32_t wsLoad(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(uint32_t(__cvta_generic_to_shared(p))) : "memory");
+  return v;
+}
+__device__ __forceinline__ void wsStore(uint32_t *p, uint32_t v) {
+  asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(uint32_t(__cvta_generic_to_shared(p))), "r"(v) : "memory");
+}
+
+// producer side; the caller has made room (wsDrain in the kernel)
+__device__ __forceinline__ void wsPush(WsChannel &ch, uint32_t &head, const uint32_t *q, int n, int lane) {
+  for (int i = lane; i < n; i += 32) ch.ring[(head + uint32_t(i)) & (WS_RING - 1u)] = q[i];
+  head += uint32_t(n);
+  __syncwarp();
+  if (lane == 0) wsStore(&ch.head, head);
+}
+__device__ __forceinline__ void wsPushWord(WsChannel &ch, uint32_t &head, uint32_t w, int lane) {
+  if (lane == 0) {
+    ch.ring[head & (WS_RING - 1u)] = w;
+    wsStore(&ch.head, head + 1u);
+  }
+  head += 1u;
+  __syncwarp();
+}
+
+// The walker warp: lane j < WS_PRODUCERS runs the range recurrence over channel j until EXIT.
+//  * Words arrive in bursts (one coefficient group at a time), out of step between channels.  The
+//    walker is one instruction stream for all its lanes, so it lets work pile up until several
+//    channels have a backlog (or a producer is waiting, or a ring is half full) and then takes up to
+//    32 words from every channel in one go: few issue slots are spent on mostly idle lanes.
+//  * WS_WALK_UNROLL words per lane and round: their loads are issued together, the critical path
+//    is one shared-memory round trip plus the dependent range steps (~9 instructions each).
+constexpr int WS_WALK_UNROLL = 4;
+constexpr int WS_WALK_ROUNDS = 8;
+constexpr uint32_t WS_WALK_BACKLOG = 16;  // words that make a channel "ready"
+constexpr int WS_WALK_MIN_READY = WS_PRODUCERS / 2;
+__device__ __forceinline__ void wsWalk(WsChannel *chans, int lane) {
+  bool alive = lane < WS_PRODUCERS;
+  WsChannel &ch = chans[alive ? lane : 0];
+  uint32_t tail = 0, idle = 0, range = 510;
+#pragma unroll 1
+  while (__any_sync(FULL, alive)) {
+    uint32_t avail = 0;
+    bool urgent = false;
+    if (alive) {
+      avail = wsLoad(&ch.head) - tail;
+      urgent = avail != 0 && (wsLoad(&ch.want) != 0 || avail >= WS_RING / 2);
+    }
+    const int ready = __popc(__ballot_sync(FULL, avail >= WS_WALK_BACKLOG));
+    if (ready < WS_WALK_MIN_READY && !__any_sync(FULL, urgent)) {
+      __nanosleep(128);
+      if (++idle > WS_SPIN_LIMIT) __trap();  // a stuck hand-off traps instead of hanging the GPU
+      continue;
+    }
+    idle = 0;
+#pragma unroll 1
+    for (int round = 0; round < WS_WALK_ROUNDS && __any_sync(FULL, avail != 0); round++) {
+      uint32_t w[WS_WALK_UNROLL];
+#pragma unroll
+      for (int i = 0; i < WS_WALK_UNROLL; i++) w[i] = ch.ring[(tail + uint32_t(i)) & (WS_RING - 1u)];  // may be stale past head
+      const uint32_t n = min(avail, uint32_t(WS_WALK_UNROLL));
+#pragma unroll
+      for (int i = 0; i < WS_WALK_UNROLL; i++) {
+        if (uint32_t(i) < n) {
+          ch.rng[(tail + uint32_t(i)) & (WS_RING - 1u)] = uint16_t(range);
+          const uint32_t kind = w[i] >> 29;
+          // BinProbModel_Std::getLPS + the renormalisation of encodeBin (arith_codec.cpp:359-385), range only
+          const uint32_t lps = (((w[i] & 63u) * (range >> 5)) >> 1) + 4;
+          const uint32_t nr = (w[i] & 64u) ? lps : range - lps;
+          const uint32_t next = nr << (__clz(int(nr | 7u)) - 23);
+          range = kind == CABAC_CMD_CTX ? next : range;
+          if (kind == WS_KIND_CTL) {  // rare
+            if (((w[i] >> 27) & 3u) == WS_OP_START) range = 510;
+            else alive = false;  // EXIT is the last word a producer pushes
+          }
+        }
+      }
+      tail += n;
+      avail -= n;
+    }
+    if (lane < WS_PRODUCERS) wsStore(&ch.tail, tail);
+  }
+}
+
+// Producer side: words [d, d + m) of the ring (m <= 32, all passed by the walker) go through the
+// warp's coder.  Lane l owns word d + l: shift k and addend c of "low = (low << k) + c" from the word
+// and the range it saw; consecutive words whose bit positions fall into the same 16-bit window are
+// summed into one (K, C) piece (K <= 39, C < 2^49), and the serial coder takes one piece per step.
+// `single`: one piece per word (a substream that is not terminated reports the reference's
+// outstanding-byte count, which is only exact when bytes leave as they do there).
+__device__ __forceinline__ void wsDrainSlice(LsCoder &rc, WsChannel &ch, uint32_t d, int m, int lane, bool single) {
+  uint2 *const kc = ch.pieces;
+  const uint32_t slot = (d + uint32_t(lane)) & (WS_RING - 1u);
+  const bool active = lane < m;
+  const uint32_t w = active ? ch.ring[slot] : (uint32_t(CABAC_CMD_EP) << 29);
+  const uint32_t r = ch.rng[slot];
+  const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+  const uint32_t lps = (((w & 63u) * (r >> 5)) >> 1) + 4;
+  const uint32_t rmps = r - lps;
+  const bool isLps = (w & 64u) != 0;
+  const uint32_t nr = isLps ? lps : rmps;
+  const uint32_t sh = uint32_t(__clz(int(nr | 7u)) - 23);
+  const uint32_t k = isCtx ? sh : (w >> 24) & 31u;
+  const uint64_t c = isCtx ? (isLps ? uint64_t(rmps) << sh : 0ull) : uint64_t(r) * (w & 0xFFFFFFu);
+  // inclusive prefix sum of the shifts
+  uint32_t P = k;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(FULL, P, o);
+    if (lane >= o) P += t;
+  }
+  const uint32_t E = P - k;
+  const uint32_t g = single ? uint32_t(lane) : E >> CABAC_WS_WINDOW_BITS;
+  const uint32_t gPrev = __shfl_up_sync(FULL, g, 1);
+  const bool head = active && (lane == 0 || g != gPrev);
+  const uint32_t heads = __ballot_sync(FULL, head);
+  // last lane of this lane's piece: the one before the next head (or the last active lane)
+  const uint32_t above = heads & ~((2u << lane) - 1u);
+  const int last = (above ? __ffs(int(above)) - 1 : m) - 1;
+  const uint32_t Pend = __shfl_sync(FULL, P, last & 31);
+  const uint64_t v = active ? c << (Pend - P) : 0ull;
+  // inclusive 64-bit prefix sum of the aligned addends (< 32 * 2^49)
+  uint64_t X = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint64_t t = __shfl_up_sync(FULL, X, o);
+    if (lane >= o) X += t;
+  }
+  const uint64_t Xprev = __shfl_up_sync(FULL, X, 1), Xlast = __shfl_sync(FULL, X, last & 31);
+  const uint32_t Pprev = __shfl_up_sync(FULL, P, 1);
+  if (head) {
+    const uint64_t C = Xlast - (lane ? Xprev : 0ull);
+    const uint32_t K = Pend - (lane ? Pprev : 0u);
+    kc[__popc(heads & ((1u << lane) - 1u))] = make_uint2(uint32_t(C), (uint32_t(C >> 32) << 8) | K);
+  }
+  __syncwarp();
+  const int pieces = __popc(heads);
+#pragma unroll 1
+  for (int i = 0; i < pieces; i++) {
+    const uint2 e = kc[i];
+    const uint32_t K = e.y & 0xFFu;
+    rc.low = (rc.low << K) + ((uint64_t(e.y >> 8) << 32) | e.x);
+    rc.bitsLeft -= int(K);
+    rc.flushBits();
+  }
+  __syncwarp();
+}
 
 }  // namespace cabac

@@ -168,8 +168,18 @@ int cabac_sync(cabac_handle *h);
  * substream does binarisation and arithmetic coding (few, long substreams);
  * TWO_STAGE = warps binarise and resolve probabilities into command words,
  * then one thread per substream runs the interval coder (many substreams).
- * Both are byte-identical.  Also settable with CABAC_B200_ENCODER=fused|two_stage. */
-enum { CABAC_ENCODER_AUTO = 0, CABAC_ENCODER_FUSED = 1, CABAC_ENCODER_TWO_STAGE = 2 };
+ * WARP_SPECIALISED (residual TU lists only; experimental, never chosen by AUTO) =
+ * producer warps binarise and resolve, one walker warp per CTA runs the range
+ * recurrence of all of them lane-parallel, the producers fold their words into the
+ * code value in lane-parallel groups.
+ * All are byte-identical.  Also settable with
+ * CABAC_B200_ENCODER=fused|two_stage|warp_specialised. */
+enum {
+  CABAC_ENCODER_AUTO = 0,
+  CABAC_ENCODER_FUSED = 1,
+  CABAC_ENCODER_TWO_STAGE = 2,
+  CABAC_ENCODER_WARP_SPECIALISED = 3
+};
 int cabac_set_encoder_mode(cabac_handle *h, int mode);
 const char *cabac_last_error(cabac_handle *h);
 const char *cabac_version(void);

@@ -225,7 +225,7 @@ def test_residual_random_vs_oracle(engine, oracle, seed, flags, kw):
             assert (od[0][lo:hi] == d["coeffs"][lo:hi]).all() and od[1] == int(d["bits_read"][i])
 
 
-@pytest.mark.parametrize("mode", [1, 2], ids=["fused", "two_stage"])
+@pytest.mark.parametrize("mode", [1, 2, 3], ids=["fused", "two_stage", "warp_specialised"])
 @pytest.mark.parametrize("seed,flags,kw", [
     (301, None, {}),
     (302, T | SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3, "bdpcm_fraction": 0.1}),
@@ -234,7 +234,7 @@ def test_residual_random_vs_oracle(engine, oracle, seed, flags, kw):
     (305, T, {"preset": "qp0", "tus_per_sub": (20, 40), "ts_fraction": 0.0}),
 ])
 def test_residual_encoder_variants(engine, oracle, mode, seed, flags, kw):
-    """Both residual encoders (fused lockstep kernel, two-stage P + D) against the oracle, byte for byte."""
+    """The residual encoders (fused lockstep kernel, two-stage P + D, warp-specialised) against the oracle, byte for byte."""
     engine.set_encoder_mode(mode)
     try:
         wl = W.random_substreams(70, seed, flags=flags, **kw)
