@@ -227,4 +227,54 @@ class DecodeBatch {
   std::vector<uint32_t> bins_, bitsRead_, status_;
 };
 
+// RDO bit estimation of a batch of candidates (CABACWriter::residual_coding on a BitEstimator_Std,
+// arith_codec.cpp:603-711): every candidate is a TU list priced from its own starting contexts
+// (`ctxIn`: the Ctx snapshot the encoder's RDO loop restores between candidates, or null for a fresh
+// Ctx::init(qp, initId)).  One launch prices them all.
+class EstimateBatch {
+ public:
+  size_t add(const cabac_substream_params &p, const cabac_tu_desc *tus, size_t ntu,
+             const cabac_ctx_model *ctxIn = nullptr) {
+    const size_t i = params_.size();
+    tus_.insert(tus_.end(), tus, tus + ntu);
+    tuOff_.push_back(tus_.size());
+    params_.push_back(p);
+    if (ctxIn) {
+      haveCtxIn_ = true;
+      ctxIn_.resize((i + 1) * CABAC_NUM_CTX, cabac_ctx_model{0, 0});
+      std::copy(ctxIn, ctxIn + CABAC_NUM_CTX, ctxIn_.begin() + i * CABAC_NUM_CTX);
+      params_.back().flags |= CABAC_SUB_CTX_IN;
+    }
+    return i;
+  }
+  size_t size() const { return params_.size(); }
+  void flush(Engine &eng, const int32_t *coeffs, size_t nCoeffs, bool wantCtx = false) {
+    const size_t n = params_.size();
+    est_.assign(n, 0);
+    perTu_.assign(tus_.size(), 0);
+    status_.assign(n, 0);
+    if (wantCtx) ctxOut_.assign(n * CABAC_NUM_CTX, cabac_ctx_model{0, 0});
+    if (!n) return;
+    if (haveCtxIn_) ctxIn_.resize(n * CABAC_NUM_CTX, cabac_ctx_model{0, 0});
+    const int rc = cabac_estimate_residual_bits(eng.get(), tus_.data(), tuOff_.data(), params_.data(), n, coeffs, nCoeffs,
+                                                haveCtxIn_ ? ctxIn_.data() : nullptr, est_.data(), perTu_.data(),
+                                                nullptr, nullptr, wantCtx ? ctxOut_.data() : nullptr, status_.data());
+    eng.check(rc, "cabac_estimate_residual_bits");
+  }
+  // BitEstimatorBase::getEstFracBits() after the candidate's last TU / after its k-th TU (1/32768 bit)
+  uint64_t fracBits(size_t i) const { return est_[i]; }
+  uint64_t fracBitsAfterTu(size_t i, size_t k) const { return perTu_[tuOff_[i] + k]; }
+  uint32_t status(size_t i) const { return status_[i]; }
+  const cabac_ctx_model *ctx(size_t i) const { return ctxOut_.empty() ? nullptr : &ctxOut_[i * CABAC_NUM_CTX]; }
+  void clear() { *this = EstimateBatch(); }
+
+ private:
+  std::vector<uint64_t> tuOff_{0}, est_, perTu_;
+  std::vector<cabac_tu_desc> tus_;
+  std::vector<cabac_substream_params> params_;
+  std::vector<cabac_ctx_model> ctxIn_, ctxOut_;
+  std::vector<uint32_t> status_;
+  bool haveCtxIn_ = false;
+};
+
 }  // namespace cabac_b200

@@ -7,6 +7,7 @@
 //   B2 TU seam   : GpuBinEncoder::residual_coding markers              -> binarisation on GPU
 //   C  decode    : GpuResidualReader on bytes_ref -> coefficients, mtsIdx, CUCtx flags,
 //                  compared with CABACReader(BinDecoder_Std) on the same bytes
+//   D  estimate  : EstimateBatch vs CABACWriter(BitEstimator_Std): getEstFracBits() after every TU
 // All of B1, B2 must equal A byte for byte (after the caller's writeByteAlignment), with equal
 // getNumBins() and final contexts; C must return what the reference's reader returns (= the
 // encoder's input wherever sign hiding is off).
@@ -291,11 +292,42 @@ int main(int argc, char **argv) {
       }
   }
 
+  // ---- D: RDO bit estimates: the reference's CABACWriter on its BitEstimator_Std vs EstimateBatch ----
+  size_t totalFrac = 0;
+  {
+    EstimateBatch batch;
+    std::vector<std::vector<uint64_t>> want(nSub);
+    for (int i = 0; i < nSub; i++) {
+      const SubSpec &s = subs[i];
+      Harness hs(s.p, false);
+      BitEstimator_Std est;
+      CABACWriter wr(est);
+      est.reset(s.p.qp, s.p.init_id);
+      for (const cabac_tu_desc &d : s.tus) {
+        TuPair tp;
+        makeTu(tp, hs, d, slab.data());
+        applyTsAllowed(tp, d, false);
+        CUCtx cuCtx(s.p.qp);
+        wr.residual_coding(tp.tu, ComponentID(d.comp_id), &cuCtx);
+        want[i].push_back(est.getEstFracBits());
+      }
+      batch.add(s.p, s.tus.data(), s.tus.size());
+    }
+    batch.flush(eng, slab.data(), slab.size());
+    for (int i = 0; i < nSub; i++) {
+      EXPECT(batch.fracBits(i) == want[i].back(), "substream %d: estimate %llu vs BitEstimator_Std %llu", i,
+             (unsigned long long)batch.fracBits(i), (unsigned long long)want[i].back());
+      for (size_t t = 0; t < want[i].size(); t++)
+        EXPECT(batch.fracBitsAfterTu(i, t) == want[i][t], "substream %d TU %zu: running estimate differs", i, t);
+      totalFrac += want[i].back();
+    }
+  }
+
   if (g_fail) {
     fprintf(stderr, "DROPIN FAILED: %d mismatches\n", g_fail);
     return 1;
   }
-  printf("DROPIN OK substreams=%d bins=%zu bytes=%zu launches=%llu\n", nSub, totalBins, totalBytes,
-         (unsigned long long)cabac_launch_count(eng.get()));
+  printf("DROPIN OK substreams=%d bins=%zu bytes=%zu estimated_bits=%zu launches=%llu\n", nSub, totalBins, totalBytes,
+         totalFrac >> 15, (unsigned long long)cabac_launch_count(eng.get()));
   return 0;
 }
