@@ -227,6 +227,8 @@ cabac::Sched chunkSched(const cabac::Sched &base, size_t s0, int k) {
 
 // From this many substreams on, stage D (32 substreams per warp) fills the machine.
 constexpr size_t kTwoStageMinSubstreams = 32768;
+// AUTO: the warp-specialised fused kernel from here up to the two-stage threshold (148 SMs x 19 producers x 2)
+constexpr size_t kWarpSpecialisedMinSubstreams = 5624;
 
 #define CK(call, what)                                   \
   do {                                                   \
@@ -417,6 +419,9 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
                 (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
   if (sc.twoStage) CK(ensureCmdSlab(h, sc, n_sub), "command slab");
   sc.cmdBuf = h->cmdBuf;
+  // In between (every producer slot of the GPU filled at least twice): the warp-specialised kernel.
+  sc.warpSpecialised = h->encoderMode == CABAC_ENCODER_WARP_SPECIALISED ||
+                       (h->encoderMode == CABAC_ENCODER_AUTO && !sc.twoStage && n_sub >= kWarpSpecialisedMinSubstreams);
   CK(cabac::launchEncodeResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out, out_offsets,
                                  out_sizes, num_bins, tu_flags, ctx_out, status),
      "encode_residual kernels");

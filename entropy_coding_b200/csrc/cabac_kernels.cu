@@ -668,16 +668,67 @@ constexpr int WS_THREADS = (WS_PRODUCERS + 1) * 32;
 #define CABAC_WS_MIN_CTAS 1
 #endif
 constexpr int WS_MIN_CTAS = CABAC_WS_MIN_CTAS;
-constexpr size_t WS_SMEM_BYTES = WS_PRODUCERS * (sizeof(FusedEncWarpSmem) + sizeof(WsChannel));
+// Producer warp of the warp-specialised kernel: shared memory per substream in flight is what limits
+// the producers per SM, so a context is 4 bytes of state here; what depends on the context index alone
+// (the window shifts and the "bin == 1" increment, y/z/w of ctx_entry) is one table per CTA.
+struct __align__(16) WsEncWarpSmem {
+  uint32_t ctx[(RCTX + 3) & ~3];
+  uint8_t ring[STAGE_BYTES];
+  int32_t raw[32 * 32];
+  int16_t tile[32 * 32];
+  uint32_t queue[QUEUE_WORDS];
+  uint16_t cgMask[64];
+};
+constexpr size_t WS_RATES_BYTES = RCTX * sizeof(uint4);
+constexpr size_t WS_SMEM_BYTES = WS_PRODUCERS * (sizeof(WsEncWarpSmem) + sizeof(WsChannel)) + WS_RATES_BYTES;
 
 template <bool kWs>
-__device__ __forceinline__ FusedEncWarpSmem &fusedEncSmem(int wib) {
+__device__ __forceinline__ auto &fusedEncSmem(int wib) {
   if constexpr (kWs) {
     extern __shared__ __align__(16) unsigned char wsDynSmem[];
-    return reinterpret_cast<FusedEncWarpSmem *>(wsDynSmem)[wib];
+    return reinterpret_cast<WsEncWarpSmem *>(wsDynSmem)[wib];
   } else {
     __shared__ FusedEncWarpSmem smem[WARPS_PER_BLOCK];
     return smem[wib];
+  }
+}
+
+// contexts of a warp-specialised producer: the state word only (x of ctx_entry)
+__device__ inline void loadCtxStates(uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                     size_t sub, int lane) {
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int k = lane; k < RCTX; k += 32) {
+    const int id = rctx_inv(k);
+    if (imp) {
+      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+      ctx[k] = ctx_entry(m.state0, m.state1, 0).x;
+    } else {
+      ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], 0).x;
+    }
+  }
+  __syncwarp();
+}
+__device__ inline void storeCtxStates(const uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
+                                      cabac_ctx_model *ctxOut, size_t sub, int lane) {
+  if (!ctxOut) return;
+  __syncwarp();
+  const int qp = clipQp(p.qp);
+  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
+  for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+    cabac_ctx_model m;
+    if (is_residual_ctx(id)) {
+      const uint32_t x = ctx[rctx(id)];
+      m.state0 = uint16_t(x >> 16);
+      m.state1 = uint16_t(x & 0xFFFFu);
+    } else if (imp) {
+      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else {
+      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
+      m.state0 = uint16_t(model_state0(w));
+      m.state1 = uint16_t(model_state1(w));
+    }
+    ctxOut[sub * CABAC_NUM_CTX + id] = m;
   }
 }
 
@@ -697,10 +748,17 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
   constexpr bool kWs = kMode == FUSED_WS;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   WsChannel *chan = nullptr;
+  uint4 *wsRates = nullptr;
   uint32_t chHead = 0, drained = 0;
   if constexpr (kWs) {
     WsChannel *chans = reinterpret_cast<WsChannel *>(&fusedEncSmem<true>(WS_PRODUCERS));
     if (threadIdx.x < WS_PRODUCERS) chans[threadIdx.x].head = chans[threadIdx.x].tail = chans[threadIdx.x].want = 0;
+    wsRates = reinterpret_cast<uint4 *>(chans + WS_PRODUCERS);
+    for (int k = threadIdx.x; k < RCTX; k += WS_THREADS) {
+      uint4 e = ctx_entry(0, 0, CABAC_CTX_INIT_TABLE[3][rctx_inv(k)]);
+      e.x = 0;
+      wsRates[k] = e;
+    }
     __syncthreads();
     if (wib == WS_PRODUCERS) {
       wsWalk(chans, lane);
@@ -708,11 +766,12 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     }
     chan = chans + wib;
   }
-  FusedEncWarpSmem &sm = fusedEncSmem<kWs>(wib);
+  auto &sm = fusedEncSmem<kWs>(wib);
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    if constexpr (kWs) loadCtxStates(sm.ctx, p, ctxIn, sub, lane);
+    else loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
     if constexpr (kWs) {  // the ring is empty here: every substream ends fully drained
       wsPushWord(*chan, chHead, WS_MK_CTL(WS_OP_START), lane);
       drained = chHead;
@@ -884,7 +943,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         est += lsEstimateQueue(sm.ctx, sm.queue, nq, lane, CABAC_FRAC_BITS, estBins);
         if (endTu && estPerTu && lane == 0) estPerTu[t - 1] = est;
       } else if constexpr (kWs) {
-        rc.nbins += lsResolveQueue<false>(sm.ctx, sm.queue, nq, lane);
+        rc.nbins += lsResolveQueueStates(sm.ctx, wsRates, sm.queue, nq, lane);
         wsDrain(uint32_t(nq), false);
         if (nq) wsPush(*chan, chHead, sm.queue, nq, lane);
       } else if constexpr (kResolve) {
@@ -927,7 +986,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       if (numBins) numBins[sub] = nb;
       if (status) status[sub] = st;
     }
-    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    if constexpr (kWs) storeCtxStates(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    else storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
     __syncwarp();
   }
   if constexpr (kWs) {  // nobody waits for EXIT to be taken: mark the channel urgent for good

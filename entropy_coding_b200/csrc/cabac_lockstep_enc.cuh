@@ -559,6 +559,40 @@ __device__ __forceinline__ uint32_t lsResolveQueue(uint4 *ctx, uint32_t *queue, 
 }
 
 
+// lsResolveQueue for the warp-specialised producers: 4-byte context states, the per-index constants
+// (y, z, w of ctx_entry) in one table shared by the CTA.
+__device__ __forceinline__ uint32_t lsResolveQueueStates(uint32_t *ctx, const uint4 *rates, uint32_t *queue, int n,
+                                                         int lane) {
+  uint32_t bins = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    uint32_t w = i < n ? queue[i] : (uint32_t(CABAC_CMD_EP) << 29);
+    const bool isCtx = (w >> 29) == CABAC_CMD_CTX;
+    const uint32_t idx = w & 511u, bin = (w >> 9) & 1u;
+    const uint32_t peers = __match_any_sync(FULL, isCtx ? idx : (0x8000u | uint32_t(lane)));
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int rounds = __reduce_max_sync(FULL, isCtx ? rank : 0);
+    const uint4 k = rates[isCtx ? idx : 0u];
+    for (int r = 0; r <= rounds; r++) {
+      if (isCtx && rank == r) {
+        const uint32_t x = ctx[idx];
+        const uint32_t q = ((x >> 16) + (x & 0xFFFFu)) >> 8;
+        const uint32_t mps = q >> 7;
+        const uint32_t qq = q ^ (0xFFu & (0u - mps));
+        const uint32_t d0 = (x >> k.z) & (MASK_0 << 16);
+        const uint32_t d1 = ((x & 0xFFFFu) >> k.w) & MASK_1;
+        ctx[idx] = x - d0 - d1 + (bin ? k.y : 0u);
+        w = (qq >> 2) | ((bin ^ mps) << 6);
+      }
+      __syncwarp();
+    }
+    if (i < n) queue[i] = w;
+    bins += __reduce_add_sync(FULL, i < n ? (isCtx ? 1u : ((w >> 29) == CABAC_CMD_EP ? (w >> 24) & 31u : 0u)) : 0u);
+  }
+  __syncwarp();
+  return bins;
+}
+
 // The RDO bit estimator (BitEstimator_Std, arith_codec.cpp:603-711) over one queue: the same
 // rank-serialised model walk as lsResolveQueue, but what leaves is the 15-bit fixed-point cost of the
 // words - m_binFracBits[state()][bin] for a context-coded bin BEFORE its update (estFracBitsUpdate,
@@ -760,7 +794,7 @@ struct RangeCoder {
 //       LsCoder takes one group - two to five output bytes - per serial step.
 // ===========================================================================
 #ifndef CABAC_WS_PRODUCERS
-#define CABAC_WS_PRODUCERS 16
+#define CABAC_WS_PRODUCERS 19
 #endif
 #ifndef CABAC_WS_WINDOW_BITS
 #define CABAC_WS_WINDOW_BITS 4
@@ -819,8 +853,14 @@ __device__ __forceinline__ void wsPushWord(WsChannel &ch, uint32_t &head, uint32
 //    is one shared-memory round trip plus the dependent range steps (~9 instructions each).
 constexpr int WS_WALK_UNROLL = 4;
 constexpr int WS_WALK_ROUNDS = 8;
-constexpr uint32_t WS_WALK_BACKLOG = 16;  // words that make a channel "ready"
-constexpr int WS_WALK_MIN_READY = WS_PRODUCERS / 2;
+#ifndef CABAC_WS_BACKLOG
+#define CABAC_WS_BACKLOG 16
+#endif
+#ifndef CABAC_WS_MIN_READY
+#define CABAC_WS_MIN_READY (CABAC_WS_PRODUCERS / 2)
+#endif
+constexpr uint32_t WS_WALK_BACKLOG = CABAC_WS_BACKLOG;  // words that make a channel "ready"
+constexpr int WS_WALK_MIN_READY = CABAC_WS_MIN_READY;
 __device__ __forceinline__ void wsWalk(WsChannel *chans, int lane) {
   bool alive = lane < WS_PRODUCERS;
   WsChannel &ch = chans[alive ? lane : 0];
