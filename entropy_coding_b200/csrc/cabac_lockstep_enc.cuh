@@ -851,8 +851,14 @@ __device__ __forceinline__ void wsPushWord(WsChannel &ch, uint32_t &head, uint32
 //    32 words from every channel in one go: few issue slots are spent on mostly idle lanes.
 //  * WS_WALK_UNROLL words per lane and round: their loads are issued together, the critical path
 //    is one shared-memory round trip plus the dependent range steps (~9 instructions each).
-constexpr int WS_WALK_UNROLL = 4;
-constexpr int WS_WALK_ROUNDS = 8;
+#ifndef CABAC_WS_UNROLL
+#define CABAC_WS_UNROLL 4
+#endif
+#ifndef CABAC_WS_ROUNDS
+#define CABAC_WS_ROUNDS 8
+#endif
+constexpr int WS_WALK_UNROLL = CABAC_WS_UNROLL;
+constexpr int WS_WALK_ROUNDS = CABAC_WS_ROUNDS;
 #ifndef CABAC_WS_BACKLOG
 #define CABAC_WS_BACKLOG 16
 #endif
