@@ -1591,10 +1591,13 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
   if (nSub == 0) return cudaSuccess;
   if (!sc.twoStage) {
     if (sc.warpSpecialised && nSub < (size_t(1) << 27)) {
-      static const cudaError_t attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS>,
-                                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                           int(WS_SMEM_BYTES));
-      if (attr != cudaSuccess) return attr;
+      static bool optedIn[64] = {};  // the > 48 KB dynamic shared memory opt-in is per device
+      if (device < 0 || device >= 64 || !optedIn[device]) {
+        const cudaError_t attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS>,
+                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, int(WS_SMEM_BYTES));
+        if (attr != cudaSuccess) return attr;
+        if (device >= 0 && device < 64) optedIn[device] = true;
+      }
       int sms = 148;
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
       const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
