@@ -79,6 +79,9 @@ __device__ __forceinline__ uint32_t tuCmdCapacity(const cabac_tu_desc &d) {
 }
 
 // encode: one streaming pass over the coefficients, ~2 bins per significant bit
+// One CTA (8 warps) per substream: warp w takes the descriptor groups w, w + 8, ... of 32 blocks each
+// (one coalesced descriptor load per group, broadcast by shuffle), so a long substream is no longer one
+// warp's chain of dependent loads.
 __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__restrict__ tus,
                                                          const uint64_t *__restrict__ tuOffsets,
                                                          const int32_t *__restrict__ coeffs, size_t n,
@@ -86,50 +89,69 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          uint32_t *__restrict__ capWords,
                                                          const uint64_t *__restrict__ rawOffsets,
                                                          const cabac_substream_params *__restrict__ params) {
-  const int lane = threadIdx.x & 31;
-  const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
-  for (size_t s = warp; s < n; s += nWarps) {
+  __shared__ uint32_t sCost, sCap;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  for (size_t s = blockIdx.x; s < n; s += gridDim.x) {
+    if (threadIdx.x == 0) {
+      sCost = 0;
+      sCap = 0;
+    }
+    __syncthreads();
     uint32_t c = 0, cap = 0;
-    if (rawOffsets) {  // recorded commands: one word each, REM commands may become two
+    if (rawOffsets && threadIdx.x == 0) {  // recorded commands: one word each, REM commands may become two
       const uint32_t nRaw = uint32_t(rawOffsets[s + 1] - rawOffsets[s]);
       cap = 2u * nRaw;
-      c = lane == 0 ? nRaw : 0u;
+      c = nRaw;
     }
-    for (uint64_t t = tus ? tuOffsets[s] : 0, te = tus ? tuOffsets[s + 1] : 0; t < te; t++) {
-      const cabac_tu_desc d = tus[t];
-      const int32_t *src = coeffs + d.coeff_offset;
-      const int total = 1 << (d.log2_w + d.log2_h);
-      cap += tuCmdCapacity(d);
-      if (!coeffs) {
-        // zero-copy launches (the slab stays in pinned host memory): no pass over the coefficients;
-        // estimate from the block area, the slice QP (bins per coefficient fall ~4x per 20 QP steps)
-        // and transform skip (no frequency decay: ~1.5x the bins)
-        if (lane == 0) {
-          const int q = 70 - int(params ? params[s].qp : 32);
-          c += (uint32_t(total) * uint32_t(q * q) >> 6) * ((d.flags & CABAC_TU_TS) ? 3u : 2u);
-        }
-        continue;
-      }
-      if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
-        for (int i = lane * 4; i < total; i += 128) {
-          const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
-          c += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
-               (v.z ? 2 * (33 - __clz(abs(v.z))) : 0) + (v.w ? 2 * (33 - __clz(abs(v.w))) : 0);
-        }
-      } else {
-        for (int i = lane; i < total; i += 32) {
-          const int v = __ldg(src + i);
-          c += v ? 2 * (33 - __clz(abs(v))) : 0;
+    const uint64_t t0 = tus ? tuOffsets[s] : 0, te = tus ? tuOffsets[s + 1] : 0;
+    const int q = 70 - int(params ? params[s].qp : 32);
+    for (uint64_t base = t0 + uint64_t(wib) * 32u; base < te; base += 8u * 32u) {
+      const bool have = base + uint64_t(lane) < te;
+      cabac_tu_desc dl = {};
+      if (have) dl = tus[base + uint64_t(lane)];
+      const uint32_t area = have ? 1u << (dl.log2_w + dl.log2_h) : 0u;
+      if (have) {
+        cap += tuCmdCapacity(dl);
+        if (!coeffs) {
+          // zero-copy launches (the slab stays in pinned host memory): no pass over the coefficients;
+          // estimate from the block area, the slice QP (bins per coefficient fall ~4x per 20 QP steps)
+          // and transform skip (no frequency decay: ~1.5x the bins)
+          c += (area * uint32_t(q * q) >> 6) * ((dl.flags & CABAC_TU_TS) ? 3u : 2u);
+        } else {
+          c += 8u + (area >> 4);
         }
       }
-      c += lane == 0 ? 8u + (uint32_t(total) >> 4) : 0u;
+      if (!coeffs) continue;
+      const int cnt = int(min(uint64_t(32), te - base));
+      for (int j = 0; j < cnt; j++) {
+        const int32_t *src = coeffs + __shfl_sync(FULL, dl.coeff_offset, j);
+        const int total = int(__shfl_sync(FULL, area, j));
+        if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
+          for (int i = lane * 4; i < total; i += 128) {
+            const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
+            c += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
+                 (v.z ? 2 * (33 - __clz(abs(v.z))) : 0) + (v.w ? 2 * (33 - __clz(abs(v.w))) : 0);
+          }
+        } else {
+          for (int i = lane; i < total; i += 32) {
+            const int v = __ldg(src + i);
+            c += v ? 2 * (33 - __clz(abs(v))) : 0;
+          }
+        }
+      }
     }
     c = __reduce_add_sync(FULL, c);
-    if (lane == 0) {
-      cost[s] = c;
-      if (capWords) capWords[s] = (cap + 3u) & ~3u;  // keeps every substream's slab 16-byte aligned
+    cap = __reduce_add_sync(FULL, cap);
+    if (lane == 0 && (c | cap)) {
+      atomicAdd(&sCost, c);
+      atomicAdd(&sCap, cap);
     }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      cost[s] = sCost;
+      if (capWords) capWords[s] = (sCap + 3u) & ~3u;  // keeps every substream's slab 16-byte aligned
+    }
+    __syncthreads();
   }
 }
 
@@ -1574,7 +1596,7 @@ cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, con
                                 const uint64_t *rawOffsets, const cabac_substream_params *params) {
   (void)device;
   if (nSub == 0) return cudaSuccess;
-  cost_coeff_kernel<<<costGrid(nSub, 8), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
+  cost_coeff_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
                                                      params);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;

@@ -313,6 +313,18 @@ def test_residual_all_shapes_single_coeff(engine, oracle):
         assert outs[i].tobytes() == eb.tobytes(), (i, tus[i])
     d = engine.decode_residual(np.concatenate(outs), offsets_of(r["sizes"]), tus, wl.tu_offsets, params, coeffs.size)
     assert (d["coeffs"] == coeffs).all()
+    # the other encoder kernels and the bit estimator on the same shapes
+    for mode in (2, 3):
+        engine.set_encoder_mode(mode)
+        try:
+            r2, outs2 = run_residual(engine, wl)
+        finally:
+            engine.set_encoder_mode(0)
+        assert (r2["sizes"] == r["sizes"]).all() and all(a.tobytes() == b.tobytes() for a, b in zip(outs, outs2)), mode
+    est = engine.estimate_residual_bits(tus, wl.tu_offsets, params, coeffs)
+    for i in range(n):
+        tot, _ = oracle.estimate_residual(tus[i:i + 1], coeffs, 30, 2, T | SUB_DEP_QUANT)
+        assert int(est["est_bits"][i]) == tot, (i, tus[i])
 
 
 def test_residual_errors(engine):
