@@ -624,3 +624,27 @@ def test_estimate_empty_tu_and_empty_batch(engine):
     r = engine.estimate_residual_bits(np.zeros(0, TU_DT), np.zeros(1, np.uint64), np.zeros(0, PARAMS_DT),
                                       np.zeros(0, np.int32))
     assert r["est_bits"].size == 0
+
+
+def test_warp_specialised_matches_fused_randomised(engine):
+    """Hand-off stress: batch shapes around the CTA geometry (19 producers + 1 walker), every output of
+    the warp-specialised kernel against the fused kernel's, repeated (tests/tools/ws_stress.py, bounded)."""
+    rng = np.random.default_rng(77)
+    try:
+        for it in range(24):
+            n_sub = int(rng.choice([1, 7, 19, 20, 148, 500, 3000]))
+            flags = rng.choice([None, 1, 0, 1 | 8, 16, 2, 3])
+            wl = W.random_substreams(n_sub, int(rng.integers(1 << 30)), flags=None if flags is None else int(flags),
+                                     tus_per_sub=(1, int(rng.choice([2, 6, 30]))),
+                                     ts_fraction=float(rng.choice([0.0, 0.2, 0.9])))
+            cap = wl.out_capacity(bytes_per_coeff=5.0)
+            engine.set_encoder_mode(1)
+            a = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap, want_ctx=True)
+            engine.set_encoder_mode(3)
+            for rep in range(2):
+                b = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap, want_ctx=True)
+                assert (a["sizes"] == b["sizes"]).all() and a["out"].tobytes() == b["out"].tobytes(), (it, n_sub)
+                assert (a["num_bins"] == b["num_bins"]).all() and (a["ctx_out"] == b["ctx_out"]).all()
+                assert (a["status"] == b["status"]).all() and (a["tu_flags"] == b["tu_flags"]).all()
+    finally:
+        engine.set_encoder_mode(0)
