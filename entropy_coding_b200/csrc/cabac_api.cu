@@ -408,10 +408,15 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
-  const bool areaCost = h->areaCostNext;
+  static const bool forceAreaCost = getenv("CABAC_B200_AREA_COST") && atoi(getenv("CABAC_B200_AREA_COST"));  // experiment
+  const bool areaCost = h->areaCostNext || forceAreaCost;
   h->areaCostNext = false;
-  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, areaCost ? nullptr : coeffs, nullptr,
-                                params),
+  // Scheduling cost: the area / QP estimate of every block, calibrated on every 32nd block's coefficients
+  // (3 % of the slab: cheap in HBM, affordable over PCIe for a zero-copy slab).  CABAC_B200_COST_SAMPLE_MASK=-1
+  // restores the full pass over the slab (HBM) / the uncalibrated estimate (zero-copy).
+  static const int sampleMask = getenv("CABAC_B200_COST_SAMPLE_MASK") ? atoi(getenv("CABAC_B200_COST_SAMPLE_MASK")) : 31;
+  CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub,
+                                areaCost && sampleMask < 0 ? nullptr : coeffs, nullptr, params, sampleMask),
      "encode prepare kernels");
   // Few long substreams: one warp per substream, fused.  Many substreams: the two-stage coder,
   // whose interval stage runs one substream per thread.

@@ -88,16 +88,24 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          uint32_t *__restrict__ cost,
                                                          uint32_t *__restrict__ capWords,
                                                          const uint64_t *__restrict__ rawOffsets,
-                                                         const cabac_substream_params *__restrict__ params) {
-  __shared__ uint32_t sCost, sCap;
+                                                         const cabac_substream_params *__restrict__ params,
+                                                         int sampleMask) {
+  // sampleMask < 0: every block's coefficients are read (slab in HBM).  Otherwise the slab is pinned host
+  // memory behind PCIe: the cost is the area / QP / transform-skip estimate of all blocks, scaled by
+  // what the estimate misses on the blocks whose index has (index & sampleMask) == 0, which ARE read.
+  __shared__ uint32_t sCost, sCap, sReal, sGuess, sFixed;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   for (size_t s = blockIdx.x; s < n; s += gridDim.x) {
     if (threadIdx.x == 0) {
       sCost = 0;
       sCap = 0;
+      sReal = 0;
+      sGuess = 0;
+      sFixed = 0;
     }
     __syncthreads();
-    uint32_t c = 0, cap = 0;
+    uint32_t c = 0, cap = 0, real = 0, guess = 0, fixed = 0;
+    const bool sampling = coeffs != nullptr && sampleMask >= 0;
     if (rawOffsets && threadIdx.x == 0) {  // recorded commands: one word each, REM commands may become two
       const uint32_t nRaw = uint32_t(rawOffsets[s + 1] - rawOffsets[s]);
       cap = 2u * nRaw;
@@ -110,32 +118,40 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
       cabac_tu_desc dl = {};
       if (have) dl = tus[base + uint64_t(lane)];
       const uint32_t area = have ? 1u << (dl.log2_w + dl.log2_h) : 0u;
+      const bool sampled = have && sampling && ((base + uint64_t(lane) - t0) & uint64_t(sampleMask)) == 0;
       if (have) {
         cap += tuCmdCapacity(dl);
-        if (!coeffs) {
+        if (!coeffs || sampling) {
           // zero-copy launches (the slab stays in pinned host memory): no pass over the coefficients;
           // estimate from the block area, the slice QP (bins per coefficient fall ~4x per 20 QP steps)
           // and transform skip (no frequency decay: ~1.5x the bins)
-          c += (area * uint32_t(q * q) >> 6) * ((dl.flags & CABAC_TU_TS) ? 3u : 2u);
+          const uint32_t e = (area * uint32_t(q * q) >> 6) * ((dl.flags & CABAC_TU_TS) ? 3u : 2u);
+          c += e;
+          if (sampled) guess += e;
+          fixed += 8u + (area >> 4);  // the per-block term of the full count is known from the descriptor
         } else {
           c += 8u + (area >> 4);
         }
       }
       if (!coeffs) continue;
       const int cnt = int(min(uint64_t(32), te - base));
-      for (int j = 0; j < cnt; j++) {
+      uint32_t todo = sampling ? __ballot_sync(FULL, sampled) : (cnt == 32 ? FULL : (1u << cnt) - 1u);
+      uint32_t &acc = sampling ? real : c;
+      while (todo) {
+        const int j = __ffs(int(todo)) - 1;
+        todo &= todo - 1u;
         const int32_t *src = coeffs + __shfl_sync(FULL, dl.coeff_offset, j);
         const int total = int(__shfl_sync(FULL, area, j));
         if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
           for (int i = lane * 4; i < total; i += 128) {
             const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
-            c += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
+            acc += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
                  (v.z ? 2 * (33 - __clz(abs(v.z))) : 0) + (v.w ? 2 * (33 - __clz(abs(v.w))) : 0);
           }
         } else {
           for (int i = lane; i < total; i += 32) {
             const int v = __ldg(src + i);
-            c += v ? 2 * (33 - __clz(abs(v))) : 0;
+            acc += v ? 2 * (33 - __clz(abs(v))) : 0;
           }
         }
       }
@@ -146,9 +162,24 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
       atomicAdd(&sCost, c);
       atomicAdd(&sCap, cap);
     }
+    if (sampling) {
+      real = __reduce_add_sync(FULL, real);
+      guess = __reduce_add_sync(FULL, guess);
+      fixed = __reduce_add_sync(FULL, fixed);
+      if (lane == 0 && (real | guess | fixed)) {
+        atomicAdd(&sReal, real);
+        atomicAdd(&sGuess, guess);
+        atomicAdd(&sFixed, fixed);
+      }
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
-      cost[s] = sCost;
+      // sampled blocks: `real` counts what the HBM pass counts (2 per significant bit), `guess` is the
+      // estimate of the same blocks; the ratio corrects the estimate of all blocks
+      cost[s] = sampling && sGuess
+                    ? uint32_t(min(uint64_t(sCost) * (uint64_t(sReal) + 1u) / (uint64_t(sGuess) + 1u) + sFixed,
+                                   uint64_t(0xFFFFFFFFu)))
+                    : sCost;
       if (capWords) capWords[s] = (sCap + 3u) & ~3u;  // keeps every substream's slab 16-byte aligned
     }
     __syncthreads();
@@ -1593,11 +1624,11 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
 // slab offsets (exclusive scan; cmdOffsets[nSub] = words the slab must hold).
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
-                                const uint64_t *rawOffsets, const cabac_substream_params *params) {
+                                const uint64_t *rawOffsets, const cabac_substream_params *params, int sampleMask) {
   (void)device;
   if (nSub == 0) return cudaSuccess;
   cost_coeff_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
-                                                     params);
+                                                     params, sampleMask);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);

@@ -36,7 +36,8 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status);
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
-                                const uint64_t *rawOffsets, const cabac_substream_params *params = nullptr);
+                                const uint64_t *rawOffsets, const cabac_substream_params *params = nullptr,
+                                int sampleMask = -1);
 cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, const uint32_t *rawCmds,
                                const uint64_t *rawOffsets, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                const cabac_substream_params *params, size_t nSub, const int32_t *coeffs,
