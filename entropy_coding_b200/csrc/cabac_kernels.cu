@@ -67,6 +67,33 @@ __global__ void cost_bytes_kernel(const uint64_t *__restrict__ inOffsets, size_t
   }
 }
 
+// decode: bytes x weight + what every block costs whatever it holds (descriptor handling, clearing and
+// storing its coefficient positions).  One CTA per substream over its descriptors.
+__global__ void __launch_bounds__(256) cost_decode_kernel(const uint64_t *__restrict__ inOffsets,
+                                                          const cabac_tu_desc *__restrict__ tus,
+                                                          const uint64_t *__restrict__ tuOffsets, size_t n,
+                                                          uint32_t byteWeight, uint32_t tuConst, uint32_t areaShift,
+                                                          uint32_t *__restrict__ cost) {
+  __shared__ uint32_t sFixed;
+  for (size_t s = blockIdx.x; s < n; s += gridDim.x) {
+    if (threadIdx.x == 0) sFixed = 0;
+    __syncthreads();
+    uint32_t fixed = 0;
+    for (uint64_t t = tuOffsets[s] + threadIdx.x, te = tuOffsets[s + 1]; t < te; t += blockDim.x) {
+      const cabac_tu_desc d = tus[t];
+      fixed += tuConst + ((1u << (d.log2_w + d.log2_h)) >> areaShift);
+    }
+    fixed = __reduce_add_sync(FULL, fixed);
+    if ((threadIdx.x & 31) == 0 && fixed) atomicAdd(&sFixed, fixed);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint64_t b = (inOffsets[s + 1] - inOffsets[s]) * byteWeight + sFixed;
+      cost[s] = b > 0xFFFFFFFFull ? 0xFFFFFFFFu : uint32_t(b);
+    }
+    __syncthreads();
+  }
+}
+
 // Upper bound of the command words one block can produce: header <= 23,
 // <= 2 per coefficient group (group flag, sign word), context-coded words <= 1.75 A + 8 (the
 // regular-bin budget), <= 3 per coefficient of Golomb-Rice / sign words in the bypass passes.
@@ -89,7 +116,7 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          uint32_t *__restrict__ capWords,
                                                          const uint64_t *__restrict__ rawOffsets,
                                                          const cabac_substream_params *__restrict__ params,
-                                                         int sampleMask) {
+                                                         int sampleMask, uint32_t tuConst, uint32_t areaShift) {
   // sampleMask < 0: every block's coefficients are read (slab in HBM).  Otherwise the slab is pinned host
   // memory behind PCIe: the cost is the area / QP / transform-skip estimate of all blocks, scaled by
   // what the estimate misses on the blocks whose index has (index & sampleMask) == 0, which ARE read.
@@ -128,9 +155,9 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
           const uint32_t e = (area * uint32_t(q * q) >> 6) * ((dl.flags & CABAC_TU_TS) ? 3u : 2u);
           c += e;
           if (sampled) guess += e;
-          fixed += 8u + (area >> 4);  // the per-block term of the full count is known from the descriptor
+          fixed += tuConst + (area >> areaShift);  // the per-block term is known from the descriptor
         } else {
-          c += 8u + (area >> 4);
+          c += tuConst + (area >> areaShift);
         }
       }
       if (!coeffs) continue;
@@ -1627,8 +1654,10 @@ cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, con
                                 const uint64_t *rawOffsets, const cabac_substream_params *params, int sampleMask) {
   (void)device;
   if (nSub == 0) return cudaSuccess;
+  static const int tuConst = getenv("CABAC_B200_ENC_TU_CONST") ? atoi(getenv("CABAC_B200_ENC_TU_CONST")) : 24;
+  static const int areaShift = getenv("CABAC_B200_ENC_AREA_SHIFT") ? atoi(getenv("CABAC_B200_ENC_AREA_SHIFT")) : 4;
   cost_coeff_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
-                                                     params, sampleMask);
+                                                     params, sampleMask, uint32_t(tuConst), uint32_t(areaShift));
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
@@ -1726,7 +1755,16 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status) {
   if (nSub == 0) return cudaSuccess;
-  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
+  // LPT cost of a substream to decode: 8 x bytes + 8 per block + 1/16 per coefficient position (sweep in
+  // DESIGN.md section 4; bytes alone leave 8 % on the table: sparse substreams still pay for their blocks)
+  static const int byteWeight = getenv("CABAC_B200_DEC_BYTE_WEIGHT") ? atoi(getenv("CABAC_B200_DEC_BYTE_WEIGHT")) : 8;
+  static const int tuConst = getenv("CABAC_B200_DEC_TU_CONST") ? atoi(getenv("CABAC_B200_DEC_TU_CONST")) : 8;
+  static const int areaShift = getenv("CABAC_B200_DEC_AREA_SHIFT") ? atoi(getenv("CABAC_B200_DEC_AREA_SHIFT")) : 4;
+  if (byteWeight > 0 && tus)
+    cost_decode_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(inOffsets, tus, tuOffsets, nSub, uint32_t(byteWeight),
+                                                        uint32_t(tuConst), uint32_t(areaShift), sc.cost);
+  else
+    cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
