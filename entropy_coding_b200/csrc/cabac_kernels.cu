@@ -46,7 +46,7 @@ __device__ __forceinline__ int clipQp(int qp) { return qp < 0 ? 0 : (qp > 63 ? 6
 // QP0 CTU carries ~40x the bins of a QP51 one) and each is a serial chain, so
 // the makespan is set by when the longest ones START.  Every launch therefore
 // (1) estimates a cost per substream, (2) orders substreams longest-first with a
-// 256-bucket counting sort on a log-scale key, and (3) runs persistent warps
+// 1024-bucket counting sort on a log-scale key, and (3) runs persistent warps
 // that pull the next substream from an atomic cursor (LPT list scheduling).
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ bool nextSubstream(const uint32_t *__restrict__ order, uint32_t *cursor, size_t nSub,
@@ -213,23 +213,24 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
   }
 }
 
-__device__ __forceinline__ uint32_t costKey(uint32_t c) {  // 3 mantissa bits under the leading one
-  if (c < 8) return c;
+constexpr int COST_BUCKETS = 1024;
+__device__ __forceinline__ uint32_t costKey(uint32_t c) {  // 5 mantissa bits under the leading one (3 % steps)
+  if (c < 32) return c;
   const int e = 31 - __clz(c);
-  return uint32_t(e - 2) * 8u + ((c >> (e - 3)) & 7u);  // 8..247
+  return uint32_t(e - 4) * 32u + ((c >> (e - 5)) & 31u);  // 32..895
 }
 
 __global__ void __launch_bounds__(1024) lpt_order_kernel(const uint32_t *__restrict__ cost, size_t n,
                                                          uint32_t *__restrict__ order, uint32_t *cursor) {
-  __shared__ uint32_t hist[256], start[256];
-  if (threadIdx.x < 256) hist[threadIdx.x] = 0;
+  __shared__ uint32_t hist[COST_BUCKETS], start[COST_BUCKETS];
+  if (threadIdx.x < COST_BUCKETS) hist[threadIdx.x] = 0;
   if (threadIdx.x == 0) *cursor = 0;
   __syncthreads();
   for (size_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(&hist[costKey(cost[i])], 1u);
   __syncthreads();
   if (threadIdx.x == 0) {
     uint32_t acc = 0;
-    for (int b = 255; b >= 0; b--) {  // longest first
+    for (int b = COST_BUCKETS - 1; b >= 0; b--) {  // longest first
       start[b] = acc;
       acc += hist[b];
     }
