@@ -118,6 +118,12 @@ struct LsDecoder {
     const uint32_t sr = rmps << 23;
     const bool isLps = hi >= sr;
     const uint32_t bin = mps ^ uint32_t(isLps);
+    // update
+    const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
+    const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
+    m->x = e.x - d0 - d1 + (bin ? e.y : 0u);
+    // (an early return for "MPS, no renormalisation" - most bins - was measured: 35.6 vs 35.3 ms, the
+    // uniform branch costs what the skipped shifts save)
     // one normalisation rule for both paths: rmps >= 128, so clz gives 0 / 1 for the MPS path and
     // the renormTab value (contexts.cpp:787-789) for the LPS path
     const uint32_t nr = isLps ? lps : rmps;
@@ -125,10 +131,6 @@ struct LsDecoder {
     hi -= isLps ? sr : 0u;
     range = nr << n;
     shiftIn(n);
-    // update
-    const uint32_t d0 = (e.x >> e.z) & (MASK_0 << 16);
-    const uint32_t d1 = ((e.x & 0xFFFFu) >> e.w) & MASK_1;
-    m->x = e.x - d0 - d1 + (bin ? e.y : 0u);
     refill();
     return bin;
   }
