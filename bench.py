@@ -207,6 +207,34 @@ def dev_bytes(t, a: np.ndarray):
     return torch.from_numpy(np.frombuffer(a.tobytes(), np.uint8).copy()).to(t)
 
 
+def bind_to_gpu_numa_node(local_rank: int) -> str:
+    """One process per GPU: run (and first-touch the pinned host slabs) on the NUMA node the GPU hangs off,
+    so the end-to-end leg's PCIe traffic does not cross the socket interconnect.  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        index = int(visible.split(",")[local_rank]) if visible and visible.replace(",", "").isdigit() else local_rank
+        bdf = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bdf = (bdf.decode() if isinstance(bdf, bytes) else bdf).lower()
+        if len(bdf.split(":")[0]) == 8:
+            bdf = bdf[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return "single node"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return f"node {node}: none of its cores allowed"
+        os.sched_setaffinity(0, allowed)
+        return f"node {node}, {len(allowed)} cores"
+    except Exception as e:  # noqa: BLE001 - placement is an optimisation, never a failure
+        return f"unbound ({type(e).__name__})"
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -216,6 +244,7 @@ def run_b200_arm(args):
     rank, local_rank, world = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - entropy_coding_b200 has no CPU fallback")
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else "single process"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -309,7 +338,7 @@ def run_b200_arm(args):
     value = float(tb) / (ms_per_step * 1e-3) / 1e6
     res = dict(wl=wl, cap=cap, eng=eng, value=value, ms_per_step=ms_per_step, t_kernel=t_kernel, clk=clk,
                launches=launches, enc_bins=enc_bins, out_bytes=out_bytes, n_sub=n_sub, n_tu=n_tu, n_co=n_co,
-               world=world, rank=rank, dev=dev, barrier=barrier, all_bins=float(tb))
+               world=world, rank=rank, dev=dev, barrier=barrier, all_bins=float(tb), numa=numa)
     # free the device-resident buffers before the end-to-end leg allocates its own
     del d_out, d_packed, d_dec, d_co
     torch.cuda.empty_cache()
@@ -442,6 +471,7 @@ def main():
         "output_mb_s": r["out_bytes"] / (tk["encode_residual_kernel"] + tk["pack"]) / 1e3,
         "clocks": r["clk"], "gpu_launches": int(r["launches"]), "roofline": roof, "issue_roofline": issue,
         "verified": "decode(encode(x)) == x and equal bin counts on the timed batch",
+        "host_placement": r.get("numa", "n/a"),
     }
     if e2e:
         line["e2e"] = e2e
