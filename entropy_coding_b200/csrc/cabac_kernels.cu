@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
     }
     const uint64_t t0 = tus ? tuOffsets[s] : 0, te = tus ? tuOffsets[s + 1] : 0;
     const int q = 70 - int(params ? params[s].qp : 32);
-    for (uint64_t base = t0 + uint64_t(wib) * 32u; base < te; base += 8u * 32u) {
+    for (uint64_t base = t0 + uint64_t(wib) * 32u; base < te; base += uint64_t(blockDim.x)) {
       const bool have = base + uint64_t(lane) < te;
       cabac_tu_desc dl = {};
       if (have) dl = tus[base + uint64_t(lane)];
@@ -1619,9 +1619,9 @@ static cudaError_t launchOrder(cudaStream_t s, const Sched &sc, size_t nSub) {
   lpt_order_kernel<<<1, 1024, 0, s>>>(sc.cost, nSub, sc.order, sc.cursor);
   return cudaGetLastError();
 }
-static int costGrid(size_t n, int perBlock) {
-  const size_t b = (n + perBlock - 1) / perBlock;
-  return int(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
+static int costGrid(size_t n, int perBlock, int maxPerSm = 16) {
+  const size_t b = (n + perBlock - 1) / perBlock, cap = size_t(148) * maxPerSm;
+  return int(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
@@ -1657,8 +1657,11 @@ cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, con
   if (nSub == 0) return cudaSuccess;
   static const int tuConst = getenv("CABAC_B200_ENC_TU_CONST") ? atoi(getenv("CABAC_B200_ENC_TU_CONST")) : 24;
   static const int areaShift = getenv("CABAC_B200_ENC_AREA_SHIFT") ? atoi(getenv("CABAC_B200_ENC_AREA_SHIFT")) : 4;
-  cost_coeff_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords, rawOffsets,
-                                                     params, sampleMask, uint32_t(tuConst), uint32_t(areaShift));
+  // many substreams are short substreams: one warp each instead of eight
+  const int costThreads = nSub >= 16384 ? 32 : 256;
+  cost_coeff_kernel<<<costGrid(nSub, 1, costThreads == 32 ? 32 : 16), costThreads, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords,
+                                                             rawOffsets, params, sampleMask, uint32_t(tuConst),
+                                                             uint32_t(areaShift));
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
@@ -1761,8 +1764,9 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
   static const int byteWeight = getenv("CABAC_B200_DEC_BYTE_WEIGHT") ? atoi(getenv("CABAC_B200_DEC_BYTE_WEIGHT")) : 8;
   static const int tuConst = getenv("CABAC_B200_DEC_TU_CONST") ? atoi(getenv("CABAC_B200_DEC_TU_CONST")) : 8;
   static const int areaShift = getenv("CABAC_B200_DEC_AREA_SHIFT") ? atoi(getenv("CABAC_B200_DEC_AREA_SHIFT")) : 4;
+  const int costThreads = nSub >= 16384 ? 32 : 256;  // many substreams are short substreams
   if (byteWeight > 0 && tus)
-    cost_decode_kernel<<<costGrid(nSub, 1), 256, 0, s>>>(inOffsets, tus, tuOffsets, nSub, uint32_t(byteWeight),
+    cost_decode_kernel<<<costGrid(nSub, 1, costThreads == 32 ? 32 : 16), costThreads, 0, s>>>(inOffsets, tus, tuOffsets, nSub, uint32_t(byteWeight),
                                                         uint32_t(tuConst), uint32_t(areaShift), sc.cost);
   else
     cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
