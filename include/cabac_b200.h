@@ -168,7 +168,8 @@ int cabac_sync(cabac_handle *h);
  * substream does binarisation and arithmetic coding (few, long substreams);
  * TWO_STAGE = warps binarise and resolve probabilities into command words,
  * then one thread per substream runs the interval coder (many substreams).
- * WARP_SPECIALISED (residual TU lists only; experimental, never chosen by AUTO) =
+ * WARP_SPECIALISED (residual TU lists only; AUTO picks it between 5 624 and 32 768
+ * substreams, where every producer slot of the GPU is filled at least twice) =
  * producer warps binarise and resolve, one walker warp per CTA runs the range
  * recurrence of all of them lane-parallel, the producers fold their words into the
  * code value in lane-parallel groups.
