@@ -648,3 +648,36 @@ def test_warp_specialised_matches_fused_randomised(engine):
                 assert (a["status"] == b["status"]).all() and (a["tu_flags"] == b["tu_flags"]).all()
     finally:
         engine.set_encoder_mode(0)
+
+
+def test_bench_scale_properties_all_encoders(engine):
+    """BASELINE.json's configs[1] batch in full (64 frames 1080p, 8 640 CTU substreams, 199 M coefficient
+    positions), host-pointer API: the size-independent properties the domain offers -
+    decode(encode(x)) == x, bins conserved, every encoder kernel byte-identical (sizes + a checksum of
+    the packed bitstream), and the bit estimate within 1 % of the bits actually written."""
+    import zlib
+    wl = W.frames_as_ctu_substreams(64, 1920, 1080, seed0=3000)
+    assert wl.n_sub >= 5624
+    cap = wl.out_capacity()
+    ref = None
+    try:
+        for mode in (0, 1, 2, 3):
+            engine.set_encoder_mode(mode)
+            r = engine.encode_residual_packed(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap)
+            assert not r["status"].any()
+            sig = (zlib.crc32(r["packed"].tobytes()), zlib.crc32(r["sizes"].tobytes()), zlib.crc32(r["num_bins"].tobytes()),
+                   zlib.crc32(r["tu_flags"].tobytes()))
+            if ref is None:
+                ref, first = sig, r
+            assert sig == ref, f"encoder mode {mode} differs from AUTO"
+    finally:
+        engine.set_encoder_mode(0)
+    r = first
+    d = engine.decode_residual(r["packed"], r["entry_points"], wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size)
+    assert not d["status"].any()
+    assert (d["coeffs"] == wl.coeffs).all() and (d["num_bins"] == r["num_bins"]).all()
+    est = engine.estimate_residual_bits(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, want_per_tu=False)
+    trm = (wl.params["flags"] & SUB_TERMINATE) != 0
+    assert (est["num_bins"] + trm == r["num_bins"]).all()
+    written = 8.0 * float(r["sizes"].astype(np.int64).sum())
+    assert abs(float(est["est_bits"].astype(np.float64).sum()) / 32768.0 / written - 1.0) < 0.01
