@@ -595,22 +595,29 @@ __device__ inline int binariseCG(uint32_t *queue, const int16_t *tile, const TuG
 }
 
 // last_sig_coeff as command words, cabac_writer.cpp:2639-2722 (same words on every lane)
-__device__ __forceinline__ int pushLastSigCoeff(uint32_t *q, const TuGeom &g, int posX, int posY) {
+__device__ __forceinline__ int pushLastSigCoeff(uint32_t *q, const TuGeom &g, int posX, int posY, int lane) {
+  // last_sig_coeff_{x,y}_prefix as unary context-coded bins, then the two bypass suffixes
+  // (cabac_writer.cpp:2812-2860): at most 10 + 10 + 2 words, one lane each
   const uint32_t gx = groupIdx(posX), gy = groupIdx(posY);
   const int bx = lastXBase(g.ch) + g.lastOffsetX, by = lastYBase(g.ch) + g.lastOffsetY;
-  int n = 0;
-  uint32_t k;
-  for (k = 0; k < gx; k++) q[n++] = CABAC_MK_CTX(bx + (k >> g.lastShiftX), 1);
-  if (gx < uint32_t(g.maxLastX)) q[n++] = CABAC_MK_CTX(bx + (k >> g.lastShiftX), 0);
-  for (k = 0; k < gy; k++) q[n++] = CABAC_MK_CTX(by + (k >> g.lastShiftY), 1);
-  if (gy < uint32_t(g.maxLastY)) q[n++] = CABAC_MK_CTX(by + (k >> g.lastShiftY), 0);
+  const uint32_t nX = gx + (gx < uint32_t(g.maxLastX) ? 1u : 0u), nY = gy + (gy < uint32_t(g.maxLastY) ? 1u : 0u);
+  const uint32_t i = uint32_t(lane);
+  if (i < nX) {
+    q[i] = CABAC_MK_CTX(bx + (i >> g.lastShiftX), i < gx);
+  } else if (i < nX + nY) {
+    const uint32_t k = i - nX;
+    q[i] = CABAC_MK_CTX(by + (k >> g.lastShiftY), k < gy);
+  }
+  int n = int(nX + nY);
   if (gx > 3) {
     const uint32_t nb = (gx - 2) >> 1;
-    q[n++] = CABAC_MK_EP((posX - minInGroup(gx)) & ((1u << nb) - 1u), nb);
+    if (lane == 0) q[n] = CABAC_MK_EP((posX - minInGroup(gx)) & ((1u << nb) - 1u), nb);
+    n++;
   }
   if (gy > 3) {
     const uint32_t nb = (gy - 2) >> 1;
-    q[n++] = CABAC_MK_EP((posY - minInGroup(gy)) & ((1u << nb) - 1u), nb);
+    if (lane == 0) q[n] = CABAC_MK_EP((posY - minInGroup(gy)) & ((1u << nb) - 1u), nb);
+    n++;
   }
   return n;
 }
@@ -976,7 +983,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
           if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
           int x, y;
           scanXY(g, scanPosLast, x, y);
-          nq += pushLastSigCoeff(sm.queue + nq, g, x, y);
+          nq += pushLastSigCoeff(sm.queue + nq, g, x, y, lane);
           state = 0;
           remRegBins = regBinLimit(g);
           s = lastCG;
@@ -1243,7 +1250,7 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
           if (g.comp == 0 && !ts && scanPosLast >= 1) res |= CABAC_TUR_MTS_LAST_POS;
           int x, y;
           scanXY(g, scanPosLast, x, y);
-          nq += pushLastSigCoeff(sm.queue + nq, g, x, y);
+          nq += pushLastSigCoeff(sm.queue + nq, g, x, y, lane);
           state = 0;
           remRegBins = regBinLimit(g);
           s = lastCG;
