@@ -800,7 +800,10 @@ struct RangeCoder {
 #define CABAC_WS_WINDOW_BITS 4
 #endif
 constexpr int WS_PRODUCERS = CABAC_WS_PRODUCERS;
-constexpr uint32_t WS_RING = 256;    // words per channel (> QUEUE_WORDS + one drain slice)
+#ifndef CABAC_WS_RING
+#define CABAC_WS_RING 256
+#endif
+constexpr uint32_t WS_RING = CABAC_WS_RING;  // words per channel (a power of two > QUEUE_WORDS + one drain slice)
 constexpr uint32_t WS_KIND_CTL = 6;  // control word: bits 28..27 = op
 constexpr uint32_t WS_OP_START = 0;  // new substream: range = 510
 constexpr uint32_t WS_OP_EXIT = 2;
