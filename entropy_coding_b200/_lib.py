@@ -43,6 +43,10 @@ _SIGS = {
     "cabac_decode_residual_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_estimate_residual_bits": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_estimate_residual_bits_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_residual_ctx_bins": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_residual_ctx_bins_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P]),
+    "cabac_ctx_init_id": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
+    "cabac_ctx_init_id_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
     "cabac_frac_bits_table": (C.c_int, [_P]),
     "cabac_count_emulations": (C.c_int, [_P, _P, _P, _SZ, _P]),
     "cabac_count_emulations_dev": (C.c_int, [_P, _P, _P, _SZ, _P]),

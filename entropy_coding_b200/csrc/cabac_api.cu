@@ -459,12 +459,10 @@ int cabac_encode_stream_dev(cabac_handle *h, const uint32_t *cmds, const uint64_
   return CABAC_OK;
 }
 
-int cabac_estimate_residual_bits_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
-                                     const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
-                                     const cabac_ctx_model *ctx_in, uint64_t *est_bits, uint64_t *est_per_tu,
-                                     uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
-                                     uint32_t *status) {
-  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits_dev");
+static int estimateDev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                       const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                       const cabac_ctx_model *ctx_in, uint64_t *est_bits, uint64_t *est_per_tu, uint32_t *num_bins,
+                       uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status, uint32_t *ctx_bins) {
   DeviceGuard g(h->device);
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
@@ -473,9 +471,37 @@ int cabac_estimate_residual_bits_dev(cabac_handle *h, const cabac_tu_desc *tus, 
   CK(cabac::launchEncodePrepare(h->stream, h->device, sc, tus, tu_offsets, n_sub, coeffs, nullptr, params),
      "estimate prepare kernels");
   CK(cabac::launchEstimateResidual(h->stream, h->device, sc, tus, tu_offsets, params, n_sub, coeffs, ctx_in, est_bits,
-                                   est_per_tu, num_bins, tu_flags, ctx_out, status),
+                                   est_per_tu, num_bins, tu_flags, ctx_out, status, ctx_bins),
      "estimate_residual kernel");
   h->launches += 4;  // cost, order, slab scan (shared prepare), estimate
+  return CABAC_OK;
+}
+
+int cabac_estimate_residual_bits_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                     const cabac_ctx_model *ctx_in, uint64_t *est_bits, uint64_t *est_per_tu,
+                                     uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                     uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits_dev");
+  return estimateDev(h, tus, tu_offsets, params, n_sub, coeffs, ctx_in, est_bits, est_per_tu, num_bins, tu_flags,
+                     ctx_out, status, nullptr);
+}
+
+int cabac_residual_ctx_bins_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                const cabac_ctx_model *ctx_in, uint32_t *ctx_bins, uint32_t *num_bins,
+                                cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !ctx_bins))) return badArg(h, "cabac_residual_ctx_bins_dev");
+  return estimateDev(h, tus, tu_offsets, params, n_sub, coeffs, ctx_in, nullptr, nullptr, num_bins, nullptr, ctx_out,
+                     status, ctx_bins);
+}
+
+int cabac_ctx_init_id_dev(cabac_handle *h, const cabac_substream_params *params, const cabac_ctx_model *ctx_ref,
+                          const uint32_t *ctx_bins, size_t n, uint8_t *choice, uint64_t *costs) {
+  if (!h || (n && (!params || !ctx_ref || !ctx_bins || !choice))) return badArg(h, "cabac_ctx_init_id_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchCtxInitId(h->stream, params, ctx_ref, ctx_bins, n, choice, costs), "ctx_init_id_kernel");
+  h->launches += n ? 1 : 0;
   return CABAC_OK;
 }
 
@@ -738,12 +764,10 @@ int cabac_encode_residual(cabac_handle *h, const cabac_tu_desc *tus, const uint6
   return anySubstreamFailed(hst, n_sub);
 }
 
-int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
-                                 const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
-                                 size_t n_coeffs, const cabac_ctx_model *ctx_in, uint64_t *est_bits,
-                                 uint64_t *est_per_tu, uint32_t *num_bins, uint8_t *tu_flags,
-                                 cabac_ctx_model *ctx_out, uint32_t *status) {
-  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits");
+static int estimateHost(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                        const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs, size_t n_coeffs,
+                        const cabac_ctx_model *ctx_in, uint64_t *est_bits, uint64_t *est_per_tu, uint32_t *num_bins,
+                        uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status, uint32_t *ctx_bins) {
   if (!n_sub) return CABAC_OK;
   DeviceGuard g(h->device);
   const size_t nTu = tu_offsets[n_sub];
@@ -754,10 +778,11 @@ int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, cons
   int32_t *dCoeffs;
   cabac_ctx_model *dCin, *dCout;
   uint8_t *dTuFlags;
-  uint32_t *dBins, *dStatus;
+  uint32_t *dBins, *dStatus, *dCtxBins;
   Arena a(h);
   a.want((void **)&dTus, nTu * sizeof(*tus));
   a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dCtxBins, ctx_bins ? n_sub * CABAC_NUM_CTX * 4 : 0);
   a.want((void **)&dEst, n_sub * 8);
   a.want((void **)&dPerTu, est_per_tu ? nTu * 8 : 0);
   a.want((void **)&dP, n_sub * sizeof(*params));
@@ -773,10 +798,11 @@ int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, cons
   H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCoeffs, coeffs, n_coeffs * 4);
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
-  int rc = cabac_estimate_residual_bits_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dEst,
-                                            est_per_tu ? dPerTu : nullptr, dBins, dTuFlags,
-                                            ctx_out ? dCout : nullptr, dStatus);
+  int rc = estimateDev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dEst,
+                       est_per_tu ? dPerTu : nullptr, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus,
+                       ctx_bins ? dCtxBins : nullptr);
   if (rc) return rc;
+  D2H(ctx_bins, dCtxBins, n_sub * CABAC_NUM_CTX * 4);
   D2H(est_bits, dEst, n_sub * 8);
   D2H(est_per_tu, dPerTu, nTu * 8);
   D2H(num_bins, dBins, n_sub * 4);
@@ -787,6 +813,53 @@ int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, cons
   D2H(hst, dStatus, n_sub * 4);
   CK(cudaStreamSynchronize(h->stream), "sync");
   return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                 const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                                 size_t n_coeffs, const cabac_ctx_model *ctx_in, uint64_t *est_bits,
+                                 uint64_t *est_per_tu, uint32_t *num_bins, uint8_t *tu_flags,
+                                 cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !est_bits))) return badArg(h, "cabac_estimate_residual_bits");
+  return estimateHost(h, tus, tu_offsets, params, n_sub, coeffs, n_coeffs, ctx_in, est_bits, est_per_tu, num_bins,
+                      tu_flags, ctx_out, status, nullptr);
+}
+
+int cabac_residual_ctx_bins(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                            const cabac_substream_params *params, size_t n_sub, const int32_t *coeffs,
+                            size_t n_coeffs, const cabac_ctx_model *ctx_in, uint32_t *ctx_bins, uint32_t *num_bins,
+                            cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!tu_offsets || !params || !ctx_bins))) return badArg(h, "cabac_residual_ctx_bins");
+  return estimateHost(h, tus, tu_offsets, params, n_sub, coeffs, n_coeffs, ctx_in, nullptr, nullptr, num_bins, nullptr,
+                      ctx_out, status, ctx_bins);
+}
+
+int cabac_ctx_init_id(cabac_handle *h, const cabac_substream_params *params, const cabac_ctx_model *ctx_ref,
+                      const uint32_t *ctx_bins, size_t n, uint8_t *choice, uint64_t *costs) {
+  if (!h || (n && (!params || !ctx_ref || !ctx_bins || !choice))) return badArg(h, "cabac_ctx_init_id");
+  if (!n) return CABAC_OK;
+  DeviceGuard g(h->device);
+  cabac_substream_params *dP;
+  cabac_ctx_model *dRef;
+  uint32_t *dBins;
+  uint8_t *dChoice;
+  uint64_t *dCosts;
+  Arena a(h);
+  a.want((void **)&dP, n * sizeof(*params));
+  a.want((void **)&dRef, n * CABAC_NUM_CTX * sizeof(*ctx_ref));
+  a.want((void **)&dBins, n * CABAC_NUM_CTX * 4);
+  a.want((void **)&dChoice, n);
+  a.want((void **)&dCosts, n * 16);
+  CK(a.commit(), "scratch alloc");
+  H2D(dP, params, n * sizeof(*params));
+  H2D(dRef, ctx_ref, n * CABAC_NUM_CTX * sizeof(*ctx_ref));
+  H2D(dBins, ctx_bins, n * CABAC_NUM_CTX * 4);
+  int rc = cabac_ctx_init_id_dev(h, dP, dRef, dBins, n, dChoice, dCosts);
+  if (rc) return rc;
+  D2H(choice, dChoice, n);
+  D2H(costs, dCosts, n * 16);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
 }
 
 int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,

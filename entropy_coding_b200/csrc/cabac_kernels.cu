@@ -830,7 +830,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint32_t *__restrict__ outSizes, uint32_t *__restrict__ numBins,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
-                       uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu) {
+                       uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu,
+                       uint32_t *__restrict__ ctxBins) {
   constexpr bool kResolve = kMode == FUSED_RESOLVE;
   constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
   constexpr bool kWs = kMode == FUSED_WS;
@@ -1028,7 +1029,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       }
       __syncwarp();
       if constexpr (kEstimate) {
-        est += lsEstimateQueue(sm.ctx, sm.queue, nq, lane, CABAC_FRAC_BITS, estBins);
+        est += lsEstimateQueue(sm.ctx, sm.queue, nq, lane, CABAC_FRAC_BITS, estBins,
+                               ctxBins ? ctxBins + size_t(sub) * CABAC_NUM_CTX : nullptr);
         if (endTu && estPerTu && lane == 0) estPerTu[t - 1] = est;
       } else if constexpr (kWs) {
         rc.nbins += lsResolveQueueStates(sm.ctx, wsRates, sm.queue, nq, lane);
@@ -1047,7 +1049,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     if constexpr (kEstimate) {
       total = cap = 0;
       nb = estBins;
-      if (lane == 0) estBits[sub] = est;
+      if (lane == 0 && estBits) estBits[sub] = est;
     } else if constexpr (kWs) {
       // a no-op word (EP, 0 bins) whose recorded range is the one finish() continues from
       wsDrain(1, false);
@@ -1696,17 +1698,17 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
       const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
       encode_residual_kernel<FUSED_WS><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
       return cudaGetLastError();
     }
     if (sc.fusedResolve)
       encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
     else
       encode_residual_kernel<FUSED_LEGACY><<<persistentGrid(encode_residual_kernel<FUSED_LEGACY>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
     return cudaGetLastError();
   }
   produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
@@ -1726,11 +1728,56 @@ cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, 
                                    const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
                                    const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint64_t *estBits,
                                    uint64_t *estPerTu, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
-                                   uint32_t *status) {
+                                   uint32_t *status, uint32_t *ctxBins) {
   if (nSub == 0) return cudaSuccess;
+  if (ctxBins) {  // BinCounter rows: the kernel adds into them
+    const cudaError_t e = cudaMemsetAsync(ctxBins, 0, nSub * CABAC_NUM_CTX * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+  }
   encode_residual_kernel<FUSED_ESTIMATE><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu);
+      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins);
+  return cudaGetLastError();
+}
+
+// xGetCtxInitId (cabac_writer.cpp:41-73) for n non-intra slices: one warp per slice sums
+// numBins(k) * estFracExcessBits(final model k, model k initialised from table B / P)
+// (contexts.cpp:965-968) over the contexts and keeps the cheaper table; ties keep B.
+__global__ void ctx_init_id_kernel(const cabac_substream_params *__restrict__ params,
+                                   const cabac_ctx_model *__restrict__ ctxRef, const uint32_t *__restrict__ ctxBins,
+                                   size_t n, uint8_t *__restrict__ choice, uint64_t *__restrict__ costs) {
+  const int lane = threadIdx.x & 31;
+  const size_t i = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  if (i >= n) return;
+  const cabac_substream_params p = params[i];
+  const int qp = clipQp(p.qp);
+  unsigned long long c0 = 0, c1 = 0;
+  for (int k = lane; k < CABAC_NUM_CTX; k += 32) {
+    const uint32_t nb = ctxBins[i * CABAC_NUM_CTX + k];
+    if (!nb) continue;
+    const cabac_ctx_model m = ctxRef[i * CABAC_NUM_CTX + k];
+    const unsigned long long ns = 2u * ((uint32_t(m.state0) + m.state1) >> 8) + 1u;
+    for (int t = 0; t < 2; t++) {
+      const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[t][k], CABAC_CTX_INIT_TABLE[3][k]);
+      const uint32_t qt = (model_state0(w) + model_state1(w)) >> 8;
+      const unsigned long long x = ((512u - ns) * CABAC_FRAC_BITS[2u * qt] + ns * CABAC_FRAC_BITS[2u * qt + 1u] + 256u) >> 9;
+      (t ? c1 : c0) += nb * x;
+    }
+  }
+  for (int o = 16; o; o >>= 1) {
+    c0 += __shfl_xor_sync(0xFFFFFFFFu, c0, o);
+    c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
+  }
+  if (lane == 0) {
+    choice[i] = p.init_id == 2 ? uint8_t(2) : uint8_t(c1 < c0 ? 1 : 0);  // an intra slice keeps I_SLICE
+    if (costs) costs[2 * i] = c0, costs[2 * i + 1] = c1;
+  }
+}
+
+cudaError_t launchCtxInitId(cudaStream_t s, const cabac_substream_params *params, const cabac_ctx_model *ctxRef,
+                            const uint32_t *ctxBins, size_t n, uint8_t *choice, uint64_t *costs) {
+  if (n == 0) return cudaSuccess;
+  ctx_init_id_kernel<<<unsigned((n + 3) / 4), 128, 0, s>>>(params, ctxRef, ctxBins, n, choice, costs);
   return cudaGetLastError();
 }
 

@@ -53,7 +53,9 @@ cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, 
                                    const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
                                    const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint64_t *estBits,
                                    uint64_t *estPerTu, uint32_t *numBins, uint8_t *tuFlags, cabac_ctx_model *ctxOut,
-                                   uint32_t *status);
+                                   uint32_t *status, uint32_t *ctxBins = nullptr);
+cudaError_t launchCtxInitId(cudaStream_t s, const cabac_substream_params *params, const cabac_ctx_model *ctxRef,
+                            const uint32_t *ctxBins, size_t n, uint8_t *choice, uint64_t *costs);
 cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
                                  const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                                  const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,

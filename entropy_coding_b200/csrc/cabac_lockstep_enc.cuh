@@ -598,8 +598,12 @@ __device__ __forceinline__ uint32_t lsResolveQueueStates(uint32_t *ctx, const ui
 // words - m_binFracBits[state()][bin] for a context-coded bin BEFORE its update (estFracBitsUpdate,
 // contexts.cpp:922-925), numBins << SCALE_BITS for bypass bins (estFracBitsEP, contexts.cpp:882-884).
 // There is no interval and no serial walk.  Returns the (uniform) cost; `bins` as lsResolveQueue.
+// ctxBins (nullable, this substream's CABAC_NUM_CTX counters, zeroed by the caller) is the BinCounter
+// view (BinCounter::addCtx, arith_codec.hpp:72-93): the first lane of each same-context group adds the
+// group's size, the warp owns the row.
 __device__ __forceinline__ uint64_t lsEstimateQueue(uint4 *ctx, const uint32_t *queue, int n, int lane,
-                                                    const uint32_t *__restrict__ fracBits, uint32_t &bins) {
+                                                    const uint32_t *__restrict__ fracBits, uint32_t &bins,
+                                                    uint32_t *ctxBins = nullptr) {
   uint32_t cost = 0;  // this lane's share; <= 2 words of <= 2^20 per slice, queues are << 2^10 slices
   uint32_t nb = 0;
   for (int base = 0; base < n; base += 32) {
@@ -610,6 +614,7 @@ __device__ __forceinline__ uint64_t lsEstimateQueue(uint4 *ctx, const uint32_t *
     const uint32_t peers = __match_any_sync(FULL, isCtx ? idx : (0x8000u | uint32_t(lane)));
     const int rank = __popc(peers & ((1u << lane) - 1u));
     const int rounds = __reduce_max_sync(FULL, isCtx ? rank : 0);
+    if (ctxBins && isCtx && rank == 0) atomicAdd(ctxBins + rctx_inv(int(idx)), uint32_t(__popc(peers)));
     for (int r = 0; r <= rounds; r++) {
       if (isCtx && rank == r) {
         const uint4 e = ctx[idx];

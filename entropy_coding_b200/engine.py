@@ -215,6 +215,33 @@ class CabacEngine:
         return dict(est_bits=est, est_per_tu=per_tu, num_bins=bins, tu_flags=tu_flags, status=status,
                     ctx_out=ctx_out)
 
+    def residual_ctx_bins(self, tus, tu_offsets, params, coeffs, ctx_in=None, raise_on_status=True):
+        """BinEncIf::getNumBins(ctxId) per TU list after residual_coding (BinCounter, arith_codec.hpp:72-93):
+        ctx_bins[n, 379], with the final contexts - the two inputs of CABACWriter::getCtxInitId."""
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs = _np(params, PARAMS_DT), _np(coeffs, np.int32)
+        n = len(params)
+        ctx_bins = np.zeros((n, NUM_CTX), np.uint32)
+        bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT)
+        rc = self.lib.cabac_residual_ctx_bins(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
+                                              coeffs.size, _hp(ctx_in), _hp(ctx_bins), _hp(bins), _hp(ctx_out),
+                                              _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(ctx_bins=ctx_bins, num_bins=bins, ctx_out=ctx_out, status=status)
+
+    def ctx_init_id(self, params, ctx_ref, ctx_bins):
+        """CABACWriter::getCtxInitId (cabac_writer.cpp:41-81) for n slices: (choice[n], costs[n, 2])."""
+        params, ctx_ref = _np(params, PARAMS_DT), _np(ctx_ref, CTX_DT)
+        ctx_bins = _np(ctx_bins, np.uint32)
+        n = len(params)
+        choice, costs = np.zeros(n, np.uint8), np.zeros((n, 2), np.uint64)
+        self._check(self.lib.cabac_ctx_init_id(self.h, _hp(params), _hp(ctx_ref), _hp(ctx_bins), n, _hp(choice),
+                                               _hp(costs)))
+        return choice, costs
+
     def encode_residual_packed(self, tus, tu_offsets, params, coeffs, out_offsets, packed=None, ctx_in=None,
                                want_ctx=False, raise_on_status=True):
         """Encode + pack: returns the substreams concatenated in order plus the entry-point table."""

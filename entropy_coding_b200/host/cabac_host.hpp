@@ -105,6 +105,7 @@ struct SubstreamResult {
   const uint8_t *bytes = nullptr;
   uint32_t size = 0, numBins = 0, status = 0;
   const cabac_ctx_model *ctx = nullptr;  // CABAC_NUM_CTX models after the run
+  const uint32_t *ctxBins = nullptr;     // CABAC_NUM_CTX context-coded bin counts of the TU markers (on request)
 };
 
 // A batch of recorded substreams -> one cabac_encode_stream call.  The coefficient slab is
@@ -143,8 +144,12 @@ class EncodeBatch {
 
   // Runs the batch.  Throws Error on a CUDA / argument failure; per-substream problems are
   // reported in SubstreamResult::status (CABAC_SS_*), as the C ABI does.
-  void flush(Engine &eng, const int32_t *coeffs, size_t nCoeffs, bool wantCtx = false) {
+  // wantCtxBins: also fetch the per-context bin counts of the TU markers (BinCounter view of the
+  // device-side residual syntax, cabac_residual_ctx_bins) - what getNumBins(ctxId) needs for
+  // CABACWriter::getCtxInitId (cabac_writer.cpp:41-81).  The counts follow from the coefficients alone.
+  void flush(Engine &eng, const int32_t *coeffs, size_t nCoeffs, bool wantCtx = false, bool wantCtxBins = false) {
     const size_t n = params_.size();
+    ctxBins_.clear();
     out_.assign(outOff_.back(), 0);
     sizes_.assign(n, 0);
     bins_.assign(n, 0);
@@ -159,6 +164,12 @@ class EncodeBatch {
                                        sizes_.data(), bins_.data(), tus_.empty() ? nullptr : tuFlags_.data(),
                                        wantCtx ? ctxOut_.data() : nullptr, status_.data());
     eng.check(rc, "cabac_encode_stream");
+    if (wantCtxBins && !tus_.empty()) {
+      ctxBins_.assign(n * CABAC_NUM_CTX, 0);
+      const int rb = cabac_residual_ctx_bins(eng.get(), tus_.data(), tuOff_.data(), params_.data(), n, coeffs, nCoeffs,
+                                             nullptr, ctxBins_.data(), nullptr, nullptr, nullptr);
+      eng.check(rb, "cabac_residual_ctx_bins");
+    }
   }
   SubstreamResult result(size_t i) const {
     SubstreamResult r;
@@ -167,6 +178,7 @@ class EncodeBatch {
     r.numBins = bins_[i];
     r.status = status_[i];
     r.ctx = ctxOut_.empty() ? nullptr : &ctxOut_[i * CABAC_NUM_CTX];
+    r.ctxBins = ctxBins_.empty() ? nullptr : &ctxBins_[i * CABAC_NUM_CTX];
     return r;
   }
   const std::vector<uint8_t> &tuFlags() const { return tuFlags_; }
@@ -180,7 +192,7 @@ class EncodeBatch {
   std::vector<cabac_ctx_model> ctxIn_, ctxOut_;
   bool haveCtxIn_ = false;
   std::vector<uint8_t> out_, tuFlags_;
-  std::vector<uint32_t> sizes_, bins_, status_;
+  std::vector<uint32_t> sizes_, bins_, status_, ctxBins_;
 };
 
 // Residual decode of a batch of substreams: bytes + TU lists in, coefficients out

@@ -30,6 +30,9 @@ class GpuEncodeSession {
   Engine &engine() { return eng_; }
   // TCoeff staging slab the TU markers index (H2D source)
   std::vector<int32_t> coeffs;
+  // Inter slices: also count the device-coded bins per context, so that getNumBins(ctxId) and
+  // getCtxInitId() see the residual syntax too (one more estimator-kernel pass per flush).
+  bool countCtxBins = false;
   void submit(GpuBinEncoder *enc, const StreamRecorder &rec, bool ctxIn);
   // Runs every submitted substream in one launch sequence and completes the encoders:
   // bytes into their OutputBitstream, contexts into their Ctx, CUCtx side flags.
@@ -59,6 +62,7 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
     rec_.clear();
     tuSinks_.clear();
     numCtx_.assign(Common::Ctx::NumberOfContexts, 0);
+    devCtx_.assign(Common::Ctx::NumberOfContexts, 0);
     numEP_ = numTrm_ = 0;
     writtenBits_ = 0;
     deviceBins_ = 0;
@@ -74,7 +78,30 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
   }
   void resetBits() override { start(); }
   uint64_t getEstFracBits() const override { THROW("not supported"); }  // as BinEncoderBase, arith_codec.cpp:380-383
-  unsigned getNumBins(unsigned ctxId) const override { return numCtx_[ctxId]; }
+  // BinCounter::getNumBins(ctxId), arith_codec.hpp:72-93.  Bins coded on the device (TU markers) are
+  // included once the batch completed with GpuEncodeSession::countCtxBins set.
+  unsigned getNumBins(unsigned ctxId) const override { return numCtx_[ctxId] + devCtx_[ctxId]; }
+  // CABACWriter::getCtxInitId(slice) (cabac_writer.cpp:41-81) on this coder: the init table the next
+  // inter slice should start from, evaluated by cabac_ctx_init_id from the final contexts and
+  // getNumBins(k).  Returns the SliceType value (B_SLICE 0, P_SLICE 1, I_SLICE 2).
+  int getCtxInitId(const Common::Slice &slice) {
+    if (slice.isIntra()) return int(Common::I_SLICE);
+    const auto &st = static_cast<const Common::CtxStore<Common::BinProbModel_Std> &>(
+        static_cast<const Common::Ctx &>(*this));
+    std::vector<cabac_ctx_model> ref(CABAC_NUM_CTX);
+    std::vector<uint32_t> bins(CABAC_NUM_CTX);
+    for (unsigned k = 0; k < CABAC_NUM_CTX; k++) {
+      ref[k] = {st[k].getState0(), st[k].getState1()};
+      bins[k] = getNumBins(k);
+    }
+    cabac_substream_params p{};
+    p.qp = int8_t(slice.getSliceQp());
+    p.init_id = 0;
+    uint8_t choice = 0;
+    Engine &eng = session_->engine();
+    eng.check(cabac_ctx_init_id(eng.get(), &p, ref.data(), bins.data(), 1, &choice, nullptr), "cabac_ctx_init_id");
+    return int(choice);
+  }
 
   void encodeBin(unsigned bin, unsigned ctxId) override {
     rec_.encodeBin(bin, ctxId);
@@ -177,6 +204,7 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
   StreamRecorder rec_;
   std::vector<TuSink> tuSinks_;
   std::vector<uint32_t> numCtx_ = std::vector<uint32_t>(Common::Ctx::NumberOfContexts, 0);
+  std::vector<uint32_t> devCtx_ = std::vector<uint32_t>(Common::Ctx::NumberOfContexts, 0);
   uint32_t numEP_ = 0, numTrm_ = 0, deviceBins_ = 0;
   unsigned writtenBits_ = 0;
   bool ctxDirty_ = false, completed_ = false;
@@ -197,7 +225,7 @@ inline void GpuEncodeSession::submit(GpuBinEncoder *enc, const StreamRecorder &r
 inline void GpuEncodeSession::flush() {
   if (owners_.empty()) return;
   static const int32_t none = 0;
-  batch_.flush(eng_, coeffs.empty() ? &none : coeffs.data(), coeffs.size(), /*wantCtx=*/true);
+  batch_.flush(eng_, coeffs.empty() ? &none : coeffs.data(), coeffs.size(), /*wantCtx=*/true, countCtxBins);
   const uint8_t *tf = batch_.tuFlags().data();
   for (size_t i = 0; i < owners_.size(); i++) {
     owners_[i]->complete(batch_.result(i), tf);
@@ -224,6 +252,7 @@ inline void GpuBinEncoder::complete(const SubstreamResult &r, const uint8_t *tuF
   uint32_t host = numEP_ + numTrm_;
   for (uint32_t c : numCtx_) host += c;
   deviceBins_ = r.numBins - host;
+  if (r.ctxBins) devCtx_.assign(r.ctxBins, r.ctxBins + CABAC_NUM_CTX);
   if (r.ctx) {
     auto &st = static_cast<Common::CtxStore<Common::BinProbModel_Std> &>(static_cast<Common::Ctx &>(*this));
     for (unsigned k = 0; k < CABAC_NUM_CTX; k++)

@@ -394,6 +394,43 @@ int cabac_estimate_residual_bits(cabac_handle *h, const cabac_tu_desc *tus,
                                  uint64_t *est_bits, uint64_t *est_per_tu,
                                  uint32_t *num_bins, uint8_t *tu_flags,
                                  cabac_ctx_model *ctx_out, uint32_t *status);
+/* ---- inter-slice init-table choice: CABACWriter::getCtxInitId ----------------
+ * Replaces the two inputs and the decision of CABACWriter::getCtxInitId /
+ * xGetCtxInitId (cabac_writer.cpp:41-81) for the residual syntax coded on the device.
+ *
+ * cabac_residual_ctx_bins: ctx_bins[i * CABAC_NUM_CTX + k] = BinEncIf::getNumBins(k)
+ * (BinCounter::addCtx, arith_codec.hpp:72-93, arith_codec.cpp:281-316) after
+ * residual_coding over TU list i - the context-coded bins per context id; bypass and
+ * terminate bins are not part of it, as in the reference.  Contexts evolve exactly as
+ * in cabac_encode_residual (ctx_out = getCtx() after the list).  A host shim adds the
+ * rows to the counts of the bins it recorded itself (GpuBinEncoder::getNumBins(k)).
+ * num_bins / ctx_out / status nullable.
+ *
+ * cabac_ctx_init_id: for slice i with QP params[i].qp, final contexts
+ * ctx_ref[i * CABAC_NUM_CTX ..] and bin counts ctx_bins[i * CABAC_NUM_CTX ..]:
+ * costs[2i + t] = sum_k ctx_bins[k] * estFracExcessBits(ctx_ref[k], model k of init
+ * table t at that QP) (contexts.cpp:965-968), t = 0 (B_SLICE), 1 (P_SLICE);
+ * choice[i] = the cheaper t (ties keep B), or 2 (I_SLICE) when params[i].init_id == 2
+ * as the reference returns for an intra slice.  costs nullable. */
+int cabac_residual_ctx_bins_dev(cabac_handle *h, const cabac_tu_desc *tus,
+                                const uint64_t *tu_offsets,
+                                const cabac_substream_params *params, size_t n_sub,
+                                const int32_t *coeffs, const cabac_ctx_model *ctx_in,
+                                uint32_t *ctx_bins, uint32_t *num_bins,
+                                cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_residual_ctx_bins(cabac_handle *h, const cabac_tu_desc *tus,
+                            const uint64_t *tu_offsets,
+                            const cabac_substream_params *params, size_t n_sub,
+                            const int32_t *coeffs, size_t n_coeffs,
+                            const cabac_ctx_model *ctx_in, uint32_t *ctx_bins,
+                            uint32_t *num_bins, cabac_ctx_model *ctx_out,
+                            uint32_t *status);
+int cabac_ctx_init_id_dev(cabac_handle *h, const cabac_substream_params *params,
+                          const cabac_ctx_model *ctx_ref, const uint32_t *ctx_bins,
+                          size_t n, uint8_t *choice, uint64_t *costs);
+int cabac_ctx_init_id(cabac_handle *h, const cabac_substream_params *params,
+                      const cabac_ctx_model *ctx_ref, const uint32_t *ctx_bins,
+                      size_t n, uint8_t *choice, uint64_t *costs);
 /* m_binFracBits flattened as table_out[2 * state + bin], 512 entries. */
 int cabac_frac_bits_table(uint32_t *table_out);
 

@@ -185,6 +185,8 @@ typedef struct {
    * (arith_codec.cpp:603-711): no interval, no bytes; 15-bit fixed-point bits are summed */
   int est;
   uint64_t estBits;
+  /* BinCounter::addCtx (arith_codec.hpp:72-93) when non-NULL: context-coded bins per context id */
+  uint32_t *ctxBins;
 } Enc;
 
 /* start, arith_codec.cpp:329-337 */
@@ -225,6 +227,7 @@ static void enc_write_out(Enc *e) {
 static void enc_bin(Enc *e, CtxTab *c, unsigned bin, unsigned ctxId) {
   cabac_ctx_model *m = &c->m[ctxId];
   e->nbins++;
+  if (e->ctxBins) e->ctxBins[ctxId]++;
   if (e->est) { /* estFracBitsUpdate, contexts.cpp:922-929: table[state()][bin], then update */
     const unsigned q = ((unsigned)m->state0 + m->state1) >> 8;
     e->estBits += CABAC_FRAC_BITS[2 * q + (bin & 1)];
@@ -1423,6 +1426,49 @@ uint64_t orc_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_s
   }
   if (ctxOut) memcpy(ctxOut, ct.m, sizeof(ct.m));
   return e.estBits;
+}
+
+/* BinCounter view of a TU list: ctxBins[k] = getNumBins(k) (arith_codec.cpp:281-316) after
+ * residual_coding over the list; the contexts evolve as in orc_encode_residual. */
+long orc_residual_ctx_bins(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                           const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
+                           uint32_t *ctxBins) {
+  CtxTab ct;
+  Enc e;
+  uint8_t dummy[8];
+  ctx_begin(&ct, p, ctxIn);
+  enc_start(&e, dummy, 0);
+  e.est = 1;
+  memset(ctxBins, 0, sizeof(uint32_t) * CABAC_NUM_CTX);
+  e.ctxBins = ctxBins;
+  for (long t = 0; t < ntu; t++)
+    if (w_residual_coding(&e, &ct, &tus[t], coeffs, p->flags, NULL)) return -1;
+  if (ctxOut) memcpy(ctxOut, ct.m, sizeof(ct.m));
+  return (long)e.nbins;
+}
+
+/* xGetCtxInitId, cabac_writer.cpp:41-73: which init table (0 = B, 1 = P) the next inter slice should
+ * use - the one whose initial models cost the fewest excess bits against the contexts this slice
+ * ended with, weighted by its per-context bin counts.  estFracExcessBits, contexts.cpp:965-968.
+ * costs[0..1] = the two sums; returns the choice (ties keep B, the first candidate). */
+int orc_ctx_init_id(int qp, const cabac_ctx_model *ctxRef, const uint32_t *ctxBins, uint64_t *costs) {
+  uint64_t c[2];
+  for (int t = 0; t < 2; t++) {
+    cabac_ctx_model test[CABAC_NUM_CTX];
+    uint8_t rates[CABAC_NUM_CTX];
+    orc_ctx_init(qp, t, test, rates);
+    c[t] = 0;
+    for (int k = 0; k < CABAC_NUM_CTX; k++) {
+      if (!ctxBins[k]) continue;
+      const unsigned qs = ((unsigned)ctxRef[k].state0 + ctxRef[k].state1) >> 8; /* state() of the final model */
+      const unsigned qt = ((unsigned)test[k].state0 + test[k].state1) >> 8;
+      const uint64_t n = 2 * qs + 1;
+      const uint64_t x = ((512 - n) * CABAC_FRAC_BITS[2 * qt] + n * CABAC_FRAC_BITS[2 * qt + 1] + 256) >> 9;
+      c[t] += (uint64_t)ctxBins[k] * x;
+    }
+  }
+  if (costs) costs[0] = c[0], costs[1] = c[1];
+  return c[1] < c[0] ? 1 : 0;
 }
 
 /* Recorded command stream with CABAC_CMD_TU markers (cabac_encode_stream): the BinEncIf calls of a

@@ -43,6 +43,10 @@ void orc_frac_bits(uint32_t *out);
 uint64_t orc_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
                                const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
                                uint64_t *estPerTu, int useMTS);
+long orc_residual_ctx_bins(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                           const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
+                           uint32_t *ctxBins);
+int orc_ctx_init_id(int qp, const cabac_ctx_model *ctxRef, const uint32_t *ctxBins, uint64_t *costs);
 long orc_count_emulations(const uint8_t *d, long n);
 long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out);
 #endif

@@ -206,6 +206,38 @@ class Checker:
         assert tot != 0xFFFFFFFFFFFFFFFF
         return (tot, per_tu, ctx_out) if want_ctx else (tot, per_tu)
 
+    def residual_ctx_bins(self, tus, coeffs, qp, init_id, flags=0, ctx_in=None):
+        """BinCounter per context after residual_coding over the list: (ctx_bins[379], ctx_out, choice).
+        choice = CABACWriter::getCtxInitId on that coder (cabac_writer.cpp:41-81): the compiled
+        reference evaluates it itself, the restatement through orc_ctx_init_id."""
+        tus = np.ascontiguousarray(tus, TU_DT)
+        coeffs = np.ascontiguousarray(coeffs, np.int32)
+        p = np.zeros(1, PARAMS_DT)
+        p["qp"], p["init_id"], p["flags"] = qp, init_id, flags | (SUB_CTX_IN if ctx_in is not None else 0)
+        bins = np.zeros(NUM_CTX, np.uint32)
+        ctx_out = np.zeros(NUM_CTX, CTX_DT)
+        f = self._f("residual_ctx_bins")
+        f.restype = C.c_long
+        if self.pfx == "ref_":
+            ch = C.c_int(-1)
+            n = f(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in), _ptr(ctx_out), _ptr(bins),
+                  C.byref(ch))
+            choice = ch.value
+        else:
+            n = f(_ptr(tus), C.c_long(len(tus)), _ptr(p), _ptr(coeffs), _ptr(ctx_in), _ptr(ctx_out), _ptr(bins))
+            choice = 2 if init_id == 2 else self.ctx_init_id(qp, ctx_out, bins)[0]
+        assert n >= 0
+        return bins, ctx_out, choice
+
+    def ctx_init_id(self, qp, ctx_ref, ctx_bins):
+        """xGetCtxInitId for a non-intra slice (restatement only): (choice, costs[2])."""
+        assert self.pfx == "orc_"
+        costs = np.zeros(2, np.uint64)
+        ctx_ref = np.ascontiguousarray(ctx_ref, CTX_DT)
+        ctx_bins = np.ascontiguousarray(ctx_bins, np.uint32)
+        ch = self.lib.orc_ctx_init_id(C.c_int(int(qp)), _ptr(ctx_ref), _ptr(ctx_bins), _ptr(costs))
+        return int(ch), costs
+
     def encode_stream(self, cmds, tus, coeffs, qp, init_id, flags, ctx_in=None, want_ctx=False, cap=None):
         """Recorded commands with CMD_TU markers (marker k codes tus[k])."""
         cmds = np.ascontiguousarray(cmds, np.uint32)

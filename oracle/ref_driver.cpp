@@ -430,4 +430,31 @@ uint64_t ref_estimate_residual(const cabac_tu_desc *tus, long ntu, const cabac_s
   return est.getEstFracBits();
 }
 
+// BinCounter view of a TU list on the real encoder: ctxBins[k] = getNumBins(k)
+// (arith_codec.cpp:281-316), and *choice = CABACWriter::getCtxInitId(slice)
+// (cabac_writer.cpp:41-81; SliceType B = 0, P = 1, I = 2) evaluated on that coder.
+long ref_residual_ctx_bins(const cabac_tu_desc *tus, long ntu, const cabac_substream_params *p,
+                           const int32_t *coeffs, const cabac_ctx_model *ctxIn, cabac_ctx_model *ctxOut,
+                           uint32_t *ctxBins, int *choice) {
+  Harness hs(*p, false);
+  BinEncoder_Std enc;
+  CABACWriter wr(enc);
+  OutputBitstream bs;
+  wr.initBitstream(&bs);
+  enc.reset(p->qp, p->init_id);
+  enc.riceStatReset(10);
+  if ((p->flags & CABAC_SUB_CTX_IN) && ctxIn) importCtx(enc, ctxIn);
+  for (long t = 0; t < ntu; t++) {
+    TuPair tp;
+    makeTu(tp, hs, tus[t], const_cast<TCoeff *>(coeffs));
+    applyTsAllowed(tp, tus[t], false);
+    CUCtx cuCtx(p->qp);
+    wr.residual_coding(tp.tu, ComponentID(tus[t].comp_id), &cuCtx);
+  }
+  for (unsigned k = 0; k < Ctx::NumberOfContexts; k++) ctxBins[k] = enc.getNumBins(k);
+  if (choice) *choice = int(wr.getCtxInitId(*hs.slice));
+  if (ctxOut) exportCtx(enc, ctxOut);
+  return long(enc.getNumBins());
+}
+
 }  // extern "C"

@@ -129,6 +129,7 @@ int main(int argc, char **argv) {
   std::vector<std::unique_ptr<OutputBitstream>> bsB1, bsB2;
   std::vector<std::vector<uint8_t>> bytesRef(nSub);
   std::vector<uint32_t> binsRef(nSub);
+  std::vector<int> initIdRef(nSub), initIdQp(nSub);
   std::vector<std::unique_ptr<BinEncoder_Std>> encRef;
   std::vector<std::vector<uint8_t>> flagsRef(nSub);
 
@@ -177,9 +178,33 @@ int main(int argc, char **argv) {
     }
     binsRef[i] = encRef.back()->getNumBins();
     bytesRef[i] = closeSubstream(bsRef);
+    {  // CABACWriter::getCtxInitId on the reference coder (cabac_writer.cpp:41-81)
+      CABACWriter wr(*encRef.back());
+      initIdRef[i] = int(wr.getCtxInitId(*hs.slice));
+      initIdQp[i] = hs.slice->getSliceQp();
+    }
   }
   sessBins.flush();
+  sessTu.countCtxBins = true;
   sessTu.flush();
+  int initChoices[3] = {0, 0, 0};
+  for (int i = 0; i < nSub; i++) {
+    // per-context BinCounter view and the init-table choice, both seams against the reference coder
+    bool same1 = true, same2 = true;
+    for (unsigned k = 0; k < Ctx::NumberOfContexts; k++) {
+      same1 &= encB1[i]->getNumBins(k) == encRef[i]->getNumBins(k);
+      same2 &= encB2[i]->getNumBins(k) == encRef[i]->getNumBins(k);
+    }
+    EXPECT(same1, "substream %d: bin-seam getNumBins(ctxId) differ", i);
+    EXPECT(same2, "substream %d: TU-seam getNumBins(ctxId) differ", i);
+    Harness hs(subs[i].p, false);
+    const int c1 = encB1[i]->getCtxInitId(*hs.slice), c2 = encB2[i]->getCtxInitId(*hs.slice);
+    EXPECT(c1 == initIdRef[i], "substream %d: bin-seam getCtxInitId %d vs %d", i, c1, initIdRef[i]);
+    EXPECT(c2 == initIdRef[i], "substream %d: TU-seam getCtxInitId %d vs %d", i, c2, initIdRef[i]);
+    initChoices[initIdRef[i] % 3]++;
+  }
+  printf("getCtxInitId: %d B, %d P, %d I choices, all equal to the reference's\n", initChoices[0], initChoices[1],
+         initChoices[2]);
 
   size_t totalBytes = 0, totalBins = 0;
   for (int i = 0; i < nSub; i++) {

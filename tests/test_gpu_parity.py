@@ -579,6 +579,49 @@ def test_estimate_vs_oracle(engine, oracle, seed, flags, kw):
     assert (r["ctx_out"] == enc["ctx_out"]).all()
 
 
+@pytest.mark.parametrize("seed,kw", [
+    (621, {}),
+    (622, {"ts_fraction": 0.3, "flags": SUB_DEP_QUANT | SUB_SIGN_HIDING}),
+    (623, {"preset": "qp0", "tus_per_sub": (1, 4)}),
+])
+def test_ctx_bins_and_init_id_vs_oracle(engine, oracle, seed, kw):
+    """cabac_residual_ctx_bins == BinEncIf::getNumBins(k) after residual_coding, and cabac_ctx_init_id ==
+    CABACWriter::getCtxInitId (cabac_writer.cpp:41-81): choice and both cost sums."""
+    wl = W.random_substreams(48, seed, **kw)
+    params = wl.params.copy()
+    params["init_id"] = np.arange(wl.n_sub) % 3  # B, P and I slices
+    r = engine.residual_ctx_bins(wl.tus, wl.tu_offsets, params, wl.coeffs)
+    assert not r["status"].any()
+    est = engine.estimate_residual_bits(wl.tus, wl.tu_offsets, params, wl.coeffs, want_ctx=True)
+    assert (est["ctx_out"] == r["ctx_out"]).all() and (est["num_bins"] == r["num_bins"]).all()
+    choice, costs = engine.ctx_init_id(params, r["ctx_out"], r["ctx_bins"])
+    for i in range(wl.n_sub):
+        a, b, _, _ = sub_range(wl, i)
+        p = params[i]
+        bins, ctx, ch = oracle.residual_ctx_bins(wl.tus[a:b], wl.coeffs, int(p["qp"]), int(p["init_id"]),
+                                                 int(p["flags"]))
+        assert (r["ctx_bins"][i] == bins).all(), (seed, i)
+        assert (r["ctx_out"][i] == ctx).all()
+        assert int(choice[i]) == ch, (seed, i)
+        _, oc = oracle.ctx_init_id(int(p["qp"]), ctx, bins)
+        assert (costs[i] == oc).all()
+    assert (r["ctx_bins"].sum(axis=1) <= r["num_bins"]).all()
+
+
+def test_ctx_init_id_golden(engine):
+    """The device path against ctx_init_id.npz (getNumBins(k) + getCtxInitId of the compiled reference)."""
+    g, c = load_golden("residual"), load_golden("ctx_init_id")
+    for name in c["names"]:
+        tus, offs, params, coeffs = g[f"{name}_tus"], g[f"{name}_tu_offsets"], g[f"{name}_params"], g[f"{name}_coeffs"]
+        for init_id in (0, 1):
+            p = params.copy()
+            p["init_id"] = init_id
+            r = engine.residual_ctx_bins(tus, offs, p, coeffs)
+            assert (r["ctx_bins"] == c[f"{name}_ctx_bins"][:, init_id]).all(), (name, init_id)
+            choice, _ = engine.ctx_init_id(p, r["ctx_out"], r["ctx_bins"])
+            assert (choice == c[f"{name}_choice"][:, init_id]).all(), (name, init_id)
+
+
 def test_estimate_ctx_handoff_and_candidates(engine, oracle):
     """RDO use: many candidate TU lists priced from ONE saved context set (ctx_in), and an estimate
     continued across two calls equals the estimate of the concatenation."""

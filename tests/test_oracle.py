@@ -227,3 +227,34 @@ def test_estimate_golden(oracle):
             tot, per_tu = oracle.estimate_residual(tus[a:b], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]))
             assert tot == int(e[f"{name}_est_bits"][i]), (name, i)
             assert (per_tu == e[f"{name}_est_per_tu"][a:b]).all()
+
+
+def test_ctx_init_id_golden(oracle):
+    """BinCounter per context and xGetCtxInitId (cabac_writer.cpp:41-81) of the restatement against the
+    reference-generated ctx_init_id.npz (getNumBins(k) and CABACWriter::getCtxInitId of the compiled reference)."""
+    g, c = load_golden("residual"), load_golden("ctx_init_id")
+    seen = set()
+    for name in c["names"]:
+        tus, offs, params, coeffs = g[f"{name}_tus"], g[f"{name}_tu_offsets"], g[f"{name}_params"], g[f"{name}_coeffs"]
+        for i in range(len(params)):
+            a, b = int(offs[i]), int(offs[i + 1])
+            p = params[i]
+            for init_id in (0, 1):
+                bins, ctx, choice = oracle.residual_ctx_bins(tus[a:b], coeffs, int(p["qp"]), init_id, int(p["flags"]))
+                assert (bins == c[f"{name}_ctx_bins"][i, init_id]).all(), (name, i, init_id)
+                assert choice == int(c[f"{name}_choice"][i, init_id]), (name, i, init_id)
+                seen.add(choice)
+    assert seen == {0, 1}  # both tables get chosen somewhere in the fixture
+
+
+@pytest.mark.parametrize("seed", [231, 232])
+def test_oracle_vs_ref_ctx_init_id(oracle, ref, seed):
+    wl = W.random_substreams(8, seed, tus_per_sub=(1, 10), ts_fraction=0.2)
+    for i in range(wl.n_sub):
+        a, b, _, _ = sub_range(wl, i)
+        p = wl.params[i]
+        for init_id in (0, 1, 2):
+            for qp in (int(p["qp"]), 17, 40):
+                o = oracle.residual_ctx_bins(wl.tus[a:b], wl.coeffs, qp, init_id, int(p["flags"]))
+                r = ref.residual_ctx_bins(wl.tus[a:b], wl.coeffs, qp, init_id, int(p["flags"]))
+                assert (o[0] == r[0]).all() and (o[1] == r[1]).all() and o[2] == r[2], (seed, i, init_id, qp)
