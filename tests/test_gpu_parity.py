@@ -1,6 +1,8 @@
 """GPU suite (-m gpu): the CUDA path, called through the C ABI, against the CPU
 oracle and the reference-generated golden fixtures.  Bit-exact everywhere: this
 path is integer/byte work."""
+import os
+
 import numpy as np
 import pytest
 
@@ -724,3 +726,19 @@ def test_bench_scale_properties_all_encoders(engine):
     assert (est["num_bins"] + trm == r["num_bins"]).all()
     written = 8.0 * float(r["sizes"].astype(np.int64).sum())
     assert abs(float(est["est_bits"].astype(np.float64).sum()) / 32768.0 / written - 1.0) < 0.01
+
+
+def test_million_substreams_round_trip():
+    """BASELINE configs[4] upper end: 10^4, 10^5 and 10^6 substreams in one launch (a seeded base batch tiled on the
+    device, tests/tools/substream_sweep.py): decode(encode(x)) == x on every tile and all tiles code identically."""
+    import json
+    import subprocess
+    import sys
+    tool = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools", "substream_sweep.py")
+    out = subprocess.run([sys.executable, tool, "100"], capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stderr[-2000:]
+    rows = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
+    assert [r["substreams"] for r in rows] == [10_000, 100_000, 1_000_000]
+    for r in rows:
+        assert r["round_trip_ok"] and r["tiles_identical"], r
+        assert r["bins"] == rows[0]["bins"] * (r["substreams"] // 10_000)
