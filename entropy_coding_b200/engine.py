@@ -324,6 +324,16 @@ class CabacEngine:
                                                               _dp(est_per_tu), _dp(num_bins), _dp(tu_flags),
                                                               _dp(ctx_out), _dp(status)))
 
+    def residual_ctx_bins_dev(self, tus, tu_offsets, params, n_sub, coeffs, ctx_bins, num_bins=None, ctx_in=None,
+                              ctx_out=None, status=None):
+        self._check(self.lib.cabac_residual_ctx_bins_dev(self.h, _dp(tus), _dp(tu_offsets), _dp(params), n_sub,
+                                                         _dp(coeffs), _dp(ctx_in), _dp(ctx_bins), _dp(num_bins),
+                                                         _dp(ctx_out), _dp(status)))
+
+    def ctx_init_id_dev(self, params, ctx_ref, ctx_bins, n, choice, costs=None):
+        self._check(self.lib.cabac_ctx_init_id_dev(self.h, _dp(params), _dp(ctx_ref), _dp(ctx_bins), n, _dp(choice),
+                                                   _dp(costs)))
+
     def decode_residual_dev(self, data, in_offsets, tus, tu_offsets, params, n_sub, coeffs, num_bins=None,
                             bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
         self._check(self.lib.cabac_decode_residual_dev(self.h, _dp(data), _dp(in_offsets), _dp(tus), _dp(tu_offsets),

@@ -35,6 +35,14 @@ def run(wl, tag):
     te = timed(lambda: eng.encode_residual_dev(d_tus, d_tuoff, d_par, n_sub, d_co, d_out, d_cap, d_sizes, d_bins))
     bins = int(d_bins.sum().item())
     ts = timed(lambda: eng.estimate_residual_bits_dev(d_tus, d_tuoff, d_par, n_sub, d_co, d_est, d_per, d_bins))
+    # getCtxInitId inputs + decision: the estimator kernel with per-context counters, then one warp per list
+    d_cb = torch.zeros(n_sub * 379, dtype=torch.int32, device=dev)
+    d_ctx = torch.zeros(n_sub * 379 * 4, dtype=torch.uint8, device=dev)
+    d_choice = torch.zeros(n_sub, dtype=torch.uint8, device=dev)
+    tc = timed(lambda: eng.residual_ctx_bins_dev(d_tus, d_tuoff, d_par, n_sub, d_co, d_cb, d_bins, ctx_out=d_ctx))
+    ti = timed(lambda: eng.ctx_init_id_dev(d_par, d_ctx, d_cb, n_sub, d_choice))
+    print(f"{tag}: ctx bin counts {tc:.2f} ms (counted {int(d_cb.sum(dtype=torch.int64).item()) / 1e6:.1f} M context-coded "
+          f"bins), init-table choice {ti:.3f} ms, choices {torch.bincount(d_choice.int(), minlength=3).tolist()}")
     trm = int(((wl.params["flags"] & 1) != 0).sum())  # CABAC_SUB_TERMINATE: the coder counts its terminating bin
     assert int(d_bins.sum().item()) + trm == bins
     bits, size = int(d_est.sum().item()) / 32768.0, int(d_sizes.sum().item()) * 8
