@@ -39,6 +39,9 @@ UNIT = "Mbins/s"
 WORKLOAD = "1080p-all-intra-64-frames, one substream per 128x128 CTU (8640 substreams/GPU), mixed qp0/qp32/qp51 presets"
 
 
+_SAVED_STDOUT = None  # file descriptor 1 as the driver gave it, while a multi-rank run has it pointed at stderr
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -248,6 +251,13 @@ def run_b200_arm(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # stdout carries ONE JSON line: anything a library writes to file descriptor 1 while the job runs
+        # (the "NCCL version ..." banner at communicator creation) goes to stderr; the descriptor is
+        # restored for the result line
+        global _SAVED_STDOUT
+        sys.stdout.flush()
+        _SAVED_STDOUT = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -477,6 +487,9 @@ def main():
         line["e2e"] = e2e
     if r["world"] == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = run_cpu_baseline(args, r)
+    if _SAVED_STDOUT is not None:
+        sys.stdout.flush()
+        os.dup2(_SAVED_STDOUT, 1)
     print(json.dumps(line), flush=True)
 
 
