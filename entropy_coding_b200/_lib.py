@@ -52,6 +52,12 @@ _SIGS = {
     "cabac_count_emulations_dev": (C.c_int, [_P, _P, _P, _SZ, _P]),
     "cabac_insert_emulation_prevention": (C.c_int, [_P, _P, _SZ, _P, _SZ, _P]),
     "cabac_insert_emulation_prevention_dev": (C.c_int, [_P, _P, _SZ, _P, _SZ, _P]),
+    "cabac_encode_residual_wpp": (C.c_int, [_P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_residual_wpp_dev": (C.c_int, [_P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_wpp": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_wpp_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_stream_wpp": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_stream_wpp_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
     "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
 }

@@ -48,6 +48,13 @@ struct cabac_handle {
   bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
   cudaEvent_t evT0 = nullptr;
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
+  // WPP launches (cabac_*_wpp*): the sync records of the NEXT coding call (device pointer, consumed by it),
+  // snapshot rows + flags (grow-only), and a device copy of host-side sync records
+  const cabac_wpp_sync *wppNext = nullptr;
+  void *wppScratch = nullptr;
+  size_t wppSubs = 0;
+  cabac_wpp_sync *wppDev = nullptr;
+  size_t wppDevSubs = 0;
 };
 
 namespace {
@@ -123,7 +130,49 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
   sc.cmdBuf = h->cmdBuf;
   sc.fusedResolve = h->fusedResolve;
   sc.warpSpecialised = h->encoderMode == CABAC_ENCODER_WARP_SPECIALISED;
+  sc.wpp = cabac::WppArgs();
+  if (h->wppNext) {  // a WPP launch: snapshot rows + "published" flags for n substreams, flags cleared on the stream
+    const cabac_wpp_sync *sync = h->wppNext;
+    h->wppNext = nullptr;
+    if (n > h->wppSubs) {
+      if (h->wppScratch) cudaFree(h->wppScratch);
+      h->wppScratch = nullptr;
+      h->wppSubs = 0;
+      const size_t cap2 = n + (n >> 2) + 64;
+      cudaError_t e = cudaMalloc(&h->wppScratch, cap2 * (CABAC_NUM_CTX * sizeof(cabac_ctx_model) + sizeof(uint32_t)));
+      if (e != cudaSuccess) return e;
+      h->wppSubs = cap2;
+    }
+    sc.wpp.sync = sync;
+    sc.wpp.snap = static_cast<cabac_ctx_model *>(h->wppScratch);
+    sc.wpp.ready = reinterpret_cast<uint32_t *>(sc.wpp.snap + h->wppSubs * CABAC_NUM_CTX);
+    cudaError_t e = cudaMemsetAsync(sc.wpp.ready, 0, n * sizeof(uint32_t), h->stream);
+    if (e != cudaSuccess) return e;
+  }
   return cudaSuccess;
+}
+
+// Host-side sync records -> the handle's device copy (stream-ordered); marks the next coding call as WPP.
+cudaError_t stageWpp(cabac_handle *h, const cabac_wpp_sync *wpp, size_t n) {
+  if (n > h->wppDevSubs) {
+    if (h->wppDev) cudaFree(h->wppDev);
+    h->wppDev = nullptr;
+    h->wppDevSubs = 0;
+    const size_t cap = n + (n >> 2) + 64;
+    cudaError_t e = cudaMalloc(&h->wppDev, cap * sizeof(cabac_wpp_sync));
+    if (e != cudaSuccess) return e;
+    h->wppDevSubs = cap;
+  }
+  cudaError_t e = cudaMemcpyAsync(h->wppDev, wpp, n * sizeof(cabac_wpp_sync), cudaMemcpyHostToDevice, h->stream);
+  if (e != cudaSuccess) return e;
+  h->wppNext = h->wppDev;
+  return cudaSuccess;
+}
+// dep must precede the substream (claim order = index order: the deadlock-freedom argument of the kernels)
+bool wppValid(const cabac_wpp_sync *wpp, size_t n) {
+  for (size_t i = 0; i < n; i++)
+    if (wpp[i].dep != CABAC_WPP_NONE && wpp[i].dep >= i) return false;
+  return true;
 }
 
 // Reads the command-slab size the prepare kernels computed (8 bytes; the one synchronisation
@@ -292,6 +341,8 @@ void cabac_destroy(cabac_handle *h) {
   if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
   if (h->epbScratch) cudaFree(h->epbScratch);
+  if (h->wppScratch) cudaFree(h->wppScratch);
+  if (h->wppDev) cudaFree(h->wppDev);
   for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
     if (h->evCopy[i]) cudaEventDestroy(h->evCopy[i]);
     if (h->evDone[i]) cudaEventDestroy(h->evDone[i]);
@@ -420,8 +471,9 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
      "encode prepare kernels");
   // Few long substreams: one warp per substream, fused.  Many substreams: the two-stage coder,
   // whose interval stage runs one substream per thread.
-  sc.twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
-                (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
+  sc.twoStage = !sc.wpp.sync &&  // WPP: the fused kernels (contexts are final at every TU boundary there)
+                (h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                 (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams));
   if (sc.twoStage) CK(ensureCmdSlab(h, sc, n_sub), "command slab");
   sc.cmdBuf = h->cmdBuf;
   // In between (every producer slot of the GPU filled at least twice): the warp-specialised kernel.
@@ -893,8 +945,8 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, n_sub * sizeof(*params));
-  const bool twoStage = h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
-                        (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams);
+  const bool twoStage = !h->wppNext && (h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
+                                        (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams));
   const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && n_coeffs >= kZeroCopyMinCoeffs)
                                 ? static_cast<const int32_t *>(mappedHostAlias(coeffs)) : nullptr;
   a.want((void **)&dCoeffs, zcCoeffs ? 0 : n_coeffs * 4);
@@ -921,7 +973,7 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
     rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, zcCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
                                    dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
-  } else if (h->pipeChunks > 1 && !twoStage && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+  } else if (h->pipeChunks > 1 && !twoStage && !h->wppNext && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
     // ---- chunked pipeline: the slab crosses PCIe chunk by chunk while earlier chunks are coded ----
     CK(ensurePipe(h), "pipeline streams");
     uint64_t *hr = h->pinnedRanges;
@@ -1062,7 +1114,7 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
     int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, zcCoeffs,
                                        dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
-  } else if (h->pipeChunks > 1 && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+  } else if (h->pipeChunks > 1 && !h->wppNext && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
     CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
     // ---- chunked pipeline: finished coefficient ranges leave over PCIe while later chunks decode ----
     CK(ensurePipe(h), "pipeline streams");
@@ -1207,6 +1259,102 @@ int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp, size
   D2H(out, dOut, size_t(*out_size));
   CK(cudaStreamSynchronize(h->stream), "sync");
   return CABAC_OK;
+}
+
+// ---- WPP entry points: the plain calls with the sync records attached to the launch ----
+int cabac_encode_residual_wpp_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params, const cabac_wpp_sync *wpp, size_t n_sub,
+                                  const int32_t *coeffs, const cabac_ctx_model *ctx_in, uint8_t *out,
+                                  const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                                  uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_encode_residual_wpp_dev");
+  h->wppNext = n_sub ? wpp : nullptr;
+  const int rc = cabac_encode_residual_dev(h, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out, out_offsets,
+                                           out_sizes, num_bins, tu_flags, ctx_out, status);
+  h->wppNext = nullptr;
+  return rc;
+}
+
+int cabac_decode_residual_wpp_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                                  const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params, const cabac_wpp_sync *wpp, size_t n_sub,
+                                  const cabac_ctx_model *ctx_in, int32_t *coeffs, uint32_t *num_bins,
+                                  uint32_t *bits_read, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                  uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_decode_residual_wpp_dev");
+  h->wppNext = n_sub ? wpp : nullptr;
+  const int rc = cabac_decode_residual_dev(h, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in, coeffs, num_bins,
+                                           bits_read, tu_flags, ctx_out, status);
+  h->wppNext = nullptr;
+  return rc;
+}
+
+int cabac_encode_stream_wpp_dev(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets,
+                                const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                const cabac_substream_params *params, const cabac_wpp_sync *wpp, size_t n_sub,
+                                const int32_t *coeffs, const cabac_ctx_model *ctx_in, uint8_t *out,
+                                const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                                uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_encode_stream_wpp_dev");
+  h->wppNext = n_sub ? wpp : nullptr;
+  const int rc = cabac_encode_stream_dev(h, cmds, cmd_offsets, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
+                                         out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status);
+  h->wppNext = nullptr;
+  return rc;
+}
+
+int cabac_encode_residual_wpp(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                              const cabac_substream_params *params, const cabac_wpp_sync *wpp, size_t n_sub,
+                              const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in,
+                              const uint64_t *out_offsets, uint8_t *packed, size_t packed_cap,
+                              uint64_t *entry_points, uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_encode_residual_wpp");
+  if (n_sub && !wppValid(wpp, n_sub)) return badArg(h, "cabac_encode_residual_wpp: dep must be < the substream's index");
+  if (n_sub) {
+    DeviceGuard g(h->device);
+    CK(stageWpp(h, wpp, n_sub), "wpp sync records");
+  }
+  const int rc = cabac_encode_residual_packed(h, tus, tu_offsets, params, n_sub, coeffs, n_coeffs, ctx_in, out_offsets,
+                                              packed, packed_cap, entry_points, out_sizes, num_bins, tu_flags, ctx_out,
+                                              status);
+  h->wppNext = nullptr;
+  return rc;
+}
+
+int cabac_decode_residual_wpp(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets, const cabac_substream_params *params,
+                              const cabac_wpp_sync *wpp, size_t n_sub, const cabac_ctx_model *ctx_in, int32_t *coeffs,
+                              size_t n_coeffs, uint32_t *num_bins, uint32_t *bits_read, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_decode_residual_wpp");
+  if (n_sub && !wppValid(wpp, n_sub)) return badArg(h, "cabac_decode_residual_wpp: dep must be < the substream's index");
+  if (n_sub) {
+    DeviceGuard g(h->device);
+    CK(stageWpp(h, wpp, n_sub), "wpp sync records");
+  }
+  const int rc = cabac_decode_residual(h, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in, coeffs, n_coeffs,
+                                       num_bins, bits_read, tu_flags, ctx_out, status);
+  h->wppNext = nullptr;
+  return rc;
+}
+
+int cabac_encode_stream_wpp(cabac_handle *h, const uint32_t *cmds, const uint64_t *cmd_offsets, const cabac_tu_desc *tus,
+                            const uint64_t *tu_offsets, const cabac_substream_params *params,
+                            const cabac_wpp_sync *wpp, size_t n_sub, const int32_t *coeffs, size_t n_coeffs,
+                            const cabac_ctx_model *ctx_in, uint8_t *out, const uint64_t *out_offsets,
+                            uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                            uint32_t *status) {
+  if (!h || (n_sub && !wpp)) return badArg(h, "cabac_encode_stream_wpp");
+  if (n_sub && !wppValid(wpp, n_sub)) return badArg(h, "cabac_encode_stream_wpp: dep must be < the substream's index");
+  if (n_sub) {
+    DeviceGuard g(h->device);
+    CK(stageWpp(h, wpp, n_sub), "wpp sync records");
+  }
+  const int rc = cabac_encode_stream(h, cmds, cmd_offsets, tus, tu_offsets, params, n_sub, coeffs, n_coeffs, ctx_in, out,
+                                     out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status);
+  h->wppNext = nullptr;
+  return rc;
 }
 
 }  // extern "C"

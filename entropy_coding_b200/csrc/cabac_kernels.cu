@@ -257,16 +257,56 @@ __global__ void ctx_init_kernel(const cabac_substream_params *__restrict__ param
   }
 }
 
-// Residual contexts as 16-byte entries (see cabac_lockstep.cuh).
-__device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                      size_t sub, int lane) {
+// ---------------------------------------------------------------------------
+// WPP (wavefront parallel processing) inside one launch.  Substream i may name a predecessor
+// (cabac_wpp_sync::dep, the CTU row above): it starts from the contexts the predecessor held after
+// its first CTU (EncSlice.cpp:2057-2072, 2085-2089; DecSlice.cpp:194-210, 241-245; the copy is
+// Ctx::operator=, contexts.cpp:1096-1108).  The predecessor's warp writes that snapshot to global
+// memory at its sync point, fences and raises a flag; the dependant's warp spins on the flag.
+// Substreams are claimed in index order and dep < own index, so a predecessor is always already
+// claimed by a running warp when somebody waits for it: no deadlock, whatever the grid size.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ldAcquire(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void stRelease(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// The row of 379 models a substream starts from: the predecessor's snapshot (WPP), its ctx_in row
+// (CABAC_SUB_CTX_IN) or nullptr = Ctx::init(qp, initId).  Blocks until a WPP snapshot is published.
+__device__ __forceinline__ const cabac_ctx_model *ctxSource(const cabac_substream_params &p,
+                                                            const cabac_ctx_model *ctxIn, size_t sub,
+                                                            const WppArgs &wpp, int lane) {
+  if (wpp.sync) {
+    const uint32_t dep = wpp.sync[sub].dep;
+    if (dep != CABAC_WPP_NONE) {
+      if (lane == 0)
+        while (ldAcquire(wpp.ready + dep) == 0u) __nanosleep(100);
+      __syncwarp();
+      (void)ldAcquire(wpp.ready + dep);  // every lane orders its own snapshot loads after the flag
+      return wpp.snap + size_t(dep) * CABAC_NUM_CTX;
+    }
+  }
+  return ((p.flags & CABAC_SUB_CTX_IN) && ctxIn) ? ctxIn + sub * CABAC_NUM_CTX : nullptr;
+}
+__device__ __forceinline__ void wppPublish(const WppArgs &wpp, size_t sub, int lane) {
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) stRelease(wpp.ready + sub, 1u);
+}
+
+// Residual contexts as 16-byte entries (see cabac_lockstep.cuh).  src: see ctxSource.
+__device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *src,
+                                      int lane) {
   const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
   for (int k = lane; k < RCTX; k += 32) {
     const int id = rctx_inv(k);
     const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
-    if (imp) {
-      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+    if (src) {
+      const cabac_ctx_model m = src[id];
       ctx[k] = ctx_entry(m.state0, m.state1, win);
     } else {
       ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
@@ -275,38 +315,38 @@ __device__ inline void loadCtxEntries(uint4 *ctx, const cabac_substream_params &
   __syncwarp();
 }
 
-__device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                       cabac_ctx_model *ctxOut, size_t sub, int lane) {
-  if (!ctxOut) return;
+// dst: a row of CABAC_NUM_CTX models (ctx_out of the substream, or its WPP snapshot).  Contexts the
+// residual syntax does not touch pass through from the source row.
+__device__ inline void storeCtxEntries(const uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *src,
+                                       cabac_ctx_model *dst, int lane) {
+  if (!dst) return;
   __syncwarp();
   const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
   for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
     cabac_ctx_model m;
     if (is_residual_ctx(id)) {
       const uint32_t x = ctx[rctx(id)].x;
       m.state0 = uint16_t(x >> 16);
       m.state1 = uint16_t(x & 0xFFFFu);
-    } else if (imp) {
-      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else if (src) {
+      m = src[id];
     } else {
       const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
       m.state0 = uint16_t(model_state0(w));
       m.state1 = uint16_t(model_state1(w));
     }
-    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+    dst[id] = m;
   }
 }
 
 // All 379 contexts (recorded command streams address them by their reference ids).
-__device__ inline void loadCtxEntriesFull(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                          size_t sub, int lane) {
+__device__ inline void loadCtxEntriesFull(uint4 *ctx, const cabac_substream_params &p, const cabac_ctx_model *src,
+                                          int lane) {
   const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
   for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
     const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
-    if (imp) {
-      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+    if (src) {
+      const cabac_ctx_model m = src[id];
       ctx[id] = ctx_entry(m.state0, m.state1, win);
     } else {
       ctx[id] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
@@ -314,14 +354,14 @@ __device__ inline void loadCtxEntriesFull(uint4 *ctx, const cabac_substream_para
   }
   __syncwarp();
 }
-__device__ inline void storeCtxEntriesFull(const uint4 *ctx, cabac_ctx_model *ctxOut, size_t sub, int lane) {
-  if (!ctxOut) return;
+__device__ inline void storeCtxEntriesFull(const uint4 *ctx, cabac_ctx_model *dst, int lane) {
+  if (!dst) return;
   __syncwarp();
   for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
     cabac_ctx_model m;
     m.state0 = uint16_t(ctx[id].x >> 16);
     m.state1 = uint16_t(ctx[id].x & 0xFFFFu);
-    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+    dst[id] = m;
   }
 }
 
@@ -348,7 +388,7 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtxEntriesFull(sm.ctx, p, ctxIn, sub, lane);
+    loadCtxEntriesFull(sm.ctx, p, ((p.flags & CABAC_SUB_CTX_IN) && ctxIn) ? ctxIn + sub * CABAC_NUM_CTX : nullptr, lane);
     LsDecoder dec;
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
     const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
@@ -376,7 +416,7 @@ decode_bins_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ 
       if (bitsRead) bitsRead[sub] = dec.bitsRead();
       if (status) status[sub] = dec.status;
     }
-    storeCtxEntriesFull(sm.ctx, ctxOut, sub, lane);
+    storeCtxEntriesFull(sm.ctx, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
     __syncwarp();
   }
 }
@@ -430,7 +470,7 @@ __device__ __forceinline__ void prefetchBlock(int32_t *raw, const int32_t *__res
                                               int lane) {
   const int log2w = d.log2_w, log2tw = min(int(d.log2_w), 5), log2th = min(int(d.log2_h), 5);
   const uint32_t dst = uint32_t(__cvta_generic_to_shared(raw));
-  if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+  if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && log2tw >= 2) {
     const int total = 1 << (log2tw + log2th - 2);  // 16-byte units
     for (int u = lane; u < total; u += 32) {
       const int y = u >> (log2tw - 2), x = (u & ((1 << (log2tw - 2)) - 1)) << 2;
@@ -455,6 +495,15 @@ __device__ __forceinline__ bool takeBlock(int16_t *tile, const int32_t *raw, con
   __syncwarp();
   bool ok = true;
   const int n = g.tw * g.th;
+  if (n < 4) {  // 2 x 1 / 1 x 2 / 1 x 1
+    if (lane < n) {
+      const int v = raw[lane];
+      ok = v == int16_t(v);
+      tile[lane] = int16_t(v);
+    }
+    __syncwarp();
+    return __all_sync(FULL, ok);
+  }
   for (int i = lane * 4; i < n; i += 128) {
     const int4 v = *reinterpret_cast<const int4 *>(raw + i);
     ok &= (v.x == int16_t(v.x)) & (v.y == int16_t(v.y)) & (v.z == int16_t(v.z)) & (v.w == int16_t(v.w));
@@ -782,14 +831,13 @@ __device__ __forceinline__ auto &fusedEncSmem(int wib) {
 }
 
 // contexts of a warp-specialised producer: the state word only (x of ctx_entry)
-__device__ inline void loadCtxStates(uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                     size_t sub, int lane) {
+__device__ inline void loadCtxStates(uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *src,
+                                     int lane) {
   const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
   for (int k = lane; k < RCTX; k += 32) {
     const int id = rctx_inv(k);
-    if (imp) {
-      const cabac_ctx_model m = ctxIn[sub * CABAC_NUM_CTX + id];
+    if (src) {
+      const cabac_ctx_model m = src[id];
       ctx[k] = ctx_entry(m.state0, m.state1, 0).x;
     } else {
       ctx[k] = ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], 0).x;
@@ -797,26 +845,25 @@ __device__ inline void loadCtxStates(uint32_t *ctx, const cabac_substream_params
   }
   __syncwarp();
 }
-__device__ inline void storeCtxStates(const uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *ctxIn,
-                                      cabac_ctx_model *ctxOut, size_t sub, int lane) {
-  if (!ctxOut) return;
+__device__ inline void storeCtxStates(const uint32_t *ctx, const cabac_substream_params &p, const cabac_ctx_model *src,
+                                      cabac_ctx_model *dst, int lane) {
+  if (!dst) return;
   __syncwarp();
   const int qp = clipQp(p.qp);
-  const bool imp = (p.flags & CABAC_SUB_CTX_IN) && ctxIn != nullptr;
   for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
     cabac_ctx_model m;
     if (is_residual_ctx(id)) {
       const uint32_t x = ctx[rctx(id)];
       m.state0 = uint16_t(x >> 16);
       m.state1 = uint16_t(x & 0xFFFFu);
-    } else if (imp) {
-      m = ctxIn[sub * CABAC_NUM_CTX + id];
+    } else if (src) {
+      m = src[id];
     } else {
       const uint32_t w = model_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], CABAC_CTX_INIT_TABLE[3][id]);
       m.state0 = uint16_t(model_state0(w));
       m.state1 = uint16_t(model_state1(w));
     }
-    ctxOut[sub * CABAC_NUM_CTX + id] = m;
+    dst[id] = m;
   }
 }
 
@@ -831,7 +878,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
                        uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu,
-                       uint32_t *__restrict__ ctxBins) {
+                       uint32_t *__restrict__ ctxBins, const WppArgs wpp) {
   constexpr bool kResolve = kMode == FUSED_RESOLVE;
   constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
   constexpr bool kWs = kMode == FUSED_WS;
@@ -859,8 +906,9 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    if constexpr (kWs) loadCtxStates(sm.ctx, p, ctxIn, sub, lane);
-    else loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
+    if constexpr (kWs) loadCtxStates(sm.ctx, p, ctxSrc, lane);
+    else loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     if constexpr (kWs) {  // the ring is empty here: every substream ends fully drained
       wsPushWord(*chan, chHead, WS_MK_CTL(WS_OP_START), lane);
       drained = chHead;
@@ -913,6 +961,16 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     uint64_t t = tuOffsets[sub];
     const uint64_t t1 = tuOffsets[sub + 1];
     if (t < t1) prefetchBlock(sm.raw, coeffs + tus[t].coeff_offset, tus[t], lane);
+    // WPP: the contexts after this substream's first CTU go to its snapshot row for the row below
+    bool wppPending = wpp.sync != nullptr;
+    const uint64_t tSync = wppPending ? t + wpp.sync[sub].sync_tus : 0;
+    auto wppSnapshot = [&]() {
+      cabac_ctx_model *row = wpp.snap + sub * CABAC_NUM_CTX;
+      if constexpr (kWs) storeCtxStates(sm.ctx, p, ctxSrc, row, lane);
+      else storeCtxEntries(sm.ctx, p, ctxSrc, row, lane);
+      wppPublish(wpp, sub, lane);
+      wppPending = false;
+    };
 
     // per-block producer state
     bool inTu = false, tsPath = false, bdpcm = false;
@@ -928,6 +986,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     for (;;) {
       int nq = 0;
       if (!inTu) {
+        if (wppPending && t >= tSync) wppSnapshot();  // every word of the TUs before t is resolved here
         if (t == t1) break;
         d = tus[t];
         if (geomKey(d) != gKey) {
@@ -1076,8 +1135,9 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       if (numBins) numBins[sub] = nb;
       if (status) status[sub] = st;
     }
-    if constexpr (kWs) storeCtxStates(sm.ctx, p, ctxIn, ctxOut, sub, lane);
-    else storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    if (wppPending) wppSnapshot();
+    if constexpr (kWs) storeCtxStates(sm.ctx, p, ctxSrc, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
+    else storeCtxEntries(sm.ctx, p, ctxSrc, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
     __syncwarp();
   }
   if constexpr (kWs) {  // nobody waits for EXIT to be taken: mark the channel urgent for good
@@ -1107,7 +1167,7 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
                cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
                const uint32_t *__restrict__ order, uint32_t *cursor, uint8_t *__restrict__ out,
                const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
-               uint32_t *__restrict__ numBins) {
+               uint32_t *__restrict__ numBins, const WppArgs wpp) {
   typedef EncWarpSmemT<kStream ? CABAC_NUM_CTX : RCTX> Smem;
   __shared__ Smem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -1115,10 +1175,11 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
     if (kStream)
-      loadCtxEntriesFull(sm.ctx, p, ctxIn, sub, lane);
+      loadCtxEntriesFull(sm.ctx, p, ctxSrc, lane);
     else
-      loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+      loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     uint64_t rc = kStream ? rawOffsets[sub] : 0;
     const uint64_t rc1 = kStream ? rawOffsets[sub + 1] : 0;
     uint32_t *cmdBase = kFused ? nullptr : cmds + cmdOffsets[sub];  // this substream's resolved command words
@@ -1132,6 +1193,16 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
     uint64_t t = tus ? tuOffsets[sub] : 0;
     const uint64_t t1 = tus ? tuOffsets[sub + 1] : 0;
+    // WPP: snapshot after the first CTU (sync_cmds recorded words in stream mode, sync_tus TUs otherwise)
+    bool wppPending = wpp.sync != nullptr;
+    const uint64_t syncAt = !wppPending ? 0 : (kStream ? rc + wpp.sync[sub].sync_cmds : t + wpp.sync[sub].sync_tus);
+    auto wppSnapshot = [&]() {
+      cabac_ctx_model *row = wpp.snap + sub * CABAC_NUM_CTX;
+      if (kStream) storeCtxEntriesFull(sm.ctx, row, lane);
+      else storeCtxEntries(sm.ctx, p, ctxSrc, row, lane);
+      wppPublish(wpp, sub, lane);
+      wppPending = false;
+    };
 
     // per-block producer state
     bool inTu = false, tsPath = false, bdpcm = false;
@@ -1148,10 +1219,13 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
     for (;;) {
       int nq = 0;
       if (!inTu) {
+        if (wppPending && (kStream ? rc : t) >= syncAt) wppSnapshot();
         if (kStream) {
           if (rc == rc1) break;
-          // up to 32 recorded commands, stopping at the next TU marker
-          const bool have = rc + lane < rc1;
+          // up to 32 recorded commands, stopping at the next TU marker (and at the WPP sync point)
+          uint64_t rcStop = rc1;
+          if (kStream && wppPending && syncAt < rc1) rcStop = syncAt;
+          const bool have = rc + lane < rcStop;
           const uint32_t w = have ? rawCmds[rc + lane] : (uint32_t(CABAC_CMD_TU) << 29);
           const uint32_t kind = w >> 29;
           const uint32_t stop = __ballot_sync(FULL, kind == CABAC_CMD_TU);
@@ -1318,10 +1392,11 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
       cmdCounts[sub] = cmdN;
       status[sub] = st;
     }
+    if (wppPending) wppSnapshot();
     if (kStream)
-      storeCtxEntriesFull(sm.ctx, ctxOut, sub, lane);
+      storeCtxEntriesFull(sm.ctx, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
     else
-      storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+      storeCtxEntries(sm.ctx, p, ctxSrc, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
     __syncwarp();
   }
 }
@@ -1424,18 +1499,27 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
                        const cabac_ctx_model *__restrict__ ctxIn, int32_t *__restrict__ coeffs,
                        uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
-                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor) {
+                       uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
+                       const WppArgs wpp) {
   __shared__ DecWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   DecWarpSmem &sm = smem[wib];
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    loadCtxEntries(sm.ctx, p, ctxIn, sub, lane);
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
+    loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     LsDecoder dec;  // identical on every lane
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
     const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
+    bool wppPending = wpp.sync != nullptr;
+    const uint64_t tSync = wppPending ? t0 + wpp.sync[sub].sync_tus : 0;
     for (uint64_t t = t0; t < t1; t++) {
+      if (wppPending && t >= tSync) {  // contexts after the first CTU: the row below starts from them
+        storeCtxEntries(sm.ctx, p, ctxSrc, wpp.snap + sub * CABAC_NUM_CTX, lane);
+        wppPublish(wpp, sub, lane);
+        wppPending = false;
+      }
       const cabac_tu_desc d = tus[t];
       const TuGeom g = makeGeom(d);
       const int n = g.tw * g.th;
@@ -1468,7 +1552,11 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       if (bitsRead) bitsRead[sub] = dec.bitsRead();
       if (status) status[sub] = dec.status;
     }
-    storeCtxEntries(sm.ctx, p, ctxIn, ctxOut, sub, lane);
+    if (wppPending) {
+      storeCtxEntries(sm.ctx, p, ctxSrc, wpp.snap + sub * CABAC_NUM_CTX, lane);
+      wppPublish(wpp, sub, lane);
+    }
+    storeCtxEntries(sm.ctx, p, ctxSrc, ctxOut ? ctxOut + sub * CABAC_NUM_CTX : nullptr, lane);
     __syncwarp();
   }
 }
@@ -1580,15 +1668,15 @@ static void buildRom(ScanRom &r) {
         r.cgScanInv[lw][lh][ys[k] * w + xs[k]] = uint8_t(k);
       }
     }
-  const int shapes[4][2] = {{4, 4}, {2, 2}, {2, 8}, {8, 2}};
-  for (int s = 0; s < 4; s++) {
-    const int w = shapes[s][0], h = shapes[s][1];
-    diag(w, h, xs, ys);
-    for (int k = 0; k < w * h; k++) {
-      r.inScan[s][k] = uint8_t(xs[k] | (ys[k] << 4));
-      r.inScanInv[s][ys[k] * w + xs[k]] = uint8_t(k);
+  for (int lcw = 0; lcw <= 4; lcw++)
+    for (int lch = 0; lcw + lch <= 4; lch++) {  // every coefficient-group shape of g_log2SbbSize (<= 16 positions)
+      const int w = 1 << lcw, h = 1 << lch, sh = 5 * lcw + lch;
+      diag(w, h, xs, ys);
+      for (int k = 0; k < w * h; k++) {
+        r.inScan[sh][k] = uint8_t(xs[k] | (ys[k] << 4));
+        r.inScanInv[sh][ys[k] * w + xs[k]] = uint8_t(k);
+      }
     }
-  }
 }
 
 cudaError_t uploadRom() {
@@ -1698,22 +1786,22 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
       const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
       encode_residual_kernel<FUSED_WS><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
       return cudaGetLastError();
     }
     if (sc.fusedResolve)
       encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
     else
       encode_residual_kernel<FUSED_LEGACY><<<persistentGrid(encode_residual_kernel<FUSED_LEGACY>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
     return cudaGetLastError();
   }
   produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       nullptr, nullptr, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr);
+      status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;
@@ -1736,7 +1824,7 @@ cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, 
   }
   encode_residual_kernel<FUSED_ESTIMATE><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins);
+      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins, WppArgs());
   return cudaGetLastError();
 }
 
@@ -1792,12 +1880,12 @@ cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, cons
   if (!sc.twoStage) {  // few, long substreams: one warp each, bytes straight out of the producer kernel
     produce_kernel<true, true><<<persistentGrid(produce_kernel<true, true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
         rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, tuFlags, ctxOut,
-        status ? status : sc.statusScratch, sc.order, sc.cursor, out, outOffsets, outSizes, numBins);
+        status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, out, outOffsets, outSizes, numBins, sc.wpp);
     return cudaGetLastError();
   }
   produce_kernel<true, false><<<persistentGrid(produce_kernel<true, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts,
-      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr);
+      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;
@@ -1828,7 +1916,7 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
   if (e != cudaSuccess) return e;
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
-      sc.order, sc.cursor);
+      sc.wpp.sync ? nullptr : sc.order, sc.cursor, sc.wpp);
   return cudaGetLastError();
 }
 

@@ -6,6 +6,14 @@
 
 namespace cabac {
 
+// WPP hand-over inside one launch (cabac_wpp_sync, include/cabac_b200.h): per-substream sync records, the
+// snapshot rows (CABAC_NUM_CTX models per substream) and the "published" flags.  sync == nullptr: off.
+struct WppArgs {
+  const cabac_wpp_sync *sync = nullptr;
+  cabac_ctx_model *snap = nullptr;
+  uint32_t *ready = nullptr;
+};
+
 // Device scratch of the scheduler (owned by the handle): per-substream cost, the
 // longest-first order and the work cursor.  Kernels launched per call: 3.
 struct Sched {
@@ -21,6 +29,7 @@ struct Sched {
   bool warpSpecialised = false;  // fused kernel: producer warps + one walker warp per CTA (FUSED_WS)
   bool fusedResolve = false;  // fused kernel: resolve probabilities lane-parallel before the serial walk
   bool twoStage;            // residual encode: stage P + stage D instead of the fused lockstep kernel
+  WppArgs wpp;              // WPP launches: substreams are claimed in index order instead of longest-first
 };
 constexpr int kLaunchesPerCodingCall = 3;
 

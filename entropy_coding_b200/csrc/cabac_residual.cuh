@@ -60,10 +60,12 @@ __device__ __forceinline__ int lastYBase(int ch) { return R_LAST_Y + 20 * ch; }
 struct ScanRom {
   uint8_t cgScan[4][4][64];     // [log2 wig][log2 hig][k] -> cgx | cgy << 4   (SCAN_UNGROUPED / DIAG)
   uint8_t cgScanInv[4][4][64];  // [..][cgy * wig + cgx] -> k
-  uint8_t inScan[4][16];        // [shape][p] -> px | py << 4                  (within one CG)
-  uint8_t inScanInv[4][16];     // [shape][py * gw + px] -> p
+  uint8_t inScan[25][16];       // [shape][p] -> px | py << 4                  (within one CG)
+  uint8_t inScanInv[25][16];    // [shape][py * gw + px] -> p
 };
-// shapes: 0 = 4x4, 1 = 2x2, 2 = 2 wide x 8 high, 3 = 8 wide x 2 high
+// shape = 5 * log2 CG width + log2 CG height (g_log2SbbSize, rom.cpp:41-50): 4x4 for blocks with both
+// sides >= 4; 2x2, 2x8 / 8x2 for 2-wide / 2-high blocks; 1x16 / 16x1 (and the smaller 1xN / Nx1) for the
+// one-sample-wide sub-partitions intra sub-partitioning (ISP) produces
 
 __device__ ScanRom g_rom;
 
@@ -98,16 +100,19 @@ __device__ inline TuGeom makeGeom(const cabac_tu_desc &d) {
   g.tw = min(32, g.w);
   g.th = min(32, g.h);
   g.log2tw = min(5, g.log2w);
-  // g_log2SbbSize, rom.cpp:41-50, for 2 <= w, h
+  // g_log2SbbSize, rom.cpp:41-50
   if (g.log2w >= 2 && g.log2h >= 2) {
-    g.log2cgw = 2; g.log2cgh = 2; g.shape = 0;
+    g.log2cgw = 2; g.log2cgh = 2;
+  } else if (g.log2w == 0) {
+    g.log2cgw = 0; g.log2cgh = min(g.log2h, 4);
+  } else if (g.log2h == 0) {
+    g.log2cgw = min(g.log2w, 4); g.log2cgh = 0;
   } else if (g.log2w == 1) {
-    if (g.log2h <= 2) { g.log2cgw = 1; g.log2cgh = 1; g.shape = 1; }
-    else              { g.log2cgw = 1; g.log2cgh = 3; g.shape = 2; }
+    g.log2cgw = 1; g.log2cgh = g.log2h <= 2 ? 1 : 3;
   } else {  // log2h == 1, log2w >= 2
-    if (g.log2w == 2) { g.log2cgw = 1; g.log2cgh = 1; g.shape = 1; }
-    else              { g.log2cgw = 3; g.log2cgh = 1; g.shape = 3; }
+    g.log2cgw = g.log2w == 2 ? 1 : 3; g.log2cgh = 1;
   }
+  g.shape = 5 * g.log2cgw + g.log2cgh;
   g.log2cg = g.log2cgw + g.log2cgh;
   g.lwig = min(5, g.log2w) - g.log2cgw;
   g.lhig = min(5, g.log2h) - g.log2cgh;

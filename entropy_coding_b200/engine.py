@@ -13,7 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .types import (CTX_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, TU_DT)
+from .types import (CTX_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, TU_DT, WPP_DT)
 
 
 class CabacError(RuntimeError):
@@ -282,6 +282,73 @@ class CabacEngine:
             self._check(rc, status)
         return dict(coeffs=coeffs, num_bins=bins, bits_read=bits, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
 
+    # ---- WPP: CTU rows with context hand-over in one launch (cabac_*_wpp) ----
+    def encode_residual_wpp(self, tus, tu_offsets, params, wpp, coeffs, out_offsets, packed=None, ctx_in=None,
+                            want_ctx=False, raise_on_status=True):
+        """cabac_encode_residual_wpp: like encode_residual_packed, substream i starting from the contexts
+        substream wpp[i].dep published after wpp[dep].sync_tus TUs."""
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        wpp = _np(wpp, WPP_DT)
+        n = len(params)
+        assert len(wpp) == n
+        if packed is None:
+            packed = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        entry = np.zeros(n + 1, np.uint64)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_residual_wpp(self.h, _hp(tus), _hp(tu_offsets), _hp(params), _hp(wpp), n,
+                                                _hp(coeffs), coeffs.size, _hp(ctx_in), _hp(out_offsets), _hp(packed),
+                                                packed.size, _hp(entry), _hp(sizes), _hp(bins), _hp(tu_flags),
+                                                _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(packed=packed[:int(entry[-1])], entry_points=entry, sizes=sizes, num_bins=bins,
+                    tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    def decode_residual_wpp(self, data, in_offsets, tus, tu_offsets, params, wpp, n_coeffs, ctx_in=None,
+                            want_ctx=False, raise_on_status=True, coeffs_out=None):
+        data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
+        tus, tu_offsets, params = _np(tus, TU_DT), _np(tu_offsets, np.uint64), _np(params, PARAMS_DT)
+        wpp = _np(wpp, WPP_DT)
+        n = len(params)
+        assert len(wpp) == n
+        coeffs = np.zeros(n_coeffs, np.int32) if coeffs_out is None else coeffs_out
+        assert coeffs.dtype == np.int32 and coeffs.size >= n_coeffs and coeffs.flags.c_contiguous
+        bins, bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_decode_residual_wpp(self.h, _hp(data), _hp(in_offsets), _hp(tus), _hp(tu_offsets),
+                                                _hp(params), _hp(wpp), n, _hp(ctx_in), _hp(coeffs), n_coeffs,
+                                                _hp(bins), _hp(bits), _hp(tu_flags), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(coeffs=coeffs, num_bins=bins, bits_read=bits, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    def encode_stream_wpp(self, cmds, cmd_offsets, tus, tu_offsets, params, wpp, coeffs, out_offsets, ctx_in=None,
+                          want_ctx=False, raise_on_status=True):
+        """Recorded command streams with CABAC_CMD_TU markers and WPP hand-over after wpp[i].sync_cmds words."""
+        cmds, cmd_offsets = _np(cmds, np.uint32), _np(cmd_offsets, np.uint64)
+        tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
+        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        wpp = _np(wpp, WPP_DT)
+        n = len(params)
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        tu_flags = np.zeros(len(tus), np.uint8)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_stream_wpp(self.h, _hp(cmds), _hp(cmd_offsets), _hp(tus), _hp(tu_offsets),
+                                              _hp(params), _hp(wpp), n, _hp(coeffs), coeffs.size, _hp(ctx_in),
+                                              _hp(out), _hp(out_offsets), _hp(sizes), _hp(bins), _hp(tu_flags),
+                                              _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
     def count_emulations(self, data, offsets):
         """countStartCodeEmulations per segment (reference bit_stream.cpp:157-181)."""
         data, offsets = _np(data, np.uint8), _np(offsets, np.uint64)
@@ -333,6 +400,20 @@ class CabacEngine:
     def ctx_init_id_dev(self, params, ctx_ref, ctx_bins, n, choice, costs=None):
         self._check(self.lib.cabac_ctx_init_id_dev(self.h, _dp(params), _dp(ctx_ref), _dp(ctx_bins), n, _dp(choice),
                                                    _dp(costs)))
+
+    def encode_residual_wpp_dev(self, tus, tu_offsets, params, wpp, n_sub, coeffs, out, out_offsets, out_sizes,
+                                num_bins=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_encode_residual_wpp_dev(self.h, _dp(tus), _dp(tu_offsets), _dp(params), _dp(wpp),
+                                                           n_sub, _dp(coeffs), _dp(ctx_in), _dp(out), _dp(out_offsets),
+                                                           _dp(out_sizes), _dp(num_bins), _dp(tu_flags), _dp(ctx_out),
+                                                           _dp(status)))
+
+    def decode_residual_wpp_dev(self, data, in_offsets, tus, tu_offsets, params, wpp, n_sub, coeffs, num_bins=None,
+                                bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_decode_residual_wpp_dev(self.h, _dp(data), _dp(in_offsets), _dp(tus),
+                                                           _dp(tu_offsets), _dp(params), _dp(wpp), n_sub, _dp(ctx_in),
+                                                           _dp(coeffs), _dp(num_bins), _dp(bits_read), _dp(tu_flags),
+                                                           _dp(ctx_out), _dp(status)))
 
     def decode_residual_dev(self, data, in_offsets, tus, tu_offsets, params, n_sub, coeffs, num_bins=None,
                             bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):

@@ -159,10 +159,23 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
   void contextsAssigned() { ctxDirty_ = true; }
 
   // ---- CABACWriter::residual_coding(tu, compID, cuCtx) on the device ----
-  // cuCtx (may be null) receives the LFNST / MTS side flags when the batch completes.
+  // cuCtx (may be null) receives the LFNST / MTS side flags BEFORE this returns: the reference's
+  // writer reads them right after the TUs of a CU (mts_idx, cabac_writer.cpp:2541-2543;
+  // residual_lfnst_mode, :2601-2618), long before the batch runs.  They follow from the last
+  // scan position and the significant coefficient groups alone, so the shim derives them from the
+  // block it copies into the slab anyway, with the reference's own CoeffCodingContext for the scan;
+  // the device reports the same bits per TU (tu_flags) and complete() cross-checks them.
   void residual_coding(const Common::TransformUnit &tu, Common::ComponentID compID, Common::CUCtx *cuCtx = nullptr) {
     if (compID == Common::COMPONENT_Cr && tu.jointCbCr == 3) return;  // cabac_writer.cpp:2428-2430
+    refuseUnsupportedTools(tu);
     const Common::CompArea &blk = tu.blocks[compID];
+    const uint8_t hostFlags = sideFlags(tu, compID);
+    if (cuCtx) {  // cabac_writer.cpp:2460-2478, 2520-2523
+      cuCtx->violatesLfnstConstrained[Common::toChannelType(compID)] |= (hostFlags & CABAC_TUR_VIOLATES_LFNST) != 0;
+      cuCtx->lfnstLastScanPos |= (hostFlags & CABAC_TUR_LFNST_LAST_POS) != 0;
+      cuCtx->mtsLastScanPos |= (hostFlags & CABAC_TUR_MTS_LAST_POS) != 0;
+      cuCtx->violatesMtsCoeffConstraint |= (hostFlags & CABAC_TUR_VIOLATES_MTS) != 0;
+    }
     cabac_tu_desc d{};
     d.log2_w = uint8_t(Common::floorLog2(blk.width));
     d.log2_h = uint8_t(Common::floorLog2(blk.height));
@@ -178,7 +191,53 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
     const Common::TCoeff *src = tu.getCoeffs(compID).buf;  // row-major, stride == width (unit.hpp:551)
     slab.insert(slab.end(), src, src + size_t(blk.width) * blk.height);
     rec_.residual(d);
-    tuSinks_.push_back({cuCtx, int(compID)});
+    tuSinks_.push_back({hostFlags});
+  }
+
+  // The CUCtx side effects of CABACWriter::residual_coding for one block, as CABAC_TUR_* bits.
+  static uint8_t sideFlags(const Common::TransformUnit &tu, Common::ComponentID compID) {
+    const bool ts = tu.mtsIdx[compID] == Common::MTS_SKIP;
+    if (ts && !tu.cs->slice->getTSResidualCodingDisabledFlag()) return 0;  // residual_codingTS touches no CUCtx
+    Common::CoeffCodingContext cctx(tu, compID, tu.cs->slice->getSignDataHidingEnabledFlag());
+    const Common::TCoeff *coeff = tu.getCoeffs(compID).buf;
+    const Common::CompArea &blk = tu.blocks[compID];
+    const bool luma = Common::isLuma(compID);
+    const bool sbtZero = tu.cs->sps->getUseMTS() && tu.cu->sbtInfo != 0 && blk.height <= 32 && blk.width <= 32 &&
+                         compID == Common::COMPONENT_Y;
+    int last = -1;
+    bool farGroup = false;  // a significant, coded group beyond the 16 x 16 low-frequency corner
+    for (int scanPos = 0; scanPos < int(cctx.maxNumCoeff()); scanPos++) {
+      if (!coeff[cctx.blockPos(scanPos)]) continue;
+      last = scanPos;
+      const int cg = scanPos >> cctx.log2CGSize();
+      if (luma && !farGroup) {
+        cctx.initSubblock(cg, true);
+        const bool zeroed = sbtZero && ((blk.height == 32 && cctx.cgPosY() >= (16 >> cctx.log2CGHeight())) ||
+                                        (blk.width == 32 && cctx.cgPosX() >= (16 >> cctx.log2CGWidth())));
+        farGroup = !zeroed && (cctx.cgPosY() > 3 || cctx.cgPosX() > 3);
+      }
+    }
+    CHECK(last < 0, "Coefficient coding called for empty TU");
+    uint8_t f = 0;
+    if (!ts && blk.height >= 4 && blk.width >= 4) {
+      const int maxLfnstPos = ((blk.height == 4 && blk.width == 4) || (blk.height == 8 && blk.width == 8)) ? 7 : 15;
+      if (last > maxLfnstPos) f |= CABAC_TUR_VIOLATES_LFNST;
+      if (last >= (luma ? Common::LFNST_LAST_SIG_LUMA : Common::LFNST_LAST_SIG_CHROMA)) f |= CABAC_TUR_LFNST_LAST_POS;
+    }
+    if (luma && !ts && last >= 1) f |= CABAC_TUR_MTS_LAST_POS;
+    if (farGroup) f |= CABAC_TUR_VIOLATES_MTS;
+    return f;
+  }
+  // Range-extension tools change the Rice derivation (persistent Rice adaptation, cabac_writer.cpp:2495-2503,
+  // 2822-2850; RRC Rice extension, context_modelling.cpp:74-78; TSRC Rice, cabac_writer.cpp:2898-2920; extended
+  // precision: maxLog2TrDynamicRange != 15).  The device path implements VVC v1: refuse instead of mis-coding.
+  static void refuseUnsupportedTools(const Common::TransformUnit &tu) {
+    const auto &rext = tu.cs->sps->getSpsRangeExtension();
+    CHECK(rext.getPersistentRiceAdaptationEnabledFlag(), "B200 CABAC engine: persistent Rice adaptation is not supported");
+    CHECK(rext.getRrcRiceExtensionEnableFlag(), "B200 CABAC engine: RRC Rice extension is not supported");
+    CHECK(rext.getExtendedPrecisionProcessingFlag(), "B200 CABAC engine: extended precision processing is not supported");
+    CHECK(rext.getTSRCRicePresentFlag() && tu.cs->slice->get_tsrc_index() != 0,
+          "B200 CABAC engine: TSRC Rice index != 0 is not supported");
   }
 
  private:
@@ -195,8 +254,7 @@ class GpuBinEncoder : public EntropyCoding::BinEncIf {
   void complete(const SubstreamResult &r, const uint8_t *tuFlags);
 
   struct TuSink {
-    Common::CUCtx *cuCtx;
-    int comp;
+    uint8_t hostFlags;  // sideFlags() at record time; the device must report the same
   };
   std::unique_ptr<GpuEncodeSession> own_;
   GpuEncodeSession *session_;
@@ -258,16 +316,11 @@ inline void GpuBinEncoder::complete(const SubstreamResult &r, const uint8_t *tuF
     for (unsigned k = 0; k < CABAC_NUM_CTX; k++)
       st[k] = Common::BinProbModel_Std(r.ctx[k].state0, r.ctx[k].state1, st[k].getRate());
   }
-  for (size_t t = 0; t < tuSinks_.size(); t++) {  // cabac_writer.cpp:2460-2478, 2520-2523
-    Common::CUCtx *c = tuSinks_[t].cuCtx;
-    if (!c) continue;
-    const uint8_t f = tuFlags[t];
-    const Common::ChannelType ch = Common::toChannelType(Common::ComponentID(tuSinks_[t].comp));
-    c->violatesLfnstConstrained[ch] |= (f & CABAC_TUR_VIOLATES_LFNST) != 0;
-    c->lfnstLastScanPos |= (f & CABAC_TUR_LFNST_LAST_POS) != 0;
-    if (tuSinks_[t].comp == 0) c->mtsLastScanPos |= (f & CABAC_TUR_MTS_LAST_POS) != 0;
-    c->violatesMtsCoeffConstraint |= (f & CABAC_TUR_VIOLATES_MTS) != 0;
-  }
+  constexpr uint8_t side = CABAC_TUR_VIOLATES_LFNST | CABAC_TUR_LFNST_LAST_POS | CABAC_TUR_MTS_LAST_POS | CABAC_TUR_VIOLATES_MTS;
+  for (size_t t = 0; t < tuSinks_.size(); t++)  // the CUCtx was filled at record time; the device agrees or we stop
+    CHECK((tuFlags[t] & side) != tuSinks_[t].hostFlags,
+          "CUCtx side flags of TU " + std::to_string(t) + ": device " + std::to_string(tuFlags[t] & side) + " vs host " +
+              std::to_string(tuSinks_[t].hostFlags));
   completed_ = true;
 }
 

@@ -37,6 +37,13 @@ class GpuResidualReader {
   // Queues residual_coding(tu, compID, cuCtx) on the current substream.
   void residual_coding(Common::TransformUnit &tu, Common::ComponentID compID, Common::CUCtx *cuCtx = nullptr) {
     if (compID == Common::COMPONENT_Cr && tu.jointCbCr == 3) return;  // cabac_reader.cpp:2651-2653
+    {  // VVC v1 residual coding only: refuse the range-extension Rice tools instead of mis-parsing
+      const auto &rext = tu.cs->sps->getSpsRangeExtension();
+      CHECK(rext.getPersistentRiceAdaptationEnabledFlag() || rext.getRrcRiceExtensionEnableFlag() ||
+                rext.getExtendedPrecisionProcessingFlag() ||
+                (rext.getTSRCRicePresentFlag() && tu.cs->slice->get_tsrc_index() != 0),
+            "B200 CABAC engine: range-extension residual coding tools are not supported");
+    }
     const Common::CompArea &blk = tu.blocks[compID];
     const Common::CodingUnit &cu = *tu.cu;
     cabac_tu_desc d{};

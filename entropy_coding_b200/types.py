@@ -9,7 +9,9 @@ PARAMS_DT = np.dtype([("qp", "i1"), ("init_id", "u1"), ("flags", "u1"), ("reserv
 TU_DT = np.dtype([("coeff_offset", "<u8"), ("log2_w", "u1"), ("log2_h", "u1"), ("comp_id", "u1"),
                   ("flags", "u1"), ("reserved", "<u4")])
 CTX_DT = np.dtype([("state0", "<u2"), ("state1", "<u2")])
-assert PARAMS_DT.itemsize == 4 and TU_DT.itemsize == 16 and CTX_DT.itemsize == 4
+WPP_DT = np.dtype([("dep", "<u4"), ("sync_tus", "<u4"), ("sync_cmds", "<u4"), ("reserved", "<u4")])  # cabac_wpp_sync
+WPP_NONE = 0xFFFFFFFF
+assert PARAMS_DT.itemsize == 4 and TU_DT.itemsize == 16 and CTX_DT.itemsize == 4 and WPP_DT.itemsize == 16
 
 # status codes
 OK, ERR_CUDA, ERR_ARG, ERR_SUBSTREAM = 0, -1, -2, -3

@@ -137,8 +137,8 @@ enum {
 typedef struct cabac_tu_desc {
   uint64_t coeff_offset; /* first TCoeff (int32) of the block in the slab;
                             row-major, stride == width (unit.hpp:551)        */
-  uint8_t log2_w;        /* width  = 1 << log2_w, 2..64                      */
-  uint8_t log2_h;        /* height = 1 << log2_h, 2..64                      */
+  uint8_t log2_w;        /* width  = 1 << log2_w, 1..64 (1 and 2: ISP parts) */
+  uint8_t log2_h;        /* height = 1 << log2_h, 1..64                      */
   uint8_t comp_id;       /* 0 = Y, 1 = Cb, 2 = Cr                            */
   uint8_t flags;         /* CABAC_TU_*                                       */
   uint32_t reserved;
@@ -347,6 +347,95 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in,
                               int32_t *coeffs, uint32_t *num_bins,
                               uint32_t *bits_read, uint8_t *tu_flags,
                               cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* ---- WPP: CTU rows with context hand-over, one launch ---------------------- */
+/* With entropy_coding_sync_enabled a slice is one substream per CTU row and row r
+ * starts from the contexts row r-1 held after its FIRST CTU
+ * (VTM Lib/EncoderLib/EncSlice.cpp:2057-2072 load, :2085-2089 store;
+ * Lib/DecoderLib/DecSlice.cpp:194-210, 241-245; the copy is Ctx::operator=,
+ * src/common/contexts.cpp:1096-1108).  The *_wpp entry points take one
+ * cabac_wpp_sync per substream and resolve the hand-over on the device: the
+ * predecessor's warp publishes its contexts at its sync point, the dependant's
+ * warp waits for them - every CTU is coded once, in one launch.
+ *   dep        index of the substream this one starts from, CABAC_WPP_NONE for
+ *              a row that starts from Ctx::init / its ctx_in row (first row of
+ *              a slice or tile).  Must be < the substream's own index.
+ *   sync_tus   residual entry points: the substream's contexts are published
+ *              after this many of its TUs (its first CTU)
+ *   sync_cmds  stream entry point: ... after this many of its command words
+ *              (TU markers count as one word)
+ * A substream shorter than its sync point publishes at its end.             */
+#define CABAC_WPP_NONE 0xFFFFFFFFu
+typedef struct cabac_wpp_sync {
+  uint32_t dep;
+  uint32_t sync_tus;
+  uint32_t sync_cmds;
+  uint32_t reserved;
+} cabac_wpp_sync;
+
+int cabac_encode_residual_wpp_dev(cabac_handle *h, const cabac_tu_desc *tus,
+                                  const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params,
+                                  const cabac_wpp_sync *wpp, size_t n_sub,
+                                  const int32_t *coeffs,
+                                  const cabac_ctx_model *ctx_in, uint8_t *out,
+                                  const uint64_t *out_offsets, uint32_t *out_sizes,
+                                  uint32_t *num_bins, uint8_t *tu_flags,
+                                  cabac_ctx_model *ctx_out, uint32_t *status);
+/* Host pointers; returns the packed payload + entry points like
+ * cabac_encode_residual_packed.                                             */
+int cabac_encode_residual_wpp(cabac_handle *h, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets,
+                              const cabac_substream_params *params,
+                              const cabac_wpp_sync *wpp, size_t n_sub,
+                              const int32_t *coeffs, size_t n_coeffs,
+                              const cabac_ctx_model *ctx_in,
+                              const uint64_t *out_offsets, uint8_t *packed,
+                              size_t packed_cap, uint64_t *entry_points,
+                              uint32_t *out_sizes, uint32_t *num_bins,
+                              uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                              uint32_t *status);
+int cabac_decode_residual_wpp_dev(cabac_handle *h, const uint8_t *in,
+                                  const uint64_t *in_offsets,
+                                  const cabac_tu_desc *tus,
+                                  const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params,
+                                  const cabac_wpp_sync *wpp, size_t n_sub,
+                                  const cabac_ctx_model *ctx_in, int32_t *coeffs,
+                                  uint32_t *num_bins, uint32_t *bits_read,
+                                  uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                  uint32_t *status);
+int cabac_decode_residual_wpp(cabac_handle *h, const uint8_t *in,
+                              const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets,
+                              const cabac_substream_params *params,
+                              const cabac_wpp_sync *wpp, size_t n_sub,
+                              const cabac_ctx_model *ctx_in, int32_t *coeffs,
+                              size_t n_coeffs, uint32_t *num_bins,
+                              uint32_t *bits_read, uint8_t *tu_flags,
+                              cabac_ctx_model *ctx_out, uint32_t *status);
+/* Recorded command streams (the CABACWriter seam) with WPP hand-over.       */
+int cabac_encode_stream_wpp_dev(cabac_handle *h, const uint32_t *cmds,
+                                const uint64_t *cmd_offsets,
+                                const cabac_tu_desc *tus,
+                                const uint64_t *tu_offsets,
+                                const cabac_substream_params *params,
+                                const cabac_wpp_sync *wpp, size_t n_sub,
+                                const int32_t *coeffs,
+                                const cabac_ctx_model *ctx_in, uint8_t *out,
+                                const uint64_t *out_offsets, uint32_t *out_sizes,
+                                uint32_t *num_bins, uint8_t *tu_flags,
+                                cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_encode_stream_wpp(cabac_handle *h, const uint32_t *cmds,
+                            const uint64_t *cmd_offsets, const cabac_tu_desc *tus,
+                            const uint64_t *tu_offsets,
+                            const cabac_substream_params *params,
+                            const cabac_wpp_sync *wpp, size_t n_sub,
+                            const int32_t *coeffs, size_t n_coeffs,
+                            const cabac_ctx_model *ctx_in, uint8_t *out,
+                            const uint64_t *out_offsets, uint32_t *out_sizes,
+                            uint32_t *num_bins, uint8_t *tu_flags,
+                            cabac_ctx_model *ctx_out, uint32_t *status);
 
 /* ---- substream packing + entry points ------------------------------------ */
 /* Compacts the per-substream output slabs of an encode call into one

@@ -160,19 +160,20 @@ int main(int argc, char **argv) {
         applyTsAllowed(tp, s.tus[t], false);
         CUCtx cuCtx(s.p.qp);
         if (v == 2) {
-          static_cast<GpuBinEncoder *>(coder[v])->residual_coding(tp.tu, ComponentID(s.tus[t].comp_id), nullptr);
+          static_cast<GpuBinEncoder *>(coder[v])->residual_coding(tp.tu, ComponentID(s.tus[t].comp_id), &cuCtx);
         } else {
           wr.residual_coding(tp.tu, ComponentID(s.tus[t].comp_id), &cuCtx);
         }
-        if (v == 0) {
-          uint8_t f = 0;
-          if (tp.tu.mtsIdx[s.tus[t].comp_id] == MTS_SKIP) f |= CABAC_TUR_TS;
-          if (cuCtx.violatesLfnstConstrained[toChannelType(ComponentID(s.tus[t].comp_id))]) f |= CABAC_TUR_VIOLATES_LFNST;
-          if (cuCtx.lfnstLastScanPos) f |= CABAC_TUR_LFNST_LAST_POS;
-          if (cuCtx.mtsLastScanPos) f |= CABAC_TUR_MTS_LAST_POS;
-          if (cuCtx.violatesMtsCoeffConstraint) f |= CABAC_TUR_VIOLATES_MTS;
-          flagsRef[i].push_back(f);
-        }
+        uint8_t f = 0;
+        if (tp.tu.mtsIdx[s.tus[t].comp_id] == MTS_SKIP) f |= CABAC_TUR_TS;
+        if (cuCtx.violatesLfnstConstrained[toChannelType(ComponentID(s.tus[t].comp_id))]) f |= CABAC_TUR_VIOLATES_LFNST;
+        if (cuCtx.lfnstLastScanPos) f |= CABAC_TUR_LFNST_LAST_POS;
+        if (cuCtx.mtsLastScanPos) f |= CABAC_TUR_MTS_LAST_POS;
+        if (cuCtx.violatesMtsCoeffConstraint) f |= CABAC_TUR_VIOLATES_MTS;
+        if (v == 0) flagsRef[i].push_back(f);
+        // the TU seam must have filled the CUCtx when residual_coding returns (mts_idx / residual_lfnst_mode
+        // read it right after the TUs of a CU, cabac_writer.cpp:2541-2543, 2601-2618) - not at flush time
+        if (v == 2) EXPECT(f == flagsRef[i][t], "substream %d TU %zu: TU-seam CUCtx at record time %u vs %u", i, t, f, flagsRef[i][t]);
       }
       wr.end_of_slice();  // encodeBinTrm(1) + finish(), cabac_writer.cpp:104-107
     }
@@ -346,6 +347,62 @@ int main(int argc, char **argv) {
         EXPECT(batch.fracBitsAfterTu(i, t) == want[i][t], "substream %d TU %zu: running estimate differs", i, t);
       totalFrac += want[i].back();
     }
+  }
+
+  // ---- E: the consumers of the CUCtx: residual_coding + mts_idx per CU, MTS enabled ----
+  // mts_idx (cabac_writer.cpp:2537-2563) is signalled only if the CUCtx the TU call just filled says
+  // so; with flags delivered at flush time the TU seam would silently drop it.
+  size_t mtsSignalled = 0;
+  {
+    GpuEncodeSession sess(eng);
+    std::vector<std::unique_ptr<GpuBinEncoder>> encs;
+    std::vector<std::unique_ptr<OutputBitstream>> bss;
+    std::vector<std::vector<uint8_t>> want(nSub);
+    std::mt19937 r2(seed + 99);
+    for (int i = 0; i < nSub; i++) {
+      const SubSpec &s = subs[i];
+      Harness hs(s.p, true);
+      const unsigned cuSeed = u(r2);
+      encs.emplace_back(new GpuBinEncoder(sess));
+      bss.emplace_back(new OutputBitstream());
+      BinEncoder_Std ref;
+      OutputBitstream bsRef;
+      BinEncIf *coder[2] = {&ref, encs.back().get()};
+      OutputBitstream *bs[2] = {&bsRef, bss.back().get()};
+      for (int v = 0; v < 2; v++) {
+        CABACWriter wr(*coder[v]);
+        wr.initBitstream(bs[v]);
+        coder[v]->reset(s.p.qp, s.p.init_id);
+        if (v) encs.back()->setSliceTools(s.p.flags & CABAC_SUB_DEP_QUANT, s.p.flags & CABAC_SUB_SIGN_HIDING, false);
+        std::mt19937 cuRng(cuSeed);
+        for (const cabac_tu_desc &d0 : s.tus) {
+          if (d0.comp_id != 0 || d0.log2_w > 5 || d0.log2_h > 5 || (d0.flags & (CABAC_TU_TS | CABAC_TU_BDPCM))) continue;
+          cabac_tu_desc d = d0;
+          d.flags = CABAC_TU_TS_ALLOWED;
+          TuPair tp;
+          makeTu(tp, hs, d, slab.data());
+          static_cast<UnitArea &>(tp.cu) = static_cast<const UnitArea &>(tp.tu);
+          tp.cu.firstTU = tp.cu.lastTU = &tp.tu;
+          const int pick = int(cuRng() % 6);
+          tp.tu.mtsIdx[COMPONENT_Y] = pick < 2 ? MTS_DCT2_DCT2 : uint8_t(MTS_DST7_DST7 + (pick - 2));
+          CUCtx cuCtx(s.p.qp);
+          const unsigned before = coder[v]->getNumBins();
+          if (v) encs.back()->residual_coding(tp.tu, COMPONENT_Y, &cuCtx);
+          else wr.residual_coding(tp.tu, COMPONENT_Y, &cuCtx);
+          const unsigned mid = coder[v]->getNumBins();
+          wr.mts_idx(tp.cu, &cuCtx);
+          if (!v) mtsSignalled += coder[v]->getNumBins() != mid;
+          (void)before;
+        }
+        wr.end_of_slice();
+      }
+      want[i] = closeSubstream(bsRef);
+    }
+    sess.flush();
+    for (int i = 0; i < nSub; i++)
+      EXPECT(closeSubstream(*bss[i]) == want[i], "substream %d: residual_coding + mts_idx bytes differ on the TU seam", i);
+    printf("mts_idx after device-side residual_coding: signalled for %zu CUs, bytes equal\n", mtsSignalled);
+    EXPECT(mtsSignalled > 0, "mts_idx was never signalled: the case is not exercised");
   }
 
   if (g_fail) {

@@ -292,10 +292,11 @@ def test_stream_mixed_vs_oracle(engine, oracle, seed, flags):
 
 
 def test_residual_all_shapes_single_coeff(engine, oracle):
-    """Every block shape 2..64 x 2..64, one level at DC / at the last coded column, extreme magnitudes."""
+    """Every block shape 1..64 x 1..64 (1- and 2-wide: ISP sub-partitions), one level at DC / at the last
+    coded column, extreme magnitudes."""
     tus, coeffs, cur = [], [], 0
-    for lw in range(1, 7):
-        for lh in range(1, 7):
+    for lw in range(0, 7):
+        for lh in range(0, 7):
             for pos, val in ((0, -3), ((1 << min(lw, 5)) - 1, 32767), (0, -32768)):
                 t = np.zeros(1, TU_DT)
                 t["coeff_offset"], t["log2_w"], t["log2_h"], t["comp_id"] = cur, lw, lh, (lw + lh) % 3
@@ -327,6 +328,55 @@ def test_residual_all_shapes_single_coeff(engine, oracle):
     for i in range(n):
         tot, _ = oracle.estimate_residual(tus[i:i + 1], coeffs, 30, 2, T | SUB_DEP_QUANT)
         assert int(est["est_bits"][i]) == tot, (i, tus[i])
+
+
+def test_residual_narrow_isp_shapes_random(engine, oracle):
+    """Intra sub-partition blocks (1xN, 2xN, Nx1, Nx2: coefficient groups 1x16 / 2x8 / 16x1 / 8x2 / 2x2,
+    rom.cpp:41-50) with dense random levels: every encoder kernel and the decoder against the oracle."""
+    rng = np.random.default_rng(1234)
+    shapes = [(0, 4), (0, 5), (0, 6), (4, 0), (5, 0), (6, 0), (1, 3), (1, 4), (1, 5), (3, 1), (4, 1), (5, 1), (6, 1),
+              (1, 6), (1, 1), (1, 2), (2, 1), (0, 2), (2, 0), (0, 3), (3, 0), (0, 1), (1, 0)]
+    tus, coeffs, cur = [], [], 0
+    for rep in range(6):
+        for lw, lh in shapes:
+            t = np.zeros(1, TU_DT)
+            t["coeff_offset"], t["log2_w"], t["log2_h"], t["comp_id"] = cur, lw, lh, 0 if rep < 4 else 1 + rep % 2
+            w, h = 1 << lw, 1 << lh
+            c = np.rint(rng.laplace(0, [0.6, 2.0, 9.0, 200.0][rep % 4], (h, w))).astype(np.int32)
+            c[min(h, 32):, :] = 0
+            c[:, min(w, 32):] = 0
+            if not c.any():
+                c[0, 0] = 2
+            tus.append(t)
+            coeffs.append(c.reshape(-1))
+            cur += c.size
+    tus, coeffs = np.concatenate(tus), np.concatenate(coeffs)
+    per = len(shapes)
+    n = len(tus) // per
+    params = np.zeros(n, PARAMS_DT)
+    params["qp"], params["init_id"] = [0, 22, 37, 51, 30, 30], 2
+    params["flags"] = [T | SUB_DEP_QUANT, T | SUB_SIGN_HIDING, T, T | SUB_DEP_QUANT, T | SUB_DEP_QUANT, T]
+    wl = W.Workload(tus, (np.arange(n + 1) * per).astype(np.uint64), params, coeffs)
+    want = []
+    for i in range(n):
+        p = params[i]
+        want.append(oracle.encode_residual(tus[i * per:(i + 1) * per], coeffs, int(p["qp"]), 2, int(p["flags"]), want_ctx=True))
+    for mode in (1, 2, 3):
+        engine.set_encoder_mode(mode)
+        try:
+            r, outs = run_residual(engine, wl)
+        finally:
+            engine.set_encoder_mode(0)
+        for i in range(n):
+            assert outs[i].tobytes() == want[i][0].tobytes(), (mode, i)
+            assert int(r["num_bins"][i]) == want[i][1] and (r["tu_flags"][i * per:(i + 1) * per] == want[i][2]).all()
+    d = engine.decode_residual(np.concatenate(outs), offsets_of(r["sizes"]), tus, wl.tu_offsets, params, coeffs.size)
+    for i in range(n):
+        dec = oracle.decode_residual(want[i][0], tus[i * per:(i + 1) * per], coeffs.size, int(params[i]["qp"]), 2,
+                                     int(params[i]["flags"]))[0]
+        a = int(tus[i * per]["coeff_offset"])
+        b = int(tus[(i + 1) * per - 1]["coeff_offset"]) + (1 << int(tus[(i + 1) * per - 1]["log2_w"] + tus[(i + 1) * per - 1]["log2_h"]))
+        assert (d["coeffs"][a:b] == dec[a:b]).all(), i
 
 
 def test_residual_errors(engine):

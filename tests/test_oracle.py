@@ -152,8 +152,8 @@ def test_oracle_edge_cases(oracle):
     # empty command stream, terminate only (KAT0); zero-length EP; single-coefficient TUs of every shape
     out, nb = oracle.encode_bins([mk_ep(0, 0)], 32, 2, T)
     assert out.tobytes().hex() == "fe80" and nb == 1
-    for lw in range(1, 7):
-        for lh in range(1, 7):
+    for lw in range(0, 7):
+        for lh in range(0, 7):
             tus = np.zeros(1, TU_DT)
             tus["log2_w"], tus["log2_h"] = lw, lh
             for pos in (0, (1 << (min(lw, 5))) - 1):
@@ -169,6 +169,36 @@ def test_oracle_edge_cases(oracle):
     out, nb, tuf = oracle.encode_residual(tus, coeffs, 0, 2, T | SUB_DEP_QUANT)
     dec, bits, tuf2, st = oracle.decode_residual(out, tus, 16, 0, 2, T | SUB_DEP_QUANT)
     assert st == 0 and (dec == coeffs).all()
+
+
+def test_oracle_vs_ref_isp_shapes(oracle, ref):
+    """1xN / 2xN / Nx1 / Nx2 blocks (intra sub-partitions; coefficient groups 1x16, 2x8, 16x1, 8x2, 2x2 of
+    g_log2SbbSize, rom.cpp:41-50): restatement == compiled reference on dense random levels, encode + decode."""
+    rng = np.random.default_rng(4321)
+    shapes = [(0, 4), (0, 5), (0, 6), (4, 0), (5, 0), (6, 0), (1, 3), (1, 4), (1, 5), (3, 1), (4, 1), (5, 1), (6, 1),
+              (1, 6), (1, 1), (1, 2), (2, 1), (0, 2), (2, 0), (0, 3), (3, 0), (0, 1), (1, 0), (0, 0)]
+    for rep in range(8):
+        tus, coeffs, cur = np.zeros(len(shapes), TU_DT), [], 0
+        for k, (lw, lh) in enumerate(shapes):
+            w, h = 1 << lw, 1 << lh
+            c = np.rint(rng.laplace(0, [0.6, 2.0, 9.0, 300.0][rep % 4], (h, w))).astype(np.int32)
+            c[min(h, 32):, :] = 0
+            c[:, min(w, 32):] = 0
+            if not c.any():
+                c[0, 0] = -1
+            tus[k]["coeff_offset"], tus[k]["log2_w"], tus[k]["log2_h"], tus[k]["comp_id"] = cur, lw, lh, rep % 3
+            coeffs.append(c.reshape(-1))
+            cur += c.size
+        coeffs = np.concatenate(coeffs)
+        flags = T | (SUB_DEP_QUANT if rep % 2 else SUB_SIGN_HIDING)
+        qp = [0, 22, 37, 51][rep % 4]
+        ro = oracle.encode_residual(tus, coeffs, qp, 2, flags, want_ctx=True)
+        rr = ref.encode_residual(tus, coeffs, qp, 2, flags, want_ctx=True)
+        assert ro[0].tobytes() == rr[0].tobytes() and ro[1] == rr[1] and (ro[2] == rr[2]).all()
+        assert (ro[3] == rr[3]).all()
+        od = oracle.decode_residual(ro[0], tus, coeffs.size, qp, 2, flags)
+        rd = ref.decode_residual(ro[0], tus, coeffs.size, qp, 2, flags)
+        assert (od[0] == rd[0]).all() and od[1] == rd[1] and od[3] == rd[3] == 0
 
 
 def test_stream_oracle_vs_reference(oracle, ref):
