@@ -143,6 +143,10 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
       if (e != cudaSuccess) return e;
       h->wppSubs = cap2;
     }
+    static const uint32_t spinLimit = getenv("CABAC_B200_WPP_SPIN") ? uint32_t(atoll(getenv("CABAC_B200_WPP_SPIN"))) : (1u << 24);
+    sc.wpp.spinLimit = spinLimit;
+    static const uint32_t dbg = getenv("CABAC_B200_WPP_DEBUG") ? uint32_t(atoi(getenv("CABAC_B200_WPP_DEBUG"))) : 0u;
+    sc.wpp.debug = dbg;
     sc.wpp.sync = sync;
     sc.wpp.snap = static_cast<cabac_ctx_model *>(h->wppScratch);
     sc.wpp.ready = reinterpret_cast<uint32_t *>(sc.wpp.snap + h->wppSubs * CABAC_NUM_CTX);

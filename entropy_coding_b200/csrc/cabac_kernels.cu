@@ -279,13 +279,29 @@ __device__ __forceinline__ void stRelease(uint32_t *p, uint32_t v) {
 // (CABAC_SUB_CTX_IN) or nullptr = Ctx::init(qp, initId).  Blocks until a WPP snapshot is published.
 __device__ __forceinline__ const cabac_ctx_model *ctxSource(const cabac_substream_params &p,
                                                             const cabac_ctx_model *ctxIn, size_t sub,
-                                                            const WppArgs &wpp, int lane) {
+                                                            const WppArgs &wpp, int lane, uint32_t &st) {
   if (wpp.sync) {
     const uint32_t dep = wpp.sync[sub].dep;
-    if (dep != CABAC_WPP_NONE) {
-      if (lane == 0)
-        while (ldAcquire(wpp.ready + dep) == 0u) __nanosleep(100);
+    if (dep != CABAC_WPP_NONE && !(wpp.debug & 1u)) {
+      // A predecessor that never publishes (a malformed dep chain) ends in a status bit, not in a hung GPU:
+      // ~2^24 polls of >= 100 ns are far beyond any legitimate wait (a chain of first CTUs).
+      // every lane polls (a warp-uniform loop: no lane-0-only region for the others to wait out)
+      const volatile uint32_t *flag = wpp.ready + dep;
+      uint32_t spins = 0;
+      bool ok = true;
+      while (*flag == 0u) {
+        __nanosleep(100);
+        if (++spins > wpp.spinLimit) {
+          ok = false;
+          break;
+        }
+      }
       __syncwarp();
+      if (!__all_sync(FULL, ok)) {
+        st |= CABAC_SS_WPP_TIMEOUT;
+        return nullptr;
+      }
+      __threadfence();
       (void)ldAcquire(wpp.ready + dep);  // every lane orders its own snapshot loads after the flag
       return wpp.snap + size_t(dep) * CABAC_NUM_CTX;
     }
@@ -293,6 +309,7 @@ __device__ __forceinline__ const cabac_ctx_model *ctxSource(const cabac_substrea
   return ((p.flags & CABAC_SUB_CTX_IN) && ctxIn) ? ctxIn + sub * CABAC_NUM_CTX : nullptr;
 }
 __device__ __forceinline__ void wppPublish(const WppArgs &wpp, size_t sub, int lane) {
+  if (wpp.debug & 2u) return;
   __threadfence();
   __syncwarp();
   if (lane == 0) stRelease(wpp.ready + sub, 1u);
@@ -906,7 +923,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
+    uint32_t st = 0;
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane, st);
     if constexpr (kWs) loadCtxStates(sm.ctx, p, ctxSrc, lane);
     else loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     if constexpr (kWs) {  // the ring is empty here: every substream ends fully drained
@@ -955,7 +973,6 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       enc.out.flushed = 0;
       enc.out.lane = lane;
     }
-    uint32_t st = 0;
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
     uint64_t t = tuOffsets[sub];
@@ -1175,7 +1192,8 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
+    uint32_t st = 0;
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane, st);
     if (kStream)
       loadCtxEntriesFull(sm.ctx, p, ctxSrc, lane);
     else
@@ -1184,7 +1202,6 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
     const uint64_t rc1 = kStream ? rawOffsets[sub + 1] : 0;
     uint32_t *cmdBase = kFused ? nullptr : cmds + cmdOffsets[sub];  // this substream's resolved command words
     uint32_t cmdN = 0;
-    uint32_t st = 0;
     LsCoder coder;
     if constexpr (kFused)
       coder.start(sm.ring, out + outOffsets[sub], uint32_t(outOffsets[sub + 1] - outOffsets[sub]), lane,
@@ -1507,10 +1524,12 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
   size_t sub;
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
-    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane);
+    uint32_t wppStatus = 0;
+    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane, wppStatus);
     loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     LsDecoder dec;  // identical on every lane
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+    dec.status |= wppStatus;
     const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
     bool wppPending = wpp.sync != nullptr;
     const uint64_t tSync = wppPending ? t0 + wpp.sync[sub].sync_tus : 0;
@@ -1916,7 +1935,7 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
   if (e != cudaSuccess) return e;
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
-      sc.wpp.sync ? nullptr : sc.order, sc.cursor, sc.wpp);
+      (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp);
   return cudaGetLastError();
 }
 

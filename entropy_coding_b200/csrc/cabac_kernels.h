@@ -12,6 +12,8 @@ struct WppArgs {
   const cabac_wpp_sync *sync = nullptr;
   cabac_ctx_model *snap = nullptr;
   uint32_t *ready = nullptr;
+  uint32_t spinLimit = 1u << 24;  // polls of >= 100 ns before a wait gives up with CABAC_SS_WPP_TIMEOUT
+  uint32_t debug = 0;             // dev: bit 0 skips the waits, bit 1 the snapshots, bit 2 keeps the LPT order
 };
 
 // Device scratch of the scheduler (owned by the handle): per-substream cost, the

@@ -55,8 +55,10 @@ enum {
                                 bit_stream.cpp:269                           */
   CABAC_SS_COEFF_RANGE = 16, /* "TransCoeffLevel outside allowable range",
                                 cabac_reader.cpp:2942-2946                   */
-  CABAC_SS_NO_TERMINATE = 32 /* terminating bin / stop pattern missing,
+  CABAC_SS_NO_TERMINATE = 32, /* terminating bin / stop pattern missing,
                                 arith_codec.cpp:68-73                        */
+  CABAC_SS_WPP_TIMEOUT = 64  /* cabac_*_wpp: the predecessor never published
+                                its contexts (malformed dep chain)           */
 };
 
 /* ---- probability model as exchanged over the boundary ------------------- */

@@ -74,15 +74,19 @@ class RecordingBinEncoder : public EntropyCoding::BinEncoder_Std {
   }
   void encodeBinsEP(unsigned bins, unsigned numBins) override {
     first();
-    if (!inTu_) rec_.encodeBinsEP(bins, numBins);
-    full_.encodeBinsEP(bins, numBins);
+    if (!nested_) {  // BinEncoderBase::encodeRemAbsEP emits its two words through this virtual (arith_codec.cpp:426-458)
+      if (!inTu_) rec_.encodeBinsEP(bins, numBins);
+      full_.encodeBinsEP(bins, numBins);
+    }
     Base::encodeBinsEP(bins, numBins);
   }
   void encodeRemAbsEP(unsigned bins, unsigned goRicePar, unsigned cutoff, int maxLog2TrDynamicRange) override {
     first();
     if (!inTu_) rec_.encodeRemAbsEP(bins, goRicePar, cutoff, maxLog2TrDynamicRange);
     full_.encodeRemAbsEP(bins, goRicePar, cutoff, maxLog2TrDynamicRange);
+    nested_ = true;
     Base::encodeRemAbsEP(bins, goRicePar, cutoff, maxLog2TrDynamicRange);
+    nested_ = false;
   }
   void encodeBinTrm(unsigned bin) override {
     first();
@@ -208,7 +212,7 @@ class RecordingBinEncoder : public EntropyCoding::BinEncoder_Std {
   std::vector<uint8_t> before_, after_;
   std::vector<uint32_t> ctuMarks_;
   std::vector<uint16_t> ctxIn_;
-  bool haveCtxIn_ = false, skipped_ = false;
+  bool haveCtxIn_ = false, skipped_ = false, nested_ = false;
   int inTu_ = 0;
   uint32_t tools_ = 0;
 };
