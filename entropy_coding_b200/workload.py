@@ -217,3 +217,54 @@ def frames_as_ctu_rows(n_frames: int, width: int, height: int, seed0: int = 1000
         params[f * rows:(f + 1) * rows] = params[f * rows]
     return (Workload(wl.tus, wl.tu_offsets[0::cpr].copy(), params, wl.coeffs,
                      f"{width}x{height}-WPP-{n_frames}f-row-substreams"), rows, first)
+
+
+# ------------------------------------------------------------------------------------------------
+# Batch shaping helpers for bench.py (host-side index arithmetic only)
+# ------------------------------------------------------------------------------------------------
+def merge_substreams(wl: Workload, group: int) -> Workload:
+    """Every `group` consecutive substreams become one (same TUs, same slab): the 135 CTUs of a 1080p
+    frame as ONE slice (BASELINE configs[2] read literally).  The merged substream keeps the
+    parameters of its first member."""
+    assert wl.n_sub % group == 0
+    return Workload(wl.tus, wl.tu_offsets[::group].copy(), wl.params[::group].copy(), wl.coeffs,
+                    wl.name + f"-merged{group}")
+
+
+def tile_descriptors(wl: Workload, tiles: int, cap: np.ndarray):
+    """Descriptor arrays of `tiles` back-to-back copies of a workload (copy k owns coefficient tile k,
+    output slab k): (tus, tu_offsets, params, cap_offsets).  The coefficient slab itself is replicated on
+    the device by the caller."""
+    nco, ntu = int(wl.coeffs.size), len(wl.tus)
+    tus = np.tile(wl.tus, tiles)
+    tus["coeff_offset"] += np.repeat(np.arange(tiles, dtype=np.uint64) * np.uint64(nco), ntu)
+    tu_off = np.concatenate([[0], (np.arange(tiles)[:, None] * ntu +
+                                   wl.tu_offsets[1:].astype(np.int64)[None, :]).ravel()]).astype(np.uint64)
+    cap_t = np.concatenate([[0], (np.arange(tiles)[:, None] * int(cap[-1]) +
+                                  cap[1:].astype(np.int64)[None, :]).ravel()]).astype(np.uint64)
+    return tus, tu_off, np.tile(wl.params, tiles), cap_t
+
+
+def sweep_substreams(n_sub: int, seed: int, tus_per_sub=(64, 256)) -> Workload:
+    """BASELINE configs[4] (decode sweep): independent substreams of 64+ small TUs each (count log-uniform
+    in tus_per_sub, one block shape and one QP preset per substream, luma + chroma mixed), generated one
+    vectorised draw per substream."""
+    rng = np.random.default_rng(seed)
+    shapes = [(4, 4), (8, 8), (8, 4), (4, 8), (16, 16), (16, 8), (8, 16), (4, 16), (16, 4)]
+    weights = np.array([6, 5, 3, 3, 1, 1, 1, 1, 1], np.float64)
+    weights /= weights.sum()
+    names = list(PRESETS)
+    tus, co, offs, cursor = [], [], [0], 0
+    params = np.zeros(n_sub, PARAMS_DT)
+    lo, hi = np.log(tus_per_sub[0]), np.log(tus_per_sub[1] + 1)
+    for i in range(n_sub):
+        scale, decay, qp = PRESETS[names[int(rng.integers(len(names)))]]
+        params[i] = (qp, 2, SUB_DEP_QUANT | SUB_TERMINATE | SUB_ALIGN, 0)
+        n = int(np.exp(rng.uniform(lo, hi)))
+        w, h = shapes[int(rng.choice(len(shapes), p=weights))]
+        comp = int(rng.integers(3))
+        blk = laplace_block(rng, n, w, h, scale * (1.0 if comp == 0 else 0.6), decay)
+        cursor = _emit(tus, co, cursor, blk, int(np.log2(w)), int(np.log2(h)), comp, TU_TS_ALLOWED)
+        offs.append(offs[-1] + n)
+    return Workload(np.concatenate(tus), np.asarray(offs, np.uint64), params, np.concatenate(co),
+                    f"sweep-{n_sub}x{tus_per_sub}-seed{seed}")
