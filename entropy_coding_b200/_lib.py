@@ -58,6 +58,12 @@ _SIGS = {
     "cabac_decode_residual_wpp_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_encode_stream_wpp": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_encode_stream_wpp_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_remove_emulation_prevention": (C.c_int, [_P, _P, _SZ, C.c_int, _P, _P, _P, _P]),
+    "cabac_remove_emulation_prevention_dev": (C.c_int, [_P, _P, _SZ, C.c_int, _P, _P, _P, _P]),
+    "cabac_entry_point_syntax": (C.c_int, [_P, _P, _P, _SZ, _P, _P]),
+    "cabac_entry_point_syntax_dev": (C.c_int, [_P, _P, _P, _SZ, _P, _P]),
+    "cabac_substream_ranges": (C.c_int, [_P, _P, _SZ, _P, _SZ, C.c_uint64, C.c_uint64, _P]),
+    "cabac_substream_ranges_dev": (C.c_int, [_P, _P, _SZ, _P, _SZ, C.c_uint64, C.c_uint64, _P]),
     "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
     "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
 }

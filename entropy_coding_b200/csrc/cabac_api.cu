@@ -1265,6 +1265,132 @@ int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp, size
   return CABAC_OK;
 }
 
+// ---- decode side of substream assembly ----
+static int ensureEpbScratch(cabac_handle *h, size_t n) {
+  const size_t tiles = cabac::emulationTiles(n);
+  if (tiles > h->epbTiles) {
+    if (h->epbScratch) cudaFree(h->epbScratch);
+    h->epbScratch = nullptr;
+    h->epbTiles = 0;
+    const size_t cap = tiles + (tiles >> 2) + 256;
+    CK(cudaMalloc(&h->epbScratch, cap * 4 + (cap + 1) * 8 + 16), "emulation scratch");
+    h->epbTiles = cap;
+  }
+  return CABAC_OK;
+}
+
+int cabac_remove_emulation_prevention_dev(cabac_handle *h, const uint8_t *nal, size_t n, int strip_trailing_zeros,
+                                          uint8_t *rbsp, uint64_t *sizes, uint32_t *epb_locations,
+                                          uint32_t *violations) {
+  if (!h || !sizes || !violations || (n && (!nal || !rbsp))) return badArg(h, "cabac_remove_emulation_prevention_dev");
+  DeviceGuard g(h->device);
+  if (int rc = ensureEpbScratch(h, n)) return rc;
+  uint64_t *tileBase = static_cast<uint64_t *>(h->epbScratch);
+  uint32_t *tileCounts = reinterpret_cast<uint32_t *>(tileBase + h->epbTiles + 1);
+  CK(cabac::launchEmulationRemove(h->stream, nal, n, strip_trailing_zeros, tileCounts, tileBase, rbsp, epb_locations,
+                                  sizes, violations),
+     "emulation removal kernels");
+  h->launches += n ? 3 : 0;
+  return CABAC_OK;
+}
+
+int cabac_remove_emulation_prevention(cabac_handle *h, const uint8_t *nal, size_t n, int strip_trailing_zeros,
+                                      uint8_t *rbsp, uint64_t *sizes, uint32_t *epb_locations, uint32_t *violations) {
+  if (!h || !sizes || (n && (!nal || !rbsp))) return badArg(h, "cabac_remove_emulation_prevention");
+  DeviceGuard g(h->device);
+  uint8_t *dIn, *dOut;
+  uint64_t *dSizes;
+  uint32_t *dEpb, *dViol;
+  Arena a(h);
+  a.want((void **)&dIn, n);
+  a.want((void **)&dOut, n);
+  a.want((void **)&dSizes, 16);
+  a.want((void **)&dViol, 4);
+  a.want((void **)&dEpb, (n / 3 + 1) * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dIn, nal, n);
+  int rc = cabac_remove_emulation_prevention_dev(h, dIn, n, strip_trailing_zeros, dOut, dSizes, dEpb, dViol);
+  if (rc) return rc;
+  uint32_t viol = 0;
+  D2H(sizes, dSizes, 16);
+  D2H(&viol, dViol, 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  if (violations) *violations = viol;
+  D2H(rbsp, dOut, size_t(sizes[0]));
+  D2H(epb_locations, dEpb, size_t(sizes[1]) * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  if (viol) return badArg(h, "cabac_remove_emulation_prevention: malformed NAL payload (NALread.cpp:66, 79, 84)");
+  return CABAC_OK;
+}
+
+int cabac_entry_point_syntax_dev(cabac_handle *h, const uint32_t *sizes, const uint32_t *emulations, size_t n_sub,
+                                 uint32_t *offset_minus1, uint32_t *offset_len_minus1) {
+  if (!h || !offset_len_minus1 || (n_sub && !sizes) || (n_sub > 1 && !offset_minus1))
+    return badArg(h, "cabac_entry_point_syntax_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchEntryPointSyntax(h->stream, sizes, emulations, n_sub, offset_minus1, offset_len_minus1),
+     "entry_point_syntax_kernel");
+  h->launches += 1;
+  return CABAC_OK;
+}
+
+int cabac_entry_point_syntax(cabac_handle *h, const uint32_t *sizes, const uint32_t *emulations, size_t n_sub,
+                             uint32_t *offset_minus1, uint32_t *offset_len_minus1) {
+  if (!h || !offset_len_minus1 || (n_sub && !sizes) || (n_sub > 1 && !offset_minus1))
+    return badArg(h, "cabac_entry_point_syntax");
+  DeviceGuard g(h->device);
+  uint32_t *dS, *dE, *dO, *dL;
+  Arena a(h);
+  a.want((void **)&dS, n_sub * 4);
+  a.want((void **)&dE, emulations ? n_sub * 4 : 0);
+  a.want((void **)&dO, n_sub * 4);
+  a.want((void **)&dL, 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dS, sizes, n_sub * 4);
+  H2D(dE, emulations, n_sub * 4);
+  int rc = cabac_entry_point_syntax_dev(h, dS, emulations ? dE : nullptr, n_sub, dO, dL);
+  if (rc) return rc;
+  if (n_sub > 1) D2H(offset_minus1, dO, (n_sub - 1) * 4);
+  D2H(offset_len_minus1, dL, 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
+int cabac_substream_ranges_dev(cabac_handle *h, const uint32_t *offset_minus1, size_t n_entry,
+                               const uint32_t *epb_locations, size_t n_epb, uint64_t slice_data_pos,
+                               uint64_t rbsp_size, uint64_t *in_offsets) {
+  if (!h || !in_offsets || (n_entry && !offset_minus1) || (n_epb && !epb_locations))
+    return badArg(h, "cabac_substream_ranges_dev");
+  DeviceGuard g(h->device);
+  CK(cabac::launchSubstreamRanges(h->stream, offset_minus1, n_entry, epb_locations, n_epb, slice_data_pos, rbsp_size,
+                                  in_offsets),
+     "substream_ranges_kernel");
+  h->launches += 1;
+  return CABAC_OK;
+}
+
+int cabac_substream_ranges(cabac_handle *h, const uint32_t *offset_minus1, size_t n_entry,
+                           const uint32_t *epb_locations, size_t n_epb, uint64_t slice_data_pos, uint64_t rbsp_size,
+                           uint64_t *in_offsets) {
+  if (!h || !in_offsets || (n_entry && !offset_minus1) || (n_epb && !epb_locations))
+    return badArg(h, "cabac_substream_ranges");
+  DeviceGuard g(h->device);
+  uint32_t *dO, *dE;
+  uint64_t *dR;
+  Arena a(h);
+  a.want((void **)&dO, n_entry * 4);
+  a.want((void **)&dE, n_epb * 4);
+  a.want((void **)&dR, (n_entry + 2) * 8);
+  CK(a.commit(), "scratch alloc");
+  H2D(dO, offset_minus1, n_entry * 4);
+  H2D(dE, epb_locations, n_epb * 4);
+  int rc = cabac_substream_ranges_dev(h, dO, n_entry, dE, n_epb, slice_data_pos, rbsp_size, dR);
+  if (rc) return rc;
+  D2H(in_offsets, dR, (n_entry + 2) * 8);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return CABAC_OK;
+}
+
 // ---- WPP entry points: the plain calls with the sync records attached to the launch ----
 int cabac_encode_residual_wpp_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
                                   const cabac_substream_params *params, const cabac_wpp_sync *wpp, size_t n_sub,

@@ -2102,6 +2102,186 @@ cudaError_t launchEmulationInsert(cudaStream_t s, const uint8_t *data, size_t n,
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------
+// K8: the decode side of substream assembly.
+//   remove : convertPayloadToRBSP (VTM Lib/DecoderLib/NALread.cpp:59-106): drop every
+//            emulation_prevention_three_byte, record its position in the escaped buffer.  In a payload
+//            the CHECKs of that function accept, a byte is an EPB iff it is 0x03 and follows two zero
+//            bytes (the zero count restarts after an EPB, and a third zero / a 01 / a 02 after two zeros
+//            is one of the refused cases), so the decision is local; refused patterns are counted.
+//   syntax : sh_entry_offset_len_minus1 / sh_entry_point_offset_minus1 (VLCWriter.cpp:2833-2866) from the
+//            substream sizes + emulation counts (EncSlice.cpp:2118-2125)
+//   ranges : the substreams' RBSP byte ranges from the signalled offsets and the EPB locations
+//            (VLCReader.cpp:4346-4381, DecSlice.cpp:106-114, bit_stream.cpp:382-415)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool isEpb(const uint8_t *__restrict__ d, uint64_t i) {
+  return i >= 2 && d[i] == 3 && d[i - 1] == 0 && d[i - 2] == 0;
+}
+__device__ __forceinline__ bool epbViolation(const uint8_t *__restrict__ d, uint64_t n, uint64_t i) {
+  if (i >= 2 && d[i] < 3 && d[i - 1] == 0 && d[i - 2] == 0) return true;  // 00 00 00 / 01 / 02
+  if (isEpb(d, i) && i + 1 < n && d[i + 1] > 3) return true;              // "Read a value bigger than '3'"
+  return i + 1 == n && d[i] == 0;                                          // "Zero count not '0'"
+}
+
+__global__ void __launch_bounds__(256) epb_remove_count_kernel(const uint8_t *__restrict__ data, uint64_t n,
+                                                               uint32_t *__restrict__ tileCounts,
+                                                               uint32_t *__restrict__ violations) {
+  const uint64_t base = uint64_t(blockIdx.x) * EPB_TILE + uint64_t(threadIdx.x) * EPB_PER_THREAD;
+  uint32_t c = 0, v = 0;
+  for (int k = 0; k < EPB_PER_THREAD; k++)
+    if (base + k < n) {
+      c += isEpb(data, base + k) ? 1u : 0u;
+      v += epbViolation(data, n, base + k) ? 1u : 0u;
+    }
+  __shared__ uint32_t ws[8];
+  c = __reduce_add_sync(FULL, c);
+  v = __reduce_add_sync(FULL, v);
+  if ((threadIdx.x & 31) == 0) {
+    ws[threadIdx.x >> 5] = c;
+    if (v) atomicAdd(violations, v);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; w++) t += ws[w];
+    tileCounts[blockIdx.x] = t;
+  }
+}
+
+// tileBase = exclusive scan of the tile counts ([tiles] = total).  sizes[0] = RBSP length, sizes[1] = #EPB.
+__global__ void __launch_bounds__(256) epb_remove_kernel(const uint8_t *__restrict__ data, uint64_t n,
+                                                         const uint64_t *__restrict__ tileBase, uint64_t tiles,
+                                                         int stripTrailingZeros, uint8_t *__restrict__ out,
+                                                         uint32_t *__restrict__ epbLocations,
+                                                         uint64_t *__restrict__ sizes) {
+  const uint64_t base = uint64_t(blockIdx.x) * EPB_TILE + uint64_t(threadIdx.x) * EPB_PER_THREAD;
+  uint32_t mask = 0;
+  for (int k = 0; k < EPB_PER_THREAD; k++)
+    if (base + k < n && isEpb(data, base + k)) mask |= 1u << k;
+  const uint32_t c = __popc(mask);
+  __shared__ uint32_t ws[8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(FULL, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) ws[w] = inc;
+  __syncthreads();
+  uint64_t before = tileBase[blockIdx.x] + (inc - c);
+  for (int k = 0; k < w; k++) before += ws[k];
+  for (int k = 0; k < EPB_PER_THREAD && base + k < n; k++) {
+    if ((mask >> k) & 1u) {
+      if (epbLocations) epbLocations[before] = uint32_t(base + k);
+      before++;
+    } else {
+      out[base + k - before] = data[base + k];
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    uint64_t len = n - tileBase[tiles];
+    if (stripTrailingZeros) {  // cabac_zero_words at the end of a VCL NAL unit, NALread.cpp:92-103
+      uint64_t i = n;          // walk back over trailing zero bytes of the ESCAPED buffer (EPBs are not zero,
+      while (len > 0) {        // so map the last RBSP byte back: skip EPBs from the end)
+        while (i > 0 && isEpb(data, i - 1)) i--;
+        if (i == 0 || data[i - 1] != 0) break;
+        i--;
+        len--;
+      }
+    }
+    sizes[0] = len;
+    sizes[1] = tileBase[tiles];
+  }
+}
+
+cudaError_t launchEmulationRemove(cudaStream_t s, const uint8_t *data, size_t n, int stripTrailingZeros,
+                                  uint32_t *tileCounts, uint64_t *tileBase, uint8_t *out, uint32_t *epbLocations,
+                                  uint64_t *sizes, uint32_t *violations) {
+  cudaError_t e = cudaMemsetAsync(violations, 0, sizeof(uint32_t), s);
+  if (e != cudaSuccess) return e;
+  if (n == 0) return cudaMemsetAsync(sizes, 0, 2 * sizeof(uint64_t), s);
+  const size_t tiles = emulationTiles(n);
+  epb_remove_count_kernel<<<unsigned(tiles), 256, 0, s>>>(data, n, tileCounts, violations);
+  entry_points_kernel<<<1, 1024, 0, s>>>(tileCounts, nullptr, tiles, tileBase);
+  epb_remove_kernel<<<unsigned(tiles), 256, 0, s>>>(data, n, tileBase, tiles, stripTrailingZeros, out, epbLocations, sizes);
+  return cudaGetLastError();
+}
+
+// one CTA: offsets[i] = sizes[i] + emulations[i] - 1 (i < n - 1), *lenMinus1 = bits of the largest size - 1
+__global__ void __launch_bounds__(256) entry_point_syntax_kernel(const uint32_t *__restrict__ sizes,
+                                                                 const uint32_t *__restrict__ emulations, size_t n,
+                                                                 uint32_t *__restrict__ offsetMinus1,
+                                                                 uint32_t *__restrict__ lenMinus1) {
+  __shared__ uint32_t sMax;
+  if (threadIdx.x == 0) sMax = 0;
+  __syncthreads();
+  uint32_t m = 0;
+  for (size_t i = threadIdx.x; i + 1 < n; i += blockDim.x) {
+    const uint32_t v = sizes[i] + (emulations ? emulations[i] : 0u);
+    offsetMinus1[i] = v - 1u;
+    m = max(m, v);
+  }
+  m = __reduce_max_sync(FULL, m);
+  if ((threadIdx.x & 31) == 0) atomicMax(&sMax, m);
+  __syncthreads();
+  if (threadIdx.x == 0) *lenMinus1 = sMax < 2u ? 0u : uint32_t(31 - __clz(sMax));  // smallest len with max < 2^(len+1)
+}
+
+// one CTA: the loops of parseSliceHeader as lower-bound searches in the (ascending) EPB locations
+__global__ void __launch_bounds__(256) substream_ranges_kernel(const uint32_t *__restrict__ offsetMinus1, size_t nEntry,
+                                                               const uint32_t *__restrict__ epb, size_t nEpb,
+                                                               uint64_t hdrEnd, uint64_t rbspSize,
+                                                               uint64_t *__restrict__ inOffsets) {
+  __shared__ uint64_t sHdrEsc;
+  __shared__ uint64_t part[256];
+  auto lowerBound = [&](uint64_t v) {  // EPBs with location < v
+    size_t lo = 0, hi = nEpb;
+    while (lo < hi) {
+      const size_t mid = (lo + hi) >> 1;
+      if (uint64_t(epb[mid]) < v) lo = mid + 1; else hi = mid;
+    }
+    return uint64_t(lo);
+  };
+  if (threadIdx.x == 0) {  // endOfSliceHeaderLocation in escaped coordinates, VLCReader.cpp:4350-4360
+    uint64_t h = hdrEnd;
+    for (size_t k = 0; k < nEpb; k++)
+      if (uint64_t(epb[k]) < h) h++;
+    sHdrEsc = h;
+  }
+  __syncthreads();
+  // sequential over entries per thread block-chunk: prefix sums of the signalled and the RBSP sizes
+  const size_t per = (nEntry + blockDim.x - 1) / blockDim.x;
+  const size_t a = min(nEntry, threadIdx.x * per), b = min(nEntry, a + per);
+  uint64_t sumSig = 0;
+  for (size_t i = a; i < b; i++) sumSig += uint64_t(offsetMinus1[i]) + 1u;
+  part[threadIdx.x] = sumSig;
+  __syncthreads();
+  uint64_t cur = 0;
+  for (int t = 0; t < int(threadIdx.x); t++) cur += part[t];
+  // RBSP position of entry i's start = hdrEnd + signalled bytes before it - EPBs inside [hdr, its start)
+  for (size_t i = a; i < b; i++) {
+    cur += uint64_t(offsetMinus1[i]) + 1u;
+    const uint64_t removed = lowerBound(cur + sHdrEsc) - lowerBound(sHdrEsc);
+    inOffsets[i + 1] = hdrEnd + cur - removed;
+  }
+  if (threadIdx.x == 0) {
+    inOffsets[0] = hdrEnd;
+    inOffsets[nEntry + 1] = rbspSize;
+  }
+}
+
+cudaError_t launchEntryPointSyntax(cudaStream_t s, const uint32_t *sizes, const uint32_t *emulations, size_t n,
+                                   uint32_t *offsetMinus1, uint32_t *lenMinus1) {
+  entry_point_syntax_kernel<<<1, 256, 0, s>>>(sizes, emulations, n, offsetMinus1, lenMinus1);
+  return cudaGetLastError();
+}
+cudaError_t launchSubstreamRanges(cudaStream_t s, const uint32_t *offsetMinus1, size_t nEntry, const uint32_t *epb,
+                                  size_t nEpb, uint64_t hdrEnd, uint64_t rbspSize, uint64_t *inOffsets) {
+  substream_ranges_kernel<<<1, 256, 0, s>>>(offsetMinus1, nEntry, epb, nEpb, hdrEnd, rbspSize, inOffsets);
+  return cudaGetLastError();
+}
+
 cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
                        const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints) {
   entry_points_kernel<<<1, 1024, 0, s>>>(outSizes, outOffsets, nSub, entryPoints);

@@ -81,6 +81,13 @@ cudaError_t launchEmulationCount(cudaStream_t s, const uint8_t *data, const uint
 size_t emulationTiles(size_t n);
 cudaError_t launchEmulationInsert(cudaStream_t s, const uint8_t *data, size_t n, uint32_t *tileCounts,
                                   uint64_t *tileBase, uint8_t *out, size_t outCap, uint64_t *outSize);
+cudaError_t launchEmulationRemove(cudaStream_t s, const uint8_t *data, size_t n, int stripTrailingZeros,
+                                  uint32_t *tileCounts, uint64_t *tileBase, uint8_t *out, uint32_t *epbLocations,
+                                  uint64_t *sizes, uint32_t *violations);
+cudaError_t launchEntryPointSyntax(cudaStream_t s, const uint32_t *sizes, const uint32_t *emulations, size_t n,
+                                   uint32_t *offsetMinus1, uint32_t *lenMinus1);
+cudaError_t launchSubstreamRanges(cudaStream_t s, const uint32_t *offsetMinus1, size_t nEntry, const uint32_t *epb,
+                                  size_t nEpb, uint64_t hdrEnd, uint64_t rbspSize, uint64_t *inOffsets);
 cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uint64_t *outOffsets,
                        const uint32_t *outSizes, size_t nSub, uint8_t *packed, uint64_t *entryPoints);
 

@@ -366,6 +366,38 @@ class CabacEngine:
                                                                _hp(size)))
         return out[:int(size[0])]
 
+    def remove_emulation_prevention(self, nal, vcl=False, raise_on_violation=True):
+        """NAL unit bytes -> dict(rbsp, epb_locations, violations) (VTM NALread.cpp:59-106)."""
+        nal = _np(nal, np.uint8)
+        rbsp = np.zeros(max(nal.size, 1), np.uint8)
+        sizes = np.zeros(2, np.uint64)
+        epb = np.zeros(nal.size // 3 + 1, np.uint32)
+        viol = np.zeros(1, np.uint32)
+        rc = self.lib.cabac_remove_emulation_prevention(self.h, _hp(nal), nal.size, int(vcl), _hp(rbsp), _hp(sizes),
+                                                        _hp(epb), _hp(viol))
+        if rc != OK and (raise_on_violation or not int(viol[0])):
+            self._check(rc)
+        return dict(rbsp=rbsp[:int(sizes[0])], epb_locations=epb[:int(sizes[1])], violations=int(viol[0]))
+
+    def entry_point_syntax(self, sizes, emulations=None):
+        """(sh_entry_offset_len_minus1, sh_entry_point_offset_minus1[n_sub - 1]) (VLCWriter.cpp:2833-2866)."""
+        sizes = _np(sizes, np.uint32)
+        emulations = _np(emulations, np.uint32)
+        off = np.zeros(max(len(sizes) - 1, 1), np.uint32)
+        ln = np.zeros(1, np.uint32)
+        self._check(self.lib.cabac_entry_point_syntax(self.h, _hp(sizes), _hp(emulations), len(sizes), _hp(off), _hp(ln)))
+        return int(ln[0]), off[:max(len(sizes) - 1, 0)]
+
+    def substream_ranges(self, offset_minus1, epb_locations, slice_data_pos, rbsp_size):
+        """RBSP byte ranges of a slice's substreams from the signalled entry points (VLCReader.cpp:4346-4381)."""
+        off = _np(offset_minus1, np.uint32)
+        epb = _np(epb_locations, np.uint32)
+        out = np.zeros(len(off) + 2, np.uint64)
+        self._check(self.lib.cabac_substream_ranges(self.h, _hp(off) if len(off) else None, len(off),
+                                                    _hp(epb) if len(epb) else None, len(epb), int(slice_data_pos),
+                                                    int(rbsp_size), _hp(out)))
+        return out
+
     def pack(self, out, out_offsets, sizes):
         out, out_offsets, sizes = _np(out, np.uint8), _np(out_offsets, np.uint64), _np(sizes, np.uint32)
         n = len(sizes)

@@ -548,6 +548,55 @@ int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp,
                                       size_t n, uint8_t *out, size_t out_cap,
                                       uint64_t *out_size);
 
+/* ---- the decode side of substream assembly -------------------------------- */
+/* NAL unit bytes -> RBSP: convertPayloadToRBSP, VTM Lib/DecoderLib/NALread.cpp:59-106.
+ * Every emulation_prevention_three_byte (a 0x03 after two zero bytes) is dropped and
+ * its position in the ESCAPED buffer recorded (InputBitstream::
+ * pushEmulationPreventionByteLocation) - the slice-header parser needs the positions
+ * to turn signalled entry points into RBSP ranges.
+ *   strip_trailing_zeros  VCL NAL units: drop trailing cabac_zero_words (NALread.cpp:92-103)
+ *   rbsp                  n bytes of room
+ *   sizes[2]              [0] RBSP length, [1] number of EPBs
+ *   epb_locations         nullable; n / 3 + 1 entries of room, ascending
+ *   violations            number of positions where VTM's CHECKs throw (00 00 0x with
+ *                         x < 3, a byte > 3 after an EPB, a trailing zero byte); the
+ *                         host flavour returns CABAC_ERR_ARG when it is non-zero       */
+int cabac_remove_emulation_prevention_dev(cabac_handle *h, const uint8_t *nal, size_t n,
+                                          int strip_trailing_zeros, uint8_t *rbsp,
+                                          uint64_t *sizes, uint32_t *epb_locations,
+                                          uint32_t *violations);
+int cabac_remove_emulation_prevention(cabac_handle *h, const uint8_t *nal, size_t n,
+                                      int strip_trailing_zeros, uint8_t *rbsp,
+                                      uint64_t *sizes, uint32_t *epb_locations,
+                                      uint32_t *violations);
+/* Slice-header form of the entry points.  offset_minus1[i] (i < n_sub - 1) =
+ * sh_entry_point_offset_minus1 = sizes[i] + emulations[i] - 1 (EncSlice.cpp:2118-2125:
+ * the signalled size counts the substream's emulation prevention bytes; emulations from
+ * cabac_count_emulations, nullable = none); *offset_len_minus1 =
+ * sh_entry_offset_len_minus1 (HLSWriter::codeTilesWPPEntryPoint, VLCWriter.cpp:2833-2866). */
+int cabac_entry_point_syntax_dev(cabac_handle *h, const uint32_t *sizes,
+                                 const uint32_t *emulations, size_t n_sub,
+                                 uint32_t *offset_minus1, uint32_t *offset_len_minus1);
+int cabac_entry_point_syntax(cabac_handle *h, const uint32_t *sizes,
+                             const uint32_t *emulations, size_t n_sub,
+                             uint32_t *offset_minus1, uint32_t *offset_len_minus1);
+/* The inverse on the decoder: RBSP byte ranges of the n_entry + 1 substreams of a
+ * slice from the signalled offsets and the EPB locations (HLSyntaxReader::
+ * parseSliceHeader, VLCReader.cpp:4346-4381: each signalled size minus the EPBs inside
+ * it; DecSlice.cpp:106-114 + InputBitstream::extractSubstream, bit_stream.cpp:382-415:
+ * consecutive ranges, the last substream takes the rest).
+ *   slice_data_pos  RBSP byte position of the first slice-data byte
+ *   in_offsets      n_entry + 2 entries: substream i is rbsp[in_offsets[i] ..
+ *                   in_offsets[i + 1]) - the in / in_offsets arguments of cabac_decode_*   */
+int cabac_substream_ranges_dev(cabac_handle *h, const uint32_t *offset_minus1,
+                               size_t n_entry, const uint32_t *epb_locations,
+                               size_t n_epb, uint64_t slice_data_pos,
+                               uint64_t rbsp_size, uint64_t *in_offsets);
+int cabac_substream_ranges(cabac_handle *h, const uint32_t *offset_minus1,
+                           size_t n_entry, const uint32_t *epb_locations, size_t n_epb,
+                           uint64_t slice_data_pos, uint64_t rbsp_size,
+                           uint64_t *in_offsets);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1667,3 +1667,71 @@ long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out) {
   if (zeroCount > 0) out[o++] = 3;
   return o;
 }
+
+/* convertPayloadToRBSP, VVCSoftware_VTM/source/Lib/DecoderLib/NALread.cpp:59-106: NAL unit bytes -> RBSP.
+ * An emulation_prevention_three_byte is a 0x03 that follows two zero bytes of the output; its position
+ * in the ESCAPED buffer is recorded (pushEmulationPreventionByteLocation).  vcl: trailing zero bytes
+ * (cabac_zero_words) are dropped.  Returns the RBSP length, or -1 where VTM's CHECKs throw. */
+long orc_remove_emulation_prevention(const uint8_t *nal, long n, int vcl, uint8_t *rbsp, uint32_t *epb,
+                                     long *n_epb) {
+  long w = 0, k = 0;
+  unsigned zeroCount = 0;
+  for (long r = 0; r < n; r++) {
+    if (zeroCount >= 2 && nal[r] < 3) return -1; /* "Zero count is '2' and read value is small than '3'" */
+    if (zeroCount == 2 && nal[r] == 3) {
+      if (epb) epb[k] = (uint32_t)r;
+      k++;
+      r++;
+      zeroCount = 0;
+      if (r == n) break;
+      if (nal[r] > 3) return -1; /* "Read a value bigger than '3'" */
+    }
+    zeroCount = nal[r] == 0 ? zeroCount + 1 : 0;
+    rbsp[w++] = nal[r];
+  }
+  if (zeroCount != 0) return -1; /* "Zero count not '0'" */
+  if (vcl)
+    while (w > 0 && rbsp[w - 1] == 0) w--;
+  if (n_epb) *n_epb = k;
+  return w;
+}
+
+/* Slice-header form of the entry points.  EncSlice.cpp:2118-2125: the signalled size of substream i
+ * (all but the last) is its byte count plus its start-code emulations; HLSWriter::codeTilesWPPEntryPoint,
+ * VLCWriter.cpp:2833-2866: sh_entry_offset_len_minus1 is the smallest length that holds the largest
+ * size, each sh_entry_point_offset_minus1 is size - 1.  Returns sh_entry_offset_len_minus1. */
+int orc_entry_point_syntax(const uint32_t *sizes, const uint32_t *emulations, long n_sub, uint32_t *offset_minus1) {
+  uint32_t maxOffset = 0;
+  for (long i = 0; i + 1 < n_sub; i++) {
+    const uint32_t s = sizes[i] + emulations[i];
+    if (s > maxOffset) maxOffset = s;
+    offset_minus1[i] = s - 1;
+  }
+  int len = 0;
+  while (maxOffset >= (1u << (len + 1))) len++;
+  return len;
+}
+
+/* Decoder side: HLSyntaxReader::parseSliceHeader, VLCReader.cpp:4346-4381 (the signalled sizes minus the
+ * emulation prevention bytes inside each substream) and DecSlice.cpp:106-114 + InputBitstream::
+ * extractSubstream, bit_stream.cpp:382-415 (consecutive byte ranges, the last substream takes the rest).
+ * hdr_end: RBSP byte position of the first slice-data byte; epb: locations in the escaped buffer.
+ * in_offsets[n_entry + 2]: RBSP byte range of every substream. */
+void orc_substream_ranges(const uint32_t *offset_minus1, long n_entry, const uint32_t *epb, long n_epb,
+                          uint64_t hdr_end, uint64_t rbsp_size, uint64_t *in_offsets) {
+  uint64_t endOfSliceHeaderLocation = hdr_end;
+  for (long k = 0; k < n_epb; k++)
+    if (epb[k] < endOfSliceHeaderLocation) endOfSliceHeaderLocation++;
+  uint64_t cur = 0, prev = 0, pos = hdr_end;
+  in_offsets[0] = pos;
+  for (long i = 0; i < n_entry; i++) {
+    cur += (uint64_t)offset_minus1[i] + 1;
+    uint64_t cnt = 0;
+    for (long k = 0; k < n_epb; k++)
+      if (epb[k] >= prev + endOfSliceHeaderLocation && epb[k] < cur + endOfSliceHeaderLocation) cnt++;
+    pos += (uint64_t)offset_minus1[i] + 1 - cnt;
+    in_offsets[i + 1] = pos;
+    prev = cur;
+  }
+  in_offsets[n_entry + 1] = rbsp_size;
+}

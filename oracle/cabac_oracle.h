@@ -49,4 +49,8 @@ long orc_residual_ctx_bins(const cabac_tu_desc *tus, long ntu, const cabac_subst
 int orc_ctx_init_id(int qp, const cabac_ctx_model *ctxRef, const uint32_t *ctxBins, uint64_t *costs);
 long orc_count_emulations(const uint8_t *d, long n);
 long orc_insert_emulation_prevention(const uint8_t *in, long n, uint8_t *out);
+long orc_remove_emulation_prevention(const uint8_t *nal, long n, int vcl, uint8_t *rbsp, uint32_t *epb, long *n_epb);
+int orc_entry_point_syntax(const uint32_t *sizes, const uint32_t *emulations, long n_sub, uint32_t *offset_minus1);
+void orc_substream_ranges(const uint32_t *offset_minus1, long n_entry, const uint32_t *epb, long n_epb,
+                          uint64_t hdr_end, uint64_t rbsp_size, uint64_t *in_offsets);
 #endif

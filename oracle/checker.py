@@ -75,6 +75,35 @@ def available(kind: str) -> bool:
     return os.path.exists(lib_path(kind))
 
 
+class NalRef:
+    """VTM's own NALwrite.cpp / NALread.cpp (oracle/_ref/libnal_ref.so, built by `make -C oracle nalref`)."""
+    PATH = os.path.join(HERE, "_ref", "libnal_ref.so")
+
+    @classmethod
+    def available(cls) -> bool:
+        return os.path.exists(cls.PATH)
+
+    def __init__(self):
+        self.lib = C.CDLL(self.PATH)
+        self.lib.nalref_insert.restype = C.c_long
+        self.lib.nalref_remove.restype = C.c_long
+
+    def insert(self, rbsp) -> np.ndarray:
+        rbsp = np.ascontiguousarray(rbsp, np.uint8)
+        out = np.zeros(2 * rbsp.size + 2, np.uint8)
+        n = self.lib.nalref_insert(_ptr(rbsp), C.c_long(rbsp.size), _ptr(out))
+        return out[:n].copy()
+
+    def remove(self, nal):
+        """NAL unit incl. its 2 header bytes -> (rbsp incl. header, epb_locations) or None when VTM throws."""
+        nal = np.ascontiguousarray(nal, np.uint8)
+        rbsp = np.zeros(nal.size + 1, np.uint8)
+        epb = np.zeros(nal.size // 3 + 2, np.uint32)
+        k = C.c_long(0)
+        n = self.lib.nalref_remove(_ptr(nal), C.c_long(nal.size), _ptr(rbsp), _ptr(epb), C.byref(k))
+        return None if n < 0 else (rbsp[:n].copy(), epb[:k.value].copy())
+
+
 class Checker:
     def __init__(self, kind: str = "oracle"):
         assert kind in ("ref", "oracle")
@@ -136,6 +165,34 @@ class Checker:
         f = self.lib.orc_insert_emulation_prevention
         f.restype = C.c_long
         return out[:int(f(_ptr(data), C.c_long(data.size), _ptr(out)))].copy()
+
+    def remove_emulation_prevention(self, nal, vcl=False):
+        """Oracle only: (rbsp, epb_locations) or None where VTM's CHECKs would throw (NALread.cpp:59-106)."""
+        nal = np.ascontiguousarray(nal, np.uint8)
+        rbsp = np.zeros(nal.size + 1, np.uint8)
+        epb = np.zeros(nal.size // 3 + 2, np.uint32)
+        k = C.c_long(0)
+        f = self.lib.orc_remove_emulation_prevention
+        f.restype = C.c_long
+        n = int(f(_ptr(nal), C.c_long(nal.size), C.c_int(int(vcl)), _ptr(rbsp), _ptr(epb), C.byref(k)))
+        return None if n < 0 else (rbsp[:n].copy(), epb[:k.value].copy())
+
+    def entry_point_syntax(self, sizes, emulations):
+        """Oracle only: (sh_entry_offset_len_minus1, sh_entry_point_offset_minus1[n_sub - 1])."""
+        sizes = np.ascontiguousarray(sizes, np.uint32)
+        emulations = np.ascontiguousarray(emulations, np.uint32)
+        out = np.zeros(max(len(sizes) - 1, 0), np.uint32)
+        ln = self.lib.orc_entry_point_syntax(_ptr(sizes), _ptr(emulations), C.c_long(len(sizes)), _ptr(out))
+        return int(ln), out
+
+    def substream_ranges(self, offset_minus1, epb, hdr_end, rbsp_size):
+        """Oracle only: RBSP byte ranges of the substreams of a slice (in_offsets[n_entry + 2])."""
+        off = np.ascontiguousarray(offset_minus1, np.uint32)
+        epb = np.ascontiguousarray(epb, np.uint32)
+        out = np.zeros(len(off) + 2, np.uint64)
+        self.lib.orc_substream_ranges(_ptr(off), C.c_long(len(off)), _ptr(epb), C.c_long(len(epb)),
+                                      C.c_uint64(int(hdr_end)), C.c_uint64(int(rbsp_size)), _ptr(out))
+        return out
 
     # ---- bin level --------------------------------------------------------
     def encode_bins(self, cmds, qp, init_id, flags=SUB_TERMINATE | SUB_ALIGN, ctx_in=None,
