@@ -55,6 +55,17 @@ struct cabac_handle {
   size_t wppSubs = 0;
   cabac_wpp_sync *wppDev = nullptr;
   size_t wppDevSubs = 0;
+  // cabac_pin_descriptors: device copies of a batch description the caller promised not to change
+  const void *pinTus = nullptr, *pinTuOff = nullptr, *pinParams = nullptr;
+  size_t pinSubs = 0, pinTuCount = 0;
+  void *pinDev = nullptr;  // [tus | tu_offsets | params], grow-only
+  size_t pinDevBytes = 0;
+  cabac_tu_desc *pinDevTus = nullptr;
+  uint64_t *pinDevTuOff = nullptr;
+  cabac_substream_params *pinDevParams = nullptr;
+  bool pinned(const void *t, const void *o, const void *p, size_t n) const {
+    return pinDev && pinTuOff && t == pinTus && o == pinTuOff && p == pinParams && n == pinSubs;
+  }
 };
 
 namespace {
@@ -135,7 +146,8 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     const cabac_wpp_sync *sync = h->wppNext;
     h->wppNext = nullptr;
     if (n > h->wppSubs) {
-      if (h->wppScratch) cudaFree(h->wppScratch);
+      if (h->pinDev) cudaFree(h->pinDev);
+  if (h->wppScratch) cudaFree(h->wppScratch);
       h->wppScratch = nullptr;
       h->wppSubs = 0;
       const size_t cap2 = n + (n >> 2) + 64;
@@ -345,6 +357,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
   if (h->epbScratch) cudaFree(h->epbScratch);
+  if (h->pinDev) cudaFree(h->pinDev);
   if (h->wppScratch) cudaFree(h->wppScratch);
   if (h->wppDev) cudaFree(h->wppDev);
   for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
@@ -630,6 +643,45 @@ int cabac_insert_emulation_prevention_dev(cabac_handle *h, const uint8_t *rbsp, 
     if ((bytes) && (dst))                                                                          \
       CK(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, h->stream), "D2H copy");   \
   } while (0)
+
+int cabac_unpin_descriptors(cabac_handle *h) {
+  if (!h) return CABAC_ERR_ARG;
+  h->pinTus = h->pinTuOff = h->pinParams = nullptr;  // the device buffer stays for the next pin (grow-only)
+  h->pinSubs = h->pinTuCount = 0;
+  return CABAC_OK;
+}
+
+int cabac_pin_descriptors(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                          const cabac_substream_params *params, size_t n_sub) {
+  if (!h || !tu_offsets || !params || !n_sub) return badArg(h, "cabac_pin_descriptors");
+  cabac_unpin_descriptors(h);
+  DeviceGuard g(h->device);
+  const size_t nTu = tu_offsets[n_sub];
+  if (nTu && !tus) return badArg(h, "cabac_pin_descriptors: tus");
+  const size_t bTus = (nTu * sizeof(cabac_tu_desc) + 255) & ~size_t(255), bOff = ((n_sub + 1) * 8 + 255) & ~size_t(255);
+  const size_t need = bTus + bOff + n_sub * sizeof(cabac_substream_params) + 256;
+  if (need > h->pinDevBytes) {
+    CK(cudaStreamSynchronize(h->stream), "sync");
+    if (h->pinDev) cudaFree(h->pinDev);
+    h->pinDev = nullptr;
+    h->pinDevBytes = 0;
+    CK(cudaMalloc(&h->pinDev, need + (need >> 3)), "descriptor copy");
+    h->pinDevBytes = need + (need >> 3);
+  }
+  h->pinDevTus = static_cast<cabac_tu_desc *>(h->pinDev);
+  h->pinDevTuOff = reinterpret_cast<uint64_t *>(static_cast<char *>(h->pinDev) + bTus);
+  h->pinDevParams = reinterpret_cast<cabac_substream_params *>(static_cast<char *>(h->pinDev) + bTus + bOff);
+  // stream-ordered: the calls that use the copy are queued behind these transfers on the same stream
+  H2D(h->pinDevTus, tus, nTu * sizeof(cabac_tu_desc));
+  H2D(h->pinDevTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(h->pinDevParams, params, n_sub * sizeof(cabac_substream_params));
+  h->pinTus = tus;
+  h->pinTuOff = tu_offsets;
+  h->pinParams = params;
+  h->pinSubs = n_sub;
+  h->pinTuCount = nTu;
+  return CABAC_OK;
+}
 
 int cabac_ctx_init(cabac_handle *h, const cabac_substream_params *params, size_t n, cabac_ctx_model *out) {
   if (!h || (n && (!params || !out))) return badArg(h, "cabac_ctx_init");
@@ -941,14 +993,15 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   cabac_ctx_model *dCin, *dCout;
   uint8_t *dOut, *dTuFlags, *dPacked;
   uint32_t *dSizes, *dBins, *dStatus;
+  const bool pinnedDesc = h->pinned(tus, tu_offsets, params, n_sub);  // cabac_pin_descriptors: already on the device
   Arena a(h);
-  a.want((void **)&dTus, nTu * sizeof(*tus));
-  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dTus, pinnedDesc ? 0 : nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, pinnedDesc ? 0 : (n_sub + 1) * 8);
   a.want((void **)&dOutOff, (n_sub + 1) * 8);
   a.want((void **)&dEntry, (n_sub + 1) * 8);
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
-  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dP, pinnedDesc ? 0 : n_sub * sizeof(*params));
   const bool twoStage = !h->wppNext && (h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
                                         (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams));
   const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && n_coeffs >= kZeroCopyMinCoeffs)
@@ -963,10 +1016,16 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   a.want((void **)&dBins, n_sub * 4);
   a.want((void **)&dStatus, n_sub * 4);
   CK(a.commit(), "scratch alloc");
-  H2D(dTus, tus, nTu * sizeof(*tus));
-  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  if (pinnedDesc) {
+    dTus = h->pinDevTus;
+    dTuOff = h->pinDevTuOff;
+    dP = h->pinDevParams;
+  } else {
+    H2D(dTus, tus, nTu * sizeof(*tus));
+    H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+    H2D(dP, params, n_sub * sizeof(*params));
+  }
   H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
-  H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
   int rc;
   if (zcCoeffs) {
@@ -1068,13 +1127,14 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   cabac_ctx_model *dCin, *dCout;
   uint8_t *dIn, *dTuFlags;
   uint32_t *dBins, *dBits, *dStatus;
+  const bool pinnedDesc = h->pinned(tus, tu_offsets, params, n_sub);  // cabac_pin_descriptors: already on the device
   Arena a(h);
-  a.want((void **)&dTus, nTu * sizeof(*tus));
-  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dTus, pinnedDesc ? 0 : nTu * sizeof(*tus));
+  a.want((void **)&dTuOff, pinnedDesc ? 0 : (n_sub + 1) * 8);
   a.want((void **)&dInOff, (n_sub + 1) * 8);
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
-  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dP, pinnedDesc ? 0 : n_sub * sizeof(*params));
   int32_t *zcCandidate = (h->zeroCopy && n_coeffs >= kZeroCopyMinCoeffs)
                              ? static_cast<int32_t *>(mappedHostAlias(coeffs)) : nullptr;
   a.want((void **)&dCoeffs, n_coeffs * 4);  // kept even for a zero-copy candidate: the coverage check may refuse
@@ -1086,10 +1146,16 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   a.want((void **)&dBits, n_sub * 4);
   a.want((void **)&dStatus, n_sub * 4);
   CK(a.commit(), "scratch alloc");
-  H2D(dTus, tus, nTu * sizeof(*tus));
-  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  if (pinnedDesc) {
+    dTus = h->pinDevTus;
+    dTuOff = h->pinDevTuOff;
+    dP = h->pinDevParams;
+  } else {
+    H2D(dTus, tus, nTu * sizeof(*tus));
+    H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+    H2D(dP, params, n_sub * sizeof(*params));
+  }
   H2D(dInOff, in_offsets, (n_sub + 1) * 8);
-  H2D(dP, params, n_sub * sizeof(*params));
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
   H2D(dIn, in, nIn);
   // positions no descriptor covers come back as zero

@@ -194,6 +194,19 @@ uint64_t cabac_launch_count(cabac_handle *h);
 void *cabac_host_alloc(size_t bytes);
 void cabac_host_free(void *p);
 
+/* ---- batch descriptors resident on the device ----------------------------- */
+/* The host-pointer residual calls upload tus / tu_offsets / params on every call.
+ * A caller that makes several calls over the SAME descriptor arrays (encode and
+ * decode of one batch, an estimate followed by the final pass, repeated passes of
+ * an RDO loop) uploads them once: after cabac_pin_descriptors the host-pointer
+ * residual entry points that are passed exactly these three pointers and n_sub
+ * use the device copy instead.  The arrays must stay unchanged until
+ * cabac_unpin_descriptors (or the next cabac_pin_descriptors / cabac_destroy). */
+int cabac_pin_descriptors(cabac_handle *h, const cabac_tu_desc *tus,
+                          const uint64_t *tu_offsets,
+                          const cabac_substream_params *params, size_t n_sub);
+int cabac_unpin_descriptors(cabac_handle *h);
+
 /* ---- (2) context initialisation ----------------------------------------- */
 /* Ctx::init(qp, initId) for n (qp, init_id) pairs, contexts.cpp:996-1015,
  * 893-901.  out: n * CABAC_NUM_CTX models.                                   */
