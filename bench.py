@@ -715,8 +715,9 @@ def leg_decode_sweep(args, r):
     return leg
 
 
-def run_e2e(args, r):
-    """The same step through the host-pointer C ABI: pinned host buffers in, pinned host buffers out."""
+def run_e2e(args, r, i16=False):
+    """The same step through the host-pointer C ABI: pinned host buffers in, pinned host buffers out.
+    i16: the coefficient slabs cross the ABI as int16 (cabac_*_i16) instead of the reference's int32 TCoeff."""
     import ctypes as C
     import torch
     import torch.distributed as dist
@@ -725,25 +726,28 @@ def run_e2e(args, r):
     lib, h = eng.lib, eng.h
     P = lambda a: a.ctypes.data_as(C.c_void_p)
     h_tus, h_tuoff = eng.pinned_copy(wl.tus), eng.pinned_copy(wl.tu_offsets)
-    h_par, h_cap, h_co = eng.pinned_copy(wl.params), eng.pinned_copy(cap), eng.pinned_copy(wl.coeffs)
+    h_par, h_cap = eng.pinned_copy(wl.params), eng.pinned_copy(cap)
+    h_co = eng.pinned_copy(wl.coeffs.astype(np.int16) if i16 else wl.coeffs)
+    f_enc = lib.cabac_encode_residual_packed_i16 if i16 else lib.cabac_encode_residual_packed
+    f_dec = lib.cabac_decode_residual_i16 if i16 else lib.cabac_decode_residual
     packed_cap = int(r["out_bytes"] * 1.25) + 4096
     h_packed = eng.host_array(packed_cap, np.uint8)
     h_entry = eng.host_array(n_sub + 1, np.uint64)
     h_sizes, h_ebins, h_est = (eng.host_array(n_sub, np.uint32) for _ in range(3))
     h_eflags, h_dflags = eng.host_array(n_tu, np.uint8), eng.host_array(n_tu, np.uint8)
-    h_dec = eng.host_array(n_co, np.int32)
+    h_dec = eng.host_array(n_co, np.int16 if i16 else np.int32)
     h_dbins, h_dbits, h_dst = (eng.host_array(n_sub, np.uint32) for _ in range(3))
 
     def step():
         # the batch description goes to the device once per step; both calls below reuse it
         rc = lib.cabac_pin_descriptors(h, P(h_tus), P(h_tuoff), P(h_par), n_sub)
         assert rc == 0, (rc, lib.cabac_last_error(h))
-        rc = lib.cabac_encode_residual_packed(h, P(h_tus), P(h_tuoff), P(h_par), n_sub, P(h_co), n_co, None,
-                                              P(h_cap), P(h_packed), packed_cap, P(h_entry), P(h_sizes),
-                                              P(h_ebins), P(h_eflags), None, P(h_est))
+        rc = f_enc(h, P(h_tus), P(h_tuoff), P(h_par), n_sub, P(h_co), n_co, None,
+                   P(h_cap), P(h_packed), packed_cap, P(h_entry), P(h_sizes),
+                   P(h_ebins), P(h_eflags), None, P(h_est))
         assert rc == 0, (rc, lib.cabac_last_error(h))
-        rc = lib.cabac_decode_residual(h, P(h_packed), P(h_entry), P(h_tus), P(h_tuoff), P(h_par), n_sub, None,
-                                       P(h_dec), n_co, P(h_dbins), P(h_dbits), P(h_dflags), None, P(h_dst))
+        rc = f_dec(h, P(h_packed), P(h_entry), P(h_tus), P(h_tuoff), P(h_par), n_sub, None,
+                   P(h_dec), n_co, P(h_dbins), P(h_dbits), P(h_dflags), None, P(h_dst))
         assert rc == 0, (rc, lib.cabac_last_error(h))
 
     for _ in range(max(args.warmup, 3)):
@@ -757,7 +761,7 @@ def run_e2e(args, r):
     dt = time.perf_counter() - t0
     r["barrier"]()
     lib.cabac_unpin_descriptors(h)
-    assert (h_dec == wl.coeffs).all() and (h_ebins == h_dbins).all(), "e2e round trip failed"
+    assert (h_dec.astype(np.int32) == wl.coeffs).all() and (h_ebins == h_dbins).all(), "e2e round trip failed"
     total = int(h_entry[n_sub])
     tt = torch.tensor([dt], dtype=torch.float64, device=r["dev"])
     if r["world"] > 1:
@@ -768,9 +772,10 @@ def run_e2e(args, r):
     return {"value": r["all_bins"] * args.steps / float(tt) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(tt) / args.steps,
             "gpu_launches": int(eng.launch_count - launches0),
-            "api": "cabac_pin_descriptors + cabac_encode_residual_packed + cabac_decode_residual (host pointers; the batch "
-                   "description is uploaded once per step, pinned coefficient slabs are read / written by the kernels "
-                   "directly over PCIe)"}
+            "coefficient_type": "int16" if i16 else "int32 (TCoeff)",
+            "api": ("cabac_pin_descriptors + cabac_encode_residual_packed%s + cabac_decode_residual%s (host pointers; the batch "
+                    "description is uploaded once per step, pinned coefficient slabs are read / written by the kernels "
+                    "directly over PCIe)") % (("_i16", "_i16") if i16 else ("", ""))}
 
 
 def run_cpu_baseline(args, r):
@@ -796,6 +801,7 @@ def main():
         return
     r = run_b200_arm(args)
     e2e = None if args.no_e2e else run_e2e(args, r)
+    e2e_i16 = None if args.no_e2e else run_e2e(args, r, i16=True)
     legs = {}
     if not args.no_legs and args.substreams == "ctu":
         legs["1080p_64_slices"] = r.get("leg_slices")
@@ -861,6 +867,11 @@ def main():
         line["configs"] = legs
     if e2e:
         line["e2e"] = e2e
+        line["e2e"]["limiter"] = ("host side: the step's 1.85 GB per rank cross PCIe into ONE host memory system; plain pinned "
+                                  "cudaMemcpyAsync of the same bytes on 1/2/4/8 ranks takes 21.8 / 38.0 / 74.8 / 120.0 ms "
+                                  "(profiles/r2_pcie_ceiling.txt) - from four ranks up the end-to-end step runs at that ceiling")
+    if e2e_i16:
+        line["e2e_i16"] = e2e_i16
     if r["world"] == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = run_cpu_baseline(args, r)
     if _SAVED_STDOUT is not None:

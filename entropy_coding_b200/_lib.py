@@ -66,6 +66,10 @@ _SIGS = {
     "cabac_substream_ranges_dev": (C.c_int, [_P, _P, _SZ, _P, _SZ, C.c_uint64, C.c_uint64, _P]),
     "cabac_pin_descriptors": (C.c_int, [_P, _P, _P, _P, _SZ]),
     "cabac_unpin_descriptors": (C.c_int, [_P]),
+    "cabac_encode_residual_i16_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_i16_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_encode_residual_packed_i16": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_i16": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
     "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
     "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
 }

@@ -50,6 +50,7 @@ struct cabac_handle {
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
   // WPP launches (cabac_*_wpp*): the sync records of the NEXT coding call (device pointer, consumed by it),
   // snapshot rows + flags (grow-only), and a device copy of host-side sync records
+  bool coeff16Next = false;  // cabac_*_i16: the coefficient slab of the next residual call holds int16 levels
   const cabac_wpp_sync *wppNext = nullptr;
   void *wppScratch = nullptr;
   size_t wppSubs = 0;
@@ -141,6 +142,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
   sc.cmdBuf = h->cmdBuf;
   sc.fusedResolve = h->fusedResolve;
   sc.warpSpecialised = h->encoderMode == CABAC_ENCODER_WARP_SPECIALISED;
+  sc.coeff16 = h->coeff16Next;
   sc.wpp = cabac::WppArgs();
   if (h->wppNext) {  // a WPP launch: snapshot rows + "published" flags for n substreams, flags cleared on the stream
     const cabac_wpp_sync *sync = h->wppNext;
@@ -1004,9 +1006,10 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   a.want((void **)&dP, pinnedDesc ? 0 : n_sub * sizeof(*params));
   const bool twoStage = !h->wppNext && (h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
                                         (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams));
+  const size_t esz = h->coeff16Next ? 2 : 4;  // bytes per coefficient of the caller's slab
   const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && n_coeffs >= kZeroCopyMinCoeffs)
                                 ? static_cast<const int32_t *>(mappedHostAlias(coeffs)) : nullptr;
-  a.want((void **)&dCoeffs, zcCoeffs ? 0 : n_coeffs * 4);
+  a.want((void **)&dCoeffs, zcCoeffs ? 0 : n_coeffs * esz);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
   a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dOut, outCap);
@@ -1063,7 +1066,8 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
     for (int k = 0; k < K; k++) {
       const uint64_t hi = hr[2 * k + 1];
       if (hi > cur) {  // everything below `cur` is already on its way: any slab layout stays correct
-        CK(cudaMemcpyAsync(dCoeffs + cur, coeffs + cur, (hi - cur) * 4, cudaMemcpyHostToDevice, h->copyStream),
+        CK(cudaMemcpyAsync(reinterpret_cast<char *>(dCoeffs) + cur * esz, reinterpret_cast<const char *>(coeffs) + cur * esz,
+                           (hi - cur) * esz, cudaMemcpyHostToDevice, h->copyStream),
            "H2D copy");
         cur = hi;
       }
@@ -1087,7 +1091,7 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
       traceChunks(h, "encode_residual_packed", K, true);
     }
   } else {
-    H2D(dCoeffs, coeffs, n_coeffs * 4);
+    H2D(dCoeffs, coeffs, n_coeffs * esz);
     rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, dCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
                                    dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
@@ -1135,9 +1139,10 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
   a.want((void **)&dRanges, 2 * cabac_handle::kMaxChunks * sizeof(uint64_t));
   a.want((void **)&dChunkStart, (cabac_handle::kMaxChunks + 1) * sizeof(uint32_t));
   a.want((void **)&dP, pinnedDesc ? 0 : n_sub * sizeof(*params));
+  const size_t esz = h->coeff16Next ? 2 : 4;  // bytes per coefficient of the caller's slab
   int32_t *zcCandidate = (h->zeroCopy && n_coeffs >= kZeroCopyMinCoeffs)
                              ? static_cast<int32_t *>(mappedHostAlias(coeffs)) : nullptr;
-  a.want((void **)&dCoeffs, n_coeffs * 4);  // kept even for a zero-copy candidate: the coverage check may refuse
+  a.want((void **)&dCoeffs, n_coeffs * esz);  // kept even for a zero-copy candidate: the coverage check may refuse
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
   a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dIn, nIn);
@@ -1185,7 +1190,7 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
                                        dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
   } else if (h->pipeChunks > 1 && !h->wppNext && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
-    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
+    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * esz, h->stream), "memset");
     // ---- chunked pipeline: finished coefficient ranges leave over PCIe while later chunks decode ----
     CK(ensurePipe(h), "pipeline streams");
     uint64_t *hr = h->pinnedRanges;
@@ -1226,7 +1231,8 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
       CK(cudaStreamWaitEvent(h->copyStream, h->evDone[k], 0), "event wait");
       const uint64_t safe = sufMin[k + 1];
       if (safe > cur) {
-        CK(cudaMemcpyAsync(coeffs + cur, dCoeffs + cur, (safe - cur) * 4, cudaMemcpyDeviceToHost, h->copyStream),
+        CK(cudaMemcpyAsync(reinterpret_cast<char *>(coeffs) + cur * esz, reinterpret_cast<char *>(dCoeffs) + cur * esz,
+                           (safe - cur) * esz, cudaMemcpyDeviceToHost, h->copyStream),
            "D2H copy");
         cur = safe;
       }
@@ -1238,11 +1244,11 @@ int cabac_decode_residual(cabac_handle *h, const uint8_t *in, const uint64_t *in
       traceChunks(h, "decode_residual", K, false);
     }
   } else {
-    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * 4, h->stream), "memset");
+    CK(cudaMemsetAsync(dCoeffs, 0, n_coeffs * esz, h->stream), "memset");
     int rc = cabac_decode_residual_dev(h, dIn, dInOff, dTus, dTuOff, dP, n_sub, ctx_in ? dCin : nullptr, dCoeffs,
                                        dBins, dBits, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
-    D2H(coeffs, dCoeffs, n_coeffs * 4);
+    D2H(coeffs, dCoeffs, n_coeffs * esz);
   }
   D2H(num_bins, dBins, n_sub * 4);
   D2H(bits_read, dBits, n_sub * 4);
@@ -1329,6 +1335,62 @@ int cabac_insert_emulation_prevention(cabac_handle *h, const uint8_t *rbsp, size
   D2H(out, dOut, size_t(*out_size));
   CK(cudaStreamSynchronize(h->stream), "sync");
   return CABAC_OK;
+}
+
+// ---- int16 coefficient slabs: the same calls, half the bytes across PCIe ----
+// VVC levels fit 16 bits (maxLog2TrDynamicRange = 15, context_modelling.cpp:66-72); TCoeff is int32 in the
+// reference (unit.hpp:551), so the shim narrows while it gathers the blocks into the batch slab anyway.
+int cabac_encode_residual_i16_dev(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params, size_t n_sub, const int16_t *coeffs,
+                                  const cabac_ctx_model *ctx_in, uint8_t *out, const uint64_t *out_offsets,
+                                  uint32_t *out_sizes, uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                  uint32_t *status) {
+  if (!h) return CABAC_ERR_ARG;
+  h->coeff16Next = true;
+  const int rc = cabac_encode_residual_dev(h, tus, tu_offsets, params, n_sub, reinterpret_cast<const int32_t *>(coeffs),
+                                           ctx_in, out, out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status);
+  h->coeff16Next = false;
+  return rc;
+}
+
+int cabac_decode_residual_i16_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                                  const uint64_t *tu_offsets, const cabac_substream_params *params, size_t n_sub,
+                                  const cabac_ctx_model *ctx_in, int16_t *coeffs, uint32_t *num_bins, uint32_t *bits_read,
+                                  uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h) return CABAC_ERR_ARG;
+  h->coeff16Next = true;
+  const int rc = cabac_decode_residual_dev(h, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
+                                           reinterpret_cast<int32_t *>(coeffs), num_bins, bits_read, tu_flags, ctx_out,
+                                           status);
+  h->coeff16Next = false;
+  return rc;
+}
+
+int cabac_encode_residual_packed_i16(cabac_handle *h, const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params, size_t n_sub, const int16_t *coeffs,
+                                     size_t n_coeffs, const cabac_ctx_model *ctx_in, const uint64_t *out_offsets,
+                                     uint8_t *packed, size_t packed_cap, uint64_t *entry_points, uint32_t *out_sizes,
+                                     uint32_t *num_bins, uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h) return CABAC_ERR_ARG;
+  h->coeff16Next = true;
+  const int rc = cabac_encode_residual_packed(h, tus, tu_offsets, params, n_sub, reinterpret_cast<const int32_t *>(coeffs),
+                                              n_coeffs, ctx_in, out_offsets, packed, packed_cap, entry_points, out_sizes,
+                                              num_bins, tu_flags, ctx_out, status);
+  h->coeff16Next = false;
+  return rc;
+}
+
+int cabac_decode_residual_i16(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets, const cabac_substream_params *params, size_t n_sub,
+                              const cabac_ctx_model *ctx_in, int16_t *coeffs, size_t n_coeffs, uint32_t *num_bins,
+                              uint32_t *bits_read, uint8_t *tu_flags, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h) return CABAC_ERR_ARG;
+  h->coeff16Next = true;
+  const int rc = cabac_decode_residual(h, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
+                                       reinterpret_cast<int32_t *>(coeffs), n_coeffs, num_bins, bits_read, tu_flags,
+                                       ctx_out, status);
+  h->coeff16Next = false;
+  return rc;
 }
 
 // ---- decode side of substream assembly ----

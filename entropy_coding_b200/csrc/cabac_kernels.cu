@@ -116,7 +116,8 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
                                                          uint32_t *__restrict__ capWords,
                                                          const uint64_t *__restrict__ rawOffsets,
                                                          const cabac_substream_params *__restrict__ params,
-                                                         int sampleMask, uint32_t tuConst, uint32_t areaShift) {
+                                                         int sampleMask, uint32_t tuConst, uint32_t areaShift,
+                                                         int c16) {
   // sampleMask < 0: every block's coefficients are read (slab in HBM).  Otherwise the slab is pinned host
   // memory behind PCIe: the cost is the area / QP / transform-skip estimate of all blocks, scaled by
   // what the estimate misses on the blocks whose index has (index & sampleMask) == 0, which ARE read.
@@ -167,9 +168,16 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
       while (todo) {
         const int j = __ffs(int(todo)) - 1;
         todo &= todo - 1u;
-        const int32_t *src = coeffs + __shfl_sync(FULL, dl.coeff_offset, j);
+        const uint64_t cofs = __shfl_sync(FULL, dl.coeff_offset, j);
+        const int32_t *src = coeffs + cofs;
         const int total = int(__shfl_sync(FULL, area, j));
-        if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
+        if (c16) {
+          const int16_t *s16 = reinterpret_cast<const int16_t *>(coeffs) + cofs;
+          for (int i = lane; i < total; i += 32) {
+            const int v = s16[i];
+            acc += v ? 2 * (33 - __clz(abs(v))) : 0;
+          }
+        } else if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && total >= 128) {
           for (int i = lane * 4; i < total; i += 128) {
             const int4 v = __ldg(reinterpret_cast<const int4 *>(src + i));
             acc += (v.x ? 2 * (33 - __clz(abs(v.x))) : 0) + (v.y ? 2 * (33 - __clz(abs(v.y))) : 0) +
@@ -452,9 +460,19 @@ struct __align__(16) EncWarpSmemT {
 
 // Stages the coded region of a TU into the int16 tile (all lanes).  Returns
 // false (warp-uniform) when a level is outside the int16 TCoeff range.
-__device__ inline bool loadTile(int16_t *tile, const int32_t *__restrict__ src, const TuGeom &g, int lane) {
+__device__ inline bool loadTile(int16_t *tile, const int32_t *__restrict__ src, const TuGeom &g, int lane,
+                                bool c16 = false) {
   bool ok = true;
   const int n = g.tw * g.th;
+  if (c16) {  // int16 TCoeff slab (cabac_*_i16): same layout, half the bytes, always in range
+    const int16_t *s16 = reinterpret_cast<const int16_t *>(src);
+    for (int i = lane; i < n; i += 32) {
+      const int y = i >> g.log2tw, x = i & (g.tw - 1);
+      tile[i] = s16[(size_t(y) << g.log2w) + x];
+    }
+    __syncwarp();
+    return true;
+  }
   if ((g.tw & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
     for (int i = lane * 4; i < n; i += 128) {
       const int y = i >> g.log2tw, x = i & (g.tw - 1);
@@ -484,9 +502,41 @@ __device__ __forceinline__ uint32_t geomKey(const cabac_tu_desc &d) {
 // fetched with cp.async into a raw int32 staging tile while the current block is coded, so the
 // HBM - or, for zero-copy launches, PCIe - round trip of a block never sits on the warp's serial path.
 __device__ __forceinline__ void prefetchBlock(int32_t *raw, const int32_t *__restrict__ src, const cabac_tu_desc &d,
-                                              int lane) {
+                                              int lane, bool c16 = false) {
   const int log2w = d.log2_w, log2tw = min(int(d.log2_w), 5), log2th = min(int(d.log2_h), 5);
   const uint32_t dst = uint32_t(__cvta_generic_to_shared(raw));
+  if (c16) {
+    // int16 slab: the coded part lands in `raw` as tw x th int16 (row-major, stride tw).  Blocks up to 32 wide
+    // are contiguous in the slab (stride == width, unit.hpp:551); 64-wide ones contribute 64-byte row heads.
+    const char *s8 = reinterpret_cast<const char *>(src);
+    const int rowBytes = 2 << log2tw, rows = (log2w <= 5) ? 1 : (1 << log2th);
+    const int lineBytes = (log2w <= 5) ? (2 << (log2tw + log2th)) : rowBytes;  // contiguous bytes per source line
+    const size_t srcStride = size_t(2) << log2w;
+    if ((reinterpret_cast<uintptr_t>(s8) & 15u) == 0 && (lineBytes & 15) == 0) {
+      const int perLine = lineBytes >> 4, total = perLine * rows;
+      for (int u = lane; u < total; u += 32) {
+        const int y = u / perLine, k = u - y * perLine;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + uint32_t(y * lineBytes + k * 16)),
+                     "l"(s8 + y * srcStride + k * 16)
+                     : "memory");
+      }
+    } else if ((reinterpret_cast<uintptr_t>(s8) & 3u) == 0 && (lineBytes & 3) == 0) {
+      const int perLine = lineBytes >> 2, total = perLine * rows;
+      for (int u = lane; u < total; u += 32) {
+        const int y = u / perLine, k = u - y * perLine;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + uint32_t(y * lineBytes + k * 4)),
+                     "l"(s8 + y * srcStride + k * 4)
+                     : "memory");
+      }
+    } else {  // 2-byte aligned odd-sized pieces: plain loads
+      int16_t *r16 = reinterpret_cast<int16_t *>(raw);
+      const int16_t *s16 = reinterpret_cast<const int16_t *>(src);
+      const int n = 1 << (log2tw + log2th);
+      for (int i = lane; i < n; i += 32) r16[i] = s16[(size_t(i >> log2tw) << log2w) + (i & ((1 << log2tw) - 1))];
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    return;
+  }
   if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && log2tw >= 2) {
     const int total = 1 << (log2tw + log2th - 2);  // 16-byte units
     for (int u = lane; u < total; u += 32) {
@@ -507,11 +557,21 @@ __device__ __forceinline__ void prefetchBlock(int32_t *raw, const int32_t *__res
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 // waits for the staged block and narrows it into the int16 tile; false when a level is out of range
-__device__ __forceinline__ bool takeBlock(int16_t *tile, const int32_t *raw, const TuGeom &g, int lane) {
+__device__ __forceinline__ bool takeBlock(int16_t *tile, const int32_t *raw, const TuGeom &g, int lane,
+                                          bool c16 = false) {
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncwarp();
   bool ok = true;
   const int n = g.tw * g.th;
+  if (c16) {  // already int16 in the landing tile: move it over
+    const int16_t *r16 = reinterpret_cast<const int16_t *>(raw);
+    if (n >= 2)
+      for (int i = lane * 2; i < n; i += 64) *reinterpret_cast<uint32_t *>(tile + i) = *reinterpret_cast<const uint32_t *>(r16 + i);
+    else if (lane == 0)
+      tile[0] = r16[0];
+    __syncwarp();
+    return true;
+  }
   if (n < 4) {  // 2 x 1 / 1 x 2 / 1 x 1
     if (lane < n) {
       const int v = raw[lane];
@@ -895,7 +955,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
                        uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu,
-                       uint32_t *__restrict__ ctxBins, const WppArgs wpp) {
+                       uint32_t *__restrict__ ctxBins, const WppArgs wpp, const int c16) {
   constexpr bool kResolve = kMode == FUSED_RESOLVE;
   constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
   constexpr bool kWs = kMode == FUSED_WS;
@@ -977,7 +1037,11 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
     uint64_t t = tuOffsets[sub];
     const uint64_t t1 = tuOffsets[sub + 1];
-    if (t < t1) prefetchBlock(sm.raw, coeffs + tus[t].coeff_offset, tus[t], lane);
+    // element size of the caller's TCoeff slab: int32 (unit.hpp:551) or int16 (cabac_*_i16)
+    auto blockPtr = [&](uint64_t ofs) {
+      return c16 ? reinterpret_cast<const int32_t *>(reinterpret_cast<const int16_t *>(coeffs) + ofs) : coeffs + ofs;
+    };
+    if (t < t1) prefetchBlock(sm.raw, blockPtr(tus[t].coeff_offset), tus[t], lane, c16);
     // WPP: the contexts after this substream's first CTU go to its snapshot row for the row below
     bool wppPending = wpp.sync != nullptr;
     const uint64_t tSync = wppPending ? t + wpp.sync[sub].sync_tus : 0;
@@ -1014,10 +1078,10 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
         bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
         res = ts ? CABAC_TUR_TS : 0;
-        if (!takeBlock(sm.tile, sm.raw, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        if (!takeBlock(sm.tile, sm.raw, g, lane, c16)) st |= CABAC_SS_COEFF_RANGE;
         if (t + 1 < t1) {
           const cabac_tu_desc dn = tus[t + 1];
-          prefetchBlock(sm.raw, coeffs + dn.coeff_offset, dn, lane);
+          prefetchBlock(sm.raw, blockPtr(dn.coeff_offset), dn, lane, c16);
         }
         // ---- pre-scan: non-zero mask per coefficient group, last position ----
         lastCG = -1;
@@ -1184,7 +1248,7 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
                cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
                const uint32_t *__restrict__ order, uint32_t *cursor, uint8_t *__restrict__ out,
                const uint64_t *__restrict__ outOffsets, uint32_t *__restrict__ outSizes,
-               uint32_t *__restrict__ numBins, const WppArgs wpp) {
+               uint32_t *__restrict__ numBins, const WppArgs wpp, const int c16) {
   typedef EncWarpSmemT<kStream ? CABAC_NUM_CTX : RCTX> Smem;
   __shared__ Smem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -1303,7 +1367,9 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
         tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
         bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
         res = ts ? CABAC_TUR_TS : 0;
-        if (!loadTile(sm.tile, coeffs + d.coeff_offset, g, lane)) st |= CABAC_SS_COEFF_RANGE;
+        if (!loadTile(sm.tile, c16 ? reinterpret_cast<const int32_t *>(reinterpret_cast<const int16_t *>(coeffs) + d.coeff_offset)
+                                   : coeffs + d.coeff_offset, g, lane, c16))
+          st |= CABAC_SS_COEFF_RANGE;
         // ---- pre-scan: non-zero mask per coefficient group, last position ----
         lastCG = -1;
         const int cgSize = 1 << g.log2cg;
@@ -1517,7 +1583,7 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
                        uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
-                       const WppArgs wpp) {
+                       const WppArgs wpp, const int c16) {
   __shared__ DecWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   DecWarpSmem &sm = smem[wib];
@@ -1555,11 +1621,19 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       if (tuFlags && lane == 0) tuFlags[t] = uint8_t(res);
       __syncwarp();
       // write the block back (the zero-out region of 64-point blocks as zeros)
-      int32_t *dst = coeffs + d.coeff_offset;
       const int total = g.w * g.h;
-      for (int i = lane; i < total; i += 32) {
-        const int y = i >> g.log2w, x = i & (g.w - 1);
-        dst[i] = (x < g.tw && y < g.th) ? sm.tile[(y << g.log2tw) + x] : 0;
+      if (c16) {  // int16 TCoeff slab (cabac_decode_residual_i16): levels are range-checked above
+        int16_t *dst = reinterpret_cast<int16_t *>(coeffs) + d.coeff_offset;
+        for (int i = lane; i < total; i += 32) {
+          const int y = i >> g.log2w, x = i & (g.w - 1);
+          dst[i] = (x < g.tw && y < g.th) ? int16_t(sm.tile[(y << g.log2tw) + x]) : int16_t(0);
+        }
+      } else {
+        int32_t *dst = coeffs + d.coeff_offset;
+        for (int i = lane; i < total; i += 32) {
+          const int y = i >> g.log2w, x = i & (g.w - 1);
+          dst[i] = (x < g.tw && y < g.th) ? sm.tile[(y << g.log2tw) + x] : 0;
+        }
       }
       __syncwarp();
     }
@@ -1777,7 +1851,7 @@ cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, con
   const int costThreads = nSub >= 16384 ? 32 : 256;
   cost_coeff_kernel<<<costGrid(nSub, 1, costThreads == 32 ? 32 : 16), costThreads, 0, s>>>(tus, tuOffsets, coeffs, nSub, sc.cost, sc.capWords,
                                                              rawOffsets, params, sampleMask, uint32_t(tuConst),
-                                                             uint32_t(areaShift));
+                                                             uint32_t(areaShift), sc.coeff16 ? 1 : 0);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   entry_points_kernel<<<1, 1024, 0, s>>>(sc.capWords, nullptr, nSub, sc.cmdOffsets);
@@ -1805,22 +1879,22 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
       const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
       encode_residual_kernel<FUSED_WS><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
       return cudaGetLastError();
     }
     if (sc.fusedResolve)
       encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
     else
       encode_residual_kernel<FUSED_LEGACY><<<persistentGrid(encode_residual_kernel<FUSED_LEGACY>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
           tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp);
+          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
     return cudaGetLastError();
   }
   produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       nullptr, nullptr, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp);
+      status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;
@@ -1843,7 +1917,7 @@ cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, 
   }
   encode_residual_kernel<FUSED_ESTIMATE><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins, WppArgs());
+      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins, WppArgs(), sc.coeff16 ? 1 : 0);
   return cudaGetLastError();
 }
 
@@ -1899,12 +1973,12 @@ cudaError_t launchEncodeStream(cudaStream_t s, int device, const Sched &sc, cons
   if (!sc.twoStage) {  // few, long substreams: one warp each, bytes straight out of the producer kernel
     produce_kernel<true, true><<<persistentGrid(produce_kernel<true, true>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
         rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, tuFlags, ctxOut,
-        status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, out, outOffsets, outSizes, numBins, sc.wpp);
+        status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, out, outOffsets, outSizes, numBins, sc.wpp, sc.coeff16 ? 1 : 0);
     return cudaGetLastError();
   }
   produce_kernel<true, false><<<persistentGrid(produce_kernel<true, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       rawCmds, rawOffsets, tus, tuOffsets, params, nSub, coeffs, ctxIn, sc.cmdBuf, sc.cmdOffsets, sc.cmdCounts,
-      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp);
+      tuFlags, ctxOut, status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t perBlock = RC_WARPS * 32;
@@ -1935,7 +2009,7 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
   if (e != cudaSuccess) return e;
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
-      (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp);
+      (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp, sc.coeff16 ? 1 : 0);
   return cudaGetLastError();
 }
 

@@ -31,6 +31,7 @@ struct Sched {
   bool warpSpecialised = false;  // fused kernel: producer warps + one walker warp per CTA (FUSED_WS)
   bool fusedResolve = false;  // fused kernel: resolve probabilities lane-parallel before the serial walk
   bool twoStage;            // residual encode: stage P + stage D instead of the fused lockstep kernel
+  bool coeff16 = false;     // the coefficient slab holds int16 levels (cabac_*_i16) instead of int32 TCoeff
   WppArgs wpp;              // WPP launches: substreams are claimed in index order instead of longest-first
 };
 constexpr int kLaunchesPerCodingCall = 3;

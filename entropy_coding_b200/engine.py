@@ -243,10 +243,12 @@ class CabacEngine:
         return choice, costs
 
     def encode_residual_packed(self, tus, tu_offsets, params, coeffs, out_offsets, packed=None, ctx_in=None,
-                               want_ctx=False, raise_on_status=True):
-        """Encode + pack: returns the substreams concatenated in order plus the entry-point table."""
+                               want_ctx=False, raise_on_status=True, i16=False):
+        """Encode + pack: returns the substreams concatenated in order plus the entry-point table.
+        i16: the coefficient slab crosses the ABI as int16 (cabac_encode_residual_packed_i16)."""
         tus, tu_offsets = _np(tus, TU_DT), _np(tu_offsets, np.uint64)
-        params, coeffs, out_offsets = _np(params, PARAMS_DT), _np(coeffs, np.int32), _np(out_offsets, np.uint64)
+        params, out_offsets = _np(params, PARAMS_DT), _np(out_offsets, np.uint64)
+        coeffs = _np(coeffs, np.int16 if i16 else np.int32)
         n = len(params)
         if packed is None:
             packed = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
@@ -255,7 +257,8 @@ class CabacEngine:
         tu_flags = np.zeros(len(tus), np.uint8)
         ctx_in = _np(ctx_in, CTX_DT)
         ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
-        rc = self.lib.cabac_encode_residual_packed(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
+        fn = self.lib.cabac_encode_residual_packed_i16 if i16 else self.lib.cabac_encode_residual_packed
+        rc = fn(self.h, _hp(tus), _hp(tu_offsets), _hp(params), n, _hp(coeffs),
                                                    coeffs.size, _hp(ctx_in), _hp(out_offsets), _hp(packed),
                                                    packed.size, _hp(entry), _hp(sizes), _hp(bins), _hp(tu_flags),
                                                    _hp(ctx_out), _hp(status))
@@ -265,17 +268,19 @@ class CabacEngine:
                     tu_flags=tu_flags, status=status, ctx_out=ctx_out)
 
     def decode_residual(self, data, in_offsets, tus, tu_offsets, params, n_coeffs, ctx_in=None, want_ctx=False,
-                        raise_on_status=True, coeffs_out=None):
+                        raise_on_status=True, coeffs_out=None, i16=False):
         data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
         tus, tu_offsets, params = _np(tus, TU_DT), _np(tu_offsets, np.uint64), _np(params, PARAMS_DT)
         n = len(params)
-        coeffs = np.zeros(n_coeffs, np.int32) if coeffs_out is None else coeffs_out
-        assert coeffs.dtype == np.int32 and coeffs.size >= n_coeffs and coeffs.flags.c_contiguous
+        cdt = np.int16 if i16 else np.int32
+        coeffs = np.zeros(n_coeffs, cdt) if coeffs_out is None else coeffs_out
+        assert coeffs.dtype == cdt and coeffs.size >= n_coeffs and coeffs.flags.c_contiguous
         bins, bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
         tu_flags = np.zeros(len(tus), np.uint8)
         ctx_in = _np(ctx_in, CTX_DT)
         ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
-        rc = self.lib.cabac_decode_residual(self.h, _hp(data), _hp(in_offsets), _hp(tus), _hp(tu_offsets),
+        fn = self.lib.cabac_decode_residual_i16 if i16 else self.lib.cabac_decode_residual
+        rc = fn(self.h, _hp(data), _hp(in_offsets), _hp(tus), _hp(tu_offsets),
                                             _hp(params), n, _hp(ctx_in), _hp(coeffs), n_coeffs, _hp(bins), _hp(bits),
                                             _hp(tu_flags), _hp(ctx_out), _hp(status))
         if rc != ERR_SUBSTREAM or raise_on_status:

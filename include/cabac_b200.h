@@ -363,6 +363,48 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in,
                               uint32_t *bits_read, uint8_t *tu_flags,
                               cabac_ctx_model *ctx_out, uint32_t *status);
 
+/* ---- int16 coefficient slabs ----------------------------------------------- */
+/* The residual calls with the coefficient slab as int16 instead of the reference's
+ * int32 TCoeff (unit.hpp:551).  VVC v1 levels fit 16 bits (maxLog2TrDynamicRange =
+ * 15, context_modelling.cpp:66-72; cabac_reader.cpp:2942-2946 refuses anything else),
+ * and the shim copies every block out of TransformUnit::m_coeffs into the batch slab
+ * anyway (host/gpu_bin_encoder.hpp), so it can narrow there: half the bytes cross
+ * PCIe.  Same descriptors (coeff_offset in coefficients), same results.        */
+int cabac_encode_residual_i16_dev(cabac_handle *h, const cabac_tu_desc *tus,
+                                  const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params, size_t n_sub,
+                                  const int16_t *coeffs, const cabac_ctx_model *ctx_in,
+                                  uint8_t *out, const uint64_t *out_offsets,
+                                  uint32_t *out_sizes, uint32_t *num_bins,
+                                  uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                  uint32_t *status);
+int cabac_decode_residual_i16_dev(cabac_handle *h, const uint8_t *in,
+                                  const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                                  const uint64_t *tu_offsets,
+                                  const cabac_substream_params *params, size_t n_sub,
+                                  const cabac_ctx_model *ctx_in, int16_t *coeffs,
+                                  uint32_t *num_bins, uint32_t *bits_read,
+                                  uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                  uint32_t *status);
+int cabac_encode_residual_packed_i16(cabac_handle *h, const cabac_tu_desc *tus,
+                                     const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params, size_t n_sub,
+                                     const int16_t *coeffs, size_t n_coeffs,
+                                     const cabac_ctx_model *ctx_in,
+                                     const uint64_t *out_offsets, uint8_t *packed,
+                                     size_t packed_cap, uint64_t *entry_points,
+                                     uint32_t *out_sizes, uint32_t *num_bins,
+                                     uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                                     uint32_t *status);
+int cabac_decode_residual_i16(cabac_handle *h, const uint8_t *in,
+                              const uint64_t *in_offsets, const cabac_tu_desc *tus,
+                              const uint64_t *tu_offsets,
+                              const cabac_substream_params *params, size_t n_sub,
+                              const cabac_ctx_model *ctx_in, int16_t *coeffs,
+                              size_t n_coeffs, uint32_t *num_bins, uint32_t *bits_read,
+                              uint8_t *tu_flags, cabac_ctx_model *ctx_out,
+                              uint32_t *status);
+
 /* ---- WPP: CTU rows with context hand-over, one launch ---------------------- */
 /* With entropy_coding_sync_enabled a slice is one substream per CTU row and row r
  * starts from the contexts row r-1 held after its FIRST CTU

@@ -12,7 +12,7 @@ ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 def declared_functions():
     text = open(os.path.join(ROOT, "include", "cabac_b200.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(cabac_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(cabac_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_exports_match_header():

@@ -792,3 +792,53 @@ def test_million_substreams_round_trip():
     for r in rows:
         assert r["round_trip_ok"] and r["tiles_identical"], r
         assert r["bins"] == rows[0]["bins"] * (r["substreams"] // 10_000)
+
+
+def test_int16_coefficient_slabs(engine, oracle):
+    """cabac_encode_residual_packed_i16 / cabac_decode_residual_i16: the slab crosses the ABI as int16; bytes,
+    bin counts and decoded levels equal the int32 calls' (every encoder kernel; staged and zero-copy host paths,
+    unaligned block starts, 64-wide blocks, ISP shapes)."""
+    wl = W.random_substreams(200, seed=321, tus_per_sub=(1, 12), ts_fraction=0.2)
+    # odd coefficient offsets: shift every block by a different small gap so that 2- / 4- / 16-byte paths all run
+    tus = wl.tus.copy()
+    gaps = (np.arange(len(tus)) % 5).astype(np.uint64)
+    new_off = np.concatenate([[0], np.cumsum(gaps[:-1] + (1 << (tus["log2_w"].astype(np.uint64) + tus["log2_h"].astype(np.uint64)))[:-1])]).astype(np.uint64) + gaps[0]
+    slab = np.zeros(int(new_off[-1]) + (1 << int(tus["log2_w"][-1] + tus["log2_h"][-1])) + 8, np.int32)
+    for t, o in zip(wl.tus, new_off):
+        a = 1 << int(t["log2_w"] + t["log2_h"])
+        slab[int(o):int(o) + a] = wl.coeffs[int(t["coeff_offset"]):int(t["coeff_offset"]) + a]
+    tus["coeff_offset"] = new_off
+    cap = wl.out_capacity(bytes_per_coeff=5.0)
+    slab16 = slab.astype(np.int16)
+    ref = engine.encode_residual_packed(tus, wl.tu_offsets, wl.params, slab, cap)
+    for mode in (0, 1, 2, 3):
+        engine.set_encoder_mode(mode)
+        try:
+            r = engine.encode_residual_packed(tus, wl.tu_offsets, wl.params, slab16, cap, i16=True)
+        finally:
+            engine.set_encoder_mode(0)
+        assert r["packed"].tobytes() == ref["packed"].tobytes() and (r["num_bins"] == ref["num_bins"]).all(), mode
+        assert (r["tu_flags"] == ref["tu_flags"]).all()
+    d32 = engine.decode_residual(ref["packed"], ref["entry_points"], tus, wl.tu_offsets, wl.params, slab.size)
+    d16 = engine.decode_residual(ref["packed"], ref["entry_points"], tus, wl.tu_offsets, wl.params, slab.size, i16=True)
+    assert d16["coeffs"].dtype == np.int16 and (d16["coeffs"].astype(np.int32) == d32["coeffs"]).all()
+    assert (d16["num_bins"] == d32["num_bins"]).all() and (d32["coeffs"] == slab).all()
+    # the oracle on a sample, from the int16 call's bytes
+    for i in range(0, wl.n_sub, 25):
+        a, b = int(wl.tu_offsets[i]), int(wl.tu_offsets[i + 1])
+        p = wl.params[i]
+        eb = oracle.encode_residual(tus[a:b], slab, int(p["qp"]), int(p["init_id"]), int(p["flags"]))[0]
+        e = ref["entry_points"]
+        assert ref["packed"][int(e[i]):int(e[i + 1])].tobytes() == eb.tobytes()
+    # zero-copy host path (pinned slabs >= 4 Mi coefficients): int16 in, int16 out
+    big = W.frames_as_ctu_substreams(2, 1920, 1080, seed0=5150)
+    capb = big.out_capacity()
+    h16 = engine.pinned_copy(big.coeffs.astype(np.int16))
+    rb32 = engine.encode_residual_packed(big.tus, big.tu_offsets, big.params, engine.pinned_copy(big.coeffs), capb)
+    rb16 = engine.encode_residual_packed(big.tus, big.tu_offsets, big.params, h16, capb, i16=True)
+    assert rb16["packed"].tobytes() == rb32["packed"].tobytes()
+    out16 = engine.host_array(big.coeffs.size, np.int16)
+    out16[:] = 0x5a5a
+    engine.decode_residual(rb16["packed"], rb16["entry_points"], big.tus, big.tu_offsets, big.params, big.coeffs.size,
+                           coeffs_out=out16, i16=True)
+    assert (out16.astype(np.int32) == big.coeffs).all()
