@@ -56,6 +56,7 @@ struct cabac_handle {
   size_t wppSubs = 0;
   cabac_wpp_sync *wppDev = nullptr;
   size_t wppDevSubs = 0;
+  cabac::SlicedWork sliced;  // scratch of the sliced encoder
   // cabac_pin_descriptors: device copies of a batch description the caller promised not to change
   const void *pinTus = nullptr, *pinTuOff = nullptr, *pinParams = nullptr;
   size_t pinSubs = 0, pinTuCount = 0;
@@ -149,6 +150,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     h->wppNext = nullptr;
     if (n > h->wppSubs) {
       if (h->pinDev) cudaFree(h->pinDev);
+  cabac::freeSlicedWork(h->sliced);
   if (h->wppScratch) cudaFree(h->wppScratch);
       h->wppScratch = nullptr;
       h->wppSubs = 0;
@@ -292,6 +294,10 @@ cabac::Sched chunkSched(const cabac::Sched &base, size_t s0, int k) {
   return c;
 }
 
+// AUTO takes the sliced encoder (parallel inside every substream) for batches of fewer substreams than
+// fill the warp slots of the fused kernels, when they are long: measured crossover on 1080p frames cut
+// into n substreams: ~2 500 (the fused kernels need one warp per substream, 2 960 resident).
+constexpr size_t kSlicedMaxSubstreams = 2048, kSlicedMinTusPerSubstream = 256, kSlicedMinTus = 65536;
 // From this many substreams on, stage D (32 substreams per warp) fills the machine.
 constexpr size_t kTwoStageMinSubstreams = 32768;
 // AUTO: the warp-specialised fused kernel from here up to the two-stage threshold (148 SMs x 19 producers x 2)
@@ -345,6 +351,7 @@ cabac_handle *cabac_create(int device) {
     if (!strcmp(m, "fused")) h->encoderMode = CABAC_ENCODER_FUSED;
     if (!strcmp(m, "two_stage")) h->encoderMode = CABAC_ENCODER_TWO_STAGE;
     if (!strcmp(m, "warp_specialised")) h->encoderMode = CABAC_ENCODER_WARP_SPECIALISED;
+    if (!strcmp(m, "sliced")) h->encoderMode = CABAC_ENCODER_SLICED;
   }
   return h;
 }
@@ -360,6 +367,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
   if (h->epbScratch) cudaFree(h->epbScratch);
   if (h->pinDev) cudaFree(h->pinDev);
+  cabac::freeSlicedWork(h->sliced);
   if (h->wppScratch) cudaFree(h->wppScratch);
   if (h->wppDev) cudaFree(h->wppDev);
   for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
@@ -381,7 +389,7 @@ int cabac_set_stream(cabac_handle *h, void *cuda_stream) {
 }
 
 int cabac_set_encoder_mode(cabac_handle *h, int mode) {
-  if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_WARP_SPECIALISED) return CABAC_ERR_ARG;
+  if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_SLICED) return CABAC_ERR_ARG;
   h->encoderMode = mode;
   return CABAC_OK;
 }
@@ -478,6 +486,20 @@ int cabac_encode_residual_dev(cabac_handle *h, const cabac_tu_desc *tus, const u
   if (!n_sub) return CABAC_OK;
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  // Few, long substreams (slices, frames): the sliced encoder, parallel inside every substream.  It needs the
+  // slab on the device (several passes), terminated substreams and no WPP hand-over; otherwise it declines.
+  if (!sc.wpp.sync && !h->areaCostNext &&
+      (h->encoderMode == CABAC_ENCODER_SLICED || (h->encoderMode == CABAC_ENCODER_AUTO && n_sub < kSlicedMaxSubstreams))) {
+    bool used = false;
+    int launches = 0;
+    const bool forced = h->encoderMode == CABAC_ENCODER_SLICED;
+    CK(cabac::launchEncodeSliced(h->stream, h->device, h->sliced, tus, tu_offsets, params, n_sub, coeffs, sc.coeff16, ctx_in,
+                                 out, out_offsets, out_sizes, num_bins, tu_flags, ctx_out, status ? status : sc.statusScratch,
+                                 forced ? 0 : kSlicedMinTusPerSubstream, forced ? 0 : kSlicedMinTus, &used, &launches),
+       "sliced encoder");
+    h->launches += uint64_t(launches);
+    if (used) return CABAC_OK;
+  }
   static const bool forceAreaCost = getenv("CABAC_B200_AREA_COST") && atoi(getenv("CABAC_B200_AREA_COST"));  // experiment
   const bool areaCost = h->areaCostNext || forceAreaCost;
   h->areaCostNext = false;
@@ -665,6 +687,7 @@ int cabac_pin_descriptors(cabac_handle *h, const cabac_tu_desc *tus, const uint6
   if (need > h->pinDevBytes) {
     CK(cudaStreamSynchronize(h->stream), "sync");
     if (h->pinDev) cudaFree(h->pinDev);
+  cabac::freeSlicedWork(h->sliced);
     h->pinDev = nullptr;
     h->pinDevBytes = 0;
     CK(cudaMalloc(&h->pinDev, need + (need >> 3)), "descriptor copy");
@@ -1007,7 +1030,11 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
   const bool twoStage = !h->wppNext && (h->encoderMode == CABAC_ENCODER_TWO_STAGE ||
                                         (h->encoderMode == CABAC_ENCODER_AUTO && n_sub >= kTwoStageMinSubstreams));
   const size_t esz = h->coeff16Next ? 2 : 4;  // bytes per coefficient of the caller's slab
-  const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && n_coeffs >= kZeroCopyMinCoeffs)
+  // few, long substreams go to the sliced encoder, which makes its passes over a slab in HBM
+  const bool slicedLikely = !h->wppNext && (h->encoderMode == CABAC_ENCODER_SLICED ||
+                                            (h->encoderMode == CABAC_ENCODER_AUTO && n_sub < kSlicedMaxSubstreams &&
+                                             nTu >= kSlicedMinTus && nTu >= kSlicedMinTusPerSubstream * n_sub));
+  const int32_t *zcCoeffs = (h->zeroCopy && !twoStage && !slicedLikely && n_coeffs >= kZeroCopyMinCoeffs)
                                 ? static_cast<const int32_t *>(mappedHostAlias(coeffs)) : nullptr;
   a.want((void **)&dCoeffs, zcCoeffs ? 0 : n_coeffs * esz);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
@@ -1039,7 +1066,8 @@ int cabac_encode_residual_packed(cabac_handle *h, const cabac_tu_desc *tus, cons
     rc = cabac_encode_residual_dev(h, dTus, dTuOff, dP, n_sub, zcCoeffs, ctx_in ? dCin : nullptr, dOut, dOutOff,
                                    dSizes, dBins, dTuFlags, ctx_out ? dCout : nullptr, dStatus);
     if (rc) return rc;
-  } else if (h->pipeChunks > 1 && !twoStage && !h->wppNext && n_coeffs >= h->pipeMinCoeffs && n_sub >= h->pipeMinSubstreams) {
+  } else if (h->pipeChunks > 1 && !twoStage && !slicedLikely && !h->wppNext && n_coeffs >= h->pipeMinCoeffs &&
+             n_sub >= h->pipeMinSubstreams) {
     // ---- chunked pipeline: the slab crosses PCIe chunk by chunk while earlier chunks are coded ----
     CK(ensurePipe(h), "pipeline streams");
     uint64_t *hr = h->pinnedRanges;

@@ -8,6 +8,7 @@
 #include <cstdlib>
 
 #include <cstring>
+#include <algorithm>
 
 #include "cabac_lockstep_enc.cuh"
 #include "cabac_kernels.h"
@@ -1813,6 +1814,10 @@ static int costGrid(size_t n, int perBlock, int maxPerSm = 16) {
   const size_t b = (n + perBlock - 1) / perBlock, cap = size_t(148) * maxPerSm;
   return int(b < 1 ? 1 : (b > cap ? cap : b));
 }
+
+}  // namespace cabac
+#include "cabac_sliced.cuh"
+namespace cabac {
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
                           cabac_ctx_model *out) {

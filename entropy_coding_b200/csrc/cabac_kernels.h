@@ -61,6 +61,20 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  const cabac_ctx_model *ctxIn, uint8_t *out, const uint64_t *outOffsets,
                                  uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status);
+// Scratch of the sliced encoder (few, long substreams; cabac_sliced.cuh), owned by the handle, grow-only.
+struct SlicedWork {
+  static constexpr int kBufs = 13;
+  void *buf[kBufs] = {};
+  size_t bytes[kBufs] = {};
+  uint64_t *pinned = nullptr;
+};
+cudaError_t launchEncodeSliced(cudaStream_t s, int device, SlicedWork &W, const cabac_tu_desc *tus,
+                               const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
+                               const int32_t *coeffs, bool coeff16, const cabac_ctx_model *ctxIn, uint8_t *out,
+                               const uint64_t *outOffsets, uint32_t *outSizes, uint32_t *numBins, uint8_t *tuFlags,
+                               cabac_ctx_model *ctxOut, uint32_t *status, size_t minTusPerSub, size_t minTus,
+                               bool *used, int *launches);
+void freeSlicedWork(SlicedWork &W);
 cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                    const uint64_t *tuOffsets, const cabac_substream_params *params, size_t nSub,
                                    const int32_t *coeffs, const cabac_ctx_model *ctxIn, uint64_t *estBits,

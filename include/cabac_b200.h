@@ -181,7 +181,11 @@ enum {
   CABAC_ENCODER_AUTO = 0,
   CABAC_ENCODER_FUSED = 1,
   CABAC_ENCODER_TWO_STAGE = 2,
-  CABAC_ENCODER_WARP_SPECIALISED = 3
+  CABAC_ENCODER_WARP_SPECIALISED = 3,
+  CABAC_ENCODER_SLICED = 4 /* few, LONG substreams (slices, frames), terminated: every stage parallel INSIDE
+                              a substream - all TUs binarised at once, the contexts resolved as independent
+                              chains, the interval coder split into segments whose pieces are summed
+                              (DESIGN.md section 4).  AUTO picks it below 2 048 substreams of >= 256 TUs. */
 };
 int cabac_set_encoder_mode(cabac_handle *h, int mode);
 const char *cabac_last_error(cabac_handle *h);

@@ -317,7 +317,7 @@ def test_residual_all_shapes_single_coeff(engine, oracle):
     d = engine.decode_residual(np.concatenate(outs), offsets_of(r["sizes"]), tus, wl.tu_offsets, params, coeffs.size)
     assert (d["coeffs"] == coeffs).all()
     # the other encoder kernels and the bit estimator on the same shapes
-    for mode in (2, 3):
+    for mode in (2, 3, 4):
         engine.set_encoder_mode(mode)
         try:
             r2, outs2 = run_residual(engine, wl)
@@ -361,7 +361,7 @@ def test_residual_narrow_isp_shapes_random(engine, oracle):
     for i in range(n):
         p = params[i]
         want.append(oracle.encode_residual(tus[i * per:(i + 1) * per], coeffs, int(p["qp"]), 2, int(p["flags"]), want_ctx=True))
-    for mode in (1, 2, 3):
+    for mode in (1, 2, 3, 4):
         engine.set_encoder_mode(mode)
         try:
             r, outs = run_residual(engine, wl)
@@ -811,7 +811,7 @@ def test_int16_coefficient_slabs(engine, oracle):
     cap = wl.out_capacity(bytes_per_coeff=5.0)
     slab16 = slab.astype(np.int16)
     ref = engine.encode_residual_packed(tus, wl.tu_offsets, wl.params, slab, cap)
-    for mode in (0, 1, 2, 3):
+    for mode in (0, 1, 2, 3, 4):
         engine.set_encoder_mode(mode)
         try:
             r = engine.encode_residual_packed(tus, wl.tu_offsets, wl.params, slab16, cap, i16=True)
@@ -842,3 +842,68 @@ def test_int16_coefficient_slabs(engine, oracle):
     engine.decode_residual(rb16["packed"], rb16["entry_points"], big.tus, big.tu_offsets, big.params, big.coeffs.size,
                            coeffs_out=out16, i16=True)
     assert (out16.astype(np.int32) == big.coeffs).all()
+
+
+def test_sliced_encoder_long_substreams(engine, oracle):
+    """CABAC_ENCODER_SLICED (few, long substreams; every stage parallel inside a substream): bytes, bin counts,
+    final contexts and TU flags equal the fused kernel's and the oracle's - substreams of hundreds of
+    segments, handed-in contexts, sign hiding, transform skip, one substream of a single TU, an output slab
+    that is too small, and AUTO picking the path for a frame-sized slice."""
+    wl = W.random_substreams(7, seed=77, tus_per_sub=(200, 900), ts_fraction=0.15)
+    tiny = W.random_substreams(2, seed=78, tus_per_sub=(1, 1))
+    # append the two one-TU substreams
+    tus2 = tiny.tus.copy()
+    tus2["coeff_offset"] += np.uint64(wl.coeffs.size)
+    tus = np.concatenate([wl.tus, tus2])
+    tu_off = np.concatenate([wl.tu_offsets, wl.tu_offsets[-1] + tiny.tu_offsets[1:]]).astype(np.uint64)
+    params = np.concatenate([wl.params, tiny.params])
+    params["flags"][1] = T | SUB_SIGN_HIDING
+    params["flags"][2] = T
+    params["init_id"][3] = 0
+    coeffs = np.concatenate([wl.coeffs, tiny.coeffs])
+    batch = W.Workload(tus, tu_off, params, coeffs)
+    n = batch.n_sub
+    ctx_in = np.zeros((n, 379), CTX_DT)
+    ctx_in[4] = oracle.ctx_init(17, 1)[0]
+    params["flags"][4] |= SUB_CTX_IN
+    cap = batch.out_capacity(bytes_per_coeff=5.0)
+    engine.set_encoder_mode(1)
+    a = engine.encode_residual(tus, tu_off, params, coeffs, cap, ctx_in=ctx_in, want_ctx=True)
+    engine.set_encoder_mode(4)
+    try:
+        b = engine.encode_residual(tus, tu_off, params, coeffs, cap, ctx_in=ctx_in, want_ctx=True)
+        assert (a["sizes"] == b["sizes"]).all() and (a["num_bins"] == b["num_bins"]).all()
+        for i in range(n):
+            x = a["out"][int(cap[i]):int(cap[i]) + int(a["sizes"][i])]
+            y = b["out"][int(cap[i]):int(cap[i]) + int(b["sizes"][i])]
+            assert x.tobytes() == y.tobytes(), i
+        assert (a["ctx_out"] == b["ctx_out"]).all() and (a["tu_flags"] == b["tu_flags"]).all()
+        for i in (0, 4, n - 1):
+            p = params[i]
+            t0, t1 = int(tu_off[i]), int(tu_off[i + 1])
+            eb, nb, _ = oracle.encode_residual(tus[t0:t1], coeffs, int(p["qp"]), int(p["init_id"]), int(p["flags"]),
+                                               ctx_in=ctx_in[i] if i == 4 else None)
+            assert b["out"][int(cap[i]):int(cap[i]) + int(b["sizes"][i])].tobytes() == eb.tobytes() and int(b["num_bins"][i]) == nb
+        # an output slab that is too small is reported, nothing is written past it
+        small = cap.copy()
+        small[1:] = np.cumsum(np.maximum(64, (np.diff(cap.astype(np.int64)) // 40) // 16 * 16))
+        c = engine.encode_residual(tus, tu_off, params, coeffs, small, ctx_in=ctx_in, raise_on_status=False)
+        assert (c["status"][:7] & SS_OUT_OVERFLOW).all()
+    finally:
+        engine.set_encoder_mode(0)
+    # AUTO: a frame-sized slice takes the sliced path (same bytes as the CTU-substream kernels on a sample check)
+    big = W.frames_as_ctu_substreams(2, 1920, 1080, seed0=99)  # 2 slices of ~86 000 TUs
+    slices = W.merge_substreams(big, big.n_sub // 2)
+    capb = slices.out_capacity()
+    l0 = engine.launch_count
+    r0 = engine.encode_residual(slices.tus, slices.tu_offsets, slices.params, slices.coeffs, capb)
+    assert engine.launch_count - l0 > 15  # the multi-kernel sliced pipeline, not one fused launch
+    engine.set_encoder_mode(1)
+    try:
+        r1 = engine.encode_residual(slices.tus, slices.tu_offsets, slices.params, slices.coeffs, capb)
+    finally:
+        engine.set_encoder_mode(0)
+    assert (r0["sizes"] == r1["sizes"]).all() and r0["out"].tobytes() == r1["out"].tobytes()
+    d = engine.decode_residual(np.concatenate([r0["out"][int(capb[i]):int(capb[i]) + int(r0["sizes"][i])] for i in range(2)]),
+                               offsets_of(r0["sizes"]), slices.tus, slices.tu_offsets, slices.params, slices.coeffs.size)
+    assert (d["coeffs"] == slices.coeffs).all()
