@@ -21,6 +21,7 @@ _SIGS = {
     "cabac_set_stream": (C.c_int, [_P, _P]),
     "cabac_sync": (C.c_int, [_P]),
     "cabac_set_encoder_mode": (C.c_int, [_P, C.c_int]),
+    "cabac_set_decoder_mode": (C.c_int, [_P, C.c_int]),
     "cabac_last_error": (C.c_char_p, [_P]),
     "cabac_version": (C.c_char_p, []),
     "cabac_launch_count": (C.c_uint64, [_P]),

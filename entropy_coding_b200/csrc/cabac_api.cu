@@ -32,6 +32,9 @@ struct cabac_handle {
   size_t cmdCapWords = 0;
   uint64_t *pinnedTotal = nullptr;  // page-locked landing spot for the slab size read-back
   int encoderMode = CABAC_ENCODER_AUTO;
+  int decoderMode = CABAC_DECODER_AUTO;
+  uint32_t *threadCtx = nullptr;  // context rows of the thread-per-substream decoder, grow-only
+  size_t threadCtxSubs = 0;
   bool zeroCopy = true;      // CABAC_B200_ZERO_COPY=0: always stage pinned host slabs through device memory
   bool areaCostNext = false; // next residual encode: schedule from areas, do not read the slab (zero-copy)
   bool fusedResolve = true;  // CABAC_B200_FUSED_RESOLVE=0 selects the classic single-site drain
@@ -151,6 +154,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     if (n > h->wppSubs) {
       if (h->pinDev) cudaFree(h->pinDev);
   cabac::freeSlicedWork(h->sliced);
+  if (h->threadCtx) cudaFree(h->threadCtx);
   if (h->wppScratch) cudaFree(h->wppScratch);
       h->wppScratch = nullptr;
       h->wppSubs = 0;
@@ -169,6 +173,25 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     cudaError_t e = cudaMemsetAsync(sc.wpp.ready, 0, n * sizeof(uint32_t), h->stream);
     if (e != cudaSuccess) return e;
   }
+  return cudaSuccess;
+}
+
+// AUTO keeps the warp-lockstep decoder at every batch size: measured at 10^5 substreams the thread-per-substream
+// kernel issues 4.8x fewer warp instructions but runs them 7.4 lanes wide at 15 % occupancy and ends up 1.2x slower
+// (profiles/r2_decoder_modes.md). CABAC_DECODER_THREAD selects it explicitly.
+cudaError_t threadDecodeFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
+  sc.threadDecode = !sc.wpp.sync && n > 0 && h->decoderMode == CABAC_DECODER_THREAD;
+  if (!sc.threadDecode) return cudaSuccess;
+  if (n > h->threadCtxSubs) {
+    if (h->threadCtx) cudaFree(h->threadCtx);
+    h->threadCtx = nullptr;
+    h->threadCtxSubs = 0;
+    const size_t cap = n + (n >> 3) + 1024;
+    cudaError_t e = cudaMalloc(&h->threadCtx, cap * 230 * sizeof(uint32_t));
+    if (e != cudaSuccess) return e;
+    h->threadCtxSubs = cap;
+  }
+  sc.threadCtx = h->threadCtx;
   return cudaSuccess;
 }
 
@@ -353,6 +376,10 @@ cabac_handle *cabac_create(int device) {
     if (!strcmp(m, "warp_specialised")) h->encoderMode = CABAC_ENCODER_WARP_SPECIALISED;
     if (!strcmp(m, "sliced")) h->encoderMode = CABAC_ENCODER_SLICED;
   }
+  if (const char *m = getenv("CABAC_B200_DECODER")) {
+    if (!strcmp(m, "lockstep")) h->decoderMode = CABAC_DECODER_LOCKSTEP;
+    if (!strcmp(m, "thread")) h->decoderMode = CABAC_DECODER_THREAD;
+  }
   return h;
 }
 
@@ -368,6 +395,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->epbScratch) cudaFree(h->epbScratch);
   if (h->pinDev) cudaFree(h->pinDev);
   cabac::freeSlicedWork(h->sliced);
+  if (h->threadCtx) cudaFree(h->threadCtx);
   if (h->wppScratch) cudaFree(h->wppScratch);
   if (h->wppDev) cudaFree(h->wppDev);
   for (int i = 0; i < cabac_handle::kMaxChunks; i++) {
@@ -391,6 +419,12 @@ int cabac_set_stream(cabac_handle *h, void *cuda_stream) {
 int cabac_set_encoder_mode(cabac_handle *h, int mode) {
   if (!h || mode < CABAC_ENCODER_AUTO || mode > CABAC_ENCODER_SLICED) return CABAC_ERR_ARG;
   h->encoderMode = mode;
+  return CABAC_OK;
+}
+
+int cabac_set_decoder_mode(cabac_handle *h, int mode) {
+  if (!h || mode < CABAC_DECODER_AUTO || mode > CABAC_DECODER_THREAD) return CABAC_ERR_ARG;
+  h->decoderMode = mode;
   return CABAC_OK;
 }
 
@@ -608,10 +642,11 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
   DeviceGuard g(h->device);
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(threadDecodeFor(h, n_sub, sc), "thread decoder scratch");
   CK(cabac::launchDecodeResidual(h->stream, h->device, sc, in, in_offsets, tus, tu_offsets, params, n_sub, ctx_in,
                                  coeffs, num_bins, bits_read, tu_flags, ctx_out, status),
      "decode_residual_kernel");
-  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall + (sc.threadDecode ? 1 : 0) : 0;
   return CABAC_OK;
 }
 
@@ -688,6 +723,7 @@ int cabac_pin_descriptors(cabac_handle *h, const cabac_tu_desc *tus, const uint6
     CK(cudaStreamSynchronize(h->stream), "sync");
     if (h->pinDev) cudaFree(h->pinDev);
   cabac::freeSlicedWork(h->sliced);
+  if (h->threadCtx) cudaFree(h->threadCtx);
     h->pinDev = nullptr;
     h->pinDevBytes = 0;
     CK(cudaMalloc(&h->pinDev, need + (need >> 3)), "descriptor copy");

@@ -1781,7 +1781,9 @@ cudaError_t uploadRom() {
   uint32_t recip[256] = {0};
   for (uint32_t range = 256; range <= 510; range++)
     recip[range - 256] = uint32_t(((1ull << 34) + range - 1) / range);  // ceil(2^34 / range)
-  return cudaMemcpyToSymbol(c_recip, recip, sizeof(recip));
+  e = cudaMemcpyToSymbol(c_recip, recip, sizeof(recip));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpyToSymbol(g_recipTab, recip, sizeof(recip));
 }
 
 const unsigned char *hostInitTable(int row) { return hosttab::CABAC_CTX_INIT_TABLE[row]; }
@@ -1817,6 +1819,7 @@ static int costGrid(size_t n, int perBlock, int maxPerSm = 16) {
 
 }  // namespace cabac
 #include "cabac_sliced.cuh"
+#include "cabac_decode_thread.cuh"
 namespace cabac {
 
 cudaError_t launchCtxInit(cudaStream_t s, int device, const cabac_substream_params *params, size_t n,
@@ -2012,6 +2015,28 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
     cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
+  if (sc.threadDecode && !sc.wpp.sync) {  // one thread per substream (cabac_decode_thread.cuh)
+    const unsigned zb = unsigned(std::min<size_t>(nSub * 4 + 1, size_t(148) * 32));
+    // One warp per block: a block keeps its slot until its slowest substream ends, so small blocks retire sooner
+    // (100 000 substreams: 139 ms at 128 threads, 116 at 64, 111 at 32; profiles/r2_decoder_modes.md). Dev knobs.
+    static const int tdBlock = getenv("CABAC_B200_TD_BLOCK") ? atoi(getenv("CABAC_B200_TD_BLOCK")) : 32;
+    static const int tdDense = getenv("CABAC_B200_TD_DENSE") ? atoi(getenv("CABAC_B200_TD_DENSE")) : 0;
+    const unsigned bs = unsigned(tdBlock >= 32 && tdBlock <= 128 ? tdBlock & ~31 : 32);
+    const unsigned grid = unsigned((nSub + bs - 1) / bs);
+#define TD_LAUNCH(T, MINB)                                                                                              \
+  decode_residual_thread_kernel<T, MINB><<<grid, bs, 0, s>>>(in, inOffsets, tus, tuOffsets, params, nSub, ctxIn,        \
+                                                             reinterpret_cast<T *>(coeffs), numBins, bitsRead, tuFlags, \
+                                                             ctxOut, status, sc.order, sc.threadCtx)
+    if (sc.coeff16) {
+      td_zero_blocks_kernel<int16_t><<<zb, 256, 0, s>>>(tus, tuOffsets, nSub, reinterpret_cast<int16_t *>(coeffs));
+      if (tdDense) TD_LAUNCH(int16_t, 8); else TD_LAUNCH(int16_t, 1);
+    } else {
+      td_zero_blocks_kernel<int32_t><<<zb, 256, 0, s>>>(tus, tuOffsets, nSub, coeffs);
+      if (tdDense) TD_LAUNCH(int32_t, 8); else TD_LAUNCH(int32_t, 1);
+    }
+#undef TD_LAUNCH
+    return cudaGetLastError();
+  }
   decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
       (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp, sc.coeff16 ? 1 : 0);

@@ -31,6 +31,8 @@ struct Sched {
   bool warpSpecialised = false;  // fused kernel: producer warps + one walker warp per CTA (FUSED_WS)
   bool fusedResolve = false;  // fused kernel: resolve probabilities lane-parallel before the serial walk
   bool twoStage;            // residual encode: stage P + stage D instead of the fused lockstep kernel
+  bool threadDecode = false;  // residual decode: one thread per substream instead of one warp (>= 10^5 substreams)
+  uint32_t *threadCtx = nullptr;  // [n][230] packed models, the thread decoder's context rows
   bool coeff16 = false;     // the coefficient slab holds int16 levels (cabac_*_i16) instead of int32 TCoeff
   WppArgs wpp;              // WPP launches: substreams are claimed in index order instead of longest-first
 };

@@ -27,6 +27,8 @@ namespace cabac {
 
 // ceil(2^34 / r) for r = 256..510: floor(A / r) == (A * M) >> 34 for all A < 2^25.
 __device__ __constant__ uint32_t c_recip[256];
+// the same table in global memory for the thread-per-substream decoder (a per-lane index is slow in the constant bank)
+__device__ uint32_t g_recipTab[256];
 
 // Context entry: everything a bin needs in one 16-byte shared-memory word.
 //   x = state1 (bits 0..14) | state0 << 16        BinProbModel_Std::m_state, contexts.hpp:184-190

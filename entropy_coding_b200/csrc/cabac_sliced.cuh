@@ -20,7 +20,7 @@
 //      which is added with carry propagation by one thread per substream (D3).
 //   The byte stream the reference writes (writeOut / finish, arith_codec.cpp:339-357, 524-546) is the bit
 //   string of X >> 8 on T + 1 bits, then the stop bit (bit_stream.cpp:152-155).  tests/tools/segment_model.py
-//   checks both statements against the oracle in exact integer arithmetic.
+//   checks both statements against the CPU checker in exact integer arithmetic.
 #pragma once
 
 namespace cabac {

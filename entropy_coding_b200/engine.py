@@ -82,6 +82,10 @@ class CabacEngine:
         """0 = auto, 1 = fused lockstep kernel, 2 = two-stage (stage P + stage D)."""
         self._check(self.lib.cabac_set_encoder_mode(self.h, int(mode)))
 
+    def set_decoder_mode(self, mode: int):
+        """0 = auto, 1 = lockstep (one warp per substream), 2 = one thread per substream."""
+        self._check(self.lib.cabac_set_decoder_mode(self.h, int(mode)))
+
     def sync(self):
         self._check(self.lib.cabac_sync(self.h))
 

@@ -188,6 +188,13 @@ enum {
                               (DESIGN.md section 4).  AUTO picks it below 2 048 substreams of >= 256 TUs. */
 };
 int cabac_set_encoder_mode(cabac_handle *h, int mode);
+/* Residual decoder variant.  LOCKSTEP = one warp per substream, all lanes run the same arithmetic decoder
+ * and share the parallel parts (context templates, signs).  THREAD = one thread per substream with its
+ * context models in a global-memory row.  Identical results.  AUTO = LOCKSTEP at every batch size: on
+ * B200 the thread kernel issues 4.8x fewer warp instructions but diverges to 7.4 active lanes and is
+ * 1.2x slower at 10^5 substreams (profiles/r2_decoder_modes.md).  CABAC_B200_DECODER=lockstep|thread. */
+enum { CABAC_DECODER_AUTO = 0, CABAC_DECODER_LOCKSTEP = 1, CABAC_DECODER_THREAD = 2 };
+int cabac_set_decoder_mode(cabac_handle *h, int mode);
 const char *cabac_last_error(cabac_handle *h);
 const char *cabac_version(void);
 /* Number of kernel launches issued through this handle so far.              */

@@ -907,3 +907,51 @@ def test_sliced_encoder_long_substreams(engine, oracle):
     d = engine.decode_residual(np.concatenate([r0["out"][int(capb[i]):int(capb[i]) + int(r0["sizes"][i])] for i in range(2)]),
                                offsets_of(r0["sizes"]), slices.tus, slices.tu_offsets, slices.params, slices.coeffs.size)
     assert (d["coeffs"] == slices.coeffs).all()
+
+
+@pytest.mark.parametrize("seed,flags,kw", [
+    (901, None, {"ts_fraction": 0.25, "bdpcm_fraction": 0.05, "sbt_fraction": 0.05}),
+    (902, T | SUB_DEP_QUANT | SUB_SIGN_HIDING, {"ts_fraction": 0.3}),
+    (903, T | SUB_DEP_QUANT | SUB_TSRC_DISABLED, {"ts_fraction": 0.4}),
+    (904, T, {"preset": "qp0", "tus_per_sub": (1, 3)}),
+])
+def test_thread_decoder_matches_lockstep_and_oracle(engine, oracle, seed, flags, kw):
+    """CABAC_DECODER_THREAD (one thread per substream, contexts in a global row): levels, bin counts, bits read,
+    TU flags, final contexts and status words equal the lockstep decoder's; a sample against the oracle; int16
+    slabs; a truncated substream reports the same status."""
+    wl = W.random_substreams(300, seed, flags=flags, **kw)
+    r = engine.encode_residual_packed(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, wl.out_capacity(bytes_per_coeff=5.0))
+    ent = r["entry_points"]
+    res = {}
+    for mode in (1, 2):
+        engine.set_decoder_mode(mode)
+        try:
+            res[mode] = engine.decode_residual(r["packed"], ent, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size,
+                                               want_ctx=True)
+            res[mode, 16] = engine.decode_residual(r["packed"], ent, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size,
+                                                   i16=True)
+        finally:
+            engine.set_decoder_mode(0)
+    a, b = res[1], res[2]
+    for k in ("coeffs", "num_bins", "bits_read", "tu_flags", "status"):
+        assert (a[k] == b[k]).all(), k
+    assert (a["ctx_out"] == b["ctx_out"]).all() and (b["num_bins"] == r["num_bins"]).all()
+    assert (res[2, 16]["coeffs"].astype(np.int32) == b["coeffs"]).all()
+    for i in range(0, wl.n_sub, 29):
+        t0, t1, lo, hi = sub_range(wl, i)
+        p = wl.params[i]
+        od = oracle.decode_residual(r["packed"][int(ent[i]):int(ent[i + 1])], wl.tus[t0:t1], wl.coeffs.size, int(p["qp"]),
+                                    int(p["init_id"]), int(p["flags"]))
+        assert (od[0][lo:hi] == b["coeffs"][lo:hi]).all() and od[1] == int(b["bits_read"][i])
+    # every substream cut to half its bytes: same status words from both kernels
+    cut = np.concatenate([[0], np.cumsum((np.diff(ent) + 1) // 2)]).astype(np.uint64)
+    half = np.concatenate([r["packed"][int(ent[i]):int(ent[i]) + int(cut[i + 1] - cut[i])] for i in range(wl.n_sub)])
+    st = {}
+    for mode in (1, 2):
+        engine.set_decoder_mode(mode)
+        try:
+            st[mode] = engine.decode_residual(half, cut, wl.tus, wl.tu_offsets, wl.params, wl.coeffs.size,
+                                              raise_on_status=False)["status"]
+        finally:
+            engine.set_decoder_mode(0)
+    assert (st[1] == st[2]).all() and st[2].any()
