@@ -42,6 +42,7 @@ _SIGS = {
     "cabac_encode_residual_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_decode_residual": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
     "cabac_decode_residual_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
+    "cabac_decode_residual_static_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_estimate_residual_bits": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_estimate_residual_bits_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_residual_ctx_bins": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _P, _P]),

@@ -356,10 +356,11 @@ cabac_handle *cabac_create(int device) {
   h->device = device;
   DeviceGuard g(device);
   if (cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking) != cudaSuccess ||
-      cabac::uploadRom() != cudaSuccess) {
+      cabac::uploadRom() != cudaSuccess || cabac::setupStaticScratch(device) != cudaSuccess) {
     delete h;
     return nullptr;
   }
+  h->err.reserve(256);  // error texts of the allocation-free entry point fit without a heap call
   h->stream = h->ownStream;
   if (const char *c = getenv("CABAC_B200_PIPE_CHUNKS")) {  // 1 disables the chunked copy/compute pipeline
     const int v = atoi(c);
@@ -647,6 +648,37 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
                                  coeffs, num_bins, bits_read, tu_flags, ctx_out, status),
      "decode_residual_kernel");
   h->launches += n_sub ? cabac::kLaunchesPerCodingCall + (sc.threadDecode ? 1 : 0) : 0;
+  return CABAC_OK;
+}
+
+int cabac_decode_residual_static_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                                     const cabac_tu_desc *tus, const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
+                                     int32_t *coeffs, uint32_t *num_bins, uint32_t *bits_read, uint8_t *tu_flags,
+                                     cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h) return CABAC_ERR_ARG;
+  if (n_sub && (!in || !in_offsets || !tu_offsets || !params || !coeffs)) {
+    h->err.assign("bad argument: cabac_decode_residual_static_dev");
+    return CABAC_ERR_ARG;
+  }
+  if (n_sub > size_t(CABAC_STATIC_MAX_SUBSTREAMS)) {
+    char msg[160];
+    snprintf(msg, sizeof(msg),
+             "cabac_decode_residual_static_dev: n_sub %zu exceeds CABAC_STATIC_MAX_SUBSTREAMS (%d); split the batch or "
+             "use cabac_decode_residual_dev",
+             n_sub, CABAC_STATIC_MAX_SUBSTREAMS);
+    h->err.assign(msg);
+    return CABAC_ERR_ARG;
+  }
+  DeviceGuard g(h->device);
+  cudaError_t e = cabac::launchDecodeResidualStatic(h->stream, h->device, in, in_offsets, tus, tu_offsets, params, n_sub,
+                                                    ctx_in, coeffs, num_bins, bits_read, tu_flags, ctx_out, status);
+  if (e != cudaSuccess) {
+    h->err.assign("decode_residual_thread_kernel (static scratch): ");
+    h->err.append(cudaGetErrorString(e));
+    return CABAC_ERR_CUDA;
+  }
+  h->launches += n_sub ? 2 : 0;
   return CABAC_OK;
 }
 

@@ -2044,6 +2044,56 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
 }
 
 // ---------------------------------------------------------------------------
+// Allocation-free residual decode (cabac_decode_residual_static_dev; no counterpart in the reference).
+// The thread-per-substream decoder with its context rows in a file-scope device array instead of a cudaMalloc'd
+// buffer: nothing is allocated per call, so the call is legal where cudaMalloc is not. Every GPU that loads the
+// library holds the array (kStaticMaxSubstreams x 230 words = 14.4 MiB) until exit. All calls share it: the kernel
+// rewrites a substream's whole row before the first bin, so stale contents never matter, but two calls that overlap
+// on the GPU (different streams) race on the rows.
+// ---------------------------------------------------------------------------
+constexpr size_t kStaticMaxSubstreams = CABAC_STATIC_MAX_SUBSTREAMS;
+static __device__ __align__(256) uint32_t g_staticCtxRows[kStaticMaxSubstreams * RCTX];
+
+// In host code `g_staticCtxRows` is only a handle for the symbol, not a device address: the address is looked up once
+// per device (with that device current) and kept here.
+constexpr int kMaxDevices = 64;
+static uint32_t *s_staticCtxRows[kMaxDevices] = {};
+
+cudaError_t setupStaticScratch(int device) {
+  if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+  if (s_staticCtxRows[device]) return cudaSuccess;
+  void *p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_staticCtxRows);
+  if (e != cudaSuccess) return e;
+  if (!p) return cudaErrorInvalidSymbol;
+  // Load the two kernels now (lazy module loading would otherwise do it, and allocate, inside the first call).
+  cudaFuncAttributes fa;
+  e = cudaFuncGetAttributes(&fa, td_zero_blocks_kernel<int32_t>);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncGetAttributes(&fa, decode_residual_thread_kernel<int32_t, 1>);
+  if (e != cudaSuccess) return e;
+  s_staticCtxRows[device] = static_cast<uint32_t *>(p);
+  return cudaSuccess;
+}
+
+cudaError_t launchDecodeResidualStatic(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+                                       const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                       const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
+                                       int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
+                                       cabac_ctx_model *ctxOut, uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  if (nSub > kStaticMaxSubstreams || device < 0 || device >= kMaxDevices) return cudaErrorInvalidValue;
+  uint32_t *rows = s_staticCtxRows[device];
+  if (!rows) return cudaErrorNotReady;  // setupStaticScratch did not run on this device
+  const unsigned zb = unsigned(std::min<size_t>(nSub * 4 + 1, size_t(148) * 32));
+  td_zero_blocks_kernel<int32_t><<<zb, 256, 0, s>>>(tus, tuOffsets, nSub, coeffs);
+  decode_residual_thread_kernel<int32_t, 1><<<unsigned((nSub + 31) / 32), 32, 0, s>>>(
+      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status, nullptr,
+      rows);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // Coefficient range [lo, hi) (TCoeff units) the TUs of each chunk of substreams touch:
 // lets the host-pointer entry points stream the slab over PCIe chunk by chunk while earlier
 // chunks are already being coded.  ranges[2k] = lo, ranges[2k+1] = hi; pre-set to ~0 / 0.

@@ -89,6 +89,13 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
                                  const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                                  int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
                                  cabac_ctx_model *ctxOut, uint32_t *status);
+// Allocation-free variant (context rows in a file-scope device array; cabac_kernels.cu).
+cudaError_t setupStaticScratch(int device);  // once per device, with that device current
+cudaError_t launchDecodeResidualStatic(cudaStream_t s, int device, const uint8_t *in, const uint64_t *inOffsets,
+                                       const cabac_tu_desc *tus, const uint64_t *tuOffsets,
+                                       const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
+                                       int32_t *coeffs, uint32_t *numBins, uint32_t *bitsRead, uint8_t *tuFlags,
+                                       cabac_ctx_model *ctxOut, uint32_t *status);
 // per-chunk coefficient ranges: chunk k = substreams [chunkStart[k], chunkStart[k+1]); device pointers
 cudaError_t launchCoeffRanges(cudaStream_t s, const cabac_tu_desc *tus, const uint64_t *tuOffsets,
                               const uint32_t *chunkStart, int nChunks, uint64_t *ranges,

@@ -462,6 +462,15 @@ class CabacEngine:
                                                        _dp(params), n_sub, _dp(ctx_in), _dp(coeffs), _dp(num_bins),
                                                        _dp(bits_read), _dp(tu_flags), _dp(ctx_out), _dp(status)))
 
+    def decode_residual_static_dev(self, data, in_offsets, tus, tu_offsets, params, n_sub, coeffs, num_bins=None,
+                                   bits_read=None, tu_flags=None, ctx_in=None, ctx_out=None, status=None):
+        """cabac_decode_residual_static_dev: the same call without any allocation (context rows in a static device
+        array, at most types.STATIC_MAX_SUBSTREAMS substreams; calls that overlap on the GPU race)."""
+        self._check(self.lib.cabac_decode_residual_static_dev(self.h, _dp(data), _dp(in_offsets), _dp(tus),
+                                                              _dp(tu_offsets), _dp(params), n_sub, _dp(ctx_in),
+                                                              _dp(coeffs), _dp(num_bins), _dp(bits_read), _dp(tu_flags),
+                                                              _dp(ctx_out), _dp(status)))
+
     def encode_bins_dev(self, cmds, cmd_offsets, params, n_sub, out, out_offsets, out_sizes, num_bins=None,
                         ctx_in=None, ctx_out=None, status=None):
         self._check(self.lib.cabac_encode_bins_dev(self.h, _dp(cmds), _dp(cmd_offsets), _dp(params), n_sub,

@@ -374,6 +374,32 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in,
                               uint32_t *bits_read, uint8_t *tu_flags,
                               cabac_ctx_model *ctx_out, uint32_t *status);
 
+/* Allocation-free residual decode.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, meaning and results as cabac_decode_residual_dev (all
+ * pointers are device pointers); runs the thread-per-substream kernel with its
+ * per-substream context rows in a static device array of
+ * CABAC_STATIC_MAX_SUBSTREAMS x 230 words (14.4 MiB, held by every GPU that
+ * loads the library until the process exits) and calls no cudaMalloc /
+ * cudaFree / allocating routine.  n_sub > CABAC_STATIC_MAX_SUBSTREAMS is
+ * refused with CABAC_ERR_ARG (cabac_last_error says so).  The array is shared
+ * by every call and every handle on the device: a call rewrites the rows it
+ * uses before reading them, so nothing has to be cleared between calls, but
+ * two calls whose kernels overlap on the GPU (different streams) race.       */
+#define CABAC_STATIC_MAX_SUBSTREAMS 16384
+int cabac_decode_residual_static_dev(cabac_handle *h, const uint8_t *in,
+                                     const uint64_t *in_offsets,
+                                     const cabac_tu_desc *tus,
+                                     const uint64_t *tu_offsets,
+                                     const cabac_substream_params *params,
+                                     size_t n_sub,
+                                     const cabac_ctx_model *ctx_in,
+                                     int32_t *coeffs, uint32_t *num_bins,
+                                     uint32_t *bits_read, uint8_t *tu_flags,
+                                     cabac_ctx_model *ctx_out,
+                                     uint32_t *status);
+
 /* ---- int16 coefficient slabs ----------------------------------------------- */
 /* The residual calls with the coefficient slab as int16 instead of the reference's
  * int32 TCoeff (unit.hpp:551).  VVC v1 levels fit 16 bits (maxLog2TrDynamicRange =
