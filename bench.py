@@ -460,6 +460,12 @@ def leg_slices(args, r, d_tus, d_co, d_out, d_packed, d_dec):
            "gpu_launches": int(eng.launch_count - l0),
            "note": "few, long substreams: one serial chain per slice; decode has no intra-substream parallelism "
                    "(every bin selects the next context), so its figure is the latency floor of 64 chains",
+           "decode_cycles_per_bin": t_dec * 1e-3 * _sm_mhz(r) * 1e6 / (bins / max(1, n_sub)),
+           "decode_chain": "one warp per slice walks its bins one after another: decode_cycles_per_bin SM clocks per bin "
+                           "(41 dependent warp instructions at ~5 clocks); a thread-per-slice kernel is slower still "
+                           "(64 scalar instructions per bin, 418 vs 576 Mbins/s, profiles/r2_decoder_modes.md); a 3+ GHz "
+                           "out-of-order CPU core does a bin in ~70 clocks, so 64 chains cannot beat 16 such cores - "
+                           "throughput comes from more slices in flight (the headline batch, decode_sweep)",
            "verified": "decode(encode(x)) == x, equal bin counts"}
     if r["rank"] == 0 and not args.no_cpu_baseline:
         chk, kind = cpu_checker()
@@ -840,6 +846,22 @@ def main():
                              "frac": a / b, "issue_active_pct_ncu": f.get("issue_active_pct"),
                              "shared_bank_conflicts_ncu": f.get("shared_bank_conflicts"),
                              "dram_bytes_ncu": f.get("dram_bytes_per_launch")}
+    for k, v in per_kernel.items():
+        tpw = facts.get(k, {}).get("thread_inst_per_warp_inst")
+        if tpw:
+            tib = v["warp_instr_per_bin"] * tpw
+            lane_bound = 148 * 128 * sm_mhz * 1e6 / tib / 1e6
+            v.update({"thread_inst_per_warp_inst": tpw, "thread_instr_per_bin": tib, "lane_mbins_s_bound": lane_bound,
+                      "lane_frac": v["mbins_s_achieved"] / lane_bound})
+    if dom in per_kernel and "lane_frac" in per_kernel[dom]:
+        issue.update({"lane_frac": per_kernel[dom]["lane_frac"], "lane_mbins_s_bound": per_kernel[dom]["lane_mbins_s_bound"],
+                      "thread_instr_per_bin": per_kernel[dom]["thread_instr_per_bin"]})
+    issue["definitions"] = ("frac = achieved / (148 SMs x 4 warp-issue slots x clock / warp-instructions per bin); lane_frac = "
+                            "achieved / (148 x 128 lanes x clock / thread-instructions per bin): the first says how busy the "
+                            "issue ports are with THIS instruction stream, the second counts the lanes as well - it equals "
+                            "frac because the lockstep kernels run 25-31 of 32 lanes on every instruction, most of them "
+                            "repeating the same serial arithmetic (profiles/r2_decoder_modes.md: one thread per substream "
+                            "needs 4.8x fewer warp instructions but runs 7.4 lanes wide)")
     issue["kernels"] = per_kernel
     issue["source"] = "instructions per bin, issue activity, bank conflicts and DRAM bytes: profiles/kernel_facts.json (ncu)"
     line = {
@@ -852,7 +874,10 @@ def main():
                    "tus_per_gpu": r["n_tu"], "coeff_positions_per_gpu": r["n_co"],
                    "bins_per_step_per_gpu": 2 * r["enc_bins"], "bitstream_bytes_per_gpu": r["out_bytes"],
                    "l2": "inputs larger than L2 (coefficient slab %.0f MB per pass)" % (4 * r["n_co"] / 1e6),
-                   "step": "encode_residual + pack + decode_residual"},
+                   "step": "encode_residual + pack + decode_residual",
+                   "sample": "the whole batch every step (the reference arm codes a bounded sample of the same batch per "
+                             "step - its `config.sample` names the frames; both lines are bins per second, so the ratio "
+                             "compares like with like)"},
         "encode_mbins_s": r["enc_bins"] / (tk["encode_residual_kernel"] + tk["pack"]) / 1e3,
         "decode_mbins_s": r["enc_bins"] / tk["decode_residual_kernel"] / 1e3,
         "output_mb_s": r["out_bytes"] / (tk["encode_residual_kernel"] + tk["pack"]) / 1e3,

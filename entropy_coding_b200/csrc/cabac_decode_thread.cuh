@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(256) td_zero_blocks_kernel(const cabac_tu_desc
   const size_t warp = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const size_t nWarps = (size_t(gridDim.x) * blockDim.x) >> 5;
   for (size_t t = tuOffsets[0] + warp; t < nTu; t += nWarps) {
-    const cabac_tu_desc d = tus[t];
+    const cabac_tu_desc d = loadDesc(tus + t);
     T *dst = coeffs + d.coeff_offset;
     const int n = 1 << (d.log2_w + d.log2_h);
     for (int i = lane; i < n; i += 32) dst[i] = T(0);
@@ -362,8 +362,14 @@ decode_residual_thread_kernel(const uint8_t *__restrict__ in, const uint64_t *__
                               uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
                               uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                               uint32_t *__restrict__ status, const uint32_t *__restrict__ order,
-                              uint32_t *__restrict__ ctxRows) {
-  const size_t slot = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+                              uint32_t *__restrict__ ctxRows, int spread) {
+  // spread: one substream per WARP (lane 0 works) - few, long substreams are latency-bound, every chain gets a
+  // scheduler slot of its own instead of sharing a warp's instruction stream with 31 diverged neighbours
+  size_t slot = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (spread) {
+    if (threadIdx.x & 31) return;
+    slot >>= 5;
+  }
   if (slot >= nSub) return;
   const size_t sub = order ? size_t(order[slot]) : slot;
   const cabac_substream_params p = params[sub];
@@ -381,7 +387,8 @@ decode_residual_thread_kernel(const uint8_t *__restrict__ in, const uint64_t *__
   dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
   const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
   for (uint64_t t = t0; t < t1; t++) {
-    const cabac_tu_desc d = tus[t];
+    const cabac_tu_desc d = loadDesc(tus + t);
+    if (d.flags & DESC_CLAMPED) dec.status |= CABAC_SS_BAD_DESC;
     const TuGeom g = makeGeom(d);
     TdBlock<T> blk;
     blk.p = coeffs + d.coeff_offset;

@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) cost_decode_kernel(const uint64_t *__rest
     __syncthreads();
     uint32_t fixed = 0;
     for (uint64_t t = tuOffsets[s] + threadIdx.x, te = tuOffsets[s + 1]; t < te; t += blockDim.x) {
-      const cabac_tu_desc d = tus[t];
+      const cabac_tu_desc d = loadDesc(tus + t);
       fixed += tuConst + ((1u << (d.log2_w + d.log2_h)) >> areaShift);
     }
     fixed = __reduce_add_sync(FULL, fixed);
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) cost_coeff_kernel(const cabac_tu_desc *__
     for (uint64_t base = t0 + uint64_t(wib) * 32u; base < te; base += uint64_t(blockDim.x)) {
       const bool have = base + uint64_t(lane) < te;
       cabac_tu_desc dl = {};
-      if (have) dl = tus[base + uint64_t(lane)];
+      if (have) dl = loadDesc(tus + base + uint64_t(lane));
       const uint32_t area = have ? 1u << (dl.log2_w + dl.log2_h) : 0u;
       const bool sampled = have && sampling && ((base + uint64_t(lane) - t0) & uint64_t(sampleMask)) == 0;
       if (have) {
@@ -1042,7 +1042,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
     auto blockPtr = [&](uint64_t ofs) {
       return c16 ? reinterpret_cast<const int32_t *>(reinterpret_cast<const int16_t *>(coeffs) + ofs) : coeffs + ofs;
     };
-    if (t < t1) prefetchBlock(sm.raw, blockPtr(tus[t].coeff_offset), tus[t], lane, c16);
+    if (t < t1) prefetchBlock(sm.raw, blockPtr(tus[t].coeff_offset), loadDesc(tus + t), lane, c16);
     // WPP: the contexts after this substream's first CTU go to its snapshot row for the row below
     bool wppPending = wpp.sync != nullptr;
     const uint64_t tSync = wppPending ? t + wpp.sync[sub].sync_tus : 0;
@@ -1070,7 +1070,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
       if (!inTu) {
         if (wppPending && t >= tSync) wppSnapshot();  // every word of the TUs before t is resolved here
         if (t == t1) break;
-        d = tus[t];
+        d = loadDesc(tus + t);
+        if (d.flags & DESC_CLAMPED) st |= CABAC_SS_BAD_DESC;
         if (geomKey(d) != gKey) {
           g = makeGeom(d);
           gKey = geomKey(d);
@@ -1081,7 +1082,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
         res = ts ? CABAC_TUR_TS : 0;
         if (!takeBlock(sm.tile, sm.raw, g, lane, c16)) st |= CABAC_SS_COEFF_RANGE;
         if (t + 1 < t1) {
-          const cabac_tu_desc dn = tus[t + 1];
+          const cabac_tu_desc dn = loadDesc(tus + t + 1);
           prefetchBlock(sm.raw, blockPtr(dn.coeff_offset), dn, lane, c16);
         }
         // ---- pre-scan: non-zero mask per coefficient group, last position ----
@@ -1359,7 +1360,8 @@ produce_kernel(const uint32_t *__restrict__ rawCmds, const uint64_t *__restrict_
         } else if (t == t1) {
           break;
         }
-        d = tus[t];
+        d = loadDesc(tus + t);
+        if (d.flags & DESC_CLAMPED) st |= CABAC_SS_BAD_DESC;
         if (geomKey(d) != gKey) {
           g = makeGeom(d);
           gKey = geomKey(d);
@@ -1606,7 +1608,8 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
         wppPublish(wpp, sub, lane);
         wppPending = false;
       }
-      const cabac_tu_desc d = tus[t];
+      const cabac_tu_desc d = loadDesc(tus + t);
+      if (d.flags & DESC_CLAMPED) dec.status |= CABAC_SS_BAD_DESC;
       const TuGeom g = makeGeom(d);
       const int n = g.tw * g.th;
       for (int i = lane; i < n; i += 32) sm.tile[i] = 0;
@@ -2021,12 +2024,14 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
     // (100 000 substreams: 139 ms at 128 threads, 116 at 64, 111 at 32; profiles/r2_decoder_modes.md). Dev knobs.
     static const int tdBlock = getenv("CABAC_B200_TD_BLOCK") ? atoi(getenv("CABAC_B200_TD_BLOCK")) : 32;
     static const int tdDense = getenv("CABAC_B200_TD_DENSE") ? atoi(getenv("CABAC_B200_TD_DENSE")) : 0;
-    const unsigned bs = unsigned(tdBlock >= 32 && tdBlock <= 128 ? tdBlock & ~31 : 32);
-    const unsigned grid = unsigned((nSub + bs - 1) / bs);
+    static const long tdSpreadMax = getenv("CABAC_B200_TD_SPREAD_MAX") ? atol(getenv("CABAC_B200_TD_SPREAD_MAX")) : 2048;
+    const int spread = nSub <= size_t(tdSpreadMax) ? 1 : 0;
+    const unsigned bs = spread ? 32u : unsigned(tdBlock >= 32 && tdBlock <= 128 ? tdBlock & ~31 : 32);
+    const unsigned grid = spread ? unsigned(nSub) : unsigned((nSub + bs - 1) / bs);
 #define TD_LAUNCH(T, MINB)                                                                                              \
   decode_residual_thread_kernel<T, MINB><<<grid, bs, 0, s>>>(in, inOffsets, tus, tuOffsets, params, nSub, ctxIn,        \
                                                              reinterpret_cast<T *>(coeffs), numBins, bitsRead, tuFlags, \
-                                                             ctxOut, status, sc.order, sc.threadCtx)
+                                                             ctxOut, status, sc.order, sc.threadCtx, spread)
     if (sc.coeff16) {
       td_zero_blocks_kernel<int16_t><<<zb, 256, 0, s>>>(tus, tuOffsets, nSub, reinterpret_cast<int16_t *>(coeffs));
       if (tdDense) TD_LAUNCH(int16_t, 8); else TD_LAUNCH(int16_t, 1);
@@ -2089,7 +2094,7 @@ cudaError_t launchDecodeResidualStatic(cudaStream_t s, int device, const uint8_t
   td_zero_blocks_kernel<int32_t><<<zb, 256, 0, s>>>(tus, tuOffsets, nSub, coeffs);
   decode_residual_thread_kernel<int32_t, 1><<<unsigned((nSub + 31) / 32), 32, 0, s>>>(
       in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status, nullptr,
-      rows);
+      rows, 0);
   return cudaGetLastError();
 }
 
@@ -2107,7 +2112,7 @@ __global__ void __launch_bounds__(256) coeff_range_kernel(const cabac_tu_desc *_
   const uint64_t t0 = tuOffsets[chunkStart[k]], t1 = tuOffsets[chunkStart[k + 1]];
   unsigned long long lo = ~0ull, hi = 0, sum = 0;
   for (uint64_t t = t0 + blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; t < t1; t += uint64_t(gridDim.x) * blockDim.x) {
-    const cabac_tu_desc d = tus[t];
+    const cabac_tu_desc d = loadDesc(tus + t);
     const unsigned long long a = d.coeff_offset, b = a + (1ull << (d.log2_w + d.log2_h));
     lo = a < lo ? a : lo;
     hi = b > hi ? b : hi;

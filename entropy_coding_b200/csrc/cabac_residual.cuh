@@ -91,6 +91,24 @@ struct TuGeom {
   bool sbtZero;
 };
 
+// A descriptor the reference would CHECK() away (a block side above 64 samples, a component above Cr) must not
+// turn into wild shared-memory indices: every kernel reads descriptors through loadDesc, which clamps the geometry
+// into range; the coding kernels report CABAC_SS_BAD_DESC for the substream (its output is then meaningless).
+__device__ __forceinline__ bool descBad(const cabac_tu_desc &d) {
+  return d.log2_w > 6 || d.log2_h > 6 || d.comp_id > 2;
+}
+__device__ __forceinline__ cabac_tu_desc loadDesc(const cabac_tu_desc *__restrict__ p) {
+  cabac_tu_desc d = *p;
+  if (descBad(d)) {
+    d.log2_w = d.log2_w > 6 ? 6 : d.log2_w;
+    d.log2_h = d.log2_h > 6 ? 6 : d.log2_h;
+    d.comp_id = d.comp_id > 2 ? 2 : d.comp_id;
+    d.flags |= 0x80;  // CABAC_TU_* uses bits 0-4; bit 7 marks the clamped copy inside the kernels
+  }
+  return d;
+}
+constexpr uint8_t DESC_CLAMPED = 0x80;
+
 __device__ inline TuGeom makeGeom(const cabac_tu_desc &d) {
   TuGeom g;
   g.log2w = d.log2_w;

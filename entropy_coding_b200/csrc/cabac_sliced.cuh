@@ -94,7 +94,7 @@ static cudaError_t launchScan(cudaStream_t s, const uint32_t *in, size_t n, uint
 __global__ void __launch_bounds__(256) sl_capacity_kernel(const cabac_tu_desc *__restrict__ tus, size_t nTu,
                                                           uint32_t *__restrict__ cap) {
   for (size_t t = blockIdx.x * size_t(blockDim.x) + threadIdx.x; t < nTu; t += size_t(gridDim.x) * blockDim.x)
-    cap[t] = tuCmdCapacity(tus[t]);
+    cap[t] = tuCmdCapacity(loadDesc(tus + t));
 }
 
 // ---------------------------------------------------------------------------
@@ -131,12 +131,12 @@ sl_produce_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restr
     const cabac_substream_params p = params[sub];
     const bool depQuant = (p.flags & CABAC_SUB_DEP_QUANT) != 0;
     const bool signHiding = (p.flags & CABAC_SUB_SIGN_HIDING) != 0;
-    const cabac_tu_desc d = tus[t];
+    const cabac_tu_desc d = loadDesc(tus + t);
     const TuGeom g = makeGeom(d);
     const bool ts = (d.flags & CABAC_TU_TS) != 0;
     const bool tsPath = ts && !(p.flags & CABAC_SUB_TSRC_DISABLED);
     const bool bdpcm = (d.flags & CABAC_TU_BDPCM) != 0;
-    uint32_t res = ts ? CABAC_TUR_TS : 0, st = 0;
+    uint32_t res = ts ? CABAC_TUR_TS : 0, st = (d.flags & DESC_CLAMPED) ? uint32_t(CABAC_SS_BAD_DESC) : 0u;
     uint32_t *dst = words + wordOff[t];
     uint32_t cnt = 0;
     if (!loadTile(sm.tile, c16 ? reinterpret_cast<const int32_t *>(reinterpret_cast<const int16_t *>(coeffs) + d.coeff_offset)

@@ -18,6 +18,7 @@ OK, ERR_CUDA, ERR_ARG, ERR_SUBSTREAM = 0, -1, -2, -3
 # per-substream status bits
 SS_OUT_OVERFLOW, SS_EMPTY_TU, SS_BAD_CMD, SS_IN_OVERRUN, SS_COEFF_RANGE, SS_NO_TERMINATE = 1, 2, 4, 8, 16, 32
 SS_WPP_TIMEOUT = 64
+SS_BAD_DESC = 128
 STATIC_MAX_SUBSTREAMS = 16384  # CABAC_STATIC_MAX_SUBSTREAMS (cabac_decode_residual_static_dev)
 # substream flags
 SUB_DEP_QUANT, SUB_SIGN_HIDING, SUB_TSRC_DISABLED = 1, 2, 4

@@ -57,8 +57,13 @@ enum {
                                 cabac_reader.cpp:2942-2946                   */
   CABAC_SS_NO_TERMINATE = 32, /* terminating bin / stop pattern missing,
                                 arith_codec.cpp:68-73                        */
-  CABAC_SS_WPP_TIMEOUT = 64  /* cabac_*_wpp: the predecessor never published
+  CABAC_SS_WPP_TIMEOUT = 64, /* cabac_*_wpp: the predecessor never published
                                 its contexts (malformed dep chain)           */
+  CABAC_SS_BAD_DESC = 128    /* a cabac_tu_desc with log2_w / log2_h > 6 or
+                                comp_id > 2 (the reference CHECKs the block
+                                size, context_modelling.cpp:7-79); the block
+                                was coded with the fields clamped into range,
+                                so the substream's output is not meaningful   */
 };
 
 /* ---- probability model as exchanged over the boundary ------------------- */

@@ -955,3 +955,48 @@ def test_thread_decoder_matches_lockstep_and_oracle(engine, oracle, seed, flags,
         finally:
             engine.set_decoder_mode(0)
     assert (st[1] == st[2]).all() and st[2].any()
+
+
+def test_malformed_descriptors_are_flagged_not_followed(engine):
+    """A cabac_tu_desc outside the legal geometry (side > 64 samples, component > Cr: the reference CHECKs both) sets
+    CABAC_SS_BAD_DESC on its substream in every kernel; the kernels clamp the fields instead of indexing with them,
+    and every other substream of the batch codes exactly as in the clean batch."""
+    from entropy_coding_b200.types import SS_BAD_DESC
+    wl = W.random_substreams(60, seed=888, flags=T | SUB_DEP_QUANT, tus_per_sub=(3, 9), ts_fraction=0.2)
+    cap = wl.out_capacity(bytes_per_coeff=5.0)
+    clean = engine.encode_residual(wl.tus, wl.tu_offsets, wl.params, wl.coeffs, cap)
+    clean_outs = split(clean["out"], cap, clean["sizes"])
+    tus = wl.tus.copy()
+    bad = {7: ("log2_w", 9), 20: ("comp_id", 5), 33: ("log2_h", 255)}
+    for sub, (field, val) in bad.items():
+        t = int(wl.tu_offsets[sub]) + 1
+        tus[field][t] = val
+        tus["coeff_offset"][t] = wl.coeffs.size  # the clamped (up to 64 x 64) block lives in the padding below
+    slab = np.concatenate([wl.coeffs, np.zeros(1 << 13, np.int32)])
+    good = np.array([i not in bad for i in range(wl.n_sub)])
+    for mode in (0, 1, 2, 3, 4):
+        engine.set_encoder_mode(mode)
+        try:
+            r = engine.encode_residual(tus, wl.tu_offsets, wl.params, slab, cap, raise_on_status=False)
+        finally:
+            engine.set_encoder_mode(0)
+        assert all(int(r["status"][i]) & SS_BAD_DESC for i in bad), mode
+        assert not r["status"][good].any(), mode
+        outs = split(r["out"], cap, r["sizes"])
+        assert all(outs[i].tobytes() == clean_outs[i].tobytes() for i in range(wl.n_sub) if good[i]), mode
+    est = engine.estimate_residual_bits(tus, wl.tu_offsets, wl.params, slab, raise_on_status=False)
+    assert all(int(est["status"][i]) & SS_BAD_DESC for i in bad) and not est["status"][good].any()
+    ioff = offsets_of(clean["sizes"])
+    data = np.concatenate(clean_outs)
+    for mode in (1, 2):
+        engine.set_decoder_mode(mode)
+        try:
+            d = engine.decode_residual(data, ioff, tus, wl.tu_offsets, wl.params, slab.size, raise_on_status=False)
+        finally:
+            engine.set_decoder_mode(0)
+        assert all(int(d["status"][i]) & SS_BAD_DESC for i in bad), mode
+        assert not d["status"][good].any(), mode
+        for i in range(wl.n_sub):
+            if good[i]:
+                a, b, lo, hi = sub_range(wl, i)
+                assert (d["coeffs"][lo:hi] == wl.coeffs[lo:hi]).all(), (mode, i)

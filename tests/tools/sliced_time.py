@@ -33,3 +33,22 @@ for it in range(reps):
     e1.record(st)
     torch.cuda.synchronize()
     print(f"pass {it}: {e0.elapsed_time(e1):.2f} ms, {int(d_bins.sum())} bins, {int(d_bins.sum()) / e0.elapsed_time(e1) / 1e6:.2f} Gbins/s", flush=True)
+# decode of the same slices: lockstep (1) vs thread (2) kernel
+d_pk = torch.empty_like(d_out)
+d_ent = torch.zeros(wl.n_sub + 1, dtype=torch.int64, device=dev)
+eng.pack_dev(d_out, d_cap, d_sizes, wl.n_sub, d_pk, d_ent)
+d_dec = torch.empty_like(d_co)
+d_db = torch.zeros_like(d_bins)
+d_st = torch.zeros_like(d_bins)
+for mode in (1, 2):
+    eng.set_decoder_mode(mode)
+    for it in range(2):
+        d_dec.fill_(0x5a5a5a5a)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        eng.decode_residual_dev(d_pk, d_ent, d_tus, d_off, d_par, wl.n_sub, d_dec, d_db, status=d_st)
+        e1.record(st)
+        torch.cuda.synchronize()
+        ok = bool(torch.equal(d_dec, d_co)) and int(d_st.abs().max()) == 0 and bool(torch.equal(d_db, d_bins))
+        ms = e0.elapsed_time(e1)
+        print(f"decode mode {mode} pass {it}: {ms:.2f} ms, {int(d_db.sum()) / ms / 1e3:.1f} Mbins/s, ok={ok}", flush=True)
