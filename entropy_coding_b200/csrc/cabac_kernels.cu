@@ -1014,6 +1014,7 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
           if (++spins > WS_SPIN_LIMIT) __trap();
         }
         if (spins && lane == 0) wsStore(&chan->want, 0u);
+        __threadfence_block();  // tail observed above; rng[] read by the slice below
         wsDrainSlice(rc, *chan, drained, int(m), lane, wsSingle);
         drained += m;
       }

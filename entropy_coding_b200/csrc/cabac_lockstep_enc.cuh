@@ -825,8 +825,11 @@ struct __align__(16) WsChannel {
   uint32_t pad;
 };
 
-// Head / tail hand-off inside one CTA: shared-memory accesses of a warp are performed in program
-// order, so volatile accesses (no reordering by the compiler) are enough; no fence is needed.
+// Head / tail hand-off inside one CTA: the data words (ring[], rng[]) are plain shared-memory stores, the
+// counters volatile ones.  A __threadfence_block() sits between the data and the counter on both sides
+// (writer: data, fence, counter; reader: counter, fence, data) so the order is what the PTX memory model
+// guarantees, not just what current hardware happens to do; one fence per push / walker round is free at
+// this rate.
 __device__ __forceinline__ uint32_t wsLoad(const uint32_t *p) {
   uint32_t v;
   asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(uint32_t(__cvta_generic_to_shared(p))) : "memory");
@@ -840,12 +843,14 @@ __device__ __forceinline__ void wsStore(uint32_t *p, uint32_t v) {
 __device__ __forceinline__ void wsPush(WsChannel &ch, uint32_t &head, const uint32_t *q, int n, int lane) {
   for (int i = lane; i < n; i += 32) ch.ring[(head + uint32_t(i)) & (WS_RING - 1u)] = q[i];
   head += uint32_t(n);
+  __threadfence_block();
   __syncwarp();
   if (lane == 0) wsStore(&ch.head, head);
 }
 __device__ __forceinline__ void wsPushWord(WsChannel &ch, uint32_t &head, uint32_t w, int lane) {
   if (lane == 0) {
     ch.ring[head & (WS_RING - 1u)] = w;
+    __threadfence_block();
     wsStore(&ch.head, head + 1u);
   }
   head += 1u;
@@ -894,6 +899,7 @@ __device__ __forceinline__ void wsWalk(WsChannel *chans, int lane) {
       continue;
     }
     idle = 0;
+    __threadfence_block();  // head observed above; the ring words below
 #pragma unroll 1
     for (int round = 0; round < WS_WALK_ROUNDS && __any_sync(FULL, avail != 0); round++) {
       uint32_t w[WS_WALK_UNROLL];
@@ -919,6 +925,7 @@ __device__ __forceinline__ void wsWalk(WsChannel *chans, int lane) {
       tail += n;
       avail -= n;
     }
+    __threadfence_block();  // rng[] before the tail that releases it
     if (lane < WS_PRODUCERS) wsStore(&ch.tail, tail);
   }
 }
