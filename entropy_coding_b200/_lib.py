@@ -72,6 +72,8 @@ _SIGS = {
     "cabac_decode_residual_i16_dev": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P, _P]),
     "cabac_encode_residual_packed_i16": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, _P]),
     "cabac_decode_residual_i16": (C.c_int, [_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _P, _P, _P]),
+    "cabac_decode_slices": (C.c_int, [_P, _P, _P, _P, _P, _SZ] + [_P] * 15),
+    "cabac_decode_slices_dev": (C.c_int, [_P, _P, _P, _P, _P, _SZ] + [_P] * 15),
     "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
     "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
 }

@@ -651,6 +651,27 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
   return CABAC_OK;
 }
 
+int cabac_decode_slices_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                            const cabac_substream_params *params, const cabac_slice_params *slice_params, size_t n_sub,
+                            const cabac_ctx_model *ctx_in, const uint64_t *cu_offsets, const uint64_t *tu_offsets,
+                            const uint64_t *ctu_offsets, const uint64_t *coeff_offsets, cabac_cu_desc *cus,
+                            cabac_tu_desc *tus, uint8_t *tu_flags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                            uint32_t *counts, uint32_t *num_bins, uint32_t *bits_read, cabac_ctx_model *ctx_out,
+                            uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !params || !slice_params || !cu_offsets || !tu_offsets || !ctu_offsets ||
+                       !coeff_offsets || !tus || !coeffs)))
+    return badArg(h, "cabac_decode_slices_dev");
+  DeviceGuard g(h->device);
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchDecodeSlices(h->stream, h->device, sc, in, in_offsets, params, slice_params, n_sub, ctx_in, cu_offsets,
+                               tu_offsets, ctu_offsets, coeff_offsets, cus, tus, tu_flags, ctus, coeffs, counts, num_bins,
+                               bits_read, ctx_out, status),
+     "decode_slice_kernel");
+  h->launches += n_sub ? cabac::kLaunchesPerCodingCall : 0;
+  return CABAC_OK;
+}
+
 int cabac_decode_residual_static_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
                                      const cabac_tu_desc *tus, const uint64_t *tu_offsets,
                                      const cabac_substream_params *params, size_t n_sub, const cabac_ctx_model *ctx_in,
@@ -901,6 +922,88 @@ int cabac_decode_bins(cabac_handle *h, const uint8_t *in, const uint64_t *in_off
   std::vector<uint32_t> st(status ? 0 : n_sub);
   uint32_t *hst = status ? status : st.data();
   D2H(hst, dStatus, n_sub * 4);
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                        const cabac_substream_params *params, const cabac_slice_params *slice_params, size_t n_sub,
+                        const cabac_ctx_model *ctx_in, const uint64_t *cu_offsets, const uint64_t *tu_offsets,
+                        const uint64_t *ctu_offsets, const uint64_t *coeff_offsets, cabac_cu_desc *cus,
+                        cabac_tu_desc *tus, uint8_t *tu_flags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                        uint32_t *counts, uint32_t *num_bins, uint32_t *bits_read, cabac_ctx_model *ctx_out,
+                        uint32_t *status) {
+  if (!h || (n_sub && (!in || !in_offsets || !params || !slice_params || !cu_offsets || !tu_offsets || !ctu_offsets ||
+                       !coeff_offsets || !tus || !coeffs || !counts)))
+    return badArg(h, "cabac_decode_slices");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nIn = in_offsets[n_sub], nCu = cu_offsets[n_sub], nTu = tu_offsets[n_sub], nCtu = ctu_offsets[n_sub],
+               nCo = coeff_offsets[n_sub];
+  uint8_t *dIn, *dTuFlags;
+  uint64_t *dInOff, *dCuOff, *dTuOff, *dCtuOff, *dCoOff;
+  cabac_substream_params *dP;
+  cabac_slice_params *dSp;
+  cabac_ctx_model *dCin, *dCout;
+  cabac_cu_desc *dCus;
+  cabac_tu_desc *dTus;
+  cabac_ctu_desc *dCtus;
+  int32_t *dCoeffs;
+  uint32_t *dCounts, *dBins, *dBits, *dStatus;
+  Arena a(h);
+  a.want((void **)&dIn, nIn);
+  a.want((void **)&dInOff, (n_sub + 1) * 8);
+  a.want((void **)&dCuOff, (n_sub + 1) * 8);
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dCtuOff, (n_sub + 1) * 8);
+  a.want((void **)&dCoOff, (n_sub + 1) * 8);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dSp, n_sub * sizeof(*slice_params));
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dCus, cus ? nCu * sizeof(*cus) : 0);
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dCtus, ctus ? nCtu * sizeof(*ctus) : 0);
+  a.want((void **)&dCoeffs, nCo * 4);
+  a.want((void **)&dCounts, n_sub * 12);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dBits, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dIn, in, nIn);
+  H2D(dInOff, in_offsets, (n_sub + 1) * 8);
+  H2D(dCuOff, cu_offsets, (n_sub + 1) * 8);
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dCtuOff, ctu_offsets, (n_sub + 1) * 8);
+  H2D(dCoOff, coeff_offsets, (n_sub + 1) * 8);
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dSp, slice_params, n_sub * sizeof(*slice_params));
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  int rc = cabac_decode_slices_dev(h, dIn, dInOff, dP, dSp, n_sub, ctx_in ? dCin : nullptr, dCuOff, dTuOff, dCtuOff, dCoOff,
+                                   cus ? dCus : nullptr, dTus, dTuFlags, ctus ? dCtus : nullptr, dCoeffs, dCounts, dBins,
+                                   dBits, ctx_out ? dCout : nullptr, dStatus);
+  if (rc) return rc;
+  // the counts decide how much of every region comes back
+  D2H(counts, dCounts, n_sub * 12);
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  D2H(hst, dStatus, n_sub * 4);
+  D2H(num_bins, dBins, n_sub * 4);
+  D2H(bits_read, dBits, n_sub * 4);
+  D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  for (size_t i = 0; i < n_sub; i++) {
+    const size_t cuCap = cu_offsets[i + 1] - cu_offsets[i], tuCap = tu_offsets[i + 1] - tu_offsets[i],
+                 coCap = coeff_offsets[i + 1] - coeff_offsets[i];
+    const size_t nc = std::min<size_t>(counts[3 * i], cuCap), nt = std::min<size_t>(counts[3 * i + 1], tuCap),
+                 nk = std::min<size_t>(counts[3 * i + 2], coCap);
+    if (cus) D2H(cus + cu_offsets[i], dCus + cu_offsets[i], nc * sizeof(*cus));
+    D2H(tus + tu_offsets[i], dTus + tu_offsets[i], nt * sizeof(*tus));
+    if (tu_flags) D2H(tu_flags + tu_offsets[i], dTuFlags + tu_offsets[i], nt);
+    D2H(coeffs + coeff_offsets[i], dCoeffs + coeff_offsets[i], nk * 4);
+  }
+  if (ctus) D2H(ctus, dCtus, nCtu * sizeof(*ctus));
   CK(cudaStreamSynchronize(h->stream), "sync");
   return anySubstreamFailed(hst, n_sub);
 }

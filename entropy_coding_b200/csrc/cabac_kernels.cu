@@ -2456,3 +2456,6 @@ cudaError_t launchPack(cudaStream_t s, int device, const uint8_t *out, const uin
 }
 
 }  // namespace cabac
+
+// K9: whole-substream decoder (CTU-level syntax on the device)
+#include "cabac_slice.cuh"

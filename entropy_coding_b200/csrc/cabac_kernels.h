@@ -48,6 +48,13 @@ cudaError_t launchDecodeBins(cudaStream_t s, int device, const Sched &sc, const 
                              const uint32_t *cmds, const uint64_t *cmdOffsets,
                              const cabac_substream_params *params, size_t nSub, const cabac_ctx_model *ctxIn,
                              uint32_t *values, uint32_t *bitsRead, cabac_ctx_model *ctxOut, uint32_t *status);
+cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
+                               const cabac_substream_params *params, const cabac_slice_params *sliceParams, size_t nSub,
+                               const cabac_ctx_model *ctxIn, const uint64_t *cuOffsets, const uint64_t *tuOffsets,
+                               const uint64_t *ctuOffsets, const uint64_t *coeffOffsets, cabac_cu_desc *cus,
+                               cabac_tu_desc *tus, uint8_t *tuFlags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                               uint32_t *counts, uint32_t *numBins, uint32_t *bitsRead, cabac_ctx_model *ctxOut,
+                               uint32_t *status);
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
                                 const uint64_t *rawOffsets, const cabac_substream_params *params = nullptr,

@@ -1,0 +1,221 @@
+// cabac_slice.cuh - K9: whole-substream decoder (cabac_decode_slices).
+// Included by cabac_kernels.cu after the lockstep residual decoder.
+//
+// One warp per substream (a slice or a tile: an independently initialised and terminated substream,
+// EncSlice.cpp:2046-2054).  The warp runs the CTU-level parser of cabac_syntax.cuh in lockstep: all 32
+// lanes hold the same arithmetic-decoder state and take the same branches, exactly as in
+// decode_residual_kernel; inside residual_coding the lanes split the coefficient group's template work
+// (lsResidualRegular / lsResidualTS).  Per warp in shared memory: all 379 contexts as expanded entries
+// (6 KB; the 230 residual ones first, in the dense order the residual decoder indexes), the 32x32
+// coefficient tile (4 KB), and the neighbour lines of the partitioner contexts (one 16-bit word per 4
+// luma samples of the substream's width, per tree: <= 4 KB for 4096 samples).  Parsing a substream
+// is a dependent chain from the first bin to the last - every bin picks the context of the next - so one
+// substream cannot be spread over more than one warp; the launch is parallel over substreams only and a
+// batch of few, long slices is latency-bound.
+#pragma once
+#include "cabac_syntax.cuh"
+
+namespace cabac {
+
+constexpr int SLICE_WARPS_PER_BLOCK = 2;
+constexpr int SLICE_MAX_LINE = 1024;  // 4096 luma samples
+constexpr int SLICE_MAX_CTU_COLS = 128;
+
+struct __align__(16) SliceWarpSmem {
+  int32_t tile[32 * 32];
+  uint4 ctx[CABAC_NUM_CTX];  // [0, RCTX): residual contexts in rctx() order; [RCTX, 379): the others
+  uint16_t above[2][SLICE_MAX_LINE];
+  uint16_t left[2][32];
+  uint8_t ctuLine[SLICE_MAX_CTU_COLS];
+};
+
+// reference context id -> slot in SliceWarpSmem::ctx
+__host__ __device__ constexpr int sliceCtxSlot(int id) {
+  return id < 86 ? RCTX + id
+                 : id < 292 ? id - 86
+                            : id < 310 ? RCTX + 86 + (id - 292)
+                                       : id < 312 ? 206 + (id - 310) : id < 357 ? RCTX + 104 + (id - 312) : 208 + (id - 357);
+}
+static_assert(sliceCtxSlot(86) == rctx(86) && sliceCtxSlot(291) == rctx(291) && sliceCtxSlot(310) == rctx(310) &&
+                  sliceCtxSlot(357) == rctx(357) && sliceCtxSlot(378) == rctx(378) && sliceCtxSlot(356) == CABAC_NUM_CTX - 1 &&
+                  sliceCtxSlot(0) == RCTX && sliceCtxSlot(292) == RCTX + 86 && sliceCtxSlot(312) == RCTX + 104,
+              "context slot map");
+
+struct SliceResidualRet {
+  LsDecoder dec;
+  uint32_t res;
+};
+
+// residual_coding of one block (cabac_reader.cpp:2647-2735 with ts_flag :2737-2752): the body of
+// decode_residual_kernel's TU loop.  Out of line - the CU parser calls it from four places - with the
+// decoder state passed and returned by value so that it stays in registers on both sides.
+__device__ __noinline__ SliceResidualRet sliceResidual(LsDecoder dec, uint4 *ctx, int32_t *tile, const cabac_tu_desc d,
+                                                       uint32_t subFlags, int32_t *__restrict__ coeffs, int lane) {
+  const TuGeom g = makeGeom(d);
+  const int n = g.tw * g.th;
+  for (int i = lane; i < n; i += 32) tile[i] = 0;
+  __syncwarp();
+  bool ts = (d.flags & CABAC_TU_BDPCM) != 0;
+  if (d.flags & CABAC_TU_TS_ALLOWED) ts = lsDecodeBin(dec, ctx + R_TS_FLAG + (g.comp ? 1 : 0)) != 0;
+  uint32_t res = ts ? CABAC_TUR_TS : 0;
+  if (ts && !(subFlags & CABAC_SUB_TSRC_DISABLED))
+    lsResidualTS(dec, ctx, tile, g, (d.flags & CABAC_TU_BDPCM) != 0, lane);
+  else
+    res |= lsResidualRegular(dec, ctx, tile, g, subFlags, ts, lane);
+  __syncwarp();
+  const int total = g.w * g.h;
+  int32_t *dst = coeffs + d.coeff_offset;
+  for (int i = lane; i < total; i += 32) {
+    const int y = i >> g.log2w, x = i & (g.w - 1);
+    dst[i] = (x < g.tw && y < g.th) ? tile[(y << g.log2tw) + x] : 0;
+  }
+  __syncwarp();
+  SliceResidualRet r;
+  r.dec = dec;
+  r.res = res;
+  return r;
+}
+
+struct SliceEngine {
+  LsDecoder dec;
+  SliceWarpSmem &sm;
+  const int lane;
+  const uint32_t subFlags;
+  cabac_cu_desc *cus;
+  cabac_tu_desc *tus;
+  uint8_t *tuFlags;
+  cabac_ctu_desc *ctus;
+  int32_t *coeffs;
+  bool dead = false;
+
+  __device__ __forceinline__ SliceEngine(SliceWarpSmem &s, int l, uint32_t f, cabac_cu_desc *c, cabac_tu_desc *t,
+                                         uint8_t *tf, cabac_ctu_desc *ct, int32_t *co)
+      : sm(s), lane(l), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
+
+  __device__ __forceinline__ uint32_t bin(int id) { return dec.decodeBin(sm.ctx + sliceCtxSlot(id)); }
+  __device__ __forceinline__ uint32_t ep(int n) { return n <= 16 ? dec.ep(n) : dec.epLong(uint32_t(n)); }
+  __device__ __forceinline__ uint32_t trm() { return dec.decodeBinTrm(); }
+  __device__ __forceinline__ uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
+    const SliceResidualRet r = sliceResidual(dec, sm.ctx, sm.tile, d, subFlags, coeffs, lane);
+    dec = r.dec;
+    if (lane == 0) {
+      cabac_tu_desc o = d;
+      if (r.res & CABAC_TUR_TS) o.flags |= CABAC_TU_TS;
+      tus[idx] = o;
+      if (tuFlags) tuFlags[idx] = uint8_t(r.res);
+    }
+    return r.res;
+  }
+  __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.above[ch]; }
+  __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.left[ch]; }
+  __device__ __forceinline__ uint8_t *ctuLine() { return sm.ctuLine; }
+  __device__ __forceinline__ void ctuLineStore(int col, uint8_t v) {
+    if (lane == 0 && col < SLICE_MAX_CTU_COLS) sm.ctuLine[col] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void fill(uint16_t *p, int n, uint16_t v) {
+    for (int i = lane; i < n; i += 32) p[i] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void putCu(uint32_t i, const cabac_cu_desc &c) {
+    if (lane == 0 && cus) cus[i] = c;
+  }
+  __device__ __forceinline__ void putCtu(uint32_t i, const cabac_ctu_desc &c) {
+    if (lane == 0 && ctus) ctus[i] = c;
+  }
+  __device__ __forceinline__ void abort() { dead = true; }
+  __device__ __forceinline__ bool aborted() const { return dead; }
+};
+
+__global__ void __launch_bounds__(SLICE_WARPS_PER_BLOCK * 32)
+decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
+                    const cabac_substream_params *__restrict__ params,
+                    const cabac_slice_params *__restrict__ sliceParams, size_t nSub,
+                    const cabac_ctx_model *__restrict__ ctxIn, const uint64_t *__restrict__ cuOffsets,
+                    const uint64_t *__restrict__ tuOffsets, const uint64_t *__restrict__ ctuOffsets,
+                    const uint64_t *__restrict__ coeffOffsets, cabac_cu_desc *__restrict__ cus,
+                    cabac_tu_desc *__restrict__ tus, uint8_t *__restrict__ tuFlags, cabac_ctu_desc *__restrict__ ctus,
+                    int32_t *__restrict__ coeffs, uint32_t *__restrict__ counts, uint32_t *__restrict__ numBins,
+                    uint32_t *__restrict__ bitsRead, cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
+                    const uint32_t *__restrict__ order, uint32_t *cursor) {
+  __shared__ SliceWarpSmem smem[SLICE_WARPS_PER_BLOCK];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  SliceWarpSmem &sm = smem[wib];
+  size_t sub;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {
+    const cabac_substream_params p = params[sub];
+    const cabac_slice_params sp = sliceParams[sub];
+    const cabac_ctx_model *src = ((p.flags & CABAC_SUB_CTX_IN) && ctxIn) ? ctxIn + sub * CABAC_NUM_CTX : nullptr;
+    const int qp = clipQp(p.qp);
+    for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+      const uint32_t win = CABAC_CTX_INIT_TABLE[3][id];
+      sm.ctx[sliceCtxSlot(id)] = src ? ctx_entry(src[id].state0, src[id].state1, win)
+                                     : ctx_entry_init(qp, CABAC_CTX_INIT_TABLE[p.init_id][id], win);
+    }
+    __syncwarp();
+    const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub], co0 = coeffOffsets[sub];
+    SliceEngine eng(sm, lane, p.flags, cus ? cus + cu0 : nullptr, tus + tu0, tuFlags ? tuFlags + tu0 : nullptr,
+                    ctus ? ctus + ctu0 : nullptr, coeffs);
+    eng.dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+    cabac_syntax::SliceParser<SliceEngine> ps(eng, sp, uint32_t(cuOffsets[sub + 1] - cu0), uint32_t(tuOffsets[sub + 1] - tu0),
+                                              uint32_t(ctuOffsets[sub + 1] - ctu0), coeffOffsets[sub + 1] - co0, co0);
+    if (((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SLICE_MAX_LINE) ||
+        ((sp.x1 - sp.x0) >> sp.log2_ctu) >= uint32_t(SLICE_MAX_CTU_COLS))
+      ps.status |= CABAC_SS_UNSUPPORTED;
+    else
+      ps.run((p.flags & CABAC_SUB_TERMINATE) != 0);
+    eng.dec.checkOverrun();
+    if (lane == 0) {
+      if (counts) {
+        counts[3 * sub + 0] = ps.nCu;
+        counts[3 * sub + 1] = ps.nTu;
+        counts[3 * sub + 2] = uint32_t(ps.nCoeff);
+      }
+      if (numBins) numBins[sub] = eng.dec.nbins;
+      if (bitsRead) bitsRead[sub] = eng.dec.bitsRead();
+      if (status) status[sub] = eng.dec.status | ps.status;
+    }
+    if (ctxOut) {
+      __syncwarp();
+      cabac_ctx_model *dst = ctxOut + sub * CABAC_NUM_CTX;
+      for (int id = lane; id < CABAC_NUM_CTX; id += 32) {
+        const uint32_t x = sm.ctx[sliceCtxSlot(id)].x;
+        cabac_ctx_model m;
+        m.state0 = uint16_t(x >> 16);
+        m.state1 = uint16_t(x & 0xFFFFu);
+        dst[id] = m;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,
+                               const cabac_substream_params *params, const cabac_slice_params *sliceParams, size_t nSub,
+                               const cabac_ctx_model *ctxIn, const uint64_t *cuOffsets, const uint64_t *tuOffsets,
+                               const uint64_t *ctuOffsets, const uint64_t *coeffOffsets, cabac_cu_desc *cus,
+                               cabac_tu_desc *tus, uint8_t *tuFlags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                               uint32_t *counts, uint32_t *numBins, uint32_t *bitsRead, cabac_ctx_model *ctxOut,
+                               uint32_t *status) {
+  if (nSub == 0) return cudaSuccess;
+  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(inOffsets, nSub, sc.cost);
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
+  int sms = 148, perSm = 1;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  cudaFuncSetAttribute(decode_slice_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, decode_slice_kernel, SLICE_WARPS_PER_BLOCK * 32, 0) !=
+          cudaSuccess ||
+      perSm < 1)
+    perSm = 1;
+  // few substreams: one warp per CTA spreads them over the SMs instead of pairing them
+  const size_t blocksWanted = nSub <= size_t(sms) ? nSub : (nSub + SLICE_WARPS_PER_BLOCK - 1) / SLICE_WARPS_PER_BLOCK;
+  const size_t cap = size_t(sms) * perSm;
+  const int blocks = int(blocksWanted < 1 ? 1 : (blocksWanted > cap ? cap : blocksWanted));
+  decode_slice_kernel<<<blocks, SLICE_WARPS_PER_BLOCK * 32, 0, s>>>(
+      in, inOffsets, params, sliceParams, nSub, ctxIn, cuOffsets, tuOffsets, ctuOffsets, coeffOffsets, cus, tus, tuFlags,
+      ctus, coeffs, counts, numBins, bitsRead, ctxOut, status, sc.order, sc.cursor);
+  return cudaGetLastError();
+}
+
+}  // namespace cabac

@@ -1,0 +1,819 @@
+// cabac_syntax.cuh - the CTU-level syntax of an all-intra, dual-tree VVC substream (SURVEY.md
+// section 8, row f2): coding_tree_unit -> sao / alf -> coding_tree (split_cu_mode with the
+// QTBT partitioner's legality rules) -> coding_unit -> intra modes -> transform_tree ->
+// transform_unit (cbf, cu_qp_delta, joint_cb_cr, residual_coding) -> lfnst / mts.
+//
+// The parser is control flow only: every bin goes through the engine E, which owns the arithmetic
+// decoder, the 379 contexts and the residual decoder.  In the product E is the warp-lockstep device
+// engine of decode_slice_kernel (cabac_kernels.cu): all 32 lanes of a warp run this code on the
+// same values (warp-uniform control flow) and take part in every bin and every coefficient group.
+// The test tree compiles the same header for the host with a scalar engine (syntax_host.cpp), so the
+// walk can be checked on the CPU against the call sequence the reference's writer recorded.
+//
+// Reference (src/entropy_codec/cabac_reader.cpp unless noted): coding_tree_unit :103-209, sao
+// :284-419, coding_tree :429-655, split_cu_mode :677-751, coding_unit :764-825, bdpcm_mode :1063,
+// xReadTruncBinCode :1162, extend_ref_line :1188, intra_luma_pred_modes :1231, intra_chroma_pred_mode
+// :1353, cu_residual :1396, transform_tree :2297, cbf_comp :2353, transform_unit :2456, cu_qp_delta
+// :2578, cu_chroma_qp_offset :2602, joint_cb_cr :2632, mts_idx :2754, isp_mode :2785,
+// residual_lfnst_mode :2808, mip_flag / mip_pred_mode :3381-3408; QTBTPartitioner::canSplit /
+// getImplicitSplit / splitCurrArea (src/common/unit_partitioner.cpp:303-470, 94-190);
+// DeriveCtx::CtxSplit / CtxMipFlag / CtxQtCbf (src/common/context_modelling.cpp:108-230, 317-331);
+// CodingUnit::checkCCLMAllowed (src/common/unit.cpp:289-372); CU::canUseISP / getISPSplitDim /
+// canUseLfnstWithISP / isMTSAllowed / bdpcmAllowed, TU::isTSAllowed (src/common/unit_tools.cpp).
+#pragma once
+#include <stdint.h>
+
+#include "cabac_b200.h"
+
+#if defined(__CUDACC__)
+#define SX_FN __device__ __forceinline__
+#define SX_FN_NOINLINE __device__ __noinline__
+#else
+#define SX_FN inline
+#define SX_FN_NOINLINE inline
+#endif
+
+namespace cabac_syntax {
+
+// Context-set offsets (positional in src/common/contexts.cpp; tests/test_syntax.py compares them
+// with the compiled reference through ref_driver.cpp:ref_syntax_ctx_offsets).
+enum : int {
+  SX_SPLIT_FLAG = 0,
+  SX_SPLIT_QT_FLAG = 9,
+  SX_SPLIT_HV_FLAG = 15,
+  SX_SPLIT12_FLAG = 20,
+  SX_MODE_CONS_FLAG = 24,
+  SX_MIP_FLAG = 46,
+  SX_INTRA_LUMA_MPM_FLAG = 40,
+  SX_INTRA_LUMA_PLANAR_FLAG = 41,
+  SX_CCLM_MODE_FLAG = 43,
+  SX_CCLM_MODE_IDX = 44,
+  SX_INTRA_CHROMA_PRED_MODE = 45,
+  SX_MULTI_REF_LINE_IDX = 38,
+  SX_ISP_MODE = 316,
+  SX_BDPCM_MODE = 71,
+  SX_QT_CBF_Y = 77,
+  SX_QT_CBF_CB = 81,
+  SX_QT_CBF_CR = 83,
+  SX_DELTA_QP = 50,
+  SX_CHROMA_QP_ADJ_FLAG = 325,
+  SX_CHROMA_QP_ADJ_IDC = 326,
+  SX_JOINT_CBCR_FLAG = 354,
+  SX_MTS_IDX = 312,
+  SX_LFNST_IDX = 296,
+  SX_SAO_MERGE_FLAG = 294,
+  SX_SAO_TYPE_IDX = 295,
+  SX_CTB_ALF_FLAG = 332,
+  SX_CTB_ALF_ALTERNATIVE = 341,
+  SX_ALF_USE_TEMPORAL_FILT = 343,
+  SX_CCALF_FILTER_CONTROL_FLAG = 344
+};
+constexpr int SX_NUM_OFFSETS = 29;
+#if !defined(__CUDACC__)
+inline void syntaxCtxOffsets(uint32_t *o) {
+  const int v[SX_NUM_OFFSETS] = {SX_SPLIT_FLAG, SX_SPLIT_QT_FLAG, SX_SPLIT_HV_FLAG, SX_SPLIT12_FLAG, SX_MODE_CONS_FLAG,
+                                 SX_MIP_FLAG, SX_INTRA_LUMA_MPM_FLAG, SX_INTRA_LUMA_PLANAR_FLAG, SX_CCLM_MODE_FLAG,
+                                 SX_CCLM_MODE_IDX, SX_INTRA_CHROMA_PRED_MODE, SX_MULTI_REF_LINE_IDX, SX_ISP_MODE,
+                                 SX_BDPCM_MODE, SX_QT_CBF_Y, SX_QT_CBF_CB, SX_QT_CBF_CR, SX_DELTA_QP,
+                                 SX_CHROMA_QP_ADJ_FLAG, SX_CHROMA_QP_ADJ_IDC, SX_JOINT_CBCR_FLAG, SX_MTS_IDX,
+                                 SX_LFNST_IDX, SX_SAO_MERGE_FLAG, SX_SAO_TYPE_IDX, SX_CTB_ALF_FLAG,
+                                 SX_CTB_ALF_ALTERNATIVE, SX_ALF_USE_TEMPORAL_FILT, SX_CCALF_FILTER_CONTROL_FLAG};
+  for (int i = 0; i < SX_NUM_OFFSETS; i++) o[i] = uint32_t(v[i]);
+}
+#endif
+
+// PartSplit, src/common/type_def.hpp (only the CU-level values are used)
+enum : int { SPL_CTU_LEVEL = 0, SPL_NONE = 2000, SPL_QUAD = 1, SPL_HORZ = 2, SPL_VERT = 3, SPL_TRIH = 4, SPL_TRIV = 5 };
+
+constexpr int SX_MAX_DEPTH = 12;      // 128 -> 4 is five QT levels; MTT depth <= 4 plus implicit boundary splits
+constexpr int SX_MAX_LINE = 2048;     // above-line entries: pictures up to 8192 luma samples wide
+
+// What a decoded CU leaves behind for its right / lower neighbours (CtxSplit, CtxMipFlag): one 16-bit word per
+// 4 luma samples of the picture width (above line) and of the CTU height (left column), per tree.
+SX_FN uint16_t nbPack(int log2w, int log2h, int qtDepth, int mip) {
+  return uint16_t(0x8000 | log2w | (log2h << 3) | (qtDepth << 6) | (mip << 9));
+}
+SX_FN int nbLog2W(uint16_t v) { return v & 7; }
+SX_FN int nbLog2H(uint16_t v) { return (v >> 3) & 7; }
+SX_FN int nbQt(uint16_t v) { return (v >> 6) & 7; }
+SX_FN int nbMip(uint16_t v) { return (v >> 9) & 1; }
+
+struct Node {  // one level of the coding tree: an area and the partitioner's depth counters for it
+  int16_t x, y;
+  uint8_t log2w, log2h;
+  uint8_t lastSplit;   // the split that produced this node (PartLevel::split of its parent level)
+  uint8_t partIdx;     // index among its siblings
+  uint8_t qt, mt, bt, implBt;
+  uint8_t subdiv;
+  uint8_t qg, qgChroma;  // currQgEnable / currQgChromaEnable
+  uint8_t split;       // this node's own split once parsed
+  int8_t next;         // next child to visit, -1 = not parsed yet
+  uint8_t implicit;    // this node's split equals the implicit one (boundary)
+};
+
+template <class E>
+struct SliceParser {
+  E &e;
+  const cabac_slice_params &sp;
+  uint32_t nCu = 0, nTu = 0, nCtu = 0;
+  uint64_t nCoeff = 0;
+  uint32_t status = 0;
+  // capacities of this substream's regions
+  uint32_t capCu, capTu, capCtu;
+  uint64_t capCoeff, coeffBase;
+  // per-CU accumulators of CUCtx (cabac_reader.cpp:1417-1421)
+  uint32_t cuRes = 0;
+  bool isDqpCoded = true, isChromaQpAdjCoded = true;
+  // the luma 64x64 node the chroma tree is collocated with (checkCCLMAllowed)
+  int lumaRootSplit = SPL_NONE, lumaRootIsp = 0;
+  // left / above CTU in-loop filter flags
+  uint8_t leftCtuFlags = 0;
+
+  SX_FN SliceParser(E &eng, const cabac_slice_params &p, uint32_t cCu, uint32_t cTu, uint32_t cCtu, uint64_t cCoeff,
+                    uint64_t cBase)
+      : e(eng), sp(p), capCu(cCu), capTu(cTu), capCtu(cCtu), capCoeff(cCoeff), coeffBase(cBase) {}
+
+  SX_FN bool tool(uint32_t t) const { return (sp.tools & t) != 0; }
+
+  // ---- small binarisations ----
+  SX_FN uint32_t truncBin(uint32_t maxSymbol) {  // xReadTruncBinCode, cabac_reader.cpp:1162-1186 (maxSymbol <= 256)
+    int thresh = 0;
+    while ((2u << thresh) <= maxSymbol) thresh++;  // g_tbMax[maxSymbol] = floor(log2)
+    const uint32_t val = 1u << thresh, b = maxSymbol - val;
+    uint32_t symbol = thresh ? e.ep(thresh) : 0;
+    if (symbol >= val - b) symbol = ((symbol << 1) | e.ep(1)) - (val - b);
+    return symbol;
+  }
+  SX_FN uint32_t unaryMaxEp(uint32_t maxSymbol) {  // unary_max_eqprob, :3359-3366
+    for (uint32_t k = 0; k < maxSymbol; k++)
+      if (!e.ep(1)) return k;
+    return maxSymbol;
+  }
+  SX_FN uint32_t unaryMaxSymbol(int ctx0, int ctxN, uint32_t maxSymbol) {  // :3349-3357
+    uint32_t ones = 0;
+    while (ones < maxSymbol && e.bin(ones == 0 ? ctx0 : ctxN)) ones++;
+    return ones;
+  }
+  SX_FN uint32_t expGolombEp(uint32_t count) {  // exp_golomb_eqprob, :3368-3379
+    uint32_t symbol = 0, bit = 1;
+    while (bit) {
+      bit = e.ep(1);
+      symbol += bit << count++;
+      if (count > 31) {
+        status |= CABAC_SS_COEFF_RANGE;
+        break;
+      }
+    }
+    if (--count) symbol += e.ep(count);
+    return symbol;
+  }
+
+  // ---- neighbours ----
+  SX_FN bool leftAvail(int x) const { return x > int(sp.x0); }
+  SX_FN bool aboveAvail(int y) const { return y > int(sp.y0); }
+  SX_FN uint16_t nbLeft(int ch, int x, int y) {
+    return leftAvail(x) ? e.leftCol(ch)[(y & ((1 << sp.log2_ctu) - 1)) >> 2] : uint16_t(0);
+  }
+  SX_FN uint16_t nbAbove(int ch, int x, int y) {
+    return aboveAvail(y) ? e.aboveLine(ch)[(x - int(sp.x0)) >> 2] : uint16_t(0);
+  }
+  SX_FN void nbStore(int ch, const Node &n, int mip) {
+    const uint16_t v = nbPack(n.log2w, n.log2h, n.qt, mip);
+    // clip to the picture: a CU never extends beyond it (implicit splits), but stay safe
+    e.fill(e.aboveLine(ch) + ((n.x - int(sp.x0)) >> 2), (1 << n.log2w) >> 2, v);
+    e.fill(e.leftCol(ch) + ((n.y & ((1 << sp.log2_ctu) - 1)) >> 2), (1 << n.log2h) >> 2, v);
+  }
+
+  // ---- QTBTPartitioner::getImplicitSplit, unit_partitioner.cpp:425-470 ----
+  SX_FN int implicitSplit(const Node &n, int ch) const {
+    const int w = 1 << n.log2w, h = 1 << n.log2h;
+    const bool blIn = n.y + h - 1 < int(sp.pic_h), trIn = n.x + w - 1 < int(sp.pic_w);  // x, y themselves are inside
+    const int maxBt = 1 << sp.log2_max_bt[ch], minQt = 1 << sp.log2_min_qt[ch];
+    const bool btAllowed = w <= maxBt && h <= maxBt && n.mt < sp.max_mtt_depth[ch] + n.implBt;
+    const bool qtAllowed = w > minQt && h > minQt && n.bt == 0;
+    int split = SPL_NONE;
+    if (!blIn && !trIn && qtAllowed)
+      split = SPL_QUAD;
+    else if (!blIn && btAllowed && w <= 64)
+      split = SPL_HORZ;
+    else if (!trIn && btAllowed && h <= 64)
+      split = SPL_VERT;
+    else if (!blIn || !trIn)
+      split = SPL_QUAD;
+    if (tool(CABAC_SL_DUAL_TREE) && (w > 64 || h > 64)) split = SPL_QUAD;
+    return split;
+  }
+
+  // ---- QTBTPartitioner::canSplit, unit_partitioner.cpp:303-391; bit i of the result = canSpl[i]
+  //      (0 no split, 1 QT, 2 BT hor, 3 BT ver, 4 TT hor, 5 TT ver) ----
+  SX_FN uint32_t canSplit(const Node &n, int ch, int implicit) const {
+    const int w = 1 << n.log2w, h = 1 << n.log2h;
+    const int maxBtd = int(sp.max_mtt_depth[ch]) + n.implBt;
+    const int maxBt = 1 << sp.log2_max_bt[ch], minBt = 1 << sp.log2_min_bt[ch];
+    const int maxTt = 1 << sp.log2_max_tt[ch], minTt = 1 << sp.log2_min_tt[ch];
+    const int minQt = 1 << sp.log2_min_qt[ch];
+    const int cw = w >> 1, chh = h >> 1;  // chroma block of a chroma-tree node (4:2:0)
+    bool canNo = true, canQt = true, canBh = true, canBv = true, canTh = true, canTv = true;
+    bool canBtt = n.mt < maxBtd;
+    if (n.lastSplit != SPL_CTU_LEVEL && n.lastSplit != SPL_QUAD) canQt = false;
+    if (w <= minQt) canQt = false;
+    if (ch && cw <= 4) canQt = false;  // MIN_DUALTREE_CHROMA_WIDTH
+    if (implicit != SPL_NONE) {
+      canNo = canTh = canTv = false;
+      canBh = implicit == SPL_HORZ;
+      canBv = implicit == SPL_VERT;
+      if (ch && cw == 4) canBv = false;
+      if (!canBh && !canBv && !canQt) canQt = true;
+      return uint32_t(canNo) | (uint32_t(canQt) << 1) | (uint32_t(canBh) << 2) | (uint32_t(canBv) << 3);
+    }
+    if ((n.lastSplit == SPL_TRIH || n.lastSplit == SPL_TRIV) && n.partIdx == 1) {
+      const int parl = n.lastSplit == SPL_TRIH ? SPL_HORZ : SPL_VERT;
+      canBh = parl != SPL_HORZ;
+      canBv = parl != SPL_VERT;
+    }
+    if (canBtt && (w <= minBt && h <= minBt) && (w <= minTt && h <= minTt)) canBtt = false;
+    if (canBtt && (w > maxBt || h > maxBt) && (w > maxTt || h > maxTt)) canBtt = false;
+    if (!canBtt) return uint32_t(canNo) | (uint32_t(canQt) << 1);
+    if (w > maxBt || h > maxBt) canBh = canBv = false;
+    if (h <= minBt) canBh = false;
+    if (w > 64 && h <= 64) canBh = false;
+    if (ch && cw * chh <= 16) canBh = false;  // MIN_DUALTREE_CHROMA_SIZE
+    if (w <= minBt) canBv = false;
+    if (w <= 64 && h > 64) canBv = false;
+    if (ch && (cw * chh <= 16 || cw == 4)) canBv = false;
+    if (h <= 2 * minTt || h > maxTt || w > maxTt) canTh = false;
+    if (w > 64 || h > 64) canTh = false;
+    if (ch && cw * chh <= 32) canTh = false;
+    if (w <= 2 * minTt || w > maxTt || h > maxTt) canTv = false;
+    if (w > 64 || h > 64) canTv = false;
+    if (ch && (cw * chh <= 32 || cw == 8)) canTv = false;
+    return uint32_t(canNo) | (uint32_t(canQt) << 1) | (uint32_t(canBh) << 2) | (uint32_t(canBv) << 3) |
+           (uint32_t(canTh) << 4) | (uint32_t(canTv) << 5);
+  }
+
+  // ---- split_cu_mode (:677-751) with DeriveCtx::CtxSplit (context_modelling.cpp:108-204) ----
+  SX_FN int splitCuMode(const Node &n, int ch, int implicit) {
+    const uint32_t can = canSplit(n, ch, implicit);
+    const bool canNo = can & 1, canQt = can & 2, canBh = can & 4, canBv = can & 8, canTh = can & 16, canTv = can & 32;
+    const uint16_t left = nbLeft(ch, n.x, n.y), above = nbAbove(ch, n.x, n.y);
+    bool isSplit = canBh || canBv || canTh || canTv || canQt;
+    if (canNo && isSplit) {
+      int ctx = 0;
+      if (left) ctx += nbLog2H(left) < n.log2h;
+      if (above) ctx += nbLog2W(above) < n.log2w;
+      int numSplit = (canQt ? 2 : 0) + (canBh ? 1 : 0) + (canBv ? 1 : 0) + (canTh ? 1 : 0) + (canTv ? 1 : 0);
+      if (numSplit > 0) numSplit--;
+      ctx += 3 * (numSplit >> 1);
+      isSplit = e.bin(SX_SPLIT_FLAG + ctx) != 0;
+    }
+    if (!isSplit) return SPL_NONE;
+    const bool canBtt = canBh || canBv || canTh || canTv;
+    bool isQt = canQt;
+    if (isQt && canBtt) {
+      int ctx = (left && nbQt(left) > n.qt) ? 1 : 0;
+      ctx += (above && nbQt(above) > n.qt) ? 1 : 0;
+      ctx += n.qt < 2 ? 0 : 3;
+      isQt = e.bin(SX_SPLIT_QT_FLAG + ctx) != 0;
+    }
+    if (isQt) return SPL_QUAD;
+    const bool canHor = canBh || canTh;
+    bool isVer = canBv || canTv;
+    if (isVer && canHor) {
+      int ctx;
+      const int numHor = (canBh ? 1 : 0) + (canTh ? 1 : 0), numVer = (canBv ? 1 : 0) + (canTv ? 1 : 0);
+      if (numVer == numHor) {
+        const int wAbove = above ? (1 << nbLog2W(above)) : 1, hLeft = left ? (1 << nbLog2H(left)) : 1;
+        const int depAbove = (1 << n.log2w) / wAbove, depLeft = (1 << n.log2h) / hLeft;
+        if (depAbove == depLeft || !left || !above)
+          ctx = 0;
+        else if (depAbove < depLeft)
+          ctx = 1;
+        else
+          ctx = 2;
+      } else {
+        ctx = numVer < numHor ? 3 : 4;
+      }
+      isVer = e.bin(SX_SPLIT_HV_FLAG + ctx) != 0;
+    }
+    const bool can14 = isVer ? canTv : canTh;
+    bool is12 = isVer ? canBv : canBh;
+    if (is12 && can14) is12 = e.bin(SX_SPLIT12_FLAG + (isVer ? (n.mt <= 1 ? 3 : 2) : (n.mt <= 1 ? 1 : 0))) != 0;
+    return isVer ? (is12 ? SPL_VERT : SPL_TRIV) : (is12 ? SPL_HORZ : SPL_TRIH);
+  }
+
+  // ---- child areas + depth counters: getCUSubPartitions / splitCurrArea / nextPart,
+  //      unit_partitioner.cpp:94-190, 232-276, 604-760 ----
+  SX_FN static int numParts(int split) { return split == SPL_QUAD ? 4 : (split == SPL_HORZ || split == SPL_VERT) ? 2 : 3; }
+  SX_FN Node child(const Node &p, int i) const {
+    Node c = p;
+    c.lastSplit = p.split;
+    c.partIdx = uint8_t(i);
+    c.next = -1;
+    c.split = 0;
+    c.implicit = 0;
+    switch (p.split) {
+      case SPL_QUAD:
+        c.log2w = p.log2w - 1;
+        c.log2h = p.log2h - 1;
+        c.x = int16_t(p.x + ((i & 1) << c.log2w));
+        c.y = int16_t(p.y + ((i >> 1) << c.log2h));
+        c.qt = p.qt + 1;
+        c.mt = c.bt = 0;
+        c.subdiv = p.subdiv + 2;
+        break;
+      case SPL_HORZ:
+        c.log2h = p.log2h - 1;
+        c.y = int16_t(p.y + (i << c.log2h));
+        c.mt = p.mt + 1;
+        c.bt = p.bt + 1;
+        c.implBt = p.implBt + p.implicit;
+        c.subdiv = p.subdiv + 1;
+        break;
+      case SPL_VERT:
+        c.log2w = p.log2w - 1;
+        c.x = int16_t(p.x + (i << c.log2w));
+        c.mt = p.mt + 1;
+        c.bt = p.bt + 1;
+        c.implBt = p.implBt + p.implicit;
+        c.subdiv = p.subdiv + 1;
+        break;
+      case SPL_TRIH:
+        c.log2h = p.log2h - (i == 1 ? 1 : 2);
+        c.y = int16_t(p.y + (i == 0 ? 0 : i == 1 ? (1 << (p.log2h - 2)) : (3 << (p.log2h - 2))));
+        c.mt = p.mt + 1;
+        c.bt = p.bt + (i == 1 ? 1 : 2);
+        c.implBt = p.implBt + p.implicit;
+        c.subdiv = p.subdiv + (i == 1 ? 1 : 2);
+        break;
+      default:  // SPL_TRIV
+        c.log2w = p.log2w - (i == 1 ? 1 : 2);
+        c.x = int16_t(p.x + (i == 0 ? 0 : i == 1 ? (1 << (p.log2w - 2)) : (3 << (p.log2w - 2))));
+        c.mt = p.mt + 1;
+        c.bt = p.bt + (i == 1 ? 1 : 2);
+        c.implBt = p.implBt + p.implicit;
+        c.subdiv = p.subdiv + (i == 1 ? 1 : 2);
+        break;
+    }
+    c.qg = p.qg && c.subdiv <= sp.cu_qp_delta_subdiv;
+    c.qgChroma = p.qgChroma && c.subdiv <= sp.cu_chroma_qp_offset_subdiv;
+    return c;
+  }
+
+  // ---- coding_tree (:429-655) for one tree (ch = 0 luma, 1 chroma) rooted at `root` ----
+  SX_FN_NOINLINE void codingTree(Node root, int ch) {
+    Node st[SX_MAX_DEPTH];
+    int sp_ = 0;
+    root.next = -1;
+    st[0] = root;
+    while (sp_ >= 0) {
+      Node &n = st[sp_];
+      if (n.next < 0) {
+        if (n.x >= int(sp.pic_w) || n.y >= int(sp.pic_h)) {  // cs.area.blocks[chType].contains(pos), :468, :600
+          sp_--;
+          continue;
+        }
+        // quantisation-group resets, :436-445
+        if (tool(CABAC_SL_DQP) && n.qg && ch == 0) isDqpCoded = false;
+        if (tool(CABAC_SL_CHROMA_QP_ADJ) && n.qgChroma) isChromaQpAdjCoded = false;
+        const int implicit = implicitSplit(n, ch);
+        const int split = splitCuMode(n, ch, implicit);
+        if (sp_ == 0 && ch == 0) lumaRootSplit = split;
+        if (split == SPL_NONE) {
+          codingUnit(n, ch, st, sp_);
+          sp_--;
+          continue;
+        }
+        n.split = uint8_t(split);
+        n.implicit = split == implicit;
+        n.next = 0;
+      }
+      if (n.next >= numParts(n.split) || sp_ + 1 >= SX_MAX_DEPTH) {
+        if (sp_ + 1 >= SX_MAX_DEPTH) status |= CABAC_SS_CAPACITY;
+        sp_--;
+        continue;
+      }
+      const Node c = child(n, n.next);
+      n.next++;
+      st[++sp_] = c;
+    }
+  }
+
+  // ---- CodingUnit::checkCCLMAllowed, unit.cpp:289-372 (dual tree) ----
+  SX_FN bool cclmAllowed(const Node &n, const Node *st, int depth) const {
+    if (sp.log2_ctu <= 5) return true;
+    // the chroma tree's stack starts at the 64x64 node: st[0].split is the split at depthFor64x64Node
+    const int s1 = depth >= 1 ? int(st[0].split) : int(SPL_NONE);
+    const int s2 = depth >= 2 ? int(st[1].split) : int(SPL_NONE);
+    bool allow = false;
+    if (s1 == SPL_QUAD || (s1 == SPL_HORZ && s2 == SPL_VERT))
+      allow = true;
+    else if (s1 == SPL_NONE)
+      allow = true;
+    else if (s1 == SPL_HORZ && s2 == SPL_NONE)
+      allow = true;
+    if (allow) {
+      // the collocated luma 64x64 node: split by BT / TT, or unsplit with ISP -> no CCLM
+      if (lumaRootSplit != SPL_NONE) {
+        if (lumaRootSplit != SPL_QUAD) allow = false;
+      } else if (lumaRootIsp) {
+        allow = false;
+      }
+    }
+    (void)n;
+    return allow;
+  }
+
+  // ---- coding_unit (:764-825) + cu_pred_data (:1097) + cu_residual (:1396) for an intra CU ----
+  SX_FN void codingUnit(const Node &n, int ch, const Node *st, int depth) {
+    cabac_cu_desc cu;
+    cu.x = uint16_t(n.x);
+    cu.y = uint16_t(n.y);
+    cu.log2_w = n.log2w;
+    cu.log2_h = n.log2h;
+    cu.ch_type = uint8_t(ch);
+    cu.qt_depth = n.qt;
+    cu.mt_depth = n.mt;
+    cu.flags = cu.bdpcm = cu.mrl_idx = cu.isp = cu.lfnst_idx = cu.mts_idx = cu.pred_syntax = 0;
+    cu.first_tu = nTu;
+    cu.n_tu = 0;
+    cu.qp_delta = 0;
+    cu.chroma_qp_adj = 0;
+    const int w = 1 << n.log2w, h = 1 << n.log2h;
+    const int tsMax = 1 << sp.log2_max_ts, maxTb = 1 << sp.log2_max_tb;
+    if (ch == 0) {
+      // bdpcm_mode(Y), :1063-1095 with CU::bdpcmAllowed, unit_tools.cpp:226-241
+      if (tool(CABAC_SL_BDPCM) && w <= tsMax && h <= tsMax) {
+        if (e.bin(SX_BDPCM_MODE + 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 1));
+      }
+      if (!cu.bdpcm) {  // intra_luma_pred_modes, :1231-1316
+        int mip = 0;
+        if (tool(CABAC_SL_MIP)) {  // mip_flag :3381 + DeriveCtx::CtxMipFlag
+          const uint16_t left = nbLeft(0, n.x, n.y), above = nbAbove(0, n.x, n.y);
+          int ctx = (left ? nbMip(left) : 0) + (above ? nbMip(above) : 0);
+          if (w > 2 * h || h > 2 * w) ctx = 3;
+          mip = int(e.bin(SX_MIP_FLAG + ctx));
+        }
+        if (mip) {  // mip_pred_mode :3408
+          cu.flags |= CABAC_CU_MIP;
+          if (e.ep(1)) cu.flags |= CABAC_CU_MIP_TRANSPOSED;
+          const int numModes = (w == 4 && h == 4) ? 16 : (w == 4 || h == 4 || (w == 8 && h == 8)) ? 8 : 6;
+          cu.pred_syntax = uint8_t(truncBin(uint32_t(numModes)));
+        } else {
+          // extend_ref_line :1188-1229
+          if (tool(CABAC_SL_MRL) && (n.y & ((1 << sp.log2_ctu) - 1)) != 0) {
+            if (e.bin(SX_MULTI_REF_LINE_IDX + 0)) cu.mrl_idx = uint8_t(1 + e.bin(SX_MULTI_REF_LINE_IDX + 1));
+          }
+          // isp_mode :2785-2806, CU::canUseISP unit_tools.cpp:290-298
+          if (!cu.mrl_idx && tool(CABAC_SL_ISP) && n.log2w + n.log2h > 4 && w <= maxTb && h <= maxTb) {
+            if (e.bin(SX_ISP_MODE + 0)) cu.isp = uint8_t(1 + e.bin(SX_ISP_MODE + 1));
+          }
+          const bool mpm = cu.mrl_idx ? true : e.bin(SX_INTRA_LUMA_MPM_FLAG) != 0;
+          if (mpm) {
+            cu.flags |= CABAC_CU_MPM;
+            uint32_t idx = cu.mrl_idx ? 1u : e.bin(SX_INTRA_LUMA_PLANAR_FLAG + (cu.isp ? 0 : 1));
+            if (idx) idx += e.ep(1);
+            if (idx > 1) idx += e.ep(1);
+            if (idx > 2) idx += e.ep(1);
+            if (idx > 3) idx += e.ep(1);
+            cu.pred_syntax = uint8_t(idx);
+          } else {
+            cu.pred_syntax = uint8_t(truncBin(61));  // NUM_LUMA_MODE - NUM_MOST_PROBABLE_MODES
+          }
+        }
+      }
+      if (depth == 0) lumaRootIsp = cu.isp;
+    } else {
+      const int cw = w >> 1, chh = h >> 1;
+      if (tool(CABAC_SL_BDPCM) && cw <= tsMax && chh <= tsMax) {
+        if (e.bin(SX_BDPCM_MODE + 2)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 3));
+      }
+      if (!cu.bdpcm) {  // intra_chroma_pred_mode :1353-1394
+        bool done = false;
+        if (tool(CABAC_SL_CCLM) && cclmAllowed(n, st, depth)) {
+          if (e.bin(SX_CCLM_MODE_FLAG)) {
+            cu.flags |= CABAC_CU_CCLM;
+            uint32_t sym = e.bin(SX_CCLM_MODE_IDX);
+            if (sym) sym += e.ep(1);
+            cu.pred_syntax = uint8_t(sym);
+            done = true;
+          }
+        }
+        if (!done && e.bin(SX_INTRA_CHROMA_PRED_MODE)) cu.pred_syntax = uint8_t(1 + e.ep(2));
+      }
+    }
+
+    // ---- cu_residual :1396-1437 -> transform_tree :2297-2351 ----
+    cuRes = 0;
+    bool anyTs = false;
+    if (ch == 0 && cu.isp) {
+      // TUIntraSubPartitioner: getTUIntraSubPartitions, unit_partitioner.cpp:838-895; CU::getISPSplitDim
+      const bool rows = cu.isp == 1;
+      const int splitDim = rows ? h : w, other = rows ? w : h;
+      const int factor = other < 16 ? (16 >> (rows ? n.log2w : n.log2h)) : 1;
+      const int part = (splitDim >> 2) < factor ? factor : (splitDim >> 2);
+      const int nParts = splitDim / part;
+      int log2part = 0;
+      while ((1 << log2part) < part) log2part++;
+      bool rootCbfSoFar = false, prevCbf = false;
+      for (int i = 0; i < nParts; i++) {
+        bool cbf;
+        if (i == nParts - 1 && !rootCbfSoFar)
+          cbf = true;  // lastCbfIsInferred, :2500-2511
+        else
+          cbf = e.bin(SX_QT_CBF_Y + 2 + (prevCbf ? 1 : 0)) != 0;
+        rootCbfSoFar |= cbf;
+        prevCbf = cbf;
+        if (cbf) dqp(cu);
+        if (cbf) {
+          const int tw = rows ? n.log2w : log2part, th = rows ? log2part : n.log2h;
+          anyTs |= residual(cu, tw, th, 0, 0);  // TU::isTSAllowed: never with ISP
+        }
+      }
+    } else {
+      // TU_MAX_TR_SPLIT tiling (getMaxTuTiling, unit_partitioner.cpp:762-836): raster order
+      const int tl2w = n.log2w > int(sp.log2_max_tb) ? int(sp.log2_max_tb) : n.log2w;
+      const int tl2h = n.log2h > int(sp.log2_max_tb) ? int(sp.log2_max_tb) : n.log2h;
+      const int nx = 1 << (n.log2w - tl2w), ny = 1 << (n.log2h - tl2h);
+      for (int ty = 0; ty < ny; ty++)
+        for (int tx = 0; tx < nx; tx++) {
+          if (ch == 0) {
+            const bool cbf = e.bin(SX_QT_CBF_Y + (cu.bdpcm ? 1 : 0)) != 0;  // cbf_comp :2353-2388
+            if (cbf || w > 64 || h > 64) dqp(cu);
+            if (cbf) {
+              const bool tsAllowed = tool(CABAC_SL_TS) && !cu.bdpcm && (1 << tl2w) <= tsMax && (1 << tl2h) <= tsMax;
+              anyTs |= residual(cu, tl2w, tl2h, 0,
+                                uint8_t((tsAllowed ? CABAC_TU_TS_ALLOWED : 0) | (cu.bdpcm ? CABAC_TU_BDPCM : 0)));
+            }
+          } else {
+            const int cl2w = tl2w - 1, cl2h = tl2h - 1;
+            const bool cbfCb = e.bin(SX_QT_CBF_CB + (cu.bdpcm ? 1 : 0)) != 0;
+            const bool cbfCr = e.bin(SX_QT_CBF_CR + (cu.bdpcm ? 2 : (cbfCb ? 1 : 0))) != 0;
+            const bool cbfChroma = cbfCb || cbfCr;
+            // cu_chroma_qp_offset :2602-2630 (condition at :2551-2563)
+            if (tool(CABAC_SL_CHROMA_QP_ADJ) && ((w >> 1) > 64 || (h >> 1) > 64 || cbfChroma) && !isChromaQpAdjCoded) {
+              uint32_t adj = e.bin(SX_CHROMA_QP_ADJ_FLAG);
+              if (adj && sp.chroma_qp_offset_list_len > 1)
+                adj += unaryMaxSymbol(SX_CHROMA_QP_ADJ_IDC, SX_CHROMA_QP_ADJ_IDC, sp.chroma_qp_offset_list_len - 1);
+              cu.chroma_qp_adj = uint8_t(adj);
+              isChromaQpAdjCoded = true;
+            }
+            const int cbfMask = (cbfCb ? 2 : 0) + (cbfCr ? 1 : 0);
+            int joint = 0;
+            if (tool(CABAC_SL_JCCR) && cbfMask) {  // joint_cb_cr :2632-2645 (intra CU)
+              if (e.bin(SX_JOINT_CBCR_FLAG + cbfMask - 1)) joint = cbfMask;
+            }
+            if (joint) cu.flags |= CABAC_CU_JCCR;
+            const bool tsAllowed = tool(CABAC_SL_TS) && !cu.bdpcm && (1 << cl2w) <= tsMax && (1 << cl2h) <= tsMax;
+            const uint8_t fl = uint8_t((tsAllowed ? CABAC_TU_TS_ALLOWED : 0) | (cu.bdpcm ? CABAC_TU_BDPCM : 0));
+            if (cbfCb) anyTs |= residual(cu, cl2w, cl2h, 1, fl);
+            if (cbfCr && joint != 3) anyTs |= residual(cu, cl2w, cl2h, 2, fl);
+          }
+        }
+    }
+
+    // ---- residual_lfnst_mode :2808-2863 ----
+    {
+      bool skip = false;
+      if (cu.isp) {  // CU::canUseLfnstWithISP, unit_tools.cpp:300-318
+        const bool rows = cu.isp == 1;
+        const int splitDim = rows ? h : w, other = rows ? w : h;
+        const int factor = other < 16 ? (16 >> (rows ? n.log2w : n.log2h)) : 1;
+        const int part = (splitDim >> 2) < factor ? factor : (splitDim >> 2);
+        const int tw = rows ? w : part, th = rows ? part : h;
+        if (!(tw >= 4 && th >= 4)) skip = true;
+      }
+      if (tool(CABAC_SL_LFNST) && (cu.flags & CABAC_CU_MIP) && !(w >= 16 && h >= 16)) skip = true;
+      if (ch == 1 && ((w >> 1) < 4 || (h >> 1) < 4)) skip = true;
+      if (w > maxTb || h > maxTb) skip = true;
+      if (!skip && tool(CABAC_SL_LFNST)) {
+        const bool violates = (cuRes & CABAC_TUR_VIOLATES_LFNST) != 0;
+        const bool lastPos = (cuRes & CABAC_TUR_LFNST_LAST_POS) != 0;
+        if (!((!lastPos && !cu.isp) || violates || anyTs)) {
+          uint32_t idx = e.bin(SX_LFNST_IDX + 1);  // isSepTree: always in a dual-tree slice
+          if (idx) idx += e.bin(SX_LFNST_IDX + 2);
+          cu.lfnst_idx = uint8_t(idx);
+        }
+      }
+    }
+    // ---- mts_idx :2754-2783, CU::isMTSAllowed unit_tools.cpp:243-260 ----
+    if (ch == 0) {
+      const bool firstTuTs = anyTs && !cu.isp;  // firstTU->mtsIdx[Y] == MTS_SKIP: MTS only exists for single-TU CUs
+      cu.mts_idx = firstTuTs ? 1 : 0;
+      const bool allowed = tool(CABAC_SL_MTS_INTRA) && w <= 32 && h <= 32 && !cu.isp && !(cu.bdpcm && w <= tsMax && h <= tsMax);
+      if (allowed && !(cuRes & CABAC_TUR_VIOLATES_MTS) && (cuRes & CABAC_TUR_MTS_LAST_POS) && cu.lfnst_idx == 0 &&
+          !firstTuTs) {
+        if (e.bin(SX_MTS_IDX + 0)) {
+          int m = 2;
+          for (int i = 0; i < 3; i++) {
+            const uint32_t s = e.bin(SX_MTS_IDX + 1 + i);
+            m += int(s);
+            if (!s) break;
+          }
+          cu.mts_idx = uint8_t(m);
+        }
+      }
+    }
+    nbStore(ch, n, (cu.flags & CABAC_CU_MIP) ? 1 : 0);
+    if (nCu < capCu)
+      e.putCu(nCu, cu);
+    else
+      status |= CABAC_SS_CAPACITY;
+    nCu++;
+  }
+
+  // cu_qp_delta :2578-2600 under the condition of :2537-2545
+  SX_FN void dqp(cabac_cu_desc &cu) {
+    if (!tool(CABAC_SL_DQP) || isDqpCoded) return;
+    int dq = int(unaryMaxSymbol(SX_DELTA_QP, SX_DELTA_QP + 1, 5));
+    if (dq >= 5) dq += int(expGolombEp(0));
+    if (dq > 0 && e.ep(1)) dq = -dq;
+    cu.qp_delta = int8_t(dq);
+    cu.flags |= CABAC_CU_DQP;
+    isDqpCoded = true;
+  }
+
+  // residual_coding of one block; returns whether it was transform-skipped
+  SX_FN bool residual(cabac_cu_desc &cu, int log2w, int log2h, int comp, uint8_t flags) {
+    cabac_tu_desc d;
+    d.coeff_offset = coeffBase + nCoeff;
+    d.log2_w = uint8_t(log2w);
+    d.log2_h = uint8_t(log2h);
+    d.comp_id = uint8_t(comp);
+    d.flags = flags;
+    d.reserved = 0;
+    const uint64_t area = uint64_t(1) << (log2w + log2h);
+    if (nTu >= capTu || nCoeff + area > capCoeff) {
+      // No room: the bins still have to be consumed to stay in step, but there is nowhere to put the levels.
+      status |= CABAC_SS_CAPACITY;
+      e.abort();
+      return false;
+    }
+    const uint32_t r = e.residual(nTu, d);
+    cuRes |= r;
+    nTu++;
+    nCoeff += area;
+    cu.n_tu++;
+    return (r & CABAC_TUR_TS) != 0;
+  }
+
+  // ---- sao :284-419 ----
+  SX_FN void sao(cabac_ctu_desc &c, int ctuX, int ctuY) {
+    const bool luma = tool(CABAC_SL_SAO_LUMA), chroma = tool(CABAC_SL_SAO_CHROMA);
+    if (!luma && !chroma) return;
+    int merge = -1;
+    if (leftAvail(ctuX)) merge += int(e.bin(SX_SAO_MERGE_FLAG));
+    if (merge < 0 && aboveAvail(ctuY)) merge += int(e.bin(SX_SAO_MERGE_FLAG)) << 1;
+    if (merge >= 0) {
+      c.sao_mode[0] = 2;
+      c.sao_type[0] = uint8_t(merge);
+      if (chroma) {
+        c.sao_mode[1] = c.sao_mode[2] = 2;
+        c.sao_type[1] = c.sao_type[2] = uint8_t(merge);
+      }
+      return;
+    }
+    const int first = luma ? 0 : 1, last = chroma ? 2 : 0;
+    const int bd = int(sp.bit_depth) < 10 ? int(sp.bit_depth) : 10;
+    const uint32_t maxOffset = (1u << (bd - 5)) - 1;
+    for (int comp = first; comp <= last; comp++) {
+      if (comp != 2) {
+        if (e.bin(SX_SAO_TYPE_IDX)) {
+          c.sao_mode[comp] = 1;
+          c.sao_type[comp] = e.ep(1) ? 1 : 0;  // 1 = edge (class added below), 0 = band
+        }
+      } else {
+        c.sao_mode[2] = c.sao_mode[1];
+        c.sao_type[2] = c.sao_type[1] ? 1 : 0;
+      }
+      if (c.sao_mode[comp] == 0) continue;
+      int off[4];
+      for (int k = 0; k < 4; k++) off[k] = int(unaryMaxEp(maxOffset));
+      if (c.sao_type[comp] == 0) {  // band offset
+        for (int k = 0; k < 4; k++)
+          if (off[k] && e.ep(1)) off[k] = -off[k];
+        c.sao_band[comp] = uint8_t(e.ep(5));
+      } else if (comp != 2) {
+        c.sao_type[comp] = uint8_t(1 + e.ep(2));  // sao_eo_class
+      } else {
+        c.sao_type[2] = c.sao_type[1];
+      }
+      for (int k = 0; k < 4; k++) c.sao_offset[comp][k] = int8_t(off[k]);
+    }
+  }
+
+  // ---- coding_tree_unit :103-209 ----
+  SX_FN void codingTreeUnit(int ctuX, int ctuY) {
+    cabac_ctu_desc c;
+    for (int i = 0; i < 3; i++) {
+      c.sao_mode[i] = c.sao_type[i] = c.sao_band[i] = 0;
+      c.alf_flag[i] = 0;
+      c.reserved[i] = 0;
+      for (int k = 0; k < 4; k++) c.sao_offset[i][k] = 0;
+    }
+    c.alf_filter_idx = 0;
+    c.alf_alt[0] = c.alf_alt[1] = c.ccalf_idc[0] = c.ccalf_idc[1] = 0;
+    sao(c, ctuX, ctuY);
+    const int col = (ctuX - int(sp.x0)) >> sp.log2_ctu;
+    const bool lAvail = leftAvail(ctuX), aAvail = aboveAvail(ctuY);
+    const uint8_t aboveFlags = aAvail ? e.ctuLine()[col] : uint8_t(0);
+    const uint8_t leftFlags = lAvail ? leftCtuFlags : uint8_t(0);
+    uint8_t mine = 0;
+    if (tool(CABAC_SL_ALF_Y)) {
+      for (int comp = 0; comp < 3; comp++) {
+        if (!tool(CABAC_SL_ALF_Y << comp)) continue;
+        const int ctx = ((leftFlags >> comp) & 1) + ((aboveFlags >> comp) & 1);
+        const uint32_t f = e.bin(SX_CTB_ALF_FLAG + comp * 3 + ctx);
+        c.alf_flag[comp] = uint8_t(f);
+        mine |= uint8_t(f << comp);
+        if (comp == 0 && f) {  // readAlfCtuFilterIndex :211-235
+          const uint32_t numAps = sp.alf_num_aps_luma;
+          uint32_t idx = 0;
+          if (numAps > 0) {
+            if (e.bin(SX_ALF_USE_TEMPORAL_FILT)) {
+              if (numAps > 1) idx = truncBin(numAps);
+              idx += 16;
+            } else {
+              idx = truncBin(16);
+            }
+          } else {
+            idx = truncBin(16);
+          }
+          c.alf_filter_idx = uint8_t(idx);
+        }
+        if (comp > 0 && f) {
+          uint32_t decoded = 0;
+          while (decoded + 1 < sp.alf_chroma_num_alts && e.bin(SX_CTB_ALF_ALTERNATIVE + comp - 1)) decoded++;
+          c.alf_alt[comp - 1] = uint8_t(decoded);
+        }
+      }
+    }
+    for (int comp = 1; comp < 3; comp++) {  // ccAlfFilterControlIdc :237-276
+      if (!tool(CABAC_SL_CCALF_CB << (comp - 1))) continue;
+      int ctx = ((leftFlags >> (2 + comp)) & 1) + ((aboveFlags >> (2 + comp)) & 1) + (comp == 2 ? 3 : 0);
+      uint32_t idc = e.bin(SX_CCALF_FILTER_CONTROL_FLAG + ctx);
+      if (idc)
+        while (idc != sp.ccalf_filter_count[comp - 1] && e.ep(1)) idc++;
+      c.ccalf_idc[comp - 1] = uint8_t(idc);
+      if (idc) mine |= uint8_t(4u << comp);
+    }
+    e.ctuLineStore(col, mine);
+    leftCtuFlags = mine;
+    if (nCtu < capCtu)
+      e.putCtu(nCtu, c);
+    else
+      status |= CABAC_SS_CAPACITY;
+    nCtu++;
+
+    Node root;
+    root.x = int16_t(ctuX);
+    root.y = int16_t(ctuY);
+    root.log2w = root.log2h = uint8_t(sp.log2_ctu);
+    root.lastSplit = SPL_CTU_LEVEL;
+    root.partIdx = 0;
+    root.qt = root.mt = root.bt = root.implBt = 0;
+    root.subdiv = 0;
+    root.qg = root.qgChroma = 1;
+    root.split = 0;
+    root.next = -1;
+    root.implicit = 0;
+    if (sp.log2_ctu > 6) {
+      // dual tree above 64x64: the implicit quad split is shared, then luma and chroma alternate per 64x64 node
+      // (:464-517); split_cu_mode of the 128x128 node reads nothing (canNo = false, only QT possible)
+      if (tool(CABAC_SL_DQP)) isDqpCoded = false;
+      if (tool(CABAC_SL_CHROMA_QP_ADJ)) isChromaQpAdjCoded = false;
+      root.split = SPL_QUAD;
+      for (int i = 0; i < 4; i++) {
+        const Node q = child(root, i);
+        if (q.x >= int(sp.pic_w) || q.y >= int(sp.pic_h)) continue;
+        lumaRootSplit = SPL_NONE;
+        lumaRootIsp = 0;
+        codingTree(q, 0);
+        codingTree(q, 1);
+      }
+    } else {
+      lumaRootSplit = SPL_NONE;
+      lumaRootIsp = 0;
+      codingTree(root, 0);
+      codingTree(root, 1);
+    }
+  }
+
+  // ---- the substream: its CTUs in raster order inside the rectangle, then the terminating bin ----
+  SX_FN void run(bool terminate) {
+    const uint32_t refuse = CABAC_SL_IBC | CABAC_SL_PLT | CABAC_SL_ACT | CABAC_SL_WPP;
+    if ((sp.tools & refuse) || !tool(CABAC_SL_INTRA) || !tool(CABAC_SL_DUAL_TREE) || sp.chroma_format != 1 ||
+        sp.log2_ctu < 5 || sp.log2_ctu > 7 || ((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SX_MAX_LINE) || sp.x1 <= sp.x0 ||
+        sp.y1 <= sp.y0 || sp.x1 > sp.pic_w || sp.y1 > sp.pic_h || sp.log2_max_tb < 5 || sp.log2_max_tb > 6) {
+      status |= CABAC_SS_UNSUPPORTED;
+      return;
+    }
+    const int ctu = 1 << sp.log2_ctu;
+    for (int y = int(sp.y0); y < int(sp.y1) && !e.aborted(); y += ctu) {
+      leftCtuFlags = 0;
+      for (int x = int(sp.x0); x < int(sp.x1) && !e.aborted(); x += ctu) codingTreeUnit(x, y);
+    }
+    if (terminate && !e.aborted() && !e.trm()) status |= CABAC_SS_NO_TERMINATE;
+  }
+};
+
+}  // namespace cabac_syntax

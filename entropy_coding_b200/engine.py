@@ -13,7 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .types import (CTX_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, TU_DT, WPP_DT)
+from .types import (CTU_DT, CTX_DT, CU_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, SLICE_DT, TU_DT, WPP_DT)
 
 
 class CabacError(RuntimeError):
@@ -290,6 +290,49 @@ class CabacEngine:
         if rc != ERR_SUBSTREAM or raise_on_status:
             self._check(rc, status)
         return dict(coeffs=coeffs, num_bins=bins, bits_read=bits, tu_flags=tu_flags, status=status, ctx_out=ctx_out)
+
+    # ---- whole substreams: CTU-level syntax on the device (cabac_decode_slices) ----
+    @staticmethod
+    def slice_capacities(slice_params):
+        """Record / coefficient capacities that always suffice for each substream's CTU rectangle."""
+        sp = _np(slice_params, SLICE_DT)
+        area = (sp["x1"].astype(np.int64) - sp["x0"]) * (sp["y1"].astype(np.int64) - sp["y0"])
+        ctu = np.int64(1) << sp["log2_ctu"].astype(np.int64)
+        n_ctu = (-(-(sp["x1"].astype(np.int64) - sp["x0"]) // ctu)) * (-(-(sp["y1"].astype(np.int64) - sp["y0"]) // ctu))
+
+        def off(counts):
+            return np.concatenate([[0], np.cumsum(counts)]).astype(np.uint64)
+        return dict(cu=off(area // 16 * 2 + 8), tu=off(area // 16 * 2 + 8), ctu=off(n_ctu), coeff=off(area * 3 // 2 + 64))
+
+    def decode_slices(self, data, in_offsets, params, slice_params, ctx_in=None, want_ctx=False, raise_on_status=True):
+        data, in_offsets = _np(data, np.uint8), _np(in_offsets, np.uint64)
+        params, sp = _np(params, PARAMS_DT), _np(slice_params, SLICE_DT)
+        n = len(params)
+        cap = self.slice_capacities(sp)
+        cus, tus = np.zeros(int(cap["cu"][-1]), CU_DT), np.zeros(int(cap["tu"][-1]), TU_DT)
+        tu_flags, ctus = np.zeros(int(cap["tu"][-1]), np.uint8), np.zeros(int(cap["ctu"][-1]), CTU_DT)
+        coeffs = np.zeros(int(cap["coeff"][-1]), np.int32)
+        counts = np.zeros((n, 3), np.uint32)
+        bins, bits, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_decode_slices(self.h, _hp(data), _hp(in_offsets), _hp(params), _hp(sp), n, _hp(ctx_in),
+                                          _hp(cap["cu"]), _hp(cap["tu"]), _hp(cap["ctu"]), _hp(cap["coeff"]), _hp(cus),
+                                          _hp(tus), _hp(tu_flags), _hp(ctus), _hp(coeffs), _hp(counts), _hp(bins),
+                                          _hp(bits), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(cus=cus, tus=tus, tu_flags=tu_flags, ctus=ctus, coeffs=coeffs, counts=counts, cap=cap, num_bins=bins,
+                    bits_read=bits, status=status, ctx_out=ctx_out)
+
+    def decode_slices_dev(self, data, in_offsets, params, slice_params, n_sub, cu_offsets, tu_offsets, ctu_offsets,
+                          coeff_offsets, cus, tus, tu_flags, ctus, coeffs, counts=None, num_bins=None, bits_read=None,
+                          ctx_in=None, ctx_out=None, status=None):
+        self._check(self.lib.cabac_decode_slices_dev(self.h, _dp(data), _dp(in_offsets), _dp(params), _dp(slice_params),
+                                                     n_sub, _dp(ctx_in), _dp(cu_offsets), _dp(tu_offsets),
+                                                     _dp(ctu_offsets), _dp(coeff_offsets), _dp(cus), _dp(tus),
+                                                     _dp(tu_flags), _dp(ctus), _dp(coeffs), _dp(counts), _dp(num_bins),
+                                                     _dp(bits_read), _dp(ctx_out), _dp(status)))
 
     # ---- WPP: CTU rows with context hand-over in one launch (cabac_*_wpp) ----
     def encode_residual_wpp(self, tus, tu_offsets, params, wpp, coeffs, out_offsets, packed=None, ctx_in=None,

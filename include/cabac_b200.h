@@ -694,6 +694,151 @@ int cabac_substream_ranges(cabac_handle *h, const uint32_t *offset_minus1,
                            uint64_t slice_data_pos, uint64_t rbsp_size,
                            uint64_t *in_offsets);
 
+
+/* ---- whole substreams: the CTU-level syntax on the device ---------------
+ * Replaces, for all-intra substreams with separate luma / chroma trees, the decoder's per-CTU call
+ *   CABACReader::coding_tree_unit(cs, area, qps, ctuRsAddr)          cabac_reader.cpp:103-209
+ * and everything it calls (sao :284, readAlfCtuFilterIndex :211, ccAlfFilterControlIdc :237,
+ * coding_tree :429, split_cu_mode :677, coding_unit :764, bdpcm_mode :1063, intra_luma_pred_modes
+ * :1231, extend_ref_line :1188, isp_mode :2785, mip_flag / mip_pred_mode :3381-3408,
+ * intra_chroma_pred_mode :1353, cu_residual :1396, transform_tree :2297, transform_unit :2456,
+ * cbf_comp :2353, cu_qp_delta :2578, cu_chroma_qp_offset :2602, joint_cb_cr :2632, residual_coding
+ * :2647, mts_idx :2754, residual_lfnst_mode :2808), the QTBTPartitioner's legality rules
+ * (unit_partitioner.cpp:303-470) and DeriveCtx::CtxSplit / CtxMipFlag / CtxQtCbf
+ * (context_modelling.cpp:108-348), followed by the slice's terminating bit (DecSlice.cpp:241-262).
+ * One call parses n_sub independent substreams (slices / tiles) from their bytes alone: no TU list
+ * is needed, the kernel emits it.  What the reference keeps in CodingStructure / CodingUnit /
+ * TransformUnit comes back as flat records.                                                       */
+enum { /* cabac_slice_params.tools */
+  CABAC_SL_DUAL_TREE = 1 << 0,   /* CS::isDualITree: I slice, sps qtbtt_dual_tree_intra_flag    */
+  CABAC_SL_SAO_LUMA = 1 << 1,    /* sps SAO && slice.getSaoEnabledFlag(CHANNEL_TYPE_LUMA)       */
+  CABAC_SL_SAO_CHROMA = 1 << 2,
+  CABAC_SL_ALF_Y = 1 << 3,       /* sps ALF && slice.getAlfEnabledFlag(COMPONENT_Y)             */
+  CABAC_SL_ALF_CB = 1 << 4,
+  CABAC_SL_ALF_CR = 1 << 5,
+  CABAC_SL_CCALF_CB = 1 << 6,    /* slice.m_ccAlfFilterParam.ccAlfFilterEnabled[0]              */
+  CABAC_SL_CCALF_CR = 1 << 7,
+  CABAC_SL_MTS_INTRA = 1 << 8,   /* sps.getUseIntraMTS()                                        */
+  CABAC_SL_LFNST = 1 << 9,
+  CABAC_SL_ISP = 1 << 10,
+  CABAC_SL_MIP = 1 << 11,
+  CABAC_SL_MRL = 1 << 12,
+  CABAC_SL_TS = 1 << 13,         /* sps.getTransformSkipEnabledFlag()                           */
+  CABAC_SL_BDPCM = 1 << 14,
+  CABAC_SL_JCCR = 1 << 15,
+  CABAC_SL_CCLM = 1 << 16,
+  CABAC_SL_DQP = 1 << 17,        /* pps.getUseDQP()                                             */
+  CABAC_SL_CHROMA_QP_ADJ = 1 << 18,
+  CABAC_SL_WPP = 1 << 19,        /* entropy coding sync: refused (rows of one slice)            */
+  CABAC_SL_IBC = 1 << 20,        /* refused                                                     */
+  CABAC_SL_PLT = 1 << 21,        /* refused                                                     */
+  CABAC_SL_ACT = 1 << 22,        /* refused                                                     */
+  CABAC_SL_INTRA = 1 << 23,      /* slice.isIntra(); P / B slices are refused                   */
+  CABAC_SL_MTS = 1 << 24         /* sps.getUseMTS()                                             */
+};
+/* Field order == word order of the fixture records (tests/golden/vtm_record). */
+typedef struct cabac_slice_params {
+  uint32_t pic_w, pic_h;        /* pps.getPicWidth/HeightInLumaSamples                          */
+  uint32_t x0, y0, x1, y1;      /* the CTU rectangle this substream covers, luma samples,
+                                   x1 / y1 exclusive and clipped to the picture; neighbours
+                                   outside it are unavailable (other slice / tile)               */
+  uint32_t log2_ctu;            /* 5..7                                                          */
+  uint32_t log2_min_qt[2];      /* [luma tree, chroma tree], luma samples (PreCalcValues)        */
+  uint32_t log2_max_bt[2];
+  uint32_t log2_max_tt[2];
+  uint32_t max_mtt_depth[2];
+  uint32_t log2_min_bt[2];
+  uint32_t log2_min_tt[2];
+  uint32_t log2_max_tb;         /* sps.getMaxTbSize()                                            */
+  uint32_t log2_max_ts;         /* sps.getLog2MaxTransformSkipBlockSize()                        */
+  uint32_t bit_depth;           /* luma; SAO offset range                                        */
+  uint32_t alf_num_aps_luma;    /* slice.getNumAlfApsIdsLuma()                                   */
+  uint32_t alf_chroma_num_alts; /* AlfParam::numAlternativesChroma of the chroma APS             */
+  uint32_t ccalf_filter_count[2];
+  uint32_t cu_qp_delta_subdiv;  /* slice.getCuQpDeltaSubdiv()                                    */
+  uint32_t cu_chroma_qp_offset_subdiv;
+  uint32_t chroma_qp_offset_list_len;
+  uint32_t chroma_format;       /* 1 = 4:2:0 (anything else is refused)                          */
+  uint32_t tools;               /* CABAC_SL_*                                                    */
+  uint32_t reserved;
+} cabac_slice_params;
+
+enum { /* cabac_cu_desc.flags */
+  CABAC_CU_MIP = 1,            /* cu.mipFlag                                                    */
+  CABAC_CU_MIP_TRANSPOSED = 2, /* pu.mipTransposedFlag                                          */
+  CABAC_CU_MPM = 4,            /* intra_luma_mpm_flag (inferred 1 with a reference line != 0)    */
+  CABAC_CU_CCLM = 8,           /* chroma tree: cclm_mode_flag                                    */
+  CABAC_CU_JCCR = 16,          /* some TU of the CU has tu.jointCbCr != 0                        */
+  CABAC_CU_DQP = 32            /* cu_qp_delta_abs was coded in this CU (value in qp_delta)       */
+};
+/* One record per CodingUnit in decoding order (what coding_unit() leaves in CodingUnit /
+ * PredictionUnit, unit.hpp:283-341, as the syntax element values: the derivation of the final
+ * intra direction from the MPM list, PU::getIntraMPMs, is prediction-side work and stays with
+ * the caller). */
+typedef struct cabac_cu_desc {
+  uint16_t x, y;          /* top-left in luma samples                                           */
+  uint8_t log2_w, log2_h; /* luma samples (a chroma-tree CU covers half of that per dimension)  */
+  uint8_t ch_type;        /* 0 = luma tree, 1 = chroma tree                                     */
+  uint8_t qt_depth, mt_depth;
+  uint8_t flags;          /* CABAC_CU_*                                                         */
+  uint8_t bdpcm;          /* cu.bdpcmMode (luma tree) / cu.bdpcmModeChroma: 0, 1 = hor, 2 = ver */
+  uint8_t mrl_idx;        /* pu.multiRefIdx                                                     */
+  uint8_t isp;            /* cu.ispMode: 0, 1 = horizontal, 2 = vertical                        */
+  uint8_t lfnst_idx;      /* cu.lfnstIdx                                                        */
+  uint8_t mts_idx;        /* firstTU mtsIdx[Y]: 0 DCT2, 1 transform skip, 2..5 explicit MTS      */
+  uint8_t pred_syntax;    /* luma: MIP mode | mpm_idx (0 = planar) | rem_intra_luma_pred_mode;
+                             chroma: 0 = DM, 1..4 = intra_chroma_pred_mode candidate + 1,
+                             with CABAC_CU_CCLM: cclm_mode_idx 0..2                              */
+  uint32_t first_tu;      /* index of the CU's first record in this substream's TU list          */
+  uint16_t n_tu;          /* coded blocks (cbf = 1, residual_coding called)                      */
+  int8_t qp_delta;        /* CuQpDeltaVal when CABAC_CU_DQP                                      */
+  uint8_t chroma_qp_adj;  /* cu_chroma_qp_offset_flag + idx                                      */
+} cabac_cu_desc;
+
+/* Per-CTU in-loop filter syntax (SAOBlkParam, sample_adaptive_offset.hpp; the ALF CTU maps of
+ * Picture, picture.hpp), one record per CTU in decoding order. */
+typedef struct cabac_ctu_desc {
+  uint8_t sao_mode[3];      /* 0 off, 1 new, 2 merge                                            */
+  uint8_t sao_type[3];      /* new: 0 band, 1..4 = EO class + 1; merge: 0 left, 1 above          */
+  uint8_t sao_band[3];      /* sao_band_position                                                 */
+  int8_t sao_offset[3][4];  /* signed as parsed (band) / magnitudes (edge)                       */
+  uint8_t alf_flag[3];      /* alf_ctb_flag per component                                        */
+  uint8_t alf_filter_idx;   /* AlfCtbFilterSetIndex (luma)                                       */
+  uint8_t alf_alt[2];       /* alf_ctb_filter_alt_idx Cb, Cr                                     */
+  uint8_t ccalf_idc[2];     /* filterControlIdc Cb, Cr                                           */
+  uint8_t reserved[3];
+} cabac_ctu_desc;
+
+#define CABAC_SS_UNSUPPORTED 256 /* cabac_decode_slices: a tool outside the built scope (P / B
+                                    slice, single tree, IBC, palette, ACT, WPP, non-4:2:0)      */
+#define CABAC_SS_CAPACITY 512    /* cabac_decode_slices: a record or coefficient region is full */
+
+/* Capacities: substream i may write cus[cu_offsets[i] .. cu_offsets[i+1]), likewise tus / ctus /
+ * coeffs (TCoeff units; a region of 3/2 x the rectangle's luma area always suffices, and
+ * area / 16 x 3/2 TU records, area / 16 x 2 CU records).  TU records come back in the layout
+ * cabac_decode_residual takes (coeff_offset absolute in `coeffs`; flags = CABAC_TU_* as the
+ * encoder-side recorder would have set them, CABAC_TU_TS holding the decoded flag), tu_flags in
+ * CABAC_TUR_*.  counts[3*i + 0..2] = CUs, TUs, coefficients written by substream i.
+ * All pointers are device pointers in the _dev form and host pointers otherwise.                 */
+int cabac_decode_slices_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                            const cabac_substream_params *params,
+                            const cabac_slice_params *slice_params, size_t n_sub,
+                            const cabac_ctx_model *ctx_in, const uint64_t *cu_offsets,
+                            const uint64_t *tu_offsets, const uint64_t *ctu_offsets,
+                            const uint64_t *coeff_offsets, cabac_cu_desc *cus, cabac_tu_desc *tus,
+                            uint8_t *tu_flags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                            uint32_t *counts, uint32_t *num_bins, uint32_t *bits_read,
+                            cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
+                        const cabac_substream_params *params,
+                        const cabac_slice_params *slice_params, size_t n_sub,
+                        const cabac_ctx_model *ctx_in, const uint64_t *cu_offsets,
+                        const uint64_t *tu_offsets, const uint64_t *ctu_offsets,
+                        const uint64_t *coeff_offsets, cabac_cu_desc *cus, cabac_tu_desc *tus,
+                        uint8_t *tu_flags, cabac_ctu_desc *ctus, int32_t *coeffs,
+                        uint32_t *counts, uint32_t *num_bins, uint32_t *bits_read,
+                        cabac_ctx_model *ctx_out, uint32_t *status);
+
 #ifdef __cplusplus
 }
 #endif

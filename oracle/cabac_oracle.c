@@ -1522,6 +1522,50 @@ long orc_decode_residual(const uint8_t *in, long nbytes, const cabac_tu_desc *tu
   return dec_bits_read(&d);
 }
 
+
+/* ---- stepwise decoder handle ----------------------------------------------
+ * One BinDecoder_Std + Ctx object driven call by call (decodeBin / decodeBinsEP / decodeBinTrm /
+ * CABACReader::residual_coding).  oracle/syntax_host.cpp runs the CTU-level parser
+ * (entropy_coding_b200/csrc/cabac_syntax.cuh compiled for the host) on top of it, so the parser's
+ * control flow can be checked on the CPU against the reference writer's recorded call sequence. */
+typedef struct {
+  Dec d;
+  CtxTab ct;
+  cabac_substream_params p;
+} OrcDecHandle;
+
+void *orc_dec_open(const uint8_t *in, long n, const cabac_substream_params *p, const cabac_ctx_model *ctxIn) {
+  OrcDecHandle *h = (OrcDecHandle *)malloc(sizeof(OrcDecHandle));
+  if (!h) return NULL;
+  h->p = *p;
+  ctx_begin(&h->ct, p, ctxIn);
+  dec_start(&h->d, in, n);
+  return h;
+}
+unsigned orc_dec_bin(void *hv, unsigned ctxId) {
+  OrcDecHandle *h = (OrcDecHandle *)hv;
+  return dec_bin(&h->d, &h->ct, ctxId);
+}
+unsigned orc_dec_ep(void *hv, unsigned n) {
+  OrcDecHandle *h = (OrcDecHandle *)hv;
+  return n == 1 ? dec_bin_ep(&h->d) : dec_bins_ep(&h->d, n);
+}
+unsigned orc_dec_trm(void *hv) { return dec_trm(&((OrcDecHandle *)hv)->d); }
+void orc_dec_tu(void *hv, const cabac_tu_desc *tu, int32_t *coeffs, uint8_t *tuFlags) {
+  OrcDecHandle *h = (OrcDecHandle *)hv;
+  memset(coeffs + tu->coeff_offset, 0, sizeof(int32_t) << (tu->log2_w + tu->log2_h));
+  r_residual_coding(&h->d, &h->ct, tu, coeffs, h->p.flags, tuFlags);
+}
+long orc_dec_close(void *hv, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t *numBins) {
+  OrcDecHandle *h = (OrcDecHandle *)hv;
+  if (ctxOut) memcpy(ctxOut, h->ct.m, sizeof(h->ct.m));
+  if (status) *status = h->d.status;
+  if (numBins) *numBins = h->d.nbins;
+  const long bits = dec_bits_read(&h->d);
+  free(h);
+  return bits;
+}
+
 /* ---- timed batches (bench.py cpu_baseline, kind = "port") ---------------- */
 typedef struct {
   int k, nthreads, decode;

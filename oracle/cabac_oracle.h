@@ -53,4 +53,11 @@ long orc_remove_emulation_prevention(const uint8_t *nal, long n, int vcl, uint8_
 int orc_entry_point_syntax(const uint32_t *sizes, const uint32_t *emulations, long n_sub, uint32_t *offset_minus1);
 void orc_substream_ranges(const uint32_t *offset_minus1, long n_entry, const uint32_t *epb, long n_epb,
                           uint64_t hdr_end, uint64_t rbsp_size, uint64_t *in_offsets);
+/* stepwise decoder handle (for oracle/syntax_host.cpp) */
+void *orc_dec_open(const uint8_t *in, long n, const cabac_substream_params *p, const cabac_ctx_model *ctxIn);
+unsigned orc_dec_bin(void *h, unsigned ctxId);
+unsigned orc_dec_ep(void *h, unsigned n);
+unsigned orc_dec_trm(void *h);
+void orc_dec_tu(void *h, const cabac_tu_desc *tu, int32_t *coeffs, uint8_t *tuFlags);
+long orc_dec_close(void *h, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t *numBins);
 #endif

@@ -129,6 +129,43 @@ void ref_ctx_offsets(uint32_t *o) {
   o[k++] = Ctx::TsResidualSign();
 }
 
+
+// Offsets of the context sets the CTU-level syntax uses (cabac_reader.cpp:103-2645), in the order
+// entropy_coding_b200/csrc/cabac_syntax.cuh lists them (SX_* constants); tests/test_syntax.py compares.
+int ref_syntax_ctx_offsets(uint32_t *o) {
+  int k = 0;
+  o[k++] = Ctx::SplitFlag();
+  o[k++] = Ctx::SplitQtFlag();
+  o[k++] = Ctx::SplitHvFlag();
+  o[k++] = Ctx::Split12Flag();
+  o[k++] = Ctx::ModeConsFlag();
+  o[k++] = Ctx::MipFlag();
+  o[k++] = Ctx::IntraLumaMpmFlag();
+  o[k++] = Ctx::IntraLumaPlanarFlag();
+  o[k++] = Ctx::CclmModeFlag();
+  o[k++] = Ctx::CclmModeIdx();
+  o[k++] = Ctx::IntraChromaPredMode();
+  o[k++] = Ctx::MultiRefLineIdx();
+  o[k++] = Ctx::ISPMode();
+  o[k++] = Ctx::BDPCMMode();
+  o[k++] = Ctx::QtCbf[0]();
+  o[k++] = Ctx::QtCbf[1]();
+  o[k++] = Ctx::QtCbf[2]();
+  o[k++] = Ctx::DeltaQP();
+  o[k++] = Ctx::ChromaQpAdjFlag();
+  o[k++] = Ctx::ChromaQpAdjIdc();
+  o[k++] = Ctx::JointCbCrFlag();
+  o[k++] = Ctx::MTSIdx();
+  o[k++] = Ctx::LFNSTIdx();
+  o[k++] = Ctx::SaoMergeFlag();
+  o[k++] = Ctx::SaoTypeIdx();
+  o[k++] = Ctx::ctbAlfFlag();
+  o[k++] = Ctx::ctbAlfAlternative();
+  o[k++] = Ctx::AlfUseTemporalFilt();
+  o[k++] = Ctx::CcAlfFilterControlFlag();
+  return k;
+}
+
 // Runs one recorded command stream through BinEncoder_Std.  Returns the byte
 // count (may exceed cap; bytes are truncated to cap).
 long ref_encode_bins(const uint32_t *cmds, long ncmd,

@@ -14,7 +14,11 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-MAGIC = 0x43425243
+MAGIC = 0x43425243   # 'CBRC': 12 header words
+MAGIC2 = 0x32524243  # 'CBR2': + n_slice, n_cus (slice parameters and CU records for the CTU parser)
+CU_DT = np.dtype([("x", "<u2"), ("y", "<u2"), ("log2w", "u1"), ("log2h", "u1"), ("ch_type", "u1"), ("qt_depth", "u1"),
+                  ("mt_depth", "u1"), ("flags", "u1"), ("bdpcm", "u1"), ("mrl", "u1"), ("isp", "u1"), ("lfnst", "u1"),
+                  ("mts", "u1"), ("dir", "u1")])
 NUM_CTX = 379
 TU_DT = np.dtype([("coeff_offset", "<u8"), ("log2_w", "u1"), ("log2_h", "u1"), ("comp_id", "u1"),
                   ("flags", "u1"), ("reserved", "<u4")])
@@ -32,7 +36,8 @@ def parse_records(path: str) -> list[dict]:
 
     while pos < raw.size:
         h = take("<u4", 12)
-        assert int(h[0]) == MAGIC, "bad record magic"
+        assert int(h[0]) in (MAGIC, MAGIC2), "bad record magic"
+        n_slice, n_cus = (int(v) for v in take("<u4", 2)) if int(h[0]) == MAGIC2 else (0, 0)
         qp = int(np.int32(h[1]))
         n_cmds, n_tus, n_coeffs, n_payload, n_ctu, n_full = (int(h[4]), int(h[5]), int(h[6]), int(h[7]), int(h[9]),
                                                               int(h[11]))
@@ -42,12 +47,13 @@ def parse_records(path: str) -> list[dict]:
             cuctx_before=take("u1", n_tus), cuctx_after=take("u1", n_tus),
             ctu_marks=take("<u4", 2 * n_ctu).reshape(-1, 2),
             ctx_in=take("<u2", 2 * NUM_CTX).reshape(-1, 2), ctx_out=take("<u2", 2 * NUM_CTX).reshape(-1, 2),
-            ctx_bins=take("<u4", NUM_CTX), payload=take("u1", n_payload), full_cmds=take("<u4", n_full)))
+            ctx_bins=take("<u4", NUM_CTX), payload=take("u1", n_payload), full_cmds=take("<u4", n_full),
+            slice=take("<u4", n_slice), cus=take(CU_DT, n_cus)))
     return out
 
 
 _KEYS = ("cmds", "tus", "coeffs", "cuctx_before", "cuctx_after", "ctu_marks", "ctx_in", "ctx_out", "ctx_bins",
-         "payload", "full_cmds")
+         "payload", "full_cmds", "slice", "cus")
 _SCALARS = ("qp", "init_id", "flags", "num_bins", "tools")
 
 
@@ -71,7 +77,9 @@ def load_fixture(name: str) -> tuple[list[dict], dict]:
     n = int(z["n_sub"])
     subs = []
     for i in range(n):
-        s = {k: z[f"s{i}_{k}"] for k in _KEYS}
+        s = {k: z[f"s{i}_{k}"] for k in _KEYS if f"s{i}_{k}" in z.files}
+        if "cus" in s and s["cus"].dtype != CU_DT:
+            s["cus"] = s["cus"].view(CU_DT)
         s["coeffs"] = s["coeffs"].astype(np.int32)
         s["tus"] = s["tus"].view(TU_DT) if s["tus"].dtype != TU_DT else s["tus"]
         s.update({k: int(v) for k, v in zip(_SCALARS, z[f"s{i}_meta"])})

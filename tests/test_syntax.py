@@ -1,0 +1,261 @@
+"""the CTU-level syntax of all-intra substreams, decoded from the bytes alone.
+
+The pin is the reference itself: tests/golden/vtm_*.npz hold, per substream of a VTM-produced stream,
+every BinEncIf call the reference's CABACWriter made (`cmds`: the non-residual calls with a CABAC_CMD_TU
+marker wherever it called residual_coding), the TU descriptors and TCoeff blocks behind the markers,
+one record per coding_unit() call (`cus`), the slice parameters (`slice`), the final contexts, the bin
+count and the payload.  A decoder that walks the payload must issue the mirror image of that call
+sequence - the same context for every bin, the same EP bin counts, residual_coding at the same places -
+and must come out with the same CUs, TUs, coefficients and contexts.
+
+  CPU (-m "not gpu"): the product's parser header (csrc/cabac_syntax.cuh) compiled for the host on the
+                      oracle's scalar arithmetic decoder (oracle/syntax_host.cpp) produces exactly that
+                      trace; context-set offsets equal the compiled reference's.
+  GPU (-m gpu)      : cabac_decode_slices (decode_slice_kernel, one warp per substream) returns the same
+                      records, coefficients, contexts, bin counts and bits read, for all substreams of
+                      all fixtures in one launch.
+"""
+import ctypes as C
+import glob
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.join(HERE, "..")
+sys.path.insert(0, os.path.join(HERE, "golden"))
+from vtm_streams import load_fixture  # noqa: E402
+
+from entropy_coding_b200.types import (CTU_DT, CTX_DT, CU_DT, CU_MIP, CU_MIP_TRANSPOSED, PARAMS_DT, SL_WPP, SLICE_DT,
+                                       SS_UNSUPPORTED, SUB_CTX_IN, SUB_TERMINATE, TU_DT)
+
+FIXTURES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(HERE, "golden", "vtm_*.npz")))
+
+
+def _substreams():
+    """Every fixture substream the built scope covers: slices (whole frames) and, of the WPP fixture, the
+    first CTU row of each frame (rows below need the row above as neighbour: one slice over several
+    substreams is outside cabac_decode_slices)."""
+    out = []
+    for name in FIXTURES:
+        subs, _ = load_fixture(name)
+        for i, s in enumerate(subs):
+            if "slice" not in s or not len(s["slice"]):
+                continue
+            sp = s["slice"].astype(np.uint32).copy()
+            if int(sp[30]) & SL_WPP:
+                if int(sp[3]) != 0:
+                    continue
+                sp[30] &= ~np.uint32(SL_WPP)
+            out.append((f"{name}:{i}", s, sp.view(SLICE_DT)[0]))
+    return out
+
+
+def _flat(cmds):
+    """Command words -> one token per bin (EP words are split differently by writer and reader)."""
+    out = []
+    for w in cmds:
+        w = int(w)
+        k = w >> 29
+        if k == 0:
+            out.append(("ctx", w & 511, (w >> 9) & 1))
+        elif k == 1:
+            n, v = (w >> 24) & 31, w & 0xFFFFFF
+            out.extend(("ep", (v >> i) & 1) for i in range(n - 1, -1, -1))
+        elif k == 3:
+            out.append(("trm", w & 1))
+        elif k == 5:
+            out.append(("tu",))
+        else:
+            out.append(("other", w))
+    return out
+
+
+def _host_lib():
+    path = os.path.join(ROOT, "oracle", "libsyntax_host.so")
+    if not os.path.exists(path):
+        import subprocess
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle", "syntax"])
+    lib = C.CDLL(path)
+    lib.syn_decode_slice.restype = C.c_long
+    return lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _host_decode(lib, s, sp):
+    params = np.array([(s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)], PARAMS_DT)
+    ctx_in = np.zeros(379, CTX_DT)
+    ctx_in["state0"], ctx_in["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+    area = int(sp["x1"] - sp["x0"]) * int(sp["y1"] - sp["y0"])
+    cap_cu = cap_tu = area // 16 * 2 + 8
+    cap_co = area * 3 // 2 + 64
+    cus, tus, tuf = np.zeros(cap_cu, CU_DT), np.zeros(cap_tu, TU_DT), np.zeros(cap_tu, np.uint8)
+    ctus, coeffs = np.zeros(64, CTU_DT), np.zeros(cap_co, np.int32)
+    counts, nb, st = np.zeros(3, np.uint32), np.zeros(1, np.uint32), np.zeros(1, np.uint32)
+    ctx_out, trace, nt = np.zeros(379, CTX_DT), np.zeros(1 << 20, np.uint32), C.c_long(0)
+    payload = np.ascontiguousarray(s["payload"])
+    spa = np.array([sp], SLICE_DT)
+    bits = lib.syn_decode_slice(_p(payload), C.c_long(payload.size), _p(params), _p(spa), _p(ctx_in), _p(cus),
+                                C.c_long(cap_cu), _p(tus), _p(tuf), C.c_long(cap_tu), _p(ctus), C.c_long(64), _p(coeffs),
+                                C.c_long(cap_co), _p(counts), _p(nb), _p(ctx_out), _p(st), _p(trace),
+                                C.c_long(trace.size), C.byref(nt))
+    return dict(cus=cus[:counts[0]], tus=tus[:counts[1]], tu_flags=tuf[:counts[1]], coeffs=coeffs[:counts[2]],
+                ctus=ctus, num_bins=int(nb[0]), status=int(st[0]), ctx_out=ctx_out, trace=trace[:nt.value], bits=int(bits))
+
+
+def _check_against_fixture(tag, r, s):
+    """CUs, TUs, coefficients, contexts and bin count of one decoded substream vs what the reference's writer recorded."""
+    assert r["status"] == 0, f"{tag}: status {r['status']}"
+    assert r["num_bins"] == s["num_bins"], tag
+    t, g = r["tus"], s["tus"]
+    assert len(t) == len(g), f"{tag}: {len(t)} TUs, the writer coded {len(g)}"
+    for f in ("log2_w", "log2_h", "comp_id", "flags"):
+        assert (t[f] == g[f]).all(), f"{tag}: TU {f}"
+    assert r["coeffs"].size == s["coeffs"].size and (r["coeffs"] == s["coeffs"]).all(), f"{tag}: coefficients"
+    assert (r["ctx_out"]["state0"] == s["ctx_out"][:, 0]).all() and (r["ctx_out"]["state1"] == s["ctx_out"][:, 1]).all(), tag
+    c, w = r["cus"], s["cus"]
+    assert len(c) == len(w), f"{tag}: {len(c)} CUs, the writer coded {len(w)}"
+    for f, g_ in (("x", "x"), ("y", "y"), ("log2_w", "log2w"), ("log2_h", "log2h"), ("ch_type", "ch_type"),
+                  ("qt_depth", "qt_depth"), ("mt_depth", "mt_depth"), ("bdpcm", "bdpcm"), ("mrl_idx", "mrl"),
+                  ("isp", "isp"), ("lfnst_idx", "lfnst"), ("mts_idx", "mts")):
+        assert (c[f] == w[g_]).all(), f"{tag}: CU field {f} at {np.nonzero(c[f] != w[g_])[0][:4]}"
+    both = CU_MIP | CU_MIP_TRANSPOSED
+    assert ((c["flags"] & both) == (w["flags"] & both)).all(), f"{tag}: MIP flags"
+    mip = (c["flags"] & CU_MIP) != 0
+    assert (c["pred_syntax"][mip] == w["dir"][mip]).all(), f"{tag}: MIP modes"  # pu.intraDir[0] is the MIP mode itself
+    # the stop bit follows the terminating bin: everything but the alignment was consumed
+    assert 0 <= s["payload"].size * 8 - r["bits"] <= 8, f"{tag}: bits read {r['bits']} of {s['payload'].size * 8}"
+
+
+def test_syntax_fixtures_present():
+    tags = [t for t, _, _ in _substreams()]
+    assert any(t.startswith("vtm_qp51") for t in tags) and any(t.startswith("vtm_qp32") for t in tags), tags
+    assert any(t.startswith("vtm_wpp") for t in tags), "CTU-64 rows"
+
+
+def test_syntax_ctx_offsets_equal_reference(ref):
+    lib = _host_lib()
+    mine, theirs = np.zeros(29, np.uint32), np.zeros(40, np.uint32)
+    lib.syn_ctx_offsets(_p(mine))
+    n = ref.lib.ref_syntax_ctx_offsets(_p(theirs))
+    assert n == 29 and (mine == theirs[:29]).all()
+
+
+def test_host_parser_issues_the_writers_call_sequence():
+    lib = _host_lib()
+    seen_ctx = set()
+    n_cus = n_tus = 0
+    for tag, s, sp in _substreams():
+        r = _host_decode(lib, s, sp)
+        got, want = _flat(r["trace"]), _flat(s["cmds"])
+        bad = next((k for k in range(min(len(got), len(want))) if got[k] != want[k]), None)
+        assert bad is None and len(got) == len(want), \
+            f"{tag}: call {bad}: parser {got[bad - 2:bad + 3] if bad is not None else len(got)} " \
+            f"writer {want[bad - 2:bad + 3] if bad is not None else len(want)}"
+        _check_against_fixture(tag, r, s)
+        seen_ctx |= {t[1] for t in got if t[0] == "ctx"}
+        n_cus += len(r["cus"])
+        n_tus += len(r["tus"])
+    # coverage note: which non-residual context sets the fixtures exercise
+    assert n_cus > 200 and n_tus > 200, (n_cus, n_tus)
+    for base, what in ((0, "split_cu_flag"), (9, "split_qt_flag"), (15, "mtt_split_cu_vertical_flag"),
+                       (20, "mtt_split_cu_binary_flag"), (46, "intra_mip_flag"), (40, "intra_luma_mpm_flag"),
+                       (43, "cclm_mode_flag"), (45, "intra_chroma_pred_mode"), (38, "intra_luma_ref_idx"),
+                       (316, "intra_subpartitions_mode_flag"), (77, "tu_y_coded_flag"), (81, "tu_cb_coded_flag"),
+                       (83, "tu_cr_coded_flag"), (354, "tu_joint_cbcr_residual_flag"), (312, "mts_idx"),
+                       (296, "lfnst_idx"), (294, "sao_merge"), (295, "sao_type_idx"), (332, "alf_ctb_flag")):
+        assert any(base <= c < base + 3 for c in seen_ctx), f"no fixture substream codes {what}"
+
+
+def test_host_parser_refuses_what_is_out_of_scope():
+    lib = _host_lib()
+    tag, s, sp = _substreams()[0]
+    for bit in (19, 20, 21, 22):  # WPP rows, IBC, palette, ACT
+        sp2 = sp.copy()
+        sp2["tools"] |= np.uint32(1 << bit)
+        assert _host_decode(lib, s, sp2)["status"] & SS_UNSUPPORTED
+    sp2 = sp.copy()
+    sp2["tools"] &= ~np.uint32(1 << 23)  # P / B slice
+    assert _host_decode(lib, s, sp2)["status"] & SS_UNSUPPORTED
+    sp2 = sp.copy()
+    sp2["tools"] &= ~np.uint32(1)  # single tree
+    assert _host_decode(lib, s, sp2)["status"] & SS_UNSUPPORTED
+
+
+@pytest.mark.gpu
+def test_gpu_decode_slices_equals_reference_records(engine):
+    """All fixture substreams in one launch through the C ABI, from the payload bytes alone."""
+    items = _substreams()
+    lib = _host_lib()
+    n = len(items)
+    params = np.zeros(n, PARAMS_DT)
+    sps = np.zeros(n, SLICE_DT)
+    ctx_in = np.zeros((n, 379), CTX_DT)
+    data, off = [], [0]
+    for k, (tag, s, sp) in enumerate(items):
+        params[k] = (s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)
+        sps[k] = sp
+        ctx_in[k]["state0"], ctx_in[k]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+        data.append(s["payload"])
+        off.append(off[-1] + s["payload"].size)
+    before = engine.launch_count
+    r = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, ctx_in=ctx_in, want_ctx=True)
+    assert engine.launch_count > before
+    cap = r["cap"]
+    for k, (tag, s, sp) in enumerate(items):
+        ncu, ntu, nco = (int(v) for v in r["counts"][k])
+        c0, t0, k0 = int(cap["cu"][k]), int(cap["tu"][k]), int(cap["coeff"][k])
+        tus = r["tus"][t0:t0 + ntu].copy()
+        assert (tus["coeff_offset"] >= k0).all() and (tus["coeff_offset"] < int(cap["coeff"][k + 1])).all(), tag
+        one = dict(cus=r["cus"][c0:c0 + ncu], tus=tus, tu_flags=r["tu_flags"][t0:t0 + ntu], coeffs=r["coeffs"][k0:k0 + nco],
+                   num_bins=int(r["num_bins"][k]), status=int(r["status"][k]), ctx_out=r["ctx_out"][k],
+                   bits=int(r["bits_read"][k]))
+        _check_against_fixture(tag, one, s)
+        # and field by field against the host run of the same parser (records the fixtures do not hold)
+        h = _host_decode(lib, s, sp)
+        assert one["cus"].tobytes() == h["cus"].tobytes(), f"{tag}: CU records differ from the host run"
+        assert (one["tu_flags"] == h["tu_flags"]).all(), tag
+        nctu = int(cap["ctu"][k + 1] - cap["ctu"][k])
+        assert r["ctus"][int(cap["ctu"][k]):int(cap["ctu"][k + 1])].tobytes() == h["ctus"][:nctu].tobytes(), f"{tag}: CTU records"
+        assert one["bits"] == h["bits"], tag
+
+
+@pytest.mark.gpu
+def test_gpu_decode_slices_many_copies_and_errors(engine):
+    """4096 substreams in one launch (every fixture slice many times over): identical results per copy;
+    a truncated payload and an out-of-scope tool are flagged per substream, the rest of the batch is unharmed."""
+    items = _substreams()
+    reps = 4096 // len(items) + 1
+    order = [k % len(items) for k in range(reps * len(items))][:4096]
+    n = len(order)
+    params, sps, ctx_in = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT), np.zeros((n, 379), CTX_DT)
+    data, off = [], [0]
+    for j, k in enumerate(order):
+        tag, s, sp = items[k]
+        params[j] = (s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)
+        sps[j] = sp
+        ctx_in[j]["state0"], ctx_in[j]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+        pl = s["payload"]
+        if j == 5:
+            pl = pl[:pl.size // 2]  # truncated
+        data.append(pl)
+        off.append(off[-1] + pl.size)
+    sps[7]["tools"] |= np.uint32(1 << 20)  # IBC
+    r = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, ctx_in=ctx_in,
+                             raise_on_status=False)
+    assert r["status"][7] & SS_UNSUPPORTED and r["status"][5] != 0
+    cap = r["cap"]
+    for j, k in enumerate(order):
+        if j in (5, 7):
+            continue
+        tag, s, sp = items[k]
+        assert r["status"][j] == 0 and int(r["num_bins"][j]) == s["num_bins"], f"copy {j} of {tag}"
+        ncu, ntu, nco = (int(v) for v in r["counts"][j])
+        assert ntu == len(s["tus"]) and ncu == len(s["cus"])
+        k0 = int(cap["coeff"][j])
+        assert (r["coeffs"][k0:k0 + nco] == s["coeffs"]).all(), f"copy {j} of {tag}"
