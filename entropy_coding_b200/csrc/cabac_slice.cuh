@@ -76,8 +76,26 @@ __device__ __noinline__ SliceResidualRet sliceResidual(LsDecoder dec, uint4 *ctx
   return r;
 }
 
+#ifdef CABAC_SLICE_TRACE  // debug builds only (tests/tools/slice_trace.py): the first substream's calls as command words,
+                          // recorded by lane 0 and by lane 5 (lockstep: the two must agree)
+__device__ uint32_t g_sliceTrace[2][1 << 17];
+__device__ uint32_t g_sliceTraceN[2];
+#define SLICE_TRACE(w)                                            \
+  do {                                                            \
+    if ((lane == 0 || lane == 5) && traceOn) {                    \
+      const int t_ = lane ? 1 : 0;                                \
+      const uint32_t i_ = g_sliceTraceN[t_]++;                    \
+      if (i_ < (1u << 17)) g_sliceTrace[t_][i_] = (w);            \
+    }                                                             \
+    __syncwarp();                                                 \
+  } while (0)
+#else
+#define SLICE_TRACE(w) ((void)0)
+#endif
+
 struct SliceEngine {
   LsDecoder dec;
+  bool traceOn = false;
   SliceWarpSmem &sm;
   const int lane;
   const uint32_t subFlags;
@@ -92,18 +110,32 @@ struct SliceEngine {
                                          uint8_t *tf, cabac_ctu_desc *ct, int32_t *co)
       : sm(s), lane(l), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
 
-  __device__ __forceinline__ uint32_t bin(int id) { return dec.decodeBin(sm.ctx + sliceCtxSlot(id)); }
-  __device__ __forceinline__ uint32_t ep(int n) { return n <= 16 ? dec.ep(n) : dec.epLong(uint32_t(n)); }
-  __device__ __forceinline__ uint32_t trm() { return dec.decodeBinTrm(); }
+  __device__ __forceinline__ uint32_t bin(int id) {
+    const uint32_t b = dec.decodeBin(sm.ctx + sliceCtxSlot(id));
+    SLICE_TRACE(CABAC_MK_CTX(id, b));
+    return b;
+  }
+  __device__ __forceinline__ uint32_t ep(int n) {
+    const uint32_t v = n <= 16 ? dec.ep(n) : dec.epLong(uint32_t(n));
+    SLICE_TRACE(CABAC_MK_EP(v, n));
+    return v;
+  }
+  __device__ __forceinline__ uint32_t trm() {
+    const uint32_t b = dec.decodeBinTrm();
+    SLICE_TRACE(CABAC_MK_TRM(b));
+    return b;
+  }
   __device__ __forceinline__ uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
     const SliceResidualRet r = sliceResidual(dec, sm.ctx, sm.tile, d, subFlags, coeffs, lane);
     dec = r.dec;
+    SLICE_TRACE(CABAC_MK_TU() | dec.nbins);
     if (lane == 0) {
       cabac_tu_desc o = d;
       if (r.res & CABAC_TUR_TS) o.flags |= CABAC_TU_TS;
       tus[idx] = o;
       if (tuFlags) tuFlags[idx] = uint8_t(r.res);
     }
+    __syncwarp();  // lockstep: lane 0 must not fall behind - the next bin reads and rewrites a shared context
     return r.res;
   }
   __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.above[ch]; }
@@ -119,9 +151,11 @@ struct SliceEngine {
   }
   __device__ __forceinline__ void putCu(uint32_t i, const cabac_cu_desc &c) {
     if (lane == 0 && cus) cus[i] = c;
+    __syncwarp();
   }
   __device__ __forceinline__ void putCtu(uint32_t i, const cabac_ctu_desc &c) {
     if (lane == 0 && ctus) ctus[i] = c;
+    __syncwarp();
   }
   __device__ __forceinline__ void abort() { dead = true; }
   __device__ __forceinline__ bool aborted() const { return dead; }
@@ -157,6 +191,10 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
     SliceEngine eng(sm, lane, p.flags, cus ? cus + cu0 : nullptr, tus + tu0, tuFlags ? tuFlags + tu0 : nullptr,
                     ctus ? ctus + ctu0 : nullptr, coeffs);
     eng.dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+#ifdef CABAC_SLICE_TRACE
+    eng.traceOn = sub == 0;
+    if (sub == 0 && lane == 0) g_sliceTraceN[0] = g_sliceTraceN[1] = 0;
+#endif
     cabac_syntax::SliceParser<SliceEngine> ps(eng, sp, uint32_t(cuOffsets[sub + 1] - cu0), uint32_t(tuOffsets[sub + 1] - tu0),
                                               uint32_t(ctuOffsets[sub + 1] - ctu0), coeffOffsets[sub + 1] - co0, co0);
     if (((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SLICE_MAX_LINE) ||
@@ -219,3 +257,14 @@ cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, cons
 }
 
 }  // namespace cabac
+
+#ifdef CABAC_SLICE_TRACE
+extern "C" int cabac_debug_slice_trace(int which, uint32_t *out, size_t cap, uint32_t *n) {
+  cudaDeviceSynchronize();
+  uint32_t cnt[2];
+  if (cudaMemcpyFromSymbol(cnt, cabac::g_sliceTraceN, 8) != cudaSuccess) return -1;
+  *n = cnt[which & 1];
+  const size_t m = *n < cap ? *n : cap;
+  return cudaMemcpyFromSymbol(out, cabac::g_sliceTrace, m * 4, size_t(which & 1) * (size_t(1) << 17) * 4) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -32,6 +32,17 @@
 #define SX_FN inline
 #define SX_FN_NOINLINE inline
 #endif
+// SX_OPAQUE(v): the value goes through an instruction the optimiser cannot fold (a warp shuffle from lane 0; the
+// warp is converged and v is uniform).  Needed in one place: with CUDA 12.9 ptxas (-O3 and -O1 alike) turns the test
+// "tool bit && (cbf_cb ? 2 : 0 | cbf_cr ? 1 : 0) != 0" in front of tu_joint_cbcr_residual_flag into
+// PLOP3.LUT 0x8f over (tool, cbf_cb, cbf_cr) - skip when BOTH flags are set, read when neither is - although the PTX
+// is right (nvdisasm -g of the cubin; the device left the reference's call sequence at the first chroma TU with
+// both cbfs set, and a printf next to the test made the problem disappear).
+#if defined(__CUDA_ARCH__)
+#define SX_OPAQUE(v) ((v) = __shfl_sync(0xffffffffu, (v), 0))
+#else
+#define SX_OPAQUE(v) ((void)0)
+#endif
 
 namespace cabac_syntax {
 
@@ -557,7 +568,8 @@ struct SliceParser {
               cu.chroma_qp_adj = uint8_t(adj);
               isChromaQpAdjCoded = true;
             }
-            const int cbfMask = (cbfCb ? 2 : 0) + (cbfCr ? 1 : 0);
+            int cbfMask = (cbfCb ? 2 : 0) + (cbfCr ? 1 : 0);
+            SX_OPAQUE(cbfMask);
             int joint = 0;
             if (tool(CABAC_SL_JCCR) && cbfMask) {  // joint_cb_cr :2632-2645 (intra CU)
               if (e.bin(SX_JOINT_CBCR_FLAG + cbfMask - 1)) joint = cbfMask;
