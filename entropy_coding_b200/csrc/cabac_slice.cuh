@@ -22,6 +22,7 @@ constexpr int SLICE_MAX_LINE = 1024;  // 4096 luma samples
 constexpr int SLICE_MAX_CTU_COLS = 128;
 
 struct __align__(16) SliceWarpSmem {
+  LsDecoder dec;  // the arithmetic decoder's state: identical on all lanes, kept here between calls (see sliceBin)
   int32_t tile[32 * 32];
   uint4 ctx[CABAC_NUM_CTX];  // [0, RCTX): residual contexts in rctx() order; [RCTX, 379): the others
   uint16_t above[2][SLICE_MAX_LINE];
@@ -41,16 +42,14 @@ static_assert(sliceCtxSlot(86) == rctx(86) && sliceCtxSlot(291) == rctx(291) && 
                   sliceCtxSlot(0) == RCTX && sliceCtxSlot(292) == RCTX + 86 && sliceCtxSlot(312) == RCTX + 104,
               "context slot map");
 
-struct SliceResidualRet {
-  LsDecoder dec;
-  uint32_t res;
-};
-
 // residual_coding of one block (cabac_reader.cpp:2647-2735 with ts_flag :2737-2752): the body of
-// decode_residual_kernel's TU loop.  Out of line - the CU parser calls it from four places - with the
-// decoder state passed and returned by value so that it stays in registers on both sides.
-__device__ __noinline__ SliceResidualRet sliceResidual(LsDecoder dec, uint4 *ctx, int32_t *tile, const cabac_tu_desc d,
-                                                       uint32_t subFlags, int32_t *__restrict__ coeffs, int lane) {
+// decode_residual_kernel's TU loop.  Out of line - the CU parser calls it from four places.
+__device__ __noinline__ uint32_t sliceResidual(SliceWarpSmem *sm, const cabac_tu_desc d, uint32_t subFlags,
+                                               int32_t *__restrict__ coeffs, int lane) {
+  __syncwarp();
+  LsDecoder dec = sm->dec;
+  uint4 *ctx = sm->ctx;
+  int32_t *tile = sm->tile;
   const TuGeom g = makeGeom(d);
   const int n = g.tw * g.th;
   for (int i = lane; i < n; i += 32) tile[i] = 0;
@@ -70,10 +69,36 @@ __device__ __noinline__ SliceResidualRet sliceResidual(LsDecoder dec, uint4 *ctx
     dst[i] = (x < g.tw && y < g.th) ? tile[(y << g.log2tw) + x] : 0;
   }
   __syncwarp();
-  SliceResidualRet r;
-  r.dec = dec;
-  r.res = res;
-  return r;
+  sm->dec = dec;
+  __syncwarp();
+  return res;
+}
+
+// decodeBin / decodeBinsEP / decodeBinTrm out of line for the CU parser: it has some sixty + seventy call sites.
+// Inlined (about a hundred instructions each) the kernel was 485 KB of code, and with the decoder state passed by
+// value every call site still marshalled twelve words each way (468 KB).  The state therefore lives in shared
+// memory between calls: every lane loads it, steps it identically and stores the same values back (the contexts
+// are shared the same way).  The __syncwarp keeps the lanes together across the store / load pair.
+__device__ __noinline__ uint32_t sliceBin(SliceWarpSmem *sm, int slot) {
+  __syncwarp();
+  LsDecoder dec = sm->dec;
+  const uint32_t b = dec.decodeBin(sm->ctx + slot);
+  sm->dec = dec;
+  return b;
+}
+__device__ __noinline__ uint32_t sliceEp(SliceWarpSmem *sm, int n) {
+  __syncwarp();
+  LsDecoder dec = sm->dec;
+  const uint32_t v = n <= 16 ? dec.ep(n) : dec.epLong(uint32_t(n));
+  sm->dec = dec;
+  return v;
+}
+__device__ __noinline__ uint32_t sliceTrm(SliceWarpSmem *sm) {
+  __syncwarp();
+  LsDecoder dec = sm->dec;
+  const uint32_t b = dec.decodeBinTrm();
+  sm->dec = dec;
+  return b;
 }
 
 #ifdef CABAC_SLICE_TRACE  // debug builds only (tests/tools/slice_trace.py): the first substream's calls as command words,
@@ -94,7 +119,6 @@ __device__ uint32_t g_sliceTraceN[2];
 #endif
 
 struct SliceEngine {
-  LsDecoder dec;
   bool traceOn = false;
   SliceWarpSmem &sm;
   const int lane;
@@ -111,32 +135,31 @@ struct SliceEngine {
       : sm(s), lane(l), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
 
   __device__ __forceinline__ uint32_t bin(int id) {
-    const uint32_t b = dec.decodeBin(sm.ctx + sliceCtxSlot(id));
+    const uint32_t b = sliceBin(&sm, sliceCtxSlot(id));
     SLICE_TRACE(CABAC_MK_CTX(id, b));
     return b;
   }
   __device__ __forceinline__ uint32_t ep(int n) {
-    const uint32_t v = n <= 16 ? dec.ep(n) : dec.epLong(uint32_t(n));
+    const uint32_t v = sliceEp(&sm, n);
     SLICE_TRACE(CABAC_MK_EP(v, n));
     return v;
   }
   __device__ __forceinline__ uint32_t trm() {
-    const uint32_t b = dec.decodeBinTrm();
+    const uint32_t b = sliceTrm(&sm);
     SLICE_TRACE(CABAC_MK_TRM(b));
     return b;
   }
   __device__ __forceinline__ uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
-    const SliceResidualRet r = sliceResidual(dec, sm.ctx, sm.tile, d, subFlags, coeffs, lane);
-    dec = r.dec;
-    SLICE_TRACE(CABAC_MK_TU() | dec.nbins);
+    const uint32_t res = sliceResidual(&sm, d, subFlags, coeffs, lane);
+    SLICE_TRACE(CABAC_MK_TU() | sm.dec.nbins);
     if (lane == 0) {
       cabac_tu_desc o = d;
-      if (r.res & CABAC_TUR_TS) o.flags |= CABAC_TU_TS;
+      if (res & CABAC_TUR_TS) o.flags |= CABAC_TU_TS;
       tus[idx] = o;
-      if (tuFlags) tuFlags[idx] = uint8_t(r.res);
+      if (tuFlags) tuFlags[idx] = uint8_t(res);
     }
     __syncwarp();  // lockstep: lane 0 must not fall behind - the next bin reads and rewrites a shared context
-    return r.res;
+    return res;
   }
   __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.above[ch]; }
   __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.left[ch]; }
@@ -190,7 +213,12 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
     const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub], co0 = coeffOffsets[sub];
     SliceEngine eng(sm, lane, p.flags, cus ? cus + cu0 : nullptr, tus + tu0, tuFlags ? tuFlags + tu0 : nullptr,
                     ctus ? ctus + ctu0 : nullptr, coeffs);
-    eng.dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+    {
+      LsDecoder d0;
+      d0.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+      sm.dec = d0;
+      __syncwarp();
+    }
 #ifdef CABAC_SLICE_TRACE
     eng.traceOn = sub == 0;
     if (sub == 0 && lane == 0) g_sliceTraceN[0] = g_sliceTraceN[1] = 0;
@@ -202,16 +230,18 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
       ps.status |= CABAC_SS_UNSUPPORTED;
     else
       ps.run((p.flags & CABAC_SUB_TERMINATE) != 0);
-    eng.dec.checkOverrun();
+    __syncwarp();
+    LsDecoder dEnd = sm.dec;
+    dEnd.checkOverrun();
     if (lane == 0) {
       if (counts) {
         counts[3 * sub + 0] = ps.nCu;
         counts[3 * sub + 1] = ps.nTu;
         counts[3 * sub + 2] = uint32_t(ps.nCoeff);
       }
-      if (numBins) numBins[sub] = eng.dec.nbins;
-      if (bitsRead) bitsRead[sub] = eng.dec.bitsRead();
-      if (status) status[sub] = eng.dec.status | ps.status;
+      if (numBins) numBins[sub] = dEnd.nbins;
+      if (bitsRead) bitsRead[sub] = dEnd.bitsRead();
+      if (status) status[sub] = dEnd.status | ps.status;
     }
     if (ctxOut) {
       __syncwarp();

@@ -371,7 +371,7 @@ struct SliceParser {
   }
 
   // ---- coding_tree (:429-655) for one tree (ch = 0 luma, 1 chroma) rooted at `root` ----
-  SX_FN_NOINLINE void codingTree(Node root, int ch) {
+  SX_FN void codingTree(Node root, int ch) {
     Node st[SX_MAX_DEPTH];
     int sp_ = 0;
     root.next = -1;
@@ -788,25 +788,31 @@ struct SliceParser {
     root.split = 0;
     root.next = -1;
     root.implicit = 0;
+    // The trees of this CTU in coding order.  Above 64x64 the implicit quad split is shared and luma and chroma
+    // alternate per 64x64 node (:464-517; split_cu_mode of the 128x128 node reads nothing: canNo = false, only QT
+    // possible); otherwise the luma tree of the CTU is followed by its chroma tree (:196-208).  One loop, so the
+    // tree walk - the whole CU parser - is instantiated once and its state stays in registers.
+    Node roots[4];
+    int nRoots = 0;
     if (sp.log2_ctu > 6) {
-      // dual tree above 64x64: the implicit quad split is shared, then luma and chroma alternate per 64x64 node
-      // (:464-517); split_cu_mode of the 128x128 node reads nothing (canNo = false, only QT possible)
       if (tool(CABAC_SL_DQP)) isDqpCoded = false;
       if (tool(CABAC_SL_CHROMA_QP_ADJ)) isChromaQpAdjCoded = false;
       root.split = SPL_QUAD;
       for (int i = 0; i < 4; i++) {
         const Node q = child(root, i);
         if (q.x >= int(sp.pic_w) || q.y >= int(sp.pic_h)) continue;
-        lumaRootSplit = SPL_NONE;
-        lumaRootIsp = 0;
-        codingTree(q, 0);
-        codingTree(q, 1);
+        roots[nRoots++] = q;
       }
     } else {
-      lumaRootSplit = SPL_NONE;
-      lumaRootIsp = 0;
-      codingTree(root, 0);
-      codingTree(root, 1);
+      roots[nRoots++] = root;
+    }
+    for (int r = 0; r < 2 * nRoots; r++) {
+      const int ch = r & 1;
+      if (ch == 0) {
+        lumaRootSplit = SPL_NONE;
+        lumaRootIsp = 0;
+      }
+      codingTree(roots[r >> 1], ch);
     }
   }
 

@@ -42,7 +42,11 @@ REF = "/root/reference"
 CXX_FLAGS = ("-include cstdint -Wno-deprecated-declarations -Wno-array-compare -Wno-address -Wno-error "
              f"-I{ROOT}/include -I{ROOT}/entropy_coding_b200/host -I{HERE}/vtm_record")
 CMDLINE = "-fr 60 -f 10 -wdt 176 -hgt 144 --InputChromaFormat=420 --InputBitDepth=8".split()
+# A larger picture for the CTU-level parser (tests/test_syntax.py): 416x240, one coded frame, QP 27 - eight 128x128
+# CTUs of which three are complete, so interior split decisions, more CU shapes and a realistic bin density.
+CMDLINE_WQVGA = "-fr 60 -f 1 -wdt 416 -hgt 240 --InputChromaFormat=420 --InputBitDepth=8".split()
 RUNS = {
+    "wqvga_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),
@@ -96,7 +100,11 @@ def build(work: str, patched: bool) -> str:
     return exe
 
 
-def encode(exe: str, rundir: str, clip: str, cfg: str, extra: list[str], record: bool) -> bytes:
+def cmdline_for(name: str) -> list[str]:
+    return CMDLINE_WQVGA if name.startswith("wqvga") else CMDLINE
+
+
+def encode(exe: str, rundir: str, clip: str, cfg: str, extra: list[str], record: bool, cmdline=None) -> bytes:
     os.makedirs(rundir, exist_ok=True)
     rec = os.path.join(rundir, "rec.bin")
     if record and os.path.exists(rec):
@@ -105,12 +113,12 @@ def encode(exe: str, rundir: str, clip: str, cfg: str, extra: list[str], record:
     if record:
         env["VTM_RECORD_OUT"] = rec
     with open(os.path.join(rundir, "enc.log"), "w") as log:
-        sh([exe, "-i", clip, "-c", os.path.join(REF, "test", cfg)] + CMDLINE + extra, cwd=rundir, env=env,
+        sh([exe, "-i", clip, "-c", os.path.join(REF, "test", cfg)] + (cmdline or CMDLINE) + extra, cwd=rundir, env=env,
            stdout=log, stderr=subprocess.STDOUT)
     return open(os.path.join(rundir, "str.bin"), "rb").read()
 
 
-def to_fixture(name: str, rundir: str, cfg: str, extra: list[str]) -> None:
+def to_fixture(name: str, rundir: str, cfg: str, extra: list[str], cmdline=None) -> None:
     from oracle.checker import SUB_ALIGN, SUB_TERMINATE, Checker
     ref = Checker("ref")
     subs = parse_records(os.path.join(rundir, "rec.bin"))
@@ -137,7 +145,7 @@ def to_fixture(name: str, rundir: str, cfg: str, extra: list[str]) -> None:
             est.append(np.zeros(1, np.uint64))
     extra_arrays = {"str_bin": strbin,
                     "str_bin_md5": np.frombuffer(hashlib.md5(strbin.tobytes()).hexdigest().encode(), np.uint8),
-                    "cmdline": np.frombuffer((cfg + " " + " ".join(CMDLINE + extra)).encode(), np.uint8)}
+                    "cmdline": np.frombuffer((cfg + " " + " ".join((cmdline or CMDLINE) + extra)).encode(), np.uint8)}
     for i, e in enumerate(est):
         extra_arrays[f"est{i}"] = e
     path = os.path.join(HERE, f"vtm_{name}.npz")
@@ -151,7 +159,7 @@ def to_fixture(name: str, rundir: str, cfg: str, extra: list[str]) -> None:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--work", default="/tmp/ec_vtm")
-    ap.add_argument("--only", default=",".join(RUNS))
+    ap.add_argument("--only", default=",".join(RUNS))  # qp0 and wqvga_qp27 take tens of minutes each
     ap.add_argument("--skip-encode", action="store_true", help="reuse <work>/<run>/rec.bin + str.bin")
     ap.add_argument("--verify-unpatched", action="store_true",
                     help="also build the unpatched tree and check str.bin is identical (qp51 only: minutes)")
@@ -160,13 +168,16 @@ def main():
     os.makedirs(a.work, exist_ok=True)
     clip = os.path.join(a.work, "synth_qcif.yuv")
     open(clip, "wb").write(synth_qcif())
+    clip_wqvga = os.path.join(a.work, "synth_wqvga.yuv")
+    open(clip_wqvga, "wb").write(synth_qcif(seed=2025, w=416, h=240, frames=1))
     exe = a.exe or (None if a.skip_encode else build(a.work, True))
     for name in a.only.split(","):
         cfg, extra = RUNS[name]
         rundir = os.path.join(a.work, name)
+        cl = cmdline_for(name)
         if not a.skip_encode:
-            encode(exe, rundir, clip, cfg, extra, True)
-        to_fixture(name, rundir, cfg, extra)
+            encode(exe, rundir, clip_wqvga if name.startswith("wqvga") else clip, cfg, extra, True, cl)
+        to_fixture(name, rundir, cfg, extra, cl)
     if a.verify_unpatched:
         orig = build(a.work, False)
         b0 = encode(orig, os.path.join(a.work, "qp51_orig"), clip, RUNS["qp51"][0], [], False)
