@@ -945,7 +945,9 @@ __device__ inline void storeCtxStates(const uint32_t *ctx, const cabac_substream
   }
 }
 
-template <int kMode>
+// kC16 (int16 slab, cabac_*_i16) is compile-time like the mode: as a run-time argument it cost the int32 headline
+// path 2.4 ms of 22.8 on the bench batch.
+template <int kMode, bool kC16 = false>
 __global__ void __launch_bounds__(kMode == FUSED_WS ? WS_THREADS : WARPS_PER_BLOCK * 32,
                                   kMode == FUSED_WS ? WS_MIN_CTAS : ENC_MIN_CTAS)
 encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
@@ -956,7 +958,8 @@ encode_residual_kernel(const cabac_tu_desc *__restrict__ tus, const uint64_t *__
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
                        uint64_t *__restrict__ estBits, uint64_t *__restrict__ estPerTu,
-                       uint32_t *__restrict__ ctxBins, const WppArgs wpp, const int c16) {
+                       uint32_t *__restrict__ ctxBins, const WppArgs wpp) {
+  constexpr bool c16 = kC16;
   constexpr bool kResolve = kMode == FUSED_RESOLVE;
   constexpr bool kEstimate = kMode == FUSED_ESTIMATE;
   constexpr bool kWs = kMode == FUSED_WS;
@@ -1579,6 +1582,10 @@ struct __align__(16) DecWarpSmem {
   uint4 ctx[RCTX];
 };
 
+// WPP (context hand-over between CTU rows) and C16 (int16 slab) are compile-time: the plain int32 launch - the
+// headline path - carries neither the per-block hand-over test nor the slab-type branch (with both as run-time
+// arguments the bench batch went from 35.7 to 39.6 ms).
+template <bool WPP, bool C16>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, DEC_MIN_CTAS)
 decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__ inOffsets,
                        const cabac_tu_desc *__restrict__ tus, const uint64_t *__restrict__ tuOffsets,
@@ -1587,7 +1594,7 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
                        uint32_t *__restrict__ numBins, uint32_t *__restrict__ bitsRead,
                        uint8_t *__restrict__ tuFlags, cabac_ctx_model *__restrict__ ctxOut,
                        uint32_t *__restrict__ status, const uint32_t *__restrict__ order, uint32_t *cursor,
-                       const WppArgs wpp, const int c16) {
+                       const WppArgs wpp) {
   __shared__ DecWarpSmem smem[WARPS_PER_BLOCK];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   DecWarpSmem &sm = smem[wib];
@@ -1595,16 +1602,20 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
   while (nextSubstream(order, cursor, nSub, lane, sub)) {
     const cabac_substream_params p = params[sub];
     uint32_t wppStatus = 0;
-    const cabac_ctx_model *ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane, wppStatus);
+    const cabac_ctx_model *ctxSrc;
+    if (WPP)
+      ctxSrc = ctxSource(p, ctxIn, sub, wpp, lane, wppStatus);
+    else
+      ctxSrc = ((p.flags & CABAC_SUB_CTX_IN) && ctxIn) ? ctxIn + sub * CABAC_NUM_CTX : nullptr;
     loadCtxEntries(sm.ctx, p, ctxSrc, lane);
     LsDecoder dec;  // identical on every lane
     dec.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
     dec.status |= wppStatus;
     const uint64_t t0 = tuOffsets[sub], t1 = tuOffsets[sub + 1];
-    bool wppPending = wpp.sync != nullptr;
+    bool wppPending = WPP && wpp.sync != nullptr;
     const uint64_t tSync = wppPending ? t0 + wpp.sync[sub].sync_tus : 0;
     for (uint64_t t = t0; t < t1; t++) {
-      if (wppPending && t >= tSync) {  // contexts after the first CTU: the row below starts from them
+      if (WPP && wppPending && t >= tSync) {  // contexts after the first CTU: the row below starts from them
         storeCtxEntries(sm.ctx, p, ctxSrc, wpp.snap + sub * CABAC_NUM_CTX, lane);
         wppPublish(wpp, sub, lane);
         wppPending = false;
@@ -1627,7 +1638,7 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       __syncwarp();
       // write the block back (the zero-out region of 64-point blocks as zeros)
       const int total = g.w * g.h;
-      if (c16) {  // int16 TCoeff slab (cabac_decode_residual_i16): levels are range-checked above
+      if (C16) {  // int16 TCoeff slab (cabac_decode_residual_i16): levels are range-checked above
         int16_t *dst = reinterpret_cast<int16_t *>(coeffs) + d.coeff_offset;
         for (int i = lane; i < total; i += 32) {
           const int y = i >> g.log2w, x = i & (g.w - 1);
@@ -1650,7 +1661,7 @@ decode_residual_kernel(const uint8_t *__restrict__ in, const uint64_t *__restric
       if (bitsRead) bitsRead[sub] = dec.bitsRead();
       if (status) status[sub] = dec.status;
     }
-    if (wppPending) {
+    if (WPP && wppPending) {
       storeCtxEntries(sm.ctx, p, ctxSrc, wpp.snap + sub * CABAC_NUM_CTX, lane);
       wppPublish(wpp, sub, lane);
     }
@@ -1881,27 +1892,35 @@ cudaError_t launchEncodeResidual(cudaStream_t s, int device, const Sched &sc, co
     if (sc.warpSpecialised && nSub < (size_t(1) << 27)) {
       static bool optedIn[64] = {};  // the > 48 KB dynamic shared memory opt-in is per device
       if (device < 0 || device >= 64 || !optedIn[device]) {
-        const cudaError_t attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS>,
-                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, int(WS_SMEM_BYTES));
+        cudaError_t attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS, false>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, int(WS_SMEM_BYTES));
+        if (attr != cudaSuccess) return attr;
+        attr = cudaFuncSetAttribute(encode_residual_kernel<FUSED_WS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    int(WS_SMEM_BYTES));
         if (attr != cudaSuccess) return attr;
         if (device >= 0 && device < 64) optedIn[device] = true;
       }
       int sms = 148;
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
       const size_t blocks = (nSub + WS_PRODUCERS - 1) / WS_PRODUCERS, cap = size_t(sms) * WS_MIN_CTAS;
-      encode_residual_kernel<FUSED_WS><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(
-          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
+#define WS_LAUNCH(C)                                                                                                 \
+  encode_residual_kernel<FUSED_WS, C><<<unsigned(blocks > cap ? cap : blocks), WS_THREADS, WS_SMEM_BYTES, s>>>(          \
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,                 \
+      status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp)
+      if (sc.coeff16) WS_LAUNCH(true); else WS_LAUNCH(false);
+#undef WS_LAUNCH
       return cudaGetLastError();
     }
-    if (sc.fusedResolve)
-      encode_residual_kernel<FUSED_RESOLVE><<<persistentGrid(encode_residual_kernel<FUSED_RESOLVE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
-    else
-      encode_residual_kernel<FUSED_LEGACY><<<persistentGrid(encode_residual_kernel<FUSED_LEGACY>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-          tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,
-          status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp, sc.coeff16 ? 1 : 0);
+#define FUSED_LAUNCH(M, C)                                                                                            \
+  encode_residual_kernel<M, C><<<persistentGrid(encode_residual_kernel<M, C>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>( \
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, out, outOffsets, outSizes, numBins, tuFlags, ctxOut,                  \
+      status ? status : sc.statusScratch, sc.wpp.sync ? nullptr : sc.order, sc.cursor, nullptr, nullptr, nullptr, sc.wpp)
+    if (sc.fusedResolve) {
+      if (sc.coeff16) FUSED_LAUNCH(FUSED_RESOLVE, true); else FUSED_LAUNCH(FUSED_RESOLVE, false);
+    } else {
+      if (sc.coeff16) FUSED_LAUNCH(FUSED_LEGACY, true); else FUSED_LAUNCH(FUSED_LEGACY, false);
+    }
+#undef FUSED_LAUNCH
     return cudaGetLastError();
   }
   produce_kernel<false, false><<<persistentGrid(produce_kernel<false, false>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
@@ -1927,9 +1946,13 @@ cudaError_t launchEstimateResidual(cudaStream_t s, int device, const Sched &sc, 
     const cudaError_t e = cudaMemsetAsync(ctxBins, 0, nSub * CABAC_NUM_CTX * sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
   }
-  encode_residual_kernel<FUSED_ESTIMATE><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,
-      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins, WppArgs(), sc.coeff16 ? 1 : 0);
+#define EST_LAUNCH(C)                                                                                                  \
+  encode_residual_kernel<FUSED_ESTIMATE, C><<<persistentGrid(encode_residual_kernel<FUSED_ESTIMATE, C>, nSub, device),     \
+                                              WARPS_PER_BLOCK * 32, 0, s>>>(                                             \
+      tus, tuOffsets, params, nSub, coeffs, ctxIn, nullptr, nullptr, nullptr, numBins, tuFlags, ctxOut,                  \
+      status ? status : sc.statusScratch, sc.order, sc.cursor, estBits, estPerTu, ctxBins, WppArgs())
+  if (sc.coeff16) EST_LAUNCH(true); else EST_LAUNCH(false);
+#undef EST_LAUNCH
   return cudaGetLastError();
 }
 
@@ -2043,9 +2066,16 @@ cudaError_t launchDecodeResidual(cudaStream_t s, int device, const Sched &sc, co
 #undef TD_LAUNCH
     return cudaGetLastError();
   }
-  decode_residual_kernel<<<persistentGrid(decode_residual_kernel, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>(
-      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,
-      (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp, sc.coeff16 ? 1 : 0);
+#define LS_LAUNCH(W, C)                                                                                            \
+  decode_residual_kernel<W, C><<<persistentGrid(decode_residual_kernel<W, C>, nSub, device), WARPS_PER_BLOCK * 32, 0, s>>>( \
+      in, inOffsets, tus, tuOffsets, params, nSub, ctxIn, coeffs, numBins, bitsRead, tuFlags, ctxOut, status,        \
+      (sc.wpp.sync && !(sc.wpp.debug & 4u)) ? nullptr : sc.order, sc.cursor, sc.wpp)
+  if (sc.wpp.sync) {
+    if (sc.coeff16) LS_LAUNCH(true, true); else LS_LAUNCH(true, false);
+  } else {
+    if (sc.coeff16) LS_LAUNCH(false, true); else LS_LAUNCH(false, false);
+  }
+#undef LS_LAUNCH
   return cudaGetLastError();
 }
 
