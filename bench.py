@@ -721,6 +721,90 @@ def leg_decode_sweep(args, r):
     return leg
 
 
+def leg_slice_decode(args, r):
+    """whole slices decoded from their bytes alone (cabac_decode_slices_dev: CTU-level syntax
+    + residuals on the device).  Input: the VTM-produced fixture slices of tests/golden/vtm_*.npz (real slice payloads
+    of the reference's encoder; QCIF and 416x240), replicated on the device to 64 / 8192 substreams per launch - the
+    same bytes many times over, so the figure is a kernel rate, not a statement about a particular video.  Every copy's
+    CU / TU counts, bin count and coefficients are compared with what the reference's writer recorded."""
+    import torch
+    import entropy_coding_b200 as E
+    from entropy_coding_b200.types import CTX_DT, PARAMS_DT, SL_WPP, SLICE_DT, SUB_CTX_IN, SUB_TERMINATE
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    from vtm_streams import load_fixture
+    import glob
+    eng, stream, dev = r["eng"], r["stream"], r["dev"]
+    items = []
+    for path in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "vtm_*.npz"))):
+        for s in load_fixture(os.path.basename(path))[0]:
+            if "slice" not in s or not len(s["slice"]):
+                continue
+            sp = s["slice"].astype(np.uint32).copy()
+            if int(sp[30]) & SL_WPP:
+                if int(sp[3]) != 0:
+                    continue
+                sp[30] &= ~np.uint32(SL_WPP)
+            items.append((s, sp.view(SLICE_DT)[0]))
+    if not items:
+        return {"unavailable": "no slice fixtures under tests/golden"}
+    rows = []
+    for n in (64, 8192):
+        order = [k % len(items) for k in range(n)]
+        params, sps, ctx_in = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT), np.zeros((n, 379), CTX_DT)
+        data, off = [], [0]
+        for j, k in enumerate(order):
+            s, sp = items[k]
+            params[j] = (s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)
+            sps[j] = sp
+            ctx_in[j]["state0"], ctx_in[j]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+            data.append(s["payload"])
+            off.append(off[-1] + s["payload"].size)
+        cap = E.CabacEngine.slice_capacities(sps)
+        d = {k: dev_bytes(dev, v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)),
+                                               ("p", params), ("sp", sps), ("ci", ctx_in), ("cu", cap["cu"]),
+                                               ("tu", cap["tu"]), ("ctu", cap["ctu"]), ("co", cap["coeff"]))}
+        cus = torch.empty(int(cap["cu"][-1]) * 24, dtype=torch.uint8, device=dev)
+        tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device=dev)
+        tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device=dev)
+        ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device=dev)
+        co = torch.zeros(int(cap["coeff"][-1]), dtype=torch.int32, device=dev)
+        cnt = torch.zeros(n * 3, dtype=torch.int32, device=dev)
+        nb = torch.zeros(n, dtype=torch.int32, device=dev)
+        st = torch.zeros(n, dtype=torch.int32, device=dev)
+
+        def dec():
+            eng.decode_slices_dev(d["in"], d["off"], d["p"], d["sp"], n, d["cu"], d["tu"], d["ctu"], d["co"], cus, tus, tuf,
+                                  ctus, co, counts=cnt, num_bins=nb, ctx_in=d["ci"], status=st)
+
+        t = _time_passes(stream, dec, warm=2, reps=3)
+        assert int(st.abs().max()) == 0, "slice decode status"
+        counts, bins_h, co_h = cnt.cpu().numpy().reshape(n, 3), nb.cpu().numpy(), co.cpu().numpy()
+        n_coeff = 0
+        for j, k in enumerate(order):
+            s, _ = items[k]
+            assert int(bins_h[j]) == s["num_bins"] and int(counts[j, 0]) == len(s["cus"]) and int(counts[j, 1]) == len(s["tus"])
+            k0 = int(cap["coeff"][j])
+            assert (co_h[k0:k0 + s["coeffs"].size] == s["coeffs"]).all(), f"slice copy {j}: coefficients"
+            n_coeff += s["coeffs"].size
+        bins = int(bins_h.astype(np.int64).sum())
+        alg = off[-1] + 4 * n_coeff + 16 * int(counts[:, 1].sum()) + 24 * int(counts[:, 0].sum())
+        row = {"substreams": n, "bins": bins, "bitstream_bytes": off[-1], "cus": int(counts[:, 0].sum()),
+               "tus": int(counts[:, 1].sum()), "coefficients_out": n_coeff, "decode_ms": t,
+               "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9}
+        row["hbm_frac"] = row["hbm_gbs"] / load_peaks()[0]
+        rows.append(row)
+        del cus, tus, tuf, ctus, co, cnt, nb, st, d
+        torch.cuda.empty_cache()
+    return {"config": "SURVEY section 8 f2 (the decode side of configs[0-1]): all-intra dual-tree slices decoded from the "
+                      "bytes alone; VTM-produced fixture slices replicated on the device",
+            "per_gpu": True, "points": rows, "api": "cabac_decode_slices_dev (decode_slice_kernel: one warp per slice)",
+            "fixture_slices": len(items),
+            "note": "64 slices per launch is the latency floor of one dependent chain per slice; 8192 fills the GPU. The "
+                    "fixture slices are sparse (0.1-0.3 bins per coefficient position, large blocks with few levels), so "
+                    "per-block work - zeroing and writing back whole blocks - weighs more here than in the headline batch",
+            "verified": "every copy: bin count, CU and TU counts and all coefficients == the reference writer's records"}
+
+
 def run_e2e(args, r, i16=False):
     """The same step through the host-pointer C ABI: pinned host buffers in, pinned host buffers out.
     i16: the coefficient slabs cross the ABI as int16 (cabac_*_i16) instead of the reference's int32 TCoeff."""
@@ -813,6 +897,7 @@ def main():
         legs["1080p_64_slices"] = r.get("leg_slices")
         legs["4k_wpp"] = leg_wpp(args, r)
         legs["decode_sweep"] = leg_decode_sweep(args, r)
+        legs["slice_decode"] = leg_slice_decode(args, r)
     if r["rank"] != 0:
         return
     peak, peak_src = load_peaks()
@@ -884,9 +969,10 @@ def main():
         "clocks": r["clk"], "gpu_launches": int(r["launches"]), "roofline": roof, "issue_roofline": issue,
         "verified": r["verified"],
         "host_placement": r.get("numa", "n/a"),
-        "decode_scope": "residual-only substreams: cabac_decode_residual parses substreams made of TUs; a real VVC slice "
-                        "interleaves non-residual syntax on the same arithmetic-decoder state (SURVEY section 8 row f2, not "
-                        "on the device yet), so the figure that drops into a codec today is encode_mbins_s",
+        "decode_scope": "the headline's decode half is cabac_decode_residual: substreams made of TUs only (the TU list is an "
+                        "input). A real VVC slice interleaves CTU-level syntax on the same arithmetic-decoder state: that "
+                        "path is cabac_decode_slices (SURVEY section 8 row f2, all-intra dual-tree slices), measured in "
+                        "configs.slice_decode on VTM-produced slices; encode_mbins_s drops into a codec as it is",
     }
     if legs:
         line["configs"] = legs

@@ -17,6 +17,7 @@
 
 #include "gpu_bin_encoder.hpp"
 #include "gpu_residual_reader.hpp"
+#include "gpu_slice_reader.hpp"
 #include "ref_harness.hpp"
 
 using namespace ref_harness;
@@ -88,6 +89,18 @@ bool sameCtx(const Ctx &a, const Ctx &b) {
 
 }  // namespace
 
+// The whole-slice decode shim must compile against the unmodified reference headers (its parity run needs real
+// slice payloads: tests/test_syntax.py on the VTM fixtures); an empty batch is flushed here.
+static void sliceReaderCompiles(cabac_b200::Engine &eng, const Common::CodingStructure *cs) {
+  cabac_b200::GpuSliceReader rd(eng);
+  if (cs && cs->pps) {  // the harness builds no PPS: never taken, only instantiated
+    const cabac_slice_params sp = cabac_b200::sliceParams(*cs, 0, 0, 128, 128);
+    const uint8_t none[2] = {0, 0};
+    rd.add(none, 2, *cs, 32, 2, sp);
+  }
+  rd.flush();
+}
+
 int main(int argc, char **argv) {
   const int nSub = argc > 1 ? atoi(argv[1]) : 96;
   const unsigned seed = argc > 2 ? unsigned(atoi(argv[2])) : 7u;
@@ -124,6 +137,7 @@ int main(int argc, char **argv) {
   }
 
   Engine eng(0);
+  sliceReaderCompiles(eng, nullptr);
   GpuEncodeSession sessBins(eng), sessTu(eng);
   std::vector<std::unique_ptr<GpuBinEncoder>> encB1, encB2;
   std::vector<std::unique_ptr<OutputBitstream>> bsB1, bsB2;
