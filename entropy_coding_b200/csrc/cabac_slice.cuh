@@ -25,6 +25,7 @@ struct __align__(16) SliceWarpSmem {
   LsDecoder dec;  // the arithmetic decoder's state: identical on all lanes, kept here between calls (see sliceBin)
   int32_t tile[32 * 32];
   uint4 ctx[CABAC_NUM_CTX];  // [0, RCTX): residual contexts in rctx() order; [RCTX, 379): the others
+  uint32_t rowCtx[CABAC_NUM_CTX];  // WPP: the states (entry .x) after the first CTU of the current row
   uint16_t above[2][SLICE_MAX_LINE];
   uint16_t left[2][32];
   uint8_t ctuLine[SLICE_MAX_CTU_COLS];
@@ -180,6 +181,34 @@ struct SliceEngine {
     if (lane == 0 && ctus) ctus[i] = c;
     __syncwarp();
   }
+  // WPP row hand-over (see SliceParser::run)
+  __device__ __forceinline__ void saveRowContexts() {
+    __syncwarp();
+    for (int k = lane; k < CABAC_NUM_CTX; k += 32) sm.rowCtx[k] = sm.ctx[k].x;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void nextRow() {
+    __syncwarp();
+    const LsDecoder old = sm.dec;
+    const uint32_t used = rowStart + (old.bitsRead() >> 3) + 1u;  // the row's bytes: floor(bits / 8) + 1
+    for (int k = lane; k < CABAC_NUM_CTX; k += 32) sm.ctx[k].x = sm.rowCtx[k];
+    __syncwarp();
+    LsDecoder d;
+    if (used >= sliceBytes) {
+      d = old;
+      d.status |= CABAC_SS_IN_OVERRUN;
+      dead = true;
+    } else {
+      d.start(sliceIn + used, sliceBytes - used);
+      d.status = old.status;
+      d.nbins = old.nbins;
+      rowStart = used;
+    }
+    sm.dec = d;
+    __syncwarp();
+  }
+  const uint8_t *sliceIn = nullptr;
+  uint32_t sliceBytes = 0, rowStart = 0;
   __device__ __forceinline__ void abort() { dead = true; }
   __device__ __forceinline__ bool aborted() const { return dead; }
 };
@@ -215,7 +244,9 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
                     ctus ? ctus + ctu0 : nullptr, coeffs);
     {
       LsDecoder d0;
-      d0.start(in + inOffsets[sub], uint32_t(inOffsets[sub + 1] - inOffsets[sub]));
+      eng.sliceIn = in + inOffsets[sub];
+      eng.sliceBytes = uint32_t(inOffsets[sub + 1] - inOffsets[sub]);
+      d0.start(eng.sliceIn, eng.sliceBytes);
       sm.dec = d0;
       __syncwarp();
     }
@@ -240,7 +271,7 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
         counts[3 * sub + 2] = uint32_t(ps.nCoeff);
       }
       if (numBins) numBins[sub] = dEnd.nbins;
-      if (bitsRead) bitsRead[sub] = dEnd.bitsRead();
+      if (bitsRead) bitsRead[sub] = 8u * eng.rowStart + dEnd.bitsRead();
       if (status) status[sub] = dEnd.status | ps.status;
     }
     if (ctxOut) {

@@ -816,9 +816,15 @@ struct SliceParser {
     }
   }
 
-  // ---- the substream: its CTUs in raster order inside the rectangle, then the terminating bin ----
+  // ---- the substream: its CTUs in raster order inside the rectangle, then the terminating bin.
+  //      With entropy coding sync (WPP) the slice's bytes are its CTU-row substreams back to back
+  //      (EncSlice.cpp:2110-2125): every row ends with end_of_subset_one_bit + byte alignment, the next row
+  //      restarts the arithmetic decoder at the next byte (the decoder has then read exactly through the row's
+  //      last byte: BinDecoderBase::finish, arith_codec.cpp:68-73) and starts from the contexts saved after the
+  //      FIRST CTU of the row above (DecSlice.cpp:194-210, 241-245).  Rows are walked one after the other by the
+  //      same warp: neighbour lines carry over, so above-neighbours are available as inside any slice. ----
   SX_FN void run(bool terminate) {
-    const uint32_t refuse = CABAC_SL_IBC | CABAC_SL_PLT | CABAC_SL_ACT | CABAC_SL_WPP;
+    const uint32_t refuse = CABAC_SL_IBC | CABAC_SL_PLT | CABAC_SL_ACT;
     if ((sp.tools & refuse) || !tool(CABAC_SL_INTRA) || !tool(CABAC_SL_DUAL_TREE) || sp.chroma_format != 1 ||
         sp.log2_ctu < 5 || sp.log2_ctu > 7 || ((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SX_MAX_LINE) || sp.x1 <= sp.x0 ||
         sp.y1 <= sp.y0 || sp.x1 > sp.pic_w || sp.y1 > sp.pic_h || sp.log2_max_tb < 5 || sp.log2_max_tb > 6) {
@@ -826,9 +832,20 @@ struct SliceParser {
       return;
     }
     const int ctu = 1 << sp.log2_ctu;
+    const bool wpp = tool(CABAC_SL_WPP);
     for (int y = int(sp.y0); y < int(sp.y1) && !e.aborted(); y += ctu) {
+      if (wpp && y > int(sp.y0)) {
+        if (!e.trm()) {  // end_of_subset_one_bit
+          status |= CABAC_SS_NO_TERMINATE;
+          return;
+        }
+        e.nextRow();  // byte-aligned restart + contexts of the row above after its first CTU
+      }
       leftCtuFlags = 0;
-      for (int x = int(sp.x0); x < int(sp.x1) && !e.aborted(); x += ctu) codingTreeUnit(x, y);
+      for (int x = int(sp.x0); x < int(sp.x1) && !e.aborted(); x += ctu) {
+        codingTreeUnit(x, y);
+        if (wpp && x == int(sp.x0)) e.saveRowContexts();
+      }
     }
     if (terminate && !e.aborted() && !e.trm()) status |= CABAC_SS_NO_TERMINATE;
   }

@@ -729,7 +729,9 @@ enum { /* cabac_slice_params.tools */
   CABAC_SL_CCLM = 1 << 16,
   CABAC_SL_DQP = 1 << 17,        /* pps.getUseDQP()                                             */
   CABAC_SL_CHROMA_QP_ADJ = 1 << 18,
-  CABAC_SL_WPP = 1 << 19,        /* entropy coding sync: refused (rows of one slice)            */
+  CABAC_SL_WPP = 1 << 19,        /* entropy coding sync: the substream's bytes are the slice's
+                                    CTU-row substreams back to back; rows are parsed one after
+                                    the other with the context hand-over of DecSlice.cpp:194-245 */
   CABAC_SL_IBC = 1 << 20,        /* refused                                                     */
   CABAC_SL_PLT = 1 << 21,        /* refused                                                     */
   CABAC_SL_ACT = 1 << 22,        /* refused                                                     */
@@ -810,7 +812,7 @@ typedef struct cabac_ctu_desc {
 } cabac_ctu_desc;
 
 #define CABAC_SS_UNSUPPORTED 256 /* cabac_decode_slices: a tool outside the built scope (P / B
-                                    slice, single tree, IBC, palette, ACT, WPP, non-4:2:0)      */
+                                    slice, single tree, IBC, palette, ACT, non-4:2:0)           */
 #define CABAC_SS_CAPACITY 512    /* cabac_decode_slices: a record or coefficient region is full */
 
 /* Capacities: substream i may write cus[cu_offsets[i] .. cu_offsets[i+1]), likewise tus / ctus /

@@ -1556,6 +1556,18 @@ void orc_dec_tu(void *hv, const cabac_tu_desc *tu, int32_t *coeffs, uint8_t *tuF
   memset(coeffs + tu->coeff_offset, 0, sizeof(int32_t) << (tu->log2_w + tu->log2_h));
   r_residual_coding(&h->d, &h->ct, tu, coeffs, h->p.flags, tuFlags);
 }
+/* WPP rows inside one slice: restart the arithmetic decoder on the next row's bytes (contexts stay), and
+ * snapshot / restore the contexts (Ctx::operator=, contexts.cpp:1096-1108). */
+long orc_dec_bits(void *hv) { return dec_bits_read(&((OrcDecHandle *)hv)->d); }
+void orc_dec_restart(void *hv, const uint8_t *in, long n) {
+  OrcDecHandle *h = (OrcDecHandle *)hv;
+  const uint32_t st = h->d.status, nb = h->d.nbins;
+  dec_start(&h->d, in, n);
+  h->d.status = st;
+  h->d.nbins = nb;
+}
+void orc_dec_ctx_get(void *hv, cabac_ctx_model *out) { memcpy(out, ((OrcDecHandle *)hv)->ct.m, sizeof(((OrcDecHandle *)hv)->ct.m)); }
+void orc_dec_ctx_set(void *hv, const cabac_ctx_model *in) { memcpy(((OrcDecHandle *)hv)->ct.m, in, sizeof(((OrcDecHandle *)hv)->ct.m)); }
 long orc_dec_close(void *hv, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t *numBins) {
   OrcDecHandle *h = (OrcDecHandle *)hv;
   if (ctxOut) memcpy(ctxOut, h->ct.m, sizeof(h->ct.m));

@@ -59,5 +59,9 @@ unsigned orc_dec_bin(void *h, unsigned ctxId);
 unsigned orc_dec_ep(void *h, unsigned n);
 unsigned orc_dec_trm(void *h);
 void orc_dec_tu(void *h, const cabac_tu_desc *tu, int32_t *coeffs, uint8_t *tuFlags);
+long orc_dec_bits(void *h);
+void orc_dec_restart(void *h, const uint8_t *in, long n);
+void orc_dec_ctx_get(void *h, cabac_ctx_model *out);
+void orc_dec_ctx_set(void *h, const cabac_ctx_model *in);
 long orc_dec_close(void *h, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t *numBins);
 #endif

@@ -64,6 +64,21 @@ struct HostEngine {
   }
   void putCu(uint32_t i, const cabac_cu_desc &c) { cusOut[i] = c; }
   void putCtu(uint32_t i, const cabac_ctu_desc &c) { ctusOut[i] = c; }
+  // WPP rows (SliceParser::run)
+  const uint8_t *sliceIn = nullptr;
+  long sliceBytes = 0, rowStart = 0;
+  cabac_ctx_model rowCtx[CABAC_NUM_CTX];
+  void saveRowContexts() { orc_dec_ctx_get(dec, rowCtx); }
+  void nextRow() {
+    const long used = rowStart + (orc_dec_bits(dec) >> 3) + 1;
+    orc_dec_ctx_set(dec, rowCtx);
+    if (used >= sliceBytes) {
+      dead = true;
+      return;
+    }
+    orc_dec_restart(dec, sliceIn + used, sliceBytes - used);
+    rowStart = used;
+  }
   void abort() { dead = true; }
   bool aborted() const { return dead; }
 };
@@ -82,6 +97,8 @@ long syn_decode_slice(const uint8_t *in, long nbytes, const cabac_substream_para
                       long traceCap, long *nTrace) {
   HostEngine e;
   e.dec = orc_dec_open(in, nbytes, p, ctxIn);
+  e.sliceIn = in;
+  e.sliceBytes = nbytes;
   for (int ch = 0; ch < 2; ch++) {
     e.above[ch].assign(cabac_syntax::SX_MAX_LINE, 0);
     e.left[ch].assign(32, 0);
@@ -99,7 +116,7 @@ long syn_decode_slice(const uint8_t *in, long nbytes, const cabac_substream_para
   counts[1] = ps.nTu;
   counts[2] = uint32_t(ps.nCoeff);
   uint32_t st = 0;
-  const long bits = orc_dec_close(e.dec, ctxOut, &st, numBins);
+  const long bits = 8 * e.rowStart + orc_dec_close(e.dec, ctxOut, &st, numBins);
   *status = st | ps.status;
   *nTrace = long(e.trace.size());
   for (long i = 0; i < *nTrace && i < traceCap; i++) trace[i] = e.trace[size_t(i)];

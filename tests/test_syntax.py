@@ -34,22 +34,51 @@ from entropy_coding_b200.types import (CTU_DT, CTX_DT, CU_DT, CU_MIP, CU_MIP_TRA
 FIXTURES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(HERE, "golden", "vtm_*.npz")))
 
 
+def _merge_rows(rows):
+    """The CTU-row substreams of one WPP slice back to back, as they lie in the slice data."""
+    m = dict(rows[0])
+    for k in ("payload", "cmds", "coeffs", "cus"):
+        m[k] = np.concatenate([r[k] for r in rows])
+    tus, base = [], 0
+    for r in rows:
+        t = r["tus"].copy()
+        t["coeff_offset"] += base
+        base += r["coeffs"].size
+        tus.append(t)
+    m["tus"] = np.concatenate(tus)
+    m["num_bins"] = sum(r["num_bins"] for r in rows)
+    m["ctx_out"] = rows[-1]["ctx_out"]
+    m["row_bytes"] = [int(r["payload"].size) for r in rows]
+    sp = rows[0]["slice"].astype(np.uint32).copy()
+    sp[5] = rows[-1]["slice"][5]  # y1
+    m["slice"] = sp
+    return m
+
+
 def _substreams():
-    """Every fixture substream the built scope covers: slices (whole frames) and, of the WPP fixture, the
-    first CTU row of each frame (rows below need the row above as neighbour: one slice over several
-    substreams is outside cabac_decode_slices)."""
+    """Every fixture substream the built scope covers: slices (whole frames); of the WPP fixture each frame as ONE
+    slice of three CTU-row substreams (contexts handed over after the first CTU of the row above), and the first
+    row of each frame on its own as a plain 64x64-CTU slice."""
     out = []
     for name in FIXTURES:
         subs, _ = load_fixture(name)
-        for i, s in enumerate(subs):
-            if "slice" not in s or not len(s["slice"]):
-                continue
+        subs = [s for s in subs if "slice" in s and len(s["slice"])]
+        i = 0
+        while i < len(subs):
+            s = subs[i]
             sp = s["slice"].astype(np.uint32).copy()
             if int(sp[30]) & SL_WPP:
-                if int(sp[3]) != 0:
-                    continue
+                j = i + 1
+                while j < len(subs) and int(subs[j]["slice"][3]) != 0:
+                    j += 1
+                m = _merge_rows(subs[i:j])
+                out.append((f"{name}:{i}-{j - 1}(wpp)", m, m["slice"].view(SLICE_DT)[0]))
                 sp[30] &= ~np.uint32(SL_WPP)
-            out.append((f"{name}:{i}", s, sp.view(SLICE_DT)[0]))
+                out.append((f"{name}:{i}(row0)", s, sp.view(SLICE_DT)[0]))
+                i = j
+            else:
+                out.append((f"{name}:{i}", s, sp.view(SLICE_DT)[0]))
+                i += 1
     return out
 
 
@@ -175,7 +204,7 @@ def test_host_parser_issues_the_writers_call_sequence():
 def test_host_parser_refuses_what_is_out_of_scope():
     lib = _host_lib()
     tag, s, sp = _substreams()[0]
-    for bit in (19, 20, 21, 22):  # WPP rows, IBC, palette, ACT
+    for bit in (20, 21, 22):  # IBC, palette, ACT
         sp2 = sp.copy()
         sp2["tools"] |= np.uint32(1 << bit)
         assert _host_decode(lib, s, sp2)["status"] & SS_UNSUPPORTED

@@ -34,3 +34,34 @@ for n in (64, 1024, 8192, 65536):
     ms=e0.elapsed_time(e1)/5
     assert int(st.abs().sum())==0 and int(nb.sum())==bins
     print(f"decode_slices n={n}: {ms:.3f} ms, {bins/ms/1e6:.3f} Gbins/s, {off[-1]/ms/1e6:.3f} GB/s in, coeff out {int(cap['coeff'][-1])*4/ms/1e6:.1f} GB/s cap", flush=True)
+
+# Reference point: the SAME blocks as residual-only substreams through the lockstep residual decoder
+# (cabac_decode_residual_dev, TU list as input) - what the per-block work costs without the CTU-level parser.
+from entropy_coding_b200.types import TU_DT, SUB_ALIGN
+for n in (8192,):
+    order=[k%len(items) for k in range(n)]
+    tus=[];tuoff=[0];par=np.zeros(n,PARAMS_DT);coeffs=[];cbase=0
+    for j,k in enumerate(order):
+        tag,s,sp=items[k]
+        t=s['tus'].copy(); t['coeff_offset']+=cbase; t['flags']&=~np.uint8(0)  # flags as recorded (TS decided)
+        tus.append(t); tuoff.append(tuoff[-1]+len(t)); coeffs.append(s['coeffs']); cbase+=s['coeffs'].size
+        par[j]=(s['qp'],s['init_id'],(s['flags']&7)|SUB_TERMINATE|SUB_ALIGN,0)
+    tus=np.concatenate(tus); coeffs=np.concatenate(coeffs).astype(np.int32); tuoff=np.asarray(tuoff,np.uint64)
+    cap=np.concatenate([[0],np.cumsum([max(64,int(items[k][1]['payload'].size*2+64)) for k in order])]).astype(np.uint64)
+    r=eng.encode_residual(tus,tuoff,par,coeffs,cap)
+    sizes=r['sizes'].astype(np.int64); ent=np.concatenate([[0],np.cumsum(sizes)]).astype(np.uint64)
+    packed=np.concatenate([r['out'][int(cap[i]):int(cap[i])+int(sizes[i])] for i in range(n)])
+    bins=int(r['num_bins'].astype(np.int64).sum())
+    dev=lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()
+    d_in,d_ent,d_tus,d_tuoff,d_par=dev(packed),dev(ent),dev(tus),dev(tuoff),dev(par)
+    d_co=torch.zeros(coeffs.size,dtype=torch.int32,device='cuda'); d_nb=torch.zeros(n,dtype=torch.int32,device='cuda'); d_st=torch.zeros(n,dtype=torch.int32,device='cuda')
+    def run2(): eng.decode_residual_dev(d_in,d_ent,d_tus,d_tuoff,d_par,n,d_co,d_nb,status=d_st)
+    for _ in range(3): run2()
+    torch.cuda.synchronize()
+    e0,e1=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5): run2()
+    e1.record(); torch.cuda.synchronize()
+    ms=e0.elapsed_time(e1)/5
+    assert int(d_st.abs().sum())==0 and bool((d_co.cpu().numpy()==coeffs).all())
+    print(f"decode_residual (same blocks, residual-only substreams) n={n}: {ms:.3f} ms, {bins/ms/1e6:.3f} Gbins/s ({bins} residual bins)", flush=True)
