@@ -13,6 +13,8 @@
 // substream cannot be spread over more than one warp; the launch is parallel over substreams only and a
 // batch of few, long slices is latency-bound.
 #pragma once
+#include <new>
+
 #include "cabac_syntax.cuh"
 
 namespace cabac {
@@ -122,7 +124,6 @@ __device__ uint32_t g_sliceTraceN[2];
 struct SliceEngine {
   bool traceOn = false;
   SliceWarpSmem &sm;
-  const int lane;
   const uint32_t subFlags;
   cabac_cu_desc *cus;
   cabac_tu_desc *tus;
@@ -131,26 +132,37 @@ struct SliceEngine {
   int32_t *coeffs;
   bool dead = false;
 
-  __device__ __forceinline__ SliceEngine(SliceWarpSmem &s, int l, uint32_t f, cabac_cu_desc *c, cabac_tu_desc *t,
-                                         uint8_t *tf, cabac_ctu_desc *ct, int32_t *co)
-      : sm(s), lane(l), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
+  // The engine object itself sits in shared memory, one per warp, written identically by all lanes - so nothing in
+  // it may depend on the lane.
+  __device__ __forceinline__ SliceEngine(SliceWarpSmem &s, uint32_t f, cabac_cu_desc *c, cabac_tu_desc *t, uint8_t *tf,
+                                         cabac_ctu_desc *ct, int32_t *co)
+      : sm(s), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
+  __device__ __forceinline__ static int laneId() { return int(threadIdx.x & 31u); }
 
   __device__ __forceinline__ uint32_t bin(int id) {
+    const int lane = laneId();
+    (void)lane;
     const uint32_t b = sliceBin(&sm, sliceCtxSlot(id));
     SLICE_TRACE(CABAC_MK_CTX(id, b));
     return b;
   }
   __device__ __forceinline__ uint32_t ep(int n) {
+    const int lane = laneId();
+    (void)lane;
     const uint32_t v = sliceEp(&sm, n);
     SLICE_TRACE(CABAC_MK_EP(v, n));
     return v;
   }
   __device__ __forceinline__ uint32_t trm() {
+    const int lane = laneId();
+    (void)lane;
     const uint32_t b = sliceTrm(&sm);
     SLICE_TRACE(CABAC_MK_TRM(b));
     return b;
   }
   __device__ __forceinline__ uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
+    const int lane = laneId();
+    (void)lane;
     const uint32_t res = sliceResidual(&sm, d, subFlags, coeffs, lane);
     SLICE_TRACE(CABAC_MK_TU() | sm.dec.nbins);
     if (lane == 0) {
@@ -166,28 +178,40 @@ struct SliceEngine {
   __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.left[ch]; }
   __device__ __forceinline__ uint8_t *ctuLine() { return sm.ctuLine; }
   __device__ __forceinline__ void ctuLineStore(int col, uint8_t v) {
+    const int lane = laneId();
+    (void)lane;
     if (lane == 0 && col < SLICE_MAX_CTU_COLS) sm.ctuLine[col] = v;
     __syncwarp();
   }
   __device__ __forceinline__ void fill(uint16_t *p, int n, uint16_t v) {
+    const int lane = laneId();
+    (void)lane;
     for (int i = lane; i < n; i += 32) p[i] = v;
     __syncwarp();
   }
   __device__ __forceinline__ void putCu(uint32_t i, const cabac_cu_desc &c) {
+    const int lane = laneId();
+    (void)lane;
     if (lane == 0 && cus) cus[i] = c;
     __syncwarp();
   }
   __device__ __forceinline__ void putCtu(uint32_t i, const cabac_ctu_desc &c) {
+    const int lane = laneId();
+    (void)lane;
     if (lane == 0 && ctus) ctus[i] = c;
     __syncwarp();
   }
   // WPP row hand-over (see SliceParser::run)
   __device__ __forceinline__ void saveRowContexts() {
+    const int lane = laneId();
+    (void)lane;
     __syncwarp();
     for (int k = lane; k < CABAC_NUM_CTX; k += 32) sm.rowCtx[k] = sm.ctx[k].x;
     __syncwarp();
   }
   __device__ __forceinline__ void nextRow() {
+    const int lane = laneId();
+    (void)lane;
     __syncwarp();
     const LsDecoder old = sm.dec;
     const uint32_t used = rowStart + (old.bitsRead() >> 3) + 1u;  // the row's bytes: floor(bits / 8) + 1
@@ -224,7 +248,12 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
                     int32_t *__restrict__ coeffs, uint32_t *__restrict__ counts, uint32_t *__restrict__ numBins,
                     uint32_t *__restrict__ bitsRead, cabac_ctx_model *__restrict__ ctxOut, uint32_t *__restrict__ status,
                     const uint32_t *__restrict__ order, uint32_t *cursor) {
+  using Parser = cabac_syntax::SliceParser<SliceEngine>;
   __shared__ SliceWarpSmem smem[SLICE_WARPS_PER_BLOCK];
+  // engine + parser objects: one copy per warp in shared memory (all lanes write the same values), instead of 32
+  // per-lane copies in local memory - 12 resident warps x 32 lanes of stack no longer compete for the L1
+  __shared__ __align__(16) unsigned char engBuf[SLICE_WARPS_PER_BLOCK][(sizeof(SliceEngine) + 15) & ~size_t(15)];
+  __shared__ __align__(16) unsigned char psBuf[SLICE_WARPS_PER_BLOCK][(sizeof(Parser) + 15) & ~size_t(15)];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   SliceWarpSmem &sm = smem[wib];
   size_t sub;
@@ -240,8 +269,10 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
     }
     __syncwarp();
     const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub], co0 = coeffOffsets[sub];
-    SliceEngine eng(sm, lane, p.flags, cus ? cus + cu0 : nullptr, tus + tu0, tuFlags ? tuFlags + tu0 : nullptr,
-                    ctus ? ctus + ctu0 : nullptr, coeffs);
+    __syncwarp();
+    SliceEngine &eng = *new (engBuf[wib]) SliceEngine(sm, p.flags, cus ? cus + cu0 : nullptr, tus + tu0,
+                                                      tuFlags ? tuFlags + tu0 : nullptr, ctus ? ctus + ctu0 : nullptr, coeffs);
+    __syncwarp();
     {
       LsDecoder d0;
       eng.sliceIn = in + inOffsets[sub];
@@ -254,8 +285,9 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
     eng.traceOn = sub == 0;
     if (sub == 0 && lane == 0) g_sliceTraceN[0] = g_sliceTraceN[1] = 0;
 #endif
-    cabac_syntax::SliceParser<SliceEngine> ps(eng, sp, uint32_t(cuOffsets[sub + 1] - cu0), uint32_t(tuOffsets[sub + 1] - tu0),
-                                              uint32_t(ctuOffsets[sub + 1] - ctu0), coeffOffsets[sub + 1] - co0, co0);
+    Parser &ps = *new (psBuf[wib]) Parser(eng, sp, uint32_t(cuOffsets[sub + 1] - cu0), uint32_t(tuOffsets[sub + 1] - tu0),
+                                          uint32_t(ctuOffsets[sub + 1] - ctu0), coeffOffsets[sub + 1] - co0, co0);
+    __syncwarp();
     if (((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SLICE_MAX_LINE) ||
         ((sp.x1 - sp.x0) >> sp.log2_ctu) >= uint32_t(SLICE_MAX_CTU_COLS))
       ps.status |= CABAC_SS_UNSUPPORTED;

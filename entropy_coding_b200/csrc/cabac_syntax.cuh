@@ -124,8 +124,15 @@ struct Node {  // one level of the coding tree: an area and the partitioner's de
 
 template <class E>
 struct SliceParser {
+  // The parser's whole state lives in this object - no arrays or records on the stack - so that the device can
+  // keep ONE copy per warp in shared memory (cabac_slice.cuh) instead of 32 identical per-lane copies in local
+  // memory: all lanes hold the same values, and a noinline bin call then has little live state to save around it.
   E &e;
-  const cabac_slice_params &sp;
+  const cabac_slice_params sp;
+  Node st[SX_MAX_DEPTH];  // coding_tree: the explicit recursion stack
+  Node roots[4];          // the trees of the current CTU
+  cabac_cu_desc cuRec;    // the CU being parsed
+  cabac_ctu_desc ctuRec;  // the CTU being parsed
   uint32_t nCu = 0, nTu = 0, nCtu = 0;
   uint64_t nCoeff = 0;
   uint32_t status = 0;
@@ -372,7 +379,6 @@ struct SliceParser {
 
   // ---- coding_tree (:429-655) for one tree (ch = 0 luma, 1 chroma) rooted at `root` ----
   SX_FN void codingTree(Node root, int ch) {
-    Node st[SX_MAX_DEPTH];
     int sp_ = 0;
     root.next = -1;
     st[0] = root;
@@ -436,7 +442,7 @@ struct SliceParser {
 
   // ---- coding_unit (:764-825) + cu_pred_data (:1097) + cu_residual (:1396) for an intra CU ----
   SX_FN void codingUnit(const Node &n, int ch, const Node *st, int depth) {
-    cabac_cu_desc cu;
+    cabac_cu_desc &cu = cuRec;
     cu.x = uint16_t(n.x);
     cu.y = uint16_t(n.y);
     cu.log2_w = n.log2w;
@@ -715,7 +721,7 @@ struct SliceParser {
 
   // ---- coding_tree_unit :103-209 ----
   SX_FN void codingTreeUnit(int ctuX, int ctuY) {
-    cabac_ctu_desc c;
+    cabac_ctu_desc &c = ctuRec;
     for (int i = 0; i < 3; i++) {
       c.sao_mode[i] = c.sao_type[i] = c.sao_band[i] = 0;
       c.alf_flag[i] = 0;
@@ -792,7 +798,6 @@ struct SliceParser {
     // alternate per 64x64 node (:464-517; split_cu_mode of the 128x128 node reads nothing: canNo = false, only QT
     // possible); otherwise the luma tree of the CTU is followed by its chroma tree (:196-208).  One loop, so the
     // tree walk - the whole CU parser - is instantiated once and its state stays in registers.
-    Node roots[4];
     int nRoots = 0;
     if (sp.log2_ctu > 6) {
       if (tool(CABAC_SL_DQP)) isDqpCoded = false;
