@@ -47,6 +47,9 @@ CMDLINE = "-fr 60 -f 10 -wdt 176 -hgt 144 --InputChromaFormat=420 --InputBitDept
 CMDLINE_WQVGA = "-fr 60 -f 1 -wdt 416 -hgt 240 --InputChromaFormat=420 --InputBitDepth=8".split()
 RUNS = {
     "wqvga_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27"]),
+    # tools the three cfgs leave off but the CTU-level parser implements: cu_qp_delta (perceptual QP adaptation
+    # turns pps.useDQP on, one quantisation group per CTU) and BDPCM (intra_bdpcm_*_flag, the cbf contexts under BDPCM)
+    "dqp_bdpcm_qp32": ("encoder_intra_vtm_qp32.cfg", ["--PerceptQPA=1", "--BDPCM=1"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),
