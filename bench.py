@@ -795,6 +795,68 @@ def leg_slice_decode(args, r):
         rows.append(row)
         del cus, tus, tuf, ctus, co, cnt, nb, st, d
         torch.cuda.empty_cache()
+    cpu = None
+    if r["rank"] == 0 and not args.no_cpu_baseline:
+        cpu = _cpu_slice_decode(items)
+    leg = _slice_leg(rows, items)
+    if cpu:
+        leg["cpu_baseline"] = cpu
+    return leg
+
+
+def _cpu_slice_decode(items):
+    """CPU figure beside the slice decoder: the same slices through oracle/libsyntax_host.so (the CTU-level walk on
+    the oracle's scalar arithmetic / residual decoder), every host thread decoding copies for about ten seconds.
+    kind "port": the reference's own CABACReader::coding_tree_unit needs VTM's CodingStructure / Picture around it
+    and is not drivable from flat inputs."""
+    import ctypes as C
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+    path = os.path.join(ROOT, "oracle", "libsyntax_host.so")
+    if not os.path.exists(path):
+        return None
+    from entropy_coding_b200.types import CTU_DT, CTX_DT, CU_DT, PARAMS_DT, SLICE_DT, SUB_CTX_IN, SUB_TERMINATE, TU_DT
+    lib = C.CDLL(path)
+    lib.syn_decode_slice.restype = C.c_long
+    threads = host_threads()
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p)
+
+    def worker(tid, deadline):
+        bins = 0
+        bufs = {}
+        while time.perf_counter() < deadline:
+            for k, (s, sp) in enumerate(items):
+                if k not in bufs:
+                    area = int(sp["x1"] - sp["x0"]) * int(sp["y1"] - sp["y0"])
+                    cap = area // 16 * 2 + 8
+                    ci = np.zeros(379, CTX_DT)
+                    ci["state0"], ci["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+                    bufs[k] = (np.array([(s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)], PARAMS_DT),
+                               np.array([sp], SLICE_DT), ci, np.zeros(cap, CU_DT), np.zeros(cap, TU_DT),
+                               np.zeros(cap, np.uint8), np.zeros(64, CTU_DT), np.zeros(area * 3 // 2 + 64, np.int32),
+                               np.zeros(3, np.uint32), np.zeros(1, np.uint32), np.zeros(379, CTX_DT),
+                               np.zeros(1, np.uint32), np.zeros(1 << 16, np.uint32), np.ascontiguousarray(s["payload"]), cap)
+                par, spa, ci, cus, tus, tuf, ctus, co, cnt, nb, cout, st, tr, pay, cap = bufs[k]
+                nt = C.c_long(0)
+                lib.syn_decode_slice(p(pay), C.c_long(pay.size), p(par), p(spa), p(ci), p(cus), C.c_long(cap), p(tus), p(tuf),
+                                     C.c_long(cap), p(ctus), C.c_long(64), p(co), C.c_long(co.size), p(cnt), p(nb), p(cout),
+                                     p(st), p(tr), C.c_long(tr.size), C.byref(nt))
+                assert int(st[0]) == 0 and int(nb[0]) == s["num_bins"]
+                bins += int(nb[0])
+        return bins
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        done = list(ex.map(lambda t: worker(t, t0 + 8.0), range(threads)))
+    dt = time.perf_counter() - t0
+    return {"value": sum(done) / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"the {len(items)} fixture slices decoded over and over for {dt:.1f} s on {threads} threads "
+                      "(oracle/libsyntax_host.so: the CTU-level walk on the oracle's scalar decoder)"}
+
+
+def _slice_leg(rows, items):
     return {"config": "SURVEY section 8 f2 (the decode side of configs[0-1]): all-intra dual-tree slices decoded from the "
                       "bytes alone; VTM-produced fixture slices replicated on the device",
             "per_gpu": True, "points": rows, "api": "cabac_decode_slices_dev (decode_slice_kernel: one warp per slice)",

@@ -288,3 +288,64 @@ def test_gpu_decode_slices_many_copies_and_errors(engine):
         assert ntu == len(s["tus"]) and ncu == len(s["cus"])
         k0 = int(cap["coeff"][j])
         assert (r["coeffs"][k0:k0 + nco] == s["coeffs"]).all(), f"copy {j} of {tag}"
+
+
+def _garbage_cases(n, seed):
+    """Random bytes and corrupted real payloads under real slice parameters."""
+    rng = np.random.default_rng(seed)
+    items = _substreams()
+    cases = []
+    for k in range(n):
+        tag, s, sp = items[k % len(items)]
+        pl = s["payload"].copy()
+        kind = k % 3
+        if kind == 0:
+            pl = rng.integers(0, 256, int(rng.integers(2, 400)), dtype=np.uint8)
+        elif kind == 1:
+            pos = rng.integers(0, pl.size, 4)
+            pl[pos] ^= rng.integers(1, 256, 4, dtype=np.uint8)
+        else:
+            pl = pl[:int(rng.integers(1, pl.size))]
+        cases.append((s, sp, pl))
+    return cases
+
+
+def test_host_parser_survives_garbage():
+    """Malformed slice data must end in status bits or a (wrong but bounded) parse - never in a crash or a loop."""
+    lib = _host_lib()
+    for s, sp, pl in _garbage_cases(120, 7):
+        s2 = dict(s)
+        s2["payload"] = pl
+        r = _host_decode(lib, s2, sp)
+        assert r["num_bins"] < 10_000_000
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(120)
+def test_gpu_decode_slices_survives_garbage(engine):
+    """The same on the device: 600 malformed substreams in one launch return (no hang, no fault), every region stays
+    inside its capacity, and a well-formed batch decoded right after is still exact."""
+    cases = _garbage_cases(600, 11)
+    n = len(cases)
+    params, sps, ctx_in = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT), np.zeros((n, 379), CTX_DT)
+    data, off = [], [0]
+    for j, (s, sp, pl) in enumerate(cases):
+        params[j] = (s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)
+        sps[j] = sp
+        ctx_in[j]["state0"], ctx_in[j]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+        data.append(pl)
+        off.append(off[-1] + pl.size)
+    r = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, ctx_in=ctx_in,
+                             raise_on_status=False)
+    cap = r["cap"]
+    for j in range(n):
+        ncu, ntu, nco = (int(v) for v in r["counts"][j])
+        assert ncu <= int(cap["cu"][j + 1] - cap["cu"][j]) or r["status"][j] != 0
+        assert ntu <= int(cap["tu"][j + 1] - cap["tu"][j]) and nco <= int(cap["coeff"][j + 1] - cap["coeff"][j])
+    assert (r["status"] != 0).sum() > n // 2  # most corrupted substreams are caught (overrun / no terminating bin)
+    tag, s, sp = _substreams()[0]
+    par = np.array([(s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)], PARAMS_DT)
+    ci = np.zeros((1, 379), CTX_DT)
+    ci[0]["state0"], ci[0]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+    ok = engine.decode_slices(s["payload"], np.array([0, s["payload"].size], np.uint64), par, np.array([sp], SLICE_DT), ctx_in=ci)
+    assert int(ok["num_bins"][0]) == s["num_bins"] and (ok["coeffs"][:s["coeffs"].size] == s["coeffs"]).all()
