@@ -131,8 +131,15 @@ class GpuSliceReader {
     p.init_id = uint8_t(initId);
     p.flags = uint8_t((sl.getDepQuantEnabledFlag() ? CABAC_SUB_DEP_QUANT : 0) |
                       (sl.getSignDataHidingEnabledFlag() ? CABAC_SUB_SIGN_HIDING : 0) |
-                      (sl.getTSResidualCodingDisabledFlag() ? CABAC_SUB_TSRC_DISABLED : 0) | CABAC_SUB_TERMINATE |
-                      (ctxIn ? CABAC_SUB_CTX_IN : 0));
+                      (sl.getTSResidualCodingDisabledFlag() ? CABAC_SUB_TSRC_DISABLED : 0));
+    return addRaw(bytes, nbytes, p, sp, ctxIn);
+  }
+  // The same with the substream parameters already flat (qp, init table, CABAC_SUB_DEP_QUANT / SIGN_HIDING /
+  // TSRC_DISABLED); terminate and ctx-in are set here.
+  size_t addRaw(const uint8_t *bytes, size_t nbytes, cabac_substream_params p, const cabac_slice_params &sp,
+                const cabac_ctx_model *ctxIn = nullptr) {
+    p.flags = uint8_t((p.flags & (CABAC_SUB_DEP_QUANT | CABAC_SUB_SIGN_HIDING | CABAC_SUB_TSRC_DISABLED)) |
+                      CABAC_SUB_TERMINATE | (ctxIn ? CABAC_SUB_CTX_IN : 0));
     params_.push_back(p);
     sps_.push_back(sp);
     in_.insert(in_.end(), bytes, bytes + nbytes);

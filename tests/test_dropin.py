@@ -28,3 +28,31 @@ def test_reference_writer_on_gpu_shims(n_sub, seed):
     r = subprocess.run([BIN, str(n_sub), str(seed)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "DROPIN OK" in r.stdout
+
+
+@pytest.mark.gpu
+def test_slice_reader_shim_on_vtm_slices(tmp_path):
+    """GpuSliceReader (host/gpu_slice_reader.hpp, compiled against the unmodified reference headers) decodes the
+    VTM-produced fixture slices from their bytes through cabac_decode_slices with host pointers."""
+    if not os.path.exists(BIN):
+        pytest.skip("oracle/_ref/dropin_test not built (needs the reference tree at build time)")
+    import sys
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_syntax as T
+    items = T._substreams()
+    path = tmp_path / "slices.bin"
+    with open(path, "wb") as f:
+        f.write(np.uint32(len(items)).tobytes())
+        for tag, s, sp in items:
+            co = s["coeffs"].astype(np.int64)
+            sm = int((np.arange(1, co.size + 1, dtype=np.uint64) * co.astype(np.uint64)).sum(dtype=np.uint64))
+            f.write(np.array([sp], T.SLICE_DT).tobytes())
+            f.write(np.array([s["qp"]], np.int32).tobytes())
+            f.write(np.array([s["init_id"], s["flags"], s["payload"].size, len(s["cus"]), len(s["tus"]), s["num_bins"],
+                              co.size], np.uint32).tobytes())
+            f.write(np.uint64(sm).tobytes())
+            f.write(np.ascontiguousarray(s["ctx_in"].astype(np.uint16)).tobytes())
+            f.write(np.ascontiguousarray(s["payload"]).tobytes())
+    r = subprocess.run([BIN, "--slices", str(path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "DROPIN OK" in r.stdout, r.stdout + r.stderr
