@@ -763,7 +763,7 @@ def leg_slice_decode(args, r):
         d = {k: dev_bytes(dev, v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)),
                                                ("p", params), ("sp", sps), ("ci", ctx_in), ("cu", cap["cu"]),
                                                ("tu", cap["tu"]), ("ctu", cap["ctu"]), ("co", cap["coeff"]))}
-        cus = torch.empty(int(cap["cu"][-1]) * 24, dtype=torch.uint8, device=dev)
+        cus = torch.empty(int(cap["cu"][-1]) * 28, dtype=torch.uint8, device=dev)
         tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device=dev)
         tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device=dev)
         ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device=dev)

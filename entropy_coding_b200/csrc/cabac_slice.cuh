@@ -30,6 +30,10 @@ struct __align__(16) SliceWarpSmem {
   uint32_t rowCtx[CABAC_NUM_CTX];  // WPP: the states (entry .x) after the first CTU of the current row
   uint16_t above[2][SLICE_MAX_LINE];
   uint16_t left[2][32];
+  uint16_t edgeLeft[32];                // luma: right edge (x + w) of the CU last written at a row
+  uint8_t modeAbove[SLICE_MAX_LINE];    // luma intra direction neighbours see (MPM derivation)
+  uint8_t modeLeft[32];
+  uint8_t lumaMap[256];                 // luma directions of the current 64x64 node, 4x4 granularity (chroma candidates)
   uint8_t ctuLine[SLICE_MAX_CTU_COLS];
 };
 
@@ -177,6 +181,20 @@ struct SliceEngine {
   __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.above[ch]; }
   __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.left[ch]; }
   __device__ __forceinline__ uint8_t *ctuLine() { return sm.ctuLine; }
+  __device__ __forceinline__ uint8_t *modeAbove() { return sm.modeAbove; }
+  __device__ __forceinline__ uint8_t *modeLeft() { return sm.modeLeft; }
+  __device__ __forceinline__ uint16_t *edgeLeft() { return sm.edgeLeft; }
+  __device__ __forceinline__ uint8_t *lumaMap() { return sm.lumaMap; }
+  __device__ __forceinline__ void fill8(uint8_t *p, int n, uint8_t v) {
+    const int lane = laneId();
+    for (int i = lane; i < n; i += 32) p[i] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void fillMap(int bx, int by, int bw, int bh, uint8_t v) {
+    const int lane = laneId();
+    for (int i = lane; i < bw * bh; i += 32) sm.lumaMap[((by + i / bw) << 4) + bx + i % bw] = v;
+    __syncwarp();
+  }
   __device__ __forceinline__ void ctuLineStore(int col, uint8_t v) {
     const int lane = laneId();
     (void)lane;

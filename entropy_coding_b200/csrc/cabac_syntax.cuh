@@ -195,11 +195,76 @@ struct SliceParser {
   SX_FN uint16_t nbAbove(int ch, int x, int y) {
     return aboveAvail(y) ? e.aboveLine(ch)[(x - int(sp.x0)) >> 2] : uint16_t(0);
   }
-  SX_FN void nbStore(int ch, const Node &n, int mip) {
+  // dirNb: the luma direction the CU shows its neighbours and the chroma tree (PU::getIntraDirLuma: PLANAR for MIP)
+  SX_FN void nbStore(int ch, const Node &n, int mip, int dirNb) {
     const uint16_t v = nbPack(n.log2w, n.log2h, n.qt, mip);
-    // clip to the picture: a CU never extends beyond it (implicit splits), but stay safe
-    e.fill(e.aboveLine(ch) + ((n.x - int(sp.x0)) >> 2), (1 << n.log2w) >> 2, v);
-    e.fill(e.leftCol(ch) + ((n.y & ((1 << sp.log2_ctu) - 1)) >> 2), (1 << n.log2h) >> 2, v);
+    const int col = (n.x - int(sp.x0)) >> 2, row = (n.y & ((1 << sp.log2_ctu) - 1)) >> 2;
+    const int w4 = (1 << n.log2w) >> 2, h4 = (1 << n.log2h) >> 2;
+    e.fill(e.aboveLine(ch) + col, w4, v);
+    e.fill(e.leftCol(ch) + row, h4, v);
+    if (ch == 0) {
+      e.fill8(e.modeAbove() + col, w4, uint8_t(dirNb));
+      e.fill8(e.modeLeft() + row, h4, uint8_t(dirNb));
+      e.fill(e.edgeLeft() + row, h4, uint16_t(n.x + (1 << n.log2w)));
+      e.fillMap((n.x & 63) >> 2, (n.y & 63) >> 2, w4, h4, uint8_t(dirNb));
+    }
+  }
+
+  // PU::getIntraMPMs, unit_tools.cpp:485-577: left = the PU at the bottom-left corner (x - 1, y + h - 1) if already
+  // decoded, above = the PU at the top-right corner (x + w - 1, y - 1) if inside the same CTU
+  SX_FN void intraMpms(const Node &n, int *mpm) {
+    const int w = 1 << n.log2w, h = 1 << n.log2h, ctuMask = (1 << sp.log2_ctu) - 1;
+    int left = 0, above = 0;  // PLANAR_IDX
+    const int rowL = ((n.y + h - 1) & ctuMask) >> 2;
+    if (leftAvail(n.x) && e.leftCol(0)[rowL] && int(e.edgeLeft()[rowL]) == int(n.x)) left = e.modeLeft()[rowL];
+    if (aboveAvail(n.y) && (n.y & ctuMask) != 0) above = e.modeAbove()[(n.x + w - 1 - int(sp.x0)) >> 2];
+    const int offset = 61, mod = 64;  // NUM_LUMA_MODE - 6, offset + 3
+    mpm[0] = 0;
+    mpm[1] = 1;
+    mpm[2] = 50;
+    mpm[3] = 18;
+    mpm[4] = 46;
+    mpm[5] = 54;
+    if (left == above) {
+      if (left > 1) {
+        mpm[0] = 0;
+        mpm[1] = left;
+        mpm[2] = ((left + offset) % mod) + 2;
+        mpm[3] = ((left - 1) % mod) + 2;
+        mpm[4] = ((left + offset - 1) % mod) + 2;
+        mpm[5] = (left % mod) + 2;
+      }
+    } else if (left > 1 && above > 1) {
+      mpm[0] = 0;
+      mpm[1] = left;
+      mpm[2] = above;
+      const int mx = left > above ? left : above, mn = left > above ? above : left;
+      if (mx - mn == 1) {
+        mpm[3] = ((mn + offset) % mod) + 2;
+        mpm[4] = ((mx - 1) % mod) + 2;
+        mpm[5] = ((mn + offset - 1) % mod) + 2;
+      } else if (mx - mn >= 62) {
+        mpm[3] = ((mn - 1) % mod) + 2;
+        mpm[4] = ((mx + offset) % mod) + 2;
+        mpm[5] = (mn % mod) + 2;
+      } else if (mx - mn == 2) {
+        mpm[3] = ((mn - 1) % mod) + 2;
+        mpm[4] = ((mn + offset) % mod) + 2;
+        mpm[5] = ((mx - 1) % mod) + 2;
+      } else {
+        mpm[3] = ((mn + offset) % mod) + 2;
+        mpm[4] = ((mn - 1) % mod) + 2;
+        mpm[5] = ((mx + offset) % mod) + 2;
+      }
+    } else if (left + above >= 2) {
+      const int mx = left < above ? above : left;
+      mpm[0] = 0;
+      mpm[1] = mx;
+      mpm[2] = ((mx + offset) % mod) + 2;
+      mpm[3] = ((mx - 1) % mod) + 2;
+      mpm[4] = ((mx + offset - 1) % mod) + 2;
+      mpm[5] = (mx % mod) + 2;
+    }
   }
 
   // ---- QTBTPartitioner::getImplicitSplit, unit_partitioner.cpp:425-470 ----
@@ -455,6 +520,8 @@ struct SliceParser {
     cu.n_tu = 0;
     cu.qp_delta = 0;
     cu.chroma_qp_adj = 0;
+    cu.intra_dir = 0;
+    cu.reserved[0] = cu.reserved[1] = cu.reserved[2] = 0;
     const int w = 1 << n.log2w, h = 1 << n.log2h;
     const int tsMax = 1 << sp.log2_max_ts, maxTb = 1 << sp.log2_max_tb;
     if (ch == 0) {
@@ -498,6 +565,31 @@ struct SliceParser {
           }
         }
       }
+      // pu.intraDir[0], :1240-1316
+      if (cu.bdpcm) {
+        cu.intra_dir = cu.bdpcm == 2 ? 50 : 18;  // VER_IDX : HOR_IDX
+      } else if (cu.flags & CABAC_CU_MIP) {
+        cu.intra_dir = cu.pred_syntax;
+      } else {
+        int mpm[6];
+        intraMpms(n, mpm);
+        if (cu.flags & CABAC_CU_MPM) {
+          cu.intra_dir = uint8_t(mpm[cu.pred_syntax]);
+        } else {
+          for (int i = 1; i < 6; i++) {  // std::sort(mpm, mpm + 6)
+            const int v = mpm[i];
+            int j = i - 1;
+            while (j >= 0 && mpm[j] > v) {
+              mpm[j + 1] = mpm[j];
+              j--;
+            }
+            mpm[j + 1] = v;
+          }
+          int mode = cu.pred_syntax;
+          for (int i = 0; i < 6; i++) mode += mode >= mpm[i];
+          cu.intra_dir = uint8_t(mode);
+        }
+      }
       if (depth == 0) lumaRootIsp = cu.isp;
     } else {
       const int cw = w >> 1, chh = h >> 1;
@@ -516,6 +608,20 @@ struct SliceParser {
           }
         }
         if (!done && e.bin(SX_INTRA_CHROMA_PRED_MODE)) cu.pred_syntax = uint8_t(1 + e.ep(2));
+      }
+      // pu.intraDir[1], :1318-1394 with PU::getIntraChromaCandModes (unit_tools.cpp:460-483)
+      if (cu.bdpcm) {
+        cu.intra_dir = cu.bdpcm == 2 ? 50 : 18;
+      } else if (cu.flags & CABAC_CU_CCLM) {
+        cu.intra_dir = uint8_t(67 + cu.pred_syntax);  // LM_CHROMA_IDX, MDLM_L_IDX, MDLM_T_IDX
+      } else if (cu.pred_syntax == 0) {
+        cu.intra_dir = 70;  // DM_CHROMA_IDX (resolved at prediction time)
+      } else {
+        const int cand[4] = {0, 50, 18, 1};  // PLANAR, VER, HOR, DC
+        // the collocated luma PU: at the centre of the chroma block (PU::getCoLocatedLumaPU, unit_tools.cpp:603-613)
+        const int lumaMode = e.lumaMap()[((((n.y + (h >> 1)) & 63) >> 2) << 4) + (((n.x + (w >> 1)) & 63) >> 2)];
+        const int m = cand[cu.pred_syntax - 1];
+        cu.intra_dir = uint8_t(m == lumaMode ? 66 : m);  // VDIA_IDX replaces the candidate equal to the luma mode
       }
     }
 
@@ -631,7 +737,7 @@ struct SliceParser {
         }
       }
     }
-    nbStore(ch, n, (cu.flags & CABAC_CU_MIP) ? 1 : 0);
+    nbStore(ch, n, (cu.flags & CABAC_CU_MIP) ? 1 : 0, (cu.flags & CABAC_CU_MIP) ? 0 : cu.intra_dir);
     if (nCu < capCu)
       e.putCu(nCu, cu);
     else

@@ -773,10 +773,9 @@ enum { /* cabac_cu_desc.flags */
   CABAC_CU_JCCR = 16,          /* some TU of the CU has tu.jointCbCr != 0                        */
   CABAC_CU_DQP = 32            /* cu_qp_delta_abs was coded in this CU (value in qp_delta)       */
 };
-/* One record per CodingUnit in decoding order (what coding_unit() leaves in CodingUnit /
- * PredictionUnit, unit.hpp:283-341, as the syntax element values: the derivation of the final
- * intra direction from the MPM list, PU::getIntraMPMs, is prediction-side work and stays with
- * the caller). */
+/* One record per CodingUnit in decoding order: what coding_unit() leaves in CodingUnit /
+ * PredictionUnit (unit.hpp:283-341), the syntax element values and the intra direction derived
+ * from them. */
 typedef struct cabac_cu_desc {
   uint16_t x, y;          /* top-left in luma samples                                           */
   uint8_t log2_w, log2_h; /* luma samples (a chroma-tree CU covers half of that per dimension)  */
@@ -795,6 +794,10 @@ typedef struct cabac_cu_desc {
   uint16_t n_tu;          /* coded blocks (cbf = 1, residual_coding called)                      */
   int8_t qp_delta;        /* CuQpDeltaVal when CABAC_CU_DQP                                      */
   uint8_t chroma_qp_adj;  /* cu_chroma_qp_offset_flag + idx                                      */
+  uint8_t intra_dir;      /* pu.intraDir[chType] as the reader leaves it: luma 0..66 from the MPM
+                             list (PU::getIntraMPMs, unit_tools.cpp:485-577) or the MIP mode;
+                             chroma 0..66, 67..69 = LM / MDLM_L / MDLM_T, 70 = DM_CHROMA_IDX      */
+  uint8_t reserved[3];
 } cabac_cu_desc;
 
 /* Per-CTU in-loop filter syntax (SAOBlkParam, sample_adaptive_offset.hpp; the ALF CTU maps of

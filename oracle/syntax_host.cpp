@@ -22,7 +22,8 @@ struct HostEngine {
   void *dec = nullptr;
   std::vector<uint32_t> trace;
   std::vector<uint16_t> above[2], left[2];
-  std::vector<uint8_t> ctus;
+  std::vector<uint8_t> ctus, mAbove, mLeft, lmap;
+  std::vector<uint16_t> eLeft;
   cabac_cu_desc *cusOut;
   cabac_tu_desc *tusOut;
   uint8_t *tuFlagsOut;
@@ -58,6 +59,17 @@ struct HostEngine {
   uint16_t *aboveLine(int ch) { return above[ch].data(); }
   uint16_t *leftCol(int ch) { return left[ch].data(); }
   uint8_t *ctuLine() { return ctus.data(); }
+  uint8_t *modeAbove() { return mAbove.data(); }
+  uint8_t *modeLeft() { return mLeft.data(); }
+  uint16_t *edgeLeft() { return eLeft.data(); }
+  uint8_t *lumaMap() { return lmap.data(); }
+  void fill8(uint8_t *p, int n, uint8_t v) {
+    for (int i = 0; i < n; i++) p[i] = v;
+  }
+  void fillMap(int bx, int by, int bw, int bh, uint8_t v) {
+    for (int y = 0; y < bh; y++)
+      for (int x = 0; x < bw; x++) lmap[size_t(((by + y) << 4) + bx + x)] = v;
+  }
   void ctuLineStore(int col, uint8_t v) { ctus[size_t(col)] = v; }
   void fill(uint16_t *p, int n, uint16_t v) {
     for (int i = 0; i < n; i++) p[i] = v;
@@ -104,6 +116,10 @@ long syn_decode_slice(const uint8_t *in, long nbytes, const cabac_substream_para
     e.left[ch].assign(32, 0);
   }
   e.ctus.assign(512, 0);
+  e.mAbove.assign(cabac_syntax::SX_MAX_LINE, 0);
+  e.mLeft.assign(32, 0);
+  e.eLeft.assign(32, 0);
+  e.lmap.assign(256, 0);
   e.cusOut = cus;
   e.tusOut = tus;
   e.tuFlagsOut = tuFlags;

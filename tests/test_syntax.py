@@ -155,8 +155,10 @@ def _check_against_fixture(tag, r, s):
         assert (c[f] == w[g_]).all(), f"{tag}: CU field {f} at {np.nonzero(c[f] != w[g_])[0][:4]}"
     both = CU_MIP | CU_MIP_TRANSPOSED
     assert ((c["flags"] & both) == (w["flags"] & both)).all(), f"{tag}: MIP flags"
-    mip = (c["flags"] & CU_MIP) != 0
-    assert (c["pred_syntax"][mip] == w["dir"][mip]).all(), f"{tag}: MIP modes"  # pu.intraDir[0] is the MIP mode itself
+    # pu.intraDir[chType] as the reference's objects held it: MPM-derived luma directions, MIP modes, chroma modes
+    assert (c["intra_dir"] == w["dir"]).all(), \
+        f"{tag}: intra direction at CUs {np.nonzero(c['intra_dir'] != w['dir'])[0][:6]}: " \
+        f"{c['intra_dir'][c['intra_dir'] != w['dir']][:6]} vs {w['dir'][c['intra_dir'] != w['dir']][:6]}"
     # the stop bit follows the terminating bin: everything but the alignment was consumed
     assert 0 <= s["payload"].size * 8 - r["bits"] <= 8, f"{tag}: bits read {r['bits']} of {s['payload'].size * 8}"
 
