@@ -1578,6 +1578,62 @@ long orc_dec_close(void *hv, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t
   return bits;
 }
 
+
+/* ---- stepwise encoder handle ------------------------------------------------
+ * One BinEncoder_Std + Ctx object driven call by call.  oracle/syntax_host.cpp uses it to GENERATE legal
+ * CTU-level streams: the parser header runs on an engine that picks every bin value itself and codes it. */
+typedef struct {
+  Enc e;
+  CtxTab ct;
+  cabac_substream_params p;
+  uint8_t *out;
+  long cap, done; /* bytes of finished rows in front of the running coder */
+  uint32_t bins;
+} OrcEncHandle;
+
+void *orc_enc_open(uint8_t *out, long cap, const cabac_substream_params *p, const cabac_ctx_model *ctxIn) {
+  OrcEncHandle *h = (OrcEncHandle *)malloc(sizeof(OrcEncHandle));
+  if (!h) return NULL;
+  h->p = *p;
+  h->out = out;
+  h->cap = cap;
+  h->done = 0;
+  h->bins = 0;
+  ctx_begin(&h->ct, p, ctxIn);
+  enc_start(&h->e, out, cap);
+  return h;
+}
+void orc_enc_bin(void *hv, unsigned bin, unsigned ctxId) { enc_bin(&((OrcEncHandle *)hv)->e, &((OrcEncHandle *)hv)->ct, bin, ctxId); }
+void orc_enc_ep(void *hv, unsigned bins, unsigned n) {
+  if (n) enc_bins_ep(&((OrcEncHandle *)hv)->e, bins, n);
+}
+void orc_enc_trm(void *hv, unsigned bin) { enc_trm(&((OrcEncHandle *)hv)->e, bin); }
+unsigned orc_enc_tu(void *hv, const cabac_tu_desc *tu, const int32_t *coeffs, uint8_t *tuFlags) {
+  OrcEncHandle *h = (OrcEncHandle *)hv;
+  return w_residual_coding(&h->e, &h->ct, tu, coeffs, h->p.flags, tuFlags);
+}
+void orc_enc_ctx_get(void *hv, cabac_ctx_model *out) { memcpy(out, ((OrcEncHandle *)hv)->ct.m, sizeof(((OrcEncHandle *)hv)->ct.m)); }
+void orc_enc_ctx_set(void *hv, const cabac_ctx_model *in) { memcpy(((OrcEncHandle *)hv)->ct.m, in, sizeof(((OrcEncHandle *)hv)->ct.m)); }
+/* end of a WPP row / of the slice: the terminating bin was coded by the caller; finish(), byte alignment, and - for
+ * a row - a fresh coder behind the bytes written so far.  Returns the total bytes. */
+long orc_enc_flush(void *hv, int restart) {
+  OrcEncHandle *h = (OrcEncHandle *)hv;
+  enc_finish(&h->e);
+  bw_byte_alignment(&h->e.bw);
+  h->done += h->e.bw.n;
+  h->bins += h->e.nbins;
+  if (restart) enc_start(&h->e, h->out + (h->done < h->cap ? h->done : h->cap), h->cap > h->done ? h->cap - h->done : 0);
+  return h->done;
+}
+long orc_enc_close(void *hv, cabac_ctx_model *ctxOut, uint32_t *numBins) {
+  OrcEncHandle *h = (OrcEncHandle *)hv;
+  if (ctxOut) memcpy(ctxOut, h->ct.m, sizeof(h->ct.m));
+  if (numBins) *numBins = h->bins;
+  const long n = h->done;
+  free(h);
+  return n;
+}
+
 /* ---- timed batches (bench.py cpu_baseline, kind = "port") ---------------- */
 typedef struct {
   int k, nthreads, decode;

@@ -64,4 +64,14 @@ void orc_dec_restart(void *h, const uint8_t *in, long n);
 void orc_dec_ctx_get(void *h, cabac_ctx_model *out);
 void orc_dec_ctx_set(void *h, const cabac_ctx_model *in);
 long orc_dec_close(void *h, cabac_ctx_model *ctxOut, uint32_t *status, uint32_t *numBins);
+/* stepwise encoder handle (oracle/syntax_host.cpp: generator of legal CTU-level streams) */
+void *orc_enc_open(uint8_t *out, long cap, const cabac_substream_params *p, const cabac_ctx_model *ctxIn);
+void orc_enc_bin(void *h, unsigned bin, unsigned ctxId);
+void orc_enc_ep(void *h, unsigned bins, unsigned n);
+void orc_enc_trm(void *h, unsigned bin);
+unsigned orc_enc_tu(void *h, const cabac_tu_desc *tu, const int32_t *coeffs, uint8_t *tuFlags);
+void orc_enc_ctx_get(void *h, cabac_ctx_model *out);
+void orc_enc_ctx_set(void *h, const cabac_ctx_model *in);
+long orc_enc_flush(void *h, int restart);
+long orc_enc_close(void *h, cabac_ctx_model *ctxOut, uint32_t *numBins);
 #endif

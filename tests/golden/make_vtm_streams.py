@@ -49,7 +49,9 @@ RUNS = {
     "wqvga_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27"]),
     # tools the three cfgs leave off but the CTU-level parser implements: cu_qp_delta (perceptual QP adaptation
     # turns pps.useDQP on, one quantisation group per CTU) and BDPCM (intra_bdpcm_*_flag, the cbf contexts under BDPCM)
-    "dqp_bdpcm_qp32": ("encoder_intra_vtm_qp32.cfg", ["--PerceptQPA=1", "--BDPCM=1"]),
+    "dqp_bdpcm_qp32": ("encoder_intra_vtm_qp32.cfg", ["--PerceptQPA=1", "--BDPCM=1"]),  # (QPA stays slice-level at QCIF size: BDPCM + ALF chroma only)
+    # cu_qp_delta for real: CU-level delta-QP search, quantisation groups two subdivisions below the CTU
+    "cudqp_qp32": ("encoder_intra_vtm_qp32.cfg", ["--MaxDeltaQP=1", "--MaxCuDQPSubdiv=2"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),

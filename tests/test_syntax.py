@@ -151,8 +151,12 @@ def _check_against_fixture(tag, r, s):
     assert len(c) == len(w), f"{tag}: {len(c)} CUs, the writer coded {len(w)}"
     for f, g_ in (("x", "x"), ("y", "y"), ("log2_w", "log2w"), ("log2_h", "log2h"), ("ch_type", "ch_type"),
                   ("qt_depth", "qt_depth"), ("mt_depth", "mt_depth"), ("bdpcm", "bdpcm"), ("mrl_idx", "mrl"),
-                  ("isp", "isp"), ("lfnst_idx", "lfnst"), ("mts_idx", "mts")):
+                  ("isp", "isp"), ("lfnst_idx", "lfnst")):
         assert (c[f] == w[g_]).all(), f"{tag}: CU field {f} at {np.nonzero(c[f] != w[g_])[0][:4]}"
+    # mtsIdx[Y] of the first TU: the reader only sets it inside residual_coding (ts_flag, cabac_reader.cpp:2737-2752),
+    # so a BDPCM CU without coded luma keeps DCT2 there while the encoder's object says "skip": a don't-care
+    care = ~((c["bdpcm"] > 0) & (c["n_tu"] == 0))
+    assert (c["mts_idx"][care] == w["mts"][care]).all(), f"{tag}: CU field mts_idx"
     both = CU_MIP | CU_MIP_TRANSPOSED
     assert ((c["flags"] & both) == (w["flags"] & both)).all(), f"{tag}: MIP flags"
     # pu.intraDir[chType] as the reference's objects held it: MPM-derived luma directions, MIP modes, chroma modes
@@ -351,3 +355,139 @@ def test_gpu_decode_slices_survives_garbage(engine):
     ci[0]["state0"], ci[0]["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
     ok = engine.decode_slices(s["payload"], np.array([0, s["payload"].size], np.uint64), par, np.array([sp], SLICE_DT), ctx_in=ci)
     assert int(ok["num_bins"][0]) == s["num_bins"] and (ok["coeffs"][:s["coeffs"].size] == s["coeffs"]).all()
+
+
+# ---- generated streams: the parser on an engine that picks every bin (oracle/syntax_host.cpp: syn_generate_slice) ----
+# Not conformance (generator and parser share the walk - conformance is the VTM fixtures above): symmetry, capacity,
+# every CTU size and picture shape, and the tools no fixture exercises (BDPCM, cu_qp_delta, chroma QP offsets, ALF
+# chroma / CC-ALF CTU syntax, 32-sample maximum transform size, WPP rows at every CTU size).
+from entropy_coding_b200.types import (SL_ALF_CB, SL_ALF_CR, SL_ALF_Y, SL_BDPCM, SL_CCALF_CB, SL_CCALF_CR, SL_CCLM,  # noqa: E402
+                                       SL_CHROMA_QP_ADJ, SL_DQP, SL_DUAL_TREE, SL_INTRA, SL_ISP, SL_JCCR, SL_LFNST, SL_MIP,
+                                       SL_MRL, SL_MTS, SL_MTS_INTRA, SL_SAO_CHROMA, SL_SAO_LUMA, SL_TS, SUB_DEP_QUANT)
+
+ALL_TOOLS = (SL_DUAL_TREE | SL_SAO_LUMA | SL_SAO_CHROMA | SL_ALF_Y | SL_ALF_CB | SL_ALF_CR | SL_CCALF_CB | SL_CCALF_CR |
+             SL_MTS_INTRA | SL_LFNST | SL_ISP | SL_MIP | SL_MRL | SL_TS | SL_BDPCM | SL_JCCR | SL_CCLM | SL_DQP |
+             SL_CHROMA_QP_ADJ | SL_INTRA | SL_MTS)
+
+
+def make_slice_params(w, h, log2_ctu=7, tools=ALL_TOOLS, **kw):
+    sp = np.zeros(1, SLICE_DT)[0]
+    sp["pic_w"], sp["pic_h"], sp["x1"], sp["y1"], sp["log2_ctu"] = w, h, w, h, log2_ctu
+    mx = min(log2_ctu, 6)
+    sp["log2_min_qt_luma"] = sp["log2_min_qt_chroma"] = 3
+    sp["log2_max_bt_luma"], sp["log2_max_bt_chroma"] = min(5, mx), mx
+    sp["log2_max_tt_luma"] = sp["log2_max_tt_chroma"] = min(5, mx)
+    sp["max_mtt_depth_luma"] = sp["max_mtt_depth_chroma"] = 3
+    for f in ("log2_min_bt_luma", "log2_min_bt_chroma", "log2_min_tt_luma", "log2_min_tt_chroma"):
+        sp[f] = 2
+    sp["log2_max_tb"], sp["log2_max_ts"], sp["bit_depth"], sp["chroma_format"] = 6, 5, 10, 1
+    sp["alf_num_aps_luma"], sp["alf_chroma_num_alts"] = 2, 3
+    sp["ccalf_filter_count_cb"], sp["ccalf_filter_count_cr"], sp["chroma_qp_offset_list_len"] = 3, 2, 3
+    sp["tools"] = tools
+    for k, v in kw.items():
+        sp[k] = v
+    return sp
+
+
+def generate_slice(lib, seed, sp, qp=32, split_p=0.35, density=0.08):
+    """One legal slice for `sp` and what the generating walk recorded (CUs, TUs, CTUs, coefficients, contexts)."""
+    lib.syn_generate_slice.restype = C.c_long
+    area = int(sp["x1"] - sp["x0"]) * int(sp["y1"] - sp["y0"])
+    cap, capco = area // 16 * 2 + 8, area * 3 // 2 + 64
+    ctu = 1 << int(sp["log2_ctu"])
+    nctu = -(-int(sp["x1"] - sp["x0"]) // ctu) * -(-int(sp["y1"] - sp["y0"]) // ctu)
+    par = np.array([(qp, 2, SUB_DEP_QUANT | SUB_TERMINATE, 0)], PARAMS_DT)
+    out, cus, tus, tuf = np.zeros(area * 4 + 4096, np.uint8), np.zeros(cap, CU_DT), np.zeros(cap, TU_DT), np.zeros(cap, np.uint8)
+    ctus, co, cnt, nb = np.zeros(nctu, CTU_DT), np.zeros(capco, np.int32), np.zeros(3, np.uint32), np.zeros(1, np.uint32)
+    cout, st = np.zeros(379, CTX_DT), np.zeros(1, np.uint32)
+    n = lib.syn_generate_slice(C.c_uint64(seed), C.c_double(split_p), C.c_double(density), _p(par), _p(np.array([sp], SLICE_DT)),
+                               _p(out), C.c_long(out.size), _p(cus), C.c_long(cap), _p(tus), _p(tuf), C.c_long(cap), _p(ctus),
+                               C.c_long(nctu), _p(co), C.c_long(capco), _p(cnt), _p(nb), _p(cout), _p(st))
+    assert int(st[0]) == 0 and 0 < n <= out.size, f"generator status {int(st[0])}"
+    init = np.zeros((379, 2), np.uint16)  # placeholder: generated slices start from Ctx::init (no SUB_CTX_IN)
+    return dict(payload=out[:n].copy(), cus=cus[:cnt[0]].copy(), tus=tus[:cnt[1]].copy(), tu_flags=tuf[:cnt[1]].copy(),
+                coeffs=co[:cnt[2]].copy(), ctus=ctus, num_bins=int(nb[0]), ctx_out=cout, qp=qp, init_id=2,
+                flags=SUB_DEP_QUANT, ctx_in=init, fresh=True)
+
+
+GEN_CASES = [  # (w, h, log2_ctu, extra slice parameters, WPP)
+    (176, 144, 7, {}, False), (416, 240, 7, dict(log2_max_tb=5), True), (200, 120, 6, dict(cu_qp_delta_subdiv=2), False),
+    (96, 80, 5, dict(cu_chroma_qp_offset_subdiv=2), True), (640, 360, 7, dict(cu_qp_delta_subdiv=4, log2_max_ts=2), False),
+    (132, 68, 6, dict(tools=ALL_TOOLS & ~(SL_BDPCM | SL_DQP | SL_ALF_CB | SL_CCALF_CR)), False),
+    (64, 64, 6, dict(tools=SL_DUAL_TREE | SL_INTRA), True), (3840, 136, 7, {}, False),
+]
+
+
+def _gen_items(lib, reps=1):
+    items = []
+    for rep in range(reps):
+        for k, (w, h, l2, kw, wpp) in enumerate(GEN_CASES):
+            sp = make_slice_params(w, h, l2, **kw)
+            if wpp:
+                sp["tools"] |= np.uint32(SL_WPP)
+            items.append((f"gen{rep}:{w}x{h}/ctu{1 << l2}", generate_slice(lib, 1000 + 31 * rep + k, sp), sp))
+    return items
+
+
+def _host_decode_fresh(lib, s, sp):
+    """_host_decode without handed-over contexts (Ctx::init from qp / init table)."""
+    s2 = dict(s)
+    r = None
+    from oracle.checker import Checker
+    init, _ = Checker("oracle").ctx_init(s["qp"], s["init_id"])
+    s2["ctx_in"] = np.stack([init["state0"], init["state1"]], axis=1)
+    r = _host_decode(lib, s2, sp)
+    return r
+
+
+def _check_against_generator(tag, r, g):
+    assert r["status"] == 0 and r["num_bins"] == g["num_bins"], f"{tag}: status {r['status']}, bins {r['num_bins']} / {g['num_bins']}"
+    assert r["cus"].tobytes() == g["cus"].tobytes(), f"{tag}: CU records"
+    t, w = r["tus"], g["tus"]
+    assert len(t) == len(w) and all((t[f] == w[f]).all() for f in ("log2_w", "log2_h", "comp_id", "flags")), f"{tag}: TUs"
+    assert (r["tu_flags"] == g["tu_flags"]).all(), f"{tag}: TU result flags"
+    assert r["coeffs"].size == g["coeffs"].size and (r["coeffs"] == g["coeffs"]).all(), f"{tag}: coefficients"
+    assert r["ctx_out"].tobytes() == g["ctx_out"].tobytes(), f"{tag}: final contexts"
+
+
+def test_generated_streams_decode_on_host():
+    lib = _host_lib()
+    for tag, g, sp in _gen_items(lib):
+        r = _host_decode_fresh(lib, g, sp)
+        _check_against_generator(tag, r, g)
+        n = len(g["ctus"])
+        assert r["ctus"][:n].tobytes() == g["ctus"].tobytes(), f"{tag}: CTU records"
+        assert 0 <= g["payload"].size * 8 - r["bits"] <= 8, tag
+    # capacity: a region that is too small ends in CABAC_SS_CAPACITY, not in a write beyond it
+    tag, g, sp = _gen_items(lib)[0]
+    sp_small = sp.copy()
+    sp_small["x1"] = sp_small["pic_w"] = 64  # claims a smaller rectangle than the stream codes: regions shrink with it
+    assert _host_decode_fresh(lib, g, sp_small)["status"] != 0
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(300)
+def test_gpu_decode_slices_on_generated_streams(engine):
+    """Every CTU size, odd picture shapes, a 3840-wide strip, WPP rows, and the tools no VTM fixture exercises, three
+    seeds each, in one launch: records, coefficients, contexts and bin counts equal the generating walk's."""
+    lib = _host_lib()
+    items = _gen_items(lib, reps=3)
+    n = len(items)
+    params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+    data, off = [], [0]
+    for k, (tag, g, sp) in enumerate(items):
+        params[k] = (g["qp"], g["init_id"], g["flags"] | SUB_TERMINATE, 0)
+        sps[k] = sp
+        data.append(g["payload"])
+        off.append(off[-1] + g["payload"].size)
+    r = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, want_ctx=True)
+    cap = r["cap"]
+    for k, (tag, g, sp) in enumerate(items):
+        ncu, ntu, nco = (int(v) for v in r["counts"][k])
+        c0, t0, k0 = int(cap["cu"][k]), int(cap["tu"][k]), int(cap["coeff"][k])
+        one = dict(cus=r["cus"][c0:c0 + ncu], tus=r["tus"][t0:t0 + ntu], tu_flags=r["tu_flags"][t0:t0 + ntu],
+                   coeffs=r["coeffs"][k0:k0 + nco], num_bins=int(r["num_bins"][k]), status=int(r["status"][k]),
+                   ctx_out=r["ctx_out"][k])
+        _check_against_generator(tag, one, g)
+        a, b = int(cap["ctu"][k]), int(cap["ctu"][k + 1])
+        assert r["ctus"][a:b].tobytes() == g["ctus"].tobytes(), f"{tag}: CTU records"
