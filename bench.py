@@ -787,7 +787,7 @@ def leg_slice_decode(args, r):
             assert (co_h[k0:k0 + s["coeffs"].size] == s["coeffs"]).all(), f"slice copy {j}: coefficients"
             n_coeff += s["coeffs"].size
         bins = int(bins_h.astype(np.int64).sum())
-        alg = off[-1] + 4 * n_coeff + 16 * int(counts[:, 1].sum()) + 24 * int(counts[:, 0].sum())
+        alg = off[-1] + 4 * n_coeff + 16 * int(counts[:, 1].sum()) + 28 * int(counts[:, 0].sum())
         row = {"substreams": n, "bins": bins, "bitstream_bytes": off[-1], "cus": int(counts[:, 0].sum()),
                "tus": int(counts[:, 1].sum()), "coefficients_out": n_coeff, "decode_ms": t,
                "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9}
@@ -795,13 +795,94 @@ def leg_slice_decode(args, r):
         rows.append(row)
         del cus, tus, tuf, ctus, co, cnt, nb, st, d
         torch.cuda.empty_cache()
+    rows_gen = _slice_decode_generated(r)
     cpu = None
     if r["rank"] == 0 and not args.no_cpu_baseline:
-        cpu = _cpu_slice_decode(items)
+        # picture-sized slices keep the per-call Python overhead out of the CPU figure
+        gen_path = os.path.join(ROOT, "tests", "golden", "gen_slices.npz")
+        cpu_items = items
+        if os.path.exists(gen_path):
+            z = np.load(gen_path)
+            cpu_items = []
+            for k in range(2):
+                meta = z[f"hd{k}_meta"]
+                cpu_items.append((dict(payload=z[f"hd{k}_payload"], qp=int(meta[0]), init_id=int(meta[1]), flags=int(meta[2]),
+                                       num_bins=int(meta[3]), ctx_in=None), z[f"hd{k}_slice"].view(SLICE_DT)[0]))
+        cpu = _cpu_slice_decode(cpu_items)
     leg = _slice_leg(rows, items)
+    if rows_gen:
+        leg["generated"] = {"input": "tests/golden/gen_slices.npz: legal all-intra slices from the stream generator "
+                                     "(tests/golden/make_gen_slices.py), dense residuals (1.5 bins per coefficient "
+                                     "position), replicated on the device; ground truth = the generating walk's records",
+                            "points": rows_gen,
+                            "verified": "every copy: bin, CU and TU counts; slice 0 of every set: coefficient checksum"}
     if cpu:
         leg["cpu_baseline"] = cpu
     return leg
+
+
+def _slice_decode_generated(r):
+    """cabac_decode_slices on the committed generated slices: 64 x 1080p pictures as one slice each (the shape of
+    BASELINE configs[2], decoded from the bytes alone) and 2 048 x 416x240."""
+    import torch
+    import entropy_coding_b200 as E
+    from entropy_coding_b200.types import PARAMS_DT, SLICE_DT, SUB_TERMINATE
+    path = os.path.join(ROOT, "tests", "golden", "gen_slices.npz")
+    if not os.path.exists(path):
+        return None
+    z = np.load(path)
+    eng, stream, dev = r["eng"], r["stream"], r["dev"]
+    rows = []
+    for entry, n in (("hd", 64), ("wqvga", 2048)):
+        cnt_set = next(int(t.split(":")[1]) for t in z["sets"] if t.startswith(entry + ":"))
+        base = [(z[f"{entry}{k}_payload"], z[f"{entry}{k}_slice"].view(SLICE_DT)[0], z[f"{entry}{k}_meta"],
+                 int(z[f"{entry}{k}_checksum"])) for k in range(cnt_set)]
+        params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+        data, off = [], [0]
+        for j in range(n):
+            pl, sp, meta, _ = base[j % len(base)]
+            params[j] = (int(meta[0]), int(meta[1]), int(meta[2]) | SUB_TERMINATE, 0)
+            sps[j] = sp
+            data.append(pl)
+            off.append(off[-1] + pl.size)
+        cap = E.CabacEngine.slice_capacities(sps)
+        d = {k: dev_bytes(dev, v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)), ("p", params),
+                                               ("sp", sps), ("cu", cap["cu"]), ("tu", cap["tu"]), ("ctu", cap["ctu"]),
+                                               ("co", cap["coeff"]))}
+        cus = torch.empty(int(cap["cu"][-1]) * 28, dtype=torch.uint8, device=dev)
+        tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device=dev)
+        tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device=dev)
+        ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device=dev)
+        co = torch.zeros(int(cap["coeff"][-1]), dtype=torch.int32, device=dev)
+        cnt = torch.zeros(n * 3, dtype=torch.int32, device=dev)
+        nb = torch.zeros(n, dtype=torch.int32, device=dev)
+        st = torch.zeros(n, dtype=torch.int32, device=dev)
+
+        def dec():
+            eng.decode_slices_dev(d["in"], d["off"], d["p"], d["sp"], n, d["cu"], d["tu"], d["ctu"], d["co"], cus, tus, tuf,
+                                  ctus, co, counts=cnt, num_bins=nb, status=st)
+
+        t = _time_passes(stream, dec, warm=1, reps=2)
+        assert int(st.abs().max()) == 0, "generated slices: status"
+        counts, bins_h = cnt.cpu().numpy().reshape(n, 3), nb.cpu().numpy()
+        for j in range(n):
+            meta = base[j % len(base)][2]
+            assert int(bins_h[j]) == int(meta[3]) and int(counts[j, 0]) == int(meta[4]) and int(counts[j, 1]) == int(meta[5])
+        k0, n0 = int(cap["coeff"][0]), int(base[0][2][6])
+        c0 = co[k0:k0 + n0].to(torch.int64)
+        chk = int((c0 * torch.arange(1, n0 + 1, device=dev, dtype=torch.int64)).sum()) & 0xFFFFFFFFFFFFFFFF
+        assert chk == base[0][3], "generated slices: coefficient checksum"
+        bins = int(bins_h.astype(np.int64).sum())
+        ncoef = sum(int(base[j % len(base)][2][6]) for j in range(n))
+        alg = off[-1] + 4 * ncoef + 16 * int(counts[:, 1].sum()) + 28 * int(counts[:, 0].sum())
+        rows.append({"set": f"{n} x {int(sps[0]['pic_w'])}x{int(sps[0]['pic_h'])}", "substreams": n, "bins": bins,
+                     "bitstream_bytes": off[-1], "coefficients_out": ncoef, "decode_ms": t,
+                     "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9,
+                     "hbm_frac": alg / (t * 1e-3) / 1e9 / load_peaks()[0],
+                     "cycles_per_bin_per_warp": (t * 1e-3) * _sm_mhz(r) * 1e6 / (bins / n) if n <= 148 else None})
+        del cus, tus, tuf, ctus, co, cnt, nb, st, d
+        torch.cuda.empty_cache()
+    return rows
 
 
 def _cpu_slice_decode(items):
@@ -832,16 +913,19 @@ def _cpu_slice_decode(items):
                     area = int(sp["x1"] - sp["x0"]) * int(sp["y1"] - sp["y0"])
                     cap = area // 16 * 2 + 8
                     ci = np.zeros(379, CTX_DT)
-                    ci["state0"], ci["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
-                    bufs[k] = (np.array([(s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_CTX_IN, 0)], PARAMS_DT),
+                    fl = s["flags"] | SUB_TERMINATE
+                    if s["ctx_in"] is not None:
+                        ci["state0"], ci["state1"] = s["ctx_in"][:, 0], s["ctx_in"][:, 1]
+                        fl |= SUB_CTX_IN
+                    bufs[k] = (np.array([(s["qp"], s["init_id"], fl, 0)], PARAMS_DT),
                                np.array([sp], SLICE_DT), ci, np.zeros(cap, CU_DT), np.zeros(cap, TU_DT),
-                               np.zeros(cap, np.uint8), np.zeros(64, CTU_DT), np.zeros(area * 3 // 2 + 64, np.int32),
+                               np.zeros(cap, np.uint8), np.zeros(4096, CTU_DT), np.zeros(area * 3 // 2 + 64, np.int32),
                                np.zeros(3, np.uint32), np.zeros(1, np.uint32), np.zeros(379, CTX_DT),
                                np.zeros(1, np.uint32), np.zeros(1 << 16, np.uint32), np.ascontiguousarray(s["payload"]), cap)
                 par, spa, ci, cus, tus, tuf, ctus, co, cnt, nb, cout, st, tr, pay, cap = bufs[k]
                 nt = C.c_long(0)
                 lib.syn_decode_slice(p(pay), C.c_long(pay.size), p(par), p(spa), p(ci), p(cus), C.c_long(cap), p(tus), p(tuf),
-                                     C.c_long(cap), p(ctus), C.c_long(64), p(co), C.c_long(co.size), p(cnt), p(nb), p(cout),
+                                     C.c_long(cap), p(ctus), C.c_long(4096), p(co), C.c_long(co.size), p(cnt), p(nb), p(cout),
                                      p(st), p(tr), C.c_long(tr.size), C.byref(nt))
                 assert int(st[0]) == 0 and int(nb[0]) == s["num_bins"]
                 bins += int(nb[0])
@@ -852,7 +936,7 @@ def _cpu_slice_decode(items):
         done = list(ex.map(lambda t: worker(t, t0 + 8.0), range(threads)))
     dt = time.perf_counter() - t0
     return {"value": sum(done) / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"the {len(items)} fixture slices decoded over and over for {dt:.1f} s on {threads} threads "
+            "sample": f"{len(items)} slices ({sum(s['num_bins'] for s, _ in items)} bins) decoded over and over for {dt:.1f} s on {threads} threads "
                       "(oracle/libsyntax_host.so: the CTU-level walk on the oracle's scalar decoder)"}
 
 
