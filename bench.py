@@ -763,7 +763,7 @@ def leg_slice_decode(args, r):
         d = {k: dev_bytes(dev, v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)),
                                                ("p", params), ("sp", sps), ("ci", ctx_in), ("cu", cap["cu"]),
                                                ("tu", cap["tu"]), ("ctu", cap["ctu"]), ("co", cap["coeff"]))}
-        cus = torch.empty(int(cap["cu"][-1]) * 28, dtype=torch.uint8, device=dev)
+        cus = torch.empty(int(cap["cu"][-1]) * 32, dtype=torch.uint8, device=dev)
         tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device=dev)
         tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device=dev)
         ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device=dev)
@@ -787,7 +787,7 @@ def leg_slice_decode(args, r):
             assert (co_h[k0:k0 + s["coeffs"].size] == s["coeffs"]).all(), f"slice copy {j}: coefficients"
             n_coeff += s["coeffs"].size
         bins = int(bins_h.astype(np.int64).sum())
-        alg = off[-1] + 4 * n_coeff + 16 * int(counts[:, 1].sum()) + 28 * int(counts[:, 0].sum())
+        alg = off[-1] + 4 * n_coeff + 16 * int(counts[:, 1].sum()) + 32 * int(counts[:, 0].sum())
         row = {"substreams": n, "bins": bins, "bitstream_bytes": off[-1], "cus": int(counts[:, 0].sum()),
                "tus": int(counts[:, 1].sum()), "coefficients_out": n_coeff, "decode_ms": t,
                "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9}
@@ -849,7 +849,7 @@ def _slice_decode_generated(r):
         d = {k: dev_bytes(dev, v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)), ("p", params),
                                                ("sp", sps), ("cu", cap["cu"]), ("tu", cap["tu"]), ("ctu", cap["ctu"]),
                                                ("co", cap["coeff"]))}
-        cus = torch.empty(int(cap["cu"][-1]) * 28, dtype=torch.uint8, device=dev)
+        cus = torch.empty(int(cap["cu"][-1]) * 32, dtype=torch.uint8, device=dev)
         tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device=dev)
         tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device=dev)
         ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device=dev)
@@ -874,7 +874,7 @@ def _slice_decode_generated(r):
         assert chk == base[0][3], "generated slices: coefficient checksum"
         bins = int(bins_h.astype(np.int64).sum())
         ncoef = sum(int(base[j % len(base)][2][6]) for j in range(n))
-        alg = off[-1] + 4 * ncoef + 16 * int(counts[:, 1].sum()) + 28 * int(counts[:, 0].sum())
+        alg = off[-1] + 4 * ncoef + 16 * int(counts[:, 1].sum()) + 32 * int(counts[:, 0].sum())
         rows.append({"set": f"{n} x {int(sps[0]['pic_w'])}x{int(sps[0]['pic_h'])}", "substreams": n, "bins": bins,
                      "bitstream_bytes": off[-1], "coefficients_out": ncoef, "decode_ms": t,
                      "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9,

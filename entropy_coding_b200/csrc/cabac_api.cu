@@ -48,6 +48,8 @@ struct cabac_handle {
   cudaEvent_t evCopy[kMaxChunks] = {}, evDone[kMaxChunks] = {}, evJoin = nullptr;
   void *epbScratch = nullptr;  // tile counts / bases of the emulation-prevention pass, grow-only
   size_t epbTiles = 0;
+  void *emitScratch = nullptr;  // cabac_encode_slices_dev: per-slice word counts, statuses, command offsets; grow-only
+  size_t emitSubs = 0;
   bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
   cudaEvent_t evT0 = nullptr;
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
@@ -394,6 +396,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->pinnedTotal) cudaFreeHost(h->pinnedTotal);
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
   if (h->epbScratch) cudaFree(h->epbScratch);
+  if (h->emitScratch) cudaFree(h->emitScratch);
   if (h->pinDev) cudaFree(h->pinDev);
   cabac::freeSlicedWork(h->sliced);
   if (h->threadCtx) cudaFree(h->threadCtx);
@@ -648,6 +651,52 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
                                  coeffs, num_bins, bits_read, tu_flags, ctx_out, status),
      "decode_residual_kernel");
   h->launches += n_sub ? cabac::kLaunchesPerCodingCall + (sc.threadDecode ? 1 : 0) : 0;
+  return CABAC_OK;
+}
+
+// Writer direction of the slice syntax (cabac_slice.cuh K10 + the stream encoder).
+int cabac_encode_slices_dev(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
+                            size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
+                            const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                            const uint64_t *ctu_offsets, const int32_t *coeffs, const cabac_ctx_model *ctx_in,
+                            uint32_t *cmd_scratch, size_t cmd_scratch_words, uint8_t *out, const uint64_t *out_offsets,
+                            uint32_t *out_sizes, uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!params || !slice_params || !cus || !cu_offsets || !tus || !tu_flags || !tu_offsets || !ctus ||
+                       !ctu_offsets || !coeffs || !cmd_scratch || !out || !out_offsets || !out_sizes || !status)))
+    return badArg(h, "cabac_encode_slices_dev");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  if (n_sub > h->emitSubs) {
+    if (h->emitScratch) cudaFree(h->emitScratch);
+    h->emitScratch = nullptr;
+    h->emitSubs = 0;
+    const size_t cap = n_sub + (n_sub >> 2) + 64;
+    CK(cudaMalloc(&h->emitScratch, (cap + 1) * 8 + cap * 8), "slice emit scratch");
+    h->emitSubs = cap;
+  }
+  uint64_t *cmdOffsets = static_cast<uint64_t *>(h->emitScratch);
+  uint32_t *counts = reinterpret_cast<uint32_t *>(cmdOffsets + h->emitSubs + 1);
+  uint32_t *emitStatus = counts + h->emitSubs;
+  CK(cabac::launchEmitSlices(h->stream, h->device, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus,
+                             ctu_offsets, cmd_scratch, cmd_scratch_words, counts, emitStatus, cmdOffsets),
+     "emit_slice kernels");
+  h->launches += 3;
+  // a slice whose commands did not fit (CABAC_SS_CAPACITY) has offsets past the scratch: the encoder must not read
+  // them, so such a call stops here with every slice's status written
+  CK(cudaMemsetAsync(out_sizes, 0, n_sub * 4, h->stream), "memset");
+  uint64_t total = 0;
+  CK(cudaMemcpyAsync(&total, cmdOffsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  if (total > cmd_scratch_words) {
+    CK(cudaMemcpyAsync(status, emitStatus, n_sub * 4, cudaMemcpyDeviceToDevice, h->stream), "copy");
+    h->err = "cabac_encode_slices_dev: cmd_scratch too small (status[] says which slices: CABAC_SS_CAPACITY)";
+    return CABAC_ERR_SUBSTREAM;
+  }
+  if (int rc = cabac_encode_stream_dev(h, cmd_scratch, cmdOffsets, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
+                                       out_offsets, out_sizes, num_bins, nullptr, ctx_out, status))
+    return rc;
+  CK(cabac::launchOrStatus(h->stream, status, emitStatus, n_sub), "or_status_kernel");
+  h->launches += 1;
   return CABAC_OK;
 }
 
@@ -924,6 +973,77 @@ int cabac_decode_bins(cabac_handle *h, const uint8_t *in, const uint64_t *in_off
   D2H(hst, dStatus, n_sub * 4);
   CK(cudaStreamSynchronize(h->stream), "sync");
   return anySubstreamFailed(hst, n_sub);
+}
+
+int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
+                        size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
+                        const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                        const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in,
+                        size_t cmd_words, uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes,
+                        uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (!h || (n_sub && (!params || !slice_params || !cus || !cu_offsets || !tus || !tu_flags || !tu_offsets || !ctus ||
+                       !ctu_offsets || !coeffs || !out || !out_offsets || !out_sizes)))
+    return badArg(h, "cabac_encode_slices");
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  const size_t nCu = cu_offsets[n_sub], nTu = tu_offsets[n_sub], nCtu = ctu_offsets[n_sub], outCap = out_offsets[n_sub];
+  cabac_substream_params *dP;
+  cabac_slice_params *dSp;
+  cabac_cu_desc *dCus;
+  cabac_tu_desc *dTus;
+  cabac_ctu_desc *dCtus;
+  uint8_t *dTuFlags, *dOut;
+  uint64_t *dCuOff, *dTuOff, *dCtuOff, *dOutOff;
+  int32_t *dCoeffs;
+  cabac_ctx_model *dCin, *dCout;
+  uint32_t *dCmds, *dSizes, *dBins, *dStatus;
+  Arena a(h);
+  a.want((void **)&dP, n_sub * sizeof(*params));
+  a.want((void **)&dSp, n_sub * sizeof(*slice_params));
+  a.want((void **)&dCus, nCu * sizeof(*cus));
+  a.want((void **)&dTus, nTu * sizeof(*tus));
+  a.want((void **)&dCtus, nCtu * sizeof(*ctus));
+  a.want((void **)&dTuFlags, nTu);
+  a.want((void **)&dCuOff, (n_sub + 1) * 8);
+  a.want((void **)&dTuOff, (n_sub + 1) * 8);
+  a.want((void **)&dCtuOff, (n_sub + 1) * 8);
+  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dCoeffs, n_coeffs * 4);
+  a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
+  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dCmds, cmd_words * 4);
+  a.want((void **)&dOut, outCap);
+  a.want((void **)&dSizes, n_sub * 4);
+  a.want((void **)&dBins, n_sub * 4);
+  a.want((void **)&dStatus, n_sub * 4);
+  CK(a.commit(), "scratch alloc");
+  H2D(dP, params, n_sub * sizeof(*params));
+  H2D(dSp, slice_params, n_sub * sizeof(*slice_params));
+  H2D(dCus, cus, nCu * sizeof(*cus));
+  H2D(dTus, tus, nTu * sizeof(*tus));
+  H2D(dCtus, ctus, nCtu * sizeof(*ctus));
+  H2D(dTuFlags, tu_flags, nTu);
+  H2D(dCuOff, cu_offsets, (n_sub + 1) * 8);
+  H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
+  H2D(dCtuOff, ctu_offsets, (n_sub + 1) * 8);
+  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dCoeffs, coeffs, n_coeffs * 4);
+  H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
+  const int rc = cabac_encode_slices_dev(h, dP, dSp, n_sub, dCus, dCuOff, dTus, dTuFlags, dTuOff, dCtus, dCtuOff, dCoeffs,
+                                         ctx_in ? dCin : nullptr, dCmds, cmd_words, dOut, dOutOff, dSizes, dBins,
+                                         ctx_out ? dCout : nullptr, dStatus);
+  std::vector<uint32_t> st(status ? 0 : n_sub);
+  uint32_t *hst = status ? status : st.data();
+  if (rc && rc != CABAC_ERR_SUBSTREAM) return rc;
+  D2H(hst, dStatus, n_sub * 4);
+  if (!rc) {
+    D2H(out, dOut, outCap);
+    D2H(out_sizes, dSizes, n_sub * 4);
+    D2H(num_bins, dBins, n_sub * 4);
+    D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+  }
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  return rc ? rc : anySubstreamFailed(hst, n_sub);
 }
 
 int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,

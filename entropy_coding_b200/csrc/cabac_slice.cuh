@@ -23,18 +23,23 @@ constexpr int SLICE_WARPS_PER_BLOCK = 2;
 constexpr int SLICE_MAX_LINE = 1024;  // 4096 luma samples
 constexpr int SLICE_MAX_CTU_COLS = 128;
 
-struct __align__(16) SliceWarpSmem {
-  LsDecoder dec;  // the arithmetic decoder's state: identical on all lanes, kept here between calls (see sliceBin)
-  int32_t tile[32 * 32];
-  uint4 ctx[CABAC_NUM_CTX];  // [0, RCTX): residual contexts in rctx() order; [RCTX, 379): the others
-  uint32_t rowCtx[CABAC_NUM_CTX];  // WPP: the states (entry .x) after the first CTU of the current row
-  uint16_t above[2][SLICE_MAX_LINE];
+// Neighbour state of the walk (cabac_syntax.cuh), per warp: used by the decoder and by the writer-direction emitter.
+struct SliceLines {
+  uint16_t above[2][SLICE_MAX_LINE];    // per tree: what the CU above left behind, one word per 4 luma samples
   uint16_t left[2][32];
   uint16_t edgeLeft[32];                // luma: right edge (x + w) of the CU last written at a row
   uint8_t modeAbove[SLICE_MAX_LINE];    // luma intra direction neighbours see (MPM derivation)
   uint8_t modeLeft[32];
   uint8_t lumaMap[256];                 // luma directions of the current 64x64 node, 4x4 granularity (chroma candidates)
   uint8_t ctuLine[SLICE_MAX_CTU_COLS];
+};
+
+struct __align__(16) SliceWarpSmem {
+  LsDecoder dec;  // the arithmetic decoder's state: identical on all lanes, kept here between calls (see sliceBin)
+  int32_t tile[32 * 32];
+  uint4 ctx[CABAC_NUM_CTX];  // [0, RCTX): residual contexts in rctx() order; [RCTX, 379): the others
+  uint32_t rowCtx[CABAC_NUM_CTX];  // WPP: the states (entry .x) after the first CTU of the current row
+  SliceLines lines;
 };
 
 // reference context id -> slot in SliceWarpSmem::ctx
@@ -126,6 +131,9 @@ __device__ uint32_t g_sliceTraceN[2];
 #endif
 
 struct SliceEngine {
+  static constexpr bool kEncode = false;  // decoder direction: the `want` arguments of the walk are ignored
+  __device__ __forceinline__ const cabac_cu_desc &getCu(uint32_t) const { return *cus; }
+  __device__ __forceinline__ const cabac_ctu_desc &getCtu(uint32_t) const { return *ctus; }
   bool traceOn = false;
   SliceWarpSmem &sm;
   const uint32_t subFlags;
@@ -143,21 +151,21 @@ struct SliceEngine {
       : sm(s), subFlags(f), cus(c), tus(t), tuFlags(tf), ctus(ct), coeffs(co) {}
   __device__ __forceinline__ static int laneId() { return int(threadIdx.x & 31u); }
 
-  __device__ __forceinline__ uint32_t bin(int id) {
+  __device__ __forceinline__ uint32_t bin(int id, uint32_t = 0) {
     const int lane = laneId();
     (void)lane;
     const uint32_t b = sliceBin(&sm, sliceCtxSlot(id));
     SLICE_TRACE(CABAC_MK_CTX(id, b));
     return b;
   }
-  __device__ __forceinline__ uint32_t ep(int n) {
+  __device__ __forceinline__ uint32_t ep(int n, uint32_t = 0) {
     const int lane = laneId();
     (void)lane;
     const uint32_t v = sliceEp(&sm, n);
     SLICE_TRACE(CABAC_MK_EP(v, n));
     return v;
   }
-  __device__ __forceinline__ uint32_t trm() {
+  __device__ __forceinline__ uint32_t trm(uint32_t = 1) {
     const int lane = laneId();
     (void)lane;
     const uint32_t b = sliceTrm(&sm);
@@ -178,13 +186,13 @@ struct SliceEngine {
     __syncwarp();  // lockstep: lane 0 must not fall behind - the next bin reads and rewrites a shared context
     return res;
   }
-  __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.above[ch]; }
-  __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.left[ch]; }
-  __device__ __forceinline__ uint8_t *ctuLine() { return sm.ctuLine; }
-  __device__ __forceinline__ uint8_t *modeAbove() { return sm.modeAbove; }
-  __device__ __forceinline__ uint8_t *modeLeft() { return sm.modeLeft; }
-  __device__ __forceinline__ uint16_t *edgeLeft() { return sm.edgeLeft; }
-  __device__ __forceinline__ uint8_t *lumaMap() { return sm.lumaMap; }
+  __device__ __forceinline__ uint16_t *aboveLine(int ch) { return sm.lines.above[ch]; }
+  __device__ __forceinline__ uint16_t *leftCol(int ch) { return sm.lines.left[ch]; }
+  __device__ __forceinline__ uint8_t *ctuLine() { return sm.lines.ctuLine; }
+  __device__ __forceinline__ uint8_t *modeAbove() { return sm.lines.modeAbove; }
+  __device__ __forceinline__ uint8_t *modeLeft() { return sm.lines.modeLeft; }
+  __device__ __forceinline__ uint16_t *edgeLeft() { return sm.lines.edgeLeft; }
+  __device__ __forceinline__ uint8_t *lumaMap() { return sm.lines.lumaMap; }
   __device__ __forceinline__ void fill8(uint8_t *p, int n, uint8_t v) {
     const int lane = laneId();
     for (int i = lane; i < n; i += 32) p[i] = v;
@@ -192,13 +200,13 @@ struct SliceEngine {
   }
   __device__ __forceinline__ void fillMap(int bx, int by, int bw, int bh, uint8_t v) {
     const int lane = laneId();
-    for (int i = lane; i < bw * bh; i += 32) sm.lumaMap[((by + i / bw) << 4) + bx + i % bw] = v;
+    for (int i = lane; i < bw * bh; i += 32) sm.lines.lumaMap[((by + i / bw) << 4) + bx + i % bw] = v;
     __syncwarp();
   }
   __device__ __forceinline__ void ctuLineStore(int col, uint8_t v) {
     const int lane = laneId();
     (void)lane;
-    if (lane == 0 && col < SLICE_MAX_CTU_COLS) sm.ctuLine[col] = v;
+    if (lane == 0 && col < SLICE_MAX_CTU_COLS) sm.lines.ctuLine[col] = v;
     __syncwarp();
   }
   __device__ __forceinline__ void fill(uint16_t *p, int n, uint16_t v) {
@@ -337,6 +345,185 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
     }
     __syncwarp();
   }
+}
+
+// ---------------------------------------------------------------------------
+// K10: writer direction (cabac_encode_slices).  The same walk on an engine that turns the caller's CU / TU / CTU
+// records into the BinEncIf call sequence of the slice - command words with CABAC_CMD_TU markers - which the
+// stream encoder (cabac_encode_stream: all encoder kernels) then codes.  No arithmetic coding here: one warp per
+// slice, two passes (count, then write at the scanned offsets).
+// ---------------------------------------------------------------------------
+struct SliceEmitEngine {
+  static constexpr bool kEncode = true;
+  SliceLines &ln;
+  const cabac_cu_desc *cusIn;
+  const cabac_tu_desc *tusIn;
+  const uint8_t *tuFlagsIn;
+  const cabac_ctu_desc *ctusIn;
+  uint32_t nCuIn, nTuIn, nCtuIn;
+  uint32_t *cmds;  // nullptr: count only
+  uint32_t n = 0;
+  bool dead = false, bad = false;
+
+  __device__ __forceinline__ SliceEmitEngine(SliceLines &l, const cabac_cu_desc *c, uint32_t nc, const cabac_tu_desc *t,
+                                             const uint8_t *tf, uint32_t nt, const cabac_ctu_desc *ct, uint32_t nct,
+                                             uint32_t *out)
+      : ln(l), cusIn(c), tusIn(t), tuFlagsIn(tf), ctusIn(ct), nCuIn(nc), nTuIn(nt), nCtuIn(nct), cmds(out) {}
+  __device__ __forceinline__ static int laneId() { return int(threadIdx.x & 31u); }
+  __device__ __forceinline__ void push(uint32_t w) {
+    if (cmds && laneId() == 0) cmds[n] = w;
+    n++;
+  }
+  __device__ __forceinline__ cabac_cu_desc getCu(uint32_t i) {
+    if (i >= nCuIn) {
+      bad = dead = true;
+      return cabac_cu_desc{};
+    }
+    return cusIn[i];
+  }
+  __device__ __forceinline__ cabac_ctu_desc getCtu(uint32_t i) {
+    if (i >= nCtuIn) {
+      bad = dead = true;
+      return cabac_ctu_desc{};
+    }
+    return ctusIn[i];
+  }
+  __device__ __forceinline__ uint32_t bin(int ctx, uint32_t want) {
+    push(CABAC_MK_CTX(ctx, want & 1u));
+    return want & 1u;
+  }
+  __device__ __forceinline__ uint32_t ep(int nb, uint32_t want) {
+    const uint32_t v = nb < 32 ? want & ((1u << nb) - 1u) : want;
+    int left_ = nb;
+    while (left_ > 16) {
+      push(CABAC_MK_EP((v >> (left_ - 16)) & 0xFFFFu, 16));
+      left_ -= 16;
+    }
+    push(CABAC_MK_EP(v & ((1u << left_) - 1u), left_));
+    return v;
+  }
+  __device__ __forceinline__ uint32_t trm(uint32_t want) {
+    push(CABAC_MK_TRM(want & 1u));
+    return want & 1u;
+  }
+  __device__ __forceinline__ uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
+    if (idx >= nTuIn) {
+      bad = dead = true;
+      return 0;
+    }
+    const cabac_tu_desc t = tusIn[idx];
+    if (t.log2_w != d.log2_w || t.log2_h != d.log2_h || t.comp_id != d.comp_id || ((t.flags ^ d.flags) & uint8_t(~CABAC_TU_TS))) {
+      bad = dead = true;
+      return 0;
+    }
+    push(CABAC_MK_TU());
+    return tuFlagsIn[idx];
+  }
+  __device__ __forceinline__ uint16_t *aboveLine(int ch) { return ln.above[ch]; }
+  __device__ __forceinline__ uint16_t *leftCol(int ch) { return ln.left[ch]; }
+  __device__ __forceinline__ uint8_t *ctuLine() { return ln.ctuLine; }
+  __device__ __forceinline__ uint8_t *modeAbove() { return ln.modeAbove; }
+  __device__ __forceinline__ uint8_t *modeLeft() { return ln.modeLeft; }
+  __device__ __forceinline__ uint16_t *edgeLeft() { return ln.edgeLeft; }
+  __device__ __forceinline__ uint8_t *lumaMap() { return ln.lumaMap; }
+  __device__ __forceinline__ void ctuLineStore(int col, uint8_t v) {
+    if (laneId() == 0 && col < SLICE_MAX_CTU_COLS) ln.ctuLine[col] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void fill(uint16_t *p, int cnt, uint16_t v) {
+    for (int i = laneId(); i < cnt; i += 32) p[i] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void fill8(uint8_t *p, int cnt, uint8_t v) {
+    for (int i = laneId(); i < cnt; i += 32) p[i] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void fillMap(int bx, int by, int bw, int bh, uint8_t v) {
+    for (int i = laneId(); i < bw * bh; i += 32) ln.lumaMap[((by + i / bw) << 4) + bx + i % bw] = v;
+    __syncwarp();
+  }
+  __device__ __forceinline__ void putCu(uint32_t, const cabac_cu_desc &) {}
+  __device__ __forceinline__ void putCtu(uint32_t, const cabac_ctu_desc &) {}
+  __device__ __forceinline__ void saveRowContexts() {}
+  __device__ __forceinline__ void nextRow() {}
+  __device__ __forceinline__ void abort() { dead = true; }
+  __device__ __forceinline__ bool aborted() const { return dead; }
+};
+
+constexpr int EMIT_WARPS_PER_BLOCK = 4;
+
+// cmdOffsets == nullptr: count pass (counts[sub] = words); otherwise write pass into cmds at cmdOffsets[sub].
+__global__ void __launch_bounds__(EMIT_WARPS_PER_BLOCK * 32)
+emit_slice_kernel(const cabac_slice_params *__restrict__ sliceParams, size_t nSub, const cabac_cu_desc *__restrict__ cus,
+                  const uint64_t *__restrict__ cuOffsets, const cabac_tu_desc *__restrict__ tus,
+                  const uint8_t *__restrict__ tuFlags, const uint64_t *__restrict__ tuOffsets,
+                  const cabac_ctu_desc *__restrict__ ctus, const uint64_t *__restrict__ ctuOffsets,
+                  uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets, uint64_t capWords,
+                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus) {
+  using Emitter = cabac_syntax::SliceParser<SliceEmitEngine>;
+  __shared__ SliceLines lines[EMIT_WARPS_PER_BLOCK];
+  __shared__ __align__(16) unsigned char engBuf[EMIT_WARPS_PER_BLOCK][(sizeof(SliceEmitEngine) + 15) & ~size_t(15)];
+  __shared__ __align__(16) unsigned char psBuf[EMIT_WARPS_PER_BLOCK][(sizeof(Emitter) + 15) & ~size_t(15)];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  for (size_t sub = size_t(blockIdx.x) * EMIT_WARPS_PER_BLOCK + wib; sub < nSub; sub += size_t(gridDim.x) * EMIT_WARPS_PER_BLOCK) {
+    const cabac_slice_params sp = sliceParams[sub];
+    const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub];
+    uint32_t *dst = nullptr;
+    bool over = false;
+    if (cmdOffsets) {
+      over = cmdOffsets[sub + 1] > capWords;
+      dst = over ? nullptr : cmds + cmdOffsets[sub];
+    }
+    __syncwarp();
+    SliceEmitEngine &eng = *new (engBuf[wib]) SliceEmitEngine(
+        lines[wib], cus + cu0, uint32_t(cuOffsets[sub + 1] - cu0), tus + tu0, tuFlags + tu0, uint32_t(tuOffsets[sub + 1] - tu0),
+        ctus + ctu0, uint32_t(ctuOffsets[sub + 1] - ctu0), dst);
+    __syncwarp();
+    Emitter &ps = *new (psBuf[wib]) Emitter(eng, sp, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, ~uint64_t(0), 0);
+    __syncwarp();
+    uint32_t st = 0;
+    if (((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SLICE_MAX_LINE) || ((sp.x1 - sp.x0) >> sp.log2_ctu) >= uint32_t(SLICE_MAX_CTU_COLS))
+      st |= CABAC_SS_UNSUPPORTED;
+    else
+      ps.run(false);  // the terminating bin and finish() are the stream encoder's (CABAC_SUB_TERMINATE)
+    st |= ps.status | (eng.bad ? uint32_t(CABAC_SS_BAD_DESC) : 0u) | (over ? uint32_t(CABAC_SS_CAPACITY) : 0u);
+    if (!st && (ps.nCu != eng.nCuIn || ps.nTu != eng.nTuIn)) st |= CABAC_SS_BAD_DESC;  // records left over
+    if (lane == 0) {
+      if (!cmdOffsets) counts[sub] = st ? 0u : eng.n;  // a refused slice codes nothing (its status says why)
+      emitStatus[sub] = st;
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void or_status_kernel(uint32_t *__restrict__ status, const uint32_t *__restrict__ extra, size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+    if (extra[i]) status[i] |= extra[i];
+}
+
+// scratch: counts u32[nSub] | emitStatus u32[nSub] | cmdOffsets u64[nSub + 1] (8-byte aligned by the caller)
+cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_slice_params *sliceParams, size_t nSub,
+                             const cabac_cu_desc *cus, const uint64_t *cuOffsets, const cabac_tu_desc *tus,
+                             const uint8_t *tuFlags, const uint64_t *tuOffsets, const cabac_ctu_desc *ctus,
+                             const uint64_t *ctuOffsets, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
+                             uint32_t *emitStatus, uint64_t *cmdOffsets) {
+  if (nSub == 0) return cudaSuccess;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const size_t want = (nSub + EMIT_WARPS_PER_BLOCK - 1) / EMIT_WARPS_PER_BLOCK, cap = size_t(sms) * 8;
+  const int blocks = int(want < cap ? want : cap);
+  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(sliceParams, nSub, cus, cuOffsets, tus, tuFlags, tuOffsets, ctus,
+                                                                ctuOffsets, nullptr, nullptr, capWords, counts, emitStatus);
+  entry_points_kernel<<<1, 1024, 0, s>>>(counts, nullptr, nSub, cmdOffsets);
+  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(sliceParams, nSub, cus, cuOffsets, tus, tuFlags, tuOffsets, ctus,
+                                                                ctuOffsets, cmds, cmdOffsets, capWords, counts, emitStatus);
+  return cudaGetLastError();
+}
+
+cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, size_t n) {
+  if (!n || !status) return cudaSuccess;
+  or_status_kernel<<<unsigned((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024), 256, 0, s>>>(status, extra, n);
+  return cudaGetLastError();
 }
 
 cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, const uint8_t *in, const uint64_t *inOffsets,

@@ -154,35 +154,42 @@ struct SliceParser {
   SX_FN bool tool(uint32_t t) const { return (sp.tools & t) != 0; }
 
   // ---- small binarisations ----
-  SX_FN uint32_t truncBin(uint32_t maxSymbol) {  // xReadTruncBinCode, cabac_reader.cpp:1162-1186 (maxSymbol <= 256)
-    int thresh = 0;
+  // Every decision goes through e.bin(ctx, want) / e.ep(n, want): a decoding engine ignores `want` and returns
+  // what the stream holds, an emitting engine (E::kEncode: the writer direction, cabac_encode_slices) codes `want`
+  // and returns it.  The walk is the same in both directions; in the writer direction `want` comes from the
+  // records the caller supplies (the very records the decoder direction produces).
+  SX_FN uint32_t truncBin(uint32_t maxSymbol, uint32_t want) {  // xReadTruncBinCode :1162-1186 / xWriteTruncBinCode
+    int thresh = 0;                                             // cabac_writer.cpp:854-882 (maxSymbol <= 256)
     while ((2u << thresh) <= maxSymbol) thresh++;  // g_tbMax[maxSymbol] = floor(log2)
     const uint32_t val = 1u << thresh, b = maxSymbol - val;
-    uint32_t symbol = thresh ? e.ep(thresh) : 0;
-    if (symbol >= val - b) symbol = ((symbol << 1) | e.ep(1)) - (val - b);
+    const bool wLong = want >= val - b;
+    const uint32_t wCode = wLong ? want + (val - b) : want;  // long codes: thresh + 1 bits of (symbol + val - b)
+    uint32_t symbol = thresh ? e.ep(thresh, wLong ? wCode >> 1 : wCode) : 0;
+    if (symbol >= val - b) symbol = ((symbol << 1) | e.ep(1, wCode & 1u)) - (val - b);
     return symbol;
   }
-  SX_FN uint32_t unaryMaxEp(uint32_t maxSymbol) {  // unary_max_eqprob, :3359-3366
+  SX_FN uint32_t unaryMaxEp(uint32_t maxSymbol, uint32_t want) {  // unary_max_eqprob, :3359-3366
     for (uint32_t k = 0; k < maxSymbol; k++)
-      if (!e.ep(1)) return k;
+      if (!e.ep(1, k < want ? 1u : 0u)) return k;
     return maxSymbol;
   }
-  SX_FN uint32_t unaryMaxSymbol(int ctx0, int ctxN, uint32_t maxSymbol) {  // :3349-3357
+  SX_FN uint32_t unaryMaxSymbol(int ctx0, int ctxN, uint32_t maxSymbol, uint32_t want) {  // :3349-3357
     uint32_t ones = 0;
-    while (ones < maxSymbol && e.bin(ones == 0 ? ctx0 : ctxN)) ones++;
+    while (ones < maxSymbol && e.bin(ones == 0 ? ctx0 : ctxN, ones < want ? 1u : 0u)) ones++;
     return ones;
   }
-  SX_FN uint32_t expGolombEp(uint32_t count) {  // exp_golomb_eqprob, :3368-3379
-    uint32_t symbol = 0, bit = 1;
+  SX_FN uint32_t expGolombEp(uint32_t count, uint32_t want) {  // exp_golomb_eqprob, :3368-3379 / cabac_writer.cpp:3096-3118
+    uint32_t symbol = 0, bit = 1, rem = want;
     while (bit) {
-      bit = e.ep(1);
+      bit = e.ep(1, rem >= (1u << count) ? 1u : 0u);
+      if (bit) rem -= rem >= (1u << count) ? (1u << count) : 0u;
       symbol += bit << count++;
       if (count > 31) {
         status |= CABAC_SS_COEFF_RANGE;
         break;
       }
     }
-    if (--count) symbol += e.ep(count);
+    if (--count) symbol += e.ep(count, rem & ((1u << count) - 1u));
     return symbol;
   }
 
@@ -335,7 +342,7 @@ struct SliceParser {
   }
 
   // ---- split_cu_mode (:677-751) with DeriveCtx::CtxSplit (context_modelling.cpp:108-204) ----
-  SX_FN int splitCuMode(const Node &n, int ch, int implicit) {
+  SX_FN int splitCuMode(const Node &n, int ch, int implicit, int want) {
     const uint32_t can = canSplit(n, ch, implicit);
     const bool canNo = can & 1, canQt = can & 2, canBh = can & 4, canBv = can & 8, canTh = can & 16, canTv = can & 32;
     const uint16_t left = nbLeft(ch, n.x, n.y), above = nbAbove(ch, n.x, n.y);
@@ -347,7 +354,7 @@ struct SliceParser {
       int numSplit = (canQt ? 2 : 0) + (canBh ? 1 : 0) + (canBv ? 1 : 0) + (canTh ? 1 : 0) + (canTv ? 1 : 0);
       if (numSplit > 0) numSplit--;
       ctx += 3 * (numSplit >> 1);
-      isSplit = e.bin(SX_SPLIT_FLAG + ctx) != 0;
+      isSplit = e.bin(SX_SPLIT_FLAG + ctx, want != SPL_NONE) != 0;
     }
     if (!isSplit) return SPL_NONE;
     const bool canBtt = canBh || canBv || canTh || canTv;
@@ -356,7 +363,7 @@ struct SliceParser {
       int ctx = (left && nbQt(left) > n.qt) ? 1 : 0;
       ctx += (above && nbQt(above) > n.qt) ? 1 : 0;
       ctx += n.qt < 2 ? 0 : 3;
-      isQt = e.bin(SX_SPLIT_QT_FLAG + ctx) != 0;
+      isQt = e.bin(SX_SPLIT_QT_FLAG + ctx, want == SPL_QUAD) != 0;
     }
     if (isQt) return SPL_QUAD;
     const bool canHor = canBh || canTh;
@@ -376,11 +383,12 @@ struct SliceParser {
       } else {
         ctx = numVer < numHor ? 3 : 4;
       }
-      isVer = e.bin(SX_SPLIT_HV_FLAG + ctx) != 0;
+      isVer = e.bin(SX_SPLIT_HV_FLAG + ctx, want == SPL_VERT || want == SPL_TRIV) != 0;
     }
     const bool can14 = isVer ? canTv : canTh;
     bool is12 = isVer ? canBv : canBh;
-    if (is12 && can14) is12 = e.bin(SX_SPLIT12_FLAG + (isVer ? (n.mt <= 1 ? 3 : 2) : (n.mt <= 1 ? 1 : 0))) != 0;
+    if (is12 && can14)
+      is12 = e.bin(SX_SPLIT12_FLAG + (isVer ? (n.mt <= 1 ? 3 : 2) : (n.mt <= 1 ? 1 : 0)), want == SPL_VERT || want == SPL_HORZ) != 0;
     return isVer ? (is12 ? SPL_VERT : SPL_TRIV) : (is12 ? SPL_HORZ : SPL_TRIH);
   }
 
@@ -458,7 +466,14 @@ struct SliceParser {
         if (tool(CABAC_SL_DQP) && n.qg && ch == 0) isDqpCoded = false;
         if (tool(CABAC_SL_CHROMA_QP_ADJ) && n.qgChroma) isChromaQpAdjCoded = false;
         const int implicit = implicitSplit(n, ch);
-        const int split = splitCuMode(n, ch, implicit);
+        // writer direction: the split of this node is on the path to the next CU of the list (split_series:
+        // three bits per depth below the tree's root, the CU's own depth holding "no split" = 0)
+        int want = SPL_NONE;
+        if (E::kEncode) {
+          const uint32_t ser = (e.getCu(nCu).split_series >> (3 * sp_)) & 7u;
+          want = ser ? int(ser) : int(SPL_NONE);
+        }
+        const int split = splitCuMode(n, ch, implicit, want);
         if (sp_ == 0 && ch == 0) lumaRootSplit = split;
         if (split == SPL_NONE) {
           codingUnit(n, ch, st, sp_);
@@ -508,26 +523,40 @@ struct SliceParser {
   // ---- coding_unit (:764-825) + cu_pred_data (:1097) + cu_residual (:1396) for an intra CU ----
   SX_FN void codingUnit(const Node &n, int ch, const Node *st, int depth) {
     cabac_cu_desc &cu = cuRec;
-    cu.x = uint16_t(n.x);
-    cu.y = uint16_t(n.y);
-    cu.log2_w = n.log2w;
-    cu.log2_h = n.log2h;
-    cu.ch_type = uint8_t(ch);
-    cu.qt_depth = n.qt;
-    cu.mt_depth = n.mt;
-    cu.flags = cu.bdpcm = cu.mrl_idx = cu.isp = cu.lfnst_idx = cu.mts_idx = cu.pred_syntax = 0;
-    cu.first_tu = nTu;
-    cu.n_tu = 0;
-    cu.qp_delta = 0;
-    cu.chroma_qp_adj = 0;
-    cu.intra_dir = 0;
-    cu.reserved[0] = cu.reserved[1] = cu.reserved[2] = 0;
+    if (E::kEncode) {
+      cu = e.getCu(nCu);  // the caller's record: must describe this very node
+      if (cu.x != uint16_t(n.x) || cu.y != uint16_t(n.y) || cu.log2_w != n.log2w || cu.log2_h != n.log2h ||
+          cu.ch_type != uint8_t(ch)) {
+        status |= CABAC_SS_BAD_DESC;
+        e.abort();
+        return;
+      }
+    } else {
+      cu.x = uint16_t(n.x);
+      cu.y = uint16_t(n.y);
+      cu.log2_w = n.log2w;
+      cu.log2_h = n.log2h;
+      cu.ch_type = uint8_t(ch);
+      cu.qt_depth = n.qt;
+      cu.mt_depth = n.mt;
+      cu.flags = cu.bdpcm = cu.mrl_idx = cu.isp = cu.lfnst_idx = cu.mts_idx = cu.pred_syntax = 0;
+      cu.first_tu = nTu;
+      cu.n_tu = 0;
+      cu.qp_delta = 0;
+      cu.chroma_qp_adj = 0;
+      cu.intra_dir = 0;
+      cu.reserved = 0;
+      cu.cbf_mask = 0;
+      uint32_t ser = 0;
+      for (int d = 0; d < depth && d < 10; d++) ser |= uint32_t(st[d].split & 7u) << (3 * d);
+      cu.split_series = ser;
+    }
     const int w = 1 << n.log2w, h = 1 << n.log2h;
     const int tsMax = 1 << sp.log2_max_ts, maxTb = 1 << sp.log2_max_tb;
     if (ch == 0) {
       // bdpcm_mode(Y), :1063-1095 with CU::bdpcmAllowed, unit_tools.cpp:226-241
       if (tool(CABAC_SL_BDPCM) && w <= tsMax && h <= tsMax) {
-        if (e.bin(SX_BDPCM_MODE + 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 1));
+        if (e.bin(SX_BDPCM_MODE + 0, cu.bdpcm != 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 1, cu.bdpcm == 2));
       }
       if (!cu.bdpcm) {  // intra_luma_pred_modes, :1231-1316
         int mip = 0;
@@ -535,33 +564,35 @@ struct SliceParser {
           const uint16_t left = nbLeft(0, n.x, n.y), above = nbAbove(0, n.x, n.y);
           int ctx = (left ? nbMip(left) : 0) + (above ? nbMip(above) : 0);
           if (w > 2 * h || h > 2 * w) ctx = 3;
-          mip = int(e.bin(SX_MIP_FLAG + ctx));
+          mip = int(e.bin(SX_MIP_FLAG + ctx, (cu.flags & CABAC_CU_MIP) != 0));
         }
         if (mip) {  // mip_pred_mode :3408
           cu.flags |= CABAC_CU_MIP;
-          if (e.ep(1)) cu.flags |= CABAC_CU_MIP_TRANSPOSED;
+          if (e.ep(1, (cu.flags & CABAC_CU_MIP_TRANSPOSED) != 0)) cu.flags |= CABAC_CU_MIP_TRANSPOSED;
           const int numModes = (w == 4 && h == 4) ? 16 : (w == 4 || h == 4 || (w == 8 && h == 8)) ? 8 : 6;
-          cu.pred_syntax = uint8_t(truncBin(uint32_t(numModes)));
+          cu.pred_syntax = uint8_t(truncBin(uint32_t(numModes), cu.pred_syntax));
         } else {
           // extend_ref_line :1188-1229
           if (tool(CABAC_SL_MRL) && (n.y & ((1 << sp.log2_ctu) - 1)) != 0) {
-            if (e.bin(SX_MULTI_REF_LINE_IDX + 0)) cu.mrl_idx = uint8_t(1 + e.bin(SX_MULTI_REF_LINE_IDX + 1));
+            if (e.bin(SX_MULTI_REF_LINE_IDX + 0, cu.mrl_idx != 0))
+              cu.mrl_idx = uint8_t(1 + e.bin(SX_MULTI_REF_LINE_IDX + 1, cu.mrl_idx == 2));
           }
           // isp_mode :2785-2806, CU::canUseISP unit_tools.cpp:290-298
           if (!cu.mrl_idx && tool(CABAC_SL_ISP) && n.log2w + n.log2h > 4 && w <= maxTb && h <= maxTb) {
-            if (e.bin(SX_ISP_MODE + 0)) cu.isp = uint8_t(1 + e.bin(SX_ISP_MODE + 1));
+            if (e.bin(SX_ISP_MODE + 0, cu.isp != 0)) cu.isp = uint8_t(1 + e.bin(SX_ISP_MODE + 1, cu.isp == 2));
           }
-          const bool mpm = cu.mrl_idx ? true : e.bin(SX_INTRA_LUMA_MPM_FLAG) != 0;
+          const bool mpm = cu.mrl_idx ? true : e.bin(SX_INTRA_LUMA_MPM_FLAG, (cu.flags & CABAC_CU_MPM) != 0) != 0;
           if (mpm) {
             cu.flags |= CABAC_CU_MPM;
-            uint32_t idx = cu.mrl_idx ? 1u : e.bin(SX_INTRA_LUMA_PLANAR_FLAG + (cu.isp ? 0 : 1));
-            if (idx) idx += e.ep(1);
-            if (idx > 1) idx += e.ep(1);
-            if (idx > 2) idx += e.ep(1);
-            if (idx > 3) idx += e.ep(1);
+            const uint32_t wi = cu.pred_syntax;
+            uint32_t idx = cu.mrl_idx ? 1u : e.bin(SX_INTRA_LUMA_PLANAR_FLAG + (cu.isp ? 0 : 1), wi > 0);
+            if (idx) idx += e.ep(1, wi > 1);
+            if (idx > 1) idx += e.ep(1, wi > 2);
+            if (idx > 2) idx += e.ep(1, wi > 3);
+            if (idx > 3) idx += e.ep(1, wi > 4);
             cu.pred_syntax = uint8_t(idx);
           } else {
-            cu.pred_syntax = uint8_t(truncBin(61));  // NUM_LUMA_MODE - NUM_MOST_PROBABLE_MODES
+            cu.pred_syntax = uint8_t(truncBin(61, cu.pred_syntax));  // NUM_LUMA_MODE - NUM_MOST_PROBABLE_MODES
           }
         }
       }
@@ -594,20 +625,21 @@ struct SliceParser {
     } else {
       const int cw = w >> 1, chh = h >> 1;
       if (tool(CABAC_SL_BDPCM) && cw <= tsMax && chh <= tsMax) {
-        if (e.bin(SX_BDPCM_MODE + 2)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 3));
+        if (e.bin(SX_BDPCM_MODE + 2, cu.bdpcm != 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 3, cu.bdpcm == 2));
       }
       if (!cu.bdpcm) {  // intra_chroma_pred_mode :1353-1394
         bool done = false;
         if (tool(CABAC_SL_CCLM) && cclmAllowed(n, st, depth)) {
-          if (e.bin(SX_CCLM_MODE_FLAG)) {
+          if (e.bin(SX_CCLM_MODE_FLAG, (cu.flags & CABAC_CU_CCLM) != 0)) {
             cu.flags |= CABAC_CU_CCLM;
-            uint32_t sym = e.bin(SX_CCLM_MODE_IDX);
-            if (sym) sym += e.ep(1);
+            const uint32_t ws = cu.pred_syntax;
+            uint32_t sym = e.bin(SX_CCLM_MODE_IDX, ws > 0);
+            if (sym) sym += e.ep(1, ws > 1);
             cu.pred_syntax = uint8_t(sym);
             done = true;
           }
         }
-        if (!done && e.bin(SX_INTRA_CHROMA_PRED_MODE)) cu.pred_syntax = uint8_t(1 + e.ep(2));
+        if (!done && e.bin(SX_INTRA_CHROMA_PRED_MODE, cu.pred_syntax != 0)) cu.pred_syntax = uint8_t(1 + e.ep(2, (cu.pred_syntax - 1u) & 3u));
       }
       // pu.intraDir[1], :1318-1394 with PU::getIntraChromaCandModes (unit_tools.cpp:460-483)
       if (cu.bdpcm) {
@@ -643,9 +675,10 @@ struct SliceParser {
         if (i == nParts - 1 && !rootCbfSoFar)
           cbf = true;  // lastCbfIsInferred, :2500-2511
         else
-          cbf = e.bin(SX_QT_CBF_Y + 2 + (prevCbf ? 1 : 0)) != 0;
+          cbf = e.bin(SX_QT_CBF_Y + 2 + (prevCbf ? 1 : 0), (cu.cbf_mask >> i) & 1u) != 0;
         rootCbfSoFar |= cbf;
         prevCbf = cbf;
+        if (cbf) cu.cbf_mask |= uint16_t(1u << i);
         if (cbf) dqp(cu);
         if (cbf) {
           const int tw = rows ? n.log2w : log2part, th = rows ? log2part : n.log2h;
@@ -659,8 +692,10 @@ struct SliceParser {
       const int nx = 1 << (n.log2w - tl2w), ny = 1 << (n.log2h - tl2h);
       for (int ty = 0; ty < ny; ty++)
         for (int tx = 0; tx < nx; tx++) {
+          const int tile = (ty * nx + tx) & 3;  // at most 2 x 2 tiles (128 / 32 is not reachable in a dual tree)
           if (ch == 0) {
-            const bool cbf = e.bin(SX_QT_CBF_Y + (cu.bdpcm ? 1 : 0)) != 0;  // cbf_comp :2353-2388
+            const bool cbf = e.bin(SX_QT_CBF_Y + (cu.bdpcm ? 1 : 0), (cu.cbf_mask >> tile) & 1u) != 0;  // cbf_comp :2353-2388
+            if (cbf) cu.cbf_mask |= uint16_t(1u << tile);
             if (cbf || w > 64 || h > 64) dqp(cu);
             if (cbf) {
               const bool tsAllowed = tool(CABAC_SL_TS) && !cu.bdpcm && (1 << tl2w) <= tsMax && (1 << tl2h) <= tsMax;
@@ -669,14 +704,17 @@ struct SliceParser {
             }
           } else {
             const int cl2w = tl2w - 1, cl2h = tl2h - 1;
-            const bool cbfCb = e.bin(SX_QT_CBF_CB + (cu.bdpcm ? 1 : 0)) != 0;
-            const bool cbfCr = e.bin(SX_QT_CBF_CR + (cu.bdpcm ? 2 : (cbfCb ? 1 : 0))) != 0;
+            const bool cbfCb = e.bin(SX_QT_CBF_CB + (cu.bdpcm ? 1 : 0), (cu.cbf_mask >> (4 + tile)) & 1u) != 0;
+            const bool cbfCr = e.bin(SX_QT_CBF_CR + (cu.bdpcm ? 2 : (cbfCb ? 1 : 0)), (cu.cbf_mask >> (8 + tile)) & 1u) != 0;
+            cu.cbf_mask |= uint16_t((cbfCb ? 1u << (4 + tile) : 0u) | (cbfCr ? 1u << (8 + tile) : 0u));
             const bool cbfChroma = cbfCb || cbfCr;
             // cu_chroma_qp_offset :2602-2630 (condition at :2551-2563)
             if (tool(CABAC_SL_CHROMA_QP_ADJ) && ((w >> 1) > 64 || (h >> 1) > 64 || cbfChroma) && !isChromaQpAdjCoded) {
-              uint32_t adj = e.bin(SX_CHROMA_QP_ADJ_FLAG);
+              const uint32_t wa = cu.chroma_qp_adj;
+              uint32_t adj = e.bin(SX_CHROMA_QP_ADJ_FLAG, wa != 0);
               if (adj && sp.chroma_qp_offset_list_len > 1)
-                adj += unaryMaxSymbol(SX_CHROMA_QP_ADJ_IDC, SX_CHROMA_QP_ADJ_IDC, sp.chroma_qp_offset_list_len - 1);
+                adj += unaryMaxSymbol(SX_CHROMA_QP_ADJ_IDC, SX_CHROMA_QP_ADJ_IDC, sp.chroma_qp_offset_list_len - 1,
+                                      wa ? wa - 1 : 0);
               cu.chroma_qp_adj = uint8_t(adj);
               isChromaQpAdjCoded = true;
             }
@@ -684,9 +722,12 @@ struct SliceParser {
             SX_OPAQUE(cbfMask);
             int joint = 0;
             if (tool(CABAC_SL_JCCR) && cbfMask) {  // joint_cb_cr :2632-2645 (intra CU)
-              if (e.bin(SX_JOINT_CBCR_FLAG + cbfMask - 1)) joint = cbfMask;
+              if (e.bin(SX_JOINT_CBCR_FLAG + cbfMask - 1, (cu.cbf_mask >> (12 + tile)) & 1u)) joint = cbfMask;
             }
-            if (joint) cu.flags |= CABAC_CU_JCCR;
+            if (joint) {
+              cu.flags |= CABAC_CU_JCCR;
+              cu.cbf_mask |= uint16_t(1u << (12 + tile));
+            }
             const bool tsAllowed = tool(CABAC_SL_TS) && !cu.bdpcm && (1 << cl2w) <= tsMax && (1 << cl2h) <= tsMax;
             const uint8_t fl = uint8_t((tsAllowed ? CABAC_TU_TS_ALLOWED : 0) | (cu.bdpcm ? CABAC_TU_BDPCM : 0));
             if (cbfCb) anyTs |= residual(cu, cl2w, cl2h, 1, fl);
@@ -713,8 +754,8 @@ struct SliceParser {
         const bool violates = (cuRes & CABAC_TUR_VIOLATES_LFNST) != 0;
         const bool lastPos = (cuRes & CABAC_TUR_LFNST_LAST_POS) != 0;
         if (!((!lastPos && !cu.isp) || violates || anyTs)) {
-          uint32_t idx = e.bin(SX_LFNST_IDX + 1);  // isSepTree: always in a dual-tree slice
-          if (idx) idx += e.bin(SX_LFNST_IDX + 2);
+          uint32_t idx = e.bin(SX_LFNST_IDX + 1, cu.lfnst_idx != 0);  // isSepTree: always in a dual-tree slice
+          if (idx) idx += e.bin(SX_LFNST_IDX + 2, cu.lfnst_idx == 2);
           cu.lfnst_idx = uint8_t(idx);
         }
       }
@@ -722,14 +763,15 @@ struct SliceParser {
     // ---- mts_idx :2754-2783, CU::isMTSAllowed unit_tools.cpp:243-260 ----
     if (ch == 0) {
       const bool firstTuTs = anyTs && !cu.isp;  // firstTU->mtsIdx[Y] == MTS_SKIP: MTS only exists for single-TU CUs
+      const uint32_t wm = cu.mts_idx;
       cu.mts_idx = firstTuTs ? 1 : 0;
       const bool allowed = tool(CABAC_SL_MTS_INTRA) && w <= 32 && h <= 32 && !cu.isp && !(cu.bdpcm && w <= tsMax && h <= tsMax);
       if (allowed && !(cuRes & CABAC_TUR_VIOLATES_MTS) && (cuRes & CABAC_TUR_MTS_LAST_POS) && cu.lfnst_idx == 0 &&
           !firstTuTs) {
-        if (e.bin(SX_MTS_IDX + 0)) {
+        if (e.bin(SX_MTS_IDX + 0, wm >= 2)) {
           int m = 2;
           for (int i = 0; i < 3; i++) {
-            const uint32_t s = e.bin(SX_MTS_IDX + 1 + i);
+            const uint32_t s = e.bin(SX_MTS_IDX + 1 + i, wm > uint32_t(2 + i));
             m += int(s);
             if (!s) break;
           }
@@ -748,9 +790,11 @@ struct SliceParser {
   // cu_qp_delta :2578-2600 under the condition of :2537-2545
   SX_FN void dqp(cabac_cu_desc &cu) {
     if (!tool(CABAC_SL_DQP) || isDqpCoded) return;
-    int dq = int(unaryMaxSymbol(SX_DELTA_QP, SX_DELTA_QP + 1, 5));
-    if (dq >= 5) dq += int(expGolombEp(0));
-    if (dq > 0 && e.ep(1)) dq = -dq;
+    const int wq = cu.qp_delta;
+    const uint32_t wAbs = uint32_t(wq < 0 ? -wq : wq);
+    int dq = int(unaryMaxSymbol(SX_DELTA_QP, SX_DELTA_QP + 1, 5, wAbs));
+    if (dq >= 5) dq += int(expGolombEp(0, wAbs >= 5 ? wAbs - 5 : 0));
+    if (dq > 0 && e.ep(1, wq < 0)) dq = -dq;
     cu.qp_delta = int8_t(dq);
     cu.flags |= CABAC_CU_DQP;
     isDqpCoded = true;
@@ -776,7 +820,7 @@ struct SliceParser {
     cuRes |= r;
     nTu++;
     nCoeff += area;
-    cu.n_tu++;
+    if (!E::kEncode) cu.n_tu++;
     return (r & CABAC_TUR_TS) != 0;
   }
 
@@ -785,8 +829,11 @@ struct SliceParser {
     const bool luma = tool(CABAC_SL_SAO_LUMA), chroma = tool(CABAC_SL_SAO_CHROMA);
     if (!luma && !chroma) return;
     int merge = -1;
-    if (leftAvail(ctuX)) merge += int(e.bin(SX_SAO_MERGE_FLAG));
-    if (merge < 0 && aboveAvail(ctuY)) merge += int(e.bin(SX_SAO_MERGE_FLAG)) << 1;
+    // writer direction: the record says "merge" in sao_mode (2) and which neighbour in sao_type (0 left, 1 above)
+    const bool wMerge = c.sao_mode[0] == 2;  // the luma entry carries the merge (:330-333), whichever planes use SAO
+    const uint32_t wMergeLeft = wMerge && c.sao_type[0] == 0, wMergeUp = wMerge && c.sao_type[0] == 1;
+    if (leftAvail(ctuX)) merge += int(e.bin(SX_SAO_MERGE_FLAG, wMergeLeft));
+    if (merge < 0 && aboveAvail(ctuY)) merge += int(e.bin(SX_SAO_MERGE_FLAG, wMergeUp)) << 1;
     if (merge >= 0) {
       c.sao_mode[0] = 2;
       c.sao_type[0] = uint8_t(merge);
@@ -800,10 +847,16 @@ struct SliceParser {
     const int bd = int(sp.bit_depth) < 10 ? int(sp.bit_depth) : 10;
     const uint32_t maxOffset = (1u << (bd - 5)) - 1;
     for (int comp = first; comp <= last; comp++) {
+      const uint8_t wType = c.sao_type[comp];  // writer direction: 0 band, 1..4 = edge class + 1
+      int8_t wOff[4];
+      for (int k = 0; k < 4; k++) wOff[k] = c.sao_offset[comp][k];
+      const uint8_t wBand = c.sao_band[comp];
       if (comp != 2) {
-        if (e.bin(SX_SAO_TYPE_IDX)) {
+        if (e.bin(SX_SAO_TYPE_IDX, c.sao_mode[comp] == 1)) {
           c.sao_mode[comp] = 1;
-          c.sao_type[comp] = e.ep(1) ? 1 : 0;  // 1 = edge (class added below), 0 = band
+          c.sao_type[comp] = e.ep(1, wType != 0) ? 1 : 0;  // 1 = edge (class added below), 0 = band
+        } else {
+          c.sao_mode[comp] = 0;
         }
       } else {
         c.sao_mode[2] = c.sao_mode[1];
@@ -811,13 +864,13 @@ struct SliceParser {
       }
       if (c.sao_mode[comp] == 0) continue;
       int off[4];
-      for (int k = 0; k < 4; k++) off[k] = int(unaryMaxEp(maxOffset));
+      for (int k = 0; k < 4; k++) off[k] = int(unaryMaxEp(maxOffset, uint32_t(wOff[k] < 0 ? -wOff[k] : wOff[k])));
       if (c.sao_type[comp] == 0) {  // band offset
         for (int k = 0; k < 4; k++)
-          if (off[k] && e.ep(1)) off[k] = -off[k];
-        c.sao_band[comp] = uint8_t(e.ep(5));
+          if (off[k] && e.ep(1, wOff[k] < 0)) off[k] = -off[k];
+        c.sao_band[comp] = uint8_t(e.ep(5, wBand));
       } else if (comp != 2) {
-        c.sao_type[comp] = uint8_t(1 + e.ep(2));  // sao_eo_class
+        c.sao_type[comp] = uint8_t(1 + e.ep(2, (wType - 1u) & 3u));  // sao_eo_class
       } else {
         c.sao_type[2] = c.sao_type[1];
       }
@@ -828,14 +881,18 @@ struct SliceParser {
   // ---- coding_tree_unit :103-209 ----
   SX_FN void codingTreeUnit(int ctuX, int ctuY) {
     cabac_ctu_desc &c = ctuRec;
-    for (int i = 0; i < 3; i++) {
-      c.sao_mode[i] = c.sao_type[i] = c.sao_band[i] = 0;
-      c.alf_flag[i] = 0;
-      c.reserved[i] = 0;
-      for (int k = 0; k < 4; k++) c.sao_offset[i][k] = 0;
+    if (E::kEncode) {
+      c = e.getCtu(nCtu);
+    } else {
+      for (int i = 0; i < 3; i++) {
+        c.sao_mode[i] = c.sao_type[i] = c.sao_band[i] = 0;
+        c.alf_flag[i] = 0;
+        c.reserved[i] = 0;
+        for (int k = 0; k < 4; k++) c.sao_offset[i][k] = 0;
+      }
+      c.alf_filter_idx = 0;
+      c.alf_alt[0] = c.alf_alt[1] = c.ccalf_idc[0] = c.ccalf_idc[1] = 0;
     }
-    c.alf_filter_idx = 0;
-    c.alf_alt[0] = c.alf_alt[1] = c.ccalf_idc[0] = c.ccalf_idc[1] = 0;
     sao(c, ctuX, ctuY);
     const int col = (ctuX - int(sp.x0)) >> sp.log2_ctu;
     const bool lAvail = leftAvail(ctuX), aAvail = aboveAvail(ctuY);
@@ -846,27 +903,29 @@ struct SliceParser {
       for (int comp = 0; comp < 3; comp++) {
         if (!tool(CABAC_SL_ALF_Y << comp)) continue;
         const int ctx = ((leftFlags >> comp) & 1) + ((aboveFlags >> comp) & 1);
-        const uint32_t f = e.bin(SX_CTB_ALF_FLAG + comp * 3 + ctx);
+        const uint32_t f = e.bin(SX_CTB_ALF_FLAG + comp * 3 + ctx, c.alf_flag[comp] != 0);
         c.alf_flag[comp] = uint8_t(f);
         mine |= uint8_t(f << comp);
         if (comp == 0 && f) {  // readAlfCtuFilterIndex :211-235
           const uint32_t numAps = sp.alf_num_aps_luma;
+          const uint32_t wi = c.alf_filter_idx;
           uint32_t idx = 0;
           if (numAps > 0) {
-            if (e.bin(SX_ALF_USE_TEMPORAL_FILT)) {
-              if (numAps > 1) idx = truncBin(numAps);
+            if (e.bin(SX_ALF_USE_TEMPORAL_FILT, wi >= 16)) {
+              if (numAps > 1) idx = truncBin(numAps, wi >= 16 ? wi - 16 : 0);
               idx += 16;
             } else {
-              idx = truncBin(16);
+              idx = truncBin(16, wi & 15u);
             }
           } else {
-            idx = truncBin(16);
+            idx = truncBin(16, wi & 15u);
           }
           c.alf_filter_idx = uint8_t(idx);
         }
         if (comp > 0 && f) {
+          const uint32_t wa = c.alf_alt[comp - 1];
           uint32_t decoded = 0;
-          while (decoded + 1 < sp.alf_chroma_num_alts && e.bin(SX_CTB_ALF_ALTERNATIVE + comp - 1)) decoded++;
+          while (decoded + 1 < sp.alf_chroma_num_alts && e.bin(SX_CTB_ALF_ALTERNATIVE + comp - 1, decoded < wa)) decoded++;
           c.alf_alt[comp - 1] = uint8_t(decoded);
         }
       }
@@ -874,9 +933,10 @@ struct SliceParser {
     for (int comp = 1; comp < 3; comp++) {  // ccAlfFilterControlIdc :237-276
       if (!tool(CABAC_SL_CCALF_CB << (comp - 1))) continue;
       int ctx = ((leftFlags >> (2 + comp)) & 1) + ((aboveFlags >> (2 + comp)) & 1) + (comp == 2 ? 3 : 0);
-      uint32_t idc = e.bin(SX_CCALF_FILTER_CONTROL_FLAG + ctx);
+      const uint32_t wc = c.ccalf_idc[comp - 1];
+      uint32_t idc = e.bin(SX_CCALF_FILTER_CONTROL_FLAG + ctx, wc != 0);
       if (idc)
-        while (idc != sp.ccalf_filter_count[comp - 1] && e.ep(1)) idc++;
+        while (idc != sp.ccalf_filter_count[comp - 1] && e.ep(1, idc < wc)) idc++;
       c.ccalf_idc[comp - 1] = uint8_t(idc);
       if (idc) mine |= uint8_t(4u << comp);
     }
@@ -942,11 +1002,15 @@ struct SliceParser {
       status |= CABAC_SS_UNSUPPORTED;
       return;
     }
+    if (E::kEncode && tool(CABAC_SL_WPP)) {  // writer direction: one command stream per slice; WPP rows are separate
+      status |= CABAC_SS_UNSUPPORTED;          // substreams of the encoder (cabac_encode_stream_wpp) - not built
+      return;
+    }
     const int ctu = 1 << sp.log2_ctu;
     const bool wpp = tool(CABAC_SL_WPP);
     for (int y = int(sp.y0); y < int(sp.y1) && !e.aborted(); y += ctu) {
       if (wpp && y > int(sp.y0)) {
-        if (!e.trm()) {  // end_of_subset_one_bit
+        if (!e.trm(1)) {  // end_of_subset_one_bit
           status |= CABAC_SS_NO_TERMINATE;
           return;
         }
@@ -958,7 +1022,7 @@ struct SliceParser {
         if (wpp && x == int(sp.x0)) e.saveRowContexts();
       }
     }
-    if (terminate && !e.aborted() && !e.trm()) status |= CABAC_SS_NO_TERMINATE;
+    if (terminate && !e.aborted() && !e.trm(1)) status |= CABAC_SS_NO_TERMINATE;
   }
 };
 

@@ -334,6 +334,40 @@ class CabacEngine:
                                                      _dp(tu_flags), _dp(ctus), _dp(coeffs), _dp(counts), _dp(num_bins),
                                                      _dp(bits_read), _dp(ctx_out), _dp(status)))
 
+    def encode_slices(self, params, slice_params, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus, ctu_offsets, coeffs,
+                      out_offsets, cmd_words=None, ctx_in=None, want_ctx=False, raise_on_status=True):
+        """cabac_encode_slices: the writer direction - CU / TU / CTU records (as decode_slices returns them, compacted
+        to exact offsets) to slice payloads."""
+        params, sp = _np(params, PARAMS_DT), _np(slice_params, SLICE_DT)
+        cus, tus, ctus = _np(cus, CU_DT), _np(tus, TU_DT), _np(ctus, CTU_DT)
+        tu_flags, coeffs = _np(tu_flags, np.uint8), _np(coeffs, np.int32)
+        cu_offsets, tu_offsets = _np(cu_offsets, np.uint64), _np(tu_offsets, np.uint64)
+        ctu_offsets, out_offsets = _np(ctu_offsets, np.uint64), _np(out_offsets, np.uint64)
+        n = len(params)
+        if cmd_words is None:
+            area = (sp["x1"].astype(np.int64) - sp["x0"]) * (sp["y1"].astype(np.int64) - sp["y0"])
+            cmd_words = int(area.sum()) * 4 + 64 * n
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_slices(self.h, _hp(params), _hp(sp), n, _hp(cus), _hp(cu_offsets), _hp(tus),
+                                          _hp(tu_flags), _hp(tu_offsets), _hp(ctus), _hp(ctu_offsets), _hp(coeffs),
+                                          coeffs.size, _hp(ctx_in), int(cmd_words), _hp(out), _hp(out_offsets), _hp(sizes),
+                                          _hp(bins), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, status=status, ctx_out=ctx_out)
+
+    def encode_slices_dev(self, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus,
+                          ctu_offsets, coeffs, cmd_scratch, cmd_scratch_words, out, out_offsets, out_sizes, status,
+                          num_bins=None, ctx_in=None, ctx_out=None):
+        self._check(self.lib.cabac_encode_slices_dev(self.h, _dp(params), _dp(slice_params), n_sub, _dp(cus),
+                                                     _dp(cu_offsets), _dp(tus), _dp(tu_flags), _dp(tu_offsets), _dp(ctus),
+                                                     _dp(ctu_offsets), _dp(coeffs), _dp(ctx_in), _dp(cmd_scratch),
+                                                     int(cmd_scratch_words), _dp(out), _dp(out_offsets), _dp(out_sizes),
+                                                     _dp(num_bins), _dp(ctx_out), _dp(status)))
+
     # ---- WPP: CTU rows with context hand-over in one launch (cabac_*_wpp) ----
     def encode_residual_wpp(self, tus, tu_offsets, params, wpp, coeffs, out_offsets, packed=None, ctx_in=None,
                             want_ctx=False, raise_on_status=True):

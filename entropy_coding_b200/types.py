@@ -25,11 +25,11 @@ SLICE_DT = np.dtype([(f, "<u4") for f in SLICE_FIELDS])
 CU_DT = np.dtype([("x", "<u2"), ("y", "<u2"), ("log2_w", "u1"), ("log2_h", "u1"), ("ch_type", "u1"), ("qt_depth", "u1"),
                   ("mt_depth", "u1"), ("flags", "u1"), ("bdpcm", "u1"), ("mrl_idx", "u1"), ("isp", "u1"),
                   ("lfnst_idx", "u1"), ("mts_idx", "u1"), ("pred_syntax", "u1"), ("first_tu", "<u4"), ("n_tu", "<u2"),
-                  ("qp_delta", "i1"), ("chroma_qp_adj", "u1"), ("intra_dir", "u1"), ("reserved", "u1", 3)])
+                  ("qp_delta", "i1"), ("chroma_qp_adj", "u1"), ("intra_dir", "u1"), ("reserved", "u1"), ("cbf_mask", "<u2"), ("split_series", "<u4")])
 CTU_DT = np.dtype([("sao_mode", "u1", 3), ("sao_type", "u1", 3), ("sao_band", "u1", 3), ("sao_offset", "i1", (3, 4)),
                    ("alf_flag", "u1", 3), ("alf_filter_idx", "u1"), ("alf_alt", "u1", 2), ("ccalf_idc", "u1", 2),
                    ("reserved", "u1", 3)])
-assert SLICE_DT.itemsize == 128 and CU_DT.itemsize == 28 and CTU_DT.itemsize == 32
+assert SLICE_DT.itemsize == 128 and CU_DT.itemsize == 32 and CTU_DT.itemsize == 32
 SL_DUAL_TREE, SL_SAO_LUMA, SL_SAO_CHROMA, SL_ALF_Y, SL_ALF_CB, SL_ALF_CR, SL_CCALF_CB, SL_CCALF_CR = (1 << i for i in range(8))
 SL_MTS_INTRA, SL_LFNST, SL_ISP, SL_MIP, SL_MRL, SL_TS, SL_BDPCM, SL_JCCR = (1 << i for i in range(8, 16))
 SL_CCLM, SL_DQP, SL_CHROMA_QP_ADJ, SL_WPP, SL_IBC, SL_PLT, SL_ACT, SL_INTRA, SL_MTS = (1 << i for i in range(16, 25))

@@ -797,7 +797,12 @@ typedef struct cabac_cu_desc {
   uint8_t intra_dir;      /* pu.intraDir[chType] as the reader leaves it: luma 0..66 from the MPM
                              list (PU::getIntraMPMs, unit_tools.cpp:485-577) or the MIP mode;
                              chroma 0..66, 67..69 = LM / MDLM_L / MDLM_T, 70 = DM_CHROMA_IDX      */
-  uint8_t reserved[3];
+  uint8_t reserved;
+  uint16_t cbf_mask;      /* coded block flags as parsed: bits 0-3 luma (ISP sub-partition / transform tile i),
+                             4-7 Cb, 8-11 Cr (per tile), 12-15 tu_joint_cbcr_residual_flag (per tile)     */
+  uint32_t split_series;  /* the path from the tree's root (the CTU; the 64x64 node of a 128x128 dual-tree
+                             CTU) to this CU: 3 bits per depth, 1 QT, 2 BT hor, 3 BT ver, 4 TT hor, 5 TT ver
+                             (CU::getSplitAtDepth, unit_tools.cpp); 0 from the CU's own depth on          */
 } cabac_cu_desc;
 
 /* Per-CTU in-loop filter syntax (SAOBlkParam, sample_adaptive_offset.hpp; the ALF CTU maps of
@@ -842,6 +847,47 @@ int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_o
                         const uint64_t *coeff_offsets, cabac_cu_desc *cus, cabac_tu_desc *tus,
                         uint8_t *tu_flags, cabac_ctu_desc *ctus, int32_t *coeffs,
                         uint32_t *counts, uint32_t *num_bins, uint32_t *bits_read,
+                        cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* Writer direction of the same syntax: CABACWriter::coding_tree_unit (cabac_writer.cpp:115) and what it
+ * calls - sao :196, coding_tree :355, split_cu_mode :514, coding_unit :586, intra_luma_pred_modes :949,
+ * intra_chroma_pred_mode :1167, transform_tree :2059, transform_unit :2219, cu_qp_delta :2356,
+ * residual_coding :2424 - as one call:
+ * records in, slice payloads out, byte-identical with the reference writer's.  The records are exactly the
+ * ones cabac_decode_slices produces (an encoder fills them from its CodingStructure the way
+ * host/gpu_slice_reader.hpp reads them back): CUs in coding order with split_series, cbf_mask and the
+ * prediction syntax, TUs in coding order with coeff_offset absolute in `coeffs` and tu_flags (CABAC_TUR_*,
+ * from cabac_decode_slices or from cabac_estimate_residual on the same TUs), one CTU record per CTU.
+ * Here the offsets are exact: slice i owns cus[cu_offsets[i] .. cu_offsets[i+1]) etc.
+ * Two kernels walk the partitioning per slice (one warp each) and write the slice's BinEncIf call sequence
+ * as command words into cmd_scratch (cmd_scratch_words uint32 available; about 1.2 words per bin outside
+ * residuals - 4 words per luma sample of the rectangle always suffice); the stream encoder
+ * (cabac_encode_stream_dev) then codes them, terminating bin and finish() included
+ * (params[i].flags: CABAC_SUB_TERMINATE | CABAC_SUB_ALIGN as for every slice payload).
+ * status[i]: CABAC_SS_* of the stream encoder, plus CABAC_SS_UNSUPPORTED (see cabac_decode_slices; also
+ * CABAC_SL_WPP, whose rows are separate substreams on the writer side: pass one rectangle per CTU row
+ * and chain the contexts with cabac_encode_stream_dev's wavefront mode), CABAC_SS_BAD_DESC (records that do
+ * not describe a legal partitioning of the rectangle, or left-over records) and CABAC_SS_CAPACITY
+ * (cmd_scratch too small: nothing is encoded and the call returns CABAC_ERR_SUBSTREAM).
+ * The _dev form synchronises the stream once (it reads the total command count back).              */
+int cabac_encode_slices_dev(cabac_handle *h, const cabac_substream_params *params,
+                            const cabac_slice_params *slice_params, size_t n_sub,
+                            const cabac_cu_desc *cus, const uint64_t *cu_offsets,
+                            const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                            const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                            const uint64_t *ctu_offsets, const int32_t *coeffs,
+                            const cabac_ctx_model *ctx_in, uint32_t *cmd_scratch,
+                            size_t cmd_scratch_words, uint8_t *out, const uint64_t *out_offsets,
+                            uint32_t *out_sizes, uint32_t *num_bins, cabac_ctx_model *ctx_out,
+                            uint32_t *status);
+int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params,
+                        const cabac_slice_params *slice_params, size_t n_sub,
+                        const cabac_cu_desc *cus, const uint64_t *cu_offsets,
+                        const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                        const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                        const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs,
+                        const cabac_ctx_model *ctx_in, size_t cmd_words, uint8_t *out,
+                        const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
                         cabac_ctx_model *ctx_out, uint32_t *status);
 
 #ifdef __cplusplus

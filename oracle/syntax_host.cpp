@@ -19,6 +19,9 @@ extern "C" {
 
 namespace {
 struct HostEngine {
+  static constexpr bool kEncode = false;
+  const cabac_cu_desc &getCu(uint32_t) const { return *cusOut; }      // writer direction only
+  const cabac_ctu_desc &getCtu(uint32_t) const { return *ctusOut; }
   void *dec = nullptr;
   std::vector<uint32_t> trace;
   std::vector<uint16_t> above[2], left[2];
@@ -31,17 +34,17 @@ struct HostEngine {
   int32_t *coeffs;
   bool dead = false;
 
-  uint32_t bin(int ctx) {
+  uint32_t bin(int ctx, uint32_t = 0) {
     const uint32_t b = orc_dec_bin(dec, unsigned(ctx));
     trace.push_back(CABAC_MK_CTX(ctx, b));
     return b;
   }
-  uint32_t ep(int n) {
+  uint32_t ep(int n, uint32_t = 0) {
     const uint32_t v = orc_dec_ep(dec, unsigned(n));
     trace.push_back(CABAC_MK_EP(v, n));
     return v;
   }
-  uint32_t trm() {
+  uint32_t trm(uint32_t = 1) {
     const uint32_t b = orc_dec_trm(dec);
     trace.push_back(CABAC_MK_TRM(b));
     return b;
@@ -147,6 +150,9 @@ long syn_decode_slice(const uint8_t *in, long nbytes, const cabac_substream_para
 // CTU syntax, 32-sample maximum transform size, capacity limits - and gives the device a dense, realistic-size input.
 namespace {
 struct GenEngine {
+  static constexpr bool kEncode = false;  // it chooses values itself: the walk records them like a decoder
+  const cabac_cu_desc &getCu(uint32_t) const { return *cusOut; }
+  const cabac_ctu_desc &getCtu(uint32_t) const { return *ctusOut; }
   void *enc = nullptr;
   uint64_t rng;
   double splitP, density;
@@ -168,7 +174,7 @@ struct GenEngine {
     return rng;
   }
   double uni() { return double(next() >> 11) * (1.0 / 9007199254740992.0); }
-  uint32_t bin(int ctx) {
+  uint32_t bin(int ctx, uint32_t = 0) {
     using namespace cabac_syntax;
     double p1 = 0.5;
     if (ctx >= SX_SPLIT_FLAG && ctx < SX_SPLIT_QT_FLAG) p1 = splitP;
@@ -183,7 +189,7 @@ struct GenEngine {
     orc_enc_bin(enc, b, unsigned(ctx));
     return b;
   }
-  uint32_t ep(int n) {
+  uint32_t ep(int n, uint32_t = 0) {
     uint32_t v = uint32_t(next() >> 20);
     if (n < 32) v &= (1u << n) - 1u;
     int left_ = n;  // encodeBinsEP takes at most 32 bins; feed 16 at a time, MSB first
@@ -194,7 +200,7 @@ struct GenEngine {
     orc_enc_ep(enc, v & ((1u << left_) - 1u), unsigned(left_));
     return v;
   }
-  uint32_t trm() {
+  uint32_t trm(uint32_t = 1) {
     orc_enc_trm(enc, 1);
     return 1;
   }
@@ -291,4 +297,118 @@ extern "C" long syn_generate_slice(uint64_t seed, double splitP, double density,
   *status = ps.status | (e.dead ? uint32_t(CABAC_SS_CAPACITY) : 0u);
   orc_enc_flush(e.enc, 0);
   return orc_enc_close(e.enc, ctxOut, numBins);
+}
+
+// ---- writer direction on the host: the walk on an engine that turns records into the call sequence -------------
+namespace {
+struct EmitEngine {
+  static constexpr bool kEncode = true;
+  const cabac_cu_desc *cusIn;
+  const cabac_ctu_desc *ctusIn;
+  const cabac_tu_desc *tusIn;
+  const uint8_t *tuFlagsIn;
+  uint32_t nCuIn, nTuIn, nCtuIn;
+  std::vector<uint32_t> cmds;
+  std::vector<uint16_t> above[2], left[2], eLeft;
+  std::vector<uint8_t> ctus, mAbove, mLeft, lmap;
+  bool dead = false, bad = false;
+  cabac_cu_desc dummyCu{};
+  cabac_ctu_desc dummyCtu{};
+
+  const cabac_cu_desc &getCu(uint32_t i) {
+    if (i >= nCuIn) {
+      bad = dead = true;
+      return dummyCu;
+    }
+    return cusIn[i];
+  }
+  const cabac_ctu_desc &getCtu(uint32_t i) {
+    if (i >= nCtuIn) {
+      bad = dead = true;
+      return dummyCtu;
+    }
+    return ctusIn[i];
+  }
+  uint32_t bin(int ctx, uint32_t want) {
+    cmds.push_back(CABAC_MK_CTX(ctx, want & 1u));
+    return want & 1u;
+  }
+  uint32_t ep(int n, uint32_t want) {
+    const uint32_t v = n < 32 ? want & ((1u << n) - 1u) : want;
+    int left_ = n;
+    while (left_ > 16) {
+      cmds.push_back(CABAC_MK_EP((v >> (left_ - 16)) & 0xFFFFu, 16));
+      left_ -= 16;
+    }
+    cmds.push_back(CABAC_MK_EP(v & ((1u << left_) - 1u), left_));
+    return v;
+  }
+  uint32_t trm(uint32_t want) {
+    cmds.push_back(CABAC_MK_TRM(want & 1u));
+    return want & 1u;
+  }
+  uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
+    if (idx >= nTuIn || tusIn[idx].log2_w != d.log2_w || tusIn[idx].log2_h != d.log2_h || tusIn[idx].comp_id != d.comp_id ||
+        ((tusIn[idx].flags ^ d.flags) & uint8_t(~CABAC_TU_TS))) {
+      bad = dead = true;
+      return 0;
+    }
+    cmds.push_back(CABAC_MK_TU());
+    return tuFlagsIn[idx];
+  }
+  uint16_t *aboveLine(int ch) { return above[ch].data(); }
+  uint16_t *leftCol(int ch) { return left[ch].data(); }
+  uint8_t *ctuLine() { return ctus.data(); }
+  void ctuLineStore(int col, uint8_t v) { ctus[size_t(col)] = v; }
+  uint8_t *modeAbove() { return mAbove.data(); }
+  uint8_t *modeLeft() { return mLeft.data(); }
+  uint16_t *edgeLeft() { return eLeft.data(); }
+  uint8_t *lumaMap() { return lmap.data(); }
+  void fill(uint16_t *p, int n, uint16_t v) {
+    for (int i = 0; i < n; i++) p[i] = v;
+  }
+  void fill8(uint8_t *p, int n, uint8_t v) {
+    for (int i = 0; i < n; i++) p[i] = v;
+  }
+  void fillMap(int bx, int by, int bw, int bh, uint8_t v) {
+    for (int y = 0; y < bh; y++)
+      for (int x = 0; x < bw; x++) lmap[size_t(((by + y) << 4) + bx + x)] = v;
+  }
+  void putCu(uint32_t, const cabac_cu_desc &) {}
+  void putCtu(uint32_t, const cabac_ctu_desc &) {}
+  void saveRowContexts() {}
+  void nextRow() {}
+  void abort() { dead = true; }
+  bool aborted() const { return dead; }
+};
+}  // namespace
+
+// Records of one slice (as cabac_decode_slices returns them) -> the BinEncIf call sequence of its writer, as
+// command words with CABAC_CMD_TU markers (the input of cabac_encode_stream).  Returns the number of words.
+extern "C" long syn_emit_slice(const cabac_slice_params *sp, const cabac_cu_desc *cus, long nCu, const cabac_tu_desc *tus,
+                               const uint8_t *tuFlags, long nTu, const cabac_ctu_desc *ctus, long nCtu, uint32_t *cmds,
+                               long cap, uint32_t *status) {
+  EmitEngine e;
+  e.cusIn = cus;
+  e.ctusIn = ctus;
+  e.tusIn = tus;
+  e.tuFlagsIn = tuFlags;
+  e.nCuIn = uint32_t(nCu);
+  e.nTuIn = uint32_t(nTu);
+  e.nCtuIn = uint32_t(nCtu);
+  for (int ch = 0; ch < 2; ch++) {
+    e.above[ch].assign(cabac_syntax::SX_MAX_LINE, 0);
+    e.left[ch].assign(32, 0);
+  }
+  e.ctus.assign(512, 0);
+  e.mAbove.assign(cabac_syntax::SX_MAX_LINE, 0);
+  e.mLeft.assign(32, 0);
+  e.eLeft.assign(32, 0);
+  e.lmap.assign(256, 0);
+  cabac_syntax::SliceParser<EmitEngine> ps(e, *sp, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, ~uint64_t(0), 0);
+  ps.run(true);
+  *status = ps.status | (e.bad ? uint32_t(CABAC_SS_BAD_DESC) : 0u);
+  if (ps.nCu != e.nCuIn || ps.nTu != e.nTuIn) *status |= CABAC_SS_BAD_DESC;  // records left over
+  for (long i = 0; i < long(e.cmds.size()) && i < cap; i++) cmds[i] = e.cmds[size_t(i)];
+  return long(e.cmds.size());
 }

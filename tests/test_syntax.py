@@ -29,7 +29,7 @@ sys.path.insert(0, os.path.join(HERE, "golden"))
 from vtm_streams import load_fixture  # noqa: E402
 
 from entropy_coding_b200.types import (CTU_DT, CTX_DT, CU_DT, CU_MIP, CU_MIP_TRANSPOSED, PARAMS_DT, SL_WPP, SLICE_DT,
-                                       SS_UNSUPPORTED, SUB_CTX_IN, SUB_TERMINATE, TU_DT)
+                                       SS_BAD_DESC, SS_CAPACITY, SS_UNSUPPORTED, SUB_ALIGN, SUB_CTX_IN, SUB_TERMINATE, TU_DT)
 
 FIXTURES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(HERE, "golden", "vtm_*.npz")))
 
@@ -491,3 +491,111 @@ def test_gpu_decode_slices_on_generated_streams(engine):
         _check_against_generator(tag, one, g)
         a, b = int(cap["ctu"][k]), int(cap["ctu"][k + 1])
         assert r["ctus"][a:b].tobytes() == g["ctus"].tobytes(), f"{tag}: CTU records"
+
+
+# ---- writer direction: records -> the writer's call sequence (syn_emit_slice on the host, cabac_encode_slices on the GPU)
+def _host_emit(lib, sp, r):
+    lib.syn_emit_slice.restype = C.c_long
+    cmds, st = np.zeros(1 << 20, np.uint32), np.zeros(1, np.uint32)
+    cus, tus, tuf, ctus = (np.ascontiguousarray(r[k]) for k in ("cus", "tus", "tu_flags", "ctus"))
+    n = lib.syn_emit_slice(_p(np.array([sp], SLICE_DT)), _p(cus), C.c_long(len(cus)), _p(tus), _p(tuf), C.c_long(len(tus)),
+                           _p(ctus), C.c_long(len(ctus)), _p(cmds), C.c_long(cmds.size), _p(st))
+    return cmds[:n], int(st[0])
+
+
+def test_host_writer_direction_reproduces_the_writers_calls():
+    """Decode a VTM slice to records, then walk the records in the writer direction: the emitted BinEncIf call
+    sequence is the one the reference's CABACWriter made (so cabac_encode_stream turns it into VTM's bytes)."""
+    lib = _host_lib()
+    n = 0
+    for tag, s, sp in _substreams():
+        if int(sp["tools"]) & SL_WPP:
+            continue
+        r = _host_decode(lib, s, sp)
+        nctu = -(-int(sp["x1"] - sp["x0"]) >> int(sp["log2_ctu"])) * -(-int(sp["y1"] - sp["y0"]) >> int(sp["log2_ctu"]))
+        r["ctus"] = r["ctus"][:nctu]
+        cmds, st = _host_emit(lib, sp, r)
+        assert st == 0, f"{tag}: emit status {st}"
+        got, want = _flat(cmds), _flat(s["cmds"])
+        bad = next((k for k in range(min(len(got), len(want))) if got[k] != want[k]), None)
+        assert bad is None and len(got) == len(want), f"{tag}: call {bad}: emitted {got[bad - 2:bad + 3] if bad is not None else len(got)} writer {want[bad - 2:bad + 3] if bad is not None else len(want)}"
+        n += 1
+    assert n >= 6
+    # and on generated slices (all tools): emit(decode(x)) is the generating walk's sequence again
+    for tag, g, sp in _gen_items(lib):
+        if int(sp["tools"]) & SL_WPP:
+            continue
+        r = _host_decode_fresh(lib, g, sp)
+        r["ctus"] = r["ctus"][:len(g["ctus"])]
+        cmds, st = _host_emit(lib, sp, r)
+        assert st == 0 and _flat(cmds) == _flat(r["trace"]), tag
+
+
+def _compact(r, n):
+    """decode_slices output (capacity-spaced regions) -> exact-offset records for the writer direction."""
+    cap, cnt = r["cap"], r["counts"]
+    cus = np.concatenate([r["cus"][int(cap["cu"][k]):int(cap["cu"][k]) + int(cnt[k][0])] for k in range(n)])
+    tus = np.concatenate([r["tus"][int(cap["tu"][k]):int(cap["tu"][k]) + int(cnt[k][1])] for k in range(n)])
+    tuf = np.concatenate([r["tu_flags"][int(cap["tu"][k]):int(cap["tu"][k]) + int(cnt[k][1])] for k in range(n)])
+    off = lambda col: np.concatenate([[0], np.cumsum(cnt[:, col])]).astype(np.uint64)  # noqa: E731
+    return dict(cus=cus, cu_offsets=off(0), tus=tus, tu_flags=tuf, tu_offsets=off(1), ctus=r["ctus"], ctu_offsets=cap["ctu"],
+                coeffs=r["coeffs"])
+
+
+@pytest.mark.gpu
+def test_gpu_encode_slices_reproduces_the_reference_payloads(engine):
+    """The writer direction through the C ABI: records (from cabac_decode_slices of the VTM payloads) in, bytes out -
+    identical with what the reference writer produced, contexts and bin counts included; likewise on generated
+    slices of every tool; bad records and a small command scratch are flagged per slice."""
+    lib = _host_lib()
+    vtm = [(t, s, sp, s["flags"] | SUB_TERMINATE | SUB_CTX_IN, np.stack([s["ctx_in"][:, 0], s["ctx_in"][:, 1]], 1))
+           for t, s, sp in _substreams() if not int(sp["tools"]) & SL_WPP]
+    gen = [(t, g, sp, g["flags"] | SUB_TERMINATE, None) for t, g, sp in _gen_items(lib, reps=2) if not int(sp["tools"]) & SL_WPP]
+    assert len(vtm) >= 6 and len(gen) >= 10
+    for items in (vtm, gen):
+        n = len(items)
+        params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+        ctx_in = np.zeros((n, 379), CTX_DT) if items[0][4] is not None else None
+        data, off = [], [0]
+        for k, (tag, s, sp, fl, cin) in enumerate(items):
+            params[k] = (s["qp"], s["init_id"], fl | SUB_ALIGN, 0)  # the writer side also writes the rbsp trailing bits
+            sps[k] = sp
+            if cin is not None:
+                ctx_in[k]["state0"], ctx_in[k]["state1"] = cin[:, 0], cin[:, 1]
+            data.append(s["payload"])
+            off.append(off[-1] + s["payload"].size)
+        d = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, ctx_in=ctx_in, want_ctx=True)
+        rec = _compact(d, n)
+        out_off = np.concatenate([[0], np.cumsum([p.size + 64 for p in data])]).astype(np.uint64)
+        before = engine.launch_count
+        w = engine.encode_slices(params, sps, rec["cus"], rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                                 rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off, ctx_in=ctx_in, want_ctx=True)
+        assert engine.launch_count >= before + 7
+        for k, (tag, s, sp, fl, cin) in enumerate(items):
+            assert int(w["status"][k]) == 0, f"{tag}: status {int(w['status'][k])}"
+            got = w["out"][int(out_off[k]):int(out_off[k]) + int(w["sizes"][k])]
+            assert got.tobytes() == s["payload"].tobytes(), f"{tag}: {got.size} bytes vs the writer's {s['payload'].size}"
+            assert int(w["num_bins"][k]) == int(d["num_bins"][k]), tag
+            assert w["ctx_out"][k].tobytes() == d["ctx_out"][k].tobytes(), tag
+    # errors, on the generated batch: a missing CU record, a TU record of another size, records of another slice
+    n = len(gen)
+    bad = {k: v.copy() if isinstance(v, np.ndarray) else v for k, v in rec.items()}
+    cu_off = bad["cu_offsets"].copy()
+    cu_off[1:] -= 1  # slice 0 loses its last CU; every later slice starts one record early
+    bad["tus"]["log2_w"][int(rec["tu_offsets"][2])] ^= 1
+    w = engine.encode_slices(params, sps, bad["cus"][:-1], cu_off, bad["tus"], bad["tu_flags"], bad["tu_offsets"], bad["ctus"],
+                             bad["ctu_offsets"], bad["coeffs"], out_off, raise_on_status=False)
+    assert int(w["status"][0]) & SS_BAD_DESC and int(w["status"][2]) & SS_BAD_DESC
+    assert all(int(v) != 0 for v in w["status"][:n - 1]), "shifted records must be noticed"
+    # command scratch too small for the batch: CABAC_SS_CAPACITY on the slices past the end, nothing encoded
+    w = engine.encode_slices(params, sps, rec["cus"], rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                             rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off, cmd_words=1000, raise_on_status=False)
+    assert int(w["status"][-1]) & SS_CAPACITY and not w["sizes"].any()
+    # WPP slices are refused in this direction
+    t, s, sp = next(x for x in _substreams() if int(x[2]["tools"]) & SL_WPP)
+    h = _host_decode(lib, s, sp)
+    one = np.array([(s["qp"], s["init_id"], s["flags"] | SUB_TERMINATE | SUB_ALIGN, 0)], PARAMS_DT)
+    nctu = len(h["ctus"])
+    w = engine.encode_slices(one, np.array([sp], SLICE_DT), h["cus"], [0, len(h["cus"])], h["tus"], h["tu_flags"], [0, len(h["tus"])],
+                             h["ctus"], [0, nctu], h["coeffs"], [0, s["payload"].size + 64], raise_on_status=False)
+    assert int(w["status"][0]) & SS_UNSUPPORTED

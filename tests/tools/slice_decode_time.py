@@ -20,7 +20,7 @@ for n in (64, 1024, 8192, 65536):
     dev=lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()
     d_data=dev(np.concatenate(data)); d_off=dev(np.asarray(off,np.uint64)); d_p=dev(params); d_sp=dev(sps); d_ci=dev(ctx_in)
     d_cu=dev(cap['cu']); d_tu=dev(cap['tu']); d_ctu=dev(cap['ctu']); d_co=dev(cap['coeff'])
-    cus=torch.zeros(int(cap['cu'][-1])*28,dtype=torch.uint8,device='cuda'); tus=torch.zeros(int(cap['tu'][-1])*16,dtype=torch.uint8,device='cuda')
+    cus=torch.zeros(int(cap['cu'][-1])*32,dtype=torch.uint8,device='cuda'); tus=torch.zeros(int(cap['tu'][-1])*16,dtype=torch.uint8,device='cuda')
     tuf=torch.zeros(int(cap['tu'][-1]),dtype=torch.uint8,device='cuda'); ctus=torch.zeros(int(cap['ctu'][-1])*32,dtype=torch.uint8,device='cuda')
     co=torch.zeros(int(cap['coeff'][-1]),dtype=torch.int32,device='cuda'); cnt=torch.zeros(n*3,dtype=torch.int32,device='cuda')
     nb=torch.zeros(n,dtype=torch.int32,device='cuda'); st=torch.zeros(n,dtype=torch.int32,device='cuda')

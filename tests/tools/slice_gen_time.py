@@ -39,7 +39,7 @@ cap = E.CabacEngine.slice_capacities(sps)
 dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()  # noqa: E731
 d = {k: dev(v) for k, v in (("in", np.concatenate(data)), ("off", np.asarray(off, np.uint64)), ("p", params), ("sp", sps),
                             ("cu", cap["cu"]), ("tu", cap["tu"]), ("ctu", cap["ctu"]), ("co", cap["coeff"]))}
-cus = torch.empty(int(cap["cu"][-1]) * 28, dtype=torch.uint8, device="cuda")
+cus = torch.empty(int(cap["cu"][-1]) * 32, dtype=torch.uint8, device="cuda")
 tus = torch.empty(int(cap["tu"][-1]) * 16, dtype=torch.uint8, device="cuda")
 tuf = torch.empty(int(cap["tu"][-1]), dtype=torch.uint8, device="cuda")
 ctus = torch.empty(int(cap["ctu"][-1]) * 32, dtype=torch.uint8, device="cuda")
