@@ -792,8 +792,39 @@ def leg_slice_decode(args, r):
                "tus": int(counts[:, 1].sum()), "coefficients_out": n_coeff, "decode_ms": t,
                "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9}
         row["hbm_frac"] = row["hbm_gbs"] / load_peaks()[0]
+        # the writer direction on the same records (cabac_encode_slices_dev): records -> the writer's bytes
+        from entropy_coding_b200.types import CU_DT, SUB_ALIGN, TU_DT
+        cus_h, tus_h = cus.cpu().numpy().view(CU_DT), tus.cpu().numpy().view(TU_DT)
+        tuf_h = tuf.cpu().numpy()
+        pick = lambda a, o, col: np.concatenate([a[int(o[j]):int(o[j]) + int(counts[j, col])] for j in range(n)])  # noqa: E731
+        exact = lambda col: np.concatenate([[0], np.cumsum(counts[:, col].astype(np.int64))]).astype(np.uint64)  # noqa: E731
+        wp = params.copy()
+        wp["flags"] |= SUB_ALIGN
+        out_off = np.concatenate([[0], np.cumsum([(p.size + 79) // 16 * 16 for p in data])]).astype(np.uint64)
+        words = int(bins * 1.5) + 64 * n
+        w = {k: dev_bytes(dev, v) for k, v in (("p", wp), ("cus", pick(cus_h, cap["cu"], 0)), ("cuo", exact(0)),
+                                               ("tus", pick(tus_h, cap["tu"], 1)), ("tuf", pick(tuf_h, cap["tu"], 1)),
+                                               ("tuo", exact(1)), ("oo", out_off))}
+        cmd = torch.empty(words, dtype=torch.int32, device=dev)
+        out = torch.zeros(int(out_off[-1]), dtype=torch.uint8, device=dev)
+        osz = torch.zeros(n, dtype=torch.int32, device=dev)
+        wst = torch.zeros(n, dtype=torch.int32, device=dev)
+        wnb = torch.zeros(n, dtype=torch.int32, device=dev)
+
+        def enc():
+            eng.encode_slices_dev(w["p"], d["sp"], n, w["cus"], w["cuo"], w["tus"], w["tuf"], w["tuo"], ctus, d["ctu"], co, cmd,
+                                  words, out, w["oo"], osz, wst, num_bins=wnb, ctx_in=d["ci"])
+
+        te = _time_passes(stream, enc, warm=2, reps=3)
+        assert int(wst.abs().max()) == 0, "slice encode status"
+        out_h, osz_h = out.cpu().numpy(), osz.cpu().numpy()
+        for j, k in enumerate(order):
+            a = int(out_off[j])
+            assert out_h[a:a + int(osz_h[j])].tobytes() == items[k][0]["payload"].tobytes(), f"slice copy {j}: bytes"
+        assert (wnb.cpu().numpy() == bins_h).all()
+        row["encode_ms"], row["encode_mbins_s"] = te, bins * r["world"] / te / 1e3
         rows.append(row)
-        del cus, tus, tuf, ctus, co, cnt, nb, st, d
+        del cus, tus, tuf, ctus, co, cnt, nb, st, d, w, cmd, out, osz, wst, wnb
         torch.cuda.empty_cache()
     rows_gen = _slice_decode_generated(r)
     cpu = None
@@ -943,12 +974,15 @@ def _cpu_slice_decode(items):
 def _slice_leg(rows, items):
     return {"config": "SURVEY section 8 f2 (the decode side of configs[0-1]): all-intra dual-tree slices decoded from the "
                       "bytes alone; VTM-produced fixture slices replicated on the device",
-            "per_gpu": True, "points": rows, "api": "cabac_decode_slices_dev (decode_slice_kernel: one warp per slice)",
+            "per_gpu": True, "points": rows,
+            "api": "cabac_decode_slices_dev (decode_slice_kernel: one warp per slice); encode_*: the writer direction, "
+                   "cabac_encode_slices_dev on the records the decode produced (emit_slice_kernel x 2 + the stream encoder)",
             "fixture_slices": len(items),
             "note": "64 slices per launch is the latency floor of one dependent chain per slice; 8192 fills the GPU. The "
                     "fixture slices are sparse (0.1-0.3 bins per coefficient position, large blocks with few levels), so "
                     "per-block work - zeroing and writing back whole blocks - weighs more here than in the headline batch",
-            "verified": "every copy: bin count, CU and TU counts and all coefficients == the reference writer's records"}
+            "verified": "every copy: bin count, CU and TU counts and all coefficients == the reference writer's records; "
+                        "encode: every copy's bytes == the VTM payload"}
 
 
 def run_e2e(args, r, i16=False):

@@ -558,6 +558,37 @@ struct SliceParser {
       if (tool(CABAC_SL_BDPCM) && w <= tsMax && h <= tsMax) {
         if (e.bin(SX_BDPCM_MODE + 0, cu.bdpcm != 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 1, cu.bdpcm == 2));
       }
+      if (E::kEncode && (cu.flags & CABAC_CU_FROM_DIR) && !cu.bdpcm) {
+        // writer direction from the decision itself: pu.intraDir[0] -> mpm flag / index / remainder, the way
+        // CABACWriter::intra_luma_pred_modes binarises it (cabac_writer.cpp:949-1060)
+        if (cu.flags & CABAC_CU_MIP) {
+          cu.pred_syntax = cu.intra_dir;
+        } else {
+          int mpm[6];
+          intraMpms(n, mpm);
+          int at = -1;
+          for (int i = 5; i >= 0; i--) at = mpm[i] == int(cu.intra_dir) ? i : at;
+          if (at >= 0) {
+            cu.flags |= CABAC_CU_MPM;
+            cu.pred_syntax = uint8_t(at);
+          } else {
+            cu.flags &= uint8_t(~CABAC_CU_MPM);
+            int mode = cu.intra_dir;
+            for (int i = 0; i < 6; i++) mode -= mpm[i] < int(cu.intra_dir);  // rank among the non-MPM modes
+            cu.pred_syntax = uint8_t(mode);
+            if (cu.mrl_idx || cu.intra_dir > 66) {  // a reference line other than 0 only goes with an MPM
+              status |= CABAC_SS_BAD_DESC;
+              e.abort();
+              return;
+            }
+          }
+          if (cu.mrl_idx && at == 0) {  // ... and not with PLANAR
+            status |= CABAC_SS_BAD_DESC;
+            e.abort();
+            return;
+          }
+        }
+      }
       if (!cu.bdpcm) {  // intra_luma_pred_modes, :1231-1316
         int mip = 0;
         if (tool(CABAC_SL_MIP)) {  // mip_flag :3381 + DeriveCtx::CtxMipFlag
@@ -626,6 +657,27 @@ struct SliceParser {
       const int cw = w >> 1, chh = h >> 1;
       if (tool(CABAC_SL_BDPCM) && cw <= tsMax && chh <= tsMax) {
         if (e.bin(SX_BDPCM_MODE + 2, cu.bdpcm != 0)) cu.bdpcm = uint8_t(1 + e.bin(SX_BDPCM_MODE + 3, cu.bdpcm == 2));
+      }
+      if (E::kEncode && (cu.flags & CABAC_CU_FROM_DIR) && !cu.bdpcm) {
+        // pu.intraDir[1] -> cclm flag / index or the candidate's position (cabac_writer.cpp:1167-1210)
+        cu.flags &= uint8_t(~CABAC_CU_CCLM);
+        if (cu.intra_dir >= 67 && cu.intra_dir <= 69) {
+          cu.flags |= CABAC_CU_CCLM;
+          cu.pred_syntax = uint8_t(cu.intra_dir - 67);
+        } else if (cu.intra_dir == 70) {
+          cu.pred_syntax = 0;
+        } else {
+          const int cand[4] = {0, 50, 18, 1};
+          const int lumaMode = e.lumaMap()[((((n.y + (h >> 1)) & 63) >> 2) << 4) + (((n.x + (w >> 1)) & 63) >> 2)];
+          int at = -1;
+          for (int i = 3; i >= 0; i--) at = (cand[i] == lumaMode ? 66 : cand[i]) == int(cu.intra_dir) ? i : at;
+          if (at < 0) {
+            status |= CABAC_SS_BAD_DESC;
+            e.abort();
+            return;
+          }
+          cu.pred_syntax = uint8_t(1 + at);
+        }
       }
       if (!cu.bdpcm) {  // intra_chroma_pred_mode :1353-1394
         bool done = false;

@@ -33,7 +33,7 @@ assert SLICE_DT.itemsize == 128 and CU_DT.itemsize == 32 and CTU_DT.itemsize == 
 SL_DUAL_TREE, SL_SAO_LUMA, SL_SAO_CHROMA, SL_ALF_Y, SL_ALF_CB, SL_ALF_CR, SL_CCALF_CB, SL_CCALF_CR = (1 << i for i in range(8))
 SL_MTS_INTRA, SL_LFNST, SL_ISP, SL_MIP, SL_MRL, SL_TS, SL_BDPCM, SL_JCCR = (1 << i for i in range(8, 16))
 SL_CCLM, SL_DQP, SL_CHROMA_QP_ADJ, SL_WPP, SL_IBC, SL_PLT, SL_ACT, SL_INTRA, SL_MTS = (1 << i for i in range(16, 25))
-CU_MIP, CU_MIP_TRANSPOSED, CU_MPM, CU_CCLM, CU_JCCR, CU_DQP = 1, 2, 4, 8, 16, 32
+CU_MIP, CU_MIP_TRANSPOSED, CU_MPM, CU_CCLM, CU_JCCR, CU_DQP, CU_FROM_DIR = 1, 2, 4, 8, 16, 32, 64
 SS_UNSUPPORTED, SS_CAPACITY = 256, 512
 
 # status codes

@@ -771,7 +771,12 @@ enum { /* cabac_cu_desc.flags */
   CABAC_CU_MPM = 4,            /* intra_luma_mpm_flag (inferred 1 with a reference line != 0)    */
   CABAC_CU_CCLM = 8,           /* chroma tree: cclm_mode_flag                                    */
   CABAC_CU_JCCR = 16,          /* some TU of the CU has tu.jointCbCr != 0                        */
-  CABAC_CU_DQP = 32            /* cu_qp_delta_abs was coded in this CU (value in qp_delta)       */
+  CABAC_CU_DQP = 32,           /* cu_qp_delta_abs was coded in this CU (value in qp_delta)       */
+  CABAC_CU_FROM_DIR = 64       /* cabac_encode_slices only: take the prediction mode from intra_dir
+                                  (pu.intraDir[chType]) and derive CABAC_CU_MPM / CABAC_CU_CCLM and
+                                  pred_syntax from it (the MPM list and the chroma candidates are
+                                  derived on the device as the writer derives them); without it
+                                  pred_syntax is coded as given                                   */
 };
 /* One record per CodingUnit in decoding order: what coding_unit() leaves in CodingUnit /
  * PredictionUnit (unit.hpp:283-341), the syntax element values and the intra direction derived

@@ -21,6 +21,7 @@
 #include "gpu_bin_encoder.hpp"
 #include "gpu_residual_reader.hpp"
 #include "gpu_slice_reader.hpp"
+#include "gpu_slice_writer.hpp"
 #include "ref_harness.hpp"
 
 using namespace ref_harness;
@@ -95,6 +96,13 @@ bool sameCtx(const Ctx &a, const Ctx &b) {
 // The whole-slice decode shim must compile against the unmodified reference headers (its parity run needs real
 // slice payloads: tests/test_syntax.py on the VTM fixtures); an empty batch is flushed here.
 static void sliceReaderCompiles(cabac_b200::Engine &eng, const Common::CodingStructure *cs) {
+  cabac_b200::GpuSliceWriter wr(eng);
+  if (cs && cs->pps) {  // never taken (see below): the CodingStructure-facing half of the writer shim, instantiated
+    wr.beginSlice(*cs, 32, 2, cabac_b200::sliceParams(*cs, 0, 0, 128, 128));
+    wr.addCtu(*cs, 0);
+    for (const auto &cu : cs->cus) wr.addCu(*cu, 0);
+    wr.flush();
+  }
   cabac_b200::GpuSliceReader rd(eng);
   if (cs && cs->pps) {  // the harness builds no PPS: never taken, only instantiated
     const cabac_slice_params sp = cabac_b200::sliceParams(*cs, 0, 0, 128, 128);
@@ -122,6 +130,10 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
     uint64_t sum;
   };
   std::vector<Want> want(n);
+  std::vector<std::vector<uint8_t>> payloads(n);
+  std::vector<std::vector<cabac_ctx_model>> ctxIns(n);
+  std::vector<cabac_substream_params> subParams(n);
+  std::vector<cabac_slice_params> sliceParams(n);
   cabac_b200::GpuSliceReader rd(eng);
   for (uint32_t i = 0; i < n; i++) {
     uint32_t words[32], hdr[8];
@@ -143,6 +155,10 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
     for (int k = 0; k < CABAC_NUM_CTX; k++) ctxIn[k] = cabac_ctx_model{ctx[2 * k], ctx[2 * k + 1]};
     rd.addRaw(payload.data(), payload.size(), p, sp, ctxIn.data());
     want[i] = Want{hdr[4], hdr[5], hdr[6], hdr[7], sum};
+    payloads[i] = payload;
+    ctxIns[i] = ctxIn;
+    subParams[i] = p;
+    sliceParams[i] = sp;
   }
   fclose(f);
   rd.flush();
@@ -164,7 +180,38 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
     }
   }
   printf("part S: GpuSliceReader decoded %u VTM slices from their bytes: %s\n", n, fails ? "MISMATCH" : "equal to the writer's records");
-  return fails;
+  // ... and back: GpuSliceWriter on the decisions those records hold (intra_dir instead of the MPM / candidate syntax
+  // values: CABAC_CU_FROM_DIR) must produce the payload bytes again through cabac_encode_slices with host pointers.
+  cabac_b200::GpuSliceWriter wr(eng);
+  std::vector<uint32_t> written;
+  for (uint32_t i = 0; i < n; i++) {
+    if (sliceParams[i].tools & CABAC_SL_WPP) continue;  // rows of a WPP slice are separate substreams on the writer side
+    const auto r = rd.result(i);
+    wr.beginSliceRaw(subParams[i], sliceParams[i], ctxIns[i].data());
+    for (size_t k = 0; k < r.nCtus; k++) wr.addCtuRaw(r.ctus[k]);
+    for (size_t k = 0; k < r.nCus; k++) {
+      cabac_cu_desc c = r.cus[k];
+      c.flags = uint8_t((c.flags & ~(CABAC_CU_MPM | CABAC_CU_CCLM)) | CABAC_CU_FROM_DIR);
+      c.pred_syntax = 0;
+      wr.addCuRaw(c);
+    }
+    for (size_t t = 0; t < r.nTus; t++) wr.addTuRaw(r.tus[t], rd.coeffs() + r.tus[t].coeff_offset, r.tuFlags[t]);
+    written.push_back(i);
+  }
+  wr.flush();
+  int wfails = 0;
+  for (size_t k = 0; k < written.size(); k++) {
+    const auto w = wr.result(k);
+    const auto &pl = payloads[written[k]];
+    if (w.status || w.nbytes != pl.size() || memcmp(w.bytes, pl.data(), pl.size()) || w.numBins != want[written[k]].nBins) {
+      printf("part S slice %u: written %zu bytes / %u bins, the reference's %zu / %u, status %u\n", written[k], w.nbytes,
+             w.numBins, pl.size(), want[written[k]].nBins, w.status);
+      wfails++;
+    }
+  }
+  printf("part S: GpuSliceWriter wrote %zu slices from their records: %s\n", written.size(),
+         wfails ? "MISMATCH" : "byte-identical with the VTM payloads");
+  return fails + wfails;
 }
 
 int main(int argc, char **argv) {

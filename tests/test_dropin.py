@@ -33,7 +33,8 @@ def test_reference_writer_on_gpu_shims(n_sub, seed):
 @pytest.mark.gpu
 def test_slice_reader_shim_on_vtm_slices(tmp_path):
     """GpuSliceReader (host/gpu_slice_reader.hpp, compiled against the unmodified reference headers) decodes the
-    VTM-produced fixture slices from their bytes through cabac_decode_slices with host pointers."""
+    VTM-produced fixture slices from their bytes through cabac_decode_slices with host pointers; GpuSliceWriter
+    (host/gpu_slice_writer.hpp) codes the records back into the same bytes through cabac_encode_slices."""
     if not os.path.exists(BIN):
         pytest.skip("oracle/_ref/dropin_test not built (needs the reference tree at build time)")
     import sys
@@ -56,3 +57,5 @@ def test_slice_reader_shim_on_vtm_slices(tmp_path):
             f.write(np.ascontiguousarray(s["payload"]).tobytes())
     r = subprocess.run([BIN, "--slices", str(path)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "DROPIN OK" in r.stdout, r.stdout + r.stderr
+    # and GpuSliceWriter (host/gpu_slice_writer.hpp) turns the records back into the payload bytes
+    assert "byte-identical with the VTM payloads" in r.stdout, r.stdout

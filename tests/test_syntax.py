@@ -28,7 +28,7 @@ ROOT = os.path.join(HERE, "..")
 sys.path.insert(0, os.path.join(HERE, "golden"))
 from vtm_streams import load_fixture  # noqa: E402
 
-from entropy_coding_b200.types import (CTU_DT, CTX_DT, CU_DT, CU_MIP, CU_MIP_TRANSPOSED, PARAMS_DT, SL_WPP, SLICE_DT,
+from entropy_coding_b200.types import (CTU_DT, CTX_DT, CU_CCLM, CU_DT, CU_FROM_DIR, CU_MIP, CU_MIP_TRANSPOSED, CU_MPM, PARAMS_DT, SL_WPP, SLICE_DT,
                                        SS_BAD_DESC, SS_CAPACITY, SS_UNSUPPORTED, SUB_ALIGN, SUB_CTX_IN, SUB_TERMINATE, TU_DT)
 
 FIXTURES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(HERE, "golden", "vtm_*.npz")))
@@ -494,10 +494,20 @@ def test_gpu_decode_slices_on_generated_streams(engine):
 
 
 # ---- writer direction: records -> the writer's call sequence (syn_emit_slice on the host, cabac_encode_slices on the GPU)
-def _host_emit(lib, sp, r):
+def _from_dir(cus):
+    """The records an encoder has: decisions (intra_dir), no syntax element values for the prediction mode."""
+    cus = cus.copy()
+    cus["flags"] = (cus["flags"] & ~np.uint8(CU_MPM | CU_CCLM)) | np.uint8(CU_FROM_DIR)
+    cus["pred_syntax"] = 0xAA
+    return cus
+
+
+def _host_emit(lib, sp, r, from_dir=False):
     lib.syn_emit_slice.restype = C.c_long
     cmds, st = np.zeros(1 << 20, np.uint32), np.zeros(1, np.uint32)
     cus, tus, tuf, ctus = (np.ascontiguousarray(r[k]) for k in ("cus", "tus", "tu_flags", "ctus"))
+    if from_dir:
+        cus = _from_dir(cus)
     n = lib.syn_emit_slice(_p(np.array([sp], SLICE_DT)), _p(cus), C.c_long(len(cus)), _p(tus), _p(tuf), C.c_long(len(tus)),
                            _p(ctus), C.c_long(len(ctus)), _p(cmds), C.c_long(cmds.size), _p(st))
     return cmds[:n], int(st[0])
@@ -519,6 +529,9 @@ def test_host_writer_direction_reproduces_the_writers_calls():
         got, want = _flat(cmds), _flat(s["cmds"])
         bad = next((k for k in range(min(len(got), len(want))) if got[k] != want[k]), None)
         assert bad is None and len(got) == len(want), f"{tag}: call {bad}: emitted {got[bad - 2:bad + 3] if bad is not None else len(got)} writer {want[bad - 2:bad + 3] if bad is not None else len(want)}"
+        # and from the decisions alone (CABAC_CU_FROM_DIR: intra_dir in, MPM index / remainder / chroma candidate derived)
+        cmds2, st2 = _host_emit(lib, sp, r, from_dir=True)
+        assert st2 == 0 and np.array_equal(cmds2, cmds), f"{tag}: from intra_dir"
         n += 1
     assert n >= 6
     # and on generated slices (all tools): emit(decode(x)) is the generating walk's sequence again
@@ -529,6 +542,8 @@ def test_host_writer_direction_reproduces_the_writers_calls():
         r["ctus"] = r["ctus"][:len(g["ctus"])]
         cmds, st = _host_emit(lib, sp, r)
         assert st == 0 and _flat(cmds) == _flat(r["trace"]), tag
+        cmds2, st2 = _host_emit(lib, sp, r, from_dir=True)
+        assert st2 == 0 and np.array_equal(cmds2, cmds), f"{tag}: from intra_dir"
 
 
 def _compact(r, n):
@@ -577,6 +592,13 @@ def test_gpu_encode_slices_reproduces_the_reference_payloads(engine):
             assert got.tobytes() == s["payload"].tobytes(), f"{tag}: {got.size} bytes vs the writer's {s['payload'].size}"
             assert int(w["num_bins"][k]) == int(d["num_bins"][k]), tag
             assert w["ctx_out"][k].tobytes() == d["ctx_out"][k].tobytes(), tag
+    # the generated batch once more from the decisions alone (CABAC_CU_FROM_DIR)
+    w2 = engine.encode_slices(params, sps, _from_dir(rec["cus"]), rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                              rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off)
+    assert (w2["sizes"] == w["sizes"]).all()
+    for k, (tag, s, sp, fl, cin) in enumerate(items):
+        a = int(out_off[k])
+        assert w2["out"][a:a + int(w2["sizes"][k])].tobytes() == s["payload"].tobytes(), f"{tag}: from intra_dir"
     # errors, on the generated batch: a missing CU record, a TU record of another size, records of another slice
     n = len(gen)
     bad = {k: v.copy() if isinstance(v, np.ndarray) else v for k, v in rec.items()}
