@@ -76,6 +76,8 @@ _SIGS = {
     "cabac_decode_slices_dev": (C.c_int, [_P, _P, _P, _P, _P, _SZ] + [_P] * 15),
     "cabac_encode_slices": (C.c_int, [_P, _P, _P, _SZ] + [_P] * 8 + [_SZ, _P, _SZ] + [_P] * 6),
     "cabac_encode_slices_dev": (C.c_int, [_P, _P, _P, _SZ] + [_P] * 10 + [_SZ] + [_P] * 6),
+    "cabac_encode_slices_wpp": (C.c_int, [_P, _P, _P, _SZ] + [_P] * 8 + [_SZ, _P, _SZ, _P, _SZ] + [_P] * 6),
+    "cabac_encode_slices_wpp_dev": (C.c_int, [_P, _P, _P, _SZ] + [_P] * 10 + [_SZ, _P, _SZ] + [_P] * 6),
     "cabac_pack": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _SZ, _P]),
     "cabac_pack_dev": (C.c_int, [_P, _P, _P, _P, _SZ, _P, _P]),
 }

@@ -48,8 +48,8 @@ struct cabac_handle {
   cudaEvent_t evCopy[kMaxChunks] = {}, evDone[kMaxChunks] = {}, evJoin = nullptr;
   void *epbScratch = nullptr;  // tile counts / bases of the emulation-prevention pass, grow-only
   size_t epbTiles = 0;
-  void *emitScratch = nullptr;  // cabac_encode_slices_dev: per-slice word counts, statuses, command offsets; grow-only
-  size_t emitSubs = 0;
+  void *emitScratch = nullptr;  // cabac_encode_slices_dev: per-slice word counts / statuses, row-level arrays; grow-only
+  size_t emitBytes = 0;
   bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
   cudaEvent_t evT0 = nullptr;
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
@@ -154,10 +154,7 @@ cudaError_t schedFor(cabac_handle *h, size_t n, cabac::Sched &sc) {
     const cabac_wpp_sync *sync = h->wppNext;
     h->wppNext = nullptr;
     if (n > h->wppSubs) {
-      if (h->pinDev) cudaFree(h->pinDev);
-  cabac::freeSlicedWork(h->sliced);
-  if (h->threadCtx) cudaFree(h->threadCtx);
-  if (h->wppScratch) cudaFree(h->wppScratch);
+      if (h->wppScratch) cudaFree(h->wppScratch);
       h->wppScratch = nullptr;
       h->wppSubs = 0;
       const size_t cap2 = n + (n >> 2) + 64;
@@ -654,50 +651,94 @@ int cabac_decode_residual_dev(cabac_handle *h, const uint8_t *in, const uint64_t
   return CABAC_OK;
 }
 
-// Writer direction of the slice syntax (cabac_slice.cuh K10 + the stream encoder).
+// Writer direction of the slice syntax (cabac_slice.cuh K10 + the stream encoder).  Everything below the walk is
+// row-level: one row substream per slice, or one per CTU row of a WPP slice (row_offsets given) with the hand-over
+// resolved by the stream encoder's wavefront mode.  out_offsets / out_sizes / num_bins / ctx_out / status are per ROW.
+static int encodeSliceRows(cabac_handle *h, const char *what, const cabac_substream_params *params,
+                           const cabac_slice_params *slice_params, size_t n_sub, const cabac_cu_desc *cus,
+                           const uint64_t *cu_offsets, const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                           const uint64_t *tu_offsets, const cabac_ctu_desc *ctus, const uint64_t *ctu_offsets,
+                           const int32_t *coeffs, const cabac_ctx_model *ctx_in, uint32_t *cmd_scratch,
+                           size_t cmd_scratch_words, const uint64_t *row_offsets, size_t n_rows, uint8_t *out,
+                           const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins, cabac_ctx_model *ctx_out,
+                           uint32_t *status) {
+  if (!h || (n_sub && (!params || !slice_params || !cus || !cu_offsets || !tus || !tu_flags || !tu_offsets || !ctus ||
+                       !ctu_offsets || !coeffs || !cmd_scratch || !out || !out_offsets || !out_sizes || !status)) ||
+      n_rows < n_sub)
+    return badArg(h, what);
+  if (!n_sub) return CABAC_OK;
+  DeviceGuard g(h->device);
+  // scratch: u64 cmdOffsets[nSub+1], rowCmdOff[nRows+1], rowTuOff[nRows+1] | sync[nRows] (16 B) |
+  //          u32 counts[nSub], emitStatus[nSub], rowSlice[nRows], rowParams[nRows] | ctx rows[nRows][379] (if ctx_in)
+  const size_t need = (n_sub + 1 + 2 * (n_rows + 1)) * 8 + n_rows * sizeof(cabac_wpp_sync) + (2 * n_sub + 2 * n_rows) * 4 +
+                      (ctx_in ? n_rows * CABAC_NUM_CTX * sizeof(cabac_ctx_model) : 0) + 64;
+  if (need > h->emitBytes) {
+    CK(cudaStreamSynchronize(h->stream), "sync");
+    if (h->emitScratch) cudaFree(h->emitScratch);
+    h->emitScratch = nullptr;
+    h->emitBytes = 0;
+    CK(cudaMalloc(&h->emitScratch, need + (need >> 2)), "slice emit scratch");
+    h->emitBytes = need + (need >> 2);
+  }
+  static_assert(sizeof(cabac_substream_params) == 4, "row parameter copies are packed as words");
+  uint64_t *cmdOffsets = static_cast<uint64_t *>(h->emitScratch);
+  uint64_t *rowCmdOff = cmdOffsets + n_sub + 1, *rowTuOff = rowCmdOff + n_rows + 1;
+  cabac_wpp_sync *rowSync = reinterpret_cast<cabac_wpp_sync *>(rowTuOff + n_rows + 1);
+  uint32_t *counts = reinterpret_cast<uint32_t *>(rowSync + n_rows), *emitStatus = counts + n_sub;
+  uint32_t *rowSlice = emitStatus + n_sub;
+  cabac_substream_params *rowParams = reinterpret_cast<cabac_substream_params *>(rowSlice + n_rows);
+  cabac_ctx_model *rowCtxIn = ctx_in ? reinterpret_cast<cabac_ctx_model *>(rowParams + n_rows) : nullptr;
+  CK(cabac::launchEmitSlices(h->stream, h->device, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
+                             ctus, ctu_offsets, ctx_in, cmd_scratch, cmd_scratch_words, counts, emitStatus, cmdOffsets,
+                             row_offsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn),
+     "emit_slice kernels");
+  h->launches += 3;
+  // a slice whose commands did not fit (CABAC_SS_CAPACITY) has offsets past the scratch: the encoder must not read
+  // them, so such a call stops here with every slice's status written
+  CK(cudaMemsetAsync(out_sizes, 0, n_rows * 4, h->stream), "memset");
+  uint64_t total = 0;
+  CK(cudaMemcpyAsync(&total, cmdOffsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  if (total > cmd_scratch_words) {
+    CK(cudaMemsetAsync(status, 0, n_rows * 4, h->stream), "memset");
+    CK(cabac::launchOrStatus(h->stream, status, emitStatus, rowSlice, n_rows), "or_status_kernel");
+    h->err = std::string(what) + ": cmd_scratch too small (status[] says which slices: CABAC_SS_CAPACITY)";
+    return CABAC_ERR_SUBSTREAM;
+  }
+  const int rc = row_offsets
+                     ? cabac_encode_stream_wpp_dev(h, cmd_scratch, rowCmdOff, tus, rowTuOff, rowParams, rowSync, n_rows, coeffs,
+                                                   rowCtxIn, out, out_offsets, out_sizes, num_bins, nullptr, ctx_out, status)
+                     : cabac_encode_stream_dev(h, cmd_scratch, rowCmdOff, tus, rowTuOff, rowParams, n_rows, coeffs, rowCtxIn,
+                                               out, out_offsets, out_sizes, num_bins, nullptr, ctx_out, status);
+  if (rc) return rc;
+  CK(cabac::launchOrStatus(h->stream, status, emitStatus, rowSlice, n_rows), "or_status_kernel");
+  h->launches += 1;
+  return CABAC_OK;
+}
+
 int cabac_encode_slices_dev(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
                             size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
                             const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
                             const uint64_t *ctu_offsets, const int32_t *coeffs, const cabac_ctx_model *ctx_in,
                             uint32_t *cmd_scratch, size_t cmd_scratch_words, uint8_t *out, const uint64_t *out_offsets,
                             uint32_t *out_sizes, uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
-  if (!h || (n_sub && (!params || !slice_params || !cus || !cu_offsets || !tus || !tu_flags || !tu_offsets || !ctus ||
-                       !ctu_offsets || !coeffs || !cmd_scratch || !out || !out_offsets || !out_sizes || !status)))
-    return badArg(h, "cabac_encode_slices_dev");
-  if (!n_sub) return CABAC_OK;
-  DeviceGuard g(h->device);
-  if (n_sub > h->emitSubs) {
-    if (h->emitScratch) cudaFree(h->emitScratch);
-    h->emitScratch = nullptr;
-    h->emitSubs = 0;
-    const size_t cap = n_sub + (n_sub >> 2) + 64;
-    CK(cudaMalloc(&h->emitScratch, (cap + 1) * 8 + cap * 8), "slice emit scratch");
-    h->emitSubs = cap;
-  }
-  uint64_t *cmdOffsets = static_cast<uint64_t *>(h->emitScratch);
-  uint32_t *counts = reinterpret_cast<uint32_t *>(cmdOffsets + h->emitSubs + 1);
-  uint32_t *emitStatus = counts + h->emitSubs;
-  CK(cabac::launchEmitSlices(h->stream, h->device, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus,
-                             ctu_offsets, cmd_scratch, cmd_scratch_words, counts, emitStatus, cmdOffsets),
-     "emit_slice kernels");
-  h->launches += 3;
-  // a slice whose commands did not fit (CABAC_SS_CAPACITY) has offsets past the scratch: the encoder must not read
-  // them, so such a call stops here with every slice's status written
-  CK(cudaMemsetAsync(out_sizes, 0, n_sub * 4, h->stream), "memset");
-  uint64_t total = 0;
-  CK(cudaMemcpyAsync(&total, cmdOffsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
-  CK(cudaStreamSynchronize(h->stream), "sync");
-  if (total > cmd_scratch_words) {
-    CK(cudaMemcpyAsync(status, emitStatus, n_sub * 4, cudaMemcpyDeviceToDevice, h->stream), "copy");
-    h->err = "cabac_encode_slices_dev: cmd_scratch too small (status[] says which slices: CABAC_SS_CAPACITY)";
-    return CABAC_ERR_SUBSTREAM;
-  }
-  if (int rc = cabac_encode_stream_dev(h, cmd_scratch, cmdOffsets, tus, tu_offsets, params, n_sub, coeffs, ctx_in, out,
-                                       out_offsets, out_sizes, num_bins, nullptr, ctx_out, status))
-    return rc;
-  CK(cabac::launchOrStatus(h->stream, status, emitStatus, n_sub), "or_status_kernel");
-  h->launches += 1;
-  return CABAC_OK;
+  return encodeSliceRows(h, "cabac_encode_slices_dev", params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
+                         ctus, ctu_offsets, coeffs, ctx_in, cmd_scratch, cmd_scratch_words, nullptr, n_sub, out, out_offsets,
+                         out_sizes, num_bins, ctx_out, status);
+}
+
+int cabac_encode_slices_wpp_dev(cabac_handle *h, const cabac_substream_params *params,
+                                const cabac_slice_params *slice_params, size_t n_sub, const cabac_cu_desc *cus,
+                                const uint64_t *cu_offsets, const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                                const uint64_t *tu_offsets, const cabac_ctu_desc *ctus, const uint64_t *ctu_offsets,
+                                const int32_t *coeffs, const cabac_ctx_model *ctx_in, uint32_t *cmd_scratch,
+                                size_t cmd_scratch_words, const uint64_t *row_offsets, size_t n_rows, uint8_t *out,
+                                const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                                cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (n_sub && !row_offsets) return badArg(h, "cabac_encode_slices_wpp_dev: row_offsets");
+  return encodeSliceRows(h, "cabac_encode_slices_wpp_dev", params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags,
+                         tu_offsets, ctus, ctu_offsets, coeffs, ctx_in, cmd_scratch, cmd_scratch_words, row_offsets, n_rows,
+                         out, out_offsets, out_sizes, num_bins, ctx_out, status);
 }
 
 int cabac_decode_slices_dev(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,
@@ -824,8 +865,6 @@ int cabac_pin_descriptors(cabac_handle *h, const cabac_tu_desc *tus, const uint6
   if (need > h->pinDevBytes) {
     CK(cudaStreamSynchronize(h->stream), "sync");
     if (h->pinDev) cudaFree(h->pinDev);
-  cabac::freeSlicedWork(h->sliced);
-  if (h->threadCtx) cudaFree(h->threadCtx);
     h->pinDev = nullptr;
     h->pinDevBytes = 0;
     CK(cudaMalloc(&h->pinDev, need + (need >> 3)), "descriptor copy");
@@ -975,25 +1014,27 @@ int cabac_decode_bins(cabac_handle *h, const uint8_t *in, const uint64_t *in_off
   return anySubstreamFailed(hst, n_sub);
 }
 
-int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
-                        size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
-                        const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
-                        const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in,
-                        size_t cmd_words, uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes,
-                        uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
+static int encodeSliceRowsHost(cabac_handle *h, const char *what, const cabac_substream_params *params,
+                               const cabac_slice_params *slice_params, size_t n_sub, const cabac_cu_desc *cus,
+                               const uint64_t *cu_offsets, const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                               const uint64_t *tu_offsets, const cabac_ctu_desc *ctus, const uint64_t *ctu_offsets,
+                               const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in, size_t cmd_words,
+                               const uint64_t *row_offsets, size_t n_rows, uint8_t *out, const uint64_t *out_offsets,
+                               uint32_t *out_sizes, uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
   if (!h || (n_sub && (!params || !slice_params || !cus || !cu_offsets || !tus || !tu_flags || !tu_offsets || !ctus ||
                        !ctu_offsets || !coeffs || !out || !out_offsets || !out_sizes)))
-    return badArg(h, "cabac_encode_slices");
+    return badArg(h, what);
   if (!n_sub) return CABAC_OK;
+  if (row_offsets && (row_offsets[0] != 0 || row_offsets[n_sub] != n_rows)) return badArg(h, what);
   DeviceGuard g(h->device);
-  const size_t nCu = cu_offsets[n_sub], nTu = tu_offsets[n_sub], nCtu = ctu_offsets[n_sub], outCap = out_offsets[n_sub];
+  const size_t nCu = cu_offsets[n_sub], nTu = tu_offsets[n_sub], nCtu = ctu_offsets[n_sub], outCap = out_offsets[n_rows];
   cabac_substream_params *dP;
   cabac_slice_params *dSp;
   cabac_cu_desc *dCus;
   cabac_tu_desc *dTus;
   cabac_ctu_desc *dCtus;
   uint8_t *dTuFlags, *dOut;
-  uint64_t *dCuOff, *dTuOff, *dCtuOff, *dOutOff;
+  uint64_t *dCuOff, *dTuOff, *dCtuOff, *dOutOff, *dRowOff;
   int32_t *dCoeffs;
   cabac_ctx_model *dCin, *dCout;
   uint32_t *dCmds, *dSizes, *dBins, *dStatus;
@@ -1007,15 +1048,16 @@ int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params, c
   a.want((void **)&dCuOff, (n_sub + 1) * 8);
   a.want((void **)&dTuOff, (n_sub + 1) * 8);
   a.want((void **)&dCtuOff, (n_sub + 1) * 8);
-  a.want((void **)&dOutOff, (n_sub + 1) * 8);
+  a.want((void **)&dRowOff, row_offsets ? (n_sub + 1) * 8 : 0);
+  a.want((void **)&dOutOff, (n_rows + 1) * 8);
   a.want((void **)&dCoeffs, n_coeffs * 4);
   a.want((void **)&dCin, ctx_in ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_in) : 0);
-  a.want((void **)&dCout, ctx_out ? n_sub * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
+  a.want((void **)&dCout, ctx_out ? n_rows * CABAC_NUM_CTX * sizeof(*ctx_out) : 0);
   a.want((void **)&dCmds, cmd_words * 4);
   a.want((void **)&dOut, outCap);
-  a.want((void **)&dSizes, n_sub * 4);
-  a.want((void **)&dBins, n_sub * 4);
-  a.want((void **)&dStatus, n_sub * 4);
+  a.want((void **)&dSizes, n_rows * 4);
+  a.want((void **)&dBins, n_rows * 4);
+  a.want((void **)&dStatus, n_rows * 4);
   CK(a.commit(), "scratch alloc");
   H2D(dP, params, n_sub * sizeof(*params));
   H2D(dSp, slice_params, n_sub * sizeof(*slice_params));
@@ -1026,24 +1068,49 @@ int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params, c
   H2D(dCuOff, cu_offsets, (n_sub + 1) * 8);
   H2D(dTuOff, tu_offsets, (n_sub + 1) * 8);
   H2D(dCtuOff, ctu_offsets, (n_sub + 1) * 8);
-  H2D(dOutOff, out_offsets, (n_sub + 1) * 8);
+  H2D(dRowOff, row_offsets, (n_sub + 1) * 8);
+  H2D(dOutOff, out_offsets, (n_rows + 1) * 8);
   H2D(dCoeffs, coeffs, n_coeffs * 4);
   H2D(dCin, ctx_in, n_sub * CABAC_NUM_CTX * sizeof(*ctx_in));
-  const int rc = cabac_encode_slices_dev(h, dP, dSp, n_sub, dCus, dCuOff, dTus, dTuFlags, dTuOff, dCtus, dCtuOff, dCoeffs,
-                                         ctx_in ? dCin : nullptr, dCmds, cmd_words, dOut, dOutOff, dSizes, dBins,
-                                         ctx_out ? dCout : nullptr, dStatus);
-  std::vector<uint32_t> st(status ? 0 : n_sub);
+  const int rc = encodeSliceRows(h, what, dP, dSp, n_sub, dCus, dCuOff, dTus, dTuFlags, dTuOff, dCtus, dCtuOff, dCoeffs,
+                                 ctx_in ? dCin : nullptr, dCmds, cmd_words, row_offsets ? dRowOff : nullptr, n_rows, dOut,
+                                 dOutOff, dSizes, dBins, ctx_out ? dCout : nullptr, dStatus);
+  std::vector<uint32_t> st(status ? 0 : n_rows);
   uint32_t *hst = status ? status : st.data();
   if (rc && rc != CABAC_ERR_SUBSTREAM) return rc;
-  D2H(hst, dStatus, n_sub * 4);
+  D2H(hst, dStatus, n_rows * 4);
+  D2H(out_sizes, dSizes, n_rows * 4);
   if (!rc) {
     D2H(out, dOut, outCap);
-    D2H(out_sizes, dSizes, n_sub * 4);
-    D2H(num_bins, dBins, n_sub * 4);
-    D2H(ctx_out, dCout, n_sub * CABAC_NUM_CTX * sizeof(*ctx_out));
+    D2H(num_bins, dBins, n_rows * 4);
+    D2H(ctx_out, dCout, n_rows * CABAC_NUM_CTX * sizeof(*ctx_out));
   }
   CK(cudaStreamSynchronize(h->stream), "sync");
-  return rc ? rc : anySubstreamFailed(hst, n_sub);
+  return rc ? rc : anySubstreamFailed(hst, n_rows);
+}
+
+int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
+                        size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
+                        const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                        const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs, const cabac_ctx_model *ctx_in,
+                        size_t cmd_words, uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes,
+                        uint32_t *num_bins, cabac_ctx_model *ctx_out, uint32_t *status) {
+  return encodeSliceRowsHost(h, "cabac_encode_slices", params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
+                             ctus, ctu_offsets, coeffs, n_coeffs, ctx_in, cmd_words, nullptr, n_sub, out, out_offsets,
+                             out_sizes, num_bins, ctx_out, status);
+}
+
+int cabac_encode_slices_wpp(cabac_handle *h, const cabac_substream_params *params, const cabac_slice_params *slice_params,
+                            size_t n_sub, const cabac_cu_desc *cus, const uint64_t *cu_offsets, const cabac_tu_desc *tus,
+                            const uint8_t *tu_flags, const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                            const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs,
+                            const cabac_ctx_model *ctx_in, size_t cmd_words, const uint64_t *row_offsets, size_t n_rows,
+                            uint8_t *out, const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                            cabac_ctx_model *ctx_out, uint32_t *status) {
+  if (n_sub && !row_offsets) return badArg(h, "cabac_encode_slices_wpp: row_offsets");
+  return encodeSliceRowsHost(h, "cabac_encode_slices_wpp", params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags,
+                             tu_offsets, ctus, ctu_offsets, coeffs, n_coeffs, ctx_in, cmd_words, row_offsets, n_rows, out,
+                             out_offsets, out_sizes, num_bins, ctx_out, status);
 }
 
 int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_offsets,

@@ -55,12 +55,15 @@ cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, cons
                                cabac_tu_desc *tus, uint8_t *tuFlags, cabac_ctu_desc *ctus, int32_t *coeffs,
                                uint32_t *counts, uint32_t *numBins, uint32_t *bitsRead, cabac_ctx_model *ctxOut,
                                uint32_t *status);
-cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_slice_params *sliceParams, size_t nSub,
-                             const cabac_cu_desc *cus, const uint64_t *cuOffsets, const cabac_tu_desc *tus,
-                             const uint8_t *tuFlags, const uint64_t *tuOffsets, const cabac_ctu_desc *ctus,
-                             const uint64_t *ctuOffsets, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
-                             uint32_t *emitStatus, uint64_t *cmdOffsets);
-cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, size_t n);
+cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_substream_params *params,
+                             const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
+                             const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
+                             const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,
+                             const cabac_ctx_model *ctxIn, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
+                             uint32_t *emitStatus, uint64_t *cmdOffsets, const uint64_t *rowOffsets, uint64_t *rowCmdOff,
+                             uint64_t *rowTuOff, cabac_wpp_sync *rowSync, cabac_substream_params *rowParams,
+                             uint32_t *rowSlice, cabac_ctx_model *rowCtxIn);
+cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, const uint32_t *rowSlice, size_t nRows);
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,
                                 const uint64_t *rawOffsets, const cabac_substream_params *params = nullptr,

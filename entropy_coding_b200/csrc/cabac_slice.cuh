@@ -228,6 +228,7 @@ struct SliceEngine {
     __syncwarp();
   }
   // WPP row hand-over (see SliceParser::run)
+  __device__ __forceinline__ bool rows() const { return false; }
   __device__ __forceinline__ void saveRowContexts() {
     const int lane = laneId();
     (void)lane;
@@ -353,6 +354,17 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
 // stream encoder (cabac_encode_stream: all encoder kernels) then codes.  No arithmetic coding here: one warp per
 // slice, two passes (count, then write at the scanned offsets).
 // ---------------------------------------------------------------------------
+// Row substreams of the slice being written (WPP: one per CTU row; otherwise the slice itself): what the stream
+// encoder's wavefront mode takes per substream.  All nullptr in the count pass.
+struct SliceRowOut {
+  uint64_t *cmdOff;      // [row]: first command word (absolute in the command buffer)
+  uint64_t *tuOff;       // [row]: first TU (absolute in tus)
+  cabac_wpp_sync *sync;  // [row]: predecessor and the hand-over point (after the row's first CTU)
+  uint32_t base, count;  // the slice's rows are [base, base + count)
+  uint64_t cmdBase, tuBase;
+  bool allow;            // the caller described the rows (cabac_encode_slices_wpp): WPP slices can be written
+};
+
 struct SliceEmitEngine {
   static constexpr bool kEncode = true;
   SliceLines &ln;
@@ -362,13 +374,15 @@ struct SliceEmitEngine {
   const cabac_ctu_desc *ctusIn;
   uint32_t nCuIn, nTuIn, nCtuIn;
   uint32_t *cmds;  // nullptr: count only
-  uint32_t n = 0;
+  SliceRowOut ro;
+  uint32_t n = 0, row = 0, rowStartN = 0, rowStartTu = 0, tuSeen = 0;
   bool dead = false, bad = false;
 
   __device__ __forceinline__ SliceEmitEngine(SliceLines &l, const cabac_cu_desc *c, uint32_t nc, const cabac_tu_desc *t,
                                              const uint8_t *tf, uint32_t nt, const cabac_ctu_desc *ct, uint32_t nct,
-                                             uint32_t *out)
-      : ln(l), cusIn(c), tusIn(t), tuFlagsIn(tf), ctusIn(ct), nCuIn(nc), nTuIn(nt), nCtuIn(nct), cmds(out) {}
+                                             uint32_t *out, const SliceRowOut &r)
+      : ln(l), cusIn(c), tusIn(t), tuFlagsIn(tf), ctusIn(ct), nCuIn(nc), nTuIn(nt), nCtuIn(nct), cmds(out), ro(r) {}
+  __device__ __forceinline__ bool rows() const { return ro.allow; }
   __device__ __forceinline__ static int laneId() { return int(threadIdx.x & 31u); }
   __device__ __forceinline__ void push(uint32_t w) {
     if (cmds && laneId() == 0) cmds[n] = w;
@@ -417,6 +431,7 @@ struct SliceEmitEngine {
       return 0;
     }
     push(CABAC_MK_TU());
+    tuSeen = idx + 1;
     return tuFlagsIn[idx];
   }
   __device__ __forceinline__ uint16_t *aboveLine(int ch) { return ln.above[ch]; }
@@ -444,22 +459,54 @@ struct SliceEmitEngine {
   }
   __device__ __forceinline__ void putCu(uint32_t, const cabac_cu_desc &) {}
   __device__ __forceinline__ void putCtu(uint32_t, const cabac_ctu_desc &) {}
-  __device__ __forceinline__ void saveRowContexts() {}
-  __device__ __forceinline__ void nextRow() {}
+  // WPP: the contexts are handed to the next row after the row's first CTU (EncSlice.cpp:2085-2089) ...
+  __device__ __forceinline__ void saveRowContexts() {
+    if (ro.sync && laneId() == 0 && row < ro.count) {
+      ro.sync[ro.base + row].sync_cmds = n - rowStartN;
+      ro.sync[ro.base + row].sync_tus = tuSeen - rowStartTu;
+    }
+  }
+  // ... and the row ends with end_of_subset_one_bit, finish() and the alignment: the stream encoder's
+  // (CABAC_SUB_TERMINATE | CABAC_SUB_ALIGN on every row), so the terminating bin just pushed is taken back
+  __device__ __forceinline__ void nextRow() {
+    n--;
+    row++;
+    rowStartN = n;
+    rowStartTu = tuSeen;
+    if (row >= ro.count) {
+      bad = dead = true;
+      return;
+    }
+    if (ro.cmdOff && laneId() == 0) {
+      ro.cmdOff[ro.base + row] = ro.cmdBase + n;
+      ro.tuOff[ro.base + row] = ro.tuBase + tuSeen;
+    }
+  }
   __device__ __forceinline__ void abort() { dead = true; }
   __device__ __forceinline__ bool aborted() const { return dead; }
 };
 
 constexpr int EMIT_WARPS_PER_BLOCK = 4;
 
-// cmdOffsets == nullptr: count pass (counts[sub] = words); otherwise write pass into cmds at cmdOffsets[sub].
+// cmdOffsets == nullptr: count pass (counts[sub] = words); otherwise write pass into cmds at cmdOffsets[sub], which
+// also fills the row-level arrays the stream encoder takes (one row per slice; one per CTU row of a WPP slice).
+struct EmitRowArrays {
+  const uint64_t *rowOffsets;  // [nSub + 1] or nullptr: every slice is one row (WPP slices refused)
+  uint64_t *cmdOff, *tuOff;    // [nRows + 1]
+  cabac_wpp_sync *sync;        // [nRows]
+  cabac_substream_params *params;
+  uint32_t *slice;             // [nRows]: the slice a row belongs to
+  cabac_ctx_model *ctxIn;      // [nRows][379] or nullptr
+};
+
 __global__ void __launch_bounds__(EMIT_WARPS_PER_BLOCK * 32)
-emit_slice_kernel(const cabac_slice_params *__restrict__ sliceParams, size_t nSub, const cabac_cu_desc *__restrict__ cus,
-                  const uint64_t *__restrict__ cuOffsets, const cabac_tu_desc *__restrict__ tus,
-                  const uint8_t *__restrict__ tuFlags, const uint64_t *__restrict__ tuOffsets,
-                  const cabac_ctu_desc *__restrict__ ctus, const uint64_t *__restrict__ ctuOffsets,
+emit_slice_kernel(const cabac_substream_params *__restrict__ params, const cabac_slice_params *__restrict__ sliceParams,
+                  size_t nSub, const cabac_cu_desc *__restrict__ cus, const uint64_t *__restrict__ cuOffsets,
+                  const cabac_tu_desc *__restrict__ tus, const uint8_t *__restrict__ tuFlags,
+                  const uint64_t *__restrict__ tuOffsets, const cabac_ctu_desc *__restrict__ ctus,
+                  const uint64_t *__restrict__ ctuOffsets, const cabac_ctx_model *__restrict__ ctxIn,
                   uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets, uint64_t capWords,
-                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus) {
+                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus, EmitRowArrays ra) {
   using Emitter = cabac_syntax::SliceParser<SliceEmitEngine>;
   __shared__ SliceLines lines[EMIT_WARPS_PER_BLOCK];
   __shared__ __align__(16) unsigned char engBuf[EMIT_WARPS_PER_BLOCK][(sizeof(SliceEmitEngine) + 15) & ~size_t(15)];
@@ -468,61 +515,103 @@ emit_slice_kernel(const cabac_slice_params *__restrict__ sliceParams, size_t nSu
   for (size_t sub = size_t(blockIdx.x) * EMIT_WARPS_PER_BLOCK + wib; sub < nSub; sub += size_t(gridDim.x) * EMIT_WARPS_PER_BLOCK) {
     const cabac_slice_params sp = sliceParams[sub];
     const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub];
-    uint32_t *dst = nullptr;
-    bool over = false;
-    if (cmdOffsets) {
-      over = cmdOffsets[sub + 1] > capWords;
-      dst = over ? nullptr : cmds + cmdOffsets[sub];
+    const bool write = cmdOffsets != nullptr;
+    const bool over = write && cmdOffsets[sub + 1] > capWords;
+    // a slice the count pass refused owns no words: walk it again without writing (same status)
+    const bool empty = write && cmdOffsets[sub + 1] == cmdOffsets[sub];
+    uint32_t *dst = (write && !over && !empty) ? cmds + cmdOffsets[sub] : nullptr;
+    SliceRowOut ro{};
+    ro.allow = ra.rowOffsets != nullptr;
+    ro.base = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub]) : uint32_t(sub);
+    ro.count = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub + 1] - ra.rowOffsets[sub]) : 1u;
+    const uint32_t ctuRows = (sp.y1 - sp.y0 + (1u << sp.log2_ctu) - 1) >> sp.log2_ctu;
+    const bool rowsOk = ro.count == ((sp.tools & CABAC_SL_WPP) ? ctuRows : 1u);
+    if (write) {
+      ro.cmdOff = ra.cmdOff;
+      ro.tuOff = ra.tuOff;
+      ro.sync = ra.sync;
+      ro.cmdBase = cmdOffsets[sub];
+      ro.tuBase = tu0;
+      const cabac_substream_params p = params[sub];
+      for (uint32_t r = lane; r < ro.count; r += 32) {  // defaults; the walk overwrites offsets and hand-over points
+        cabac_substream_params pr = p;
+        if (r) pr.flags = uint8_t(pr.flags & ~CABAC_SUB_CTX_IN);  // rows below the first start from their predecessor
+        ra.params[ro.base + r] = pr;
+        ra.slice[ro.base + r] = uint32_t(sub);
+        ra.sync[ro.base + r] = cabac_wpp_sync{r ? ro.base + r - 1 : CABAC_WPP_NONE, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u};
+        ra.cmdOff[ro.base + r] = ro.cmdBase;  // a refused slice: empty rows
+        ra.tuOff[ro.base + r] = tu0;
+      }
+      if (ra.ctxIn && ctxIn && (p.flags & CABAC_SUB_CTX_IN))
+        for (int k = lane; k < CABAC_NUM_CTX; k += 32) ra.ctxIn[size_t(ro.base) * CABAC_NUM_CTX + k] = ctxIn[sub * CABAC_NUM_CTX + k];
     }
     __syncwarp();
     SliceEmitEngine &eng = *new (engBuf[wib]) SliceEmitEngine(
         lines[wib], cus + cu0, uint32_t(cuOffsets[sub + 1] - cu0), tus + tu0, tuFlags + tu0, uint32_t(tuOffsets[sub + 1] - tu0),
-        ctus + ctu0, uint32_t(ctuOffsets[sub + 1] - ctu0), dst);
+        ctus + ctu0, uint32_t(ctuOffsets[sub + 1] - ctu0), dst, ro);
+    if (!dst) eng.ro.cmdOff = nullptr, eng.ro.tuOff = nullptr, eng.ro.sync = nullptr;
     __syncwarp();
     Emitter &ps = *new (psBuf[wib]) Emitter(eng, sp, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, ~uint64_t(0), 0);
     __syncwarp();
     uint32_t st = 0;
     if (((sp.x1 - sp.x0 + 3) >> 2) > uint32_t(SLICE_MAX_LINE) || ((sp.x1 - sp.x0) >> sp.log2_ctu) >= uint32_t(SLICE_MAX_CTU_COLS))
       st |= CABAC_SS_UNSUPPORTED;
+    else if (!rowsOk)
+      st |= ro.allow ? CABAC_SS_BAD_DESC : CABAC_SS_UNSUPPORTED;  // rows not described: a WPP slice cannot be written
     else
       ps.run(false);  // the terminating bin and finish() are the stream encoder's (CABAC_SUB_TERMINATE)
     st |= ps.status | (eng.bad ? uint32_t(CABAC_SS_BAD_DESC) : 0u) | (over ? uint32_t(CABAC_SS_CAPACITY) : 0u);
-    if (!st && (ps.nCu != eng.nCuIn || ps.nTu != eng.nTuIn)) st |= CABAC_SS_BAD_DESC;  // records left over
+    if (!st && (ps.nCu != eng.nCuIn || ps.nTu != eng.nTuIn || eng.row + 1 != ro.count)) st |= CABAC_SS_BAD_DESC;  // left-overs
+    __syncwarp();
     if (lane == 0) {
-      if (!cmdOffsets) counts[sub] = st ? 0u : eng.n;  // a refused slice codes nothing (its status says why)
+      if (!write) counts[sub] = st ? 0u : eng.n;  // a refused slice codes nothing (its status says why)
       emitStatus[sub] = st;
+      if (write && sub + 1 == nSub) {
+        const uint32_t nRows = ro.base + ro.count;
+        ra.cmdOff[nRows] = cmdOffsets[nSub];
+        ra.tuOff[nRows] = tuOffsets[nSub];
+      }
     }
     __syncwarp();
   }
 }
 
-__global__ void or_status_kernel(uint32_t *__restrict__ status, const uint32_t *__restrict__ extra, size_t n) {
-  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
-    if (extra[i]) status[i] |= extra[i];
+__global__ void or_status_kernel(uint32_t *__restrict__ status, const uint32_t *__restrict__ extra,
+                                 const uint32_t *__restrict__ rowSlice, size_t nRows) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < nRows; i += size_t(gridDim.x) * blockDim.x) {
+    const uint32_t e = extra[rowSlice[i]];
+    if (e) status[i] |= e;
+  }
 }
 
-// scratch: counts u32[nSub] | emitStatus u32[nSub] | cmdOffsets u64[nSub + 1] (8-byte aligned by the caller)
-cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_slice_params *sliceParams, size_t nSub,
-                             const cabac_cu_desc *cus, const uint64_t *cuOffsets, const cabac_tu_desc *tus,
-                             const uint8_t *tuFlags, const uint64_t *tuOffsets, const cabac_ctu_desc *ctus,
-                             const uint64_t *ctuOffsets, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
-                             uint32_t *emitStatus, uint64_t *cmdOffsets) {
+cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_substream_params *params,
+                             const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
+                             const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
+                             const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,
+                             const cabac_ctx_model *ctxIn, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
+                             uint32_t *emitStatus, uint64_t *cmdOffsets, const uint64_t *rowOffsets, uint64_t *rowCmdOff,
+                             uint64_t *rowTuOff, cabac_wpp_sync *rowSync, cabac_substream_params *rowParams,
+                             uint32_t *rowSlice, cabac_ctx_model *rowCtxIn) {
   if (nSub == 0) return cudaSuccess;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   const size_t want = (nSub + EMIT_WARPS_PER_BLOCK - 1) / EMIT_WARPS_PER_BLOCK, cap = size_t(sms) * 8;
   const int blocks = int(want < cap ? want : cap);
-  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(sliceParams, nSub, cus, cuOffsets, tus, tuFlags, tuOffsets, ctus,
-                                                                ctuOffsets, nullptr, nullptr, capWords, counts, emitStatus);
+  const EmitRowArrays ra{rowOffsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn};
+  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
+                                                                tuOffsets, ctus, ctuOffsets, ctxIn, nullptr, nullptr, capWords,
+                                                                counts, emitStatus, ra);
   entry_points_kernel<<<1, 1024, 0, s>>>(counts, nullptr, nSub, cmdOffsets);
-  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(sliceParams, nSub, cus, cuOffsets, tus, tuFlags, tuOffsets, ctus,
-                                                                ctuOffsets, cmds, cmdOffsets, capWords, counts, emitStatus);
+  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
+                                                                tuOffsets, ctus, ctuOffsets, ctxIn, cmds, cmdOffsets, capWords,
+                                                                counts, emitStatus, ra);
   return cudaGetLastError();
 }
 
-cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, size_t n) {
-  if (!n || !status) return cudaSuccess;
-  or_status_kernel<<<unsigned((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024), 256, 0, s>>>(status, extra, n);
+cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, const uint32_t *rowSlice, size_t nRows) {
+  if (!nRows || !status) return cudaSuccess;
+  or_status_kernel<<<unsigned((nRows + 255) / 256 < 1024 ? (nRows + 255) / 256 : 1024), 256, 0, s>>>(status, extra, rowSlice,
+                                                                                                   nRows);
   return cudaGetLastError();
 }
 

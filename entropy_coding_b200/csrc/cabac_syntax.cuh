@@ -1054,8 +1054,8 @@ struct SliceParser {
       status |= CABAC_SS_UNSUPPORTED;
       return;
     }
-    if (E::kEncode && tool(CABAC_SL_WPP)) {  // writer direction: one command stream per slice; WPP rows are separate
-      status |= CABAC_SS_UNSUPPORTED;          // substreams of the encoder (cabac_encode_stream_wpp) - not built
+    if (E::kEncode && tool(CABAC_SL_WPP) && !e.rows()) {  // writer direction: the rows of a WPP slice are separate
+      status |= CABAC_SS_UNSUPPORTED;                       // substreams; the engine must be set up to cut them
       return;
     }
     const int ctu = 1 << sp.log2_ctu;

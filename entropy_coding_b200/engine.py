@@ -13,7 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .types import (CTU_DT, CTX_DT, CU_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, SLICE_DT, TU_DT, WPP_DT)
+from .types import (CTU_DT, CTX_DT, CU_DT, ERR_SUBSTREAM, NUM_CTX, OK, PARAMS_DT, SL_WPP, SLICE_DT, TU_DT, WPP_DT)
 
 
 class CabacError(RuntimeError):
@@ -358,6 +358,42 @@ class CabacEngine:
         if rc != ERR_SUBSTREAM or raise_on_status:
             self._check(rc, status)
         return dict(out=out, sizes=sizes, num_bins=bins, status=status, ctx_out=ctx_out)
+
+    @staticmethod
+    def slice_rows(slice_params):
+        """row_offsets for cabac_encode_slices_wpp: one row substream per CTU row of a WPP slice, one per other slice."""
+        sp = _np(slice_params, SLICE_DT)
+        ctu = np.int64(1) << sp["log2_ctu"].astype(np.int64)
+        rows = np.where(sp["tools"] & SL_WPP, -(-(sp["y1"].astype(np.int64) - sp["y0"]) // ctu), 1)
+        return np.concatenate([[0], np.cumsum(rows)]).astype(np.uint64)
+
+    def encode_slices_wpp(self, params, slice_params, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus, ctu_offsets, coeffs,
+                          out_offsets, cmd_words=None, ctx_in=None, want_ctx=False, raise_on_status=True):
+        """cabac_encode_slices_wpp: like encode_slices for any mix of WPP and other slices; out_offsets, sizes, bins,
+        status and contexts are per ROW substream (row_offsets = slice_rows(slice_params), also returned)."""
+        params, sp = _np(params, PARAMS_DT), _np(slice_params, SLICE_DT)
+        cus, tus, ctus = _np(cus, CU_DT), _np(tus, TU_DT), _np(ctus, CTU_DT)
+        tu_flags, coeffs = _np(tu_flags, np.uint8), _np(coeffs, np.int32)
+        cu_offsets, tu_offsets = _np(cu_offsets, np.uint64), _np(tu_offsets, np.uint64)
+        ctu_offsets, out_offsets = _np(ctu_offsets, np.uint64), _np(out_offsets, np.uint64)
+        n = len(params)
+        row_offsets = self.slice_rows(sp)
+        n_rows = int(row_offsets[-1])
+        assert len(out_offsets) == n_rows + 1, "out_offsets is per row substream"
+        if cmd_words is None:
+            area = (sp["x1"].astype(np.int64) - sp["x0"]) * (sp["y1"].astype(np.int64) - sp["y0"])
+            cmd_words = int(area.sum()) * 4 + 64 * n
+        out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
+        sizes, bins, status = np.zeros(n_rows, np.uint32), np.zeros(n_rows, np.uint32), np.zeros(n_rows, np.uint32)
+        ctx_in = _np(ctx_in, CTX_DT)
+        ctx_out = np.zeros((n_rows, NUM_CTX), CTX_DT) if want_ctx else None
+        rc = self.lib.cabac_encode_slices_wpp(self.h, _hp(params), _hp(sp), n, _hp(cus), _hp(cu_offsets), _hp(tus),
+                                              _hp(tu_flags), _hp(tu_offsets), _hp(ctus), _hp(ctu_offsets), _hp(coeffs),
+                                              coeffs.size, _hp(ctx_in), int(cmd_words), _hp(row_offsets), n_rows, _hp(out),
+                                              _hp(out_offsets), _hp(sizes), _hp(bins), _hp(ctx_out), _hp(status))
+        if rc != ERR_SUBSTREAM or raise_on_status:
+            self._check(rc, status)
+        return dict(out=out, sizes=sizes, num_bins=bins, status=status, ctx_out=ctx_out, row_offsets=row_offsets)
 
     def encode_slices_dev(self, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus,
                           ctu_offsets, coeffs, cmd_scratch, cmd_scratch_words, out, out_offsets, out_sizes, status,

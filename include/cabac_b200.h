@@ -870,8 +870,7 @@ int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_o
  * (cabac_encode_stream_dev) then codes them, terminating bin and finish() included
  * (params[i].flags: CABAC_SUB_TERMINATE | CABAC_SUB_ALIGN as for every slice payload).
  * status[i]: CABAC_SS_* of the stream encoder, plus CABAC_SS_UNSUPPORTED (see cabac_decode_slices; also
- * CABAC_SL_WPP, whose rows are separate substreams on the writer side: pass one rectangle per CTU row
- * and chain the contexts with cabac_encode_stream_dev's wavefront mode), CABAC_SS_BAD_DESC (records that do
+ * CABAC_SL_WPP slices, whose rows are separate substreams: cabac_encode_slices_wpp), CABAC_SS_BAD_DESC (records that do
  * not describe a legal partitioning of the rectangle, or left-over records) and CABAC_SS_CAPACITY
  * (cmd_scratch too small: nothing is encoded and the call returns CABAC_ERR_SUBSTREAM).
  * The _dev form synchronises the stream once (it reads the total command count back).              */
@@ -894,6 +893,39 @@ int cabac_encode_slices(cabac_handle *h, const cabac_substream_params *params,
                         const cabac_ctx_model *ctx_in, size_t cmd_words, uint8_t *out,
                         const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
                         cabac_ctx_model *ctx_out, uint32_t *status);
+
+/* The same for slices with entropy_coding_sync_enabled (CABAC_SL_WPP) - and any mix of WPP and other slices.
+ * The output is per ROW substream: a WPP slice has one per CTU row (EncSlice.cpp:2057-2089: the row's
+ * end_of_subset_one_bit, finish() and alignment close it, the next row starts from the contexts held after the
+ * first CTU of the row above), any other slice has one.  row_offsets[n_sub + 1] is the exclusive scan of the
+ * rows per slice (a WPP slice: ceil((y1 - y0) / CTU size); otherwise 1), n_rows = row_offsets[n_sub];
+ * out_offsets[n_rows + 1], out_sizes, num_bins, ctx_out ([n_rows][CABAC_NUM_CTX]) and status are indexed by row
+ * substream (slice i's rows are row_offsets[i] .. row_offsets[i + 1]; their payloads back to back are the slice
+ * data, their sizes the entry points: cabac_pack_dev).  The records are one
+ * list per slice as above - the walk cuts its command stream at the row ends and notes the hand-over point of
+ * every row; the stream encoder's wavefront mode (cabac_encode_stream_wpp_dev) codes all rows in one launch,
+ * every CTU once.  A slice whose row count does not match its rectangle gets CABAC_SS_BAD_DESC.            */
+int cabac_encode_slices_wpp_dev(cabac_handle *h, const cabac_substream_params *params,
+                                const cabac_slice_params *slice_params, size_t n_sub,
+                                const cabac_cu_desc *cus, const uint64_t *cu_offsets,
+                                const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                                const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                                const uint64_t *ctu_offsets, const int32_t *coeffs,
+                                const cabac_ctx_model *ctx_in, uint32_t *cmd_scratch,
+                                size_t cmd_scratch_words, const uint64_t *row_offsets,
+                                size_t n_rows, uint8_t *out, const uint64_t *out_offsets,
+                                uint32_t *out_sizes, uint32_t *num_bins,
+                                cabac_ctx_model *ctx_out, uint32_t *status);
+int cabac_encode_slices_wpp(cabac_handle *h, const cabac_substream_params *params,
+                            const cabac_slice_params *slice_params, size_t n_sub,
+                            const cabac_cu_desc *cus, const uint64_t *cu_offsets,
+                            const cabac_tu_desc *tus, const uint8_t *tu_flags,
+                            const uint64_t *tu_offsets, const cabac_ctu_desc *ctus,
+                            const uint64_t *ctu_offsets, const int32_t *coeffs, size_t n_coeffs,
+                            const cabac_ctx_model *ctx_in, size_t cmd_words,
+                            const uint64_t *row_offsets, size_t n_rows, uint8_t *out,
+                            const uint64_t *out_offsets, uint32_t *out_sizes, uint32_t *num_bins,
+                            cabac_ctx_model *ctx_out, uint32_t *status);
 
 #ifdef __cplusplus
 }

@@ -83,6 +83,7 @@ struct HostEngine {
   const uint8_t *sliceIn = nullptr;
   long sliceBytes = 0, rowStart = 0;
   cabac_ctx_model rowCtx[CABAC_NUM_CTX];
+  bool rows() const { return false; }
   void saveRowContexts() { orc_dec_ctx_get(dec, rowCtx); }
   void nextRow() {
     const long used = rowStart + (orc_dec_bits(dec) >> 3) + 1;
@@ -254,6 +255,7 @@ struct GenEngine {
   }
   void putCu(uint32_t i, const cabac_cu_desc &c) { cusOut[i] = c; }
   void putCtu(uint32_t i, const cabac_ctu_desc &c) { ctusOut[i] = c; }
+  bool rows() const { return false; }
   void saveRowContexts() { orc_enc_ctx_get(enc, rowCtx); }
   void nextRow() {  // the row's terminating bin is coded: finish + alignment, fresh coder, contexts of the row above
     orc_enc_flush(enc, 1);
@@ -376,6 +378,7 @@ struct EmitEngine {
   }
   void putCu(uint32_t, const cabac_cu_desc &) {}
   void putCtu(uint32_t, const cabac_ctu_desc &) {}
+  bool rows() const { return true; }  // the row ends stay in the sequence as terminating bins, as the writer made them
   void saveRowContexts() {}
   void nextRow() {}
   void abort() { dead = true; }

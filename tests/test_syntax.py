@@ -519,8 +519,6 @@ def test_host_writer_direction_reproduces_the_writers_calls():
     lib = _host_lib()
     n = 0
     for tag, s, sp in _substreams():
-        if int(sp["tools"]) & SL_WPP:
-            continue
         r = _host_decode(lib, s, sp)
         nctu = -(-int(sp["x1"] - sp["x0"]) >> int(sp["log2_ctu"])) * -(-int(sp["y1"] - sp["y0"]) >> int(sp["log2_ctu"]))
         r["ctus"] = r["ctus"][:nctu]
@@ -536,8 +534,6 @@ def test_host_writer_direction_reproduces_the_writers_calls():
     assert n >= 6
     # and on generated slices (all tools): emit(decode(x)) is the generating walk's sequence again
     for tag, g, sp in _gen_items(lib):
-        if int(sp["tools"]) & SL_WPP:
-            continue
         r = _host_decode_fresh(lib, g, sp)
         r["ctus"] = r["ctus"][:len(g["ctus"])]
         cmds, st = _host_emit(lib, sp, r)
@@ -621,3 +617,61 @@ def test_gpu_encode_slices_reproduces_the_reference_payloads(engine):
     w = engine.encode_slices(one, np.array([sp], SLICE_DT), h["cus"], [0, len(h["cus"])], h["tus"], h["tu_flags"], [0, len(h["tus"])],
                              h["ctus"], [0, nctu], h["coeffs"], [0, s["payload"].size + 64], raise_on_status=False)
     assert int(w["status"][0]) & SS_UNSUPPORTED
+
+
+@pytest.mark.gpu
+def test_gpu_encode_slices_wpp_rows(engine):
+    """cabac_encode_slices_wpp: WPP slices written as one substream per CTU row, contexts handed over on the device -
+    the VTM WPP frames come back row by row with the reference's row sizes; mixed in one call with every other
+    fixture slice and with generated slices (WPP at every CTU size)."""
+    lib = _host_lib()
+    vtm = [(t, s, sp, s["flags"] | SUB_TERMINATE | SUB_CTX_IN, np.stack([s["ctx_in"][:, 0], s["ctx_in"][:, 1]], 1))
+           for t, s, sp in _substreams()]
+    gen = [(t, g, sp, g["flags"] | SUB_TERMINATE, None) for t, g, sp in _gen_items(lib, reps=2)]
+    assert sum(1 for x in vtm if int(x[2]["tools"]) & SL_WPP) >= 2 and sum(1 for x in gen if int(x[2]["tools"]) & SL_WPP) >= 3
+    for items in (vtm, gen):
+        n = len(items)
+        params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+        ctx_in = np.zeros((n, 379), CTX_DT) if items[0][4] is not None else None
+        data, off = [], [0]
+        for k, (tag, s, sp, fl, cin) in enumerate(items):
+            params[k] = (s["qp"], s["init_id"], fl | SUB_ALIGN, 0)
+            sps[k] = sp
+            if cin is not None:
+                ctx_in[k]["state0"], ctx_in[k]["state1"] = cin[:, 0], cin[:, 1]
+            data.append(s["payload"])
+            off.append(off[-1] + s["payload"].size)
+        d = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, ctx_in=ctx_in, want_ctx=True)
+        rec = _compact(d, n)
+        rows = engine.slice_rows(sps)
+        cap = np.concatenate([[data[k].size + 64] * int(rows[k + 1] - rows[k]) for k in range(n)])
+        out_off = np.concatenate([[0], np.cumsum(cap)]).astype(np.uint64)
+        w = engine.encode_slices_wpp(params, sps, rec["cus"], rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                                     rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off, ctx_in=ctx_in, want_ctx=True)
+        assert (w["row_offsets"] == rows).all()
+        for k, (tag, s, sp, fl, cin) in enumerate(items):
+            a, b = int(rows[k]), int(rows[k + 1])
+            assert not w["status"][a:b].any(), f"{tag}: status {w['status'][a:b]}"
+            got = np.concatenate([w["out"][int(out_off[r]):int(out_off[r]) + int(w["sizes"][r])] for r in range(a, b)])
+            assert got.tobytes() == s["payload"].tobytes(), f"{tag}: {got.size} bytes vs the writer's {s['payload'].size}"
+            if "row_bytes" in s:
+                assert [int(v) for v in w["sizes"][a:b]] == s["row_bytes"], tag
+            assert int(w["num_bins"][a:b].sum()) == int(d["num_bins"][k]), tag
+            assert w["ctx_out"][b - 1].tobytes() == d["ctx_out"][k].tobytes(), tag
+    # a row count that does not match the rectangle is refused for that slice only
+    k = next(i for i, x in enumerate(gen) if int(x[2]["tools"]) & SL_WPP and int(rows[i + 1] - rows[i]) > 1)
+    sps2 = sps.copy()
+    sps2[k]["tools"] &= ~np.uint32(SL_WPP)  # one row announced (slice_rows), records of a slice with several
+    rows2 = engine.slice_rows(sps2)
+    sps2[k]["tools"] |= np.uint32(SL_WPP)
+    cap2 = np.concatenate([[data[i].size + 64] * int(rows2[i + 1] - rows2[i]) for i in range(n)])
+    out2 = np.concatenate([[0], np.cumsum(cap2)]).astype(np.uint64)
+    lib_rc = engine.lib.cabac_encode_slices_wpp
+    sizes, bins, status = np.zeros(int(rows2[-1]), np.uint32), np.zeros(int(rows2[-1]), np.uint32), np.zeros(int(rows2[-1]), np.uint32)
+    out = np.zeros(int(out2[-1]), np.uint8)
+    P = lambda a: np.ascontiguousarray(a).ctypes.data_as(C.c_void_p)  # noqa: E731
+    keep = [np.ascontiguousarray(rec[x]) for x in ("cus", "cu_offsets", "tus", "tu_flags", "tu_offsets", "ctus", "ctu_offsets", "coeffs")]
+    rc = lib_rc(engine.h, P(params), P(sps2), n, P(keep[0]), P(keep[1]), P(keep[2]), P(keep[3]), P(keep[4]), P(keep[5]), P(keep[6]),
+                P(keep[7]), keep[7].size, None, 1 << 22, P(rows2), int(rows2[-1]), P(out), P(out2), P(sizes), P(bins), None, P(status))
+    assert rc == -3 and int(status[int(rows2[k])]) & SS_BAD_DESC
+    assert not np.delete(status, int(rows2[k])).any()
