@@ -7,8 +7,10 @@
 // cabac_cu_desc per CodingUnit in coding order (partitioning path, prediction mode, coded block flags, ...), one
 // cabac_tu_desc + TCoeff block per coded transform block, one cabac_ctu_desc per CTU (SAO / ALF) - and flush()
 // walks the syntax on the device (split_cu_mode with the partitioner's legality rules, MPM derivation, cbf / LFNST /
-// MTS conditions) and codes it; bytes(i) is what CABACWriter + BinEncoder would have left in the slice's
-// OutputBitstream (terminating bin, finish() and the rbsp trailing bits included).
+// MTS conditions) and codes it; result(i).bytes is what CABACWriter + BinEncoder would have left in the slice's
+// OutputBitstream (terminating bin, finish() and the rbsp trailing bits included) - for a slice with
+// entropy_coding_sync_enabled its CTU-row substreams back to back, with the row sizes for the entry points
+// (cabac_encode_slices_wpp: the rows are coded in one launch, contexts handed over on the device).
 #pragma once
 #include <algorithm>
 #include <vector>
@@ -60,9 +62,11 @@ inline cabac_ctu_desc ctuDesc(const Common::CodingStructure &cs, unsigned ctuRsA
 class GpuSliceWriter {
  public:
   struct Result {
-    const uint8_t *bytes;
+    const uint8_t *bytes;         // the slice data: a WPP slice's CTU-row substreams back to back
     size_t nbytes;
-    const cabac_ctx_model *ctx;  // Ctx after the slice
+    const uint32_t *rowBytes;     // bytes per row substream (the entry points of a WPP slice); nRows == 1 otherwise
+    size_t nRows;
+    const cabac_ctx_model *ctx;   // Ctx after the slice
     uint32_t numBins, status;
   };
 
@@ -90,6 +94,10 @@ class GpuSliceWriter {
     ctxIn_.resize(params_.size() * CABAC_NUM_CTX);
     if (ctxIn) std::copy(ctxIn, ctxIn + CABAC_NUM_CTX, ctxIn_.begin() + (params_.size() - 1) * CABAC_NUM_CTX);
     anyCtxIn_ |= ctxIn != nullptr;
+    const uint32_t ctu = 1u << sp.log2_ctu;
+    rowOff_.push_back(rowOff_.back() + ((sp.tools & CABAC_SL_WPP) ? (sp.y1 - sp.y0 + ctu - 1) / ctu : 1u));
+    rowCoeffs_.resize(rowOff_.back(), 0);
+    curRow_ = 0;
     open_ = true;
     return params_.size() - 1;
   }
@@ -114,6 +122,7 @@ class GpuSliceWriter {
     cabac_cu_desc d{};
     d.x = uint16_t(b.x << sh);
     d.y = uint16_t(b.y << sh);
+    setRow(d.y);
     d.log2_w = uint8_t(C::floorLog2(b.width << sh));
     d.log2_h = uint8_t(C::floorLog2(b.height << sh));
     d.ch_type = uint8_t(cu.chType);
@@ -158,11 +167,16 @@ class GpuSliceWriter {
     d.n_tu = uint16_t(tus_.size() - tuOff_.back() - d.first_tu);
     addCuRaw(d);
   }
-  void addCuRaw(const cabac_cu_desc &d) { cus_.push_back(d); }
+  // Raw records: a CU, then its coded transform blocks (so that the output capacity can be sized per CTU row).
+  void addCuRaw(const cabac_cu_desc &d) {
+    setRow(d.y);
+    cus_.push_back(d);
+  }
   // A coded transform block with its coefficients (row-major, stride == width) and CABAC_TUR_* side flags.
   void addTuRaw(cabac_tu_desc d, const int32_t *coeff, uint8_t tuFlags) {
     d.coeff_offset = coeffs_.size();
     coeffs_.insert(coeffs_.end(), coeff, coeff + (size_t(1) << (d.log2_w + d.log2_h)));
+    rowCoeffs_[rowOff_[params_.size() - 1] + curRow_] += uint64_t(1) << (d.log2_w + d.log2_h);
     tus_.push_back(d);
     tuFlags_.push_back(tuFlags);
   }
@@ -172,34 +186,51 @@ class GpuSliceWriter {
   void flush() {
     closeSlice();
     const size_t n = params_.size();
-    outOff_.assign(1, 0);
+    const size_t nRows = rowOff_.back();
+    std::vector<uint64_t> rowCap(1, 0);
     size_t words = 0;
     for (size_t i = 0; i < n; i++) {
       const cabac_slice_params &s = sps_[i];
-      const uint64_t area = uint64_t(s.x1 - s.x0) * (s.y1 - s.y0);
-      const uint64_t co = coOff_[i + 1] - coOff_[i];
-      outOff_.push_back(outOff_.back() + area / 4 + co * 3 + 256);  // <= 20 bits per coefficient + syntax
+      const uint64_t area = uint64_t(s.x1 - s.x0) * (s.y1 - s.y0), rows = rowOff_[i + 1] - rowOff_[i];
+      for (uint64_t r = rowOff_[i]; r < rowOff_[i + 1]; r++)  // <= 20 bits per coefficient + syntax
+        rowCap.push_back(rowCap.back() + area / rows / 4 + rowCoeffs_[r] * 3 + 256);
       words += area * 4 + 64;
     }
-    out_.resize(outOff_.back());
-    sizes_.resize(n);
-    bins_.resize(n);
-    status_.resize(n);
-    ctxOut_.resize(n * CABAC_NUM_CTX);
+    rows_.resize(rowCap.back());
+    sizes_.resize(nRows);
+    rowBins_.resize(nRows);
+    rowStatus_.resize(nRows);
+    rowCtx_.resize(nRows * CABAC_NUM_CTX);
     const int32_t none = 0;
-    const int rc = cabac_encode_slices(eng_.get(), params_.data(), sps_.data(), n, cus_.data(), cuOff_.data(), tus_.data(),
-                                       tuFlags_.data(), tuOff_.data(), ctus_.data(), ctuOff_.data(),
-                                       coeffs_.empty() ? &none : coeffs_.data(), coeffs_.size(),
-                                       anyCtxIn_ ? ctxIn_.data() : nullptr, words, out_.data(), outOff_.data(),
-                                       sizes_.data(), bins_.data(), ctxOut_.data(), status_.data());
-    eng_.check(rc, "cabac_encode_slices");
+    const int rc = cabac_encode_slices_wpp(eng_.get(), params_.data(), sps_.data(), n, cus_.data(), cuOff_.data(), tus_.data(),
+                                           tuFlags_.data(), tuOff_.data(), ctus_.data(), ctuOff_.data(),
+                                           coeffs_.empty() ? &none : coeffs_.data(), coeffs_.size(),
+                                           anyCtxIn_ ? ctxIn_.data() : nullptr, words, rowOff_.data(), nRows, rows_.data(),
+                                           rowCap.data(), sizes_.data(), rowBins_.data(), rowCtx_.data(), rowStatus_.data());
+    eng_.check(rc, "cabac_encode_slices_wpp");
+    // per slice: the rows back to back, bins summed, the last row's contexts
+    out_.clear();
+    outOff_.assign(1, 0);
+    bins_.assign(n, 0);
+    status_.assign(n, 0);
+    ctxOut_.resize(n * CABAC_NUM_CTX);
     for (size_t i = 0; i < n; i++) {
+      for (uint64_t r = rowOff_[i]; r < rowOff_[i + 1]; r++) {
+        out_.insert(out_.end(), rows_.begin() + rowCap[r], rows_.begin() + rowCap[r] + sizes_[r]);
+        bins_[i] += rowBins_[r];
+        status_[i] |= rowStatus_[r];
+      }
+      outOff_.push_back(out_.size());
+      std::copy_n(rowCtx_.begin() + (rowOff_[i + 1] - 1) * CABAC_NUM_CTX, CABAC_NUM_CTX, ctxOut_.begin() + i * CABAC_NUM_CTX);
       const uint32_t st = status_[i];
       CHECK(st & CABAC_SS_UNSUPPORTED, "B200 CABAC engine: slice uses a tool outside the device writer's scope");
       CHECK(st & CABAC_SS_BAD_DESC, "B200 CABAC engine: the CU / TU records do not describe a legal partitioning");
       CHECK(st & CABAC_SS_COEFF_RANGE, "TransCoeffLevel outside allowable range");
       CHECK(st & (CABAC_SS_CAPACITY | CABAC_SS_OUT_OVERFLOW), "B200 CABAC engine: output capacity exceeded");
     }
+    doneRowOff_ = rowOff_;
+    rowOff_.assign(1, 0);
+    rowCoeffs_.clear();
     done_ = n;
     params_.clear();
     sps_.clear();
@@ -218,7 +249,8 @@ class GpuSliceWriter {
 
   size_t size() const { return done_; }
   Result result(size_t i) const {
-    return Result{out_.data() + outOff_[i], sizes_[i], ctxOut_.data() + i * CABAC_NUM_CTX, bins_[i], status_[i]};
+    return Result{out_.data() + outOff_[i], size_t(outOff_[i + 1] - outOff_[i]), sizes_.data() + doneRowOff_[i],
+                  size_t(doneRowOff_[i + 1] - doneRowOff_[i]), ctxOut_.data() + i * CABAC_NUM_CTX, bins_[i], status_[i]};
   }
 
  private:
@@ -237,6 +269,11 @@ class GpuSliceWriter {
                       (bdpcm ? CABAC_TU_BDPCM : 0));
     addTuRaw(d, tu.getCoeffs(compID).buf, uint8_t(GpuBinEncoder::sideFlags(tu, compID) | (ts ? CABAC_TUR_TS : 0)));
   }
+  void setRow(unsigned y) {
+    const cabac_slice_params &sp = sps_.back();
+    curRow_ = (sp.tools & CABAC_SL_WPP) ? (y - sp.y0) >> sp.log2_ctu : 0;
+    CHECK(rowOff_[params_.size() - 1] + curRow_ >= rowOff_.back(), "B200 CABAC engine: CU outside the slice's rectangle");
+  }
   void closeSlice() {
     if (!open_) return;
     cuOff_.push_back(cus_.size());
@@ -254,9 +291,11 @@ class GpuSliceWriter {
   std::vector<uint8_t> tuFlags_, out_;
   std::vector<cabac_ctu_desc> ctus_;
   std::vector<int32_t> coeffs_;
-  std::vector<uint64_t> cuOff_{0}, tuOff_{0}, ctuOff_{0}, coOff_{0}, outOff_;
-  std::vector<cabac_ctx_model> ctxIn_, ctxOut_;
-  std::vector<uint32_t> sizes_, bins_, status_;
+  std::vector<uint8_t> rows_;
+  std::vector<uint64_t> cuOff_{0}, tuOff_{0}, ctuOff_{0}, coOff_{0}, outOff_, rowOff_{0}, doneRowOff_, rowCoeffs_;
+  std::vector<cabac_ctx_model> ctxIn_, ctxOut_, rowCtx_;
+  std::vector<uint32_t> sizes_, bins_, status_, rowBins_, rowStatus_;
+  unsigned curRow_ = 0;
   bool anyCtxIn_ = false, open_ = false;
   size_t done_ = 0;
 };

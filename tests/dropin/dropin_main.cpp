@@ -185,8 +185,7 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
   cabac_b200::GpuSliceWriter wr(eng);
   std::vector<uint32_t> written;
   for (uint32_t i = 0; i < n; i++) {
-    if (sliceParams[i].tools & CABAC_SL_WPP) continue;  // rows of a WPP slice are separate substreams on the writer side
-    const auto r = rd.result(i);
+    const auto r = rd.result(i);  // WPP slices too: their rows come back as separate substreams, back to back
     wr.beginSliceRaw(subParams[i], sliceParams[i], ctxIns[i].data());
     for (size_t k = 0; k < r.nCtus; k++) wr.addCtuRaw(r.ctus[k]);
     for (size_t k = 0; k < r.nCus; k++) {
@@ -194,8 +193,9 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
       c.flags = uint8_t((c.flags & ~(CABAC_CU_MPM | CABAC_CU_CCLM)) | CABAC_CU_FROM_DIR);
       c.pred_syntax = 0;
       wr.addCuRaw(c);
+      for (uint32_t t = c.first_tu; t < c.first_tu + c.n_tu; t++)
+        wr.addTuRaw(r.tus[t], rd.coeffs() + r.tus[t].coeff_offset, r.tuFlags[t]);
     }
-    for (size_t t = 0; t < r.nTus; t++) wr.addTuRaw(r.tus[t], rd.coeffs() + r.tus[t].coeff_offset, r.tuFlags[t]);
     written.push_back(i);
   }
   wr.flush();
@@ -203,7 +203,9 @@ static int sliceReaderPart(cabac_b200::Engine &eng, const char *path) {
   for (size_t k = 0; k < written.size(); k++) {
     const auto w = wr.result(k);
     const auto &pl = payloads[written[k]];
-    if (w.status || w.nbytes != pl.size() || memcmp(w.bytes, pl.data(), pl.size()) || w.numBins != want[written[k]].nBins) {
+    const bool wpp = (sliceParams[written[k]].tools & CABAC_SL_WPP) != 0;
+    if (w.status || w.nbytes != pl.size() || memcmp(w.bytes, pl.data(), pl.size()) || w.numBins != want[written[k]].nBins ||
+        (wpp ? w.nRows < 2 : w.nRows != 1)) {
       printf("part S slice %u: written %zu bytes / %u bins, the reference's %zu / %u, status %u\n", written[k], w.nbytes,
              w.numBins, pl.size(), want[written[k]].nBins, w.status);
       wfails++;
