@@ -688,11 +688,13 @@ static int encodeSliceRows(cabac_handle *h, const char *what, const cabac_substr
   uint32_t *rowSlice = emitStatus + n_sub;
   cabac_substream_params *rowParams = reinterpret_cast<cabac_substream_params *>(rowSlice + n_rows);
   cabac_ctx_model *rowCtxIn = ctx_in ? reinterpret_cast<cabac_ctx_model *>(rowParams + n_rows) : nullptr;
-  CK(cabac::launchEmitSlices(h->stream, h->device, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
+  cabac::Sched sc;
+  CK(schedFor(h, n_sub, sc), "scheduler scratch");
+  CK(cabac::launchEmitSlices(h->stream, h->device, sc, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
                              ctus, ctu_offsets, ctx_in, cmd_scratch, cmd_scratch_words, counts, emitStatus, cmdOffsets,
                              row_offsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn),
      "emit_slice kernels");
-  h->launches += 3;
+  h->launches += 7;
   // a slice whose commands did not fit (CABAC_SS_CAPACITY) has offsets past the scratch: the encoder must not read
   // them, so such a call stops here with every slice's status written
   CK(cudaMemsetAsync(out_sizes, 0, n_rows * 4, h->stream), "memset");

@@ -55,7 +55,7 @@ cudaError_t launchDecodeSlices(cudaStream_t s, int device, const Sched &sc, cons
                                cabac_tu_desc *tus, uint8_t *tuFlags, cabac_ctu_desc *ctus, int32_t *coeffs,
                                uint32_t *counts, uint32_t *numBins, uint32_t *bitsRead, cabac_ctx_model *ctxOut,
                                uint32_t *status);
-cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_substream_params *params,
+cudaError_t launchEmitSlices(cudaStream_t s, int device, const Sched &sc, const cabac_substream_params *params,
                              const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
                              const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
                              const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,

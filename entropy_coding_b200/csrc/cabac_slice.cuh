@@ -426,7 +426,11 @@ struct SliceEmitEngine {
       return 0;
     }
     const cabac_tu_desc t = tusIn[idx];
-    if (t.log2_w != d.log2_w || t.log2_h != d.log2_h || t.comp_id != d.comp_id || ((t.flags ^ d.flags) & uint8_t(~CABAC_TU_TS))) {
+    // the shape and the flags are the walk's; transform_skip_flag is the record's, where the syntax has one (a BDPCM
+    // block is transform-skipped by inference)
+    const bool tsOk = !(t.flags & CABAC_TU_TS) || (d.flags & (CABAC_TU_TS_ALLOWED | CABAC_TU_BDPCM));
+    if (t.log2_w != d.log2_w || t.log2_h != d.log2_h || t.comp_id != d.comp_id || ((t.flags ^ d.flags) & uint8_t(~CABAC_TU_TS)) ||
+        !tsOk) {
       bad = dead = true;
       return 0;
     }
@@ -506,13 +510,15 @@ emit_slice_kernel(const cabac_substream_params *__restrict__ params, const cabac
                   const uint64_t *__restrict__ tuOffsets, const cabac_ctu_desc *__restrict__ ctus,
                   const uint64_t *__restrict__ ctuOffsets, const cabac_ctx_model *__restrict__ ctxIn,
                   uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets, uint64_t capWords,
-                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus, EmitRowArrays ra) {
+                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus, EmitRowArrays ra,
+                  const uint32_t *__restrict__ order, uint32_t *cursor) {
   using Emitter = cabac_syntax::SliceParser<SliceEmitEngine>;
   __shared__ SliceLines lines[EMIT_WARPS_PER_BLOCK];
   __shared__ __align__(16) unsigned char engBuf[EMIT_WARPS_PER_BLOCK][(sizeof(SliceEmitEngine) + 15) & ~size_t(15)];
   __shared__ __align__(16) unsigned char psBuf[EMIT_WARPS_PER_BLOCK][(sizeof(Emitter) + 15) & ~size_t(15)];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  for (size_t sub = size_t(blockIdx.x) * EMIT_WARPS_PER_BLOCK + wib; sub < nSub; sub += size_t(gridDim.x) * EMIT_WARPS_PER_BLOCK) {
+  size_t sub = 0;
+  while (nextSubstream(order, cursor, nSub, lane, sub)) {  // longest slice first (by CU count), warps pull from a cursor
     const cabac_slice_params sp = sliceParams[sub];
     const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub];
     const bool write = cmdOffsets != nullptr;
@@ -584,7 +590,7 @@ __global__ void or_status_kernel(uint32_t *__restrict__ status, const uint32_t *
   }
 }
 
-cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_substream_params *params,
+cudaError_t launchEmitSlices(cudaStream_t s, int device, const Sched &sc, const cabac_substream_params *params,
                              const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
                              const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
                              const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,
@@ -598,13 +604,17 @@ cudaError_t launchEmitSlices(cudaStream_t s, int device, const cabac_substream_p
   const size_t want = (nSub + EMIT_WARPS_PER_BLOCK - 1) / EMIT_WARPS_PER_BLOCK, cap = size_t(sms) * 8;
   const int blocks = int(want < cap ? want : cap);
   const EmitRowArrays ra{rowOffsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn};
+  cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cuOffsets, nSub, sc.cost);  // CUs per slice: the walk's length
+  cudaError_t e = launchOrder(s, sc, nSub);
+  if (e != cudaSuccess) return e;
   emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
                                                                 tuOffsets, ctus, ctuOffsets, ctxIn, nullptr, nullptr, capWords,
-                                                                counts, emitStatus, ra);
+                                                                counts, emitStatus, ra, sc.order, sc.cursor);
   entry_points_kernel<<<1, 1024, 0, s>>>(counts, nullptr, nSub, cmdOffsets);
+  if ((e = launchOrder(s, sc, nSub)) != cudaSuccess) return e;  // same order, cursor back to 0
   emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
                                                                 tuOffsets, ctus, ctuOffsets, ctxIn, cmds, cmdOffsets, capWords,
-                                                                counts, emitStatus, ra);
+                                                                counts, emitStatus, ra, sc.order, sc.cursor);
   return cudaGetLastError();
 }
 

@@ -526,7 +526,8 @@ struct SliceParser {
     if (E::kEncode) {
       cu = e.getCu(nCu);  // the caller's record: must describe this very node
       if (cu.x != uint16_t(n.x) || cu.y != uint16_t(n.y) || cu.log2_w != n.log2w || cu.log2_h != n.log2h ||
-          cu.ch_type != uint8_t(ch)) {
+          cu.ch_type != uint8_t(ch) || cu.bdpcm > 2 || cu.mrl_idx > 2 || cu.isp > 2 || cu.lfnst_idx > 2 || cu.mts_idx > 5 ||
+          cu.intra_dir > 70 || (!(cu.flags & CABAC_CU_FROM_DIR) && cu.pred_syntax > 60)) {
         status |= CABAC_SS_BAD_DESC;
         e.abort();
         return;
@@ -636,7 +637,7 @@ struct SliceParser {
         int mpm[6];
         intraMpms(n, mpm);
         if (cu.flags & CABAC_CU_MPM) {
-          cu.intra_dir = uint8_t(mpm[cu.pred_syntax]);
+          cu.intra_dir = uint8_t(mpm[cu.pred_syntax < 6 ? cu.pred_syntax : 5]);
         } else {
           for (int i = 1; i < 6; i++) {  // std::sort(mpm, mpm + 6)
             const int v = mpm[i];
@@ -704,7 +705,7 @@ struct SliceParser {
         const int cand[4] = {0, 50, 18, 1};  // PLANAR, VER, HOR, DC
         // the collocated luma PU: at the centre of the chroma block (PU::getCoLocatedLumaPU, unit_tools.cpp:603-613)
         const int lumaMode = e.lumaMap()[((((n.y + (h >> 1)) & 63) >> 2) << 4) + (((n.x + (w >> 1)) & 63) >> 2)];
-        const int m = cand[cu.pred_syntax - 1];
+        const int m = cand[(cu.pred_syntax - 1) & 3];
         cu.intra_dir = uint8_t(m == lumaMode ? 66 : m);  // VDIA_IDX replaces the candidate equal to the luma mode
       }
     }

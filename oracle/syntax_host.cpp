@@ -351,7 +351,8 @@ struct EmitEngine {
   }
   uint32_t residual(uint32_t idx, const cabac_tu_desc &d) {
     if (idx >= nTuIn || tusIn[idx].log2_w != d.log2_w || tusIn[idx].log2_h != d.log2_h || tusIn[idx].comp_id != d.comp_id ||
-        ((tusIn[idx].flags ^ d.flags) & uint8_t(~CABAC_TU_TS))) {
+        ((tusIn[idx].flags ^ d.flags) & uint8_t(~CABAC_TU_TS)) ||
+        ((tusIn[idx].flags & CABAC_TU_TS) && !(d.flags & (CABAC_TU_TS_ALLOWED | CABAC_TU_BDPCM)))) {
       bad = dead = true;
       return 0;
     }

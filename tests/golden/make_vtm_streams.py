@@ -52,6 +52,10 @@ RUNS = {
     "dqp_bdpcm_qp32": ("encoder_intra_vtm_qp32.cfg", ["--PerceptQPA=1", "--BDPCM=1"]),  # (QPA stays slice-level at QCIF size: BDPCM + ALF chroma only)
     # cu_qp_delta for real: CU-level delta-QP search, quantisation groups two subdivisions below the CTU
     "cudqp_qp32": ("encoder_intra_vtm_qp32.cfg", ["--MaxDeltaQP=1", "--MaxCuDQPSubdiv=2"]),
+    # cu_chroma_qp_offset: with offset lists in the PPS the VTM encoder cycles cu_chroma_qp_offset_idx over the chroma
+    # quantisation groups (EncCu::xCompressCU); a lower QP so that the loop-filter search may also pick CC-ALF
+    "cqpadj_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27", "--MaxCuChromaQpOffsetSubdiv=2", "--CbQpOffsetList=2,-2",
+                                                   "--CrQpOffsetList=-2,2", "--CbCrQpOffsetList=1,-1"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),

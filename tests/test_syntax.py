@@ -675,3 +675,49 @@ def test_gpu_encode_slices_wpp_rows(engine):
                 P(keep[7]), keep[7].size, None, 1 << 22, P(rows2), int(rows2[-1]), P(out), P(out2), P(sizes), P(bins), None, P(status))
     assert rc == -3 and int(status[int(rows2[k])]) & SS_BAD_DESC
     assert not np.delete(status, int(rows2[k])).any()
+
+
+@pytest.mark.gpu
+def test_gpu_encode_slices_survives_garbage_records(engine):
+    """Records with random bytes flipped (CU fields, TU shapes and flags, CTU parameters; coefficient offsets stay valid)
+    come back with status bits or with some legal stream - no hang, no write outside a slice's output region."""
+    lib = _host_lib()
+    items = [(t, g, sp) for t, g, sp in _gen_items(lib, reps=1)]
+    n = len(items)
+    params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+    data, off = [], [0]
+    for k, (tag, g, sp) in enumerate(items):
+        params[k] = (g["qp"], g["init_id"], g["flags"] | SUB_TERMINATE | SUB_ALIGN, 0)
+        sps[k] = sp
+        data.append(g["payload"])
+        off.append(off[-1] + g["payload"].size)
+    d = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps)
+    rec = _compact(d, n)
+    rows = engine.slice_rows(sps)
+    cap = np.concatenate([[data[k].size * 2 + 256] * int(rows[k + 1] - rows[k]) for k in range(n)])
+    out_off = np.concatenate([[0], np.cumsum(cap)]).astype(np.uint64)
+    rng = np.random.default_rng(77)
+    flagged = 0
+    for trial in range(6):
+        cus, tus, ctus = rec["cus"].copy(), rec["tus"].copy(), rec["ctus"].copy()
+        cb = cus.view(np.uint8).reshape(len(cus), -1)
+        for _ in range(40 << trial):
+            cb[rng.integers(len(cus)), rng.integers(cb.shape[1])] ^= np.uint8(1 << rng.integers(8))
+        tb = tus.view(np.uint8).reshape(len(tus), -1)
+        for _ in range(10 << trial):
+            tb[rng.integers(len(tus)), 8 + rng.integers(4)] ^= np.uint8(1 << rng.integers(8))  # log2_w, log2_h, comp_id, flags
+        ub = ctus.view(np.uint8).reshape(len(ctus), -1)
+        for _ in range(10 << trial):
+            ub[rng.integers(len(ctus)), rng.integers(ub.shape[1])] ^= np.uint8(1 << rng.integers(8))
+        w = engine.encode_slices_wpp(params, sps, cus, rec["cu_offsets"], tus, rec["tu_flags"], rec["tu_offsets"], ctus,
+                                     rec["ctu_offsets"], rec["coeffs"], out_off, raise_on_status=False)
+        assert (w["sizes"].astype(np.int64) <= cap).all()
+        flagged += int((w["status"] != 0).sum())
+    assert flagged > 0
+    # and the clean records still code to the payloads afterwards
+    w = engine.encode_slices_wpp(params, sps, rec["cus"], rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                                 rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off)
+    for k, (tag, g, sp) in enumerate(items):
+        a, b = int(rows[k]), int(rows[k + 1])
+        got = np.concatenate([w["out"][int(out_off[r]):int(out_off[r]) + int(w["sizes"][r])] for r in range(a, b)])
+        assert got.tobytes() == g["payload"].tobytes(), tag
