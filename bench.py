@@ -846,7 +846,8 @@ def leg_slice_decode(args, r):
                                      "(tests/golden/make_gen_slices.py), dense residuals (1.5 bins per coefficient "
                                      "position), replicated on the device; ground truth = the generating walk's records",
                             "points": rows_gen,
-                            "verified": "every copy: bin, CU and TU counts; slice 0 of every set: coefficient checksum"}
+                            "verified": "every copy: bin, CU and TU counts; slice 0 of every set: coefficient checksum; encode_* = "
+                                    "cabac_encode_slices_dev on the decoded records: every copy's bytes == the generated payload"}
     if cpu:
         leg["cpu_baseline"] = cpu
     return leg
@@ -906,7 +907,36 @@ def _slice_decode_generated(r):
         bins = int(bins_h.astype(np.int64).sum())
         ncoef = sum(int(base[j % len(base)][2][6]) for j in range(n))
         alg = off[-1] + 4 * ncoef + 16 * int(counts[:, 1].sum()) + 32 * int(counts[:, 0].sum())
+        # the writer direction on the records just decoded (compacted on the device): bytes == the generated payloads
+        from entropy_coding_b200.types import SUB_ALIGN
+        cu_cap, tu_cap = cap["cu"].astype(np.int64), cap["tu"].astype(np.int64)
+        cus2 = torch.cat([cus.view(-1, 32)[int(cu_cap[j]):int(cu_cap[j]) + int(counts[j, 0])] for j in range(n)]).contiguous()
+        tus2 = torch.cat([tus.view(-1, 16)[int(tu_cap[j]):int(tu_cap[j]) + int(counts[j, 1])] for j in range(n)]).contiguous()
+        tuf2 = torch.cat([tuf[int(tu_cap[j]):int(tu_cap[j]) + int(counts[j, 1])] for j in range(n)]).contiguous()
+        exact = lambda col: np.concatenate([[0], np.cumsum(counts[:, col].astype(np.int64))]).astype(np.uint64)  # noqa: E731
+        wp = params.copy()
+        wp["flags"] |= SUB_ALIGN
+        out_off = np.concatenate([[0], np.cumsum([(p.size + 79) // 16 * 16 for p in data])]).astype(np.uint64)
+        words = bins + 64 * n
+        w = {k: dev_bytes(dev, v) for k, v in (("p", wp), ("cuo", exact(0)), ("tuo", exact(1)), ("oo", out_off))}
+        cmd = torch.empty(words, dtype=torch.int32, device=dev)
+        out = torch.zeros(int(out_off[-1]), dtype=torch.uint8, device=dev)
+        osz = torch.zeros(n, dtype=torch.int32, device=dev)
+        wst = torch.zeros(n, dtype=torch.int32, device=dev)
+
+        def enc():
+            eng.encode_slices_dev(w["p"], d["sp"], n, cus2, w["cuo"], tus2, tuf2, w["tuo"], ctus, d["ctu"], co, cmd, words, out,
+                                  w["oo"], osz, wst)
+
+        te = _time_passes(stream, enc, warm=1, reps=2)
+        assert int(wst.abs().max()) == 0, "generated slices: writer status"
+        out_h, osz_h = out.cpu().numpy(), osz.cpu().numpy()
+        for j in range(n):
+            a = int(out_off[j])
+            assert out_h[a:a + int(osz_h[j])].tobytes() == data[j].tobytes(), f"generated slice copy {j}: written bytes"
+        del cus2, tus2, tuf2, cmd, out, osz, wst, w
         rows.append({"set": f"{n} x {int(sps[0]['pic_w'])}x{int(sps[0]['pic_h'])}", "substreams": n, "bins": bins,
+                     "encode_ms": te, "encode_mbins_s": bins * r["world"] / te / 1e3,
                      "bitstream_bytes": off[-1], "coefficients_out": ncoef, "decode_ms": t,
                      "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9,
                      "hbm_frac": alg / (t * 1e-3) / 1e9 / load_peaks()[0],

@@ -95,8 +95,7 @@ struct TuGeom {
 // turn into wild shared-memory indices: every kernel reads descriptors through loadDesc, which clamps the geometry
 // into range; the coding kernels report CABAC_SS_BAD_DESC for the substream (its output is then meaningless).
 __device__ __forceinline__ bool descBad(const cabac_tu_desc &d) {
-  // transform skip exists up to 32 x 32 (log2_transform_skip_max_size_minus2 <= 3): the tile holds no more
-  return d.log2_w > 6 || d.log2_h > 6 || d.comp_id > 2 || ((d.flags & CABAC_TU_TS) && (d.log2_w > 5 || d.log2_h > 5));
+  return d.log2_w > 6 || d.log2_h > 6 || d.comp_id > 2;
 }
 __device__ __forceinline__ cabac_tu_desc loadDesc(const cabac_tu_desc *__restrict__ p) {
   cabac_tu_desc d = *p;
@@ -104,7 +103,6 @@ __device__ __forceinline__ cabac_tu_desc loadDesc(const cabac_tu_desc *__restric
     d.log2_w = d.log2_w > 6 ? 6 : d.log2_w;
     d.log2_h = d.log2_h > 6 ? 6 : d.log2_h;
     d.comp_id = d.comp_id > 2 ? 2 : d.comp_id;
-    if (d.log2_w > 5 || d.log2_h > 5) d.flags &= uint8_t(~CABAC_TU_TS);
     d.flags |= 0x80;  // CABAC_TU_* uses bits 0-4; bit 7 marks the clamped copy inside the kernels
   }
   return d;
