@@ -50,6 +50,8 @@ struct cabac_handle {
   size_t epbTiles = 0;
   void *emitScratch = nullptr;  // cabac_encode_slices_dev: per-slice word counts / statuses, row-level arrays; grow-only
   size_t emitBytes = 0;
+  uint32_t *emitStage = nullptr;  // the walk's staging words (one bounded region per slice), grow-only
+  size_t emitStageWords = 0;
   bool trace = false;  // CABAC_B200_TRACE=1: per-chunk copy / compute completion times on stderr
   cudaEvent_t evT0 = nullptr;
   uint64_t *pinnedRanges = nullptr;  // [2 * kMaxChunks] ranges + [kMaxChunks + 1] u32 chunk starts
@@ -394,6 +396,7 @@ void cabac_destroy(cabac_handle *h) {
   if (h->pinnedRanges) cudaFreeHost(h->pinnedRanges);
   if (h->epbScratch) cudaFree(h->epbScratch);
   if (h->emitScratch) cudaFree(h->emitScratch);
+  if (h->emitStage) cudaFree(h->emitStage);
   if (h->pinDev) cudaFree(h->pinDev);
   cabac::freeSlicedWork(h->sliced);
   if (h->threadCtx) cudaFree(h->threadCtx);
@@ -668,9 +671,23 @@ static int encodeSliceRows(cabac_handle *h, const char *what, const cabac_substr
     return badArg(h, what);
   if (!n_sub) return CABAC_OK;
   DeviceGuard g(h->device);
-  // scratch: u64 cmdOffsets[nSub+1], rowCmdOff[nRows+1], rowTuOff[nRows+1] | sync[nRows] (16 B) |
+  // staging for the walk: one region per slice, bounded by its record counts (the totals come back first)
+  uint64_t tot[3] = {0, 0, 0};
+  CK(cudaMemcpyAsync(&tot[0], cu_offsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
+  CK(cudaMemcpyAsync(&tot[1], tu_offsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
+  CK(cudaMemcpyAsync(&tot[2], ctu_offsets + n_sub, 8, cudaMemcpyDeviceToHost, h->stream), "copy");
+  CK(cudaStreamSynchronize(h->stream), "sync");
+  const uint64_t stageWords = cabac::emitStageWords(tot[0], tot[1], tot[2], n_sub);
+  if (stageWords > h->emitStageWords) {
+    if (h->emitStage) cudaFree(h->emitStage);
+    h->emitStage = nullptr;
+    h->emitStageWords = 0;
+    CK(cudaMalloc(&h->emitStage, (stageWords + (stageWords >> 3)) * 4), "slice emit staging");
+    h->emitStageWords = stageWords + (stageWords >> 3);
+  }
+  // scratch: u64 cmdOffsets[nSub+1], stageOffsets[nSub+1], rowCmdOff[nRows+1], rowTuOff[nRows+1] | sync[nRows] (16 B) |
   //          u32 counts[nSub], emitStatus[nSub], rowSlice[nRows], rowParams[nRows] | ctx rows[nRows][379] (if ctx_in)
-  const size_t need = (n_sub + 1 + 2 * (n_rows + 1)) * 8 + n_rows * sizeof(cabac_wpp_sync) + (2 * n_sub + 2 * n_rows) * 4 +
+  const size_t need = (2 * (n_sub + 1) + 2 * (n_rows + 1)) * 8 + n_rows * sizeof(cabac_wpp_sync) + (2 * n_sub + 2 * n_rows) * 4 +
                       (ctx_in ? n_rows * CABAC_NUM_CTX * sizeof(cabac_ctx_model) : 0) + 64;
   if (need > h->emitBytes) {
     CK(cudaStreamSynchronize(h->stream), "sync");
@@ -682,7 +699,8 @@ static int encodeSliceRows(cabac_handle *h, const char *what, const cabac_substr
   }
   static_assert(sizeof(cabac_substream_params) == 4, "row parameter copies are packed as words");
   uint64_t *cmdOffsets = static_cast<uint64_t *>(h->emitScratch);
-  uint64_t *rowCmdOff = cmdOffsets + n_sub + 1, *rowTuOff = rowCmdOff + n_rows + 1;
+  uint64_t *stageOffsets = cmdOffsets + n_sub + 1;
+  uint64_t *rowCmdOff = stageOffsets + n_sub + 1, *rowTuOff = rowCmdOff + n_rows + 1;
   cabac_wpp_sync *rowSync = reinterpret_cast<cabac_wpp_sync *>(rowTuOff + n_rows + 1);
   uint32_t *counts = reinterpret_cast<uint32_t *>(rowSync + n_rows), *emitStatus = counts + n_sub;
   uint32_t *rowSlice = emitStatus + n_sub;
@@ -691,10 +709,11 @@ static int encodeSliceRows(cabac_handle *h, const char *what, const cabac_substr
   cabac::Sched sc;
   CK(schedFor(h, n_sub, sc), "scheduler scratch");
   CK(cabac::launchEmitSlices(h->stream, h->device, sc, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets,
-                             ctus, ctu_offsets, ctx_in, cmd_scratch, cmd_scratch_words, counts, emitStatus, cmdOffsets,
+                             ctus, ctu_offsets, ctx_in, h->emitStage, stageOffsets, cmd_scratch, cmd_scratch_words, counts,
+                             emitStatus, cmdOffsets,
                              row_offsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn),
      "emit_slice kernels");
-  h->launches += 7;
+  h->launches += 8;
   // a slice whose commands did not fit (CABAC_SS_CAPACITY) has offsets past the scratch: the encoder must not read
   // them, so such a call stops here with every slice's status written
   CK(cudaMemsetAsync(out_sizes, 0, n_rows * 4, h->stream), "memset");

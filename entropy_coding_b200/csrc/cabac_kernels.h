@@ -59,10 +59,11 @@ cudaError_t launchEmitSlices(cudaStream_t s, int device, const Sched &sc, const 
                              const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
                              const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
                              const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,
-                             const cabac_ctx_model *ctxIn, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
-                             uint32_t *emitStatus, uint64_t *cmdOffsets, const uint64_t *rowOffsets, uint64_t *rowCmdOff,
-                             uint64_t *rowTuOff, cabac_wpp_sync *rowSync, cabac_substream_params *rowParams,
-                             uint32_t *rowSlice, cabac_ctx_model *rowCtxIn);
+                             const cabac_ctx_model *ctxIn, uint32_t *stage, uint64_t *stageOffsets, uint32_t *cmds,
+                             uint64_t capWords, uint32_t *counts, uint32_t *emitStatus, uint64_t *cmdOffsets,
+                             const uint64_t *rowOffsets, uint64_t *rowCmdOff, uint64_t *rowTuOff, cabac_wpp_sync *rowSync,
+                             cabac_substream_params *rowParams, uint32_t *rowSlice, cabac_ctx_model *rowCtxIn);
+uint64_t emitStageWords(uint64_t nCu, uint64_t nTu, uint64_t nCtu, uint64_t nSub);
 cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, const uint32_t *rowSlice, size_t nRows);
 cudaError_t launchEncodePrepare(cudaStream_t s, int device, const Sched &sc, const cabac_tu_desc *tus,
                                 const uint64_t *tuOffsets, size_t nSub, const int32_t *coeffs,

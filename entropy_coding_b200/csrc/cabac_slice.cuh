@@ -355,13 +355,14 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
 // slice, two passes (count, then write at the scanned offsets).
 // ---------------------------------------------------------------------------
 // Row substreams of the slice being written (WPP: one per CTU row; otherwise the slice itself): what the stream
-// encoder's wavefront mode takes per substream.  All nullptr in the count pass.
+// encoder's wavefront mode takes per substream.  cmdOff is relative to the slice's first word until
+// emit_compact_kernel has placed the slice.
 struct SliceRowOut {
   uint64_t *cmdOff;      // [row]: first command word (absolute in the command buffer)
   uint64_t *tuOff;       // [row]: first TU (absolute in tus)
   cabac_wpp_sync *sync;  // [row]: predecessor and the hand-over point (after the row's first CTU)
   uint32_t base, count;  // the slice's rows are [base, base + count)
-  uint64_t cmdBase, tuBase;
+  uint64_t tuBase;
   bool allow;            // the caller described the rows (cabac_encode_slices_wpp): WPP slices can be written
 };
 
@@ -373,19 +374,21 @@ struct SliceEmitEngine {
   const uint8_t *tuFlagsIn;
   const cabac_ctu_desc *ctusIn;
   uint32_t nCuIn, nTuIn, nCtuIn;
-  uint32_t *cmds;  // nullptr: count only
+  uint32_t *cmds;  // the slice's staging region (capWords words: the bound of emitBound())
+  uint32_t capWords;
   SliceRowOut ro;
   uint32_t n = 0, row = 0, rowStartN = 0, rowStartTu = 0, tuSeen = 0;
   bool dead = false, bad = false;
 
   __device__ __forceinline__ SliceEmitEngine(SliceLines &l, const cabac_cu_desc *c, uint32_t nc, const cabac_tu_desc *t,
                                              const uint8_t *tf, uint32_t nt, const cabac_ctu_desc *ct, uint32_t nct,
-                                             uint32_t *out, const SliceRowOut &r)
-      : ln(l), cusIn(c), tusIn(t), tuFlagsIn(tf), ctusIn(ct), nCuIn(nc), nTuIn(nt), nCtuIn(nct), cmds(out), ro(r) {}
+                                             uint32_t *out, uint32_t cap, const SliceRowOut &r)
+      : ln(l), cusIn(c), tusIn(t), tuFlagsIn(tf), ctusIn(ct), nCuIn(nc), nTuIn(nt), nCtuIn(nct), cmds(out), capWords(cap),
+        ro(r) {}
   __device__ __forceinline__ bool rows() const { return ro.allow; }
   __device__ __forceinline__ static int laneId() { return int(threadIdx.x & 31u); }
   __device__ __forceinline__ void push(uint32_t w) {
-    if (cmds && laneId() == 0) cmds[n] = w;
+    if (laneId() == 0 && n < capWords) cmds[n] = w;
     n++;
   }
   __device__ __forceinline__ cabac_cu_desc getCu(uint32_t i) {
@@ -465,7 +468,7 @@ struct SliceEmitEngine {
   __device__ __forceinline__ void putCtu(uint32_t, const cabac_ctu_desc &) {}
   // WPP: the contexts are handed to the next row after the row's first CTU (EncSlice.cpp:2085-2089) ...
   __device__ __forceinline__ void saveRowContexts() {
-    if (ro.sync && laneId() == 0 && row < ro.count) {
+    if (laneId() == 0 && row < ro.count) {
       ro.sync[ro.base + row].sync_cmds = n - rowStartN;
       ro.sync[ro.base + row].sync_tus = tuSeen - rowStartTu;
     }
@@ -481,8 +484,8 @@ struct SliceEmitEngine {
       bad = dead = true;
       return;
     }
-    if (ro.cmdOff && laneId() == 0) {
-      ro.cmdOff[ro.base + row] = ro.cmdBase + n;
+    if (laneId() == 0) {
+      ro.cmdOff[ro.base + row] = n;
       ro.tuOff[ro.base + row] = ro.tuBase + tuSeen;
     }
   }
@@ -492,8 +495,9 @@ struct SliceEmitEngine {
 
 constexpr int EMIT_WARPS_PER_BLOCK = 4;
 
-// cmdOffsets == nullptr: count pass (counts[sub] = words); otherwise write pass into cmds at cmdOffsets[sub], which
-// also fills the row-level arrays the stream encoder takes (one row per slice; one per CTU row of a WPP slice).
+// One walk per slice into its staging region (stageOffsets: exclusive scan of emitBound(), the most words a slice of
+// that many CUs / TUs / CTUs can need), with the row-level arrays the stream encoder takes (one row per slice; one
+// per CTU row of a WPP slice); emit_compact_kernel then packs the slices at the scanned word counts.
 struct EmitRowArrays {
   const uint64_t *rowOffsets;  // [nSub + 1] or nullptr: every slice is one row (WPP slices refused)
   uint64_t *cmdOff, *tuOff;    // [nRows + 1]
@@ -503,15 +507,30 @@ struct EmitRowArrays {
   cabac_ctx_model *ctxIn;      // [nRows][379] or nullptr
 };
 
+// Words per CU: <= 12 for the split flags of its share of the tree, 14 luma / 7 chroma prediction syntax, 16
+// cu_qp_delta, 6 chroma QP offset, 13 cbf / joint flags, 12 TU markers, 6 LFNST / MTS; per CTU: SAO 3 x (4 x 31
+// offset bins + 7) + ALF / CC-ALF 35.
+__host__ __device__ inline uint64_t emitBound(uint64_t nCu, uint64_t nTu, uint64_t nCtu) {
+  return 80 * nCu + nTu + 450 * nCtu + 64;
+}
+
+__global__ void emit_bound_kernel(const uint64_t *__restrict__ cuOffsets, const uint64_t *__restrict__ tuOffsets,
+                                  const uint64_t *__restrict__ ctuOffsets, size_t n, uint32_t *__restrict__ bound) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const uint64_t b = emitBound(cuOffsets[i + 1] - cuOffsets[i], tuOffsets[i + 1] - tuOffsets[i], ctuOffsets[i + 1] - ctuOffsets[i]);
+    bound[i] = b > 0xFFFFFFFFull ? 0xFFFFFFFFu : uint32_t(b);
+  }
+}
+
 __global__ void __launch_bounds__(EMIT_WARPS_PER_BLOCK * 32)
 emit_slice_kernel(const cabac_substream_params *__restrict__ params, const cabac_slice_params *__restrict__ sliceParams,
                   size_t nSub, const cabac_cu_desc *__restrict__ cus, const uint64_t *__restrict__ cuOffsets,
                   const cabac_tu_desc *__restrict__ tus, const uint8_t *__restrict__ tuFlags,
                   const uint64_t *__restrict__ tuOffsets, const cabac_ctu_desc *__restrict__ ctus,
                   const uint64_t *__restrict__ ctuOffsets, const cabac_ctx_model *__restrict__ ctxIn,
-                  uint32_t *__restrict__ cmds, const uint64_t *__restrict__ cmdOffsets, uint64_t capWords,
-                  uint32_t *__restrict__ counts, uint32_t *__restrict__ emitStatus, EmitRowArrays ra,
-                  const uint32_t *__restrict__ order, uint32_t *cursor) {
+                  uint32_t *__restrict__ stage, const uint64_t *__restrict__ stageOffsets, uint32_t *__restrict__ counts,
+                  uint32_t *__restrict__ emitStatus, EmitRowArrays ra, const uint32_t *__restrict__ order,
+                  uint32_t *cursor) {
   using Emitter = cabac_syntax::SliceParser<SliceEmitEngine>;
   __shared__ SliceLines lines[EMIT_WARPS_PER_BLOCK];
   __shared__ __align__(16) unsigned char engBuf[EMIT_WARPS_PER_BLOCK][(sizeof(SliceEmitEngine) + 15) & ~size_t(15)];
@@ -521,41 +540,33 @@ emit_slice_kernel(const cabac_substream_params *__restrict__ params, const cabac
   while (nextSubstream(order, cursor, nSub, lane, sub)) {  // longest slice first (by CU count), warps pull from a cursor
     const cabac_slice_params sp = sliceParams[sub];
     const uint64_t cu0 = cuOffsets[sub], tu0 = tuOffsets[sub], ctu0 = ctuOffsets[sub];
-    const bool write = cmdOffsets != nullptr;
-    const bool over = write && cmdOffsets[sub + 1] > capWords;
-    // a slice the count pass refused owns no words: walk it again without writing (same status)
-    const bool empty = write && cmdOffsets[sub + 1] == cmdOffsets[sub];
-    uint32_t *dst = (write && !over && !empty) ? cmds + cmdOffsets[sub] : nullptr;
     SliceRowOut ro{};
     ro.allow = ra.rowOffsets != nullptr;
     ro.base = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub]) : uint32_t(sub);
     ro.count = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub + 1] - ra.rowOffsets[sub]) : 1u;
     const uint32_t ctuRows = (sp.y1 - sp.y0 + (1u << sp.log2_ctu) - 1) >> sp.log2_ctu;
     const bool rowsOk = ro.count == ((sp.tools & CABAC_SL_WPP) ? ctuRows : 1u);
-    if (write) {
-      ro.cmdOff = ra.cmdOff;
-      ro.tuOff = ra.tuOff;
-      ro.sync = ra.sync;
-      ro.cmdBase = cmdOffsets[sub];
-      ro.tuBase = tu0;
-      const cabac_substream_params p = params[sub];
-      for (uint32_t r = lane; r < ro.count; r += 32) {  // defaults; the walk overwrites offsets and hand-over points
-        cabac_substream_params pr = p;
-        if (r) pr.flags = uint8_t(pr.flags & ~CABAC_SUB_CTX_IN);  // rows below the first start from their predecessor
-        ra.params[ro.base + r] = pr;
-        ra.slice[ro.base + r] = uint32_t(sub);
-        ra.sync[ro.base + r] = cabac_wpp_sync{r ? ro.base + r - 1 : CABAC_WPP_NONE, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u};
-        ra.cmdOff[ro.base + r] = ro.cmdBase;  // a refused slice: empty rows
-        ra.tuOff[ro.base + r] = tu0;
-      }
-      if (ra.ctxIn && ctxIn && (p.flags & CABAC_SUB_CTX_IN))
-        for (int k = lane; k < CABAC_NUM_CTX; k += 32) ra.ctxIn[size_t(ro.base) * CABAC_NUM_CTX + k] = ctxIn[sub * CABAC_NUM_CTX + k];
+    ro.cmdOff = ra.cmdOff;
+    ro.tuOff = ra.tuOff;
+    ro.sync = ra.sync;
+    ro.tuBase = tu0;
+    const cabac_substream_params p = params[sub];
+    for (uint32_t r = lane; r < ro.count; r += 32) {  // defaults; the walk overwrites offsets and hand-over points
+      cabac_substream_params pr = p;
+      if (r) pr.flags = uint8_t(pr.flags & ~CABAC_SUB_CTX_IN);  // rows below the first start from their predecessor
+      ra.params[ro.base + r] = pr;
+      ra.slice[ro.base + r] = uint32_t(sub);
+      ra.sync[ro.base + r] = cabac_wpp_sync{r ? ro.base + r - 1 : CABAC_WPP_NONE, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u};
+      ra.cmdOff[ro.base + r] = 0;
+      ra.tuOff[ro.base + r] = tu0;
     }
+    if (ra.ctxIn && ctxIn && (p.flags & CABAC_SUB_CTX_IN))
+      for (int k = lane; k < CABAC_NUM_CTX; k += 32) ra.ctxIn[size_t(ro.base) * CABAC_NUM_CTX + k] = ctxIn[sub * CABAC_NUM_CTX + k];
     __syncwarp();
+    const uint64_t room = stageOffsets[sub + 1] - stageOffsets[sub];
     SliceEmitEngine &eng = *new (engBuf[wib]) SliceEmitEngine(
         lines[wib], cus + cu0, uint32_t(cuOffsets[sub + 1] - cu0), tus + tu0, tuFlags + tu0, uint32_t(tuOffsets[sub + 1] - tu0),
-        ctus + ctu0, uint32_t(ctuOffsets[sub + 1] - ctu0), dst, ro);
-    if (!dst) eng.ro.cmdOff = nullptr, eng.ro.tuOff = nullptr, eng.ro.sync = nullptr;
+        ctus + ctu0, uint32_t(ctuOffsets[sub + 1] - ctu0), stage + stageOffsets[sub], uint32_t(room), ro);
     __syncwarp();
     Emitter &ps = *new (psBuf[wib]) Emitter(eng, sp, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, ~uint64_t(0), 0);
     __syncwarp();
@@ -566,19 +577,40 @@ emit_slice_kernel(const cabac_substream_params *__restrict__ params, const cabac
       st |= ro.allow ? CABAC_SS_BAD_DESC : CABAC_SS_UNSUPPORTED;  // rows not described: a WPP slice cannot be written
     else
       ps.run(false);  // the terminating bin and finish() are the stream encoder's (CABAC_SUB_TERMINATE)
-    st |= ps.status | (eng.bad ? uint32_t(CABAC_SS_BAD_DESC) : 0u) | (over ? uint32_t(CABAC_SS_CAPACITY) : 0u);
+    st |= ps.status | (eng.bad ? uint32_t(CABAC_SS_BAD_DESC) : 0u) | (eng.n > eng.capWords ? uint32_t(CABAC_SS_CAPACITY) : 0u);
     if (!st && (ps.nCu != eng.nCuIn || ps.nTu != eng.nTuIn || eng.row + 1 != ro.count)) st |= CABAC_SS_BAD_DESC;  // left-overs
     __syncwarp();
+    if (st)  // a refused slice codes nothing (its status says why): empty rows
+      for (uint32_t r = lane; r < ro.count; r += 32) ra.cmdOff[ro.base + r] = 0, ra.tuOff[ro.base + r] = tu0;
     if (lane == 0) {
-      if (!write) counts[sub] = st ? 0u : eng.n;  // a refused slice codes nothing (its status says why)
+      counts[sub] = st ? 0u : eng.n;
       emitStatus[sub] = st;
-      if (write && sub + 1 == nSub) {
-        const uint32_t nRows = ro.base + ro.count;
-        ra.cmdOff[nRows] = cmdOffsets[nSub];
-        ra.tuOff[nRows] = tuOffsets[nSub];
-      }
     }
     __syncwarp();
+  }
+}
+
+// Packs the staged slices at cmdOffsets (the scan of their word counts), makes the rows' command offsets absolute
+// and closes the row arrays.  A slice that does not fit the caller's scratch is flagged and not copied.
+__global__ void __launch_bounds__(256)
+emit_compact_kernel(const uint32_t *__restrict__ stage, const uint64_t *__restrict__ stageOffsets,
+                    const uint64_t *__restrict__ cmdOffsets, size_t nSub, uint64_t capWords, uint32_t *__restrict__ cmds,
+                    uint32_t *__restrict__ emitStatus, EmitRowArrays ra, const uint64_t *__restrict__ tuOffsets) {
+  for (size_t sub = blockIdx.x; sub < nSub; sub += gridDim.x) {
+    const uint64_t c0 = cmdOffsets[sub], c1 = cmdOffsets[sub + 1];
+    const uint32_t base = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub]) : uint32_t(sub);
+    const uint32_t count = ra.rowOffsets ? uint32_t(ra.rowOffsets[sub + 1] - ra.rowOffsets[sub]) : 1u;
+    for (uint32_t r = threadIdx.x; r < count; r += blockDim.x) ra.cmdOff[base + r] += c0;
+    if (threadIdx.x == 0 && sub + 1 == nSub) {
+      ra.cmdOff[base + count] = c1;
+      ra.tuOff[base + count] = tuOffsets[nSub];
+    }
+    if (c1 > capWords) {
+      if (threadIdx.x == 0) emitStatus[sub] |= CABAC_SS_CAPACITY;
+      continue;
+    }
+    const uint32_t *src = stage + stageOffsets[sub];
+    for (uint64_t i = threadIdx.x; i < c1 - c0; i += blockDim.x) cmds[c0 + i] = src[i];
   }
 }
 
@@ -594,28 +626,33 @@ cudaError_t launchEmitSlices(cudaStream_t s, int device, const Sched &sc, const 
                              const cabac_slice_params *sliceParams, size_t nSub, const cabac_cu_desc *cus,
                              const uint64_t *cuOffsets, const cabac_tu_desc *tus, const uint8_t *tuFlags,
                              const uint64_t *tuOffsets, const cabac_ctu_desc *ctus, const uint64_t *ctuOffsets,
-                             const cabac_ctx_model *ctxIn, uint32_t *cmds, uint64_t capWords, uint32_t *counts,
-                             uint32_t *emitStatus, uint64_t *cmdOffsets, const uint64_t *rowOffsets, uint64_t *rowCmdOff,
-                             uint64_t *rowTuOff, cabac_wpp_sync *rowSync, cabac_substream_params *rowParams,
-                             uint32_t *rowSlice, cabac_ctx_model *rowCtxIn) {
+                             const cabac_ctx_model *ctxIn, uint32_t *stage, uint64_t *stageOffsets, uint32_t *cmds,
+                             uint64_t capWords, uint32_t *counts, uint32_t *emitStatus, uint64_t *cmdOffsets,
+                             const uint64_t *rowOffsets, uint64_t *rowCmdOff, uint64_t *rowTuOff, cabac_wpp_sync *rowSync,
+                             cabac_substream_params *rowParams, uint32_t *rowSlice, cabac_ctx_model *rowCtxIn) {
   if (nSub == 0) return cudaSuccess;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   const size_t want = (nSub + EMIT_WARPS_PER_BLOCK - 1) / EMIT_WARPS_PER_BLOCK, cap = size_t(sms) * 8;
   const int blocks = int(want < cap ? want : cap);
   const EmitRowArrays ra{rowOffsets, rowCmdOff, rowTuOff, rowSync, rowParams, rowSlice, rowCtxIn};
+  emit_bound_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cuOffsets, tuOffsets, ctuOffsets, nSub, counts);
+  entry_points_kernel<<<1, 1024, 0, s>>>(counts, nullptr, nSub, stageOffsets);
   cost_bytes_kernel<<<costGrid(nSub, 256), 256, 0, s>>>(cuOffsets, nSub, sc.cost);  // CUs per slice: the walk's length
   cudaError_t e = launchOrder(s, sc, nSub);
   if (e != cudaSuccess) return e;
   emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
-                                                                tuOffsets, ctus, ctuOffsets, ctxIn, nullptr, nullptr, capWords,
-                                                                counts, emitStatus, ra, sc.order, sc.cursor);
+                                                                tuOffsets, ctus, ctuOffsets, ctxIn, stage, stageOffsets, counts,
+                                                                emitStatus, ra, sc.order, sc.cursor);
   entry_points_kernel<<<1, 1024, 0, s>>>(counts, nullptr, nSub, cmdOffsets);
-  if ((e = launchOrder(s, sc, nSub)) != cudaSuccess) return e;  // same order, cursor back to 0
-  emit_slice_kernel<<<blocks, EMIT_WARPS_PER_BLOCK * 32, 0, s>>>(params, sliceParams, nSub, cus, cuOffsets, tus, tuFlags,
-                                                                tuOffsets, ctus, ctuOffsets, ctxIn, cmds, cmdOffsets, capWords,
-                                                                counts, emitStatus, ra, sc.order, sc.cursor);
+  const size_t cb = nSub < size_t(sms) * 8 ? nSub : size_t(sms) * 8;
+  emit_compact_kernel<<<unsigned(cb), 256, 0, s>>>(stage, stageOffsets, cmdOffsets, nSub, capWords, cmds, emitStatus, ra,
+                                                  tuOffsets);
   return cudaGetLastError();
+}
+
+uint64_t emitStageWords(uint64_t nCu, uint64_t nTu, uint64_t nCtu, uint64_t nSub) {
+  return emitBound(nCu, nTu, nCtu) + 64 * nSub;
 }
 
 cudaError_t launchOrStatus(cudaStream_t s, uint32_t *status, const uint32_t *extra, const uint32_t *rowSlice, size_t nRows) {
