@@ -344,9 +344,8 @@ class CabacEngine:
         cu_offsets, tu_offsets = _np(cu_offsets, np.uint64), _np(tu_offsets, np.uint64)
         ctu_offsets, out_offsets = _np(ctu_offsets, np.uint64), _np(out_offsets, np.uint64)
         n = len(params)
-        if cmd_words is None:
-            area = (sp["x1"].astype(np.int64) - sp["x0"]) * (sp["y1"].astype(np.int64) - sp["y0"])
-            cmd_words = int(area.sum()) * 4 + 64 * n
+        if cmd_words is None:  # the bound the library itself stages with
+            cmd_words = 80 * len(cus) + len(tus) + 450 * len(ctus) + 64 * n + 64
         out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
         sizes, bins, status = np.zeros(n, np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
         ctx_in = _np(ctx_in, CTX_DT)
@@ -380,9 +379,8 @@ class CabacEngine:
         row_offsets = self.slice_rows(sp)
         n_rows = int(row_offsets[-1])
         assert len(out_offsets) == n_rows + 1, "out_offsets is per row substream"
-        if cmd_words is None:
-            area = (sp["x1"].astype(np.int64) - sp["x0"]) * (sp["y1"].astype(np.int64) - sp["y0"])
-            cmd_words = int(area.sum()) * 4 + 64 * n
+        if cmd_words is None:  # the bound the library itself stages with
+            cmd_words = 80 * len(cus) + len(tus) + 450 * len(ctus) + 64 * n + 64
         out = np.zeros(int(out_offsets[-1]) if n else 0, np.uint8)
         sizes, bins, status = np.zeros(n_rows, np.uint32), np.zeros(n_rows, np.uint32), np.zeros(n_rows, np.uint32)
         ctx_in = _np(ctx_in, CTX_DT)

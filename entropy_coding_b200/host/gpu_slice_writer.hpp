@@ -194,8 +194,8 @@ class GpuSliceWriter {
       const uint64_t area = uint64_t(s.x1 - s.x0) * (s.y1 - s.y0), rows = rowOff_[i + 1] - rowOff_[i];
       for (uint64_t r = rowOff_[i]; r < rowOff_[i + 1]; r++)  // <= 20 bits per coefficient + syntax
         rowCap.push_back(rowCap.back() + area / rows / 4 + rowCoeffs_[r] * 3 + 256);
-      words += area * 4 + 64;
     }
+    words = 80 * cus_.size() + tus_.size() + 450 * ctus_.size() + 64 * n + 64;  // the library's own staging bound
     rows_.resize(rowCap.back());
     sizes_.resize(nRows);
     rowBins_.resize(nRows);

@@ -864,16 +864,17 @@ int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_o
  * prediction syntax, TUs in coding order with coeff_offset absolute in `coeffs` and tu_flags (CABAC_TUR_*,
  * from cabac_decode_slices or from cabac_estimate_residual on the same TUs), one CTU record per CTU.
  * Here the offsets are exact: slice i owns cus[cu_offsets[i] .. cu_offsets[i+1]) etc.
- * Two kernels walk the partitioning per slice (one warp each) and write the slice's BinEncIf call sequence
- * as command words into cmd_scratch (cmd_scratch_words uint32 available; about 1.2 words per bin outside
- * residuals - 4 words per luma sample of the rectangle always suffice); the stream encoder
+ * One warp per slice walks the partitioning and writes the slice's BinEncIf call sequence as command words
+ * (into handle-owned staging sized by the record counts: 80 words per CU + 1 per TU + 450 per CTU), a copy
+ * packs the slices into cmd_scratch (cmd_scratch_words uint32 available; the packed stream needs one word per
+ * bin outside the residuals plus one per TU - num_bins of the slices always suffices); the stream encoder
  * (cabac_encode_stream_dev) then codes them, terminating bin and finish() included
  * (params[i].flags: CABAC_SUB_TERMINATE | CABAC_SUB_ALIGN as for every slice payload).
  * status[i]: CABAC_SS_* of the stream encoder, plus CABAC_SS_UNSUPPORTED (see cabac_decode_slices; also
  * CABAC_SL_WPP slices, whose rows are separate substreams: cabac_encode_slices_wpp), CABAC_SS_BAD_DESC (records that do
  * not describe a legal partitioning of the rectangle, or left-over records) and CABAC_SS_CAPACITY
  * (cmd_scratch too small: nothing is encoded and the call returns CABAC_ERR_SUBSTREAM).
- * The _dev form synchronises the stream once (it reads the total command count back).              */
+ * The _dev form synchronises the stream twice (it reads the record totals and the total command count back). */
 int cabac_encode_slices_dev(cabac_handle *h, const cabac_substream_params *params,
                             const cabac_slice_params *slice_params, size_t n_sub,
                             const cabac_cu_desc *cus, const uint64_t *cu_offsets,
