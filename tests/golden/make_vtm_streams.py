@@ -56,6 +56,9 @@ RUNS = {
     # quantisation groups (EncCu::xCompressCU); a lower QP so that the loop-filter search may also pick CC-ALF
     "cqpadj_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27", "--MaxCuChromaQpOffsetSubdiv=2", "--CbQpOffsetList=2,-2",
                                                    "--CrQpOffsetList=-2,2", "--CbCrQpOffsetList=1,-1"]),
+    # CC-ALF: a clip whose chroma texture follows the luma texture (synth_qcif(chroma_detail=True)), two frames
+    "ccalf_qp37": ("encoder_intra_vtm_qp32.cfg", ["-q", "37", "-f", "2"]),
+    "ccalf_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27", "-f", "2"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),
@@ -65,7 +68,7 @@ RUNS = {
 }
 
 
-def synth_qcif(seed=2024, w=176, h=144, frames=10) -> bytes:
+def synth_qcif(seed=2024, w=176, h=144, frames=10, chroma_detail=False) -> bytes:
     """Seeded clip with gradients, a moving blob, a checker patch (sharp edges: transform skip) and
     noise, so that the intra search uses a mix of tools."""
     rng = np.random.default_rng(seed)
@@ -80,8 +83,14 @@ def synth_qcif(seed=2024, w=176, h=144, frames=10) -> bytes:
         y[100:130, 20:90] = 30 + 180 * (((xx[100:130, 20:90].astype(int) // 3) +
                                           (yy[100:130, 20:90].astype(int) // 5)) % 2)
         y += 6 * tex + rng.normal(0, 2, (h, w))
+        if chroma_detail:  # fine luma structure the chroma planes share (below)
+            y += 25 * np.sin((xx + 3 * f) / 2.5) * np.cos(yy / 3.0)
         u = 128 + 30 * np.sin(xx[::2, ::2] / 20.0 + f / 5.0) + rng.normal(0, 1.5, (h // 2, w // 2))
         v = 128 + 30 * np.cos(yy[::2, ::2] / 17.0) + 20 * (xx[::2, ::2] > 88) + rng.normal(0, 1.5, (h // 2, w // 2))
+        if chroma_detail:  # chroma texture that follows the luma texture: what the cross-component ALF predicts
+            d = (6 * tex + 40 * np.sin((xx + 3 * f) / 2.5) * np.cos(yy / 3.0))[::2, ::2]
+            u = u + 0.8 * d
+            v = v - 0.6 * d
         for p in (y, u, v):
             out += np.clip(np.rint(p), 0, 255).astype(np.uint8).tobytes()
     return bytes(out)
@@ -179,13 +188,16 @@ def main():
     open(clip, "wb").write(synth_qcif())
     clip_wqvga = os.path.join(a.work, "synth_wqvga.yuv")
     open(clip_wqvga, "wb").write(synth_qcif(seed=2025, w=416, h=240, frames=1))
+    clip_cd = os.path.join(a.work, "synth_qcif_cd.yuv")
+    open(clip_cd, "wb").write(synth_qcif(seed=2026, chroma_detail=True))
     exe = a.exe or (None if a.skip_encode else build(a.work, True))
     for name in a.only.split(","):
         cfg, extra = RUNS[name]
         rundir = os.path.join(a.work, name)
         cl = cmdline_for(name)
         if not a.skip_encode:
-            encode(exe, rundir, clip_wqvga if name.startswith("wqvga") else clip, cfg, extra, True, cl)
+            encode(exe, rundir, clip_wqvga if name.startswith("wqvga") else clip_cd if name.startswith("ccalf") else clip,
+                   cfg, extra, True, cl)
         to_fixture(name, rundir, cfg, extra, cl)
     if a.verify_unpatched:
         orig = build(a.work, False)

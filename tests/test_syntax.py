@@ -721,3 +721,32 @@ def test_gpu_encode_slices_survives_garbage_records(engine):
         a, b = int(rows[k]), int(rows[k + 1])
         got = np.concatenate([w["out"][int(out_off[r]):int(out_off[r]) + int(w["sizes"][r])] for r in range(a, b)])
         assert got.tobytes() == g["payload"].tobytes(), tag
+
+
+@pytest.mark.gpu
+def test_gpu_slice_round_trip_at_1080p(engine):
+    """BASELINE configs[2]'s substream shape at f2 level: whole 1920x1080 pictures as one slice each (3.0 Mbins per slice,
+    tests/golden/gen_slices.npz) - parsed from the bytes, written back from the records: the same bytes, bins, contexts."""
+    z = np.load(os.path.join(HERE, "golden", "gen_slices.npz"))
+    n = 2
+    params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
+    data, off = [], [0]
+    for k in range(n):
+        meta = z[f"hd{k}_meta"]
+        params[k] = (int(meta[0]), int(meta[1]), int(meta[2]) | SUB_TERMINATE | SUB_ALIGN, 0)
+        sps[k] = z[f"hd{k}_slice"].view(SLICE_DT)[0]
+        data.append(z[f"hd{k}_payload"])
+        off.append(off[-1] + data[-1].size)
+    assert int(sps[0]["pic_w"]) == 1920 and int(sps[0]["pic_h"]) == 1080
+    d = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, want_ctx=True)
+    for k in range(n):
+        meta = z[f"hd{k}_meta"]
+        assert int(d["status"][k]) == 0 and int(d["num_bins"][k]) == int(meta[3]) and int(d["counts"][k][0]) == int(meta[4])
+    rec = _compact(d, n)
+    out_off = np.concatenate([[0], np.cumsum([p.size + 256 for p in data])]).astype(np.uint64)
+    w = engine.encode_slices(params, sps, _from_dir(rec["cus"]), rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
+                             rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off, want_ctx=True)
+    for k in range(n):
+        got = w["out"][int(out_off[k]):int(out_off[k]) + int(w["sizes"][k])]
+        assert got.tobytes() == data[k].tobytes(), f"1080p slice {k}"
+        assert int(w["num_bins"][k]) == int(d["num_bins"][k]) and w["ctx_out"][k].tobytes() == d["ctx_out"][k].tobytes()
