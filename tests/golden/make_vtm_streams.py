@@ -59,6 +59,8 @@ RUNS = {
     # CC-ALF: a clip whose chroma texture follows the luma texture (synth_qcif(chroma_detail=True)), two frames
     "ccalf_qp37": ("encoder_intra_vtm_qp32.cfg", ["-q", "37", "-f", "2"]),
     "ccalf_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27", "-f", "2"]),
+    # chroma BDPCM: a clip with a checker patch in the chroma planes (synth_qcif(chroma_checker=True))
+    "cbdpcm_qp27": ("encoder_intra_vtm_qp32.cfg", ["-q", "27", "-f", "2", "--BDPCM=1"]),
     "qp51": ("encoder_intra_vtm_qp51.cfg", []),
     "qp32": ("encoder_intra_vtm_qp32.cfg", []),
     "qp0": ("encoder_intra_vtm_qp0.cfg", []),
@@ -68,7 +70,7 @@ RUNS = {
 }
 
 
-def synth_qcif(seed=2024, w=176, h=144, frames=10, chroma_detail=False) -> bytes:
+def synth_qcif(seed=2024, w=176, h=144, frames=10, chroma_detail=False, chroma_checker=False) -> bytes:
     """Seeded clip with gradients, a moving blob, a checker patch (sharp edges: transform skip) and
     noise, so that the intra search uses a mix of tools."""
     rng = np.random.default_rng(seed)
@@ -91,6 +93,10 @@ def synth_qcif(seed=2024, w=176, h=144, frames=10, chroma_detail=False) -> bytes
             d = (6 * tex + 40 * np.sin((xx + 3 * f) / 2.5) * np.cos(yy / 3.0))[::2, ::2]
             u = u + 0.8 * d
             v = v - 0.6 * d
+        if chroma_checker:  # sharp horizontal / vertical chroma edges: what chroma BDPCM / transform skip are for
+            cxx, cyy = xx[::2, ::2].astype(int), yy[::2, ::2].astype(int)
+            u[8:40, 8:56] = 60 + 140 * (((cxx[8:40, 8:56] // 4) + (cyy[8:40, 8:56] // 3)) % 2)
+            v[30:64, 40:80] = 200 - 150 * ((cxx[30:64, 40:80] // 5) % 2)
         for p in (y, u, v):
             out += np.clip(np.rint(p), 0, 255).astype(np.uint8).tobytes()
     return bytes(out)
@@ -190,13 +196,15 @@ def main():
     open(clip_wqvga, "wb").write(synth_qcif(seed=2025, w=416, h=240, frames=1))
     clip_cd = os.path.join(a.work, "synth_qcif_cd.yuv")
     open(clip_cd, "wb").write(synth_qcif(seed=2026, chroma_detail=True))
+    clip_cc = os.path.join(a.work, "synth_qcif_cc.yuv")
+    open(clip_cc, "wb").write(synth_qcif(seed=2027, chroma_checker=True))
     exe = a.exe or (None if a.skip_encode else build(a.work, True))
     for name in a.only.split(","):
         cfg, extra = RUNS[name]
         rundir = os.path.join(a.work, name)
         cl = cmdline_for(name)
         if not a.skip_encode:
-            encode(exe, rundir, clip_wqvga if name.startswith("wqvga") else clip_cd if name.startswith("ccalf") else clip,
+            encode(exe, rundir, clip_wqvga if name.startswith("wqvga") else clip_cd if name.startswith("ccalf") else clip_cc if name.startswith("cbdpcm") else clip,
                    cfg, extra, True, cl)
         to_fixture(name, rundir, cfg, extra, cl)
     if a.verify_unpatched:

@@ -750,3 +750,31 @@ def test_gpu_slice_round_trip_at_1080p(engine):
         got = w["out"][int(out_off[k]):int(out_off[k]) + int(w["sizes"][k])]
         assert got.tobytes() == data[k].tobytes(), f"1080p slice {k}"
         assert int(w["num_bins"][k]) == int(d["num_bins"][k]) and w["ctx_out"][k].tobytes() == d["ctx_out"][k].tobytes()
+
+
+# ---- what the VTM fixtures pin: the non-residual contexts the reference's writer actually used in them ----
+WALK_CTX_SETS = [("split_cu_flag", 0, 9), ("split_qt_flag", 9, 6), ("mtt_split_cu_vertical_flag", 15, 5),
+                 ("mtt_split_cu_binary_flag", 20, 4), ("multi_ref_line_idx", 38, 2), ("intra_luma_mpm_flag", 40, 1),
+                 ("intra_luma_planar_flag", 41, 2), ("cclm_mode_flag", 43, 1), ("cclm_mode_idx", 44, 1),
+                 ("intra_chroma_pred_mode", 45, 1), ("mip_flag", 46, 4), ("cu_qp_delta_abs", 50, 2), ("bdpcm_mode", 71, 4),
+                 ("cbf_y", 77, 4), ("cbf_cb", 81, 2), ("cbf_cr", 83, 3), ("sao_merge_flag", 294, 1), ("sao_type_idx", 295, 1),
+                 ("lfnst_idx (separate trees)", 297, 2), ("mts_idx", 312, 4), ("isp_mode", 316, 2),
+                 ("cu_chroma_qp_offset_flag", 325, 1), ("cu_chroma_qp_offset_idx", 326, 1), ("alf_ctb_flag", 332, 9),
+                 ("alf_ctb_filter_alt_idx", 341, 2), ("alf_use_aps_flag", 343, 1), ("cc_alf_ctb_idc", 344, 6),
+                 ("tu_joint_cbcr_residual_flag", 354, 3)]
+# DESIGN.md section 2 names these as reached by generated streams only
+NOT_REACHED_BY_VTM_FIXTURES = {11, 74, 82, 85, 314, 315}
+
+
+def test_fixture_context_coverage_is_what_design_md_says():
+    """Every context the CTU-level walk can select, except the documented handful, is used by at least one call the
+    reference's writer made while producing the fixtures - so the pin of the walk is not narrower than claimed."""
+    hit = np.zeros(512, np.int64)
+    for name in FIXTURES:
+        for s in load_fixture(name)[0]:
+            c = np.asarray(s["cmds"], np.uint32)
+            np.add.at(hit, c[(c >> 29) == 0] & 511, 1)
+    walk = [a + i for _, a, n in WALK_CTX_SETS for i in range(n)]
+    assert len(walk) == 84
+    missing = {k for k in walk if hit[k] == 0}
+    assert missing <= NOT_REACHED_BY_VTM_FIXTURES, f"contexts no fixture reaches: {sorted(missing)}"
