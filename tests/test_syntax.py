@@ -763,7 +763,7 @@ WALK_CTX_SETS = [("split_cu_flag", 0, 9), ("split_qt_flag", 9, 6), ("mtt_split_c
                  ("alf_ctb_filter_alt_idx", 341, 2), ("alf_use_aps_flag", 343, 1), ("cc_alf_ctb_idc", 344, 6),
                  ("tu_joint_cbcr_residual_flag", 354, 3)]
 # DESIGN.md section 2 names these as reached by generated streams only
-NOT_REACHED_BY_VTM_FIXTURES = {11, 74, 82, 85, 314, 315}
+NOT_REACHED_BY_VTM_FIXTURES = {314, 315}  # mts_idx beyond the second bin
 
 
 def test_fixture_context_coverage_is_what_design_md_says():
