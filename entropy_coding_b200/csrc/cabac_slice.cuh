@@ -352,7 +352,8 @@ decode_slice_kernel(const uint8_t *__restrict__ in, const uint64_t *__restrict__
 // K10: writer direction (cabac_encode_slices).  The same walk on an engine that turns the caller's CU / TU / CTU
 // records into the BinEncIf call sequence of the slice - command words with CABAC_CMD_TU markers - which the
 // stream encoder (cabac_encode_stream: all encoder kernels) then codes.  No arithmetic coding here: one warp per
-// slice, two passes (count, then write at the scanned offsets).
+// slice writes into a staging region bounded by the slice's record counts (emitBound), emit_compact_kernel packs
+// the slices at the scan of their word counts.
 // ---------------------------------------------------------------------------
 // Row substreams of the slice being written (WPP: one per CTU row; otherwise the slice itself): what the stream
 // encoder's wavefront mode takes per substream.  cmdOff is relative to the slice's first word until
