@@ -842,7 +842,8 @@ def leg_slice_decode(args, r):
         cpu = _cpu_slice_decode(cpu_items)
     leg = _slice_leg(rows, items)
     if rows_gen:
-        leg["generated"] = {"input": "tests/golden/gen_slices.npz: legal all-intra slices from the stream generator "
+        leg["generated"] = {"input": "tests/golden/gen_slices.npz (+ gen_slices_wpp.npz: the 1080p pictures with WPP, nine row substreams per slice, "
+                                     "written through cabac_encode_slices_wpp_dev): legal all-intra slices from the stream generator "
                                      "(tests/golden/make_gen_slices.py), dense residuals (1.5 bins per coefficient "
                                      "position), replicated on the device; ground truth = the generating walk's records",
                             "points": rows_gen,
@@ -862,11 +863,19 @@ def _slice_decode_generated(r):
     path = os.path.join(ROOT, "tests", "golden", "gen_slices.npz")
     if not os.path.exists(path):
         return None
-    z = np.load(path)
+    z = dict(np.load(path))
+    sets = list(z["sets"])
+    legs = [("hd", 64), ("wqvga", 2048)]
+    wpath = os.path.join(ROOT, "tests", "golden", "gen_slices_wpp.npz")
+    if os.path.exists(wpath):  # the 1080p pictures again with entropy_coding_sync_enabled: nine row substreams each
+        zw = np.load(wpath)
+        z.update({k: zw[k] for k in zw.files if k != "sets"})
+        sets += list(zw["sets"])
+        legs.append(("hdwpp", 64))
     eng, stream, dev = r["eng"], r["stream"], r["dev"]
     rows = []
-    for entry, n in (("hd", 64), ("wqvga", 2048)):
-        cnt_set = next(int(t.split(":")[1]) for t in z["sets"] if t.startswith(entry + ":"))
+    for entry, n in legs:
+        cnt_set = next(int(t.split(":")[1]) for t in sets if t.startswith(entry + ":"))
         base = [(z[f"{entry}{k}_payload"], z[f"{entry}{k}_slice"].view(SLICE_DT)[0], z[f"{entry}{k}_meta"],
                  int(z[f"{entry}{k}_checksum"])) for k in range(cnt_set)]
         params, sps = np.zeros(n, PARAMS_DT), np.zeros(n, SLICE_DT)
@@ -916,27 +925,33 @@ def _slice_decode_generated(r):
         exact = lambda col: np.concatenate([[0], np.cumsum(counts[:, col].astype(np.int64))]).astype(np.uint64)  # noqa: E731
         wp = params.copy()
         wp["flags"] |= SUB_ALIGN
-        out_off = np.concatenate([[0], np.cumsum([(p.size + 79) // 16 * 16 for p in data])]).astype(np.uint64)
         words = bins + 64 * n
-        w = {k: dev_bytes(dev, v) for k, v in (("p", wp), ("cuo", exact(0)), ("tuo", exact(1)), ("oo", out_off))}
+        w = {k: dev_bytes(dev, v) for k, v in (("p", wp), ("cuo", exact(0)), ("tuo", exact(1)))}
         cmd = torch.empty(words, dtype=torch.int32, device=dev)
+        # row substreams: one per slice, or one per CTU row of a WPP slice (each row gets the slice's capacity)
+        row_off = E.CabacEngine.slice_rows(sps)
+        n_rows = int(row_off[-1])
+        per_row = np.concatenate([[(data[j].size + 79) // 16 * 16] * int(row_off[j + 1] - row_off[j]) for j in range(n)])
+        out_off = np.concatenate([[0], np.cumsum(per_row)]).astype(np.uint64)
+        w["oo"], w["ro"] = dev_bytes(dev, out_off), dev_bytes(dev, row_off)
         out = torch.zeros(int(out_off[-1]), dtype=torch.uint8, device=dev)
-        osz = torch.zeros(n, dtype=torch.int32, device=dev)
-        wst = torch.zeros(n, dtype=torch.int32, device=dev)
+        osz = torch.zeros(n_rows, dtype=torch.int32, device=dev)
+        wst = torch.zeros(n_rows, dtype=torch.int32, device=dev)
 
         def enc():
-            eng.encode_slices_dev(w["p"], d["sp"], n, cus2, w["cuo"], tus2, tuf2, w["tuo"], ctus, d["ctu"], co, cmd, words, out,
-                                  w["oo"], osz, wst)
+            eng.encode_slices_wpp_dev(w["p"], d["sp"], n, cus2, w["cuo"], tus2, tuf2, w["tuo"], ctus, d["ctu"], co, cmd, words,
+                                      w["ro"], n_rows, out, w["oo"], osz, wst)
 
         te = _time_passes(stream, enc, warm=1, reps=2)
         assert int(wst.abs().max()) == 0, "generated slices: writer status"
         out_h, osz_h = out.cpu().numpy(), osz.cpu().numpy()
         for j in range(n):
-            a = int(out_off[j])
-            assert out_h[a:a + int(osz_h[j])].tobytes() == data[j].tobytes(), f"generated slice copy {j}: written bytes"
+            got = np.concatenate([out_h[int(out_off[q]):int(out_off[q]) + int(osz_h[q])]
+                                  for q in range(int(row_off[j]), int(row_off[j + 1]))])
+            assert got.tobytes() == data[j].tobytes(), f"generated slice copy {j}: written bytes"
         del cus2, tus2, tuf2, cmd, out, osz, wst, w
-        rows.append({"set": f"{n} x {int(sps[0]['pic_w'])}x{int(sps[0]['pic_h'])}", "substreams": n, "bins": bins,
-                     "encode_ms": te, "encode_mbins_s": bins * r["world"] / te / 1e3,
+        rows.append({"set": f"{n} x {int(sps[0]['pic_w'])}x{int(sps[0]['pic_h'])}" + (" WPP" if entry.endswith("wpp") else ""),
+                     "substreams": n, "row_substreams": n_rows, "bins": bins, "encode_ms": te, "encode_mbins_s": bins * r["world"] / te / 1e3,
                      "bitstream_bytes": off[-1], "coefficients_out": ncoef, "decode_ms": t,
                      "decode_mbins_s": bins * r["world"] / t / 1e3, "hbm_gbs": alg / (t * 1e-3) / 1e9,
                      "hbm_frac": alg / (t * 1e-3) / 1e9 / load_peaks()[0],

@@ -402,6 +402,17 @@ class CabacEngine:
                                                      int(cmd_scratch_words), _dp(out), _dp(out_offsets), _dp(out_sizes),
                                                      _dp(num_bins), _dp(ctx_out), _dp(status)))
 
+    def encode_slices_wpp_dev(self, params, slice_params, n_sub, cus, cu_offsets, tus, tu_flags, tu_offsets, ctus,
+                              ctu_offsets, coeffs, cmd_scratch, cmd_scratch_words, row_offsets, n_rows, out, out_offsets,
+                              out_sizes, status, num_bins=None, ctx_in=None, ctx_out=None):
+        """Device pointers; out_offsets / out_sizes / num_bins / ctx_out / status are per row substream."""
+        self._check(self.lib.cabac_encode_slices_wpp_dev(self.h, _dp(params), _dp(slice_params), n_sub, _dp(cus),
+                                                         _dp(cu_offsets), _dp(tus), _dp(tu_flags), _dp(tu_offsets),
+                                                         _dp(ctus), _dp(ctu_offsets), _dp(coeffs), _dp(ctx_in),
+                                                         _dp(cmd_scratch), int(cmd_scratch_words), _dp(row_offsets),
+                                                         int(n_rows), _dp(out), _dp(out_offsets), _dp(out_sizes),
+                                                         _dp(num_bins), _dp(ctx_out), _dp(status)))
+
     # ---- WPP: CTU rows with context hand-over in one launch (cabac_*_wpp) ----
     def encode_residual_wpp(self, tus, tu_offsets, params, wpp, coeffs, out_offsets, packed=None, ctx_in=None,
                             want_ctx=False, raise_on_status=True):

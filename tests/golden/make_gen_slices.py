@@ -25,11 +25,20 @@ SETS = {  # name: (width, height, slices, split_p, density)
 }
 
 
+# the same picture shape with entropy_coding_sync_enabled: nine CTU-row substreams per slice (gen_slices_wpp.npz)
+SETS_WPP = {"hdwpp": (1920, 1080, 2, 0.45, 0.5)}
+
+
 def main():
     lib = T._host_lib()
+    write(lib, SETS, T.ALL_TOOLS, "gen_slices.npz")
+    write(lib, SETS_WPP, T.ALL_TOOLS | T.SL_WPP, "gen_slices_wpp.npz")
+
+
+def write(lib, sets, tools, fname):
     d = {}
-    for name, (w, h, n, split_p, density) in SETS.items():
-        sp = T.make_slice_params(w, h, 7)
+    for name, (w, h, n, split_p, density) in sets.items():
+        sp = T.make_slice_params(w, h, 7, tools=tools)
         for k in range(n):
             g = T.generate_slice(lib, 7000 + 17 * k + len(name), sp, split_p=split_p, density=density)
             co = g["coeffs"].astype(np.int64).astype(np.uint64)
@@ -41,8 +50,8 @@ def main():
                                          g["coeffs"].size], np.int64)
             d[key + "_checksum"] = np.uint64(cs)
             print(key, g["payload"].size, "bytes", g["num_bins"], "bins", len(g["cus"]), "CUs", len(g["tus"]), "TUs")
-    d["sets"] = np.array([f"{k}:{v[2]}" for k, v in SETS.items()])
-    path = os.path.join(HERE, "gen_slices.npz")
+    d["sets"] = np.array([f"{k}:{v[2]}" for k, v in sets.items()])
+    path = os.path.join(HERE, fname)
     np.savez_compressed(path, **d)
     print(path, os.path.getsize(path), "bytes")
 

@@ -750,6 +750,29 @@ def test_gpu_slice_round_trip_at_1080p(engine):
         got = w["out"][int(out_off[k]):int(out_off[k]) + int(w["sizes"][k])]
         assert got.tobytes() == data[k].tobytes(), f"1080p slice {k}"
         assert int(w["num_bins"][k]) == int(d["num_bins"][k]) and w["ctx_out"][k].tobytes() == d["ctx_out"][k].tobytes()
+    # the same pictures with entropy_coding_sync_enabled (gen_slices_wpp.npz): nine CTU-row substreams per slice, parsed
+    # as one unit, written as rows with the context hand-over on the device
+    zw = np.load(os.path.join(HERE, "golden", "gen_slices_wpp.npz"))
+    data, off = [], [0]
+    for k in range(n):
+        meta = zw[f"hdwpp{k}_meta"]
+        params[k] = (int(meta[0]), int(meta[1]), int(meta[2]) | SUB_TERMINATE | SUB_ALIGN, 0)
+        sps[k] = zw[f"hdwpp{k}_slice"].view(SLICE_DT)[0]
+        data.append(zw[f"hdwpp{k}_payload"])
+        off.append(off[-1] + data[-1].size)
+    assert int(sps[0]["tools"]) & SL_WPP
+    d = engine.decode_slices(np.concatenate(data), np.asarray(off, np.uint64), params, sps, want_ctx=True)
+    rec = _compact(d, n)
+    rows = engine.slice_rows(sps)
+    assert int(rows[-1]) == 18
+    out_off = np.concatenate([[0], np.cumsum([data[k].size + 256 for k in range(n) for _ in range(9)])]).astype(np.uint64)
+    w = engine.encode_slices_wpp(params, sps, _from_dir(rec["cus"]), rec["cu_offsets"], rec["tus"], rec["tu_flags"],
+                                 rec["tu_offsets"], rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off, want_ctx=True)
+    for k in range(n):
+        a, b = int(rows[k]), int(rows[k + 1])
+        got = np.concatenate([w["out"][int(out_off[q]):int(out_off[q]) + int(w["sizes"][q])] for q in range(a, b)])
+        assert got.tobytes() == data[k].tobytes(), f"1080p WPP slice {k}"
+        assert int(w["num_bins"][a:b].sum()) == int(d["num_bins"][k]) and w["ctx_out"][b - 1].tobytes() == d["ctx_out"][k].tobytes()
 
 
 # ---- what the VTM fixtures pin: the non-residual contexts the reference's writer actually used in them ----
