@@ -1049,6 +1049,15 @@ static int encodeSliceRowsHost(cabac_handle *h, const char *what, const cabac_su
   if (row_offsets && (row_offsets[0] != 0 || row_offsets[n_sub] != n_rows)) return badArg(h, what);
   DeviceGuard g(h->device);
   const size_t nCu = cu_offsets[n_sub], nTu = tu_offsets[n_sub], nCtu = ctu_offsets[n_sub], outCap = out_offsets[n_rows];
+  // the kernels read coefficients where the TU records point: with host pointers the slab's size is known, so a record
+  // pointing outside it is refused here (the _dev form trusts coeff_offset like every other _dev entry point)
+  for (size_t t = 0; t < nTu; t++) {
+    const uint64_t area = uint64_t(1) << ((tus[t].log2_w > 6 ? 6 : tus[t].log2_w) + (tus[t].log2_h > 6 ? 6 : tus[t].log2_h));
+    if (tus[t].coeff_offset > n_coeffs || area > n_coeffs - tus[t].coeff_offset) {
+      h->err = std::string(what) + ": TU record " + std::to_string(t) + " points outside the coefficient slab";
+      return CABAC_ERR_ARG;
+    }
+  }
   cabac_substream_params *dP;
   cabac_slice_params *dSp;
   cabac_cu_desc *dCus;

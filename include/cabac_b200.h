@@ -874,7 +874,8 @@ int cabac_decode_slices(cabac_handle *h, const uint8_t *in, const uint64_t *in_o
  * CABAC_SL_WPP slices, whose rows are separate substreams: cabac_encode_slices_wpp), CABAC_SS_BAD_DESC (records that do
  * not describe a legal partitioning of the rectangle, or left-over records) and CABAC_SS_CAPACITY
  * (cmd_scratch too small: nothing is encoded and the call returns CABAC_ERR_SUBSTREAM).
- * The _dev form synchronises the stream twice (it reads the record totals and the total command count back). */
+ * The _dev form synchronises the stream twice (it reads the record totals and the total command count back).
+ * The host-pointer form returns CABAC_ERR_ARG when a TU record's coeff_offset + area exceeds n_coeffs.     */
 int cabac_encode_slices_dev(cabac_handle *h, const cabac_substream_params *params,
                             const cabac_slice_params *slice_params, size_t n_sub,
                             const cabac_cu_desc *cus, const uint64_t *cu_offsets,

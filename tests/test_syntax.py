@@ -714,6 +714,12 @@ def test_gpu_encode_slices_survives_garbage_records(engine):
         assert (w["sizes"].astype(np.int64) <= cap).all()
         flagged += int((w["status"] != 0).sum())
     assert flagged > 0
+    # a TU record pointing outside the coefficient slab is refused by the host-pointer call before anything runs
+    tus = rec["tus"].copy()
+    tus["coeff_offset"][len(tus) // 2] = rec["coeffs"].size - 3
+    with pytest.raises(Exception, match="outside the coefficient slab"):
+        engine.encode_slices_wpp(params, sps, rec["cus"], rec["cu_offsets"], tus, rec["tu_flags"], rec["tu_offsets"], rec["ctus"],
+                                 rec["ctu_offsets"], rec["coeffs"], out_off)
     # and the clean records still code to the payloads afterwards
     w = engine.encode_slices_wpp(params, sps, rec["cus"], rec["cu_offsets"], rec["tus"], rec["tu_flags"], rec["tu_offsets"],
                                  rec["ctus"], rec["ctu_offsets"], rec["coeffs"], out_off)
